@@ -1,0 +1,206 @@
+"""ctypes binding to the in-tree sm_100a kernel library (``deepspeed_b200/ops/lib/libdsb200.so``).
+
+The library exposes a plain C ABI (declared in ``include/dsb200.h``): every launcher takes raw device pointers,
+sizes and a ``cudaStream_t``. Python passes ``tensor.data_ptr()`` and the current torch stream, so the kernels
+run in-order with the surrounding PyTorch work and no torch C++ headers are needed to build (the whole library
+cross-compiles in seconds with ``nvcc -gencode arch=compute_100a,code=sm_100a``).
+
+Replaces the reference's per-op JIT builders (``op_builder/builder.py`` ``OpBuilder.load()``, 5.9 k LoC): there
+is one target architecture, so one shared object.
+
+On a machine with a GPU the library is REQUIRED: a missing/unbuildable library raises instead of silently
+falling back to eager PyTorch.
+"""
+import ctypes
+import os
+import threading
+
+import torch
+
+_LIB = None
+_LIB_ERR = None
+_LOCK = threading.Lock()
+LIB_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib")
+LIB_PATH = os.path.join(LIB_DIR, "libdsb200.so")
+
+c_void_p, c_int, c_int64, c_float, c_double = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float, ctypes.c_double
+
+
+def _load():
+    global _LIB, _LIB_ERR
+    if _LIB is not None or _LIB_ERR is not None:
+        return _LIB
+    with _LOCK:
+        if _LIB is not None:
+            return _LIB
+        try:
+            if not os.path.exists(LIB_PATH):
+                from .builder import build_cuda_library
+                build_cuda_library(verbose=False)
+            _LIB = ctypes.CDLL(LIB_PATH)
+            _declare(_LIB)
+        except Exception as e:  # noqa: BLE001
+            _LIB_ERR = e
+            _LIB = None
+    return _LIB
+
+
+def available():
+    """True when CUDA is usable and the kernel library is loaded. Raises on a GPU box without the library."""
+    if not torch.cuda.is_available():
+        return False
+    lib = _load()
+    if lib is None:
+        raise RuntimeError(f"deepspeed_b200: CUDA device present but kernel library failed to load/build: {_LIB_ERR}")
+    return True
+
+
+def lib():
+    if not available():
+        raise RuntimeError("deepspeed_b200 kernel library requires a CUDA device")
+    return _LIB
+
+
+def _stream():
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return c_void_p(t.data_ptr()) if t is not None else c_void_p(0)
+
+
+_DT = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
+
+
+def _dt(t):
+    return _DT[t.dtype]
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise RuntimeError(f"dsb200 kernel '{what}' failed with code {rc}: {last_error()}")
+
+
+def last_error():
+    try:
+        _LIB.dsb200_last_error.restype = ctypes.c_char_p
+        return _LIB.dsb200_last_error().decode()
+    except Exception:  # noqa: BLE001
+        return "?"
+
+
+def _declare(L):
+    """Argument/return types for every entry point (mirrors include/dsb200.h)."""
+    def sig(name, *argtypes):
+        fn = getattr(L, name, None)
+        if fn is not None:
+            fn.argtypes = list(argtypes)
+            fn.restype = c_int
+    P, I, L64, F, D = c_void_p, c_int, c_int64, c_float, c_double
+    sig("dsb200_sumsq", P, L64, I, P, P)
+    sig("dsb200_multi_sumsq", P, I, P, P)
+    sig("dsb200_multi_tensor_optim", I, P, I, P, I, F, P)
+    sig("dsb200_lamb_step", P, P, P, P, P, L64, I, P, P, F, F, F, F, F, F, F, I, F, F, P)
+    sig("dsb200_rmsnorm_fwd", P, P, P, P, P, I, I, F, I, P)
+    sig("dsb200_rmsnorm_bwd", P, P, P, P, P, P, P, I, I, I, P)
+    sig("dsb200_layernorm_fwd", P, P, P, P, P, P, I, I, F, I, P)
+    sig("dsb200_layernorm_bwd", P, P, P, P, P, P, P, P, P, I, I, I, P)
+    sig("dsb200_rope", P, P, P, I, I, I, I, I, I, I, P)
+    sig("dsb200_swiglu_fwd", P, P, P, L64, I, I, P)
+    sig("dsb200_swiglu_bwd", P, P, P, P, P, L64, I, I, P)
+    sig("dsb200_ce_fwd", P, P, P, P, I, I, I, I, P)
+    sig("dsb200_ce_bwd", P, P, P, P, F, I, I, I, I, P)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# reductions
+# ---------------------------------------------------------------------------------------------------------
+_SCRATCH = {}
+
+
+def _scratch(device, n_float):
+    key = (device.index, torch.cuda.current_stream().cuda_stream)
+    buf = _SCRATCH.get(key)
+    if buf is None or buf.numel() < n_float:
+        buf = torch.empty(max(n_float, 4096), dtype=torch.float32, device=device)
+        _SCRATCH[key] = buf
+    return buf
+
+
+def sumsq(t):
+    """fp32 sum of squares of one contiguous tensor (two-stage deterministic reduction)."""
+    t = t.contiguous()
+    out = torch.empty((), dtype=torch.float32, device=t.device)
+    scratch = _scratch(t.device, 2048)
+    _check(lib().dsb200_sumsq(_ptr(t), t.numel(), _dt(t), _ptr(scratch), _ptr(out), _stream()), "sumsq")
+    return out
+
+
+def multi_tensor_sumsq(tensors):
+    total = None
+    for t in tensors:
+        s = sumsq(t)
+        total = s if total is None else total + s
+    return total
+
+
+# ---------------------------------------------------------------------------------------------------------
+# multi-tensor optimizers
+# ---------------------------------------------------------------------------------------------------------
+CHUNK = 65536
+_KIND = {"adam": 0, "lion": 1, "adagrad": 2, "sgd": 3}
+
+
+class ChunkTable:
+    """Device-resident table of work chunks: (p, g, m, v, lp, n, group, gdt|ldt|sdt)."""
+
+    def __init__(self, dev_table, n_chunks, keepalive):
+        self.dev_table, self.n_chunks, self.keepalive = dev_table, n_chunks, keepalive
+
+
+def build_chunk_table(items, states):
+    import numpy as np
+    rows = []
+    for (gi, p, g, lp), sts in zip(items, states):
+        assert p.dtype == torch.float32 or p.dtype in _DT
+        n = p.numel()
+        m = sts[0]
+        v = sts[1] if len(sts) > 1 else None
+        esz = {0: 4, 1: 2, 2: 2}
+        pdt, gdt = _dt(p), _dt(g)
+        sdt = _dt(m)
+        ldt = _dt(lp) if lp is not None else 0
+        for off in range(0, n, CHUNK):
+            cnt = min(CHUNK, n - off)
+            rows.append((p.data_ptr() + off * esz[pdt], g.data_ptr() + off * esz[gdt], m.data_ptr() + off * esz[sdt],
+                         (v.data_ptr() + off * esz[sdt]) if v is not None else 0,
+                         (lp.data_ptr() + off * esz[ldt]) if lp is not None else 0, cnt, gi,
+                         pdt | (gdt << 4) | (sdt << 8) | (ldt << 12)))
+    arr = np.zeros(len(rows), dtype=np.dtype([("p", "u8"), ("g", "u8"), ("m", "u8"), ("v", "u8"), ("lp", "u8"),
+                                              ("n", "i4"), ("group", "i4"), ("dt", "i4"), ("pad", "i4")]))
+    for i, r in enumerate(rows):
+        arr[i] = r + (0, )
+    host = torch.from_numpy(arr.view(np.uint8).copy())
+    dev = host.to(items[0][1].device)
+    return ChunkTable(dev, len(rows), [items, states])
+
+
+def multi_tensor_optim(kind, table, hyper, grad_scale):
+    import numpy as np
+    assert len(hyper) <= 64, "at most 64 param groups per launch"
+    h = np.zeros((len(hyper), 8), dtype=np.float32)
+    for i, d in enumerate(hyper):
+        h[i] = (d["lr"], d["beta1"], d["beta2"], d["eps"], d["wd"], d["bc1"], d["bc2"], float(d["mode"]))
+    _check(
+        lib().dsb200_multi_tensor_optim(_KIND[kind], _ptr(table.dev_table), table.n_chunks,
+                                        h.ctypes.data_as(c_void_p), len(hyper), float(grad_scale), _stream()),
+        f"multi_tensor_{kind}")
+
+
+def lamb_step(p, g, m, v, lp, h, coeffs_out):
+    scratch = _scratch(p.device, 4096 + 8)
+    _check(
+        lib().dsb200_lamb_step(_ptr(p), _ptr(g), _ptr(m), _ptr(v), _ptr(lp), p.numel(), (_dt(lp) if lp is not None else 0),
+                               _ptr(scratch), _ptr(scratch[4096:]), h["lr"], h["beta1"], h["beta2"], h["eps"], h["wd"],
+                               h["bc1"], h["bc2"], int(h["mode"]), h["max_coeff"], h["min_coeff"], _stream()), "lamb")
+    coeffs_out.append(scratch[4096 + 2])

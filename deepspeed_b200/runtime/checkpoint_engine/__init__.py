@@ -1,0 +1,178 @@
+"""Checkpoint engines: torch (sync), fast (pinned double-buffer native writer), decoupled (writer process).
+
+Interface follows reference ``runtime/checkpoint_engine/checkpoint_engine.py:21-63``
+(``create/save/load/commit/makedirs/is_data_parallel_writer/is_decoupled``); factory ``utils.py:15``.
+"""
+import multiprocessing as mp
+import os
+import queue as _q
+
+import torch
+
+from ...utils.logging import log_dist, logger
+
+
+class CheckpointCommitInfo:
+
+    def __init__(self, tag, save_dir, save_latest):
+        self.tag, self.save_dir, self.save_latest = tag, save_dir, save_latest
+
+
+class CheckpointEngine:
+
+    def __init__(self, config_params=None):
+        self.name = None
+        self.config_params = config_params
+
+    def create(self, info):
+        log_dist(f"[{type(self).__name__}] Checkpoint {getattr(info, 'tag', info)} is about to be saved!", [0])
+
+    def save(self, state_dict, path):
+        raise NotImplementedError
+
+    def load(self, path, map_location=None):
+        return torch.load(path, map_location=map_location, weights_only=False)
+
+    def commit(self, info):
+        return True
+
+    def makedirs(self, path, exist_ok=False):
+        os.makedirs(path, exist_ok=exist_ok)
+
+    def is_data_parallel_writer(self, dp_rank):
+        return dp_rank == 0
+
+    def is_decoupled(self):
+        return False
+
+    def set_commit_info(self, info):
+        self._info = info
+
+    def get_commit_info(self):
+        return getattr(self, "_info", None)
+
+    def cleanup(self):
+        pass
+
+    def preserves_storage_sharing(self):
+        return True
+
+
+class TorchCheckpointEngine(CheckpointEngine):
+
+    def save(self, state_dict, path):
+        torch.save(state_dict, path)
+
+    def commit(self, info):
+        logger.info(f"[Torch] Checkpoint {getattr(info, 'tag', info)} is ready now!")
+        return True
+
+
+class FastCheckpointEngine(CheckpointEngine):
+    """Serialises with torch's pickle protocol into a pinned double-buffered native writer
+    (:class:`deepspeed_b200.io.FastFileWriter`, O_DIRECT + worker threads)."""
+
+    def __init__(self, config_params=None, dp_writer=True):
+        super().__init__(config_params)
+        from ...io.fast_file_writer import FastFileWriter, FastFileWriterConfig
+        self._writer_cls, self._cfg_cls = FastFileWriter, FastFileWriterConfig
+        w = getattr(config_params, "writer", None)
+        self.io_buffer_size = getattr(w, "io_buffer_size", 1 << 28) if w else 1 << 28
+        self.double = getattr(w, "io_buffer_double", True) if w else True
+
+    def save(self, state_dict, path):
+        writer = self._writer_cls(path, self._cfg_cls(io_buffer_size=self.io_buffer_size, double_buffer=self.double))
+        torch.save(state_dict, writer, _use_new_zipfile_serialization=False)
+        writer.close()
+
+
+def _writer_main(q, done):
+    while True:
+        item = q.get()
+        if item is None:
+            break
+        kind, payload = item
+        if kind == "save":
+            sd, path = payload
+            torch.save(sd, path)
+        elif kind == "commit":
+            save_dir, tag, save_latest = payload
+            if save_latest:
+                with open(os.path.join(save_dir, "latest"), "w") as f:
+                    f.write(tag)
+            done.put(tag)
+
+
+class DecoupledCheckpointEngine(CheckpointEngine):
+    """Hands CPU copies of the state to a separate writer *process*; commit is confirmed at the next GAS
+    boundary (reference ``decoupled_checkpoint_engine.py``; engine.py:3452-3453)."""
+
+    def __init__(self, config_params=None):
+        super().__init__(config_params)
+        ctx = mp.get_context("spawn")
+        self.q, self.done = ctx.Queue(), ctx.Queue()
+        self.proc = ctx.Process(target=_writer_main, args=(self.q, self.done), daemon=True)
+        self.proc.start()
+        self.pending = []
+
+    def is_decoupled(self):
+        return True
+
+    def _alive(self):
+        if not self.proc.is_alive():
+            raise RuntimeError("decoupled checkpoint writer process died")
+
+    @staticmethod
+    def _to_cpu(obj):
+        if torch.is_tensor(obj):
+            return obj.detach().cpu().clone()
+        if isinstance(obj, dict):
+            return type(obj)((k, DecoupledCheckpointEngine._to_cpu(v)) for k, v in obj.items())
+        if isinstance(obj, (list, tuple)):
+            return type(obj)(DecoupledCheckpointEngine._to_cpu(v) for v in obj)
+        return obj
+
+    def save(self, state_dict, path):
+        self._alive()
+        self.q.put(("save", (self._to_cpu(state_dict), path)))
+
+    def commit(self, info):
+        self._alive()
+        self.q.put(("commit", (info.save_dir, info.tag, info.save_latest)))
+        self.pending.append(info.tag)
+        return True
+
+    def commit_pending(self, block=False):
+        while self.pending:
+            try:
+                tag = self.done.get(block=block, timeout=600 if block else None)
+            except _q.Empty:
+                return
+            if tag in self.pending:
+                self.pending.remove(tag)
+                logger.info(f"[Decoupled] Checkpoint {tag} is ready now!")
+
+    def cleanup(self):
+        try:
+            self.commit_pending(block=True)
+            self.q.put(None)
+            self.proc.join(timeout=30)
+        except Exception:
+            pass
+
+
+def create_checkpoint_engine(config):
+    ck = getattr(config, "checkpoint_config", None)
+    w = getattr(ck, "writer", None) if ck is not None else None
+    kind = (getattr(w, "type", "torch") or "torch").lower() if w is not None else "torch"
+    if w is not None and getattr(w, "decoupled", False):
+        kind = "decoupled"
+    if kind == "fast":
+        try:
+            return FastCheckpointEngine(ck)
+        except Exception as e:
+            logger.warning(f"FastCheckpointEngine unavailable ({e}); falling back to torch")
+            return TorchCheckpointEngine(ck)
+    if kind == "decoupled":
+        return DecoupledCheckpointEngine(ck)
+    return TorchCheckpointEngine(ck)

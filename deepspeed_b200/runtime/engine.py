@@ -1,0 +1,898 @@
+"""``DeepSpeedEngine``: nn.Module wrapper that owns config, groups, the ZeRO optimizer and fwd/bwd/step.
+
+Public surface follows the reference ``runtime/engine.py:252-5863`` (ctor :255-533, ``forward`` :2801,
+``backward`` :3205, ``step`` :3405, ``_take_model_step`` :3326, ``no_sync`` :3033, ``save_checkpoint`` :4749,
+``load_checkpoint`` :4271, ``save_16bit_model`` :5567, ~140 config accessors :989-1482). Architecture differs:
+the engine is small and delegates all sharding to one :class:`ZeroShardedOptimizer` (stages 0-3); there is no
+accelerator abstraction (CUDA/B200, with CPU+gloo only as the plumbing/test configuration).
+"""
+import contextlib
+import os
+from collections import OrderedDict
+from typing import Optional
+
+import torch
+from torch.nn.modules import Module
+
+from .. import comm as dist
+from ..config import DeepSpeedConfig
+from ..monitor.monitor import MonitorMaster
+from ..utils import groups
+from ..utils.logging import log_dist, logger
+from ..utils.memory import see_memory_usage
+from ..utils.nvtx import instrument_w_nvtx
+from ..utils.timer import (BACKWARD_GLOBAL_TIMER, BACKWARD_INNER_GLOBAL_TIMER, BACKWARD_INNER_MICRO_TIMER,
+                           BACKWARD_MICRO_TIMER, BACKWARD_REDUCE_GLOBAL_TIMER, BACKWARD_REDUCE_MICRO_TIMER,
+                           FORWARD_GLOBAL_TIMER, FORWARD_MICRO_TIMER, STEP_GLOBAL_TIMER, STEP_MICRO_TIMER, NoopTimer,
+                           SynchronizedWallClockTimer, ThroughputTimer)
+from . import lr_schedules
+from .dataloader import DeepSpeedDataLoader
+from .zero.sharded_optimizer import ZeroShardedOptimizer
+
+MEMORY_OPT_ALLREDUCE_SIZE = 500000000
+DeepSpeedOptimizerCallable = None
+DeepSpeedSchedulerCallable = None
+
+
+class EngineTimers:
+    """Names of the wall-clock timers the engine drives (reference engine.py:198-234)."""
+
+    def __init__(self, enable_micro_timers, enable_global_timers):
+        self.forward_timers = [FORWARD_MICRO_TIMER] if enable_micro_timers else []
+        self.backward_timers = [BACKWARD_MICRO_TIMER] if enable_micro_timers else []
+        self.backward_inner_timers = [BACKWARD_INNER_MICRO_TIMER] if enable_micro_timers else []
+        self.backward_reduce_timers = [BACKWARD_REDUCE_MICRO_TIMER] if enable_micro_timers else []
+        self.step_timers = [STEP_MICRO_TIMER] if enable_micro_timers else []
+        self.micro_timers = self.forward_timers + self.backward_timers + self.backward_inner_timers + \
+            self.backward_reduce_timers + self.step_timers
+        self.global_timers = []
+        if enable_global_timers:
+            self.forward_timers += [FORWARD_GLOBAL_TIMER]
+            self.backward_timers += [BACKWARD_GLOBAL_TIMER]
+            self.backward_inner_timers += [BACKWARD_INNER_GLOBAL_TIMER]
+            self.backward_reduce_timers += [BACKWARD_REDUCE_GLOBAL_TIMER]
+            self.step_timers += [STEP_GLOBAL_TIMER]
+            self.global_timers = [FORWARD_GLOBAL_TIMER, BACKWARD_GLOBAL_TIMER, BACKWARD_INNER_GLOBAL_TIMER,
+                                  BACKWARD_REDUCE_GLOBAL_TIMER, STEP_GLOBAL_TIMER]
+
+
+def _split_half_float_double(tensors):
+    buckets = {}
+    for t in tensors:
+        buckets.setdefault(t.dtype, []).append(t)
+    return list(buckets.values())
+
+
+class DeepSpeedEngine(Module):
+
+    def __init__(self, args=None, model=None, optimizer=None, model_parameters=None, training_data=None,
+                 lr_scheduler=None, mpu=None, dist_init_required=None, collate_fn=None, config=None,
+                 config_class: Optional[DeepSpeedConfig] = None, mesh_device=None, dont_change_device=False):
+        super().__init__()
+        self.dont_change_device = dont_change_device
+        self.client_optimizer = optimizer
+        self.client_lr_scheduler = lr_scheduler
+        self.training_data = training_data
+        self.collate_fn = collate_fn
+        self.mpu = mpu
+        self.mesh_device = mesh_device
+        self.global_steps = 0
+        self.global_samples = 0
+        self.micro_steps = 0
+        self.skipped_steps = 0
+        self.gradient_average = True
+        self.warn_unscaled_loss = True
+        self.loaded_checkpoint_mp_world_size = None
+        self.loaded_checkpoint_dp_world_size = None
+        self.enable_backward_allreduce = True
+        self.inside_no_sync_ctxt = False
+        self._is_gradient_accumulation_boundary = None
+        self.scale_wrt_gas = None
+        self.losses = None
+        self._step_applied = False
+        self._global_grad_norm = None
+        self.checkpoint_engine = None
+        self.optimizer = None
+        self.basic_optimizer = None
+        self.lr_scheduler = None
+        self.has_moe_layers = False
+        self.num_experts = []
+        self.gate_modules = []
+        self.moe_layers = []
+        self._running_engine_backward = False
+        self.flops_profiler = None
+        self._config = config_class if config_class is not None else DeepSpeedConfig(config, mpu, mesh_device)
+        if dist_init_required is not False and not dist.is_initialized():
+            dist.init_distributed(config=self._config)
+        dist.configure(self._config)
+
+        self._configure_parallel_groups()
+        self.module = model
+        self._configure_distributed_model(model)
+        self.monitor = MonitorMaster(self._config.monitor_config)
+        self.timers = SynchronizedWallClockTimer() if self.wall_clock_breakdown() else NoopTimer()
+        self.engine_timers = EngineTimers(enable_micro_timers=self.wall_clock_breakdown(),
+                                          enable_global_timers=self.wall_clock_breakdown() or
+                                          self._config.flops_profiler_config.enabled)
+        self.tput_timer = ThroughputTimer(self._config.timers_config.throughput,
+                                          batch_size=self.train_batch_size(),
+                                          steps_per_output=self.steps_per_print(),
+                                          monitor_memory=False)
+        if self._config.flops_profiler_config.enabled:
+            from ..profiling.flops_profiler import FlopsProfiler
+            self.flops_profiler = FlopsProfiler(self.module, self, self._config.flops_profiler_config.recompute_fwd_factor)
+        self.training_dataloader = self.deepspeed_io(training_data) if training_data is not None else None
+
+        if model_parameters is None:
+            model_parameters = [p for p in self.module.parameters() if p.requires_grad]
+        has_optimizer = optimizer is not None or self._config.optimizer_name is not None
+        if has_optimizer:
+            self._configure_optimizer(optimizer, model_parameters)
+            self._configure_lr_scheduler()
+        elif self.zero_optimization_stage() == 3:
+            # inference / eval with partitioned params: params stay sharded, no optimizer state
+            self._configure_zero_inference(model_parameters)
+        self._configure_checkpointing()
+        self._configure_aux_features()
+        if self.global_rank == 0 and self._config.dump_state:
+            self._config.print("DeepSpeedEngine configuration")
+        see_memory_usage("DeepSpeedEngine: after init", force=self.memory_breakdown())
+
+    # ------------------------------------------------------------------ setup ------------------
+    def _configure_parallel_groups(self):
+        cfg = self._config
+        tp = max(1, cfg.tensor_parallel_config.autotp_size or cfg.tensor_parallel_config.tensor_parallel.tp_size)
+        sp = cfg.sequence_parallel_size
+        groups.initialize(tp_size=tp, sp_size=sp, mpu=self.mpu)
+        self.global_rank = dist.get_rank()
+        self.world_size = dist.get_world_size()
+        self.local_rank = dist.get_local_rank()
+        self.data_parallel_group = groups._get_data_parallel_group()
+        self.dp_world_size = groups._get_data_parallel_world_size()
+        self.mp_world_size = groups._get_model_parallel_world_size()
+        self.sequence_parallel_size = groups._get_sequence_parallel_world_size()
+        self.seq_data_parallel_group = groups._get_sequence_data_parallel_group()
+        self.seq_dp_world_size = groups._get_sequence_data_parallel_world_size()
+        self.seq_dp_rank = groups._get_sequence_data_parallel_rank()
+        self.model_parallel_group = groups._get_model_parallel_group() if self.mp_world_size > 1 else None
+        if torch.cuda.is_available():
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        else:
+            self.device = torch.device("cpu")
+
+    def _model_dtype(self):
+        if self._config.bfloat16_enabled:
+            return torch.bfloat16
+        if self._config.fp16_enabled:
+            return torch.float16
+        return torch.float32
+
+    def _configure_distributed_model(self, model):
+        dt = self._model_dtype()
+        self.communication_data_type = self._config.communication_data_type or dt
+        zero_init_params = any(hasattr(p, "ds_init_shard") for p in model.parameters())
+        if self._config.tensor_parallel_config.autotp_size > 1:
+            from ..parallel.tp import apply_autotp
+            apply_autotp(model, self._config.tensor_parallel_config, groups._get_model_parallel_group())
+        if self._config.expert_parallel_config.enabled:
+            from ..parallel.auto_ep import apply_autoep
+            apply_autoep(model, self._config.expert_parallel_config)
+        if not (self._config.torch_autocast_config.enabled):
+            for p in model.parameters():
+                if p.is_floating_point() and p.dtype != dt and not hasattr(p, "ds_init_shard"):
+                    p.data = p.data.to(dt)
+        if not self.dont_change_device and not zero_init_params:
+            model.to(self.device)
+        elif not self.dont_change_device:
+            for name, buf in list(model.named_buffers()):
+                if buf is not None and buf.device != self.device:
+                    from .zero.init_context import _set_buffer
+                    _set_buffer(model, name, buf.to(self.device))
+        # MoE discovery (reference engine.py:1775-1792)
+        from ..moe.layer import MoE
+        for m in model.modules():
+            if isinstance(m, MoE):
+                self.has_moe_layers = True
+                self.num_experts.append(m.num_experts)
+                self.moe_layers.append(m)
+        if self.has_moe_layers:
+            for m in self.moe_layers:
+                m.set_deepspeed_parallelism(self._config.use_data_before_expert_parallel_)
+        if not zero_init_params and self.dp_world_size * self.sequence_parallel_size > 1:
+            self._broadcast_model()
+
+    def _broadcast_model(self):
+        """Make every DP replica start from rank-0's weights (expert params over their expert-DP group)."""
+        src_dp = dist.get_global_rank(self.seq_data_parallel_group, 0)
+        for p in self.module.parameters():
+            if hasattr(p, "allreduce") and not p.allreduce and hasattr(p, "group_name"):
+                g = groups._get_expert_data_parallel_group(p.group_name)
+                if groups._get_expert_data_parallel_world_size(p.group_name) > 1:
+                    dist.broadcast(p.data, groups._get_expert_broadcast_src_rank(p.group_name), group=g)
+            elif torch.is_tensor(p) and p.numel() > 0:
+                dist.broadcast(p.data, src_dp, group=self.seq_data_parallel_group)
+        for b in self.module.buffers():
+            if b is not None and b.numel() > 0 and b.is_floating_point():
+                dist.broadcast(b.data, src_dp, group=self.seq_data_parallel_group)
+
+    # ------------------------------------------------------------------ optimizer --------------
+    def _configure_basic_optimizer(self, model_parameters):
+        from ..ops import optimizers as O
+        name = self._config.optimizer_name
+        params = dict(self._config.optimizer_params)
+        if "max_grad_norm" in params and name not in ("lamb", ):
+            params.pop("max_grad_norm")
+        lname = (name or "").lower()
+        offload = self.zero_cpu_offload()
+        if lname in ("adam", "adamw"):
+            torch_adam = params.pop("torch_adam", False)
+            adam_w_mode = params.pop("adam_w_mode", True)
+            effective_w = adam_w_mode or lname == "adamw"
+            if torch_adam:
+                cls = torch.optim.AdamW if effective_w else torch.optim.Adam
+                return cls(model_parameters, **params)
+            if offload:
+                from ..ops.cpu_optimizers import DeepSpeedCPUAdam
+                return DeepSpeedCPUAdam(model_parameters, **params, adamw_mode=effective_w)
+            return O.FusedAdam(model_parameters, **params, adam_w_mode=effective_w)
+        if lname == "lamb":
+            return O.FusedLamb(model_parameters, **params)
+        if lname == "lion":
+            if offload:
+                from ..ops.cpu_optimizers import DeepSpeedCPULion
+                return DeepSpeedCPULion(model_parameters, **params)
+            return O.FusedLion(model_parameters, **params)
+        if lname == "adagrad":
+            if offload:
+                from ..ops.cpu_optimizers import DeepSpeedCPUAdagrad
+                return DeepSpeedCPUAdagrad(model_parameters, **params)
+            return O.FusedAdagrad(model_parameters, **params)
+        if lname == "sgd":
+            return O.FusedSGD(model_parameters, **params)
+        if lname == "muon":
+            from ..ops.muon import Muon
+            return Muon(model_parameters, **params)
+        if lname in ("onebitadam", "zerooneadam", "onebitlamb"):
+            from ..runtime.onebit import build_onebit_optimizer
+            return build_onebit_optimizer(lname, model_parameters, params, self)
+        if hasattr(torch.optim, name or ""):
+            return getattr(torch.optim, name)(model_parameters, **params)
+        raise ValueError(f"Unknown optimizer type '{name}'")
+
+    def _configure_optimizer(self, client_optimizer, model_parameters):
+        if client_optimizer is None:
+            basic = self._configure_basic_optimizer(model_parameters)
+            log_dist(f"Using DeepSpeed Optimizer param name {self._config.optimizer_name} as basic optimizer", [0])
+        elif isinstance(client_optimizer, torch.optim.Optimizer):
+            basic = client_optimizer
+            log_dist("Using client Optimizer as basic optimizer", [0])
+        elif callable(client_optimizer):
+            basic = client_optimizer(model_parameters)
+            log_dist("Using client callable to create basic optimizer", [0])
+        else:
+            raise TypeError(f"unsupported optimizer argument {type(client_optimizer)}")
+        self.basic_optimizer = basic
+        zc = self._config.zero_config
+        dt = self._model_dtype()
+        fused = zc.fused_collectives
+        self.optimizer = ZeroShardedOptimizer(
+            self.module, basic, stage=self.zero_optimization_stage(), dp_group=self.seq_data_parallel_group,
+            dp_world=self.seq_dp_world_size, dp_rank=self.seq_dp_rank, sp_size=self.sequence_parallel_size,
+            mp_group=self.model_parallel_group, reduce_bucket_size=zc.reduce_bucket_size,
+            overlap_comm=bool(zc.overlap_comm), contiguous_gradients=zc.contiguous_gradients,
+            reduce_scatter=zc.reduce_scatter, clip_grad=self.gradient_clipping(), dtype=dt,
+            fp16_config=self._config.float16_config if self._config.fp16_enabled else None,
+            grad_accum_dtype=self._grad_accum_dtype(), communication_data_type=self._config.communication_data_type,
+            gradient_accumulation_steps=self.gradient_accumulation_steps(),
+            gradient_predivide_factor=self._config.gradient_predivide_factor,
+            gradient_average=(self._config.gradient_allreduce_op == "mean"),
+            master_weights_in_lp=(self._config.bfloat16_config.bf16_master_weights_and_grads
+                                  or self._config.fp16_master_weights_and_gradients),
+            offload_optimizer=zc.offload_optimizer, offload_param=zc.offload_param, unit_max_numel=zc.unit_max_numel,
+            param_persistence_threshold=zc.param_persistence_threshold, prefetch=zc.prefetch_bucket_size > 0,
+            mics_shard_size=zc.mics_shard_size, hpz_size=zc.zero_hpz_partition_size,
+            quantized_weights=zc.zero_quantized_weights, quantized_gradients=zc.zero_quantized_gradients,
+            leaf_modules=self._leaf_module_classes(), elastic_checkpoint=zc.elastic_checkpoint, timers=self.timers,
+            fused_collectives=fused, ignore_unused_parameters=zc.ignore_unused_parameters)
+
+    def _configure_zero_inference(self, model_parameters):
+        dummy = torch.optim.SGD([p for p in self.module.parameters()], lr=0.0)
+        self._configure_optimizer(dummy, None)
+        self._zero_inference = True
+
+    def _leaf_module_classes(self):
+        zc = self._config.zero_config.leaf_module
+        names = set(zc.classes)
+        out = []
+        for m in self.module.modules():
+            if getattr(m, "_z3_leaf", False) or f"{type(m).__module__}.{type(m).__name__}" in names \
+                    or type(m).__name__ in names:
+                if type(m) not in out:
+                    out.append(type(m))
+        return tuple(out)
+
+    def _grad_accum_dtype(self):
+        name = self._config.grad_accum_dtype
+        if name is None:
+            return None
+        from ..config.config import _dtype_from_str
+        return _dtype_from_str(name)
+
+    def _configure_lr_scheduler(self):
+        if self.client_lr_scheduler is not None:
+            if callable(self.client_lr_scheduler) and not hasattr(self.client_lr_scheduler, "step"):
+                self.lr_scheduler = self.client_lr_scheduler(self.basic_optimizer)
+            else:
+                self.lr_scheduler = self.client_lr_scheduler
+        elif self._config.scheduler_name is not None:
+            self.lr_scheduler = lr_schedules.build_lr_scheduler(self._config.scheduler_name, self.basic_optimizer,
+                                                                self._config.scheduler_params)
+        log_dist(f"DeepSpeed LR Scheduler = {self.lr_scheduler}", [0])
+
+    def _configure_checkpointing(self):
+        from .checkpoint_engine import create_checkpoint_engine
+        self.checkpoint_engine = create_checkpoint_engine(self._config)
+        dp_rank = self.seq_dp_rank
+        # who writes what (reference engine.py:1574-1597)
+        self.save_non_zero_checkpoint = (dp_rank == 0) or self.zero_optimization_partition_weights()
+        self.save_zero_checkpoint = self.zero_optimization() or self.bfloat16_enabled()
+
+    def _configure_aux_features(self):
+        cfg = self._config
+        self.progressive_layer_drop = None
+        if cfg.pld_enabled:
+            from .progressive_layer_drop import ProgressiveLayerDrop
+            self.progressive_layer_drop = ProgressiveLayerDrop(**cfg.pld_params)
+        self.curriculum_scheduler_legacy = None
+        if cfg.curriculum_enabled_legacy:
+            from .data_pipeline.curriculum_scheduler import CurriculumScheduler
+            self.curriculum_scheduler_legacy = CurriculumScheduler(cfg.curriculum_params_legacy)
+        self.eigenvalue = None
+        if cfg.eigenvalue_enabled:
+            from .eigenvalue import Eigenvalue
+            ec = dict(cfg.eigenvalue_config)
+            ec.pop("enabled", None)
+            self.eigenvalue = Eigenvalue(**ec)
+        if cfg.activation_checkpointing_config is not None:
+            from . import activation_checkpointing as ac
+            ac.configure(self.mpu, deepspeed_config=cfg)
+        self.compression_scheduler = None
+        if cfg.compression_config:
+            from ..compression.scheduler import compression_scheduler
+            self.compression_scheduler = compression_scheduler(self.module, cfg.compression_config)
+
+    # ------------------------------------------------------------------ dataloader -------------
+    def deepspeed_io(self, dataset, batch_size=None, route="train", pin_memory=True, data_sampler=None,
+                     collate_fn=None, num_local_io_workers=None):
+        if batch_size is None:
+            batch_size = self.train_micro_batch_size_per_gpu()
+        if collate_fn is None:
+            collate_fn = self.collate_fn
+        dp_world = self.dp_world_size
+        dp_rank = groups._get_data_parallel_rank()
+        if self.mpu is not None and hasattr(self.mpu, "get_data_parallel_rank"):
+            dp_world, dp_rank = self.mpu.get_data_parallel_world_size(), self.mpu.get_data_parallel_rank()
+        return DeepSpeedDataLoader(dataset=dataset, batch_size=batch_size, pin_memory=pin_memory and
+                                   torch.cuda.is_available(), collate_fn=collate_fn, local_rank=self.local_rank,
+                                   tput_timer=None, num_local_io_workers=num_local_io_workers,
+                                   data_sampler=data_sampler, data_parallel_world_size=dp_world,
+                                   data_parallel_rank=dp_rank, dataloader_drop_last=self._config.dataloader_drop_last)
+
+    # ------------------------------------------------------------------ accessors --------------
+    def train_batch_size(self):
+        return self._config.train_batch_size
+
+    def train_micro_batch_size_per_gpu(self):
+        return self._config.train_micro_batch_size_per_gpu
+
+    def gradient_accumulation_steps(self):
+        return self._config.gradient_accumulation_steps
+
+    def set_train_batch_size(self, train_batch_size):
+        if train_batch_size % (self.train_micro_batch_size_per_gpu() * self.dp_world_size) != 0:
+            raise ValueError("Train batch size must be divisible by micro-batch data parallelism")
+        self._config.gradient_accumulation_steps = train_batch_size // (self.train_micro_batch_size_per_gpu() *
+                                                                        self.dp_world_size)
+        self._config.train_batch_size = train_batch_size
+
+    def set_train_micro_batch_size(self, micro_batch_size):
+        self._config.train_batch_size = micro_batch_size * self.gradient_accumulation_steps() * self.dp_world_size
+        self._config.train_micro_batch_size_per_gpu = micro_batch_size
+
+    def set_gradient_accumulation_steps(self, gas):
+        self._config.gradient_accumulation_steps = gas
+        self._config.train_batch_size = self.train_micro_batch_size_per_gpu() * gas * self.dp_world_size
+
+    def steps_per_print(self):
+        return self._config.steps_per_print
+
+    def zero_optimization(self):
+        return self._config.zero_enabled
+
+    def zero_optimization_stage(self):
+        return self._config.zero_optimization_stage
+
+    def zero_optimization_partition_gradients(self):
+        return self.zero_optimization_stage() >= 2
+
+    def zero_optimization_partition_weights(self):
+        return self.zero_optimization_stage() >= 3
+
+    def zero_cpu_offload(self):
+        oc = self._config.zero_config.offload_optimizer
+        return oc is not None and str(oc.device) in ("cpu", "nvme", "OffloadDeviceEnum.cpu", "OffloadDeviceEnum.nvme")
+
+    def zero_offload_param(self):
+        return self._config.zero_config.offload_param
+
+    def zero_reduce_bucket_size(self):
+        return self._config.zero_config.reduce_bucket_size
+
+    def zero_allgather_bucket_size(self):
+        return self._config.zero_config.allgather_bucket_size
+
+    def zero_overlap_comm(self):
+        return self._config.zero_config.overlap_comm
+
+    def zero_contiguous_gradients(self):
+        return self._config.zero_config.contiguous_gradients
+
+    def zero_reduce_scatter(self):
+        return self._config.zero_config.reduce_scatter
+
+    def zero_sub_group_size(self):
+        return self._config.zero_config.sub_group_size
+
+    def zero_prefetch_bucket_size(self):
+        return self._config.zero_config.prefetch_bucket_size
+
+    def zero_param_persistence_threshold(self):
+        return self._config.zero_config.param_persistence_threshold
+
+    def zero_max_live_parameters(self):
+        return self._config.zero_config.max_live_parameters
+
+    def zero_max_reuse_distance(self):
+        return self._config.zero_config.max_reuse_distance
+
+    def zero_gather_16bit_weights_on_model_save(self):
+        return self._config.zero_config.gather_16bit_weights_on_model_save
+
+    def zero_elastic_checkpoint(self):
+        return self._config.zero_config.elastic_checkpoint
+
+    def zero_hpz_partition_size(self):
+        return self._config.zero_config.zero_hpz_partition_size
+
+    def zero_quantized_weights(self):
+        return self._config.zero_config.zero_quantized_weights
+
+    def zero_quantized_gradients(self):
+        return self._config.zero_config.zero_quantized_gradients
+
+    def zero_load_from_fp32_weights(self):
+        return self._config.zero_config.load_from_fp32_weights
+
+    def fp16_enabled(self):
+        return self._config.fp16_enabled
+
+    def bfloat16_enabled(self):
+        return self._config.bfloat16_enabled
+
+    def amp_enabled(self):
+        return self._config.amp_enabled
+
+    def loss_scale(self):
+        return self._config.loss_scale
+
+    def dynamic_loss_scale(self):
+        return self._config.loss_scale == 0
+
+    def gradient_clipping(self):
+        return self._config.gradient_clipping
+
+    def gradient_predivide_factor(self):
+        return self._config.gradient_predivide_factor
+
+    def postscale_gradients(self):
+        return not self._config.prescale_gradients
+
+    def wall_clock_breakdown(self):
+        return self._config.wall_clock_breakdown
+
+    def memory_breakdown(self):
+        return self._config.memory_breakdown
+
+    def sparse_gradients_enabled(self):
+        return self._config.sparse_gradients_enabled
+
+    def optimizer_name(self):
+        return self.client_optimizer.__class__.__name__ if self.client_optimizer else self._config.optimizer_name
+
+    def optimizer_params(self):
+        return self._config.optimizer_params
+
+    def scheduler_name(self):
+        return self._config.scheduler_name
+
+    def scheduler_params(self):
+        return self._config.scheduler_params
+
+    def flops_profiler_enabled(self):
+        return self._config.flops_profiler_config.enabled
+
+    def flops_profiler_profile_step(self):
+        return self._config.flops_profiler_config.profile_step
+
+    def checkpoint_tag_validation_enabled(self):
+        return self._config.checkpoint_tag_validation_enabled
+
+    def checkpoint_tag_validation_fail(self):
+        return self._config.checkpoint_tag_validation_fail
+
+    def load_universal_checkpoint(self):
+        return self._config.load_universal_checkpoint
+
+    def elasticity_enabled(self):
+        return self._config.elasticity_enabled
+
+    def pld_enabled(self):
+        return self._config.pld_enabled
+
+    def pld_theta(self):
+        return self._config.pld_params["theta"]
+
+    def pld_gamma(self):
+        return self._config.pld_params["gamma"]
+
+    def eigenvalue_enabled(self):
+        return self._config.eigenvalue_enabled
+
+    def curriculum_enabled_legacy(self):
+        return self._config.curriculum_enabled_legacy
+
+    def data_efficiency_enabled(self):
+        return self._config.data_efficiency_enabled
+
+    def tensorboard_enabled(self):
+        return self._config.monitor_config.tensorboard.enabled
+
+    def get_data_types(self):
+        dt = self._model_dtype()
+        return dt, (self._grad_accum_dtype() or dt)
+
+    @property
+    def config(self):
+        return self._config.to_dict()
+
+    def get_lr(self):
+        return [g["lr"] for g in self.basic_optimizer.param_groups]
+
+    def get_mom(self):
+        out = []
+        for g in self.basic_optimizer.param_groups:
+            out.append(g["betas"] if "betas" in g else g.get("momentum"))
+        return out
+
+    def get_type(self):
+        return [g.get("type") for g in self.basic_optimizer.param_groups]
+
+    def get_global_grad_norm(self):
+        return self._global_grad_norm
+
+    @property
+    def cur_scale(self):
+        return self.optimizer.cur_scale
+
+    def get_batch_info(self):
+        return self.train_batch_size(), self.train_micro_batch_size_per_gpu(), self.gradient_accumulation_steps()
+
+    def get_sequence_parallel_group(self):
+        return groups._get_sequence_parallel_group()
+
+    # ------------------------------------------------------------------ train / eval -----------
+    def train(self, mode=True):
+        self.warn_unscaled_loss = True
+        self.module.train(mode)
+        return self
+
+    def eval(self):
+        self.warn_unscaled_loss = True
+        self.module.train(False)
+        return self
+
+    def __getattr__(self, name):
+        # forward unknown attributes to the wrapped module (reference engine.py __getattr__)
+        try:
+            return super().__getattr__(name)
+        except AttributeError:
+            mod = self.__dict__.get("_modules", {}).get("module")
+            if mod is not None and hasattr(mod, name):
+                return getattr(mod, name)
+            raise
+
+    # ------------------------------------------------------------------ forward ----------------
+    @instrument_w_nvtx
+    def forward(self, *inputs, **kwargs):
+        if self.flops_profiler is not None and self.global_steps == self.flops_profiler_profile_step() \
+                and self.global_rank == 0 and self.micro_steps % self.gradient_accumulation_steps() == 0:
+            self.flops_profiler.start_profile(ignore_list=None)
+        if self.module.training and self.progressive_layer_drop is not None:
+            kwargs.update(self.progressive_layer_drop.get_state())
+        if self.module.training and self.curriculum_scheduler_legacy is not None:
+            self.curriculum_scheduler_legacy.update_difficulty(self.global_steps + 1)
+            if self._config.curriculum_params_legacy.get("curriculum_type") == "seqlen":
+                kwargs["curriculum_seqlen"] = self.curriculum_scheduler_legacy.get_current_difficulty()
+        if self.training_dataloader is None and self.micro_steps % self.gradient_accumulation_steps() == 0:
+            self.tput_timer.start()
+        for t in self.engine_timers.forward_timers:
+            self.timers(t).start()
+        if self.fp16_enabled() and self._config.fp16_auto_cast:
+            inputs = tuple(i.half() if torch.is_tensor(i) and i.is_floating_point() else i for i in inputs)
+        ac = self._config.torch_autocast_config
+        ctx = torch.autocast(device_type=self.device.type, dtype=getattr(torch, ac.dtype.replace("torch.", ""))) \
+            if ac.enabled else contextlib.nullcontext()
+        with ctx:
+            loss = self.module(*inputs, **kwargs)
+        for t in self.engine_timers.forward_timers:
+            self.timers(t).stop()
+        if self.flops_profiler is not None and self.flops_profiler.started:
+            self.flops_profiler.stop_profile()
+        return loss
+
+    # ------------------------------------------------------------------ backward ---------------
+    def is_gradient_accumulation_boundary(self):
+        if self._is_gradient_accumulation_boundary is None:
+            return (self.micro_steps + 1) % self.gradient_accumulation_steps() == 0
+        return self._is_gradient_accumulation_boundary
+
+    def set_gradient_accumulation_boundary(self, is_boundary):
+        self._is_gradient_accumulation_boundary = is_boundary
+        if self.optimizer is not None:
+            self.optimizer.is_gradient_accumulation_boundary = is_boundary
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        """Skip gradient reduction inside the context (illegal with ZeRO-2/3 where grads are partitioned)."""
+        assert not self.zero_optimization_partition_gradients(), \
+            f"no_sync context manager is incompatible with gradient partitioning logic of ZeRO stage " \
+            f"{self.zero_optimization_stage()}"
+        assert not self.inside_no_sync_ctxt, "no_sync context manager reentry is unsupported"
+        self.inside_no_sync_ctxt = True
+        if self.optimizer is not None:
+            self.optimizer._require_reduce = False
+        try:
+            yield
+        finally:
+            self.inside_no_sync_ctxt = False
+            if self.optimizer is not None:
+                self.optimizer._require_reduce = True
+
+    def _scale_loss_by_gas(self, loss):
+        if torch.is_tensor(loss):
+            return loss / self.gradient_accumulation_steps()
+        if isinstance(loss, (tuple, list)) and torch.is_tensor(loss[0]):
+            return type(loss)(l / self.gradient_accumulation_steps() for l in loss)
+        if self.warn_unscaled_loss:
+            logger.warning(f"DeepSpeed unable to scale loss because of type: {type(loss)}")
+            self.warn_unscaled_loss = False
+        return loss
+
+    def scale(self, loss):
+        """User-driven backward: returns the loss scaled for ``loss.backward()`` outside the engine."""
+        if self.gradient_accumulation_steps() > 1:
+            loss = self._scale_loss_by_gas(loss)
+        return self.optimizer.scale_if_loss(loss)
+
+    @instrument_w_nvtx
+    def backward(self, loss, retain_graph=False, scale_wrt_gas=True):
+        assert self.optimizer is not None, "must provide optimizer during init in order to use backward"
+        if self.inside_no_sync_ctxt:
+            pass
+        for t in self.engine_timers.backward_timers:
+            self.timers(t).start()
+        if self.gradient_accumulation_steps() > 1 and scale_wrt_gas:
+            loss = self._scale_loss_by_gas(loss.float())
+        if self.monitor.enabled and self.is_gradient_accumulation_boundary():
+            self.losses = loss.detach() if self.losses is None else self.losses + loss.detach()
+        self.optimizer.is_gradient_accumulation_boundary = self.is_gradient_accumulation_boundary()
+        self.optimizer.backward_prologue()
+        for t in self.engine_timers.backward_inner_timers:
+            self.timers(t).start()
+        scaled = self.optimizer.scale_if_loss(loss)
+        scaled.backward(retain_graph=retain_graph)
+        for t in self.engine_timers.backward_inner_timers:
+            self.timers(t).stop()
+        for t in self.engine_timers.backward_reduce_timers:
+            self.timers(t).start()
+        self.optimizer.backward_epilogue()
+        for t in self.engine_timers.backward_reduce_timers:
+            self.timers(t).stop()
+        for t in self.engine_timers.backward_timers:
+            self.timers(t).stop()
+        return loss
+
+    def allreduce_gradients(self, bucket_size=MEMORY_OPT_ALLREDUCE_SIZE):
+        if self.optimizer is not None:
+            self.optimizer.reduce_gradients()
+
+    # ------------------------------------------------------------------ step -------------------
+    def zero_grad(self):
+        if self.optimizer is not None:
+            self.optimizer.zero_grad()
+
+    def _take_model_step(self, lr_kwargs=None):
+        self.optimizer.step()
+        self._global_grad_norm = self.optimizer.get_global_grad_norm()
+        overflow = bool(getattr(self.optimizer, "overflow", False))
+        self.optimizer.zero_grad()
+        self._step_applied = not overflow
+        if overflow:
+            self.skipped_steps += 1
+        else:
+            if self.compression_scheduler is not None:
+                self.compression_scheduler.step()
+            if self.lr_scheduler is not None:
+                try:
+                    self.lr_scheduler.step(**(lr_kwargs or {}))
+                except TypeError:
+                    self.lr_scheduler.step()
+        if self.steps_per_print() and (self.global_steps + 1) % self.steps_per_print() == 0 and self.global_rank == 0:
+            self._report_progress(self.global_steps + 1)
+        self.global_steps += 1
+        self.global_samples += self.train_batch_size()
+
+    @instrument_w_nvtx
+    def step(self, lr_kwargs=None):
+        assert self.optimizer is not None, "must provide optimizer during init in order to use step"
+        for t in self.engine_timers.step_timers:
+            self.timers(t).start()
+        boundary = self.is_gradient_accumulation_boundary()
+        self._step_applied = False
+        if boundary:
+            if self.checkpoint_engine is not None and getattr(self.checkpoint_engine, "is_decoupled", lambda: False)():
+                self.checkpoint_engine.commit_pending()
+            if self.progressive_layer_drop is not None:
+                self.progressive_layer_drop.update_state(self.global_steps)
+            if self.eigenvalue is not None and self.global_steps % self.eigenvalue.gas_boundary_resolution == 0:
+                self.block_eigenvalue = self.eigenvalue.compute_eigenvalue(self.module, self.device)
+            self._take_model_step(lr_kwargs)
+        self.tput_timer.stop(global_step=boundary)
+        for t in self.engine_timers.step_timers:
+            self.timers(t).stop()
+        if boundary and self.monitor.enabled and self.global_rank == 0:
+            ev = [("Train/Samples/lr", self.get_lr()[0], self.global_samples)]
+            if self.losses is not None:
+                ev.append(("Train/Samples/train_loss", float(self.losses), self.global_samples))
+                self.losses = None
+            if self.fp16_enabled():
+                ev.append(("Train/Samples/loss_scale", self.optimizer.cur_scale, self.global_samples))
+            self.monitor.write_events(ev)
+        if self.wall_clock_breakdown() and boundary:
+            self.timers.log(self.engine_timers.micro_timers + self.engine_timers.global_timers,
+                            memory_breakdown=self.memory_breakdown())
+        if self.flops_profiler is not None and boundary and \
+                self.global_steps == self.flops_profiler_profile_step() + 1 and self.global_rank == 0:
+            fc = self._config.flops_profiler_config
+            self.flops_profiler.print_model_profile(profile_step=self.global_steps - 1, module_depth=fc.module_depth,
+                                                    top_modules=fc.top_modules, detailed=fc.detailed,
+                                                    output_file=fc.output_file)
+            self.flops_profiler.end_profile()
+        self.micro_steps += 1
+
+    def was_step_applied(self):
+        return self._step_applied
+
+    def _report_progress(self, step):
+        log_dist(f"step={step}, skipped={self.skipped_steps}, lr={self.get_lr()}, mom={self.get_mom()}", ranks=[0])
+
+    def train_batch(self, data_iter=None):
+        """Convenience: run ``gas`` micro-batches from ``data_iter`` (non-pipeline engine)."""
+        if data_iter is None:
+            data_iter = iter(self.training_dataloader)
+        total = 0.0
+        for _ in range(self.gradient_accumulation_steps()):
+            batch = next(data_iter)
+            batch = batch if isinstance(batch, (tuple, list)) else (batch, )
+            batch = tuple(b.to(self.device) if torch.is_tensor(b) else b for b in batch)
+            loss = self(*batch)
+            self.backward(loss)
+            self.step()
+            total += float(loss.detach())
+        return total / self.gradient_accumulation_steps()
+
+    # ------------------------------------------------------------------ state offload ----------
+    def offload_states(self, include=None, device="cpu", pin_memory=True, non_blocking=False):
+        self.optimizer.offload_states(include=include, device=device, pin_memory=pin_memory, non_blocking=non_blocking)
+
+    def reload_states(self, non_blocking=False):
+        self.optimizer.reload_states(non_blocking=non_blocking)
+
+    def compile(self, backend=None, compile_kwargs=None, schedule=None, compiled_autograd_enabled=False):
+        """No tracing compiler on the hot path by design: kept as a passthrough for API compatibility."""
+        log_dist("engine.compile(): passthrough (B200 path uses hand-written kernels + CUDA graphs)", [0])
+        self._is_compiled = True
+
+    @property
+    def is_compiled(self):
+        return getattr(self, "_is_compiled", False)
+
+    def destroy(self):
+        if self.optimizer is not None:
+            self.optimizer.destroy()
+        if self.checkpoint_engine is not None and hasattr(self.checkpoint_engine, "cleanup"):
+            self.checkpoint_engine.cleanup()
+
+    # ------------------------------------------------------------------ state dicts / ckpt ------
+    def module_state_dict(self, destination=None, prefix="", keep_vars=False, exclude_frozen_parameters=False):
+        sd = self.module.state_dict(destination=destination, prefix=prefix, keep_vars=keep_vars)
+        if exclude_frozen_parameters:
+            frozen = {n for n, p in self.module.named_parameters() if not p.requires_grad}
+            for n in frozen:
+                sd.pop(prefix + n, None)
+        return sd
+
+    def load_module_state_dict(self, checkpoint, strict=True, custom_load_fn=None, fetch_z3_params=False):
+        sd = checkpoint["module"] if isinstance(checkpoint, dict) and "module" in checkpoint else checkpoint
+        if custom_load_fn:
+            custom_load_fn(src=sd, dst=self.module)
+        elif self.zero_optimization_partition_weights():
+            from .zero.init_context import GatheredParameters
+            params = list(self.module.parameters())
+            with GatheredParameters(params, modifier_rank=0):
+                self.module.load_state_dict(sd, strict=strict)
+        else:
+            self.module.load_state_dict(sd, strict=strict)
+
+    def save_checkpoint(self, save_dir, tag=None, client_state=None, save_latest=True, exclude_frozen_parameters=False):
+        from ..checkpoint.saver import save_engine_checkpoint
+        return save_engine_checkpoint(self, save_dir, tag, client_state or {}, save_latest, exclude_frozen_parameters)
+
+    def load_checkpoint(self, load_dir, tag=None, load_module_strict=True, load_optimizer_states=True,
+                        load_lr_scheduler_states=True, load_module_only=False, custom_load_fn=None):
+        from ..checkpoint.saver import load_engine_checkpoint
+        return load_engine_checkpoint(self, load_dir, tag, load_module_strict, load_optimizer_states,
+                                      load_lr_scheduler_states, load_module_only, custom_load_fn)
+
+    def _zero3_consolidated_16bit_state_dict(self, exclude_frozen_parameters=False):
+        """Gather ZeRO-3 shards unit by unit into a rank-0 CPU state dict (reference engine.py:5491)."""
+        from .zero.init_context import GatheredParameters
+        out = OrderedDict()
+        frozen = {id(p) for p in self.module.parameters() if not p.requires_grad} if exclude_frozen_parameters else set()
+        shared = {}
+        for u in self.optimizer.units:
+            with GatheredParameters(u.params):
+                if self.global_rank == 0:
+                    for name, p in zip(u.names, u.params):
+                        if id(p) not in frozen:
+                            out[name] = p.detach().cpu().clone()
+        if self.global_rank == 0:
+            # params shared under several names + buffers
+            names_by_id = {}
+            for name, p in self.module.named_parameters(remove_duplicate=False):
+                names_by_id.setdefault(id(p), []).append(name)
+            for names in names_by_id.values():
+                src = next((n for n in names if n in out), None)
+                if src is not None:
+                    for n in names:
+                        out.setdefault(n, out[src])
+            for name, b in self.module.named_buffers():
+                if b is not None and name.split(".")[-1] not in getattr(self.module, "_non_persistent_buffers_set", set()):
+                    out[name] = b.detach().cpu().clone()
+        return out
+
+    def save_16bit_model(self, save_dir, save_filename="pytorch_model.bin", exclude_frozen_parameters=False):
+        path = os.path.join(save_dir, save_filename)
+        if self.zero_optimization_partition_weights():
+            if not self.zero_gather_16bit_weights_on_model_save():
+                logger.info(f"Did not save the model {path} because `stage3_gather_16bit_weights_on_model_save` is False")
+                return False
+            sd = self._zero3_consolidated_16bit_state_dict(exclude_frozen_parameters)
+        else:
+            sd = self.module_state_dict(exclude_frozen_parameters=exclude_frozen_parameters)
+        if self.global_rank == 0:
+            os.makedirs(save_dir, exist_ok=True)
+            self.checkpoint_engine.save(sd, path)
+        return True
+
+    save_fp16_model = save_16bit_model

@@ -1,0 +1,255 @@
+"""ZeRO-3 unit coordinator: gather / release / prefetch of flat units around module execution.
+
+The reference walks *every* ``nn.Module`` with four hooks and a recorded trace
+(``partitioned_param_coordinator.py:73-690``, ``parameter_offload.py:331-603``). Here the granule is the
+:class:`FlatUnit` (a transformer block): one forward-pre / forward-post hook per unit module, a tensor hook on
+the unit outputs for pre-backward, and the per-parameter grad hooks of the optimizer for post-backward. The
+execution order recorded in the first iteration drives a one-unit-ahead prefetch on a side stream.
+
+A module may use parameters owned by another unit (tied embeddings, "external parameters" in the reference,
+``partition_parameters.py register_external_parameter``): ``_needed_units`` resolves that statically from
+``module.parameters()`` plus anything registered through :func:`register_external_parameter`.
+"""
+import torch
+
+from ... import comm as dist
+from ...utils.nvtx import instrument_w_nvtx
+from .units import FlatUnit
+
+
+class UnitCoordinator:
+
+    def __init__(self, zopt, prefetch=True):
+        self.z = zopt
+        self.prefetch = prefetch
+        self.handles = []
+        self.fwd_order = []  # unit ids in first-forward order
+        self._trace_done = False
+        self._fwd_pos = {}
+        self._in_backward_pass = False
+        self._module_units = {}
+        self._external = {}  # module -> [params]
+        self._slot_buffers = {}
+        self._install()
+
+    # ---- hook installation ---------------------------------------------------------------------
+    def _install(self):
+        mods = {}
+        for u in self.z.units:
+            if u.module is not None and not u.persistent:
+                mods.setdefault(u.module, []).append(u)
+        self._own_units = mods
+        for m in mods:
+            self.handles.append(m.register_forward_pre_hook(self._pre_forward, with_kwargs=True))
+            self.handles.append(m.register_forward_hook(self._post_forward))
+
+    def remove_hooks(self):
+        for h in self.handles:
+            h.remove()
+        self.handles = []
+
+    def register_external_parameter(self, module, param):
+        self._external.setdefault(module, []).append(param)
+        self._module_units.pop(module, None)
+        if module not in self._own_units:
+            self._own_units[module] = []
+            self.handles.append(module.register_forward_pre_hook(self._pre_forward, with_kwargs=True))
+            self.handles.append(module.register_forward_hook(self._post_forward))
+
+    def _needed_units(self, module):
+        """Non-persistent units owning any parameter reachable from ``module`` that no child unit-module covers."""
+        if module in self._module_units:
+            return self._module_units[module]
+        covered = set()
+        for child in module.modules():
+            if child is not module and child in self._own_units:
+                for p in child.parameters():
+                    covered.add(id(p))
+        need, seen = [], set()
+        plist = list(module.parameters()) + list(self._external.get(module, []))
+        for p in plist:
+            if id(p) in covered and p not in self._external.get(module, []):
+                continue
+            ent = self.z._unit_of_param.get(id(p))
+            if ent is None:
+                continue
+            u = ent[0]
+            if not u.persistent and u.uid not in seen:
+                seen.add(u.uid)
+                need.append(u)
+        self._module_units[module] = need
+        return need
+
+    # ---- gather / release ----------------------------------------------------------------------
+    @instrument_w_nvtx
+    def gather(self, u: FlatUnit, wait=True):
+        """Launch (if needed) and optionally complete the all-gather of a unit's parameters."""
+        z = self.z
+        if not u.gathered and u.gather_work is None:
+            use_side = z._use_streams and z.overlap_comm
+            src = u.param_shard
+            group = u.dp_group
+            if z._hpz_group is not None and self._in_backward_pass and u.sec_shard is not None:
+                src, group = u.sec_shard, z._hpz_group
+            if use_side:
+                with torch.cuda.stream(z.ag_stream):
+                    full = torch.empty(u.numel_padded, dtype=u.dtype, device=u.device)
+                    self._launch_gather(u, full, src, group)
+                    u.gather_event = torch.cuda.Event()
+                    u.gather_event.record(z.ag_stream)
+            else:
+                full = torch.empty(u.numel_padded, dtype=u.dtype, device=u.device)
+                self._launch_gather(u, full, src, group)
+            u.full_param = full
+            u.gather_work = True
+        if wait and not u.gathered:
+            if u.gather_event is not None:
+                torch.cuda.current_stream().wait_event(u.gather_event)
+                u.full_param.record_stream(torch.cuda.current_stream())
+                u.gather_event = None
+            for p, view in zip(u.params, u.view_params(u.full_param)):
+                p.data = view
+                p.ds_status = "AVAILABLE"
+            u.gathered = True
+            u.gather_work = None
+            if z.hpz_size > 1 and u.sec_shard is None and not self._in_backward_pass:
+                self._make_secondary(u)
+
+    def _launch_gather(self, u, full, src, group):
+        world = dist.get_world_size(group) if group is not None and dist.is_initialized() else 1
+        if world <= 1:
+            full[:src.numel()].copy_(src)
+            return
+        if self.z.quantized_weights and u.dtype in (torch.bfloat16, torch.float16) and full.is_cuda:
+            from ...ops.quantizer import quantized_all_gather
+            quantized_all_gather(full, src, group)
+            return
+        if dist.get_backend(group) == "gloo":
+            src = src.clone()
+        if world * src.numel() == full.numel():
+            dist.all_gather_into_tensor(full, src, group=group)
+        else:  # hpZ secondary gather: group is a subgroup holding replicated sub-shards
+            dist.all_gather_into_tensor(full, src, group=group)
+
+    def _make_secondary(self, u):
+        """hpZ: keep an intra-group replica so the backward re-gather stays inside the (smaller) group."""
+        z = self.z
+        hw = z.hpz_size
+        n = u.numel_padded // hw
+        r = dist.get_rank(z._hpz_group)
+        u.sec_shard = u.full_param[r * n:(r + 1) * n].clone()
+
+    def release(self, u: FlatUnit):
+        if u.persistent or not (u.gathered or u.gather_work):
+            return
+        if u.gather_work and not u.gathered:
+            self.gather(u, wait=True)
+        self.z._release_params(u)
+
+    # ---- module hooks --------------------------------------------------------------------------
+    def _pre_forward(self, module, args, kwargs):
+        need = self._needed_units(module)
+        for u in need:
+            if not self._trace_done and u.uid not in self._fwd_pos:
+                self._fwd_pos[u.uid] = len(self.fwd_order)
+                self.fwd_order.append(u.uid)
+            self.gather(u, wait=False)
+        if self.prefetch and self._trace_done and need and not self._in_backward_pass:
+            pos = max(self._fwd_pos.get(u.uid, -1) for u in need) + 1
+            if 0 <= pos < len(self.fwd_order):
+                self.gather(self.z.units[self.fwd_order[pos]], wait=False)
+        for u in need:
+            self.gather(u, wait=True)
+        return None
+
+    def _post_forward(self, module, args, output):
+        need = self._needed_units(module)
+        grad_mode = torch.is_grad_enabled()
+        if grad_mode:
+            self._attach_pre_backward(module, output)
+        if not self._in_backward_pass:
+            for u in need:
+                if self._still_needed_by_parent(module, u):
+                    continue
+                self.release(u)
+        return None
+
+    def _still_needed_by_parent(self, module, u):
+        # units attached to a module that is an ancestor of the running one stay until their own post-forward
+        return u.module is not None and u.module is not module and module in set(u.module.modules())
+
+    def _attach_pre_backward(self, module, output):
+        tensors = []
+        _collect_tensors(output, tensors)
+        tensors = [t for t in tensors if t.requires_grad]
+        if not tensors:
+            return
+        fired = {"done": False}
+
+        def hook(grad):
+            if not fired["done"]:
+                fired["done"] = True
+                self._pre_backward(module)
+            return grad
+
+        for t in tensors:
+            t.register_hook(hook)
+
+    def _pre_backward(self, module):
+        self._in_backward_pass = True
+        self.z._ensure_epilogue()
+        need = self._needed_units(module)
+        for u in need:
+            self.gather(u, wait=False)
+        if self.prefetch and need:
+            pos = min(self._fwd_pos.get(u.uid, 1 << 30) for u in need) - 1
+            if 0 <= pos < len(self.fwd_order):
+                nxt = self.z.units[self.fwd_order[pos]]
+                if not nxt.reduced_this_pass:
+                    self.gather(nxt, wait=False)
+        for u in need:
+            self.gather(u, wait=True)
+
+    # ---- optimizer callbacks -------------------------------------------------------------------
+    def on_unit_backward_done(self, u):
+        if not u.persistent:
+            self.release(u)
+
+    def on_backward_end(self):
+        self._in_backward_pass = False
+        if self.fwd_order:
+            self._trace_done = True
+        for u in self.z.units:
+            if not u.persistent and (u.gathered or u.gather_work):
+                self.release(u)
+
+    def on_step_done(self):
+        z = self.z
+        if z._use_streams and z.overlap_comm:
+            z.ag_stream.wait_stream(torch.cuda.current_stream())  # shards were rewritten by the step
+        for u in self.z.units:
+            u.sec_shard = None  # hpZ replicas are stale after the update (reference stage3.py:706)
+
+    def release_all(self):
+        for u in self.z.units:
+            if not u.persistent:
+                self.release(u)
+
+    def gather_all(self):
+        for u in self.z.units:
+            self.gather(u, wait=True)
+
+
+def _collect_tensors(obj, out):
+    if torch.is_tensor(obj):
+        out.append(obj)
+    elif isinstance(obj, (list, tuple)):
+        for o in obj:
+            _collect_tensors(o, out)
+    elif isinstance(obj, dict):
+        for o in obj.values():
+            _collect_tensors(o, out)
+    elif hasattr(obj, "__dict__") and not isinstance(obj, torch.nn.Module):
+        for o in vars(obj).values():
+            if torch.is_tensor(o) or isinstance(o, (list, tuple, dict)):
+                _collect_tensors(o, out)

@@ -1,0 +1,926 @@
+"""Unified ZeRO optimizer for stages 0/1/2/3 built on :class:`FlatUnit`.
+
+What the reference spreads over ``stage_1_and_2.py`` (3179 LoC), ``stage3.py`` (3887), ``bf16_optimizer.py``
+and ``fp16/fused_optimizer.py`` is one class here with a ``(partition optimizer, partition grads, partition
+params)`` triple:
+
+========  =====================  ==========================  ===================
+stage     optimizer state        gradients                   parameters
+========  =====================  ==========================  ===================
+0         replicated             all-reduce at GAS boundary  replicated
+1         sharded                reduce-scatter at boundary  replicated (+AG after step)
+2         sharded                reduce-scatter per micro-   replicated (+AG after step)
+                                 step, overlapped
+3         sharded                same as 2                   sharded; gather/release per unit
+========  =====================  ==========================  ===================
+
+Reference behaviour covered: IPG bucketing + overlap (``stage_1_and_2.py:1193-1468``), averaging with the
+sequence-parallel correction (``:1436``), partitioned step with unscale+clip (``:2279-2410``), fp16 dynamic loss
+scaling skip-step (``:2289-2311``), grad-norm over DP(+MP) (``runtime/utils.py:878``), ZeRO-3 reduce+partition
+(``stage3.py:1570-1930``), hpZ/MiCS shard-vs-replica groups (``mics.py``), CPU offload of optimizer state
+(``stage_1_and_2.py:1473-1650``), ``offload_states`` (``:2915``).
+
+On B200 the NCCL calls below are the *baseline* path; when symmetric memory is available the reduce-scatter
+(+unscale+Adam) and all-gather are replaced by the fused kernels in :mod:`deepspeed_b200.comm.symm`.
+"""
+import math
+from collections import OrderedDict
+from typing import Dict, List
+
+import torch
+
+from ... import comm as dist
+from ...utils.logging import log_dist, logger
+from ...utils.nvtx import instrument_w_nvtx
+from ..loss_scaler import CreateLossScaler
+from .units import FlatUnit, build_bucket_units, build_module_units
+
+ZERO_STAGE = "zero_stage"
+PARTITION_COUNT = "partition_count"
+BASE_OPTIMIZER_STATE = "base_optimizer_state"
+SINGLE_PARTITION_OF_FP32_GROUPS = "single_partition_of_fp32_groups"
+LOSS_SCALER = "loss_scaler"
+DYNAMIC_LOSS_SCALE = "dynamic_loss_scale"
+OVERFLOW = "overflow"
+CLIP_GRAD = "clip_grad"
+DS_VERSION = "ds_version"
+PARAM_SLICE_MAPPINGS = "param_slice_mappings"
+GROUP_PADDINGS = "group_paddings"
+UNIT_LAYOUT = "b200_unit_layout"
+
+
+class _Storage:
+    """Rank-local flat storage for all units of one communication group key."""
+
+    def __init__(self):
+        self.units: List[FlatUnit] = []
+        self.numel = 0
+        self.master = None
+        self.grad = None
+        self.lp = None
+
+
+class ZeroShardedOptimizer:
+    """See module docstring. ``optimizer`` is any ``torch.optim.Optimizer`` built over the model's params."""
+
+    def __init__(self, module, optimizer, *, stage=1, dp_group=None, dp_world=1, dp_rank=0, sp_size=1,
+                 mp_group=None, reduce_bucket_size=int(5e8), overlap_comm=True, contiguous_gradients=True,
+                 reduce_scatter=True, clip_grad=0.0, dtype=torch.bfloat16, fp16_config=None, grad_accum_dtype=None,
+                 communication_data_type=None, gradient_accumulation_steps=1, gradient_predivide_factor=1.0,
+                 gradient_average=True, master_weights_in_lp=False, offload_optimizer=None, offload_param=None,
+                 unit_max_numel=int(1e9), param_persistence_threshold=int(1e5), prefetch=True, mics_shard_size=-1,
+                 hpz_size=1, quantized_weights=False, quantized_gradients=False, expert_groups=None,
+                 leaf_modules=(), elastic_checkpoint=False, timers=None, fused_collectives=None,
+                 ignore_unused_parameters=True):
+        self.module = module
+        self.optimizer = optimizer
+        self.stage = int(stage)
+        self.partition_optimizer = self.stage >= 1
+        self.partition_grads = self.stage >= 2
+        self.partition_params = self.stage >= 3
+        self.dp_group, self.dp_world, self.dp_rank = dp_group, dp_world, dp_rank
+        self.sp_size = sp_size
+        self.mp_group = mp_group
+        self.clip_grad = float(clip_grad or 0.0)
+        self.overlap_comm = bool(overlap_comm) and torch.cuda.is_available()
+        self.gas = gradient_accumulation_steps
+        self.predivide = gradient_predivide_factor
+        self.gradient_average = gradient_average
+        self.timers = timers
+        self.elastic_checkpoint = elastic_checkpoint
+        self.expert_groups = expert_groups or {}
+        self.quantized_weights = quantized_weights
+        self.quantized_gradients = quantized_gradients
+        self.ignore_unused_parameters = ignore_unused_parameters
+        self.offload_optimizer = bool(offload_optimizer and str(getattr(offload_optimizer, "device", "none")) != "none")
+        self.offload_cfg = offload_optimizer
+        self.offload_param_cfg = offload_param
+        self.lp_dtype = dtype
+        self.master_dtype = dtype if master_weights_in_lp else torch.float32
+        self.comm_dtype = communication_data_type or dtype
+        if grad_accum_dtype is None:
+            grad_accum_dtype = torch.float32 if (self.gas > 1 or dtype == torch.float32) else dtype
+        self.grad_accum_dtype = grad_accum_dtype
+        self.micro_step_id = 0
+        self.overflow = False
+        self.skipped_steps = 0
+        self._global_grad_norm = 0.0
+        self._in_backward = False
+        self._epilogue_queued = False
+        self._require_reduce = True  # toggled by engine.no_sync
+        self.is_gradient_accumulation_boundary = True
+        self._offloaded_states = set()
+
+        # ---- loss scaling ----
+        if dtype == torch.float16:
+            fc = fp16_config
+            dynamic = (fc is None) or (fc.loss_scale == 0)
+            self.loss_scaler = CreateLossScaler(torch.half, static_loss_scale=(fc.loss_scale if fc else 1.0),
+                                                dynamic_scaling=dynamic,
+                                                dynamic_loss_args=(fc.dynamic_loss_scale_args() if fc else dict(
+                                                    init_scale=2**16, scale_window=1000, min_scale=1,
+                                                    delayed_shift=2, consecutive_hysteresis=False)))
+            self.dynamic_loss_scale = dynamic
+        else:
+            self.loss_scaler = CreateLossScaler(dtype, 1.0, False, None)
+            self.dynamic_loss_scale = False
+        self.custom_loss_scaler = False
+        self.external_loss_scale = None
+
+        # ---- shard / replica topology ----
+        shard_world = dp_world if self.partition_optimizer else 1
+        self._shard_group, self._replica_group = dp_group, None
+        self._shard_world, self._shard_rank, self._replica_world = shard_world, (dp_rank if shard_world > 1 else 0), 1
+        if not self.partition_optimizer:
+            self._shard_group, self._replica_group, self._replica_world = None, dp_group, dp_world
+        elif mics_shard_size and 0 < mics_shard_size < dp_world:
+            self._init_mics_groups(mics_shard_size)
+        self.hpz_size = hpz_size if (self.partition_params and hpz_size > 1) else 1
+        self._hpz_group = None
+        if self.hpz_size > 1:
+            from ...utils import groups
+            self._hpz_group = groups._create_zero_param_parallel_group(self.hpz_size)
+
+        # ---- units ----
+        named = [(n, p) for n, p in module.named_parameters()]
+        self._param_names = {id(p): n for n, p in named}
+        pgs = optimizer.param_groups
+        self._orig_param_groups = [list(g["params"]) for g in pgs]
+        if self.partition_params:
+            self._add_frozen_group(named, pgs)
+            self.units = build_module_units(module, self._pg_with_frozen, unit_max_numel, param_persistence_threshold,
+                                            self._world_of, self._rank_of, self._group_of, leaf_modules)
+        else:
+            self.units = build_bucket_units(named, pgs, max(int(reduce_bucket_size), 1), self._world_of,
+                                            self._rank_of, self._group_of)
+        for u in self.units:
+            u.replica_group = self._replica_group if u.group_key == "dp" else None
+            u.replica_world = self._replica_world if u.group_key == "dp" else 1
+        self._unit_of_param = {}
+        for u in self.units:
+            for i, p in enumerate(u.params):
+                self._unit_of_param[id(p)] = (u, i)
+                p.ds_unit, p.ds_index = u, i
+            u._zopt = self
+
+        self._use_streams = torch.cuda.is_available() and any(p.is_cuda for _, p in named)
+        if self._use_streams:
+            self.rs_stream = torch.cuda.Stream() if self.overlap_comm else torch.cuda.current_stream()
+            self.ag_stream = torch.cuda.Stream() if self.overlap_comm else torch.cuda.current_stream()
+        else:
+            self.rs_stream = self.ag_stream = None
+
+        self._allocate_and_link()
+        self._register_grad_hooks()
+        self.coordinator = None
+        if self.partition_params:
+            from .coordinator import UnitCoordinator
+            self.coordinator = UnitCoordinator(self, prefetch=prefetch)
+        log_dist(
+            f"ZeRO stage {self.stage}: {len(self.units)} units, shard_world={self._shard_world}, "
+            f"replica_world={self._replica_world}, lp={self.lp_dtype}, master={self.master_dtype}, "
+            f"grad_accum={self.grad_accum_dtype}, offload_optimizer={self.offload_optimizer}", [0])
+
+    # ------------------------------------------------------------------ topology helpers -------
+    def _init_mics_groups(self, shard_size):
+        """MiCS: shard inside groups of ``shard_size`` ranks, replicate (all-reduce) across groups."""
+        ranks = dist.get_all_ranks_from_group(self.dp_group)
+        assert len(ranks) % shard_size == 0
+        me = dist.get_rank()
+        shard_g = rep_g = None
+        for i in range(0, len(ranks), shard_size):
+            rl = ranks[i:i + shard_size]
+            g = dist.new_group(rl)
+            if me in rl:
+                shard_g, self._shard_rank = g, rl.index(me)
+        for j in range(shard_size):
+            rl = ranks[j::shard_size]
+            g = dist.new_group(rl)
+            if me in rl:
+                rep_g = g
+        self._shard_group, self._replica_group = shard_g, rep_g
+        self._shard_world, self._replica_world = shard_size, len(ranks) // shard_size
+
+    def _world_of(self, key):
+        if key == "dp":
+            return self._shard_world
+        if not self.partition_optimizer:
+            return 1
+        from ...utils import groups
+        return groups._get_expert_data_parallel_world_size(key)
+
+    def _rank_of(self, key):
+        if key == "dp":
+            return self._shard_rank
+        if not self.partition_optimizer:
+            return 0
+        from ...utils import groups
+        return groups._get_expert_data_parallel_rank(key)
+
+    def _group_of(self, key):
+        if key == "dp":
+            return self._shard_group
+        from ...utils import groups
+        return groups._get_expert_data_parallel_group(key)
+
+    def _add_frozen_group(self, named, pgs):
+        in_opt = {id(p) for g in pgs for p in g["params"]}
+        frozen = [p for _, p in named if id(p) not in in_opt]
+        self._pg_with_frozen = list(pgs)
+        self._frozen_group_idx = None
+        if frozen:
+            self._frozen_group_idx = len(pgs)
+            self._pg_with_frozen = list(pgs) + [{"params": frozen}]
+
+    # ------------------------------------------------------------------ allocation -------------
+    def _state_device(self, device):
+        return torch.device("cpu") if self.offload_optimizer else device
+
+    def _allocate_and_link(self):
+        """Flatten params into units, carve rank-flat master/grad/lp storage and re-point the inner optimizer."""
+        self.storages: Dict[str, _Storage] = OrderedDict()
+        for u in self.units:
+            st = self.storages.setdefault((u.group_key, u.dtype), _Storage())
+            u.shard_offset = st.numel
+            st.units.append(u)
+            st.numel += u.shard_numel
+        pin = self.offload_optimizer and torch.cuda.is_available() and getattr(self.offload_cfg, "pin_memory", True)
+        for key, st in self.storages.items():
+            dev = st.units[0].device
+            sdev = self._state_device(dev)
+            st.device, st.state_device = dev, sdev
+            st.master = torch.zeros(st.numel, dtype=self.master_dtype, device=sdev, pin_memory=(pin and sdev.type == "cpu"))
+            st.grad = torch.zeros(st.numel, dtype=self.grad_accum_dtype, device=dev)
+            if self.offload_optimizer:
+                st.grad_host = torch.zeros(st.numel, dtype=torch.float32, device=sdev,
+                                           pin_memory=(pin and sdev.type == "cpu"))
+                st.lp_host = torch.zeros(st.numel, dtype=key[1], device=sdev, pin_memory=(pin and sdev.type == "cpu"))
+            st.lp = torch.zeros(st.numel, dtype=key[1], device=dev) if self.partition_params else None
+            for u in st.units:
+                a, b = u.shard_offset, u.shard_offset + u.shard_numel
+                u.master_shard, u.grad_shard = st.master[a:b], st.grad[a:b]
+                self._flatten_unit(u, st, a, b)
+        # ---- inner optimizer param groups -> master views ----
+        self._views_by_group = [[] for _ in self.optimizer.param_groups]
+        self._segments = []  # (storage_key, start, end, group_idx, unit)
+        for key, st in self.storages.items():
+            for u in st.units:
+                for run in u.runs_in_shard():
+                    gi = run.group_idx
+                    if gi >= len(self.optimizer.param_groups):
+                        continue  # frozen params: no optimizer state
+                    a, b = u.shard_offset + run.start, u.shard_offset + run.end
+                    v = st.master[a:b]
+                    v.requires_grad_(True)
+                    self._views_by_group[gi].append(v)
+                    self._segments.append((key, a, b, gi, u, v))
+        old_state = self.optimizer.state
+        if len(old_state):
+            logger.warning("Client optimizer state is discarded when wrapping with ZeRO (state is re-created on shards)")
+        self.optimizer.state.clear()
+        for g, views in zip(self.optimizer.param_groups, self._views_by_group):
+            g["params"] = views
+        self.param_groups = self.optimizer.param_groups
+
+    @torch.no_grad()
+    def _flatten_unit(self, u: FlatUnit, st, a, b):
+        """Copy current param values into the unit's flat buffer and set up views / shards."""
+        full = torch.empty(u.numel_padded, dtype=u.dtype, device=u.device)
+        full.zero_()
+        zero_init = any(hasattr(p, "ds_init_shard") for p in u.params)
+        for p, view in zip(u.params, u.view_params(full)):
+            if hasattr(p, "ds_init_shard"):  # created under zero.Init: gather the per-param partitions
+                from .init_context import gather_init_param
+                view.copy_(gather_init_param(p).view(view.shape))
+            else:
+                view.copy_(p.data.to(u.dtype))
+        s, e = u.shard_range()
+        u.master_shard.copy_(full[s:e].to(self.master_dtype), non_blocking=False)
+        for i, p in enumerate(u.params):
+            p.ds_shape, p.ds_numel = torch.Size(u.shapes[i]), u.numels[i]
+            p.ds_id = f"{u.uid}.{i}"
+            if zero_init and hasattr(p, "ds_init_shard"):
+                del p.ds_init_shard
+        if self.partition_params and not u.persistent:
+            u.param_shard = st.lp[a:b]
+            u.param_shard.copy_(full[s:e])
+            self._release_params(u)
+            del full
+        else:
+            u.full_param = full
+            u.param_shard = full[s:e]
+            if st.lp is not None:  # persistent unit under stage 3 keeps a copy in the flat lp storage too
+                st.lp[a:b].copy_(full[s:e])
+            for p, view in zip(u.params, u.view_params(full)):
+                p.data = view
+            u.gathered = True
+
+    def _release_params(self, u: FlatUnit):
+        for p in u.params:
+            p.data = torch.empty(0, dtype=u.dtype, device=u.device)
+            p.ds_status = "NOT_AVAILABLE"
+        u.full_param = None
+        u.gathered = False
+
+    # ------------------------------------------------------------------ gradient hooks ---------
+    def _register_grad_hooks(self):
+        self._hook_handles = []
+        for u in self.units:
+            for i, p in enumerate(u.params):
+                if p.requires_grad:
+                    self._hook_handles.append(p.register_post_accumulate_grad_hook(self._make_hook(u, i)))
+
+    def _make_hook(self, u, i):
+
+        def hook(param):
+            self._on_grad_ready(u, i, param)
+
+        return hook
+
+    def _ensure_epilogue(self):
+        if not self._in_backward and not self._epilogue_queued:
+            # user-called tensor.backward(): run the epilogue when autograd finishes
+            self._epilogue_queued = True
+            torch.autograd.Variable._execution_engine.queue_callback(self._queued_epilogue)
+
+    def _queued_epilogue(self):
+        self._epilogue_queued = False
+        self.backward_epilogue()
+
+    @torch.no_grad()
+    def _on_grad_ready(self, u: FlatUnit, i, param):
+        g = param.grad
+        if g is None:
+            return
+        self._ensure_epilogue()
+        if u.full_grad is None:
+            u.full_grad = torch.zeros(u.numel_padded, dtype=self._full_grad_dtype(), device=u.device)
+            u.has_grad_data = False
+        o, n = u.offsets[i], u.numels[i]
+        view = u.full_grad[o:o + n]
+        if u.has_grad_data and not self.partition_grads:
+            view.add_(g.reshape(-1))
+        else:
+            view.copy_(g.reshape(-1))
+        param.grad = None
+        u.grads_ready += 1
+        if u.grads_ready >= u.grads_expected:
+            self._unit_backward_done(u)
+
+    def _full_grad_dtype(self):
+        # stage<=1 accumulates micro-batches in the full buffer -> use the accumulation dtype there
+        return self.comm_dtype if self.partition_grads else (self.grad_accum_dtype if self.gas > 1 else self.comm_dtype)
+
+    def _unit_backward_done(self, u):
+        u.has_grad_data = True
+        if self.coordinator is not None:
+            self.coordinator.on_unit_backward_done(u)
+        if self._should_reduce_now():
+            self._reduce_unit(u)
+
+    def _should_reduce_now(self):
+        if not self._require_reduce:
+            return False
+        return self.partition_grads or self.is_gradient_accumulation_boundary
+
+    # ------------------------------------------------------------------ reduction --------------
+    def _grad_divisor(self, u):
+        if not self.gradient_average:
+            return 1.0
+        return float(u.world * u.replica_world) / float(self.sp_size if u.group_key == "dp" else 1)
+
+    @instrument_w_nvtx
+    @torch.no_grad()
+    def _reduce_unit(self, u: FlatUnit):
+        """Reduce one unit's flat grads to the owner shards and accumulate into ``grad_shard``."""
+        if u.full_grad is None or u.reduced_this_pass:
+            return
+        u.reduced_this_pass = True
+        full = u.full_grad
+        div = self._grad_divisor(u)
+        first = not getattr(u, "_shard_has_data", False)
+        stream_ctx = None
+        if self._use_streams and self.overlap_comm:
+            self.rs_stream.wait_stream(torch.cuda.current_stream())
+            stream_ctx = torch.cuda.stream(self.rs_stream)
+            stream_ctx.__enter__()
+        try:
+            if full.dtype != self.comm_dtype:
+                full = full.to(self.comm_dtype)
+            pre = self.predivide if (self.predivide and self.predivide != 1.0) else (
+                div if self.comm_dtype == torch.float16 else 1.0)
+            if pre != 1.0:
+                full.div_(pre)
+            post = div / pre
+            if u.world > 1:
+                out = torch.empty(u.shard_numel, dtype=full.dtype, device=full.device)
+                dist.reduce_scatter_tensor(out, full, group=u.dp_group)
+            else:
+                out = full
+            if u.replica_world > 1:
+                dist.all_reduce(out, group=u.replica_group)
+            if first:
+                if post != 1.0:
+                    torch.mul(out, 1.0 / post, out=u.grad_shard) if out.dtype == u.grad_shard.dtype else \
+                        u.grad_shard.copy_(out.to(u.grad_shard.dtype).mul_(1.0 / post))
+                else:
+                    u.grad_shard.copy_(out)
+            else:
+                u.grad_shard.add_(out.to(u.grad_shard.dtype), alpha=1.0 / post)
+            u._shard_has_data = True
+            if self._use_streams and self.overlap_comm:
+                u.full_grad.record_stream(self.rs_stream)
+        finally:
+            if stream_ctx is not None:
+                stream_ctx.__exit__(None, None, None)
+        if self.partition_grads or self.is_gradient_accumulation_boundary:
+            u.full_grad = None
+            u.has_grad_data = False
+
+    # ------------------------------------------------------------------ backward bracket -------
+    def backward_prologue(self):
+        self._in_backward = True
+        if self.coordinator is not None:
+            self.coordinator._in_backward_pass = True
+
+    @torch.no_grad()
+    def backward_epilogue(self):
+        """Flush units whose hooks did not all fire (unused params), wait for side-stream reductions."""
+        for u in self.units:
+            if u.full_grad is not None and not u.reduced_this_pass and self._should_reduce_now():
+                if u.grads_ready < u.grads_expected and not self.ignore_unused_parameters:
+                    raise RuntimeError(f"{u.name}: {u.grads_expected - u.grads_ready} parameters received no gradient")
+                self._reduce_unit(u)
+        if self.coordinator is not None:
+            self.coordinator.on_backward_end()
+        for u in self.units:
+            u.grads_ready = 0
+            u.reduced_this_pass = False
+            if u.full_grad is not None:
+                u.has_grad_data = True
+        if self._use_streams and self.overlap_comm:
+            torch.cuda.current_stream().wait_stream(self.rs_stream)
+        self._in_backward = False
+        self.micro_step_id += 1
+
+    def reduce_gradients(self, pipeline_parallel=False):
+        """Boundary reduction for stages 0/1 when it was not done inside backward (e.g. after ``no_sync``)."""
+        for u in self.units:
+            if u.full_grad is not None:
+                u.reduced_this_pass = False
+                self._reduce_unit(u)
+                u.reduced_this_pass = False
+        if self._use_streams and self.overlap_comm:
+            torch.cuda.current_stream().wait_stream(self.rs_stream)
+
+    def scale_if_loss(self, value):
+        if torch.is_tensor(value) and self.lp_dtype == torch.float16:
+            scale = self.external_loss_scale if self.custom_loss_scaler else self.loss_scaler.loss_scale
+            return value * scale
+        return value
+
+    def backward(self, loss, retain_graph=False):
+        """Standalone use (engine normally drives prologue/epilogue itself)."""
+        self.backward_prologue()
+        self.scale_if_loss(loss).backward(retain_graph=retain_graph)
+        self.backward_epilogue()
+
+    @property
+    def cur_scale(self):
+        return self.external_loss_scale if self.custom_loss_scaler else self.loss_scaler.cur_scale
+
+    loss_scale = cur_scale
+
+    # ------------------------------------------------------------------ norms ------------------
+    @torch.no_grad()
+    def _global_grad_norm_sq(self):
+        """Sum of squares of all reduced grad shards across shard groups (+ model-parallel group)."""
+        total = None
+        for key, st in self.storages.items():
+            g = st.grad
+            if self.mp_group is not None and dist.get_world_size(self.mp_group) > 1:
+                sq = self._mp_aware_sq(st)
+            else:
+                sq = _sumsq(g)
+            u0 = st.units[0]
+            if u0.world > 1:
+                dist.all_reduce(sq, group=u0.dp_group)
+            total = sq if total is None else total + sq.to(total.device)
+        if total is None:
+            total = torch.zeros((), dtype=torch.float32)
+        if self.mp_group is not None and dist.get_world_size(self.mp_group) > 1:
+            dist.all_reduce(total, group=self.mp_group)
+        return total
+
+    def _mp_aware_sq(self, st):
+        """Replicated (non tensor-parallel) params are counted on mp-rank 0 only (reference runtime/utils.py:906)."""
+        mp_rank = dist.get_rank(self.mp_group)
+        sq = torch.zeros((), dtype=torch.float32, device=st.grad.device)
+        for u in st.units:
+            for (i, _, s_in_shard, n) in u.param_fragments():
+                p = u.params[i]
+                is_mp = getattr(p, "tensor_model_parallel", False) or getattr(p, "model_parallel", False) or \
+                    getattr(p, "ds_tp_sharded", False)
+                if is_mp or mp_rank == 0:
+                    sq += _sumsq(u.grad_shard[s_in_shard:s_in_shard + n])
+        return sq
+
+    def get_global_grad_norm(self):
+        return self._global_grad_norm
+
+    # ------------------------------------------------------------------ step -------------------
+    @instrument_w_nvtx
+    @torch.no_grad()
+    def step(self, closure=None):
+        """Partitioned optimizer step. Returns nothing; sets ``self.overflow`` when the step was skipped."""
+        if self._use_streams and self.overlap_comm:
+            torch.cuda.current_stream().wait_stream(self.rs_stream)
+        # any unit still holding unreduced grads (stage<=1 boundary without hooks, no_sync exit)
+        for u in self.units:
+            if u.full_grad is not None and u.has_grad_data:
+                u.reduced_this_pass = False
+                self.is_gradient_accumulation_boundary = True
+                self._reduce_unit(u)
+                u.reduced_this_pass = False
+        if self._use_streams and self.overlap_comm:
+            torch.cuda.current_stream().wait_stream(self.rs_stream)
+
+        norm_sq = self._global_grad_norm_sq()
+        scale = float(self.cur_scale)
+        check_overflow = self.lp_dtype == torch.float16
+        need_norm_host = check_overflow or self.clip_grad > 0 or True
+        norm = float(norm_sq.sqrt()) if need_norm_host else 0.0  # one host sync per step (same as the reference)
+        self.overflow = check_overflow and (not math.isfinite(norm))
+        if check_overflow:
+            prev = self.loss_scaler.cur_scale
+            if not self.custom_loss_scaler:
+                self.loss_scaler.update_scale(self.overflow)
+            if self.overflow:
+                self.skipped_steps += 1
+                log_dist(
+                    f"[zero] OVERFLOW! Skipping step. Attempted loss scale: {prev}, reducing to "
+                    f"{self.loss_scaler.cur_scale}", [0])
+                self._zero_grad_shards()
+                self._global_grad_norm = float("inf")
+                return
+        self._global_grad_norm = norm / scale
+        combined = scale
+        if self.clip_grad > 0.0:
+            clip = (norm / scale + 1e-6) / self.clip_grad
+            if clip > 1:
+                combined = clip * scale
+        inv = 1.0 / combined
+
+        self._inner_step(inv)
+        self._sync_lp_from_master()
+        self._zero_grad_shards()
+        self._post_step_gather()
+
+    def _inner_step(self, grad_scale):
+        opt = self.optimizer
+        fused = getattr(opt, "supports_flat_step", False) and not self.offload_optimizer
+        if self.offload_optimizer:
+            for key, st in self.storages.items():
+                st.grad_host.copy_(st.grad, non_blocking=True) if st.grad.dtype == torch.float32 else \
+                    st.grad_host.copy_(st.grad.float(), non_blocking=True)
+            if torch.cuda.is_available():
+                torch.cuda.current_stream().synchronize()
+        if fused:
+            lp_map, grads = {}, {}
+            for (key, a, b, gi, u, v) in self._segments:
+                st = self.storages[key]
+                grads[v] = st.grad[a:b]
+                lp_map[v] = self._lp_view(st, u, a, b)
+            opt.step_flat(grads=grads, lp_params=lp_map, grad_scale=grad_scale)
+            self._lp_written_by_step = True
+            return
+        self._lp_written_by_step = False
+        for (key, a, b, gi, u, v) in self._segments:
+            st = self.storages[key]
+            src = st.grad_host[a:b] if self.offload_optimizer else st.grad[a:b]
+            g = src.to(self.master_dtype)
+            if grad_scale != 1.0:
+                g = g * grad_scale if g.data_ptr() == src.data_ptr() else g.mul_(grad_scale)
+            v.grad = g
+        opt.step()
+        for (_, _, _, _, _, v) in self._segments:
+            v.grad = None
+
+    def _lp_view(self, st, u, a, b):
+        if self.partition_params:
+            return st.lp[a:b]
+        off = a - u.shard_offset
+        return u.param_shard[off:off + (b - a)]
+
+    @torch.no_grad()
+    def _sync_lp_from_master(self):
+        if getattr(self, "_lp_written_by_step", False):
+            if self.partition_params:
+                for u in self.units:
+                    if u.persistent:
+                        st = self.storages[(u.group_key, u.dtype)]
+                        u.param_shard.copy_(st.lp[u.shard_offset:u.shard_offset + u.shard_numel])
+            return
+        for key, st in self.storages.items():
+            if self.partition_params:
+                if self.offload_optimizer:
+                    st.lp_host.copy_(st.master)
+                    st.lp.copy_(st.lp_host, non_blocking=True)
+                else:
+                    st.lp.copy_(st.master)
+                for u in st.units:
+                    if u.persistent:
+                        u.param_shard.copy_(st.lp[u.shard_offset:u.shard_offset + u.shard_numel])
+            else:
+                if self.offload_optimizer:
+                    st.lp_host.copy_(st.master)
+                for u in st.units:
+                    a, b = u.shard_offset, u.shard_offset + u.shard_numel
+                    src = st.lp_host[a:b] if self.offload_optimizer else st.master[a:b]
+                    u.param_shard.copy_(src, non_blocking=True)
+
+    @torch.no_grad()
+    def _post_step_gather(self):
+        """All-gather updated lp shards of resident units (reference ``all_gather_dp_groups`` utils.py:1016)."""
+        for u in self.units:
+            if u.full_param is None or u.world <= 1:
+                continue
+            self._all_gather_into(u.full_param, u.param_shard, u)
+        if self.coordinator is not None:
+            self.coordinator.on_step_done()
+
+    def _all_gather_into(self, full, shard, u, async_op=False):
+        if dist.is_initialized() and dist.get_backend(u.dp_group) == "gloo":
+            shard = shard.clone()
+        return dist.all_gather_into_tensor(full, shard, group=u.dp_group, async_op=async_op)
+
+    def _zero_grad_shards(self):
+        for st in self.storages.values():
+            st.grad.zero_()
+        for u in self.units:
+            u._shard_has_data = False
+
+    def zero_grad(self, set_to_none=True):
+        for u in self.units:
+            for p in u.params:
+                p.grad = None
+            if self.partition_grads or True:
+                u.full_grad = None
+                u.has_grad_data = False
+        self.micro_step_id = 0
+
+    # ------------------------------------------------------------------ fragment / debug API ---
+    def _gather_shard_tensor(self, u, shard):
+        """Full flat tensor (all ranks' shards) for a unit from the given per-rank shard tensor."""
+        if u.world <= 1:
+            return shard.clone()
+        dev = u.device
+        s = shard.to(dev)
+        out = torch.empty(u.numel_padded, dtype=s.dtype, device=dev)
+        dist.all_gather_into_tensor(out, s.contiguous(), group=u.dp_group)
+        return out
+
+    def get_full_hp_param(self, param, optim_state_key=None):
+        """``safe_get_full_fp32_param`` / ``safe_get_full_optimizer_state`` backend (collective call)."""
+        u, i = self._unit_of_param[id(param)]
+        if optim_state_key is None:
+            shard = u.master_shard
+        else:
+            shard = self._state_shard(u, optim_state_key)
+            if shard is None:
+                return None
+        full = self._gather_shard_tensor(u, shard)
+        o, n = u.offsets[i], u.numels[i]
+        return full[o:o + n].view(u.shapes[i]).float()
+
+    def get_full_grad(self, param):
+        u, i = self._unit_of_param[id(param)]
+        full = self._gather_shard_tensor(u, u.grad_shard)
+        o, n = u.offsets[i], u.numels[i]
+        return full[o:o + n].view(u.shapes[i]).float() / float(self.cur_scale)
+
+    def set_full_hp_param(self, value, param, optim_state_key=None):
+        u, i = self._unit_of_param[id(param)]
+        flat = value.reshape(-1)
+        for (pi, s_in_p, s_in_shard, n) in u.param_fragments():
+            if pi != i:
+                continue
+            dst = u.master_shard if optim_state_key is None else self._state_shard(u, optim_state_key)
+            dst[s_in_shard:s_in_shard + n].copy_(flat[s_in_p:s_in_p + n].to(dst.dtype))
+            if optim_state_key is None:
+                lp = self.storages[(u.group_key, u.dtype)].lp
+                if lp is not None:
+                    lp[u.shard_offset + s_in_shard:u.shard_offset + s_in_shard + n].copy_(flat[s_in_p:s_in_p + n])
+                if u.full_param is not None:
+                    u.param_shard[s_in_shard:s_in_shard + n].copy_(flat[s_in_p:s_in_p + n])
+        if optim_state_key is None and u.full_param is not None and u.world > 1:
+            self._all_gather_into(u.full_param, u.param_shard, u)
+
+    def _state_shard(self, u, key):
+        """Assemble the optimizer-state shard of a unit from the per-run views held by the inner optimizer."""
+        out = torch.zeros(u.shard_numel, dtype=torch.float32, device=u.master_shard.device)
+        found = False
+        for (skey, a, b, gi, uu, v) in self._segments:
+            if uu is not u:
+                continue
+            stt = self.optimizer.state.get(v, {})
+            if key in stt and torch.is_tensor(stt[key]) and stt[key].numel() == b - a:
+                out[a - u.shard_offset:b - u.shard_offset].copy_(stt[key].view(-1))
+                found = True
+        return out if found else None
+
+    # ------------------------------------------------------------------ state dict -------------
+    def _inner_state_flat(self):
+        """Inner optimizer state as {key: {storage_key: flat tensor}} + per-group scalar state."""
+        tens, scalars = {}, {}
+        for (skey, a, b, gi, u, v) in self._segments:
+            stt = self.optimizer.state.get(v, {})
+            for k, val in stt.items():
+                if torch.is_tensor(val) and val.numel() == b - a:
+                    st = self.storages[skey]
+                    flat = tens.setdefault(k, {}).setdefault(
+                        _skey_str(skey), torch.zeros(st.numel, dtype=val.dtype, device=val.device))
+                    flat[a:b].copy_(val.view(-1))
+                else:
+                    scalars.setdefault(gi, {})[k] = val.item() if torch.is_tensor(val) else val
+        return tens, scalars
+
+    def state_dict(self):
+        tens, scalars = self._inner_state_flat()
+        pg = []
+        for g in self.optimizer.param_groups:
+            pg.append({k: v for k, v in g.items() if k != "params"})
+        sd = {
+            LOSS_SCALER: self.loss_scaler,
+            DYNAMIC_LOSS_SCALE: self.dynamic_loss_scale,
+            OVERFLOW: self.overflow,
+            CLIP_GRAD: self.clip_grad,
+            ZERO_STAGE: self.stage,
+            PARTITION_COUNT: self._shard_world,
+            DS_VERSION: _ds_version(),
+            "skipped_steps": self.skipped_steps,
+            "fp32_flat": {_skey_str(k): st.master.detach().cpu().clone() for k, st in self.storages.items()},
+            "state_flat": {k: {sk: t.detach().cpu() for sk, t in d.items()} for k, d in tens.items()},
+            "state_scalars": scalars,
+            "param_groups": pg,
+            UNIT_LAYOUT: self.layout_metadata(),
+        }
+        return sd
+
+    def layout_metadata(self):
+        """Everything an offline tool needs to rebuild full tensors from rank shards."""
+        units = []
+        for u in self.units:
+            units.append(dict(uid=u.uid, name=u.name, group_key=u.group_key, dtype=str(u.dtype), world=u.world,
+                              numel=u.numel, numel_padded=u.numel_padded, shard_numel=u.shard_numel,
+                              shard_offset=u.shard_offset, names=list(u.names), shapes=[list(s) for s in u.shapes],
+                              offsets=list(u.offsets), numels=list(u.numels), group_ids=list(u.param_group_ids),
+                              persistent=u.persistent))
+        return dict(units=units, stage=self.stage, shard_world=self._shard_world, shard_rank=self._shard_rank)
+
+    def load_state_dict(self, sd, load_optimizer_states=True, load_from_fp32_weights=True, **kw):
+        if isinstance(sd, (list, tuple)):  # list of per-rank dicts (reference passes all ranks' states)
+            sd = sd[self._shard_rank] if len(sd) > 1 else sd[0]
+        self.loss_scaler = sd.get(LOSS_SCALER, self.loss_scaler)
+        self.dynamic_loss_scale = sd.get(DYNAMIC_LOSS_SCALE, self.dynamic_loss_scale)
+        self.overflow = sd.get(OVERFLOW, False)
+        self.skipped_steps = sd.get("skipped_steps", 0)
+        saved_world = sd.get(PARTITION_COUNT, self._shard_world)
+        if saved_world != self._shard_world:
+            raise RuntimeError(f"ZeRO checkpoint was saved with shard world {saved_world}, current is "
+                               f"{self._shard_world}; use the universal checkpoint path to reshape")
+        if load_from_fp32_weights and "fp32_flat" in sd:
+            for k, st in self.storages.items():
+                st.master.copy_(sd["fp32_flat"][_skey_str(k)].to(st.master.dtype))
+            self._lp_written_by_step = False
+            self._sync_lp_from_master()
+            self._post_step_gather()
+        if load_optimizer_states:
+            for g, saved in zip(self.optimizer.param_groups, sd.get("param_groups", [])):
+                g.update(saved)
+            tens, scalars = sd.get("state_flat", {}), sd.get("state_scalars", {})
+            for (skey, a, b, gi, u, v) in self._segments:
+                stt = self.optimizer.state[v]
+                for k, d in tens.items():
+                    src = d[_skey_str(skey)][a:b]
+                    stt[k] = src.to(v.device).clone().view_as(v)
+                for k, val in scalars.get(gi, scalars.get(str(gi), {})).items():
+                    stt[k] = torch.tensor(float(val)) if k == "step" and _step_is_tensor(self.optimizer) else val
+            if hasattr(self.optimizer, "on_state_loaded"):
+                self.optimizer.on_state_loaded()
+
+    def refresh_lp_from_params(self):
+        """After module weights were loaded directly into the lp params: rebuild master shards."""
+        with torch.no_grad():
+            for u in self.units:
+                if u.full_param is None:
+                    continue
+                s, e = u.shard_range()
+                u.master_shard.copy_(u.full_param[s:e].to(self.master_dtype))
+
+    # ------------------------------------------------------------------ offload_states ---------
+    def offload_states(self, include=None, device="cpu", pin_memory=True, non_blocking=False):
+        """Move optimizer-side state to host to free HBM between phases (reference stage_1_and_2.py:2915)."""
+        include = set(include) if include is not None else {"optim_states", "hp_params", "lp_grads"}
+        include = {getattr(i, "value", i) for i in include}
+        dev = torch.device(device)
+        if "hp_params" in include:
+            for st in self.storages.values():
+                self._move_flat(st, "master", dev, pin_memory)
+            self._offloaded_states.add("hp_params")
+        if "lp_grads" in include:
+            for st in self.storages.values():
+                self._move_flat(st, "grad", dev, pin_memory)
+            self._offloaded_states.add("lp_grads")
+        if "optim_states" in include:
+            for v, stt in self.optimizer.state.items():
+                for k, t in list(stt.items()):
+                    if torch.is_tensor(t) and t.numel() > 1:
+                        stt[k] = t.to(dev)
+            self._offloaded_states.add("optim_states")
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+            torch.cuda.empty_cache()
+
+    def reload_states(self, non_blocking=False):
+        for st in self.storages.values():
+            if "hp_params" in self._offloaded_states:
+                self._move_flat(st, "master", st.state_device, False)
+            if "lp_grads" in self._offloaded_states:
+                self._move_flat(st, "grad", st.device, False)
+        if "optim_states" in self._offloaded_states:
+            for (skey, a, b, gi, u, v) in self._segments:
+                stt = self.optimizer.state.get(v, {})
+                for k, t in list(stt.items()):
+                    if torch.is_tensor(t) and t.numel() > 1:
+                        stt[k] = t.to(v.device)
+        self._offloaded_states.clear()
+
+    def _move_flat(self, st, attr, dev, pin):
+        """Move a flat buffer and re-point every view that aliases it."""
+        old = getattr(st, attr)
+        new = old.to(dev)
+        setattr(st, attr, new)
+        for u in st.units:
+            a, b = u.shard_offset, u.shard_offset + u.shard_numel
+            if attr == "master":
+                u.master_shard = new[a:b]
+            else:
+                u.grad_shard = new[a:b]
+        if attr == "master":
+            # optimizer param views must alias the new storage, preserving their state entries
+            for idx, (skey, a, b, gi, u, v) in enumerate(self._segments):
+                if self.storages[skey] is not st:
+                    continue
+                nv = new[a:b]
+                nv.requires_grad_(True)
+                stt = self.optimizer.state.pop(v, None)
+                if stt is not None:
+                    self.optimizer.state[nv] = stt
+                plist = self.optimizer.param_groups[gi]["params"]
+                for j, t in enumerate(plist):
+                    if t is v:
+                        plist[j] = nv
+                self._segments[idx] = (skey, a, b, gi, u, nv)
+
+    # ------------------------------------------------------------------ misc -------------------
+    def destroy(self):
+        for h in getattr(self, "_hook_handles", []):
+            h.remove()
+        if self.coordinator is not None:
+            self.coordinator.remove_hooks()
+
+    def estimate_memory(self):
+        n = sum(st.numel for st in self.storages.values())
+        return dict(shard_elems=n, master_bytes=n * _esize(self.master_dtype), grad_bytes=n * _esize(self.grad_accum_dtype))
+
+
+def _esize(dt):
+    return torch.empty((), dtype=dt).element_size()
+
+
+def _sumsq(t):
+    """fp32 sum of squares of a flat tensor (fused sm_100a kernel on CUDA, torch on CPU)."""
+    if t.numel() == 0:
+        return torch.zeros((), dtype=torch.float32, device=t.device)
+    if t.is_cuda:
+        from ...ops import kernels
+        if kernels.available():
+            return kernels.sumsq(t)
+    return t.float().pow(2).sum()
+
+
+def _skey_str(k):
+    return f"{k[0]}|{str(k[1]).replace('torch.', '')}"
+
+
+def _ds_version():
+    from ...version import __version__
+    return __version__
+
+
+def _step_is_tensor(opt):
+    for stt in opt.state.values():
+        if "step" in stt:
+            return torch.is_tensor(stt["step"])
+    return False

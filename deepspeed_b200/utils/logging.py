@@ -1,0 +1,85 @@
+"""Rank-aware logging helpers.
+
+Behavioural parity with the reference ``deepspeed/utils/logging.py`` (LoggerFactory :22,
+log_dist :113, print_json_dist :156, warning_once) -- re-implemented, single code path.
+"""
+import functools
+import json
+import logging
+import os
+import sys
+
+LOG_LEVELS = {
+    "debug": logging.DEBUG,
+    "info": logging.INFO,
+    "warning": logging.WARNING,
+    "error": logging.ERROR,
+    "critical": logging.CRITICAL,
+}
+
+
+def _build_logger(name="DeepSpeedB200", level=logging.INFO):
+    lg = logging.getLogger(name)
+    if lg.handlers:
+        return lg
+    lg.setLevel(level)
+    lg.propagate = False
+    h = logging.StreamHandler(stream=sys.stdout)
+    h.setFormatter(
+        logging.Formatter("[%(asctime)s] [%(levelname)s] [%(filename)s:%(lineno)d:%(funcName)s] %(message)s"))
+    lg.addHandler(h)
+    return lg
+
+
+logger = _build_logger(level=LOG_LEVELS.get(os.environ.get("DS_LOG_LEVEL", "info").lower(), logging.INFO))
+
+
+def set_log_level(level):
+    if isinstance(level, str):
+        level = LOG_LEVELS[level.lower()]
+    logger.setLevel(level)
+
+
+def _rank():
+    try:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            return dist.get_rank()
+    except Exception:
+        pass
+    return int(os.environ.get("RANK", 0))
+
+
+def should_log(ranks=None):
+    """True when this process should emit (ranks=None/[-1] means every rank)."""
+    if ranks is None or -1 in ranks:
+        return True
+    return _rank() in set(ranks)
+
+
+def log_dist(message, ranks=None, level=logging.INFO):
+    """Log ``message`` only on the listed ranks (default rank 0 when ranks is None -> all)."""
+    if should_log(ranks):
+        logger.log(level, f"[Rank {_rank()}] {message}")
+
+
+def print_json_dist(message, ranks=None, path=None):
+    """Dump a dict as JSON from the listed ranks, optionally to ``path``."""
+    if should_log(ranks):
+        message = dict(message)
+        message["rank"] = _rank()
+        if path is None:
+            print(json.dumps(message))
+        else:
+            with open(path, "w") as f:
+                json.dump(message, f)
+                os.fsync(f)
+
+
+@functools.lru_cache(None)
+def warning_once(msg):
+    logger.warning(msg)
+
+
+def get_current_level():
+    return logger.getEffectiveLevel()
