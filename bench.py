@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""Headline benchmark: Llama-3-8B, ZeRO-3, bf16, tokens/sec per box at N GPUs (BASELINE.json metric).
+
+Contract (driver): ``python bench.py --gpus N --steps K --warmup W`` (N>1 via torch.distributed.run). Prints ONE
+JSON line on rank 0. ``--impl reference`` runs the unmodified reference (``baseline/_ref``) on a Hugging Face
+Llama of the same architecture through ``deepspeed.initialize`` for the same metric/config.
+
+Two timed regions, K steps each, both bracketed by barrier + cuda synchronize, max over ranks:
+  * ``value``: device-timed (CUDA events), inputs already resident on the device;
+  * ``e2e``  : through the public API with, every step, a pinned-host -> device copy of that step's tokens and a
+               device -> host read of the loss.
+Synthetic data (random tokens), random-init weights. Inputs of consecutive steps are different buffers and every
+step streams >126 MB (weights+optimizer state are >100 GB), so no L2 flush is needed ("inputs larger than L2").
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--seq", type=int, default=4096)
+    ap.add_argument("--mbs", type=int, default=1)
+    ap.add_argument("--layers", type=int, default=32, help="debug only: fewer layers => INVALID headline number")
+    ap.add_argument("--model", default="llama3-8b")
+    ap.add_argument("--zero", type=int, default=3)
+    ap.add_argument("--no-ckpt", action="store_true", help="disable activation checkpointing")
+    ap.add_argument("--local_rank", type=int, default=-1)
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples SM clocks / throttle reasons with nvidia-smi while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.proc, self.gpu_index = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.gpu_index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for n, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def model_dims(args):
+    return dict(vocab_size=128256, hidden_size=4096, intermediate_size=14336, num_hidden_layers=args.layers,
+                num_attention_heads=32, num_key_value_heads=8, max_position_embeddings=8192, rms_norm_eps=1e-5,
+                rope_theta=500000.0)
+
+
+def ds_config(args, world):
+    return {
+        "train_micro_batch_size_per_gpu": args.mbs,
+        "gradient_accumulation_steps": 1,
+        "steps_per_print": 10**9,
+        "bf16": {"enabled": True},
+        "gradient_clipping": 1.0,
+        "optimizer": {"type": "AdamW", "params": {"lr": 1e-5, "betas": [0.9, 0.95], "eps": 1e-8, "weight_decay": 0.1}},
+        "zero_optimization": {"stage": args.zero, "overlap_comm": True, "contiguous_gradients": True,
+                              "reduce_bucket_size": 5e8, "stage3_prefetch_bucket_size": 5e8,
+                              "stage3_param_persistence_threshold": 1e5, "stage3_max_live_parameters": 1e9,
+                              "stage3_max_reuse_distance": 1e9},
+    }
+
+
+def build_ours(args, torch, world):
+    sys.path.insert(0, REPO)
+    import deepspeed_b200 as ds
+    from deepspeed_b200.models import LlamaConfig, LlamaForCausalLM
+    dev = torch.device("cuda", torch.cuda.current_device())
+    cfg = LlamaConfig(**model_dims(args), gradient_checkpointing=not args.no_ckpt, dtype=torch.bfloat16)
+    torch.manual_seed(1234)
+    model = LlamaForCausalLM(cfg, device=dev)
+    engine, _, _, _ = ds.initialize(model=model, config=ds_config(args, world))
+
+    def step(ids):
+        loss = engine(ids, labels=ids)
+        engine.backward(loss)
+        engine.step()
+        return loss
+
+    def launches():
+        from deepspeed_b200.ops import kernels
+        return kernels.launch_count()
+
+    return step, launches, cfg.num_params()
+
+
+def build_reference(args, torch, world):
+    ref = os.path.join(REPO, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref, "deepspeed")):
+        return None, "baseline/_ref missing: reference not installed"
+    sys.path.insert(0, ref)
+    os.environ.setdefault("TORCH_CUDA_ARCH_LIST", "10.0")
+    os.environ.setdefault("DS_SKIP_CUDA_CHECK", "1")
+    try:
+        import deepspeed
+        from transformers import LlamaConfig, LlamaForCausalLM
+    except Exception as e:  # noqa: BLE001
+        return None, f"reference import failed: {type(e).__name__}: {e}"
+    dims = model_dims(args)
+    hf_cfg = LlamaConfig(**dims, tie_word_embeddings=False, attention_bias=False, use_cache=False,
+                         attn_implementation="sdpa")
+    torch.manual_seed(1234)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    old = torch.get_default_dtype()
+    torch.set_default_dtype(torch.bfloat16)
+    try:
+        with torch.device(dev):
+            model = LlamaForCausalLM(hf_cfg)
+    finally:
+        torch.set_default_dtype(old)
+    if not args.no_ckpt:
+        model.gradient_checkpointing_enable(gradient_checkpointing_kwargs={"use_reentrant": False})
+    model.train()
+    cfg = ds_config(args, world)
+    try:
+        engine, _, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config=cfg)
+    except Exception as e:  # FusedAdam JIT build can fail offline -> reference's own torch_adam switch
+        cfg["optimizer"]["params"]["torch_adam"] = True
+        engine, _, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config=cfg)
+
+    def step(ids):
+        out = engine(input_ids=ids, labels=ids)
+        loss = out.loss
+        engine.backward(loss)
+        engine.step()
+        return loss
+
+    return (step, lambda: 0, sum(p.ds_numel if hasattr(p, "ds_numel") else p.numel() for p in model.parameters())), None
+
+
+def main():
+    args = parse()
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    rank = int(os.environ.get("RANK", 0))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference" and not os.path.isdir(os.path.join(REPO, "baseline", "_ref", "deepspeed")):
+        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref not present (reference not installed)"}))
+        return 0
+    import torch
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device"}))
+        return 0
+    torch.cuda.set_device(local_rank)
+    import torch.distributed as dist
+    if world > 1 or "RANK" in os.environ:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+    if not dist.is_initialized():
+        os.environ.setdefault("RANK", "0"), os.environ.setdefault("WORLD_SIZE", "1")
+        os.environ.setdefault("LOCAL_RANK", "0"), os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+
+    if args.impl == "ours":
+        step, launches, nparams = build_ours(args, torch, world)
+    else:
+        built, err = build_reference(args, torch, world)
+        if built is None:
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": err}))
+            return 0
+        step, launches, nparams = built
+
+    dev = torch.device("cuda", local_rank)
+    K, W, B, S = args.steps, args.warmup, args.mbs, args.seq
+    g = torch.Generator().manual_seed(1000 + rank)
+    n_buf = W + 2 * K
+    host = [torch.randint(0, 128256, (B, S), generator=g, dtype=torch.int64).pin_memory() for _ in range(n_buf)]
+    dev_inputs = [h.to(dev) for h in host[W:W + K]]
+
+    def sync_all():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(W):
+        loss = step(host[i].to(dev, non_blocking=True))
+    float(loss)
+    sync_all()
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    # ---- region 1: device-timed ----
+    l0 = launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    e0.record()
+    for i in range(K):
+        loss = step(dev_inputs[i])
+    e1.record()
+    sync_all()
+    dev_ms = e0.elapsed_time(e1)
+    n_launch = launches() - l0
+    last_loss = float(loss)
+    # ---- region 2: end to end (pinned H2D each step + loss D2H each step) ----
+    sync_all()
+    t0 = time.perf_counter()
+    for i in range(K):
+        ids = host[W + K + i].to(dev, non_blocking=True)
+        loss = step(ids)
+        last_loss = loss.item()
+    sync_all()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    tokens = world * B * S * K
+    value = tokens / (dev_ms / 1e3)
+    e2e_value = tokens / (e2e_ms / 1e3)
+    peak_mem = torch.cuda.max_memory_allocated() / 2**30
+    if rank == 0:
+        baseline = None
+        try:
+            with open(os.path.join(REPO, "BASELINE.json")) as f:
+                pub = json.load(f).get("published", {})
+            baseline = pub.get("tokens_per_sec") if isinstance(pub, dict) else None
+        except Exception:
+            pass
+        out = {
+            "metric": "tokens/sec/box Llama-3-8B ZeRO-3 (max over ranks)",
+            "impl": args.impl,
+            "value": value,
+            "unit": "tokens/s",
+            "n_gpus": world,
+            "steps": K,
+            "warmup": W,
+            "ms_per_step": dev_ms / K,
+            "higher_is_better": True,
+            "scaling": "weak",
+            "vs_baseline": (value / baseline) if baseline else None,
+            "dtype": "bf16",
+            "data": "synthetic random tokens, random-init weights",
+            "config": {"model": f"Llama-3-8B ({args.layers} layers, h4096, 32q/8kv heads, ffn14336, vocab128256)",
+                       "params": nparams, "global_batch": world * B, "seq_len": S,
+                       "parallelism": f"zero{args.zero}-dp{world}", "activation_checkpointing": not args.no_ckpt,
+                       "optimizer": "AdamW (fused)", "grad_clip": 1.0,
+                       "l2": "inputs larger than L2 (per-step working set >100 GB), no flush needed"},
+            "e2e": {"value": e2e_value, "unit": "tokens/s", "ms_per_step": e2e_ms / K,
+                    "h2d_bytes_per_step": B * S * 8, "d2h_bytes_per_step": 4},
+            "gpu_launches": n_launch,
+            "clocks": clocks,
+            "final_loss": last_loss,
+            "peak_mem_gib": round(peak_mem, 2),
+        }
+        if args.layers != 32:
+            out["INVALID"] = "reduced layer count (debug run)"
+        print(json.dumps(out))
+    dist.barrier()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,260 @@
+"""Autograd front-ends of the fused sm_100a training ops: RMSNorm, LayerNorm, RoPE, SwiGLU, linear+cross-entropy.
+
+On CUDA every function dispatches to ``libdsb200.so`` (raises if the library is missing); on CPU (plumbing tests)
+the same math runs in plain PyTorch so models are device-agnostic.
+"""
+import math
+
+import torch
+import torch.nn.functional as F
+
+from . import kernels as K
+
+
+def _use_cuda(x):
+    return x.is_cuda and K.available() and x.dtype in (torch.bfloat16, torch.float16)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# RMSNorm (+ fused residual add)
+# ---------------------------------------------------------------------------------------------------------
+class _RMSNormFn(torch.autograd.Function):
+
+    @staticmethod
+    def forward(ctx, x, weight, eps, residual):
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        x2 = x2 if x2.is_contiguous() else x2.contiguous()
+        res2 = None
+        if residual is not None:
+            res2 = residual.reshape(-1, shape[-1])
+            res2 = res2 if res2.is_contiguous() else res2.contiguous()
+        y, res_out, rstd = K.rmsnorm_fwd(x2, res2, weight, eps)
+        ctx.save_for_backward(res_out if residual is not None else x2, weight, rstd)
+        ctx.has_res = residual is not None
+        ctx.shape = shape
+        if residual is not None:
+            return y.view(shape), res_out.view(shape)
+        return y.view(shape), None
+
+    @staticmethod
+    def backward(ctx, dy, dres):
+        xin, weight, rstd = ctx.saved_tensors
+        dy2 = dy.reshape(-1, ctx.shape[-1])
+        dy2 = dy2 if dy2.is_contiguous() else dy2.contiguous()
+        dres2 = None
+        if ctx.has_res and dres is not None:
+            dres2 = dres.reshape(-1, ctx.shape[-1])
+            dres2 = dres2 if dres2.is_contiguous() else dres2.contiguous()
+        dx, dw = K.rmsnorm_bwd(dy2, xin, weight, rstd, dres2)
+        dx = dx.view(ctx.shape)
+        return dx, dw, None, (dx if ctx.has_res else None)
+
+
+def rms_norm(x, weight, eps=1e-6, residual=None):
+    """``y = rmsnorm(x [+ residual]) * weight``. With ``residual`` returns ``(y, x + residual)``."""
+    if _use_cuda(x):
+        y, r = _RMSNormFn.apply(x, weight, eps, residual)
+        return (y, r) if residual is not None else y
+    if residual is not None:
+        x = x + residual
+    xf = x.float()
+    y = (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps)).to(x.dtype) * weight
+    return (y, x) if residual is not None else y
+
+
+class _LayerNormFn(torch.autograd.Function):
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps):
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        x2 = x2 if x2.is_contiguous() else x2.contiguous()
+        y, stats = K.layernorm_fwd(x2, weight, bias, eps)
+        ctx.save_for_backward(x2, weight, stats)
+        ctx.shape, ctx.has_bias = shape, bias is not None
+        return y.view(shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight, stats = ctx.saved_tensors
+        dy2 = dy.reshape(-1, ctx.shape[-1])
+        dy2 = dy2 if dy2.is_contiguous() else dy2.contiguous()
+        dx, dw, db = K.layernorm_bwd(dy2, x2, weight, stats, ctx.has_bias)
+        return dx.view(ctx.shape), dw, db, None
+
+
+def layer_norm(x, weight, bias=None, eps=1e-5):
+    if _use_cuda(x):
+        return _LayerNormFn.apply(x, weight, bias, eps)
+    return F.layer_norm(x, (x.shape[-1], ), weight, bias, eps)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# RoPE
+# ---------------------------------------------------------------------------------------------------------
+def rope_tables(seq_len, dim, base=10000.0, device=None, scaling=None):
+    """fp32 cos/sin tables [seq_len, dim/2]. ``scaling``: optional dict for Llama-3 style frequency scaling."""
+    inv = 1.0 / (base**(torch.arange(0, dim, 2, dtype=torch.float32, device=device) / dim))
+    if scaling and scaling.get("rope_type", scaling.get("type")) == "llama3":
+        factor, lo, hi = scaling["factor"], scaling["low_freq_factor"], scaling["high_freq_factor"]
+        old = scaling["original_max_position_embeddings"]
+        wavelen = 2 * math.pi / inv
+        smooth = ((old / wavelen) - lo) / (hi - lo)
+        scaled = torch.where(wavelen > old / lo, inv / factor, inv)
+        mid = (wavelen <= old / lo) & (wavelen >= old / hi)
+        inv = torch.where(mid, (1 - smooth) * inv / factor + smooth * inv, scaled)
+    t = torch.arange(seq_len, dtype=torch.float32, device=device)
+    fr = torch.outer(t, inv)
+    return fr.cos().contiguous(), fr.sin().contiguous()
+
+
+class _RopeFn(torch.autograd.Function):
+
+    @staticmethod
+    def forward(ctx, x, cos, sin, pos, seq_len):
+        ctx.save_for_backward(cos, sin, pos if pos is not None else torch.empty(0))
+        ctx.has_pos, ctx.seq_len = pos is not None, seq_len
+        out = x.clone() if not x.is_contiguous() else x.clone()
+        K.rope_(out, cos, sin, pos, seq_len, backward=False)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        cos, sin, pos = ctx.saved_tensors
+        g = dout.contiguous().clone()
+        K.rope_(g, cos, sin, pos if ctx.has_pos else None, ctx.seq_len, backward=True)
+        return g, None, None, None, None
+
+
+def _rope_torch(x, cos, sin, pos, seq_len):
+    # x: [B, S, H, D]
+    B, S, H, D = x.shape
+    if pos is None:
+        c, s = cos[:S], sin[:S]
+        c, s = c.view(1, S, 1, D // 2), s.view(1, S, 1, D // 2)
+    else:
+        c, s = cos[pos.view(B, S)].view(B, S, 1, D // 2), sin[pos.view(B, S)].view(B, S, 1, D // 2)
+    x1, x2 = x[..., :D // 2].float(), x[..., D // 2:].float()
+    return torch.cat([x1 * c - x2 * s, x2 * c + x1 * s], dim=-1).to(x.dtype)
+
+
+def apply_rope(x, cos, sin, position_ids=None):
+    """Half-rotation RoPE on ``x`` [B, S, H, D] (HF Llama convention). ``position_ids``: int [B, S] or None."""
+    if _use_cuda(x):
+        pos = position_ids.reshape(-1).to(torch.int32) if position_ids is not None else None
+        return _RopeFn.apply(x, cos, sin, pos, x.shape[1])
+    return _rope_torch(x, cos, sin, position_ids, x.shape[1])
+
+
+# ---------------------------------------------------------------------------------------------------------
+# SwiGLU
+# ---------------------------------------------------------------------------------------------------------
+class _SwiGLUFn(torch.autograd.Function):
+
+    @staticmethod
+    def forward(ctx, gate_up):
+        ctx.save_for_backward(gate_up)
+        return K.swiglu_fwd(gate_up)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (gate_up, ) = ctx.saved_tensors
+        return K.swiglu_bwd(dy.contiguous(), gate_up)
+
+
+def swiglu(gate_up):
+    """``silu(gate) * up`` where ``gate_up = [..., 2*I]`` holds gate in the first half, up in the second."""
+    if _use_cuda(gate_up) and gate_up.is_contiguous():
+        return _SwiGLUFn.apply(gate_up)
+    g, u = gate_up.chunk(2, dim=-1)
+    return F.silu(g) * u
+
+
+# ---------------------------------------------------------------------------------------------------------
+# fused (chunked) linear + cross entropy: never materialises [tokens, vocab] in fp32
+# ---------------------------------------------------------------------------------------------------------
+class _LinearCrossEntropyFn(torch.autograd.Function):
+    """loss = mean CE(h @ W^T, target). Gradients wrt h and W are produced during the forward pass, chunk by
+    chunk (logits chunk -> in-place softmax-grad -> two GEMMs), so backward only rescales them."""
+
+    @staticmethod
+    def forward(ctx, h, weight, target, ignore_index, chunk_tokens, reduction_tokens):
+        N, H = h.shape
+        V = weight.shape[0]
+        valid = (target != ignore_index)
+        denom = reduction_tokens if reduction_tokens is not None else valid.sum().clamp(min=1)
+        inv = 1.0 / denom if not torch.is_tensor(denom) else (1.0 / denom.float())
+        need_h, need_w = h.requires_grad, weight.requires_grad
+        dh = torch.empty_like(h) if need_h else None
+        main_grad = getattr(weight, "_ds_grad_view", None)
+        dw = None
+        if need_w:
+            dw = torch.zeros(V, H, dtype=torch.float32 if main_grad is None else weight.dtype, device=h.device) \
+                if main_grad is None else None
+        loss_sum = torch.zeros((), dtype=torch.float32, device=h.device)
+        inv_f = float(inv) if not torch.is_tensor(inv) else None
+        for s in range(0, N, chunk_tokens):
+            e = min(N, s + chunk_tokens)
+            logits = torch.matmul(h[s:e], weight.t())
+            scale = inv_f if inv_f is not None else 1.0
+            loss_rows = K.cross_entropy_inplace_grad(logits, target[s:e], ignore_index, scale)
+            loss_sum += loss_rows.sum()
+            if inv_f is None:
+                logits.mul_(inv.to(logits.dtype))
+            if need_h:
+                torch.matmul(logits, weight, out=dh[s:e])
+            if need_w:
+                if dw is not None:
+                    dw.add_(torch.matmul(logits.t(), h[s:e]))  # fp32 accumulation across chunks
+                else:
+                    main_grad.addmm_(logits.t(), h[s:e])
+            del logits
+        ctx.save_for_backward(dh if need_h else torch.empty(0), dw if dw is not None else torch.empty(0))
+        ctx.need_h, ctx.need_w, ctx.w_dtype = need_h, need_w and dw is not None, weight.dtype
+        return loss_sum * inv
+
+    @staticmethod
+    def backward(ctx, gloss):
+        dh, dw = ctx.saved_tensors
+        gh = (dh * gloss.to(dh.dtype)) if ctx.need_h else None
+        gw = (dw * gloss).to(ctx.w_dtype) if ctx.need_w else None
+        return gh, gw, None, None, None, None
+
+
+def linear_cross_entropy(h, weight, target, ignore_index=-100, chunk_tokens=4096, reduction_tokens=None):
+    """Mean token cross-entropy of ``h @ weight.T`` against ``target`` without keeping the logits."""
+    h2 = h.reshape(-1, h.shape[-1])
+    t2 = target.reshape(-1)
+    if _use_cuda(h2):
+        return _LinearCrossEntropyFn.apply(h2.contiguous(), weight, t2, ignore_index, chunk_tokens, reduction_tokens)
+    logits = F.linear(h2, weight).float()
+    if reduction_tokens is not None:
+        return F.cross_entropy(logits, t2, ignore_index=ignore_index, reduction="sum") / reduction_tokens
+    return F.cross_entropy(logits, t2, ignore_index=ignore_index)
+
+
+class _CrossEntropyFn(torch.autograd.Function):
+
+    @staticmethod
+    def forward(ctx, logits, target, ignore_index):
+        loss_rows, lse = K.cross_entropy_fwd(logits, target, ignore_index)
+        ctx.save_for_backward(logits, target, lse)
+        ctx.ignore_index = ignore_index
+        return loss_rows
+
+    @staticmethod
+    def backward(ctx, gl):
+        logits, target, lse = ctx.saved_tensors
+        p = torch.exp(logits.float() - lse.unsqueeze(1))
+        valid = (target != ctx.ignore_index)
+        p[torch.arange(p.shape[0], device=p.device)[valid], target[valid]] -= 1.0
+        p = p * (gl * valid).unsqueeze(1)
+        return p.to(logits.dtype), None, None
+
+
+def cross_entropy_rows(logits, target, ignore_index=-100):
+    """Per-row CE loss (fp32) for 16-bit logits [N, V]."""
+    if _use_cuda(logits) and logits.is_contiguous():
+        return _CrossEntropyFn.apply(logits, target, ignore_index)
+    return F.cross_entropy(logits.float(), target, ignore_index=ignore_index, reduction="none")

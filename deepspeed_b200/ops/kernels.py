@@ -76,9 +76,20 @@ def _dt(t):
     return _DT[t.dtype]
 
 
+_LAUNCHES = 0
+_KERNELS_PER_CALL = {"rmsnorm_bwd": 2, "layernorm_bwd": 3, "lamb": 2}
+
+
+def launch_count():
+    """Number of kernels of this library launched so far in this process."""
+    return _LAUNCHES
+
+
 def _check(rc, what):
+    global _LAUNCHES
     if rc != 0:
         raise RuntimeError(f"dsb200 kernel '{what}' failed with code {rc}: {last_error()}")
+    _LAUNCHES += _KERNELS_PER_CALL.get(what, 1)
 
 
 def last_error():
@@ -101,15 +112,14 @@ def _declare(L):
     sig("dsb200_multi_sumsq", P, I, P, P)
     sig("dsb200_multi_tensor_optim", I, P, I, P, I, F, P)
     sig("dsb200_lamb_step", P, P, P, P, P, L64, I, P, P, F, F, F, F, F, F, F, I, F, F, P)
-    sig("dsb200_rmsnorm_fwd", P, P, P, P, P, I, I, F, I, P)
-    sig("dsb200_rmsnorm_bwd", P, P, P, P, P, P, P, I, I, I, P)
-    sig("dsb200_layernorm_fwd", P, P, P, P, P, P, I, I, F, I, P)
-    sig("dsb200_layernorm_bwd", P, P, P, P, P, P, P, P, P, I, I, I, P)
-    sig("dsb200_rope", P, P, P, I, I, I, I, I, I, I, P)
-    sig("dsb200_swiglu_fwd", P, P, P, L64, I, I, P)
-    sig("dsb200_swiglu_bwd", P, P, P, P, P, L64, I, I, P)
-    sig("dsb200_ce_fwd", P, P, P, P, I, I, I, I, P)
-    sig("dsb200_ce_bwd", P, P, P, P, F, I, I, I, I, P)
+    sig("dsb200_rmsnorm_fwd", P, P, P, P, P, P, I, I, F, I, P)
+    sig("dsb200_rmsnorm_bwd", P, P, P, P, P, P, P, P, I, I, I, I, P)
+    sig("dsb200_layernorm_fwd", P, P, P, P, P, P, P, I, I, F, I, P)
+    sig("dsb200_layernorm_bwd", P, P, P, P, P, P, P, P, P, I, I, I, I, P)
+    sig("dsb200_rope", P, P, P, P, I, I, I, L64, I, I, I, P)
+    sig("dsb200_swiglu_fwd", P, P, P, L64, I, L64, I, P)
+    sig("dsb200_swiglu_bwd", P, P, P, P, P, L64, I, L64, I, P)
+    sig("dsb200_ce_fwd", P, P, P, P, I, I, L64, I, I, F, I, P)
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -122,7 +132,7 @@ def _scratch(device, n_float):
     key = (device.index, torch.cuda.current_stream().cuda_stream)
     buf = _SCRATCH.get(key)
     if buf is None or buf.numel() < n_float:
-        buf = torch.empty(max(n_float, 4096), dtype=torch.float32, device=device)
+        buf = torch.zeros(max(n_float, 8192), dtype=torch.float32, device=device)
         _SCRATCH[key] = buf
     return buf
 
@@ -204,3 +214,102 @@ def lamb_step(p, g, m, v, lp, h, coeffs_out):
                                _ptr(scratch), _ptr(scratch[4096:]), h["lr"], h["beta1"], h["beta2"], h["eps"], h["wd"],
                                h["bc1"], h["bc2"], int(h["mode"]), h["max_coeff"], h["min_coeff"], _stream()), "lamb")
     coeffs_out.append(scratch[4096 + 2])
+
+
+# ---------------------------------------------------------------------------------------------------------
+# norms
+# ---------------------------------------------------------------------------------------------------------
+def _norm_grid(rows, cols):
+    return min(rows, 148 * 4)
+
+
+def rmsnorm_fwd(x2, res2, weight, eps):
+    rows, cols = x2.shape
+    y = torch.empty_like(x2)
+    res_out = torch.empty_like(x2) if res2 is not None else None
+    rstd = torch.empty(rows, dtype=torch.float32, device=x2.device)
+    _check(lib().dsb200_rmsnorm_fwd(_ptr(x2), _ptr(res2), _ptr(weight), _ptr(y), _ptr(res_out), _ptr(rstd), rows, cols,
+                                    float(eps), _dt(x2), _stream()), "rmsnorm_fwd")
+    return y, res_out, rstd
+
+
+def rmsnorm_bwd(dy2, x2, weight, rstd, dres2):
+    rows, cols = x2.shape
+    dx = torch.empty_like(x2)
+    dw = torch.empty_like(weight)
+    scratch = _scratch(x2.device, _norm_grid(rows, cols) * cols)
+    _check(lib().dsb200_rmsnorm_bwd(_ptr(dy2), _ptr(x2), _ptr(weight), _ptr(rstd), _ptr(dres2), _ptr(dx), _ptr(dw),
+                                    _ptr(scratch), rows, cols, 0, _dt(x2), _stream()), "rmsnorm_bwd")
+    return dx, dw
+
+
+def layernorm_fwd(x2, weight, bias, eps):
+    rows, cols = x2.shape
+    y = torch.empty_like(x2)
+    stats = torch.empty(rows * 2, dtype=torch.float32, device=x2.device)
+    _check(lib().dsb200_layernorm_fwd(_ptr(x2), c_void_p(0), _ptr(weight), _ptr(bias), _ptr(y), c_void_p(0),
+                                      _ptr(stats), rows, cols, float(eps), _dt(x2), _stream()), "layernorm_fwd")
+    return y, stats
+
+
+def layernorm_bwd(dy2, x2, weight, stats, has_bias):
+    rows, cols = x2.shape
+    dx = torch.empty_like(x2)
+    dw = torch.empty_like(weight)
+    db = torch.empty_like(weight) if has_bias else None
+    scratch = _scratch(x2.device, 2 * _norm_grid(rows, cols) * cols)
+    _check(lib().dsb200_layernorm_bwd(_ptr(dy2), _ptr(x2), _ptr(weight), _ptr(stats), c_void_p(0), _ptr(dx), _ptr(dw),
+                                      _ptr(db), _ptr(scratch), rows, cols, 0, _dt(x2), _stream()), "layernorm_bwd")
+    return dx, dw, db
+
+
+# ---------------------------------------------------------------------------------------------------------
+# rope / swiglu / cross-entropy
+# ---------------------------------------------------------------------------------------------------------
+def rope_(x, cos, sin, pos, seq_len, backward=False):
+    """In-place half-rotation RoPE on contiguous x [B, S, H, D]."""
+    B, S, H, D = x.shape
+    assert x.is_contiguous() and cos.dtype == torch.float32 and cos.shape[-1] == D // 2
+    _check(lib().dsb200_rope(_ptr(x), _ptr(cos), _ptr(sin), _ptr(pos), B * S, H, D, H * D, seq_len,
+                             1 if backward else 0, _dt(x), _stream()), "rope")
+    return x
+
+
+def swiglu_fwd(gate_up):
+    inter = gate_up.shape[-1] // 2
+    rows = gate_up.numel() // (2 * inter)
+    y = torch.empty(gate_up.shape[:-1] + (inter, ), dtype=gate_up.dtype, device=gate_up.device)
+    esz = gate_up.element_size()
+    _check(lib().dsb200_swiglu_fwd(c_void_p(gate_up.data_ptr()), c_void_p(gate_up.data_ptr() + inter * esz), _ptr(y),
+                                   rows, inter, 2 * inter, _dt(gate_up), _stream()), "swiglu_fwd")
+    return y
+
+
+def swiglu_bwd(dy, gate_up):
+    inter = gate_up.shape[-1] // 2
+    rows = gate_up.numel() // (2 * inter)
+    dgu = torch.empty_like(gate_up)
+    esz = gate_up.element_size()
+    _check(lib().dsb200_swiglu_bwd(_ptr(dy), c_void_p(gate_up.data_ptr()), c_void_p(gate_up.data_ptr() + inter * esz),
+                                   c_void_p(dgu.data_ptr()), c_void_p(dgu.data_ptr() + inter * esz), rows, inter,
+                                   2 * inter, _dt(gate_up), _stream()), "swiglu_bwd")
+    return dgu
+
+
+def cross_entropy_inplace_grad(logits, target, ignore_index, grad_scale):
+    """Per-row loss (fp32); ``logits`` is overwritten with ``(softmax - onehot) * grad_scale``."""
+    rows, vocab = logits.shape
+    assert logits.stride(1) == 1
+    loss = torch.empty(rows, dtype=torch.float32, device=logits.device)
+    _check(lib().dsb200_ce_fwd(_ptr(logits), _ptr(target), _ptr(loss), c_void_p(0), rows, vocab, logits.stride(0),
+                               int(ignore_index), 1, float(grad_scale), _dt(logits), _stream()), "ce_fwd")
+    return loss
+
+
+def cross_entropy_fwd(logits, target, ignore_index):
+    rows, vocab = logits.shape
+    loss = torch.empty(rows, dtype=torch.float32, device=logits.device)
+    lse = torch.empty(rows, dtype=torch.float32, device=logits.device)
+    _check(lib().dsb200_ce_fwd(_ptr(logits), _ptr(target), _ptr(loss), _ptr(lse), rows, vocab, logits.stride(0),
+                               int(ignore_index), 0, 1.0, _dt(logits), _stream()), "ce_fwd")
+    return loss, lse
