@@ -145,23 +145,35 @@ def build_reference(args, torch, world):
     dims = model_dims(args)
     hf_cfg = LlamaConfig(**dims, tie_word_embeddings=False, attention_bias=False, use_cache=False,
                          attn_implementation="sdpa")
-    torch.manual_seed(1234)
     dev = torch.device("cuda", torch.cuda.current_device())
-    old = torch.get_default_dtype()
-    torch.set_default_dtype(torch.bfloat16)
-    try:
-        with torch.device(dev):
-            model = LlamaForCausalLM(hf_cfg)
-    finally:
-        torch.set_default_dtype(old)
-    if not args.no_ckpt:
-        model.gradient_checkpointing_enable(gradient_checkpointing_kwargs={"use_reentrant": False})
-    model.train()
+
+    def make_model():
+        torch.manual_seed(1234)
+        old = torch.get_default_dtype()
+        torch.set_default_dtype(torch.bfloat16)
+        try:
+            with torch.device(dev):
+                m = LlamaForCausalLM(hf_cfg)
+        finally:
+            torch.set_default_dtype(old)
+        if not args.no_ckpt:
+            m.gradient_checkpointing_enable(gradient_checkpointing_kwargs={"use_reentrant": False})
+        m.train()
+        return m
+
     cfg = ds_config(args, world)
+    model = make_model()
     try:
         engine, _, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config=cfg)
-    except Exception as e:  # FusedAdam JIT build can fail offline -> reference's own torch_adam switch
+    except Exception as e:  # FusedAdam JIT build can fail offline -> the reference's own torch_adam switch
+        import traceback
+        print(f"[bench] reference initialize failed with its fused optimizer ({type(e).__name__}: {e}); "
+              f"retrying with optimizer.params.torch_adam=true", file=sys.stderr)
+        traceback.print_exc()
+        del model
+        torch.cuda.empty_cache()
         cfg["optimizer"]["params"]["torch_adam"] = True
+        model = make_model()
         engine, _, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config=cfg)
 
     def step(ids):

@@ -1,0 +1,198 @@
+"""Symmetric-memory layer: peer-mapped buffers, NVLS multicast, epoch flags, and the fused collective launchers.
+
+Reference analogue: ``comm/torch.py:455 enable_symm_mem_for_group`` + ``csrc/compile/z3.cpp:95-113`` (barrier ->
+per-peer ``copy_`` -> barrier). Here a :class:`SymmContext` (one per process group) owns
+
+* a symmetric *flag* buffer (epoch counters written with ``st.release.sys`` by peers, see ``csrc/symm.cu``),
+* a pool of symmetric data buffers allocated through ``torch.distributed._symmetric_memory`` (rendezvous gives the
+  peer pointer table and, when the fabric supports it, the NVSwitch multicast pointer),
+* per-channel monotonically increasing epochs (every rank issues the same sequence of collectives per channel).
+
+and the launchers :meth:`reduce_scatter`, :meth:`all_gather`, :meth:`all_to_all` run ONE kernel that moves the
+data over NVLink from inside the kernel and fuses the adjacent elementwise work.
+Availability: CUDA, single NVSwitch domain, world <= 16, ``torch.distributed._symmetric_memory`` usable. Otherwise
+callers use the NCCL path in :mod:`deepspeed_b200.comm.comm` (also the numerical oracle in tests).
+"""
+import ctypes
+import os
+
+import torch
+
+from ..ops import kernels as K
+from ..utils.logging import log_dist, logger
+from . import comm as dist
+
+CH_RS_READY, CH_RS_DONE, CH_AG_READY, CH_AG_DONE, CH_A2A_READY, CH_A2A_DONE, CH_USER = 0, 1, 2, 3, 4, 5, 6
+_CONTEXTS = {}
+
+
+def _declare(L):
+    P, I, L64, F, U = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float, ctypes.c_uint
+    U64 = ctypes.c_uint64
+    L.dsb200_symm_reduce_scatter.argtypes = [P, P, U64, I, I, L64, I, P, I, I, F, P, P, I, I, U, I, P]
+    L.dsb200_symm_reduce_scatter.restype = I
+    L.dsb200_symm_all_gather.argtypes = [P, P, U64, I, I, L64, P, P, P, I, I, U, U, I, P]
+    L.dsb200_symm_all_gather.restype = I
+    L.dsb200_symm_all_to_all.argtypes = [P, P, I, I, L64, L64, I, P, P, I, I, U, I, P]
+    L.dsb200_symm_all_to_all.restype = I
+    L.dsb200_symm_wait.argtypes = [P, I, I, I, U, P]
+    L.dsb200_symm_wait.restype = I
+    L.dsb200_symm_signal.argtypes = [P, I, I, I, U, P]
+    L.dsb200_symm_signal.restype = I
+
+
+def is_supported(group=None):
+    """Can the fused NVLink collectives be used for this group?"""
+    if os.environ.get("DSB200_DISABLE_SYMM", "0") == "1":
+        return False
+    if not (torch.cuda.is_available() and dist.is_initialized()):
+        return False
+    world = dist.get_world_size(group)
+    if world < 2 or world > 16 or dist.get_backend(group) != "nccl":
+        return False
+    try:
+        import torch.distributed._symmetric_memory  # noqa: F401
+    except Exception:
+        return False
+    return K.available()
+
+
+class SymmBuffer:
+    """A symmetric allocation: same size on every rank, every rank can address all copies."""
+
+    def __init__(self, ctx, nbytes, want_multicast=True):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.ctx = ctx
+        self.nbytes = int((nbytes + 255) // 256 * 256)
+        self.tensor = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=ctx.device)
+        self.handle = symm_mem.rendezvous(self.tensor, ctx.group)
+        self.ptrs = (ctypes.c_uint64 * 16)(*([int(p) for p in self.handle.buffer_ptrs] + [0] * (16 - ctx.world)))
+        mc = 0
+        if want_multicast:
+            try:
+                mc = int(self.handle.multicast_ptr or 0) if self.handle.has_multicast_support else 0
+            except Exception:
+                mc = 0
+        self.mc_ptr = mc
+        self.last_rs_epoch = 0  # epoch of the last reduce-scatter that read this buffer
+
+    def view(self, numel, dtype, offset_bytes=0):
+        esz = torch.empty((), dtype=dtype).element_size()
+        return self.tensor[offset_bytes:offset_bytes + numel * esz].view(dtype)
+
+
+class SymmContext:
+
+    def __init__(self, group):
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self.lib = K.lib()
+        _declare(self.lib)
+        self.flags = SymmBuffer(self, 64 * 32 * 4, want_multicast=False)
+        self.flags.tensor.zero_()
+        self.tickets = torch.zeros(64, dtype=torch.int32, device=self.device)
+        self.partials = torch.zeros(64 * 16, dtype=torch.float32, device=self.device)
+        self.epoch = [0] * 64
+        torch.cuda.synchronize()
+        dist.barrier(group=group)
+        self.multicast = False
+        log_dist(f"SymmContext: world={self.world} symmetric memory ready", [0])
+
+    @staticmethod
+    def get(group):
+        key = id(group)
+        if key not in _CONTEXTS:
+            _CONTEXTS[key] = SymmContext(group)
+        return _CONTEXTS[key]
+
+    def alloc(self, nbytes, want_multicast=True):
+        return SymmBuffer(self, nbytes, want_multicast)
+
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def _next(self, ch):
+        self.epoch[ch] += 1
+        return self.epoch[ch]
+
+    # ---- collectives ---------------------------------------------------------------------------
+    def reduce_scatter(self, buf: SymmBuffer, in_dtype, shard_numel, out, accumulate, scale, use_multicast=None,
+                       ctas=0, want_sumsq=False):
+        """out (+)= scale * sum_p buf_p[rank*shard : (rank+1)*shard]. Returns epoch (for DONE waits)."""
+        ep = self._next(CH_RS_READY)
+        mc = buf.mc_ptr if (use_multicast if use_multicast is not None else True) else 0
+        rc = self.lib.dsb200_symm_reduce_scatter(
+            buf.ptrs, self.flags.ptrs, ctypes.c_uint64(mc if in_dtype == torch.bfloat16 else 0), self.rank, self.world,
+            shard_numel, K._DT[in_dtype], ctypes.c_void_p(out.data_ptr()), K._DT[out.dtype], 1 if accumulate else 0,
+            float(scale), ctypes.c_void_p(self.partials.data_ptr()) if want_sumsq else ctypes.c_void_p(0),
+            ctypes.c_void_p(self.tickets.data_ptr()), CH_RS_READY, CH_RS_DONE, ep, ctas, self._stream())
+        if rc < 0:
+            raise RuntimeError(f"symm reduce_scatter failed: {K.last_error()}")
+        K._LAUNCHES += 1
+        buf.last_rs_epoch = ep
+        return ep
+
+    def wait_rs_done(self, epoch):
+        """Enqueue (current stream) a wait until every peer finished reading my buffer in RS ``epoch``."""
+        if epoch > 0:
+            self.lib.dsb200_symm_wait(self.flags.ptrs, self.rank, self.world, CH_RS_DONE, epoch, self._stream())
+            K._LAUNCHES += 1
+
+    def all_gather(self, shard_buf: SymmBuffer, shard_offset_bytes, shard_bytes, full, ctas=0):
+        """full[p*shard_bytes ...] = peer p's bytes at ``shard_offset_bytes`` of ``shard_buf`` (pull over NVLink)."""
+        ep = self._next(CH_AG_READY)
+        ptrs = (ctypes.c_uint64 * 16)(*[(int(p) + shard_offset_bytes) if p else 0 for p in shard_buf.ptrs])
+        rc = self.lib.dsb200_symm_all_gather(ptrs, self.flags.ptrs, ctypes.c_uint64(0), self.rank, self.world,
+                                             shard_bytes, ctypes.c_void_p(0), ctypes.c_void_p(full.data_ptr()),
+                                             ctypes.c_void_p(self.tickets.data_ptr() + 4), CH_AG_READY, CH_AG_DONE, ep,
+                                             0, ctas, self._stream())
+        if rc != 0:
+            raise RuntimeError(f"symm all_gather failed: {K.last_error()}")
+        K._LAUNCHES += 1
+        return ep
+
+    def all_to_all(self, in_buf: SymmBuffer, rows, row_bytes, out, interleave=False, ctas=0):
+        """out[p] = peer p's chunk ``rank`` of its input buffer viewed as [world, rows, row_bytes]."""
+        ep = self._next(CH_A2A_READY)
+        rc = self.lib.dsb200_symm_all_to_all(in_buf.ptrs, self.flags.ptrs, self.rank, self.world, rows, row_bytes,
+                                             1 if interleave else 0, ctypes.c_void_p(out.data_ptr()),
+                                             ctypes.c_void_p(self.tickets.data_ptr() + 8), CH_A2A_READY, CH_A2A_DONE,
+                                             ep, ctas, self._stream())
+        if rc != 0:
+            raise RuntimeError(f"symm all_to_all failed: {K.last_error()}")
+        K._LAUNCHES += 1
+        in_buf.last_a2a_epoch = ep
+        return ep
+
+    def wait_a2a_done(self, epoch):
+        if epoch > 0:
+            self.lib.dsb200_symm_wait(self.flags.ptrs, self.rank, self.world, CH_A2A_DONE, epoch, self._stream())
+            K._LAUNCHES += 1
+
+    def wait_ag_done(self, epoch):
+        if epoch > 0:
+            self.lib.dsb200_symm_wait(self.flags.ptrs, self.rank, self.world, CH_AG_DONE, epoch, self._stream())
+            K._LAUNCHES += 1
+
+
+class SymmSlotPool:
+    """Round-robin pool of symmetric buffers (gradient buckets / a2a staging). Before a slot is rewritten the
+    producer stream waits for the peers' DONE flag of the collective that last read it."""
+
+    def __init__(self, ctx: SymmContext, slot_bytes, n_slots=3, kind="rs"):
+        self.ctx, self.kind = ctx, kind
+        self.slots = [ctx.alloc(slot_bytes) for _ in range(n_slots)]
+        self.next = 0
+        self.slot_bytes = self.slots[0].nbytes
+
+    def acquire(self):
+        """Next slot; enqueues the DONE wait of its previous use on the current stream."""
+        s = self.slots[self.next]
+        self.next = (self.next + 1) % len(self.slots)
+        if self.kind == "rs":
+            self.ctx.wait_rs_done(getattr(s, "last_rs_epoch", 0))
+        else:
+            self.ctx.wait_a2a_done(getattr(s, "last_a2a_epoch", 0))
+        return s

@@ -92,8 +92,29 @@ def attention(q, k, v, causal=True, impl="auto"):
     if gqa and not q.is_cuda:
         rep = qt.shape[1] // kt.shape[1]
         kt, vt, gqa = kt.repeat_interleave(rep, dim=1), vt.repeat_interleave(rep, dim=1), False
-    out = F.scaled_dot_product_attention(qt, kt, vt, is_causal=causal, enable_gqa=gqa)
+    backend = _sdpa_backend() if q.is_cuda else None
+    if backend is not None:
+        with torch.nn.attention.sdpa_kernel(backend):
+            out = F.scaled_dot_product_attention(qt, kt, vt, is_causal=causal, enable_gqa=gqa)
+    else:
+        out = F.scaled_dot_product_attention(qt, kt, vt, is_causal=causal, enable_gqa=gqa)
     return out.transpose(1, 2)
+
+
+_SDPA_BACKEND = "unset"
+
+
+def _sdpa_backend():
+    """Library attention backend used until the native tcgen05 kernel serves the shape (env DSB200_SDPA)."""
+    global _SDPA_BACKEND
+    if _SDPA_BACKEND == "unset":
+        import os
+        from torch.nn.attention import SDPBackend
+        name = os.environ.get("DSB200_SDPA", "auto").lower()
+        table = {"cudnn": [SDPBackend.CUDNN_ATTENTION], "flash": [SDPBackend.FLASH_ATTENTION],
+                 "efficient": [SDPBackend.EFFICIENT_ATTENTION], "math": [SDPBackend.MATH]}
+        _SDPA_BACKEND = table.get(name)
+    return _SDPA_BACKEND
 
 
 class LlamaAttention(nn.Module):

@@ -189,9 +189,9 @@ class _LinearCrossEntropyFn(torch.autograd.Function):
         dh = torch.empty_like(h) if need_h else None
         main_grad = getattr(weight, "_ds_grad_view", None)
         dw = None
-        if need_w:
-            dw = torch.zeros(V, H, dtype=torch.float32 if main_grad is None else weight.dtype, device=h.device) \
-                if main_grad is None else None
+        single = N <= chunk_tokens
+        if need_w and main_grad is None and not single:
+            dw = torch.zeros(V, H, dtype=torch.float32, device=h.device)
         loss_sum = torch.zeros((), dtype=torch.float32, device=h.device)
         inv_f = float(inv) if not torch.is_tensor(inv) else None
         for s in range(0, N, chunk_tokens):
@@ -205,7 +205,9 @@ class _LinearCrossEntropyFn(torch.autograd.Function):
             if need_h:
                 torch.matmul(logits, weight, out=dh[s:e])
             if need_w:
-                if dw is not None:
+                if single and main_grad is None:
+                    dw = torch.matmul(logits.t(), h[s:e])
+                elif dw is not None:
                     dw.add_(torch.matmul(logits.t(), h[s:e]))  # fp32 accumulation across chunks
                 else:
                     main_grad.addmm_(logits.t(), h[s:e])

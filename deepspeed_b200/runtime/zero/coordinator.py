@@ -120,6 +120,13 @@ class UnitCoordinator:
         if world <= 1:
             full[:src.numel()].copy_(src)
             return
+        st = self.z.storages.get((u.group_key, u.dtype))
+        if self.z.symm is not None and st is not None and getattr(st, "lp_symm", None) is not None \
+                and src.data_ptr() == u.param_shard.data_ptr() and not self.z.quantized_weights:
+            # fused path 2 (v1): pull every peer's shard straight out of its symmetric lp storage over NVLink
+            esz = src.element_size()
+            self.z.symm.all_gather(st.lp_symm, u.shard_offset * esz, u.shard_numel * esz, full)
+            return
         if self.z.quantized_weights and u.dtype in (torch.bfloat16, torch.float16) and full.is_cuda:
             from ...ops.quantizer import quantized_all_gather
             quantized_all_gather(full, src, group)

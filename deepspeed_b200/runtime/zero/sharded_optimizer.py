@@ -170,6 +170,23 @@ class ZeroShardedOptimizer:
         else:
             self.rs_stream = self.ag_stream = None
 
+        # ---- fused NVLink collectives (symmetric memory) ----
+        self.symm = None
+        self._grad_pool = None
+        if fused_collectives is not False and self.partition_grads and self._replica_world == 1 \
+                and self._shard_world > 1 and all(u.group_key == "dp" for u in self.units):
+            from ...comm import symm as _symm
+            if _symm.is_supported(self._shard_group):
+                try:
+                    self.symm = _symm.SymmContext.get(self._shard_group)
+                    esz = torch.empty((), dtype=self.comm_dtype).element_size()
+                    slot_bytes = max(u.numel_padded for u in self.units) * esz
+                    self._grad_pool = _symm.SymmSlotPool(self.symm, slot_bytes, n_slots=3, kind="rs")
+                except Exception as e:  # noqa: BLE001
+                    if fused_collectives is True:
+                        raise
+                    logger.warning(f"symmetric-memory collectives unavailable ({e}); using NCCL")
+                    self.symm, self._grad_pool = None, None
         self._allocate_and_link()
         self._register_grad_hooks()
         self.coordinator = None
@@ -255,7 +272,16 @@ class ZeroShardedOptimizer:
                 st.grad_host = torch.zeros(st.numel, dtype=torch.float32, device=sdev,
                                            pin_memory=(pin and sdev.type == "cpu"))
                 st.lp_host = torch.zeros(st.numel, dtype=key[1], device=sdev, pin_memory=(pin and sdev.type == "cpu"))
-            st.lp = torch.zeros(st.numel, dtype=key[1], device=dev) if self.partition_params else None
+            st.lp, st.lp_symm = None, None
+            if self.partition_params:
+                if self.symm is not None and key[0] == "dp":
+                    # shards live in symmetric memory: peers pull them over NVLink inside the all-gather kernel
+                    esz_lp = torch.empty((), dtype=key[1]).element_size()
+                    st.lp_symm = self.symm.alloc(st.numel * esz_lp, want_multicast=False)
+                    st.lp = st.lp_symm.view(st.numel, key[1])
+                    st.lp.zero_()
+                else:
+                    st.lp = torch.zeros(st.numel, dtype=key[1], device=dev)
             for u in st.units:
                 a, b = u.shard_offset, u.shard_offset + u.shard_numel
                 u.master_shard, u.grad_shard = st.master[a:b], st.grad[a:b]
@@ -354,11 +380,20 @@ class ZeroShardedOptimizer:
             return
         self._ensure_epilogue()
         if u.full_grad is None:
-            u.full_grad = torch.zeros(u.numel_padded, dtype=self._full_grad_dtype(), device=u.device)
+            # no memset: every parameter overwrites its own region; alignment gaps / params that never produce a
+            # gradient are zeroed just before the reduction (_zero_unwritten)
+            if self._grad_pool is not None and u.world > 1:
+                u._slot = self._grad_pool.acquire()  # waits (on this stream) until peers released the slot
+                u.full_grad = u._slot.view(u.numel_padded, self._full_grad_dtype())
+            else:
+                u._slot = None
+                u.full_grad = torch.empty(u.numel_padded, dtype=self._full_grad_dtype(), device=u.device)
             u.has_grad_data = False
+            u._written = set()
+        u._written.add(i)
         o, n = u.offsets[i], u.numels[i]
         view = u.full_grad[o:o + n]
-        if u.has_grad_data and not self.partition_grads:
+        if u.has_grad_data and not self.partition_grads and i in getattr(u, "_accumulated", ()):
             view.add_(g.reshape(-1))
         else:
             view.copy_(g.reshape(-1))
@@ -389,6 +424,21 @@ class ZeroShardedOptimizer:
             return 1.0
         return float(u.world * u.replica_world) / float(self.sp_size if u.group_key == "dp" else 1)
 
+    def _zero_unwritten(self, u: FlatUnit):
+        """Zero the regions of ``full_grad`` nobody wrote: alignment gaps, tail padding, params without grad."""
+        full, written = u.full_grad, getattr(u, "_written", set())
+        prev_end = 0
+        for i, (o, n) in enumerate(zip(u.offsets, u.numels)):
+            if o > prev_end:
+                full[prev_end:o].zero_()
+            if i not in written:
+                full[o:o + n].zero_()
+            prev_end = o + n
+        if prev_end < u.numel_padded:
+            full[prev_end:].zero_()
+        u._written = set(range(len(u.params)))
+        u._accumulated = u._written
+
     @instrument_w_nvtx
     @torch.no_grad()
     def _reduce_unit(self, u: FlatUnit):
@@ -396,6 +446,7 @@ class ZeroShardedOptimizer:
         if u.full_grad is None or u.reduced_this_pass:
             return
         u.reduced_this_pass = True
+        self._zero_unwritten(u)
         full = u.full_grad
         div = self._grad_divisor(u)
         first = not getattr(u, "_shard_has_data", False)
@@ -405,37 +456,48 @@ class ZeroShardedOptimizer:
             stream_ctx = torch.cuda.stream(self.rs_stream)
             stream_ctx.__enter__()
         try:
-            if full.dtype != self.comm_dtype:
-                full = full.to(self.comm_dtype)
-            pre = self.predivide if (self.predivide and self.predivide != 1.0) else (
-                div if self.comm_dtype == torch.float16 else 1.0)
-            if pre != 1.0:
-                full.div_(pre)
-            post = div / pre
-            if u.world > 1:
-                out = torch.empty(u.shard_numel, dtype=full.dtype, device=full.device)
-                dist.reduce_scatter_tensor(out, full, group=u.dp_group)
+            if getattr(u, "_slot", None) is not None and self.symm is not None:
+                # ONE kernel: NVLink loads from every peer's bucket + fp32 sum + average + cast + accumulate
+                self.symm.reduce_scatter(u._slot, full.dtype, u.shard_numel, u.grad_shard, accumulate=not first,
+                                         scale=1.0 / div)
+                u._slot = None
             else:
-                out = full
-            if u.replica_world > 1:
-                dist.all_reduce(out, group=u.replica_group)
-            if first:
-                if post != 1.0:
-                    torch.mul(out, 1.0 / post, out=u.grad_shard) if out.dtype == u.grad_shard.dtype else \
-                        u.grad_shard.copy_(out.to(u.grad_shard.dtype).mul_(1.0 / post))
-                else:
-                    u.grad_shard.copy_(out)
-            else:
-                u.grad_shard.add_(out.to(u.grad_shard.dtype), alpha=1.0 / post)
+                self._reduce_unit_nccl(u, full, div, first)
             u._shard_has_data = True
-            if self._use_streams and self.overlap_comm:
-                u.full_grad.record_stream(self.rs_stream)
         finally:
             if stream_ctx is not None:
                 stream_ctx.__exit__(None, None, None)
         if self.partition_grads or self.is_gradient_accumulation_boundary:
             u.full_grad = None
             u.has_grad_data = False
+            u._accumulated = set()
+
+    def _reduce_unit_nccl(self, u, full, div, first):
+        """Baseline path: (pre-divide) -> NCCL reduce-scatter / all-reduce -> scale + cast + accumulate."""
+        if full.dtype != self.comm_dtype:
+            full = full.to(self.comm_dtype)
+        pre = self.predivide if (self.predivide and self.predivide != 1.0) else (
+            div if self.comm_dtype == torch.float16 else 1.0)
+        if pre != 1.0:
+            full.div_(pre)
+        post = div / pre
+        if u.world > 1:
+            out = torch.empty(u.shard_numel, dtype=full.dtype, device=full.device)
+            dist.reduce_scatter_tensor(out, full, group=u.dp_group)
+        else:
+            out = full
+        if u.replica_world > 1:
+            dist.all_reduce(out, group=u.replica_group)
+        if first:
+            if post != 1.0:
+                torch.mul(out, 1.0 / post, out=u.grad_shard) if out.dtype == u.grad_shard.dtype else \
+                    u.grad_shard.copy_(out.to(u.grad_shard.dtype).mul_(1.0 / post))
+            else:
+                u.grad_shard.copy_(out)
+        else:
+            u.grad_shard.add_(out.to(u.grad_shard.dtype), alpha=1.0 / post)
+        if self._use_streams and self.overlap_comm:
+            u.full_grad.record_stream(self.rs_stream)
 
     # ------------------------------------------------------------------ backward bracket -------
     def backward_prologue(self):
@@ -457,6 +519,8 @@ class ZeroShardedOptimizer:
             u.grads_ready = 0
             u.reduced_this_pass = False
             if u.full_grad is not None:
+                if len(getattr(u, "_accumulated", ())) != len(u.params):
+                    self._zero_unwritten(u)
                 u.has_grad_data = True
         if self._use_streams and self.overlap_comm:
             torch.cuda.current_stream().wait_stream(self.rs_stream)
@@ -545,6 +609,7 @@ class ZeroShardedOptimizer:
         if self._use_streams and self.overlap_comm:
             torch.cuda.current_stream().wait_stream(self.rs_stream)
 
+        self._zero_stale_shards()
         norm_sq = self._global_grad_norm_sq()
         scale = float(self.cur_scale)
         check_overflow = self.lp_dtype == torch.float16
@@ -655,18 +720,23 @@ class ZeroShardedOptimizer:
         return dist.all_gather_into_tensor(full, shard, group=u.dp_group, async_op=async_op)
 
     def _zero_grad_shards(self):
-        for st in self.storages.values():
-            st.grad.zero_()
+        # no flat memset: the next reduction of a unit overwrites its shard (``first`` path in _reduce_unit);
+        # units that receive no gradient at all in the next step are zeroed in step() (_zero_stale_shards)
         for u in self.units:
             u._shard_has_data = False
+
+    def _zero_stale_shards(self):
+        for u in self.units:
+            if not getattr(u, "_shard_has_data", False):
+                u.grad_shard.zero_()
 
     def zero_grad(self, set_to_none=True):
         for u in self.units:
             for p in u.params:
                 p.grad = None
-            if self.partition_grads or True:
-                u.full_grad = None
-                u.has_grad_data = False
+            u.full_grad = None
+            u.has_grad_data = False
+            u._accumulated = set()
         self.micro_step_id = 0
 
     # ------------------------------------------------------------------ fragment / debug API ---

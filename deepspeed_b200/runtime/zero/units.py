@@ -208,6 +208,11 @@ def build_module_units(model, param_groups, unit_max_numel, persistence_threshol
         total = sum(numel_of(p) for p in ps)
         children = list(module.children())
         leaf = isinstance(module, tuple(leaf_modules)) if leaf_modules else False
+        container = isinstance(module, (torch.nn.ModuleList, torch.nn.ModuleDict))  # no forward(): hooks never fire
+        if container:
+            for c in children:
+                visit(c, False)
+            return
         if leaf or not children or (total <= unit_max_numel and not is_root) or (is_root and total <= min(
                 unit_max_numel, persistence_threshold)):
             take(module, ps)
