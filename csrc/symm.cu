@@ -112,21 +112,36 @@ __global__ void __launch_bounds__(512) symm_reduce_scatter_kernel(PeerPtrs bufs,
     wait_all(flags, rank, world, ch_ready, epoch);
 
     constexpr int VEC = 16 / sizeof(T);
+    constexpr int U = 8;  // independent 16-byte loads in flight per thread and peer (NVLink latency ~2 us)
     const int64_t nvec = shard_numel / VEC;
     const int64_t base = (int64_t)rank * shard_numel;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     float ss = 0.f;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
-        float acc[VEC];
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < nvec; i0 += stride * U) {
+        float acc[U][VEC];
 #pragma unroll
-        for (int k = 0; k < VEC; k++) acc[k] = 0.f;
-        // start with my own copy, then walk the peers in a rank-rotated order to spread NVLink traffic
-#pragma unroll 1
+        for (int u = 0; u < U; u++)
+#pragma unroll
+            for (int k = 0; k < VEC; k++) acc[u][k] = 0.f;
+        // walk the peers in a rank-rotated order to spread NVLink traffic; 2 peers x U loads issued per round
+#pragma unroll 2
         for (int s = 0; s < world; s++) {
             const int p = (rank + s) % world;
-            const T* src = reinterpret_cast<const T*>(bufs.p[p]) + base + i * VEC;
-            accum8<T>(acc, ld_peer_v4(src));
+            const T* src = reinterpret_cast<const T*>(bufs.p[p]) + base;
+            uint4 raw[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int64_t i = i0 + u * stride;
+                raw[u] = (i < nvec) ? ld_peer_v4(src + i * VEC) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) accum8<T>(acc[u], raw[u]);
         }
-        ss += store_out<OutT, VEC>(out + i * VEC, acc, accumulate, scale);
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int64_t i = i0 + u * stride;
+            if (i < nvec) ss += store_out<OutT, VEC>(out + i * VEC, acc[u], accumulate, scale);
+        }
     }
     if (sumsq_partials != nullptr) {
         ss = dsb::block_sum(ss, red);
@@ -156,19 +171,32 @@ __global__ void __launch_bounds__(512) symm_reduce_scatter_mc_bf16_kernel(const 
     if (blockIdx.x == 0) signal_all(flags, rank, world, ch_ready, epoch);
     wait_all(flags, rank, world, ch_ready, epoch);
     const int64_t nvec = shard_numel / 8;
+    constexpr int U = 8;
     const __nv_bfloat16* src0 = reinterpret_cast<const __nv_bfloat16*>(mc_base) + (int64_t)rank * shard_numel;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     float ss = 0.f;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
-        uint4 r;
-        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
-                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                     : "l"(src0 + i * 8)
-                     : "memory");
-        const __nv_bfloat16* e = reinterpret_cast<const __nv_bfloat16*>(&r);
-        float acc[8];
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < nvec; i0 += stride * U) {
+        uint4 r[U];
 #pragma unroll
-        for (int k = 0; k < 8; k++) acc[k] = __bfloat162float(e[k]);
-        ss += store_out<OutT, 8>(out + i * 8, acc, accumulate, scale);
+        for (int u = 0; u < U; u++) {
+            const int64_t i = i0 + u * stride;
+            r[u] = make_uint4(0, 0, 0, 0);
+            if (i < nvec)
+                asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(r[u].x), "=r"(r[u].y), "=r"(r[u].z), "=r"(r[u].w)
+                             : "l"(src0 + i * 8)
+                             : "memory");
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int64_t i = i0 + u * stride;
+            if (i >= nvec) continue;
+            const __nv_bfloat16* e = reinterpret_cast<const __nv_bfloat16*>(&r[u]);
+            float acc[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) acc[k] = __bfloat162float(e[k]);
+            ss += store_out<OutT, 8>(out + i * 8, acc, accumulate, scale);
+        }
     }
     if (sumsq_partials != nullptr) {
         ss = dsb::block_sum(ss, red);
@@ -195,14 +223,25 @@ __global__ void __launch_bounds__(512) symm_all_gather_kernel(PeerPtrs shards, P
     if (blockIdx.x == 0) signal_all(flags, rank, world, ch_ready, epoch);
     wait_all(flags, rank, world, ch_ready, epoch);
     const int64_t nvec = shard_bytes / 16;
-    const int64_t total = nvec * world;
-    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-         idx += (int64_t)gridDim.x * blockDim.x) {
-        const int s = idx / nvec;
-        const int64_t i = idx - (int64_t)s * nvec;
+    constexpr int U = 16;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int s = 0; s < world; s++) {
         const int p = (rank + s) % world;
-        const uint4 v = ld_peer_v4(reinterpret_cast<const uint8_t*>(shards.p[p]) + i * 16);
-        *reinterpret_cast<uint4*>(full + (int64_t)p * shard_bytes + i * 16) = v;
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(shards.p[p]);
+        uint8_t* dst = full + (int64_t)p * shard_bytes;
+        for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < nvec; i0 += stride * U) {
+            uint4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int64_t i = i0 + u * stride;
+                if (i < nvec) v[u] = ld_peer_v4(src + i * 16);
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int64_t i = i0 + u * stride;
+                if (i < nvec) *reinterpret_cast<uint4*>(dst + i * 16) = v[u];
+            }
+        }
     }
     __syncthreads();
     __shared__ bool last;
@@ -260,18 +299,29 @@ __global__ void __launch_bounds__(512) symm_all_to_all_kernel(PeerPtrs ins, Peer
     wait_all(flags, rank, world, ch_ready, epoch);
     const int64_t vec_per_row = row_bytes / 16;
     const int64_t per_peer = rows * vec_per_row;
-    const int64_t total = per_peer * world;
-    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-         idx += (int64_t)gridDim.x * blockDim.x) {
-        const int s = idx / per_peer;
-        const int64_t rem = idx - (int64_t)s * per_peer;
-        const int64_t r = rem / vec_per_row, c = rem - r * vec_per_row;
+    constexpr int U = 16;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int s = 0; s < world; s++) {
         const int p = (rank + s) % world;
-        const uint8_t* src = reinterpret_cast<const uint8_t*>(ins.p[p]) + ((int64_t)rank * rows + r) * row_bytes + c * 16;
-        const uint4 v = ld_peer_v4(src);
-        uint8_t* dst = interleave ? out + (r * world + p) * row_bytes + c * 16
-                                  : out + ((int64_t)p * rows + r) * row_bytes + c * 16;
-        *reinterpret_cast<uint4*>(dst) = v;
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(ins.p[p]) + (int64_t)rank * rows * row_bytes;
+        for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < per_peer; i0 += stride * U) {
+            uint4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int64_t i = i0 + u * stride;
+                if (i < per_peer) v[u] = ld_peer_v4(src + i * 16);
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int64_t i = i0 + u * stride;
+                if (i < per_peer) {
+                    const int64_t r = i / vec_per_row, c = i - r * vec_per_row;
+                    uint8_t* dst = interleave ? out + (r * world + p) * row_bytes + c * 16
+                                              : out + ((int64_t)p * rows + r) * row_bytes + c * 16;
+                    *reinterpret_cast<uint4*>(dst) = v[u];
+                }
+            }
+        }
     }
     __syncthreads();
     __shared__ bool last;

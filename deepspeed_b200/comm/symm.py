@@ -51,7 +51,8 @@ def is_supported(group=None):
     if world < 2 or world > 16 or dist.get_backend(group) != "nccl":
         return False
     try:
-        import torch.distributed._symmetric_memory  # noqa: F401
+        import importlib
+        importlib.import_module("torch.distributed._symmetric_memory")
     except Exception:
         return False
     return K.available()
@@ -95,6 +96,9 @@ class SymmContext:
         self.tickets = torch.zeros(64, dtype=torch.int32, device=self.device)
         self.partials = torch.zeros(64 * 16, dtype=torch.float32, device=self.device)
         self.epoch = [0] * 64
+        # CTAs per communication kernel: enough loads in flight to fill NVLink (~2 us x 900 GB/s = 1.8 MB ->
+        # 16-32 CTAs x 512 threads x 16 B x unroll), few enough to leave the SMs to the overlapped GEMMs
+        self.default_ctas = int(os.environ.get("DSB200_COMM_CTAS", "24"))
         torch.cuda.synchronize()
         dist.barrier(group=group)
         self.multicast = False
@@ -119,7 +123,7 @@ class SymmContext:
 
     # ---- collectives ---------------------------------------------------------------------------
     def reduce_scatter(self, buf: SymmBuffer, in_dtype, shard_numel, out, accumulate, scale, use_multicast=None,
-                       ctas=0, want_sumsq=False):
+                       ctas=None, want_sumsq=False):
         """out (+)= scale * sum_p buf_p[rank*shard : (rank+1)*shard]. Returns epoch (for DONE waits)."""
         ep = self._next(CH_RS_READY)
         mc = buf.mc_ptr if (use_multicast if use_multicast is not None else True) else 0
@@ -127,7 +131,8 @@ class SymmContext:
             buf.ptrs, self.flags.ptrs, ctypes.c_uint64(mc if in_dtype == torch.bfloat16 else 0), self.rank, self.world,
             shard_numel, K._DT[in_dtype], ctypes.c_void_p(out.data_ptr()), K._DT[out.dtype], 1 if accumulate else 0,
             float(scale), ctypes.c_void_p(self.partials.data_ptr()) if want_sumsq else ctypes.c_void_p(0),
-            ctypes.c_void_p(self.tickets.data_ptr()), CH_RS_READY, CH_RS_DONE, ep, ctas, self._stream())
+            ctypes.c_void_p(self.tickets.data_ptr()), CH_RS_READY, CH_RS_DONE, ep,
+            self.default_ctas if ctas is None else ctas, self._stream())
         if rc < 0:
             raise RuntimeError(f"symm reduce_scatter failed: {K.last_error()}")
         K._LAUNCHES += 1
@@ -140,26 +145,26 @@ class SymmContext:
             self.lib.dsb200_symm_wait(self.flags.ptrs, self.rank, self.world, CH_RS_DONE, epoch, self._stream())
             K._LAUNCHES += 1
 
-    def all_gather(self, shard_buf: SymmBuffer, shard_offset_bytes, shard_bytes, full, ctas=0):
+    def all_gather(self, shard_buf: SymmBuffer, shard_offset_bytes, shard_bytes, full, ctas=None):
         """full[p*shard_bytes ...] = peer p's bytes at ``shard_offset_bytes`` of ``shard_buf`` (pull over NVLink)."""
         ep = self._next(CH_AG_READY)
         ptrs = (ctypes.c_uint64 * 16)(*[(int(p) + shard_offset_bytes) if p else 0 for p in shard_buf.ptrs])
         rc = self.lib.dsb200_symm_all_gather(ptrs, self.flags.ptrs, ctypes.c_uint64(0), self.rank, self.world,
                                              shard_bytes, ctypes.c_void_p(0), ctypes.c_void_p(full.data_ptr()),
                                              ctypes.c_void_p(self.tickets.data_ptr() + 4), CH_AG_READY, CH_AG_DONE, ep,
-                                             0, ctas, self._stream())
+                                             0, self.default_ctas if ctas is None else ctas, self._stream())
         if rc != 0:
             raise RuntimeError(f"symm all_gather failed: {K.last_error()}")
         K._LAUNCHES += 1
         return ep
 
-    def all_to_all(self, in_buf: SymmBuffer, rows, row_bytes, out, interleave=False, ctas=0):
+    def all_to_all(self, in_buf: SymmBuffer, rows, row_bytes, out, interleave=False, ctas=None):
         """out[p] = peer p's chunk ``rank`` of its input buffer viewed as [world, rows, row_bytes]."""
         ep = self._next(CH_A2A_READY)
         rc = self.lib.dsb200_symm_all_to_all(in_buf.ptrs, self.flags.ptrs, self.rank, self.world, rows, row_bytes,
                                              1 if interleave else 0, ctypes.c_void_p(out.data_ptr()),
                                              ctypes.c_void_p(self.tickets.data_ptr() + 8), CH_A2A_READY, CH_A2A_DONE,
-                                             ep, ctas, self._stream())
+                                             ep, self.default_ctas if ctas is None else ctas, self._stream())
         if rc != 0:
             raise RuntimeError(f"symm all_to_all failed: {K.last_error()}")
         K._LAUNCHES += 1

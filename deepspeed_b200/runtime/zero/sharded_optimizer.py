@@ -165,8 +165,8 @@ class ZeroShardedOptimizer:
 
         self._use_streams = torch.cuda.is_available() and any(p.is_cuda for _, p in named)
         if self._use_streams:
-            self.rs_stream = torch.cuda.Stream() if self.overlap_comm else torch.cuda.current_stream()
-            self.ag_stream = torch.cuda.Stream() if self.overlap_comm else torch.cuda.current_stream()
+            self.rs_stream = torch.cuda.Stream(priority=-1) if self.overlap_comm else torch.cuda.current_stream()
+            self.ag_stream = torch.cuda.Stream(priority=-1) if self.overlap_comm else torch.cuda.current_stream()
         else:
             self.rs_stream = self.ag_stream = None
 
