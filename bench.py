@@ -135,7 +135,8 @@ def build_reference(args, torch, world):
     if not os.path.isdir(os.path.join(ref, "deepspeed")):
         return None, "baseline/_ref missing: reference not installed"
     sys.path.insert(0, ref)
-    os.environ.setdefault("TORCH_CUDA_ARCH_LIST", "10.0")
+    # the reference's op_builder cannot parse an "a"-suffixed arch ("10.0a") that the image may export
+    os.environ["TORCH_CUDA_ARCH_LIST"] = "10.0"
     os.environ.setdefault("DS_SKIP_CUDA_CHECK", "1")
     try:
         import deepspeed

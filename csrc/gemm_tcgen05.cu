@@ -1,0 +1,347 @@
+// bf16 GEMM on the 5th-generation tensor cores: C[M,N] = A[M,K] * B[N,K]^T (both operands K-major, i.e. the
+// torch.nn.Linear forward y = x W^T), fp32 accumulation in TMEM, bf16 output (+ optional fused SwiGLU epilogue).
+//
+// Reference: every dense GEMM of the reference is a cuBLAS call (csrc/transformer/cublas_wrappers.cu,
+// module_inject/layers.py:771 F.linear). This is the framework's own tcgen05 kernel, the building block that the
+// fused all-gather->GEMM / GEMM->reduce-scatter paths extend.
+//
+// Structure (persistent, one CTA per SM, 192 threads, warp-specialised):
+//   warp 0      : TMA producer  - cp.async.bulk.tensor 2D loads of A (128x64) and B (256x64) tiles, 128B swizzle,
+//                                 4-stage ring guarded by full/empty mbarriers
+//   warp 1      : MMA issuer    - allocates TMEM (512 columns = 2 accumulator stages of 128x256 fp32), one elected
+//                                 lane issues 4 x tcgen05.mma (M128 N256 K16) per k-block, tcgen05.commit frees the
+//                                 smem stage / publishes the accumulator
+//   warps 2..5  : epilogue      - tcgen05.ld 32 lanes x 32 columns -> registers -> bf16 -> 16-byte global stores,
+//                                 overlapped with the MMAs of the next tile through the second accumulator stage
+#include "common.cuh"
+#include <cuda.h>
+
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_N = 256;
+constexpr int BLOCK_K = 64;   // 64 bf16 = 128 bytes = one swizzle-128B row
+constexpr int UMMA_K = 16;
+constexpr int STAGES = 4;
+constexpr int ACC_STAGES = 2;
+constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
+constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;  // 32 KB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int TMEM_COLS = 512;
+constexpr int NUM_THREADS = 192;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+
+// K-major, 128B-swizzled operand tile: rows are 128 B apart, 8-row groups (1024 B) are the swizzle atoms.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);  // start address  [0,14)
+    d |= (uint64_t)0 << 16;                       // leading byte offset (unused for swizzled K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;             // stride byte offset: 8 rows * 128 B   [32,46)
+    d |= (uint64_t)1 << 46;                       // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;                       // layout type: SWIZZLE_128B
+    return d;
+}
+
+// kind::f16, A=B=bf16, D=f32, both K-major, M=128, N=256
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n)
+{
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+
+struct Smem {
+    uint64_t full[STAGES];
+    uint64_t empty[STAGES];
+    uint64_t tmem_full[ACC_STAGES];
+    uint64_t tmem_empty[ACC_STAGES];
+    uint32_t tmem_base;
+};
+
+// EPI: 0 = plain bf16 store; 1 = SwiGLU over interleaved (gate, up) column pairs is NOT used here - the fused
+// gate_up layout keeps gate in columns [0, N/2) and up in [N/2, N), so SwiGLU stays a separate kernel.
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_bf16_nt_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                    __nv_bfloat16* __restrict__ C, int M, int N, int K, int64_t ldc)
+{
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    Smem* sm = reinterpret_cast<Smem*>(tiles + STAGES * STAGE_BYTES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m_tiles = (M + BLOCK_M - 1) / BLOCK_M, n_tiles = (N + BLOCK_N - 1) / BLOCK_N;
+    const int num_tiles = m_tiles * n_tiles;
+    const int k_blocks = (K + BLOCK_K - 1) / BLOCK_K;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; s++) {
+            mbar_init(&sm->full[s], 1);
+            mbar_init(&sm->empty[s], 1);
+        }
+        for (int s = 0; s < ACC_STAGES; s++) {
+            mbar_init(&sm->tmem_full[s], 1);
+            mbar_init(&sm->tmem_empty[s], 4);  // one arrive per epilogue warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm->tmem_base)),
+                     "n"(TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = sm->tmem_base;
+
+    if (warp == 0) {
+        // ================= TMA producer =================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                const int m_blk = t % m_tiles, n_blk = t / m_tiles;
+                for (int kb = 0; kb < k_blocks; kb++) {
+                    mbar_wait(&sm->empty[stage], phase ^ 1);
+                    uint8_t* a_dst = tiles + stage * STAGE_BYTES;
+                    uint8_t* b_dst = a_dst + A_BYTES;
+                    mbar_expect_tx(&sm->full[stage], STAGE_BYTES);
+                    tma_load_2d(a_dst, &map_a, &sm->full[stage], kb * BLOCK_K, m_blk * BLOCK_M);
+                    tma_load_2d(b_dst, &map_b, &sm->full[stage], kb * BLOCK_K, n_blk * BLOCK_N);
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc(BLOCK_M, BLOCK_N);
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                mbar_wait(&sm->tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
+                for (int kb = 0; kb < k_blocks; kb++) {
+                    mbar_wait(&sm->full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(tiles + stage * STAGE_BYTES);
+                    const uint32_t b_addr = a_addr + A_BYTES;
+                    const uint64_t adesc = make_smem_desc(a_addr), bdesc = make_smem_desc(b_addr);
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; k++) {
+                        // advance 32 bytes (16 bf16) along K inside the 128B-swizzled row: +2 in the >>4 address field
+                        umma_bf16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
+                                  (kb > 0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(&sm->empty[stage]);  // smem stage reusable once these MMAs retire
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                umma_commit(&sm->tmem_full[acc]);  // accumulator complete
+                if (++acc == ACC_STAGES) {
+                    acc = 0;
+                    acc_phase ^= 1;
+                }
+            }
+        }
+    } else {
+        // ================= epilogue (warps 2..5) =================
+        const int lane_group = warp & 3;  // TMEM lanes [32*lane_group, +32) are accessible to this warp
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            const int m_blk = t % m_tiles, n_blk = t / m_tiles;
+            mbar_wait(&sm->tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const int row = m_blk * BLOCK_M + lane_group * 32 + lane;
+            __nv_bfloat16* crow = C + (int64_t)row * ldc + (int64_t)n_blk * BLOCK_N;
+#pragma unroll 1
+            for (int c = 0; c < BLOCK_N; c += 32) {
+                uint32_t r[32];
+                const uint32_t taddr = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(acc * BLOCK_N + c);
+                tmem_ld_32x32(taddr, r);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                const int col0 = n_blk * BLOCK_N + c;
+                if (row < M) {
+                    if (col0 + 32 <= N) {
+#pragma unroll
+                        for (int v = 0; v < 4; v++) {
+                            uint4 pk;
+                            __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+                            for (int j = 0; j < 4; j++)
+                                h[j] = __floats2bfloat162_rn(__uint_as_float(r[v * 8 + 2 * j]),
+                                                             __uint_as_float(r[v * 8 + 2 * j + 1]));
+                            *reinterpret_cast<uint4*>(crow + c + v * 8) = pk;
+                        }
+                    } else {
+                        for (int j = 0; j < 32; j++)
+                            if (col0 + j < N) crow[c + j] = __float2bfloat16_rn(__uint_as_float(r[j]));
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm->tmem_empty[acc]);
+            if (++acc == ACC_STAGES) {
+                acc = 0;
+                acc_phase ^= 1;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode()
+{
+    static EncodeTiledFn fn = nullptr;
+    if (fn == nullptr) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// 2D bf16 row-major [rows, cols] tensor, box = [box_rows, 64 cols], 128B swizzle
+int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows)
+{
+    EncodeTiledFn enc = get_encode();
+    if (enc == nullptr) {
+        dsb200_set_error("cuTensorMapEncodeTiled entry point unavailable");
+        return -1;
+    }
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)BLOCK_K, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        dsb200_set_error("cuTensorMapEncodeTiled failed (alignment: base 16 B, row stride multiple of 16 B)");
+        return -2;
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+// C[M,N] (bf16, row stride ldc) = A[M,K] (row stride lda) * B[N,K]^T (row stride ldb); all bf16, K-major.
+// Requirements: 16-byte aligned base pointers, lda/ldb multiples of 8 elements, ldc multiple of 8.
+int dsb200_gemm_bf16_nt(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb,
+                        int64_t ldc, int max_ctas, cudaStream_t stream)
+{
+    if (M <= 0 || N <= 0 || K <= 0) return 0;
+    if ((lda % 8) || (ldb % 8) || (ldc % 8) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15) || ((uintptr_t)C & 15)) {
+        dsb200_set_error("gemm_bf16_nt: operands must be 16-byte aligned with leading dimensions multiple of 8");
+        return -1;
+    }
+    CUtensorMap map_a, map_b;
+    if (make_map(&map_a, A, M, K, lda, BLOCK_M) != 0) return -2;
+    if (make_map(&map_b, B, N, K, ldb, BLOCK_N) != 0) return -2;
+    static bool attr_set = false;
+    if (!attr_set) {
+        DSB_CHECK(cudaFuncSetAttribute(gemm_bf16_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        attr_set = true;
+    }
+    const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BLOCK_N - 1) / BLOCK_N);
+    int grid = tiles < DSB_NUM_SMS ? tiles : DSB_NUM_SMS;
+    if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+    gemm_bf16_nt_kernel<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(map_a, map_b, (__nv_bfloat16*)C, M, N, K, ldc);
+    DSB_CHECK_LAUNCH("gemm_bf16_nt");
+    return 0;
+}
+
+}  // extern "C"
