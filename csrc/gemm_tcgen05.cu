@@ -19,17 +19,20 @@
 namespace {
 
 constexpr int BLOCK_M = 128;
-constexpr int BLOCK_N = 256;
 constexpr int BLOCK_K = 64;   // 64 bf16 = 128 bytes = one swizzle-128B row
 constexpr int UMMA_K = 16;
-constexpr int STAGES = 4;
+constexpr int MAX_STAGES = 6;
 constexpr int ACC_STAGES = 2;
 constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
-constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;  // 32 KB
-constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int TMEM_COLS = 512;
 constexpr int NUM_THREADS = 192;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+template <int BLOCK_N>
+struct Cfg {
+    static constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = (BLOCK_N >= 256) ? 4 : ((BLOCK_N >= 192) ? 5 : 6);
+    static constexpr int TMEM_COLS = (2 * BLOCK_N > 256) ? 512 : 256;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -121,8 +124,8 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
 }
 
 struct Smem {
-    uint64_t full[STAGES];
-    uint64_t empty[STAGES];
+    uint64_t full[MAX_STAGES];
+    uint64_t empty[MAX_STAGES];
     uint64_t tmem_full[ACC_STAGES];
     uint64_t tmem_empty[ACC_STAGES];
     uint32_t tmem_base;
@@ -130,10 +133,14 @@ struct Smem {
 
 // EPI: 0 = plain bf16 store; 1 = SwiGLU over interleaved (gate, up) column pairs is NOT used here - the fused
 // gate_up layout keeps gate in columns [0, N/2) and up in [N/2, N), so SwiGLU stays a separate kernel.
+template <int BLOCK_N>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_nt_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                     __nv_bfloat16* __restrict__ C, int M, int N, int K, int64_t ldc)
 {
+    constexpr int B_BYTES = Cfg<BLOCK_N>::B_BYTES, STAGE_BYTES = Cfg<BLOCK_N>::STAGE_BYTES;
+    constexpr int STAGES = Cfg<BLOCK_N>::STAGES, TMEM_COLS = Cfg<BLOCK_N>::TMEM_COLS;
+    (void)B_BYTES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     Smem* sm = reinterpret_cast<Smem*>(tiles + STAGES * STAGE_BYTES);
@@ -321,25 +328,54 @@ extern "C" {
 // C[M,N] (bf16, row stride ldc) = A[M,K] (row stride lda) * B[N,K]^T (row stride ldb); all bf16, K-major.
 // Requirements: 16-byte aligned base pointers, lda/ldb multiples of 8 elements, ldc multiple of 8.
 int dsb200_gemm_bf16_nt(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb,
-                        int64_t ldc, int max_ctas, cudaStream_t stream)
+                        int64_t ldc, int max_ctas, int force_bn, cudaStream_t stream)
 {
     if (M <= 0 || N <= 0 || K <= 0) return 0;
     if ((lda % 8) || (ldb % 8) || (ldc % 8) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15) || ((uintptr_t)C & 15)) {
         dsb200_set_error("gemm_bf16_nt: operands must be 16-byte aligned with leading dimensions multiple of 8");
         return -1;
     }
+    // pick BLOCK_N to minimise wave quantisation: cost ~ waves(tiles / 148) * BLOCK_N (+ small-tile penalty)
+    const int m_tiles = (M + BLOCK_M - 1) / BLOCK_M;
+    int best_bn = 256;
+    double best_cost = 1e30;
+    const int cands[3] = {256, 192, 128};
+    const double penalty[3] = {1.0, 1.05, 1.25};  // measured: narrower tiles re-read A more often (L2-bound)
+    for (int i = 0; i < 3; i++) {
+        const int bn = cands[i];
+        const long tiles_i = (long)m_tiles * ((N + bn - 1) / bn);
+        const long waves = (tiles_i + DSB_NUM_SMS - 1) / DSB_NUM_SMS;
+        const double cost = (double)waves * bn * penalty[i];
+        if (cost < best_cost - 1e-9) {
+            best_cost = cost;
+            best_bn = bn;
+        }
+    }
+    if (force_bn == 128 || force_bn == 192 || force_bn == 256) best_bn = force_bn;
     CUtensorMap map_a, map_b;
     if (make_map(&map_a, A, M, K, lda, BLOCK_M) != 0) return -2;
-    if (make_map(&map_b, B, N, K, ldb, BLOCK_N) != 0) return -2;
-    static bool attr_set = false;
-    if (!attr_set) {
-        DSB_CHECK(cudaFuncSetAttribute(gemm_bf16_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        attr_set = true;
-    }
-    const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BLOCK_N - 1) / BLOCK_N);
+    if (make_map(&map_b, B, N, K, ldb, best_bn) != 0) return -2;
+    const int tiles = m_tiles * ((N + best_bn - 1) / best_bn);
     int grid = tiles < DSB_NUM_SMS ? tiles : DSB_NUM_SMS;
     if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
-    gemm_bf16_nt_kernel<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(map_a, map_b, (__nv_bfloat16*)C, M, N, K, ldc);
+#define GEMM_LAUNCH(BN)                                                                                              \
+    do {                                                                                                             \
+        static bool attr_set = false;                                                                                \
+        if (!attr_set) {                                                                                             \
+            DSB_CHECK(cudaFuncSetAttribute(gemm_bf16_nt_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
+                                           Cfg<BN>::SMEM_BYTES));                                                   \
+            attr_set = true;                                                                                         \
+        }                                                                                                            \
+        gemm_bf16_nt_kernel<BN><<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(map_a, map_b, (__nv_bfloat16*)C, \
+                                                                                    M, N, K, ldc);                  \
+    } while (0)
+    if (best_bn == 256)
+        GEMM_LAUNCH(256);
+    else if (best_bn == 192)
+        GEMM_LAUNCH(192);
+    else
+        GEMM_LAUNCH(128);
+#undef GEMM_LAUNCH
     DSB_CHECK_LAUNCH("gemm_bf16_nt");
     return 0;
 }

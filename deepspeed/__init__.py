@@ -1,0 +1,80 @@
+"""``import deepspeed`` compatibility package: the reference's import paths resolved onto ``deepspeed_b200``.
+
+A user switching from the reference keeps ``import deepspeed``, ``deepspeed.initialize``, ``deepspeed.zero.Init``,
+``deepspeed.comm``, ``from deepspeed.ops.adam import FusedAdam`` ... Module paths that moved are translated by
+``_ALIASES``; everything else maps ``deepspeed.<path>`` -> ``deepspeed_b200.<path>``. Checkpoints pickle a few small
+objects (loss scaler, fragment addresses) under the reference's module names so files are interchangeable with
+the reference's tools; this package is what makes those names importable here.
+"""
+import importlib
+import importlib.abc
+import importlib.util
+import sys
+
+import deepspeed_b200 as _impl
+
+_ALIASES = {
+    "deepspeed.runtime.fp16.loss_scaler": "deepspeed_b200.runtime.loss_scaler",
+    "deepspeed.runtime.fp16": "deepspeed_b200.runtime",
+    "deepspeed.runtime.config": "deepspeed_b200.config.config",
+    "deepspeed.runtime.config_utils": "deepspeed_b200.config.base",
+    "deepspeed.runtime.zero.config": "deepspeed_b200.config.sections",
+    "deepspeed.runtime.zero.offload_config": "deepspeed_b200.config.sections",
+    "deepspeed.runtime.zero.partition_parameters": "deepspeed_b200.runtime.zero.init_context",
+    "deepspeed.runtime.zero.stage3": "deepspeed_b200.runtime.zero.sharded_optimizer",
+    "deepspeed.runtime.zero.stage_1_and_2": "deepspeed_b200.runtime.zero.sharded_optimizer",
+    "deepspeed.runtime.activation_checkpointing.checkpointing": "deepspeed_b200.runtime.activation_checkpointing",
+    "deepspeed.runtime.activation_checkpointing": "deepspeed_b200.runtime",
+    "deepspeed.checkpointing": "deepspeed_b200.runtime.activation_checkpointing",
+    "deepspeed.pipe": "deepspeed_b200.runtime.pipe",
+    "deepspeed.ops.adam": "deepspeed_b200.ops.adam",
+    "deepspeed.ops.lamb": "deepspeed_b200.ops.lamb",
+    "deepspeed.ops.lion": "deepspeed_b200.ops.lion",
+    "deepspeed.ops.adagrad": "deepspeed_b200.ops.adagrad",
+    "deepspeed.module_inject": "deepspeed_b200.parallel",
+    "deepspeed.utils.zero_to_fp32": "deepspeed_b200.checkpoint.zero_to_fp32",
+    "deepspeed.checkpoint.ds_to_universal": "deepspeed_b200.checkpoint.ds_to_universal",
+    "deepspeed.sequence.layer": "deepspeed_b200.sequence.layer",
+    "deepspeed.runtime.sequence_parallel.ulysses_sp": "deepspeed_b200.sequence.ulysses_sp",
+    "deepspeed.runtime.sequence_parallel": "deepspeed_b200.sequence",
+}
+
+
+class _AliasLoader(importlib.abc.Loader):
+
+    def __init__(self, target):
+        self.target = target
+
+    def create_module(self, spec):
+        mod = importlib.import_module(self.target)
+        return mod
+
+    def exec_module(self, module):
+        pass
+
+
+class _AliasFinder(importlib.abc.MetaPathFinder):
+
+    def find_spec(self, fullname, path, target=None):
+        if not fullname.startswith("deepspeed."):
+            return None
+        tgt = _ALIASES.get(fullname, "deepspeed_b200." + fullname[len("deepspeed."):])
+        try:
+            importlib.import_module(tgt)
+        except ImportError:
+            return None
+        spec = importlib.util.spec_from_loader(fullname, _AliasLoader(tgt))
+        return spec
+
+
+if not any(isinstance(f, _AliasFinder) for f in sys.meta_path):
+    sys.meta_path.insert(0, _AliasFinder())
+
+from deepspeed_b200 import *  # noqa: E402,F401,F403
+from deepspeed_b200 import (__version__, add_config_arguments, comm, init_distributed, init_inference,  # noqa: E402
+                            initialize, tp_model_init, zero, DeepSpeedEngine, DeepSpeedConfig)
+from deepspeed_b200 import comm as dist  # noqa: E402,F401
+
+
+def __getattr__(name):
+    return getattr(_impl, name)

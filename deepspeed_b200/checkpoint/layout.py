@@ -22,10 +22,7 @@ import torch
 from .. import comm as dist
 
 
-@dataclass
-class fragment_address:
-    numel: int
-    start: int
+from ..utils.tensor_fragment import fragment_address  # noqa: E402  (pickled under the reference's module path)
 
 
 def _cdiv(a, b):

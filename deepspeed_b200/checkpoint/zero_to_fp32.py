@@ -1,0 +1,243 @@
+#!/usr/bin/env python
+"""Consolidate a ZeRO-1/2/3 checkpoint into a single fp32 ``state_dict`` (offline, CPU only, no deepspeed import).
+
+This script is copied into every checkpoint folder. It understands the on-disk layout produced by this framework
+and by the reference (same files/keys, see ``utils/zero_to_fp32.py:282-460`` of the reference):
+
+* ``*_optim_states.pt`` per DP rank with ``optimizer_state_dict`` -> ``zero_stage``, ``partition_count`` and
+  ``single_partition_of_fp32_groups`` (stage 1/2: per param-group contiguous rank slices of the flat fp32 vector,
+  padded to ``2*world``) or ``fp32_flat_groups`` (stage 3: every parameter split ``ceil(numel/world)`` per rank);
+* ``*_model_states.pt`` with ``param_shapes``, ``buffer_names``, ``shared_params``, frozen-parameter info.
+
+Usage::
+
+    python zero_to_fp32.py <checkpoint_dir> <output_dir_or_file> [-t TAG] [--safe_serialization] [--max_shard_size 5GB]
+"""
+import argparse
+import glob
+import math
+import os
+import re
+from collections import OrderedDict
+
+import torch
+
+ZERO_STAGE = "zero_stage"
+PARTITION_COUNT = "partition_count"
+OPTIMIZER_STATE_DICT = "optimizer_state_dict"
+SINGLE_PARTITION_OF_FP32_GROUPS = "single_partition_of_fp32_groups"
+FP32_FLAT_GROUPS = "fp32_flat_groups"
+PARAM_SHAPES = "param_shapes"
+BUFFER_NAMES = "buffer_names"
+FROZEN_PARAM_SHAPES = "frozen_param_shapes"
+FROZEN_PARAM_FRAGMENTS = "frozen_param_fragments"
+
+
+def _natural_key(text):
+    return [int(c) if c.isdigit() else c for c in re.split(r"(\d+)", text)]
+
+
+def _files(ckpt_dir, pattern):
+    out = sorted(glob.glob(os.path.join(ckpt_dir, pattern)), key=_natural_key)
+    if not out:
+        raise FileNotFoundError(f"can't find {pattern} files in directory '{ckpt_dir}'")
+    return out
+
+
+class _Stub:
+    """Placeholder for pickled helper objects (loss scaler, fragment addresses) whose class is not importable."""
+
+    def __init__(self, *a, **k):
+        pass
+
+    def __setstate__(self, state):
+        self.__dict__.update(state if isinstance(state, dict) else {})
+
+
+class _TolerantUnpickler:
+    """pickle module shim for torch.load: unknown classes become :class:`_Stub` so the script runs stand-alone."""
+    import pickle as _p
+    __name__ = "tolerant_pickle"
+
+    class Unpickler(_p.Unpickler):
+
+        def find_class(self, mod_name, name):
+            try:
+                return super().find_class(mod_name, name)
+            except (ImportError, AttributeError):
+                return _Stub
+
+    load = staticmethod(_p.load)
+    loads = staticmethod(_p.loads)
+
+
+def _load(path):
+    try:
+        return torch.load(path, map_location="cpu", weights_only=False)
+    except (ImportError, AttributeError):
+        return torch.load(path, map_location="cpu", weights_only=False, pickle_module=_TolerantUnpickler)
+
+
+def _resolve_tag(checkpoint_dir, tag):
+    if tag is None:
+        latest = os.path.join(checkpoint_dir, "latest")
+        if not os.path.isfile(latest):
+            raise ValueError(f"Unable to find 'latest' file at {latest}")
+        with open(latest) as fd:
+            tag = fd.read().strip()
+    ds_dir = os.path.join(checkpoint_dir, tag)
+    if not os.path.isdir(ds_dir):
+        raise FileNotFoundError(f"Directory '{ds_dir}' doesn't exist")
+    return ds_dir
+
+
+def _cdiv(a, b):
+    return (a + b - 1) // b
+
+
+def _merge_stage12(fp32_groups_per_rank, param_shapes, world):
+    """fp32_groups_per_rank[rank][group] -> {name: tensor}."""
+    out = OrderedDict()
+    n_groups = len(fp32_groups_per_rank[0])
+    for g in range(n_groups):
+        full = torch.cat([fp32_groups_per_rank[r][g].reshape(-1) for r in range(world)], 0)
+        off = 0
+        for name, shape in param_shapes[g].items():
+            n = int(torch.Size(shape).numel())
+            out[name] = full.narrow(0, off, n).view(shape).clone()
+            off += n
+        # sanity: what is left must be alignment padding only
+        align = 2 * world
+        if _cdiv(off, align) * align < full.numel() - align:
+            raise ValueError(f"group {g}: consumed {off} of {full.numel()} elements - layout mismatch")
+    return out
+
+
+def _merge_stage3(flat_per_rank, param_shapes, world):
+    """flat_per_rank[rank] = concatenation of all sub-group flats of that rank."""
+    out = OrderedDict()
+    shapes = OrderedDict()
+    for d in param_shapes:
+        shapes.update(d)
+    off = 0
+    for name, shape in shapes.items():
+        n = int(torch.Size(shape).numel())
+        per = _cdiv(n, world)
+        parts = [flat_per_rank[r].narrow(0, off, per) for r in range(world)]
+        out[name] = torch.cat(parts, 0).narrow(0, 0, n).view(shape).clone()
+        off += per
+    return out
+
+
+def get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir, tag=None, exclude_frozen_parameters=False,
+                                             lazy_mode=False):
+    """Return the consolidated fp32 state dict (parameters + buffers + shared-parameter aliases)."""
+    ds_dir = _resolve_tag(checkpoint_dir, tag)
+    optim_files = _files(ds_dir, "*_optim_states.pt")
+    model_files = _files(ds_dir, "*_model_states.pt")
+    optim = [_load(f)[OPTIMIZER_STATE_DICT] for f in optim_files]
+    stage = optim[0][ZERO_STAGE]
+    world = optim[0][PARTITION_COUNT]
+    world = max(world) if isinstance(world, (list, tuple)) else world
+    if world != len(optim_files):
+        raise ValueError(f"Expected {world} of '*_optim_states.pt' under '{ds_dir}' but found {len(optim_files)} files.")
+    model_state = _load(model_files[0])
+    if BUFFER_NAMES not in model_state:
+        raise ValueError(f"{model_files[0]} is not a model state checkpoint")
+    param_shapes = model_state[PARAM_SHAPES]
+    print(f"Detected checkpoint of type zero stage {stage}, world_size: {world}")
+    if stage <= 2:
+        groups = [[t.float() for t in o[SINGLE_PARTITION_OF_FP32_GROUPS]] for o in optim]
+        state = _merge_stage12(groups, param_shapes, world)
+    elif stage == 3:
+        flats = [torch.cat([t.float().reshape(-1) for t in o[FP32_FLAT_GROUPS]], 0) for o in optim]
+        state = _merge_stage3(flats, param_shapes, world)
+    else:
+        raise ValueError(f"unknown zero stage {stage}")
+    # buffers (restored to fp32), frozen params, shared params
+    buffers = {k: v.float() for k, v in model_state["module"].items() if k in set(model_state[BUFFER_NAMES])}
+    state.update(buffers)
+    if not exclude_frozen_parameters and model_state.get(FROZEN_PARAM_SHAPES):
+        frags = model_state.get(FROZEN_PARAM_FRAGMENTS) or {}
+        for name, shape in model_state[FROZEN_PARAM_SHAPES].items():
+            if stage == 3 and len(model_files) > 1:
+                pieces = [(_load(f).get(FROZEN_PARAM_FRAGMENTS) or {}).get(name) for f in model_files]
+                if all(p is not None for p in pieces) and sum(p.numel() for p in pieces) >= torch.Size(shape).numel():
+                    state[name] = torch.cat([p.reshape(-1) for p in pieces])[:torch.Size(shape).numel()].view(shape).float()
+                    continue
+            if name in frags and frags[name].numel() == torch.Size(shape).numel():
+                state[name] = frags[name].view(shape).float()
+    for alias, src in (model_state.get("shared_params") or {}).items():
+        if src in state:
+            state[alias] = state[src]
+    return state
+
+
+def _parse_size(s):
+    if isinstance(s, int):
+        return s
+    m = re.match(r"^\s*(\d+(?:\.\d+)?)\s*([KMGT]?B)\s*$", s.upper())
+    if not m:
+        raise ValueError(f"bad size {s}")
+    return int(float(m.group(1)) * {"B": 1, "KB": 2**10, "MB": 2**20, "GB": 2**30, "TB": 2**40}[m.group(2)])
+
+
+def convert_zero_checkpoint_to_fp32_state_dict(checkpoint_dir, output_dir, max_shard_size="5GB",
+                                               safe_serialization=False, tag=None, exclude_frozen_parameters=False):
+    """Write the consolidated weights as (sharded) ``pytorch_model*.bin`` or ``model*.safetensors`` + index json."""
+    state = get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir, tag, exclude_frozen_parameters)
+    if output_dir.endswith((".bin", ".pt")):
+        os.makedirs(os.path.dirname(os.path.abspath(output_dir)), exist_ok=True)
+        torch.save(state, output_dir)
+        return
+    os.makedirs(output_dir, exist_ok=True)
+    limit = _parse_size(max_shard_size)
+    shards, cur, cur_bytes = [], OrderedDict(), 0
+    for k, v in state.items():
+        nb = v.numel() * v.element_size()
+        if cur and cur_bytes + nb > limit:
+            shards.append(cur)
+            cur, cur_bytes = OrderedDict(), 0
+        cur[k] = v
+        cur_bytes += nb
+    if cur:
+        shards.append(cur)
+    base, ext = ("model", ".safetensors") if safe_serialization else ("pytorch_model", ".bin")
+    index = {"metadata": {"total_size": sum(v.numel() * v.element_size() for v in state.values())}, "weight_map": {}}
+    for i, sh in enumerate(shards):
+        name = f"{base}{ext}" if len(shards) == 1 else f"{base}-{i + 1:05d}-of-{len(shards):05d}{ext}"
+        path = os.path.join(output_dir, name)
+        if safe_serialization:
+            from safetensors.torch import save_file
+            save_file({k: v.contiguous() for k, v in sh.items()}, path, metadata={"format": "pt"})
+        else:
+            torch.save(sh, path)
+        for k in sh:
+            index["weight_map"][k] = name
+    if len(shards) > 1:
+        import json
+        with open(os.path.join(output_dir, f"{base}{ext}.index.json"), "w") as f:
+            json.dump(index, f, indent=2, sort_keys=True)
+
+
+def load_state_dict_from_zero_checkpoint(model, checkpoint_dir, tag=None):
+    """Load consolidated fp32 weights into ``model`` (on CPU)."""
+    state = get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir, tag)
+    model = model.cpu()
+    model.load_state_dict(state, strict=False)
+    return model
+
+
+if __name__ == "__main__":
+    parser = argparse.ArgumentParser()
+    parser.add_argument("checkpoint_dir", type=str, help="path to the checkpoint folder (contains 'latest')")
+    parser.add_argument("output_dir", type=str, help="output directory (or .bin/.pt file) for the fp32 weights")
+    parser.add_argument("--max_shard_size", type=str, default="5GB")
+    parser.add_argument("--safe_serialization", default=False, action="store_true")
+    parser.add_argument("-t", "--tag", type=str, default=None)
+    parser.add_argument("--exclude_frozen_parameters", action="store_true")
+    parser.add_argument("-d", "--debug", action="store_true")
+    a = parser.parse_args()
+    convert_zero_checkpoint_to_fp32_state_dict(a.checkpoint_dir, a.output_dir, max_shard_size=a.max_shard_size,
+                                               safe_serialization=a.safe_serialization, tag=a.tag,
+                                               exclude_frozen_parameters=a.exclude_frozen_parameters)

@@ -318,7 +318,7 @@ def cross_entropy_fwd(logits, target, ignore_index):
 # ---------------------------------------------------------------------------------------------------------
 # tcgen05 GEMM
 # ---------------------------------------------------------------------------------------------------------
-def gemm_bf16_nt(a, b, out=None, max_ctas=0):
+def gemm_bf16_nt(a, b, out=None, max_ctas=0, block_n=0):
     """``out[M,N] = a[M,K] @ b[N,K].T`` (bf16 in/out, fp32 accumulate in TMEM) on the hand-written tcgen05 kernel."""
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.dim() == 2 and b.dim() == 2
     assert a.stride(1) == 1 and b.stride(1) == 1 and a.shape[1] == b.shape[1]
@@ -329,9 +329,9 @@ def gemm_bf16_nt(a, b, out=None, max_ctas=0):
     L = lib()
     if not hasattr(L, "_gemm_declared"):
         L.dsb200_gemm_bf16_nt.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64, c_int64,
-                                          c_int, c_void_p]
+                                          c_int, c_int, c_void_p]
         L.dsb200_gemm_bf16_nt.restype = c_int
         L._gemm_declared = True
     _check(L.dsb200_gemm_bf16_nt(_ptr(a), _ptr(b), _ptr(out), M, N, Kd, a.stride(0), b.stride(0), out.stride(0),
-                                 int(max_ctas), _stream()), "gemm_bf16_nt")
+                                 int(max_ctas), int(block_n), _stream()), "gemm_bf16_nt")
     return out

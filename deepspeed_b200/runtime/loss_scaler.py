@@ -105,3 +105,9 @@ def CreateLossScaler(dtype, static_loss_scale, dynamic_scaling, dynamic_loss_arg
         return DynamicLossScaler(dtype=dtype, **dynamic_loss_args)
     loss_scale_value = static_loss_scale if dtype == torch.half else 1.0
     return LossScaler(scale=loss_scale_value)
+
+
+# Pickle these small objects under the reference's module path so optimizer checkpoints are interchangeable with the
+# reference's tools/engine (``deepspeed.runtime.fp16.loss_scaler``; resolved here by the ``deepspeed`` alias package).
+for _cls in (LossScalerBase, LossScaler, DynamicLossScaler):
+    _cls.__module__ = "deepspeed.runtime.fp16.loss_scaler"

@@ -3,7 +3,19 @@
 Reference: ``utils/tensor_fragment.py:134-336`` (safe_get/set_full_{fp32_param,grad,optimizer_state} and the
 ``_local_`` variants). All ``full`` getters are collective (every rank of the shard group must call).
 """
+from dataclasses import dataclass
+
 import torch
+
+
+@dataclass
+class fragment_address:
+    """(start, numel) of a parameter fragment inside a rank partition; stored in ``param_slice_mappings``."""
+    numel: int
+    start: int
+
+
+fragment_address.__module__ = "deepspeed.utils.tensor_fragment"
 
 
 def _zopt(param):

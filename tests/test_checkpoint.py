@@ -1,0 +1,118 @@
+"""Checkpoint round trips: save/load (all stages), zero_to_fp32 (ours AND the reference's script reading our
+files), universal conversion with DP reshape 2 -> 1 (reference tests/unit/checkpoint/*)."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from common import run_distributed
+from simple_model import SimpleModel, random_batches
+
+HID = 16
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _cfg(stage, universal=False):
+    c = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}},
+         "zero_optimization": {"stage": stage, "unit_max_numel": 300, "stage3_param_persistence_threshold": 20,
+                               "reduce_bucket_size": 400}, "gradient_clipping": 1.0}
+    if universal:
+        c["checkpoint"] = {"load_universal": True}
+    return c
+
+
+def _train_and_save(stage, ckpt_dir, steps=3):
+    import deepspeed_b200 as ds
+    from deepspeed_b200.utils.tensor_fragment import safe_get_full_fp32_param, safe_get_full_optimizer_state
+    torch.manual_seed(0)
+    model = SimpleModel(HID, 3)
+    eng, _, _, _ = ds.initialize(model=model, config=_cfg(stage))
+    rank, world = ds.comm.get_rank(), ds.comm.get_world_size()
+    batches = random_batches(steps * world + world, 4, HID, "cpu")
+    for i in range(steps):
+        x, y = batches[i * world + rank]
+        loss = eng(x, y)
+        eng.backward(loss)
+        eng.step()
+    eng.save_checkpoint(ckpt_dir, tag="t1", client_state={"hello": 7})
+    full = {n: safe_get_full_fp32_param(p).clone() for n, p in model.named_parameters()}
+    m = {n: safe_get_full_optimizer_state(p, "exp_avg").clone() for n, p in model.named_parameters()}
+    # one more step: the reference trajectory the reloaded engine must reproduce
+    x, y = batches[steps * world + rank]
+    loss = eng(x, y)
+    eng.backward(loss)
+    eng.step()
+    after = {n: safe_get_full_fp32_param(p).clone() for n, p in model.named_parameters()}
+    return full, m, after
+
+
+def _load_and_step(stage, ckpt_dir, steps=3, universal=False, tag=None):
+    import deepspeed_b200 as ds
+    from deepspeed_b200.utils.tensor_fragment import safe_get_full_fp32_param, safe_get_full_optimizer_state
+    torch.manual_seed(123)  # different init: everything must come from the checkpoint
+    model = SimpleModel(HID, 3)
+    eng, _, _, _ = ds.initialize(model=model, config=_cfg(stage, universal))
+    path, client = eng.load_checkpoint(ckpt_dir, tag=tag)
+    assert path is not None
+    full = {n: safe_get_full_fp32_param(p).clone() for n, p in model.named_parameters()}
+    m = {n: safe_get_full_optimizer_state(p, "exp_avg").clone() for n, p in model.named_parameters()}
+    rank, world = ds.comm.get_rank(), ds.comm.get_world_size()
+    return full, m, client, eng.global_steps
+
+
+@pytest.mark.parametrize("stage", [1, 2, 3])
+def test_save_load_roundtrip_and_zero_to_fp32(stage, tmp_path):
+    d = str(tmp_path / "ck")
+    saved = run_distributed(_train_and_save, 2, args=(stage, d))
+    full, m, after = saved[0]
+    assert open(os.path.join(d, "latest")).read() == "t1"
+    files = sorted(os.listdir(os.path.join(d, "t1")))
+    assert any(f.endswith("_optim_states.pt") for f in files) and "zero_to_fp32.py" in files
+    # ---- reload on 2 ranks ----
+    loaded = run_distributed(_load_and_step, 2, args=(stage, d))
+    lfull, lm, client, gsteps = loaded[0]
+    assert client.get("hello") == 7 and gsteps == 3
+    for n in full:
+        torch.testing.assert_close(lfull[n], full[n], rtol=0, atol=0)
+        torch.testing.assert_close(lm[n], m[n], rtol=0, atol=1e-7)
+    # ---- offline consolidation with OUR script (copied into the checkpoint) ----
+    out = str(tmp_path / "fp32.pt")
+    subprocess.check_call([sys.executable, os.path.join(d, "t1", "zero_to_fp32.py"), d, out], cwd=str(tmp_path),
+                          env=dict(os.environ, PYTHONPATH=""))
+    sd = torch.load(out, weights_only=False)
+    for n in full:
+        torch.testing.assert_close(sd[n], full[n], rtol=0, atol=0)
+    # ---- and with the REFERENCE's zero_to_fp32 reading our files (on-disk format compatibility) ----
+    ref = os.path.join(REPO, "baseline", "_ref", "deepspeed", "utils", "zero_to_fp32.py")
+    if os.path.exists(ref):
+        out2 = str(tmp_path / "ref_out")
+        subprocess.check_call([sys.executable, "-m", "deepspeed.utils.zero_to_fp32", d, out2], cwd=str(tmp_path),
+                              env=dict(os.environ, PYTHONPATH=os.path.join(REPO, "baseline", "_ref")))
+        got = {}
+        for f in os.listdir(out2):
+            if f.endswith(".bin"):
+                got.update(torch.load(os.path.join(out2, f), weights_only=False))
+        for n in full:
+            torch.testing.assert_close(got[n].float(), full[n], rtol=0, atol=0)
+
+
+@pytest.mark.parametrize("stage", [2, 3])
+def test_universal_checkpoint_dp_reshape(stage, tmp_path):
+    d = str(tmp_path / "ck")
+    saved = run_distributed(_train_and_save, 2, args=(stage, d))
+    full, m, _ = saved[0]
+    from deepspeed_b200.checkpoint import ds_to_universal
+    args = ds_to_universal.parse_arguments(["--input_folder", os.path.join(d, "t1"), "--output_folder",
+                                            os.path.join(d, "t1_universal"), "--num_extract_workers", "1",
+                                            "--num_merge_workers", "1"])
+    ds_to_universal.main(args)
+    assert open(os.path.join(d, "latest_universal")).read() == "t1_universal"
+    # load on ONE rank (dp 2 -> 1)
+    loaded = run_distributed(_load_and_step, 1, args=(stage, d), kwargs=dict(universal=True))
+    lfull, lm, _, gsteps = loaded[0]
+    assert gsteps == 3
+    for n in full:
+        torch.testing.assert_close(lfull[n], full[n], rtol=0, atol=0)
+        torch.testing.assert_close(lm[n], m[n], rtol=0, atol=1e-7)

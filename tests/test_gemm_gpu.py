@@ -25,6 +25,17 @@ def test_gemm_bf16_nt_matches_fp32(shape):
     assert (out.float() - cub).abs().max().item() <= 2e-2 * scale + 1e-2
 
 
+@pytest.mark.parametrize("block_n", [128, 192, 256])
+def test_gemm_forced_tile_widths(block_n):
+    from deepspeed_b200.ops import kernels as K
+    torch.manual_seed(2)
+    a = torch.randn(1024, 1024, device="cuda", dtype=torch.bfloat16)
+    b = torch.randn(1000, 1024, device="cuda", dtype=torch.bfloat16)
+    out = K.gemm_bf16_nt(a, b, block_n=block_n)
+    ref = a.float() @ b.float().t()
+    assert (out.float() - ref).abs().max().item() <= 1e-2 * ref.abs().max().item() + 1e-2
+
+
 def test_gemm_strided_operands():
     from deepspeed_b200.ops import kernels as K
     torch.manual_seed(1)
