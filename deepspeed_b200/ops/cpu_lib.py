@@ -1,0 +1,47 @@
+"""ctypes loader of the host runtime library ``libdsb200_cpu.so`` (AVX-512/OpenMP optimizers, async file I/O)."""
+import ctypes
+import os
+import threading
+
+_LIB = None
+_LOCK = threading.Lock()
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libdsb200_cpu.so")
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        with _LOCK:
+            if _LIB is None:
+                if not os.path.exists(LIB_PATH):
+                    from .builder import build_cpu_library
+                    build_cpu_library(verbose=False)
+                L = ctypes.CDLL(LIB_PATH)
+                P, I, L64, F = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float
+                L.dsb200_cpu_adam.argtypes = [P, P, I, P, P, P, I, L64, F, F, F, F, F, I, I, I, F]
+                L.dsb200_cpu_adam.restype = None
+                L.dsb200_cpu_adam_rollback.argtypes = [P, P, I, P, P, L64, F, F, F, F, F, I, I, I, F]
+                L.dsb200_cpu_adam_rollback.restype = None
+                L.dsb200_cpu_adagrad.argtypes = [P, P, I, P, P, I, L64, F, F, F, F]
+                L.dsb200_cpu_adagrad.restype = None
+                L.dsb200_cpu_lion.argtypes = [P, P, I, P, P, I, L64, F, F, F, F, F]
+                L.dsb200_cpu_lion.restype = None
+                L.dsb200_cpu_cast.argtypes = [P, P, I, L64]
+                L.dsb200_cpu_cast.restype = None
+                L.dsb200_cpu_sumsq.argtypes = [P, L64]
+                L.dsb200_cpu_sumsq.restype = ctypes.c_double
+                L.dsb200_cpu_num_threads.restype = I
+                L.dsb200_aio_create.argtypes = [L64, I, I, I]
+                L.dsb200_aio_create.restype = P
+                L.dsb200_aio_destroy.argtypes = [P]
+                L.dsb200_aio_pread.argtypes = [P, P, L64, ctypes.c_char_p, L64, I]
+                L.dsb200_aio_pread.restype = I
+                L.dsb200_aio_pwrite.argtypes = [P, P, L64, ctypes.c_char_p, L64, I]
+                L.dsb200_aio_pwrite.restype = I
+                L.dsb200_aio_wait.argtypes = [P]
+                L.dsb200_aio_wait.restype = L64
+                L.dsb200_aligned_alloc.argtypes = [L64, L64]
+                L.dsb200_aligned_alloc.restype = P
+                L.dsb200_aligned_free.argtypes = [P]
+                _LIB = L
+    return _LIB

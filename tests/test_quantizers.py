@@ -1,0 +1,62 @@
+"""Quantizer ops: CPU math paths here; the CUDA kernels are checked against the same math in test_quant_gpu.py."""
+import pytest
+import torch
+
+
+def test_fp8_block_roundtrip_error_bound():
+    from deepspeed_b200.ops import quantizer as Q
+    torch.manual_seed(0)
+    x = (torch.randn(8 * 512) * 3).to(torch.bfloat16)
+    q, s = Q.fp8_block_quantize(x)
+    y = Q.fp8_block_dequantize(q, s)
+    rel = (y.float() - x.float()).abs() / (x.float().abs() + 1e-3)
+    assert rel.median() < 0.04 and q.numel() == x.numel() and s.numel() == 8
+
+
+@pytest.mark.parametrize("bits", [8, 4])
+def test_int_group_quant_roundtrip_and_swizzle(bits):
+    from deepspeed_b200.ops import quantizer as Q
+    torch.manual_seed(0)
+    x = torch.randn(16 * 256).to(torch.bfloat16)
+    q, s = Q.quantize(x, 16, bits)
+    y = Q.dequantize(q, s, 16, bits)
+    tol = (x.float().abs().max() / (127 if bits == 8 else 7)).item()
+    assert (y.float() - x.float()).abs().max().item() <= tol * 0.51 + 1e-2
+    # swizzled layout is a permutation of the groups: [node, dev] -> [dev, node]
+    qs, ss = Q.swizzle_quant(x, 16, bits, 2, 4)
+    ys = Q.dequantize(qs, ss, 16, bits).view(4, 2, 2, 256).permute(1, 0, 2, 3).reshape(-1)
+    torch.testing.assert_close(ys, y)
+
+
+def test_quantized_reduction_means_chunks():
+    from deepspeed_b200.ops import quantizer as Q
+    torch.manual_seed(0)
+    x = torch.randn(4 * 1024).to(torch.bfloat16)
+    q, s = Q.quantize(x, 16, 8)
+    out = Q.quantized_reduction(q, s, 16, 4, 8, nchunks=4)
+    ref = Q.dequantize(q, s, 16, 8).float().view(4, 1024).mean(0)
+    torch.testing.assert_close(out.float(), ref, rtol=1e-2, atol=1e-2)
+
+
+@pytest.mark.parametrize("q_bits", [8, 6, 4, 12])
+def test_fp_quantize_formats(q_bits):
+    from deepspeed_b200.ops.fp_quantizer import FP_Quantize
+    torch.manual_seed(0)
+    x = torch.randn(4, 1024).to(torch.bfloat16)
+    fq = FP_Quantize(group_size=512)
+    qt = fq.quantize(x, q_bits=q_bits)
+    y = fq.dequantize(qt)
+    err = (y.float() - x.float()).abs().max().item()
+    bound = {8: 0.3, 6: 0.6, 4: 1.6, 12: 0.05}[q_bits]
+    assert y.shape == x.shape and err < bound, err
+    assert fq.get_scales().numel() == 8
+
+
+def test_fp_selective_dequantize():
+    from deepspeed_b200.ops.fp_quantizer import FP_Quantize
+    x = torch.randn(4, 8, 128).to(torch.bfloat16)
+    fq = FP_Quantize(group_size=256)
+    qt = fq.quantize(x, q_bits=8)
+    sel = fq.selective_dequantize(qt, torch.tensor([2, 0]))
+    full = fq.dequantize(qt)
+    torch.testing.assert_close(sel, full[[2, 0]])
