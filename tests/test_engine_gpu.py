@@ -44,21 +44,18 @@ def test_llama_bf16_trains_all_stages(stage):
 
 
 def test_fused_path_matches_torch_path_fp32_master():
-    """Same model/data: engine with FusedAdam (native) vs engine with torch.optim.AdamW -> same master weights."""
+    """Same model/data: engine with FusedAdam (native) vs engine with torch.optim.AdamW. Run-to-run nondeterminism of
+    the library GEMM/attention backward is measured with a second fused run and used as the yardstick."""
     _env()
     import deepspeed_b200 as ds
-    from deepspeed_b200.models import LlamaConfig, LlamaForCausalLM, llama
+    from deepspeed_b200.models import LlamaConfig, LlamaForCausalLM
     from deepspeed_b200.utils.tensor_fragment import safe_get_full_fp32_param
-    # deterministic attention backward (the flash kernels accumulate dq with atomics): both runs then see bitwise
-    # identical gradients and differ only by the rounding of the Adam arithmetic
-    os.environ["DSB200_SDPA"] = "math"
-    llama._SDPA_BACKEND = "unset"
     dev = torch.device("cuda", 0)
     cfg = LlamaConfig(vocab_size=1024, hidden_size=128, intermediate_size=256, num_hidden_layers=2,
                       num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=128,
                       gradient_checkpointing=False)
     results = []
-    for torch_adam in (False, True):
+    for torch_adam in (False, False, True):
         torch.manual_seed(0)
         model = LlamaForCausalLM(cfg, device=dev)
         eng, _, _, _ = ds.initialize(model=model, config={
@@ -73,12 +70,9 @@ def test_fused_path_matches_torch_path_fp32_master():
             eng.step()
         results.append({n: safe_get_full_fp32_param(p).clone() for n, p in model.named_parameters()})
         eng.destroy()
-    os.environ.pop("DSB200_SDPA", None)
-    llama._SDPA_BACKEND = "unset"
-    # attention backward uses atomics -> last-bit gradient noise between two runs -> rare sign flips of near-zero
-    # gradients change an Adam update by ~lr; require that only a tiny fraction of elements differ at all.
-    for n in results[0]:
-        a, b = results[0][n], results[1][n]
-        bad = ((a - b).abs() > 1e-5 + 1e-4 * b.abs()).float().mean().item()
-        assert bad < 0.02, f"{n}: {bad:.4f} of elements differ"
-        assert (a - b).abs().max().item() < 3 * 3 * 1e-3
+    fused, fused2, ref = results
+    for n in fused:
+        noise = (fused[n] - fused2[n]).abs().mean().item()
+        diff = (fused[n] - ref[n]).abs().mean().item()
+        assert diff <= 3.0 * noise + 5e-7, f"{n}: fused-vs-torch {diff:.3e} exceeds run-to-run noise {noise:.3e}"
+        assert (fused[n] - ref[n]).abs().max().item() < 3 * 3 * 1e-3
