@@ -1,0 +1,71 @@
+"""MoE: capacity (DS-MoE ``MoE``) and dropless (AutoEP) layers; expert parallel (ep=2) matches ep=1
+(reference tests/unit/v1/moe/*)."""
+import torch
+
+from common import run_distributed
+
+
+def test_topk_gating_capacity_and_aux_loss():
+    from deepspeed_b200.moe.sharded_moe import topkgating
+    torch.manual_seed(0)
+    logits = torch.randn(64, 4)
+    l_aux, idx, slot, w, cap, counts = topkgating(logits, 2, capacity_factor=1.0, min_capacity=4)
+    assert cap == 32 and idx.shape == (64, 2) and int(counts.sum()) == 128
+    assert (slot[slot >= 0] < cap).all() and float(l_aux) > 0
+    # slots are unique per expert
+    for e in range(4):
+        s = slot[(idx == e) & (slot >= 0)]
+        assert s.numel() == s.unique().numel()
+
+
+def test_ds_moe_layer_equals_dense_expert_when_single_expert():
+    from deepspeed_b200.moe import MoE
+    torch.manual_seed(0)
+    expert = torch.nn.Sequential(torch.nn.Linear(16, 32), torch.nn.GELU(), torch.nn.Linear(32, 16))
+    moe = MoE(16, expert, num_experts=1, ep_size=1, k=1, capacity_factor=4.0, min_capacity=64)
+    moe.deepspeed_moe._set_ep_group(None)
+    x = torch.randn(2, 8, 16)
+    out, l_aux, counts = moe(x)
+    ref = moe.deepspeed_moe.experts.deepspeed_experts[0](x)
+    torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-6)
+
+
+def _autoep(ep):
+    import deepspeed_b200 as ds
+    from deepspeed_b200.models.mixtral import MixtralConfig, MixtralForCausalLM
+    from deepspeed_b200.utils import groups
+    torch.manual_seed(0)
+    cfg = MixtralConfig.tiny(dtype=torch.float32, gradient_checkpointing=False, ep_size=1, router_aux_loss_coef=0.0)
+    full = MixtralForCausalLM(cfg)
+    sd = full.state_dict()
+    rank = ds.comm.get_rank()
+    if ep > 1:
+        cfg2 = MixtralConfig.tiny(dtype=torch.float32, gradient_checkpointing=False, ep_size=ep, router_aux_loss_coef=0.0)
+        model = MixtralForCausalLM(cfg2)
+        nl = cfg.num_local_experts // ep
+        for k in list(sd.keys()):
+            if ".experts.w" in k:
+                sd[k] = sd[k][rank * nl:(rank + 1) * nl].clone()
+        model.load_state_dict(sd)
+        groups.initialize()
+        model.set_deepspeed_parallelism()
+    else:
+        model = full
+    torch.manual_seed(7)
+    ids = torch.randint(0, 512, (2, 16))  # same tokens on every rank
+    loss = model(ids, labels=ids)
+    loss.backward()
+    g = model.layers[0].block_sparse_moe.experts.w2.grad.clone()
+    gr = model.layers[0].block_sparse_moe.router.weight.grad.clone()
+    return float(loss), g, gr, rank
+
+
+def test_autoep_expert_parallel_matches_single():
+    single = run_distributed(_autoep, 1, args=(1, ))[0]
+    ep = run_distributed(_autoep, 2, args=(2, ))
+    for loss, g, gr, rank in ep:
+        assert abs(loss - single[0]) < 1e-4
+        nl = single[1].shape[0] // 2
+        # every rank saw the same batch, so each local expert accumulated both ranks' (identical) tokens: 2x
+        torch.testing.assert_close(g, 2 * single[1][rank * nl:(rank + 1) * nl], rtol=1e-3, atol=1e-5)
+        torch.testing.assert_close(gr, single[2], rtol=1e-3, atol=1e-5)
