@@ -1,0 +1,181 @@
+"""``get_accelerator()`` compatibility shim. The reference's 72-method multi-backend abstraction
+(``accelerator/abstract_accelerator.py``, 9 backends) is dropped by design: there is one device family (CUDA/B200,
+with CPU for the plumbing tests). User code that calls ``get_accelerator().xxx`` keeps working."""
+import os
+
+import torch
+
+
+class B200Accelerator:
+    _name = "cuda"
+
+    def is_synchronized_device(self):
+        return False
+
+    def use_host_timers(self):
+        return not torch.cuda.is_available()
+
+    def resolves_data_dependency(self):
+        return False
+
+    def handles_memory_backpressure(self):
+        return False
+
+    def device_name(self, device_index=None):
+        base = "cuda" if torch.cuda.is_available() else "cpu"
+        return base if device_index is None or base == "cpu" else f"cuda:{device_index}"
+
+    def device(self, device_index=None):
+        return torch.device(self.device_name(device_index))
+
+    def set_device(self, device_index):
+        if torch.cuda.is_available():
+            torch.cuda.set_device(device_index)
+
+    def current_device(self):
+        return torch.cuda.current_device() if torch.cuda.is_available() else 0
+
+    def current_device_name(self):
+        return self.device_name(self.current_device())
+
+    def device_count(self):
+        return torch.cuda.device_count() if torch.cuda.is_available() else 1
+
+    def synchronize(self, device_index=None):
+        if torch.cuda.is_available():
+            torch.cuda.synchronize(device_index)
+
+    def is_available(self):
+        return torch.cuda.is_available()
+
+    def communication_backend_name(self):
+        return "nccl" if torch.cuda.is_available() else "gloo"
+
+    def manual_seed(self, seed):
+        torch.manual_seed(seed)
+        if torch.cuda.is_available():
+            torch.cuda.manual_seed(seed)
+
+    def manual_seed_all(self, seed):
+        torch.manual_seed(seed)
+        if torch.cuda.is_available():
+            torch.cuda.manual_seed_all(seed)
+
+    def get_rng_state(self, device_index=None):
+        return torch.cuda.get_rng_state(device_index) if torch.cuda.is_available() else torch.get_rng_state()
+
+    def set_rng_state(self, new_state, device_index=None):
+        if torch.cuda.is_available():
+            torch.cuda.set_rng_state(new_state, device_index if device_index is not None else "cuda")
+        else:
+            torch.set_rng_state(new_state)
+
+    def Stream(self, *a, **k):
+        return torch.cuda.Stream(*a, **k) if torch.cuda.is_available() else None
+
+    def stream(self, s):
+        import contextlib
+        return torch.cuda.stream(s) if torch.cuda.is_available() else contextlib.nullcontext()
+
+    def current_stream(self, device_index=None):
+        return torch.cuda.current_stream(device_index) if torch.cuda.is_available() else None
+
+    def default_stream(self, device_index=None):
+        return torch.cuda.default_stream(device_index) if torch.cuda.is_available() else None
+
+    def Event(self, **kw):
+        return torch.cuda.Event(**kw) if torch.cuda.is_available() else None
+
+    def empty_cache(self):
+        if torch.cuda.is_available():
+            torch.cuda.empty_cache()
+
+    def memory_allocated(self, device_index=None):
+        return torch.cuda.memory_allocated(device_index) if torch.cuda.is_available() else 0
+
+    def max_memory_allocated(self, device_index=None):
+        return torch.cuda.max_memory_allocated(device_index) if torch.cuda.is_available() else 0
+
+    def reset_peak_memory_stats(self, device_index=None):
+        if torch.cuda.is_available():
+            torch.cuda.reset_peak_memory_stats(device_index)
+
+    def memory_reserved(self, device_index=None):
+        return torch.cuda.memory_reserved(device_index) if torch.cuda.is_available() else 0
+
+    def total_memory(self, device_index=None):
+        return torch.cuda.get_device_properties(device_index or 0).total_memory if torch.cuda.is_available() else 0
+
+    def available_memory(self, device_index=None):
+        return torch.cuda.mem_get_info(device_index)[0] if torch.cuda.is_available() else 0
+
+    def is_bf16_supported(self):
+        return True
+
+    def is_fp16_supported(self):
+        return True
+
+    def supported_dtypes(self):
+        return [torch.float, torch.half, torch.bfloat16]
+
+    def is_triton_supported(self):
+        return False  # no Triton on hot paths by design
+
+    def pin_memory(self, tensor, align_bytes=1):
+        return tensor.pin_memory() if torch.cuda.is_available() else tensor
+
+    def is_pinned(self, tensor):
+        return tensor.is_pinned()
+
+    def on_accelerator(self, tensor):
+        return tensor.is_cuda
+
+    def range_push(self, msg):
+        if torch.cuda.is_available():
+            torch.cuda.nvtx.range_push(msg)
+
+    def range_pop(self):
+        if torch.cuda.is_available():
+            torch.cuda.nvtx.range_pop()
+
+    def lazy_call(self, callback):
+        callback()
+
+    def op_builder_dir(self):
+        return "deepspeed_b200.ops"
+
+    def create_op_builder(self, class_name):
+        b = self.get_op_builder(class_name)
+        return b() if b is not None else None
+
+    def get_op_builder(self, class_name):
+        from ..ops import op_builders
+        return getattr(op_builders, class_name, None)
+
+    def build_extension(self):
+        from torch.utils.cpp_extension import BuildExtension
+        return BuildExtension
+
+    def export_envs(self):
+        return ["NCCL", "CUDA", "DSB200"]
+
+    def visible_devices_envs(self):
+        return ["CUDA_VISIBLE_DEVICES"]
+
+    def get_compile_backend(self):
+        return "inductor"
+
+
+_ACC = None
+
+
+def get_accelerator():
+    global _ACC
+    if _ACC is None:
+        _ACC = B200Accelerator()
+    return _ACC
+
+
+def set_accelerator(acc):
+    global _ACC
+    _ACC = acc

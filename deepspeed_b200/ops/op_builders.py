@@ -1,0 +1,43 @@
+"""Builder shims with the reference's names (``FusedAdamBuilder().load()`` ...). Everything is prebuilt into
+``libdsb200.so`` / ``libdsb200_cpu.so`` by :mod:`deepspeed_b200.ops.builder`; ``load()`` returns the Python module
+that exposes the op."""
+import importlib
+
+
+class _Builder:
+    NAME = "op"
+    MODULE = None
+
+    def is_compatible(self, verbose=False):
+        return True
+
+    def load(self, verbose=False):
+        return importlib.import_module(self.MODULE)
+
+    def builder(self):
+        return self
+
+    def absolute_name(self):
+        return f"deepspeed_b200.ops.{self.NAME}"
+
+
+def _mk(name, module):
+    return type(name, (_Builder, ), {"NAME": name.replace("Builder", "").lower(), "MODULE": module})
+
+
+FusedAdamBuilder = _mk("FusedAdamBuilder", "deepspeed_b200.ops.optimizers")
+FusedLambBuilder = _mk("FusedLambBuilder", "deepspeed_b200.ops.optimizers")
+FusedLionBuilder = _mk("FusedLionBuilder", "deepspeed_b200.ops.optimizers")
+CPUAdamBuilder = _mk("CPUAdamBuilder", "deepspeed_b200.ops.cpu_optimizers")
+CPUAdagradBuilder = _mk("CPUAdagradBuilder", "deepspeed_b200.ops.cpu_optimizers")
+CPULionBuilder = _mk("CPULionBuilder", "deepspeed_b200.ops.cpu_optimizers")
+AsyncIOBuilder = _mk("AsyncIOBuilder", "deepspeed_b200.ops.aio")
+QuantizerBuilder = _mk("QuantizerBuilder", "deepspeed_b200.ops.quantizer")
+FPQuantizerBuilder = _mk("FPQuantizerBuilder", "deepspeed_b200.ops.fp_quantizer")
+UtilsBuilder = _mk("UtilsBuilder", "deepspeed_b200.ops.utils_op")
+TransformerBuilder = _mk("TransformerBuilder", "deepspeed_b200.ops.transformer")
+RandomLTDBuilder = _mk("RandomLTDBuilder", "deepspeed_b200.ops.random_ltd")
+SparseAttnBuilder = _mk("SparseAttnBuilder", "deepspeed_b200.ops.sparse_attention")
+EvoformerAttnBuilder = _mk("EvoformerAttnBuilder", "deepspeed_b200.ops.deepspeed4science")
+InferenceBuilder = _mk("InferenceBuilder", "deepspeed_b200.inference.kernels")
+ALL_OPS = {k: v for k, v in globals().items() if k.endswith("Builder") and k != "_Builder"}
