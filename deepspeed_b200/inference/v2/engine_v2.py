@@ -1,0 +1,132 @@
+"""FastGen-style engine: ``put(uids, tokens)`` runs one ragged forward (prefill chunks and decode tokens mixed) over
+a blocked KV cache and returns next-token logits per sequence.
+
+Reference: ``inference/v2/engine_v2.py:30`` (``InferenceEngineV2.put/query/flush``), model implementations
+``inference/v2/model_implementations/llama_v2`` (here: the framework's own Llama/Mixtral weights), ragged kernels
+``inference/v2/kernels/ragged_ops`` (blocked rotary + KV copy, blocked flash). Attention per sequence uses the
+library SDPA over the gathered blocks; the linear layers / norms / RoPE are the fused ops of this framework."""
+import torch
+import torch.nn.functional as F
+
+from ...ops import fused
+from .ragged import BlockedKVCache, DSStateManager, RaggedBatchWrapper
+
+
+class RaggedInferenceEngineConfig:
+
+    def __init__(self, kv_block_size=64, num_kv_blocks=1024, max_ragged_batch_size=768, max_ragged_sequence_count=512,
+                 max_tracked_sequences=2048):
+        self.kv_block_size, self.num_kv_blocks = kv_block_size, num_kv_blocks
+        self.max_ragged_batch_size, self.max_ragged_sequence_count = max_ragged_batch_size, max_ragged_sequence_count
+        self.max_tracked_sequences = max_tracked_sequences
+
+
+class InferenceEngineV2:
+
+    def __init__(self, model, config: RaggedInferenceEngineConfig = None):
+        self.model = model.eval()
+        self.cfg = model.cfg
+        self.config = config or RaggedInferenceEngineConfig()
+        p = next(model.parameters())
+        self.device, self.dtype = p.device, p.dtype
+        c = self.cfg
+        kv = BlockedKVCache(c.num_hidden_layers, self.config.num_kv_blocks, self.config.kv_block_size,
+                            c.num_key_value_heads, c.head_dim, self.dtype, self.device)
+        self.state_manager = DSStateManager(kv, self.config.max_tracked_sequences, self.config.max_ragged_batch_size,
+                                            self.config.max_ragged_sequence_count)
+        self.batch = RaggedBatchWrapper()
+        self.cos, self.sin = fused.rope_tables(c.max_position_embeddings, c.head_dim, c.rope_theta, self.device,
+                                               c.rope_scaling)
+
+    @property
+    def free_blocks(self):
+        return self.state_manager.free_blocks
+
+    def query(self, uid, max_request_tokens, max_request_blocks=None):
+        return self.state_manager.query(uid, max_request_tokens)
+
+    def can_schedule(self, uids, lengths):
+        total_blocks = 0
+        if sum(lengths) > self.config.max_ragged_batch_size or len(uids) > self.config.max_ragged_sequence_count:
+            return False
+        for uid, n in zip(uids, lengths):
+            ok, need = self.state_manager.query(uid, n)
+            if ok == 0:
+                return False
+            total_blocks += need
+        return total_blocks <= self.free_blocks
+
+    def flush(self, uid):
+        self.state_manager.flush_sequence(uid)
+
+    @torch.no_grad()
+    def put(self, batch_uids, batch_tokens, do_checks=True):
+        """Returns logits [n_sequences, vocab] for the last token of each sequence chunk."""
+        if do_checks and not self.can_schedule(batch_uids, [len(t) for t in batch_tokens]):
+            raise RuntimeError("ragged batch cannot be scheduled (KV blocks / batch limits)")
+        self.batch.clear()
+        for uid, toks in zip(batch_uids, batch_tokens):
+            seq = self.state_manager.get_or_create_sequence(uid)
+            toks = torch.as_tensor(toks, dtype=torch.long)
+            self.state_manager.ensure_capacity(seq, len(toks))
+            seq.pre_forward(len(toks))
+            self.batch.insert_sequence(seq, toks)
+        ids = self.batch.finalize(self.device)
+        logits = self._forward(ids)
+        for seq, _, _, _ in self.batch.seq_meta:
+            seq.post_forward()
+        return logits
+
+    def _forward(self, ids):
+        m = self.model
+        inner = getattr(m, "model", m)
+        layers = inner.layers
+        h = inner.embed_tokens(ids)  # [T, H]
+        pos = torch.cat([torch.arange(seen, seen + n, device=self.device) for (_, _, n, seen) in self.batch.seq_meta])
+        nh, nkv, hd = self.cfg.num_attention_heads, self.cfg.num_key_value_heads, self.cfg.head_dim
+        for li, layer in enumerate(layers):
+            x = layer.input_layernorm(h)
+            attn = layer.self_attn
+            qkv = attn.qkv_proj(x)
+            lnh, lnkv = attn.nh, attn.nkv
+            q, k, v = qkv.split([lnh * hd, lnkv * hd, lnkv * hd], dim=-1)
+            q = fused.apply_rope(q.reshape(1, -1, lnh, hd), self.cos, self.sin, pos.view(1, -1))[0]
+            k = fused.apply_rope(k.reshape(1, -1, lnkv, hd), self.cos, self.sin, pos.view(1, -1))[0]
+            v = v.reshape(-1, lnkv, hd)
+            outs = []
+            for (seq, start, n, seen) in self.batch.seq_meta:
+                self.state_manager.kv.write(li, seq, k[start:start + n], v[start:start + n], seen)
+                kk, vv = self.state_manager.kv.read(li, seq, seen + n)
+                qq = q[start:start + n].transpose(0, 1).unsqueeze(0)  # [1, h, n, d]
+                rep = lnh // lnkv
+                kk = kk.transpose(0, 1).repeat_interleave(rep, 0).unsqueeze(0)
+                vv = vv.transpose(0, 1).repeat_interleave(rep, 0).unsqueeze(0)
+                mask = (torch.arange(seen + n, device=self.device)[None, :] <=
+                        (torch.arange(n, device=self.device) + seen)[:, None])
+                o = F.scaled_dot_product_attention(qq, kk, vv, attn_mask=mask)
+                outs.append(o[0].transpose(0, 1).reshape(n, lnh * hd))
+            a = attn.o_proj(torch.cat(outs, 0))
+            x2, h = layer.post_attention_layernorm(a, residual=h)
+            ffn = layer.mlp if hasattr(layer, "mlp") else layer.block_sparse_moe
+            h = h + ffn(x2.unsqueeze(0))[0] if not hasattr(layer, "mlp") else h + ffn(x2)
+        h = inner.norm(h)
+        last = torch.tensor([s + n - 1 for (_, s, n, _) in self.batch.seq_meta], device=self.device)
+        head = m.lm_head
+        return head(h.index_select(0, last))
+
+
+@torch.no_grad()
+def greedy_generate(model, input_ids, max_new_tokens=16, **kw):
+    """Greedy decoding through the ragged engine (one sequence per row of ``input_ids``)."""
+    eng = InferenceEngineV2(model)
+    out = [list(map(int, row)) for row in input_ids.tolist()]
+    uids = list(range(len(out)))
+    logits = eng.put(uids, [torch.tensor(r) for r in out])
+    for _ in range(max_new_tokens):
+        nxt = logits.argmax(-1).tolist()
+        for r, t in zip(out, nxt):
+            r.append(int(t))
+        logits = eng.put(uids, [torch.tensor([t]) for t in nxt])
+    for u in uids:
+        eng.flush(u)
+    return torch.tensor(out)

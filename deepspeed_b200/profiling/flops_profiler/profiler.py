@@ -1,0 +1,227 @@
+"""FLOPs profiler: per-module MACs/FLOPs/params/latency tree.
+
+Reference: ``profiling/flops_profiler/profiler.py`` (``FlopsProfiler`` :30 patches ``torch.nn.functional`` /
+tensor methods with MAC counters :893-952, per-module forward hooks aggregate :59-66, ``print_model_profile``,
+``get_model_profile`` :1204). Implementation here: a ``TorchDispatchMode`` counts FLOPs of the *executed aten ops*
+(matmul / addmm / bmm / conv / sdpa / elementwise), attributed to the innermost active module via forward hooks -
+no monkey patching, so custom autograd functions and fused ops are seen as what they execute.
+"""
+import time
+from collections import defaultdict
+
+import torch
+from torch.utils._python_dispatch import TorchDispatchMode
+
+aten = torch.ops.aten
+
+
+def _prod(x):
+    p = 1
+    for v in x:
+        p *= int(v)
+    return p
+
+
+def _mm_flops(a, b):
+    return 2 * _prod(a.shape) * b.shape[-1]
+
+
+def _flops_of(func, args, out):
+    name = getattr(func, "_overloadpacket", func)
+    try:
+        if name in (aten.mm, ):
+            return _mm_flops(args[0], args[1])
+        if name in (aten.addmm, ):
+            return _mm_flops(args[1], args[2]) + _prod(out.shape)
+        if name in (aten.bmm, aten.baddbmm):
+            a, b = (args[0], args[1]) if name == aten.bmm else (args[1], args[2])
+            return 2 * a.shape[0] * a.shape[1] * a.shape[2] * b.shape[2]
+        if name in (aten.linear, ):
+            return 2 * _prod(args[0].shape) * args[1].shape[0]
+        if name in (aten.matmul, ):
+            return 2 * _prod(out.shape) * args[0].shape[-1]
+        if name in (aten.convolution, aten._convolution):
+            x, w = args[0], args[1]
+            return 2 * _prod(out.shape) * _prod(w.shape[1:])
+        if name in (aten._scaled_dot_product_flash_attention, aten._scaled_dot_product_efficient_attention,
+                    aten._scaled_dot_product_cudnn_attention, aten.scaled_dot_product_attention,
+                    aten._scaled_dot_product_flash_attention_for_cpu):
+            q, k = args[0], args[1]
+            b, h, sq, d = q.shape
+            sk = k.shape[-2]
+            return 4 * b * h * sq * sk * d
+        if name in (aten.add, aten.sub, aten.mul, aten.div, aten.relu, aten.gelu, aten.silu, aten.tanh, aten.sigmoid,
+                    aten.exp, aten.pow, aten.rsqrt, aten.sqrt, aten.neg):
+            return _prod(out.shape) if torch.is_tensor(out) else 0
+        if name in (aten._softmax, aten._log_softmax, aten.native_layer_norm):
+            o = out[0] if isinstance(out, (tuple, list)) else out
+            return 5 * _prod(o.shape)
+    except Exception:
+        return 0
+    return 0
+
+
+class _Counter(TorchDispatchMode):
+
+    def __init__(self, profiler):
+        super().__init__()
+        self.p = profiler
+
+    def __torch_dispatch__(self, func, types, args=(), kwargs=None):
+        out = func(*args, **(kwargs or {}))
+        f = _flops_of(func, args, out)
+        if f:
+            self.p._add_flops(f)
+        return out
+
+
+class FlopsProfiler:
+
+    def __init__(self, model, ds_engine=None, recompute_fwd_factor=0.0):
+        self.model, self.ds_engine, self.recompute_fwd_factor = model, ds_engine, recompute_fwd_factor
+        self.started = False
+        self.func_patched = False
+        self._stack, self._hooks = [], []
+        self._mode = None
+        self.flops = defaultdict(int)
+        self.latency = defaultdict(float)
+        self._t0 = {}
+
+    def _add_flops(self, f):
+        for m in self._stack:
+            self.flops[id(m)] += f
+        self.flops["__total__"] += f
+
+    def start_profile(self, ignore_list=None):
+        self.reset_profile()
+        ignore = tuple(ignore_list or ())
+
+        def pre(m, inp):
+            self._stack.append(m)
+            if torch.cuda.is_available():
+                torch.cuda.synchronize()
+            self._t0[id(m)] = time.time()
+
+        def post(m, inp, out):
+            if torch.cuda.is_available():
+                torch.cuda.synchronize()
+            self.latency[id(m)] += time.time() - self._t0.get(id(m), time.time())
+            if self._stack and self._stack[-1] is m:
+                self._stack.pop()
+
+        for m in self.model.modules():
+            if ignore and isinstance(m, ignore):
+                continue
+            self._hooks.append(m.register_forward_pre_hook(pre))
+            self._hooks.append(m.register_forward_hook(post))
+        self._mode = _Counter(self)
+        self._mode.__enter__()
+        self.started = True
+
+    def stop_profile(self):
+        if self.started and self._mode is not None:
+            self._mode.__exit__(None, None, None)
+            self._mode = None
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
+
+    def reset_profile(self):
+        self.flops.clear()
+        self.latency.clear()
+        self._stack = []
+
+    def end_profile(self):
+        self.stop_profile()
+        self.started = False
+
+    def get_total_flops(self, as_string=False):
+        t = self.flops[id(self.model)] or self.flops["__total__"]
+        return number_to_string(t) + "FLOPs" if as_string else t
+
+    def get_total_macs(self, as_string=False):
+        t = self.get_total_flops() // 2
+        return number_to_string(t) + "MACs" if as_string else t
+
+    def get_total_duration(self, as_string=False):
+        d = self.latency[id(self.model)]
+        return duration_to_string(d) if as_string else d
+
+    def get_total_params(self, as_string=False):
+        n = sum(getattr(p, "ds_numel", p.numel()) for p in self.model.parameters())
+        return number_to_string(n) if as_string else n
+
+    def print_model_profile(self, profile_step=1, module_depth=-1, top_modules=1, detailed=True, output_file=None):
+        lines = []
+        total_f, total_t, total_p = self.get_total_flops(), self.get_total_duration(), self.get_total_params()
+        lines.append("\n-------------------------- DeepSpeed-B200 Flops Profiler --------------------------")
+        lines.append(f"Profile Summary at step {profile_step}:")
+        lines.append(f"params:                         {number_to_string(total_p)}")
+        lines.append(f"fwd MACs:                       {number_to_string(total_f // 2)}MACs")
+        lines.append(f"fwd flops:                      {number_to_string(total_f)}FLOPs")
+        lines.append(f"fwd latency:                    {duration_to_string(total_t)}")
+        if total_t > 0:
+            lines.append(f"fwd FLOPS:                      {number_to_string(total_f / total_t)}FLOPS")
+        if detailed:
+            lines.append("\n------------------------------ Detailed Profile per module ------------------------------")
+
+            def walk(m, name, depth):
+                if module_depth >= 0 and depth > module_depth:
+                    return
+                f, t = self.flops[id(m)], self.latency[id(m)]
+                p = sum(getattr(q, "ds_numel", q.numel()) for q in m.parameters())
+                pct = 100.0 * f / total_f if total_f else 0.0
+                lines.append(f"{'  ' * depth}{name or type(m).__name__} ({type(m).__name__}): {number_to_string(p)} params, "
+                             f"{number_to_string(f)}FLOPs ({pct:.1f}%), {duration_to_string(t)}")
+                for cn, c in m.named_children():
+                    walk(c, cn, depth + 1)
+
+            walk(self.model, "", 0)
+        text = "\n".join(lines)
+        if output_file:
+            with open(output_file, "w") as f:
+                f.write(text)
+        else:
+            print(text)
+        return text
+
+
+def number_to_string(num, units=None, precision=2):
+    for unit, scale in (("T", 1e12), ("G", 1e9), ("M", 1e6), ("K", 1e3)):
+        if units == unit or (units is None and abs(num) >= scale):
+            return f"{num / scale:.{precision}f} {unit}"
+    return f"{num:.{precision}f} " if isinstance(num, float) else f"{num} "
+
+
+def duration_to_string(d, units=None, precision=2):
+    if d >= 1:
+        return f"{d:.{precision}f} s"
+    if d >= 1e-3:
+        return f"{d * 1e3:.{precision}f} ms"
+    return f"{d * 1e6:.{precision}f} us"
+
+
+def get_model_profile(model, input_shape=None, args=(), kwargs=None, print_profile=True, detailed=True,
+                      module_depth=-1, top_modules=1, warm_up=1, as_string=True, output_file=None, ignore_modules=None,
+                      mode="forward"):
+    """Standalone profile of one forward pass. Returns (flops, macs, params)."""
+    kwargs = kwargs or {}
+    if input_shape is not None:
+        dev = next(model.parameters()).device
+        args = (torch.ones(()).new_empty((*input_shape, ), dtype=next(model.parameters()).dtype, device=dev), )
+    prof = FlopsProfiler(model)
+    model.eval()
+    with torch.no_grad():
+        for _ in range(warm_up):
+            model(*args, **kwargs)
+        prof.start_profile(ignore_list=ignore_modules)
+        model(*args, **kwargs)
+        prof.stop_profile()
+    flops, macs, params = prof.get_total_flops(), prof.get_total_macs(), prof.get_total_params()
+    if print_profile:
+        prof.print_model_profile(module_depth=module_depth, top_modules=top_modules, detailed=detailed,
+                                 output_file=output_file)
+    prof.end_profile()
+    if as_string:
+        return number_to_string(flops) + "FLOPs", number_to_string(macs) + "MACs", number_to_string(params)
+    return flops, macs, params
