@@ -1,0 +1,156 @@
+/* dsb200.h - C ABI of the deepspeed_b200 native libraries.
+ *
+ *   libdsb200.so      sm_100a CUDA kernels (csrc/ *.cu), built with nvcc -gencode arch=compute_100a,code=sm_100a
+ *   libdsb200_cpu.so  host runtime (csrc/cpu/ *.cpp): AVX-512/OpenMP optimizers, asynchronous file I/O
+ *
+ * Conventions
+ *   - every launcher takes raw device pointers, sizes and the cudaStream_t to launch on; nothing is synchronised;
+ *   - return value: 0 on success, non-zero on failure; dsb200_last_error() returns the reason (thread local);
+ *   - dtype codes: 0 = fp32, 1 = fp16, 2 = bf16;
+ *   - unless said otherwise a launcher allocates nothing: scratch buffers are passed in by the caller.
+ * Each declaration cites the reference (deepspeedai/DeepSpeed) code whose behaviour it covers.
+ */
+#ifndef DSB200_H
+#define DSB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef __DRIVER_TYPES_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+/* ---------------------------------------------------------------- runtime ------------------------------- */
+const char* dsb200_last_error(void);
+int dsb200_version(void);
+
+/* ---------------------------------------------------------------- reductions / optimizers ---------------- */
+/* fp32 sum of squares of x[n]. scratch: >= 1025 floats, word [1024] (ticket) zero before the first use; it resets
+ * itself. Deterministic two-stage reduction in one launch. Reference: get_global_norm_of_tensors
+ * (runtime/utils.py:878), multi_tensor_l2norm. */
+int dsb200_sumsq(const void* x, int64_t n, int dt, float* scratch, float* out, cudaStream_t stream);
+
+/* One launch updates every chunk of a device-resident chunk table {p,g,m,v,lp,n,group,dtypes} (48 bytes/entry).
+ * kind: 0 Adam/AdamW, 1 Lion, 2 Adagrad, 3 SGD-momentum. hyper_host: n_groups x 8 floats
+ * (lr, beta1, beta2, eps, wd, bias_corr1, bias_corr2, mode). Fuses grad unscale/clip (grad_scale), the fp32 update and
+ * the low-precision weight write-back. Reference: csrc/adam/multi_tensor_adam.cu:33-127,
+ * csrc/lion/multi_tensor_lion.cu, multi_tensor_apply.cuh:38-125. */
+int dsb200_multi_tensor_optim(int kind, const void* table, int n_chunks, const float* hyper_host, int n_groups,
+                              float grad_scale, cudaStream_t stream);
+
+/* LAMB on one tensor: phase 1 update + per-block norms (partials: >= 4096 floats), phase 2 trust ratio + apply.
+ * coeff_out[0..2] = |w|, |update|, clamped ratio. Reference: csrc/lamb/fused_lamb_cuda_kernel.cu:357-453. */
+int dsb200_lamb_step(float* p, float* g, float* m, float* v, void* lp, int64_t n, int lpdt, float* partials,
+                     float* coeff_out, float lr, float b1, float b2, float eps, float wd, float bc1, float bc2,
+                     int eps_mode, float max_coeff, float min_coeff, cudaStream_t stream);
+
+/* ---------------------------------------------------------------- normalisation -------------------------- */
+/* y = rmsnorm(x [+ residual]) * gamma; res_out (optional) receives x + residual; stats[rows] = rstd.
+ * Reference: csrc/transformer/inference/csrc/rms_norm.cu:22,93 (forward only in the reference). */
+int dsb200_rmsnorm_fwd(const void* x, const void* residual, const void* gamma, void* y, void* res_out, float* stats,
+                       int rows, int cols, float eps, int dt, cudaStream_t stream);
+/* scratch: fp32 [min(rows, 592) * cols] partial dgamma rows. dres (optional) is added to dx. */
+int dsb200_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const float* stats, const void* dres,
+                       void* dx, void* dgamma, float* scratch, int rows, int cols, int accumulate, int dt,
+                       cudaStream_t stream);
+/* LayerNorm; stats[rows*2] = (mean, rstd). Reference: csrc/transformer/normalize_kernels.cu. */
+int dsb200_layernorm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+                         void* res_out, float* stats, int rows, int cols, float eps, int dt, cudaStream_t stream);
+/* scratch: fp32 [2 * min(rows, 592) * cols]. */
+int dsb200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* stats, const void* dres,
+                         void* dx, void* dgamma, void* dbeta, float* scratch, int rows, int cols, int accumulate,
+                         int dt, cudaStream_t stream);
+
+/* ---------------------------------------------------------------- elementwise ---------------------------- */
+/* In-place half-rotation RoPE on x[tokens, heads, dim]; backward != 0 applies the transpose rotation.
+ * Reference: csrc/transformer/inference/csrc/apply_rotary_pos_emb.cu:23-169. */
+int dsb200_rope(void* x, const float* cos_tab, const float* sin_tab, const int* pos, int tokens, int heads, int dim,
+                int64_t token_stride, int seq_len, int backward, int dt, cudaStream_t stream);
+/* y = silu(gate) * up (inputs may be halves of one fused tensor: in_stride). Reference: swiglu_triton.py:36-70. */
+int dsb200_swiglu_fwd(const void* gate, const void* up, void* y, int64_t rows, int inter, int64_t in_stride, int dt,
+                      cudaStream_t stream);
+int dsb200_swiglu_bwd(const void* dy, const void* gate, const void* up, void* dgate, void* dup, int64_t rows, int inter,
+                      int64_t in_stride, int dt, cudaStream_t stream);
+/* Row-wise softmax cross entropy; write_grad != 0 overwrites logits with (softmax - onehot) * grad_scale.
+ * Reference: TiledFusedLogitsLoss (runtime/sequence_parallel/ulysses_sp.py:1065). */
+int dsb200_ce_fwd(void* logits, const int64_t* target, float* loss, float* lse, int rows, int vocab, int64_t row_stride,
+                  int ignore_index, int write_grad, float grad_scale, int dt, cudaStream_t stream);
+
+/* ---------------------------------------------------------------- tcgen05 GEMM --------------------------- */
+/* C[M,N] = A[M,K] * B[N,K]^T, bf16 in/out, fp32 accumulation in TMEM (TMA + tcgen05.mma, persistent).
+ * force_bn in {0 (auto), 128, 192, 256}. Reference: cuBLAS calls (csrc/transformer/cublas_wrappers.cu). */
+int dsb200_gemm_bf16_nt(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb,
+                        int64_t ldc, int max_ctas, int force_bn, cudaStream_t stream);
+
+/* ---------------------------------------------------------------- quantization --------------------------- */
+/* Block-scaled FP8 (fmt 0 = e4m3, 1 = e5m2), one fp32 scale per `block` (multiple of 256) elements.
+ * Reference: csrc/quantization/quantize.cu:23 (int8 groups) - this is the native ZeRO++ wire format here. */
+int dsb200_fp8_block_quant(const void* x, int dt, void* q, float* scales, int64_t n, int block, int fmt,
+                           cudaStream_t stream);
+int dsb200_fp8_block_dequant(const void* q, const float* scales, void* y, int dt, int64_t n, int block, int fmt,
+                             cudaStream_t stream);
+/* Symmetric int8/int4 group quantization; swz_nodes*swz_devs > 0 re-orders partitions [node,dev]->[dev,node].
+ * Reference: csrc/quantization/quantize.cu, swizzled_quantize.cu:22-83, dequantize.cu:12. */
+int dsb200_int_group_quant(const void* x, int dt, void* q, float* scales, int64_t n, int group, int bits, int swz_nodes,
+                           int swz_devs, cudaStream_t stream);
+int dsb200_int_group_dequant(const void* q, const float* scales, void* y, int dt, int64_t n, int group, int bits,
+                             cudaStream_t stream);
+/* out = post * sum_c dequant(q[c]) over nchunks received chunks. Reference: csrc/quantization/quant_reduce.cu:21-133. */
+int dsb200_dequant_reduce(const void* q, const float* scales, void* out, int dt, int64_t chunk_elems, int nchunks,
+                          int group, int bits, float post, cudaStream_t stream);
+/* Group-scaled minifloat rounding (exp_bits/man_bits), RNE or stochastic. Reference: csrc/fp_quantizer. */
+int dsb200_minifloat_quant(const void* x, void* y, float* scales, int dt, int64_t n, int group, int exp_bits,
+                           int man_bits, float fmt_max, int stochastic, unsigned int seed, cudaStream_t stream);
+
+/* ---------------------------------------------------------------- NVLink collectives --------------------- */
+/* peer_* : host arrays of 16 device addresses (one per rank, unused = 0) of symmetric buffers / flag buffers.
+ * Epoch flags: channel ch_ready is signalled at kernel start, ch_done by the last CTA. See csrc/symm.cu.
+ * Reference: coalesced_collectives.py:158-218, partition_parameters.py:1301-1343, sequence/layer.py:264,
+ * csrc/compile/z3.cpp:95-113 (barrier + per-peer copy). */
+int dsb200_symm_reduce_scatter(const uint64_t* peer_bufs, const uint64_t* peer_flags, uint64_t mc_ptr, int rank,
+                               int world, int64_t shard_numel, int in_dt, void* out, int out_dt, int accumulate,
+                               float scale, float* sumsq_partials, unsigned int* ticket, int ch_ready, int ch_done,
+                               unsigned int epoch, int ctas, cudaStream_t stream);
+int dsb200_symm_all_gather(const uint64_t* peer_shards, const uint64_t* peer_flags, uint64_t mc_full, int rank,
+                           int world, int64_t shard_bytes, const void* my_shard, void* full, unsigned int* ticket,
+                           int ch_ready, int ch_done, unsigned int epoch, unsigned int done_epoch, int ctas,
+                           cudaStream_t stream);
+int dsb200_symm_all_to_all(const uint64_t* peer_ins, const uint64_t* peer_flags, int rank, int world, int64_t rows,
+                           int64_t row_bytes, int interleave, void* out, unsigned int* ticket, int ch_ready,
+                           int ch_done, unsigned int epoch, int ctas, cudaStream_t stream);
+int dsb200_symm_wait(const uint64_t* peer_flags, int rank, int world, int channel, unsigned int epoch,
+                     cudaStream_t stream);
+int dsb200_symm_signal(const uint64_t* peer_flags, int rank, int world, int channel, unsigned int epoch,
+                       cudaStream_t stream);
+
+/* ---------------------------------------------------------------- host library (libdsb200_cpu.so) -------- */
+/* Reference: csrc/adam/cpu_adam_impl.cpp:35-357, csrc/adagrad/cpu_adagrad.cpp, csrc/lion/cpu_lion_impl.cpp. */
+int dsb200_cpu_num_threads(void);
+void dsb200_cpu_adam(float* p, const void* g, int g_dt, float* m, float* v, void* lp, int lp_dt, int64_t n, float lr,
+                     float beta1, float beta2, float eps, float wd, int step, int bias_correction, int adamw,
+                     float grad_scale);
+void dsb200_cpu_adam_rollback(float* p, const void* g, int g_dt, float* m, float* v, int64_t n, float lr, float beta1,
+                              float beta2, float eps, float wd, int step, int bias_correction, int adamw,
+                              float grad_scale);
+void dsb200_cpu_adagrad(float* p, const void* g, int g_dt, float* v, void* lp, int lp_dt, int64_t n, float lr,
+                        float eps, float wd, float grad_scale);
+void dsb200_cpu_lion(float* p, const void* g, int g_dt, float* m, void* lp, int lp_dt, int64_t n, float lr,
+                     float beta1, float beta2, float wd, float grad_scale);
+void dsb200_cpu_cast(const float* src, void* dst, int dst_dt, int64_t n);
+double dsb200_cpu_sumsq(const float* x, int64_t n);
+/* Reference: csrc/aio/py_lib/py_ds_aio.cpp:17-158 (aio_handle), csrc/aio/common/deepspeed_aio_common.cpp. */
+void* dsb200_aio_create(int64_t block_size, int queue_depth, int threads, int use_direct);
+void dsb200_aio_destroy(void* h);
+int dsb200_aio_pread(void* h, void* buf, int64_t nbytes, const char* path, int64_t offset, int async);
+int dsb200_aio_pwrite(void* h, const void* buf, int64_t nbytes, const char* path, int64_t offset, int async);
+int64_t dsb200_aio_wait(void* h);
+void* dsb200_aligned_alloc(int64_t nbytes, int64_t alignment);
+void dsb200_aligned_free(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DSB200_H */
