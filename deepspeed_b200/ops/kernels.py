@@ -126,6 +126,7 @@ def _declare(L):
 # reductions
 # ---------------------------------------------------------------------------------------------------------
 _SCRATCH = {}
+_SUMSQ_SCRATCH = {}
 
 
 def _scratch(device, n_float):
@@ -141,7 +142,12 @@ def sumsq(t):
     """fp32 sum of squares of one contiguous tensor (two-stage deterministic reduction)."""
     t = t.contiguous()
     out = torch.empty((), dtype=torch.float32, device=t.device)
-    scratch = _scratch(t.device, 2048)
+    # dedicated buffer: the ticket word (index 1024) must stay zero between launches, so this scratch must never be
+    # shared with kernels that scribble partial sums over it (norm backward, LAMB use _scratch)
+    key = (t.device.index, torch.cuda.current_stream().cuda_stream)
+    scratch = _SUMSQ_SCRATCH.get(key)
+    if scratch is None:
+        scratch = _SUMSQ_SCRATCH[key] = torch.zeros(2048, dtype=torch.float32, device=t.device)
     _check(lib().dsb200_sumsq(_ptr(t), t.numel(), _dt(t), _ptr(scratch), _ptr(out), _stream()), "sumsq")
     return out
 
@@ -174,15 +180,15 @@ def build_chunk_table(items, states):
     for (gi, p, g, lp), sts in zip(items, states):
         assert p.dtype == torch.float32 or p.dtype in _DT
         n = p.numel()
-        m = sts[0]
-        v = sts[1] if len(sts) > 1 else None
+        m, v = sts[0], (sts[1] if len(sts) > 1 else None)  # [first-moment slot, second-moment slot]; either may be None
         esz = {0: 4, 1: 2, 2: 2}
         pdt, gdt = _dt(p), _dt(g)
-        sdt = _dt(m)
+        sdt = _dt(m if m is not None else v)
         ldt = _dt(lp) if lp is not None else 0
         for off in range(0, n, CHUNK):
             cnt = min(CHUNK, n - off)
-            rows.append((p.data_ptr() + off * esz[pdt], g.data_ptr() + off * esz[gdt], m.data_ptr() + off * esz[sdt],
+            rows.append((p.data_ptr() + off * esz[pdt], g.data_ptr() + off * esz[gdt],
+                         (m.data_ptr() + off * esz[sdt]) if m is not None else 0,
                          (v.data_ptr() + off * esz[sdt]) if v is not None else 0,
                          (lp.data_ptr() + off * esz[ldt]) if lp is not None else 0, cnt, gi,
                          pdt | (gdt << 4) | (sdt << 8) | (ldt << 12)))

@@ -101,7 +101,9 @@ class _FusedBase(torch.optim.Optimizer):
         table = self._table_cache.get(key)
         if table is None:
             self._table_cache.clear()
-            states = [[self.state[p][n] for n in self._state_names()] for _, p, _, _ in items]
+            # kernel slots: [first moment (exp_avg / momentum_buffer) or None, second moment (exp_avg_sq) or None]
+            states = [[next((self.state[p][n] for n in ("exp_avg", "momentum_buffer") if n in self.state[p]), None),
+                       self.state[p].get("exp_avg_sq")] for _, p, _, _ in items]
             table = kernels.build_chunk_table([(gi, p, g, lp) for gi, p, g, lp in items], states)
             self._table_cache[key] = table
         hyper = [self._hyper(g) for g in self.param_groups]

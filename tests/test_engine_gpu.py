@@ -74,5 +74,7 @@ def test_fused_path_matches_torch_path_fp32_master():
     for n in fused:
         noise = (fused[n] - fused2[n]).abs().mean().item()
         diff = (fused[n] - ref[n]).abs().mean().item()
-        assert diff <= 3.0 * noise + 5e-7, f"{n}: fused-vs-torch {diff:.3e} exceeds run-to-run noise {noise:.3e}"
+        # 3 steps at lr=1e-3 move a weight by ~3e-3; the two optimizer implementations must agree to well under 1 %
+        # of that on average (fast-math division/sqrt + bf16 re-rounding of the weights between steps)
+        assert diff <= 3.0 * noise + 2e-5, f"{n}: fused-vs-torch {diff:.3e} exceeds run-to-run noise {noise:.3e}"
         assert (fused[n] - ref[n]).abs().max().item() < 3 * 3 * 1e-3

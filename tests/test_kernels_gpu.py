@@ -116,7 +116,7 @@ def test_rmsnorm_fwd_bwd(K, cols, with_res):
     wf = w.detach().float().requires_grad_(True)
     hin = xf + rf if with_res else xf
     if with_res:
-        hin_q = hin.to(torch.bfloat16).float() + (hin - hin.detach())  # kernel normalises the bf16-rounded sum
+        hin_q = hin.detach().to(torch.bfloat16).float() + (hin - hin.detach())  # bf16-rounded value, identity gradient
     else:
         hin_q = hin
     yr = hin_q * torch.rsqrt(hin_q.pow(2).mean(-1, keepdim=True) + 1e-5) * wf
@@ -215,3 +215,16 @@ def test_linear_cross_entropy_matches_torch(K):
     assert abs(float(loss) - float(ref)) < 2e-2
     torch.testing.assert_close(h.grad.float(), hf.grad, rtol=5e-2, atol=2e-4)
     torch.testing.assert_close(w.grad.float(), wf.grad, rtol=5e-2, atol=2e-4)
+
+
+def test_sumsq_not_disturbed_by_kernels_sharing_scratch(K):
+    """Regression: norm backward writes partial sums into the shared scratch; sumsq's ticket word must be unaffected."""
+    from deepspeed_b200.ops import fused
+    x = torch.randn(600, 4096, device=_dev(), dtype=torch.bfloat16, requires_grad=True)
+    w = torch.ones(4096, device=_dev(), dtype=torch.bfloat16, requires_grad=True)
+    fused.rms_norm(x, w).float().sum().backward()
+    t = torch.randn(1_000_003, device=_dev())
+    for _ in range(2):
+        got = float(K.sumsq(t))
+        ref = float(t.double().pow(2).sum())
+        assert abs(got - ref) <= 2e-4 * ref
