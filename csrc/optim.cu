@@ -298,3 +298,106 @@ int dsb200_lamb_step(float* p, float* g, float* m, float* v, void* lp, int64_t n
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------
+// dsb200_sumsq_noalloc: the sum-of-squares reduction for callers that cannot hand us scratch memory.
+//
+// Who needs this: a host program that has given all of the device memory to its own pool (a serving process, a
+// framework allocator that reserved the whole HBM) cannot call cudaMalloc for our 4 KB of partial sums without
+// failing or forcing that pool to give memory back; a latency-critical loop must not call cudaMalloc/cudaFree
+// because both synchronise the whole device; and a plain C caller may simply have no allocator to ask. For them
+// the partial sums live in the library image itself: a file-scope __device__ array that every GPU which loads the
+// library carries until the process exits (SUMSQ_STATIC_BYTES below, about 4.3 KB per GPU).
+//
+// Rules that follow from sharing one array:
+//   * The name `g_sumsq_static_scratch` is only a host-side handle in host code. The device address is obtained
+//     with cudaGetSymbolAddress, once per device, with that device current; this happens inside the FIRST call of
+//     dsb200_sumsq_noalloc on each device. Make that first call before starting any stream capture.
+//   * All calls on one GPU use the same array and it keeps whatever the previous call left. The ticket word has
+//     to start at zero, so every call clears it (cudaMemsetAsync on the caller's stream) before the kernel.
+//   * Two calls that overlap on the same GPU (different streams, different host threads) race on the array and
+//     produce garbage. Serialise them: one stream, or an event between them.
+//   * Inputs larger than DSB200_SUMSQ_NOALLOC_MAX_ELEMS are refused: beyond that the per-thread fp32
+//     accumulation chains get long enough that the result no longer meets the library's accuracy bound.
+// Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
+// ---------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+#ifndef DSB200_SUMSQ_NOALLOC_MAX_ELEMS
+#define DSB200_SUMSQ_NOALLOC_MAX_ELEMS (1LL << 34)  // keep in sync with include/dsb200.h
+#endif
+
+namespace {
+constexpr int SUMSQ_STATIC_FLOATS = SUMSQ_MAX_BLOCKS + 64;  // partial sums + ticket word (+ padding)
+constexpr int SUMSQ_STATIC_BYTES = SUMSQ_STATIC_FLOATS * 4;
+constexpr int SUMSQ_STATIC_MAX_DEVICES = 64;
+static_assert(SUMSQ_STATIC_BYTES <= 8192, "the per-GPU static scratch is meant to stay a few KB");
+}  // namespace
+
+static __device__ __align__(256) float g_sumsq_static_scratch[SUMSQ_STATIC_FLOATS];
+
+namespace {
+float* g_sumsq_static_ptr[SUMSQ_STATIC_MAX_DEVICES] = {nullptr};
+std::mutex g_sumsq_static_mu;
+
+// Device address of the static scratch on the current device (looked up once per device).
+int sumsq_static_address(float** out)
+{
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        dsb200_set_error(cudaGetErrorString(e));
+        return (int)e;
+    }
+    if (dev < 0 || dev >= SUMSQ_STATIC_MAX_DEVICES) {
+        dsb200_set_error("sumsq_noalloc: device ordinal out of range (max 64 devices)");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(g_sumsq_static_mu);
+    if (g_sumsq_static_ptr[dev] == nullptr) {
+        float* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_sumsq_static_scratch);
+        if (e != cudaSuccess || ptr == nullptr) {
+            dsb200_set_error(e != cudaSuccess ? cudaGetErrorString(e) : "sumsq_noalloc: null symbol address");
+            return e != cudaSuccess ? (int)e : -1;
+        }
+        g_sumsq_static_ptr[dev] = ptr;
+    }
+    *out = g_sumsq_static_ptr[dev];
+    return 0;
+}
+}  // namespace
+
+extern "C" int dsb200_sumsq_noalloc(const void* x, int64_t n, int dt, float* out, cudaStream_t stream)
+{
+    if (n > DSB200_SUMSQ_NOALLOC_MAX_ELEMS) {
+        dsb200_set_error("sumsq_noalloc: n exceeds DSB200_SUMSQ_NOALLOC_MAX_ELEMS (2^34 elements); split the input");
+        return -2;
+    }
+    if (dt != DSB_DT_F32 && dt != DSB_DT_F16 && dt != DSB_DT_BF16) {
+        dsb200_set_error("sumsq_noalloc: dtype must be 0 (fp32), 1 (fp16) or 2 (bf16)");
+        return -3;
+    }
+    if (n <= 0) {
+        DSB_CHECK(cudaMemsetAsync(out, 0, sizeof(float), stream));
+        return 0;
+    }
+    float* scratch = nullptr;
+    int rc = sumsq_static_address(&scratch);
+    if (rc != 0) return rc;
+    // the array still holds the previous call's data: the ticket must be zero when the kernel starts
+    DSB_CHECK(cudaMemsetAsync(scratch + SUMSQ_MAX_BLOCKS, 0, sizeof(unsigned int), stream));
+    int64_t per_block = 512LL * 16;
+    int blocks = (int)((n + per_block - 1) / per_block);
+    if (blocks > DSB_NUM_SMS * 4) blocks = DSB_NUM_SMS * 4;
+    if (blocks > SUMSQ_MAX_BLOCKS) blocks = SUMSQ_MAX_BLOCKS;
+    if (blocks < 1) blocks = 1;
+    if (dt == DSB_DT_F32)
+        sumsq_kernel<float><<<blocks, 512, 0, stream>>>((const float*)x, n, scratch, out);
+    else if (dt == DSB_DT_BF16)
+        sumsq_kernel<__nv_bfloat16><<<blocks, 512, 0, stream>>>((const __nv_bfloat16*)x, n, scratch, out);
+    else
+        sumsq_kernel<__half><<<blocks, 512, 0, stream>>>((const __half*)x, n, scratch, out);
+    DSB_CHECK_LAUNCH("sumsq_noalloc");
+    return 0;
+}

@@ -33,6 +33,19 @@ int dsb200_version(void);
  * (runtime/utils.py:878), multi_tensor_l2norm. */
 int dsb200_sumsq(const void* x, int64_t n, int dt, float* scratch, float* out, cudaStream_t stream);
 
+/* Same reduction for callers that cannot supply scratch: a process whose own pool already holds all device memory
+ * (a raw cudaMalloc would fail or shrink that pool), a latency-critical loop that must avoid the device-wide
+ * synchronisation of cudaMalloc/cudaFree, or a C program with no allocator to pass on. The partial sums live in a
+ * __device__ array inside the library (about 4.3 KB on every GPU that loads it, kept until the process exits); the
+ * call allocates nothing. No counterpart in the reference.
+ *   - Limit: n <= DSB200_SUMSQ_NOALLOC_MAX_ELEMS (2^34 elements); larger inputs are refused with an error.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress, that device
+ *     current); make that first call before starting any stream capture.
+ *   - All calls on a GPU share the array, which keeps the previous call's contents; each call clears the one word
+ *     that must start at zero. Calls that overlap on the same GPU (other streams or threads) race: serialise them. */
+#define DSB200_SUMSQ_NOALLOC_MAX_ELEMS (1LL << 34)
+int dsb200_sumsq_noalloc(const void* x, int64_t n, int dt, float* out, cudaStream_t stream);
+
 /* One launch updates every chunk of a device-resident chunk table {p,g,m,v,lp,n,group,dtypes} (48 bytes/entry).
  * kind: 0 Adam/AdamW, 1 Lion, 2 Adagrad, 3 SGD-momentum. hyper_host: n_groups x 8 floats
  * (lr, beta1, beta2, eps, wd, bias_corr1, bias_corr2, mode). Fuses grad unscale/clip (grad_scale), the fp32 update and
