@@ -160,6 +160,18 @@ def _zero_optimizer_state(engine):
     return sd, lay
 
 
+def _data_sampler_state(engine):
+    sampler = engine.get_data_sampler() if hasattr(engine, "get_data_sampler") else None
+    if sampler is not None and hasattr(sampler, "state_dict") and engine.curriculum_learning_enabled():
+        return sampler.state_dict()
+    return None
+
+
+def _random_ltd_state(engine):
+    sch = getattr(engine, "random_ltd_scheduler", None)
+    return sch.state_dict() if sch is not None else None
+
+
 def save_engine_checkpoint(engine, save_dir, tag=None, client_state=None, save_latest=True,
                            exclude_frozen_parameters=False):
     if tag is None:
@@ -202,7 +214,8 @@ def save_engine_checkpoint(engine, save_dir, tag=None, client_state=None, save_l
                      frozen_param_shapes=frozen_shapes or None, frozen_param_fragments=frozen_frags or None,
                      shared_params=_shared_params(engine.module),
                      lr_scheduler=engine.lr_scheduler.state_dict() if engine.lr_scheduler is not None else None,
-                     data_sampler=None, random_ltd=None, sparse_tensor_module_names=set(),
+                     data_sampler=_data_sampler_state(engine), random_ltd=_random_ltd_state(engine),
+                     sparse_tensor_module_names=set(getattr(engine, "sparse_tensor_module_names", ())),
                      skipped_steps=engine.skipped_steps, global_steps=engine.global_steps,
                      global_samples=engine.global_samples, dp_world_size=engine.seq_dp_world_size,
                      mp_world_size=engine.mp_world_size,
@@ -301,6 +314,11 @@ def load_engine_checkpoint(engine, load_dir, tag=None, load_module_strict=True, 
         engine.skipped_steps = ckpt.get("skipped_steps", 0)
         if load_lr_scheduler_states and engine.lr_scheduler is not None and ckpt.get("lr_scheduler") is not None:
             engine.lr_scheduler.load_state_dict(ckpt["lr_scheduler"])
+        if getattr(engine, "random_ltd_scheduler", None) is not None and ckpt.get("random_ltd") is not None:
+            engine.random_ltd_scheduler.load_state_dict(ckpt["random_ltd"])
+        sampler = engine.get_data_sampler() if hasattr(engine, "get_data_sampler") else None
+        if sampler is not None and hasattr(sampler, "load_state_dict") and ckpt.get("data_sampler") is not None:
+            sampler.load_state_dict(ckpt["data_sampler"])
 
     if engine.optimizer is not None:
         if have_zero_files:

@@ -120,6 +120,9 @@ def _declare(L):
     sig("dsb200_swiglu_fwd", P, P, P, L64, I, L64, I, P)
     sig("dsb200_swiglu_bwd", P, P, P, P, P, L64, I, L64, I, P)
     sig("dsb200_ce_fwd", P, P, P, P, I, I, L64, I, I, F, I, P)
+    sig("dsb200_move_rows", P, P, P, I, L64, L64, L64, L64, L64, I, P)
+    sig("dsb200_scatter_add_rows", P, P, P, I, P, L64, I, L64, L64, L64, I, I, P)
+    sig("dsb200_sort_rows_i32", P, L64, I, P)
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -319,6 +322,58 @@ def cross_entropy_fwd(logits, target, ignore_index):
     _check(lib().dsb200_ce_fwd(_ptr(logits), _ptr(target), _ptr(loss), _ptr(lse), rows, vocab, logits.stride(0),
                                int(ignore_index), 0, 1.0, _dt(logits), _stream()), "ce_fwd")
     return loss, lse
+
+
+# ---------------------------------------------------------------------------------------------------------
+# row gather / scatter by index (csrc/token_ops.cu)
+# ---------------------------------------------------------------------------------------------------------
+def _idx_bytes(idx):
+    assert idx.dtype in (torch.int32, torch.int64) and idx.is_contiguous()
+    return idx.element_size()
+
+
+def gather_rows(src2, idx, out=None):
+    """``out[i] = src2[idx[i]]`` for a 2-D ``src2`` with contiguous rows; out-of-range indices leave ``out[i]``
+    untouched (pass a zeroed ``out`` for MoE capacity drops)."""
+    assert src2.dim() == 2 and src2.stride(1) == 1
+    n = idx.numel()
+    if out is None:
+        out = torch.empty((n, src2.shape[1]), dtype=src2.dtype, device=src2.device)
+    esz = src2.element_size()
+    _check(lib().dsb200_move_rows(_ptr(src2), _ptr(out), _ptr(idx), _idx_bytes(idx), n, src2.shape[1] * esz,
+                                  src2.stride(0) * esz, out.stride(0) * esz, src2.shape[0], 0, _stream()),
+           "move_rows")
+    return out
+
+
+def scatter_rows_(dst2, idx, src2):
+    """``dst2[idx[i]] = src2[i]`` (indices unique); returns ``dst2``."""
+    assert dst2.dim() == 2 and dst2.stride(1) == 1 and src2.stride(1) == 1 and dst2.dtype == src2.dtype
+    esz = src2.element_size()
+    _check(lib().dsb200_move_rows(_ptr(src2), _ptr(dst2), _ptr(idx), _idx_bytes(idx), idx.numel(),
+                                  src2.shape[1] * esz, src2.stride(0) * esz, dst2.stride(0) * esz, dst2.shape[0], 1,
+                                  _stream()), "move_rows")
+    return dst2
+
+
+def scatter_add_rows_(dst2, idx, src2, weights=None, unique=False):
+    """``dst2[idx[i]] += weights[i] * src2[i]``; atomics unless the indices are known to be unique."""
+    assert dst2.dtype == src2.dtype and dst2.stride(1) == 1 and src2.stride(1) == 1
+    w = _ptr(weights) if weights is not None else c_void_p(0)
+    if weights is not None:
+        assert weights.dtype == torch.float32 and weights.is_contiguous()
+    _check(lib().dsb200_scatter_add_rows(_ptr(src2), _ptr(dst2), _ptr(idx), _idx_bytes(idx), w, idx.numel(),
+                                         src2.shape[1], src2.stride(0), dst2.stride(0), dst2.shape[0],
+                                         0 if unique else 1, _dt(src2), _stream()), "scatter_add_rows")
+    return dst2
+
+
+def sort_rows_i32_(idx2):
+    """Ascending in-place sort of every row of an int32 [rows, n<=8192] tensor."""
+    assert idx2.dtype == torch.int32 and idx2.is_contiguous()
+    n = idx2.shape[-1]
+    _check(lib().dsb200_sort_rows_i32(_ptr(idx2), idx2.numel() // n, n, _stream()), "sort_rows_i32")
+    return idx2
 
 
 # ---------------------------------------------------------------------------------------------------------

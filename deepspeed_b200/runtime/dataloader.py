@@ -33,7 +33,7 @@ class DeepSpeedDataLoader:
         self.batch_size = batch_size
         self.curriculum_learning_enabled = bool(self.deepspeed_dataloader_config.get("curriculum_learning_enabled"))
         if self.curriculum_learning_enabled:
-            from .data_pipeline.data_sampler import DeepSpeedDataSampler
+            from .data_pipeline.data_sampling.data_sampler import DeepSpeedDataSampler
             data_sampler = DeepSpeedDataSampler(self.deepspeed_dataloader_config["data_efficiency"], len(dataset),
                                                 self.batch_size, data_parallel_rank, data_parallel_world_size,
                                                 self.deepspeed_dataloader_config.get("data_parallel_group"),

@@ -360,6 +360,69 @@ class DeepSpeedEngine(Module):
         if cfg.compression_config:
             from ..compression.scheduler import compression_scheduler
             self.compression_scheduler = compression_scheduler(self.module, cfg.compression_config)
+        self.random_ltd_scheduler = None
+        if self.random_ltd_enabled():
+            from .data_pipeline.data_routing.scheduler import RandomLTDScheduler
+            rc = self.random_ltd_config()
+            rc["global_batch_size"] = self.train_batch_size()
+            rc["micro_batch_size"] = self.train_micro_batch_size_per_gpu()
+            self.random_ltd_scheduler = RandomLTDScheduler(rc)
+
+    # ------------------------------------------------------------------ data efficiency --------
+    def data_efficiency_config(self):
+        if not hasattr(self, "_data_efficiency_full"):
+            from .data_pipeline.config import get_data_efficiency_config
+            self._data_efficiency_full = get_data_efficiency_config(
+                {"data_efficiency": self._config.data_efficiency_config})
+        return self._data_efficiency_full
+
+    def data_sampling_enabled(self):
+        return self.data_efficiency_enabled() and self.data_efficiency_config()["data_sampling"]["enabled"]
+
+    def data_sampling_config(self):
+        return self.data_efficiency_config()["data_sampling"]
+
+    def curriculum_learning_enabled(self):
+        return self.data_sampling_enabled() and self.data_sampling_config()["curriculum_learning"]["enabled"]
+
+    def curriculum_learning_config(self):
+        return self.data_sampling_config()["curriculum_learning"]
+
+    def random_ltd_enabled(self):
+        de = self.data_efficiency_config()
+        return self.data_efficiency_enabled() and de["data_routing"]["enabled"] and \
+            de["data_routing"]["random_ltd"]["enabled"]
+
+    def random_ltd_config(self):
+        return self.data_efficiency_config()["data_routing"]["random_ltd"]
+
+    def random_ltd_initialize(self):
+        """Bind every ``RandomLayerTokenDrop`` wrapper whose name matches ``random_ltd_layer_id`` to the scheduler
+        (reference engine.py:1078)."""
+        from .data_pipeline.data_routing.basic_layer import RandomLayerTokenDrop
+        assert self.random_ltd_enabled()
+        cfg = self.random_ltd_config()
+        wanted = sorted(cfg["random_ltd_layer_id"])
+        count = 0
+        for name, layer in self.module.named_modules():
+            if isinstance(layer, RandomLayerTokenDrop) and count < len(wanted):
+                if str(wanted[count]) in name:
+                    layer.init_config(cfg, self.random_ltd_scheduler, count)
+                    count += 1
+        if cfg["random_ltd_layer_num"] != count:
+            raise ValueError(f"random_ltd_layer_num {cfg['random_ltd_layer_num']} must equal the number of wrapped "
+                             f"layers matched by random_ltd_layer_id ({count})")
+
+    def get_data_sampler(self):
+        return getattr(self.training_dataloader, "data_sampler", None)
+
+    def set_data_post_process_func(self, post_process_func):
+        if self.training_dataloader is not None:
+            self.training_dataloader.post_process_func = post_process_func
+
+    def set_custom_curriculum_learning_schedule(self, schedule_func_dict):
+        if self.training_dataloader is not None and self.curriculum_learning_enabled():
+            self.training_dataloader.data_sampler.set_custom_curriculum_learning_schedule(schedule_func_dict)
 
     # ------------------------------------------------------------------ dataloader -------------
     def deepspeed_io(self, dataset, batch_size=None, route="train", pin_memory=True, data_sampler=None,
@@ -372,11 +435,22 @@ class DeepSpeedEngine(Module):
         dp_rank = groups._get_data_parallel_rank()
         if self.mpu is not None and hasattr(self.mpu, "get_data_parallel_rank"):
             dp_world, dp_rank = self.mpu.get_data_parallel_world_size(), self.mpu.get_data_parallel_rank()
+        loader_cfg = {}
+        if route == "train" and self.curriculum_learning_enabled():
+            loader_cfg = {
+                "curriculum_learning_enabled": True,
+                "data_efficiency": self.data_efficiency_config(),
+                "data_parallel_group": groups._get_data_parallel_group(),
+                "gradient_accumulation_steps": self.gradient_accumulation_steps(),
+                "global_rank": self.global_rank,
+            }
+            num_local_io_workers = self.data_sampling_config()["num_workers"]
         return DeepSpeedDataLoader(dataset=dataset, batch_size=batch_size, pin_memory=pin_memory and
                                    torch.cuda.is_available(), collate_fn=collate_fn, local_rank=self.local_rank,
                                    tput_timer=None, num_local_io_workers=num_local_io_workers,
                                    data_sampler=data_sampler, data_parallel_world_size=dp_world,
-                                   data_parallel_rank=dp_rank, dataloader_drop_last=self._config.dataloader_drop_last)
+                                   data_parallel_rank=dp_rank, dataloader_drop_last=self._config.dataloader_drop_last,
+                                   deepspeed_dataloader_config=loader_cfg)
 
     # ------------------------------------------------------------------ accessors --------------
     def train_batch_size(self):
@@ -623,6 +697,8 @@ class DeepSpeedEngine(Module):
             self.curriculum_scheduler_legacy.update_difficulty(self.global_steps + 1)
             if self._config.curriculum_params_legacy.get("curriculum_type") == "seqlen":
                 kwargs["curriculum_seqlen"] = self.curriculum_scheduler_legacy.get_current_difficulty()
+        if self.module.training and self.random_ltd_scheduler is not None:
+            self.random_ltd_scheduler.update_seq(self.global_steps)
         if self.training_dataloader is None and self.micro_steps % self.gradient_accumulation_steps() == 0:
             self.tput_timer.start()
         for t in self.engine_timers.forward_timers:
@@ -830,6 +906,9 @@ class DeepSpeedEngine(Module):
             frozen = {n for n, p in self.module.named_parameters() if not p.requires_grad}
             for n in frozen:
                 sd.pop(prefix + n, None)
+        if self.random_ltd_scheduler is not None:
+            from .data_pipeline.data_routing.helper import remove_random_ltd_state_dict
+            sd = remove_random_ltd_state_dict(sd)
         return sd
 
     def load_module_state_dict(self, checkpoint, strict=True, custom_load_fn=None, fetch_z3_params=False):

@@ -92,6 +92,20 @@ int dsb200_swiglu_bwd(const void* dy, const void* gate, const void* up, void* dg
 int dsb200_ce_fwd(void* logits, const int64_t* target, float* loss, float* lse, int rows, int vocab, int64_t row_stride,
                   int ignore_index, int write_grad, float grad_scale, int dt, cudaStream_t stream);
 
+/* ---------------------------------------------------------------- token movement ------------------------- */
+/* scatter == 0: dst[i,:] = src[idx[i],:]; scatter != 0: dst[idx[i],:] = src[i,:]. idx is int32 (idx_bytes 4) or int64
+ * (8); rows and strides are multiples of 16 bytes; indices outside [0, bound) are skipped.
+ * Reference: csrc/random_ltd/gather_scatter.cu, MoE token permutation. */
+int dsb200_move_rows(const void* src, void* dst, const void* idx, int idx_bytes, int64_t n_rows, int64_t row_bytes,
+                     int64_t src_stride_bytes, int64_t dst_stride_bytes, int64_t bound, int scatter,
+                     cudaStream_t stream);
+/* dst[idx[i],:] += w[i] * src[i,:] (w may be NULL); strides in elements; atomic != 0 when indices may repeat. */
+int dsb200_scatter_add_rows(const void* src, void* dst, const void* idx, int idx_bytes, const float* w, int64_t n_rows,
+                            int cols, int64_t src_stride, int64_t dst_stride, int64_t bound, int atomic, int dt,
+                            cudaStream_t stream);
+/* Ascending sort of every row of data[n_rows, n] (n <= 8192). Reference: csrc/random_ltd/token_sort.cu. */
+int dsb200_sort_rows_i32(int* data, int64_t n_rows, int n, cudaStream_t stream);
+
 /* ---------------------------------------------------------------- tcgen05 GEMM --------------------------- */
 /* C[M,N] = A[M,K] * B[N,K]^T, bf16 in/out, fp32 accumulation in TMEM (TMA + tcgen05.mma, persistent).
  * force_bn in {0 (auto), 128, 192, 256}. Reference: cuBLAS calls (csrc/transformer/cublas_wrappers.cu). */

@@ -1,0 +1,222 @@
+"""Data-efficiency library: curriculum schedules, mmap indexed dataset (format interop with the reference), analyzer ->
+sampler end to end, dynamic batching, random-LTD. Mirrors reference tests/unit/runtime/test_data_efficiency.py and
+tests/unit/runtime/test_data.py."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from deepspeed_b200.runtime.data_pipeline.curriculum_scheduler import CurriculumScheduler
+from deepspeed_b200.runtime.data_pipeline.data_routing.basic_layer import RandomLayerTokenDrop
+from deepspeed_b200.runtime.data_pipeline.data_routing.helper import (convert_to_random_ltd,
+                                                                      remove_random_ltd_state_dict)
+from deepspeed_b200.runtime.data_pipeline.data_routing.scheduler import RandomLTDScheduler
+from deepspeed_b200.runtime.data_pipeline.data_sampling.data_analyzer import DataAnalyzer
+from deepspeed_b200.runtime.data_pipeline.data_sampling.data_sampler import DeepSpeedDataSampler
+from deepspeed_b200.runtime.data_pipeline.data_sampling.indexed_dataset import (MMapIndexedDataset,
+                                                                                MMapIndexedDatasetBuilder)
+from deepspeed_b200.runtime.data_pipeline.data_sampling.variable_batch_size_and_lr import (
+    batch_by_seqlens, lr_scheduler_for_variable_batch_size, scale_lr)
+
+
+def test_curriculum_schedules():
+    disc = CurriculumScheduler({"min_difficulty": 1, "max_difficulty": 5, "schedule_type": "fixed_discrete",
+                                "schedule_config": {"difficulty": [1, 2, 3, 4, 5], "max_step": [2, 4, 6, 8]}})
+    got = [disc.update_difficulty(s) for s in range(1, 11)]
+    assert got == [1, 1, 2, 2, 3, 3, 4, 4, 5, 5]
+    lin = CurriculumScheduler({"min_difficulty": 8, "max_difficulty": 1024, "schedule_type": "fixed_linear",
+                               "schedule_config": {"total_curriculum_step": 100, "difficulty_step": 8}})
+    vals = [lin.update_difficulty(s) for s in (1, 25, 50, 100, 200)]
+    assert vals[0] == 16 and vals[1] == 256 and vals[2] == 512 and vals[3] == 1024 and vals[4] == 1024
+    assert all(v % 8 == 0 for v in vals)
+    root = CurriculumScheduler({"min_difficulty": 8, "max_difficulty": 1024, "schedule_type": "fixed_root",
+                                "schedule_config": {"total_curriculum_step": 100, "difficulty_step": 8,
+                                                    "root_degree": 2}})
+    assert root.update_difficulty(25) == 512  # sqrt(0.25) = 0.5
+    cust = CurriculumScheduler({"min_difficulty": 1, "max_difficulty": 9, "schedule_type": "custom"})
+    cust.set_custom_get_difficulty(lambda s: min(9, s * 2))
+    assert cust.update_difficulty(3) == 6
+
+
+def test_indexed_dataset_roundtrip_and_reference_interop(tmp_path):
+    prefix = str(tmp_path / "ds")
+    rows = [np.arange(n, dtype=np.int32) * (n + 1) for n in (3, 1, 7, 0, 5)]
+    b = MMapIndexedDatasetBuilder(prefix + ".bin", dtype=np.int32)
+    for r in rows:
+        b.add_item_numpy(r)
+        b.end_document()
+    b.finalize(prefix + ".idx")
+    ds = MMapIndexedDataset(prefix, skip_warmup=True)
+    assert len(ds) == 5 and list(ds.sizes) == [3, 1, 7, 0, 5]
+    for got, want in zip(ds[0:5], rows):
+        np.testing.assert_array_equal(got, want)
+    np.testing.assert_array_equal(ds.get(2, offset=2, length=3), rows[2][2:5])
+    # merge
+    b2 = MMapIndexedDatasetBuilder(prefix + "2.bin", dtype=np.int32)
+    b2.add_item_numpy(np.array([9, 9]))
+    b2.merge_file_(prefix)
+    b2.finalize(prefix + "2.idx")
+    ds2 = MMapIndexedDataset(prefix + "2", skip_warmup=True)
+    assert len(ds2) == 6
+    np.testing.assert_array_equal(ds2[3], rows[2])
+    # the reference implementation reads our files (same on-disk format)
+    ref_root = os.path.join(os.path.dirname(__file__), "..", "baseline", "_ref")
+    ref_file = os.path.join(ref_root, "deepspeed/runtime/data_pipeline/data_sampling/indexed_dataset.py")
+    if os.path.exists(ref_file):
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("_ref_indexed_dataset", ref_file)
+        mod = importlib.util.module_from_spec(spec)
+        saved = sys.modules.get("deepspeed")
+        try:
+            spec.loader.exec_module(mod)
+        except Exception as e:  # reference import chain not usable on this box
+            pytest.skip(f"reference module not importable: {e}")
+        finally:
+            if saved is not None:
+                sys.modules["deepspeed"] = saved
+        ref = mod.MMapIndexedDataset(prefix, skip_warmup=True)
+        assert len(ref) == 5
+        for i, want in enumerate(rows):
+            np.testing.assert_array_equal(ref[i], want)
+
+
+class _SeqDataset(torch.utils.data.Dataset):
+
+    def __init__(self, n):
+        g = np.random.default_rng(0)
+        self.lens = g.integers(1, 33, size=n)
+
+    def __len__(self):
+        return len(self.lens)
+
+    def __getitem__(self, i):
+        return torch.full((int(self.lens[i]), ), i, dtype=torch.long)
+
+
+def test_analyzer_then_curriculum_sampler(tmp_path):
+    ds = _SeqDataset(200)
+    save = str(tmp_path / "analysis")
+    DataAnalyzer(ds, num_workers=1, worker_id=0, num_threads=2, batch_size=16, metric_names=["seqlen", "total"],
+                 metric_functions=[lambda batch: [len(x) for x in batch], lambda batch: np.array([sum(len(x) for x in batch)])],
+                 metric_types=["single_value_per_sample", "accumulate_value_over_samples"],
+                 metric_dtypes=[np.int64, np.int64], save_path=save, collate_fn=lambda x: x).run_map_reduce()
+    s2m = MMapIndexedDataset(f"{save}/seqlen/seqlen_sample_to_metric", skip_warmup=True)
+    assert [int(s2m[i][0]) for i in range(200)] == [int(x) for x in ds.lens]
+    i2m = MMapIndexedDataset(f"{save}/seqlen/seqlen_index_to_metric", skip_warmup=True)
+    i2s = MMapIndexedDataset(f"{save}/seqlen/seqlen_index_to_sample", skip_warmup=True)
+    for k in range(len(i2m)):
+        assert all(ds.lens[j] == i2m[k][0] for j in i2s[k])
+    assert sum(len(i2s[k]) for k in range(len(i2s))) == 200
+    total = MMapIndexedDataset(f"{save}/total/total_metric_value", skip_warmup=True)
+    assert int(total[0][0]) == int(ds.lens.sum())
+
+    cfg = {"seed": 7, "data_sampling": {"num_epochs": 2, "curriculum_learning": {
+        "enabled": True, "data_cluster_path": str(tmp_path / "clusters"),
+        "curriculum_metrics": {"seqlen": {
+            "index_to_sample_path": f"{save}/seqlen/seqlen_index_to_sample",
+            "index_to_metric_path": f"{save}/seqlen/seqlen_index_to_metric",
+            "difficulty_type": "value", "clustering_type": "schedule_based",
+            "min_difficulty": 8, "max_difficulty": 32, "schedule_type": "fixed_linear",
+            "schedule_config": {"total_curriculum_step": 6, "difficulty_step": 8}}}}}}
+    sampler = DeepSpeedDataSampler(cfg, len(ds), micro_batch_size=4, data_parallel_rank=0, data_parallel_size=1,
+                                   data_parallel_group=None, gradient_accumulation_steps=2, global_rank=0)
+    it = iter(sampler)
+    seen_max = []
+    for step in range(16):
+        mb = next(it)
+        assert len(mb) == 4
+        seen_max.append(max(ds.lens[i] for i in mb))
+        if step < 2:  # first global batch: difficulty 8 -> only sequences of length <= 8
+            assert seen_max[-1] <= 8
+    assert max(seen_max) > 8  # harder samples are admitted later
+    state = sampler.state_dict()
+    sampler2 = DeepSpeedDataSampler(cfg, len(ds), 4, 0, 1, None, 2, 0)
+    sampler2.load_state_dict(state)
+    assert next(iter(sampler2)) == next(it)
+
+
+def test_batch_by_seqlens_and_lr_scaling():
+    g = np.random.default_rng(1)
+    seqlens = [int(x) for x in g.integers(1, 50, size=300)]
+    mb_ids, batch_sizes, max_lens = batch_by_seqlens(seqlens, max_tokens=100, effective_batch_size=4,
+                                                     sequence_picking_order="seqlen", max_batch_size=16)
+    assert len(mb_ids) == 4 * len(batch_sizes) == 4 * len(max_lens)
+    used = [i for _, ids in mb_ids for i in ids]
+    assert len(used) == len(set(used))
+    for _, ids in mb_ids:
+        assert sum(seqlens[i] for i in ids) <= 100 and 1 <= len(ids) <= 16
+    same, _, _ = batch_by_seqlens(seqlens, 100, effective_batch_size=4, required_microbatches_of_same_size=True)
+    for first in range(0, len(same), 4):
+        assert len({len(ids) for _, ids in same[first:first + 4]}) == 1
+    assert scale_lr(8, 16, 1.0, "linear") == 2.0 and abs(scale_lr(8, 32, 1.0, "sqrt") - 2.0) < 1e-12
+    opt = torch.optim.SGD([torch.nn.Parameter(torch.zeros(1))], lr=0.1)
+    sched = lr_scheduler_for_variable_batch_size(10, [10, 20, 5], None, opt)
+    assert abs(opt.param_groups[0]["lr"] - 0.1) < 1e-12
+    sched.step()
+    assert abs(opt.param_groups[0]["lr"] - 0.2) < 1e-12
+    sched.step()
+    assert abs(opt.param_groups[0]["lr"] - 0.05) < 1e-12
+
+
+class _Layer(torch.nn.Module):
+
+    def __init__(self, h):
+        super().__init__()
+        self.lin = torch.nn.Linear(h, h)
+
+    def forward(self, x, attention_mask=None):
+        return torch.tanh(self.lin(x))
+
+
+def test_random_ltd_layer_and_scheduler():
+    torch.manual_seed(0)
+    H, S, B = 16, 12, 3
+    cfg = {"total_layer_num": 4, "random_ltd_layer_num": 2, "random_ltd_layer_id": [1, 2], "model_mask_name": None,
+           "model_type": "decoder", "hidden_state_order": "batch_seq_dim", "global_batch_size": 6,
+           "micro_batch_size": 3,
+           "random_ltd_schedule": {"min_value": 4, "max_value": S, "schedule_type": "fixed_linear",
+                                   "schedule_config": {"require_steps": 10, "seq_per_step": 4}},
+           "layer_token_lr_schedule": {"enabled": False}}
+    model = torch.nn.Sequential(*[_Layer(H) for _ in range(4)])
+    convert_to_random_ltd(model, _Layer)
+    wrapped = [m for m in model if isinstance(m, RandomLayerTokenDrop)]
+    assert len(wrapped) == 4
+    sch = RandomLTDScheduler(cfg)
+    for lid, idx in enumerate((1, 2)):
+        model[idx].init_config(cfg, sch, lid)
+    sch.update_seq(0)
+    assert sch.get_current_seq() == 4
+    x = torch.randn(B, S, H, requires_grad=True)
+    model.train()
+    h0 = model[0](x)
+    h1 = model[1](h0)
+    idx = sch.state["sample_idx"][0].long()  # [B, 4]
+    assert torch.all(idx[:, 1:] > idx[:, :-1])  # sorted, unique
+    want = h0.clone()
+    for b in range(B):
+        want[b, idx[b]] = model[1].random_ltd_layer(h0[b, idx[b]])
+    torch.testing.assert_close(h1, want)
+    out = model[3](model[2](h1))
+    out.sum().backward()
+    assert x.grad is not None and torch.isfinite(x.grad).all()
+    # dropped tokens bypass layer 1: gradient check against the dense recomputation
+    x2 = x.detach().clone().requires_grad_(True)
+    h0b = model[0](x2)
+    h1b = h0b.clone()
+    for b in range(B):
+        h1b[b, idx[b]] = model[1].random_ltd_layer(h0b[b, idx[b]])
+    idx2 = sch.state["sample_idx"][1].long()
+    h2b = h1b.clone()
+    for b in range(B):
+        h2b[b, idx2[b]] = model[2].random_ltd_layer(h1b[b, idx2[b]])
+    model[3](h2b).sum().backward()
+    torch.testing.assert_close(x.grad, x2.grad)
+    # schedule grows to the full length, then the wrapper is a passthrough
+    sch.update_seq(10)
+    assert sch.get_current_seq() == S
+    torch.testing.assert_close(model[1](h0.detach()), model[1].random_ltd_layer(h0.detach()))
+    assert sch.state["consumed_layer_tokens"] == 6 * (4 * 2 + S * 2) + 6 * (S * 2 + S * 2)
+    sd = remove_random_ltd_state_dict(model.state_dict())
+    assert "1.lin.weight" in sd and not any("random_ltd_layer" in k for k in sd)
