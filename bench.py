@@ -35,7 +35,10 @@ def parse():
     ap.add_argument("--layers", type=int, default=32, help="debug only: fewer layers => INVALID headline number")
     ap.add_argument("--model", default="llama3-8b")
     ap.add_argument("--zero", type=int, default=3)
-    ap.add_argument("--no-ckpt", action="store_true", help="disable activation checkpointing")
+    ap.add_argument("--act-ckpt", default="auto",
+                    help="activation checkpointing: auto (only as many layers as HBM requires; same rule for both "
+                    "arms), on, off, or an integer number of checkpointed layers (ours only)")
+    ap.add_argument("--no-ckpt", action="store_true", help="same as --act-ckpt off")
     ap.add_argument("--local_rank", type=int, default=-1)
     return ap.parse_args()
 
@@ -92,6 +95,31 @@ def model_dims(args):
                 rope_theta=500000.0)
 
 
+def ckpt_layers(args, world, impl, total_mem_bytes):
+    """How many transformer layers recompute their activations in backward.
+
+    Recomputation is pure overhead (one extra forward = 1/4 of the GEMM work), so it is used only where the model
+    states leave no room: per rank they take ~17 B/param / world (fp32 master + 2 moments + bf16 weights + grads, plus
+    gather buffers). One layer's saved activations are ~150 KB/token with the fused kernels (ours) and ~3x that with
+    the stock HF layer (reference), which can only checkpoint all layers or none."""
+    mode = "off" if args.no_ckpt else args.act_ckpt
+    if mode == "on":
+        return args.layers
+    if mode == "off":
+        return 0
+    if mode != "auto":
+        return max(0, min(args.layers, int(mode)))
+    tokens = args.mbs * args.seq
+    params = 8.03e9 * args.layers / 32
+    states = 17.0 * params / world + 6e9           # + gathered units, logits chunk, allocator slack
+    per_layer = tokens * (150e3 if impl == "ours" else 450e3)
+    budget = 0.90 * total_mem_bytes - states
+    if impl == "reference":
+        return 0 if budget > per_layer * args.layers else args.layers
+    keep = int(max(0, budget) // per_layer)
+    return max(0, args.layers - keep)
+
+
 def ds_config(args, world):
     return {
         "train_micro_batch_size_per_gpu": args.mbs,
@@ -112,7 +140,8 @@ def build_ours(args, torch, world):
     import deepspeed_b200 as ds
     from deepspeed_b200.models import LlamaConfig, LlamaForCausalLM
     dev = torch.device("cuda", torch.cuda.current_device())
-    cfg = LlamaConfig(**model_dims(args), gradient_checkpointing=not args.no_ckpt, dtype=torch.bfloat16)
+    args.n_ckpt = ckpt_layers(args, world, "ours", torch.cuda.get_device_properties(dev).total_memory)
+    cfg = LlamaConfig(**model_dims(args), gradient_checkpointing=args.n_ckpt, dtype=torch.bfloat16)
     torch.manual_seed(1234)
     model = LlamaForCausalLM(cfg, device=dev)
     engine, _, _, _ = ds.initialize(model=model, config=ds_config(args, world))
@@ -157,11 +186,12 @@ def build_reference(args, torch, world):
                 m = LlamaForCausalLM(hf_cfg)
         finally:
             torch.set_default_dtype(old)
-        if not args.no_ckpt:
+        if args.n_ckpt:
             m.gradient_checkpointing_enable(gradient_checkpointing_kwargs={"use_reentrant": False})
         m.train()
         return m
 
+    args.n_ckpt = ckpt_layers(args, world, "reference", torch.cuda.get_device_properties(dev).total_memory)
     cfg = ds_config(args, world)
     model = make_model()
     try:
@@ -294,7 +324,7 @@ def main():
             "data": "synthetic random tokens, random-init weights",
             "config": {"model": f"Llama-3-8B ({args.layers} layers, h4096, 32q/8kv heads, ffn14336, vocab128256)",
                        "params": nparams, "global_batch": world * B, "seq_len": S,
-                       "parallelism": f"zero{args.zero}-dp{world}", "activation_checkpointing": not args.no_ckpt,
+                       "parallelism": f"zero{args.zero}-dp{world}", "activation_checkpointing": f"{args.n_ckpt}/{args.layers} layers",
                        "optimizer": "AdamW (fused)", "grad_clip": 1.0,
                        "l2": "inputs larger than L2 (per-step working set >100 GB), no flush needed"},
             "e2e": {"value": e2e_value, "unit": "tokens/s", "ms_per_step": e2e_ms / K,

@@ -194,9 +194,12 @@ class LlamaModel(nn.Module):
                 max(self.cfg.max_position_embeddings, S * getattr(self.sp_attention, "world", 1))
         cos, sin = self.rope(max_pos, input_ids.device)
         h = self.embed_tokens(input_ids)
-        ckpt = self.cfg.gradient_checkpointing and self.training and torch.is_grad_enabled()
-        for layer in self.layers:
-            if ckpt:
+        # True: recompute every layer in backward; an int k: only the first k layers (partial checkpointing, to
+        # spend exactly the HBM that is free); False/0: keep all activations
+        gc = self.cfg.gradient_checkpointing
+        n_ckpt = (len(self.layers) if gc is True else int(gc)) if (self.training and torch.is_grad_enabled()) else 0
+        for i, layer in enumerate(self.layers):
+            if i < n_ckpt:
                 h = torch.utils.checkpoint.checkpoint(layer, h, cos, sin, position_ids, self.sp_attention,
                                                       use_reentrant=False)
             else:
