@@ -225,6 +225,8 @@ def main():
     if args.impl == "reference" and not os.path.isdir(os.path.join(REPO, "baseline", "_ref", "deepspeed")):
         print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref not present (reference not installed)"}))
         return 0
+    # both arms: let the caching allocator grow segments in place (no fragmentation stalls close to the HBM limit)
+    os.environ.setdefault("PYTORCH_CUDA_ALLOC_CONF", "expandable_segments:True")
     import torch
     if not torch.cuda.is_available():
         print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device"}))

@@ -15,53 +15,9 @@
 //   flags[FLAG_DONE  + src]  : "src has finished reading my buffer for epoch e"
 // Flags only ever grow, so no reset race exists; the host passes the expected epoch.
 #include "common.cuh"
+#include "symm_common.cuh"
 
 namespace {
-
-constexpr int MAX_WORLD = 16;
-constexpr int FLAG_STRIDE = 32;  // uint32 slots per channel (>= MAX_WORLD)
-
-struct PeerPtrs {
-    void* p[MAX_WORLD];
-};
-
-__device__ __forceinline__ void st_release_sys(uint32_t* addr, uint32_t v)
-{
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* addr)
-{
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
-    return v;
-}
-__device__ __forceinline__ uint4 ld_peer_v4(const void* p)
-{
-    uint4 r;
-    asm volatile("ld.global.relaxed.sys.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p)
-                 : "memory");
-    return r;
-}
-
-// Tell every peer (including myself) that I reached `epoch` on `channel`.
-__device__ __forceinline__ void signal_all(const PeerPtrs& flags, int rank, int world, int channel, uint32_t epoch)
-{
-    if (threadIdx.x < world) {
-        uint32_t* f = reinterpret_cast<uint32_t*>(flags.p[threadIdx.x]) + channel * FLAG_STRIDE + rank;
-        st_release_sys(f, epoch);
-    }
-}
-// Wait until every peer has reached `epoch` on `channel` (reads my local flag words only).
-__device__ __forceinline__ void wait_all(const PeerPtrs& flags, int rank, int world, int channel, uint32_t epoch)
-{
-    if (threadIdx.x < world) {
-        const uint32_t* f = reinterpret_cast<const uint32_t*>(flags.p[rank]) + channel * FLAG_STRIDE + threadIdx.x;
-        while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) { __nanosleep(64); }
-    }
-    __syncthreads();
-}
 
 template <typename T>
 __device__ __forceinline__ void accum8(float (&acc)[16 / sizeof(T)], uint4 raw)

@@ -23,6 +23,7 @@ from ..utils.logging import log_dist, logger
 from . import comm as dist
 
 CH_RS_READY, CH_RS_DONE, CH_AG_READY, CH_AG_DONE, CH_A2A_READY, CH_A2A_DONE, CH_USER = 0, 1, 2, 3, 4, 5, 6
+CH_QAG_READY, CH_QAG_DONE, CH_GEMM_READY, CH_GEMM_DONE = 7, 8, 9, 10
 _CONTEXTS = {}
 
 
@@ -35,6 +36,12 @@ def _declare(L):
     L.dsb200_symm_all_gather.restype = I
     L.dsb200_symm_all_to_all.argtypes = [P, P, I, I, L64, L64, I, P, P, I, I, U, I, P]
     L.dsb200_symm_all_to_all.restype = I
+    L.dsb200_symm_rs_adam.argtypes = [P, P, I, I, L64, I, F, P, P, P, P, I, P, P, P, P, I, I, U, I, P]
+    L.dsb200_symm_rs_adam.restype = I
+    L.dsb200_symm_fp8_stage_bytes.argtypes = [L64, I]
+    L.dsb200_symm_fp8_stage_bytes.restype = L64
+    L.dsb200_symm_all_gather_fp8.argtypes = [P, I, P, P, I, I, L64, I, P, P, I, I, U, U, I, P]
+    L.dsb200_symm_all_gather_fp8.restype = I
     L.dsb200_symm_wait.argtypes = [P, I, I, I, U, P]
     L.dsb200_symm_wait.restype = I
     L.dsb200_symm_signal.argtypes = [P, I, I, I, U, P]
@@ -137,6 +144,50 @@ class SymmContext:
             raise RuntimeError(f"symm reduce_scatter failed: {K.last_error()}")
         K._LAUNCHES += 1
         buf.last_rs_epoch = ep
+        return ep
+
+    def rs_adam(self, buf: SymmBuffer, in_dtype, shard_numel, grad_scale, p, m, v, lp, seg_bounds, hyper,
+                want_sumsq=False, ctas=None):
+        """Fused path (1): reduce-scatter my gradient shard out of every peer's bucket ``buf`` and apply AdamW to the
+        fp32 master ``p`` / moments ``m``, ``v`` (+ bf16 copy ``lp``) in the same kernel. ``seg_bounds`` (len nseg+1,
+        multiples of 8) and ``hyper`` (nseg rows of lr, b1, b2, eps, wd, bc1, bc2, mode) describe the parameter-group
+        segments of the shard. Returns (epoch, grid)."""
+        ep = self._next(CH_RS_READY)
+        nseg = len(seg_bounds) - 1
+        bounds = (ctypes.c_int64 * (nseg + 1))(*[int(b) for b in seg_bounds])
+        hy = (ctypes.c_float * (nseg * 8))(*[float(x) for row in hyper for x in row])
+        grid = self.lib.dsb200_symm_rs_adam(
+            buf.ptrs, self.flags.ptrs, self.rank, self.world, shard_numel, K._DT[in_dtype], float(grad_scale),
+            ctypes.c_void_p(p.data_ptr()), ctypes.c_void_p(m.data_ptr()), ctypes.c_void_p(v.data_ptr()),
+            ctypes.c_void_p(lp.data_ptr() if lp is not None else 0), nseg, bounds, hy,
+            ctypes.c_void_p(self.partials.data_ptr()) if want_sumsq else ctypes.c_void_p(0),
+            ctypes.c_void_p(self.tickets.data_ptr()), CH_RS_READY, CH_RS_DONE, ep,
+            self.default_ctas if ctas is None else ctas, self._stream())
+        if grid < 0:
+            raise RuntimeError(f"symm rs_adam failed: {K.last_error()}")
+        K._LAUNCHES += 1
+        buf.last_rs_epoch = ep
+        return ep, grid
+
+    def fp8_stage_bytes(self, shard_elems, block=256):
+        return int(self.lib.dsb200_symm_fp8_stage_bytes(shard_elems, block))
+
+    def all_gather_fp8(self, my_shard, stage: SymmBuffer, full, block=256, ctas=None):
+        """Fused path (3), qwZ: quantize ``my_shard`` (bf16/fp16) to block-scaled e4m3 in ``stage``, pull the peers'
+        payload + scales over NVLink and dequantize into ``full`` -- one kernel, half the NVLink bytes. Every rank
+        (the owner included) ends up with the same dequantized values."""
+        ep = self._next(CH_QAG_READY)
+        n = my_shard.numel()
+        assert stage.nbytes >= self.fp8_stage_bytes(n, block) and full.numel() >= n * self.world
+        rc = self.lib.dsb200_symm_all_gather_fp8(
+            ctypes.c_void_p(my_shard.data_ptr()), K._DT[my_shard.dtype], stage.ptrs, self.flags.ptrs, self.rank,
+            self.world, n, block, ctypes.c_void_p(full.data_ptr()), ctypes.c_void_p(self.tickets.data_ptr() + 12),
+            CH_QAG_READY, CH_QAG_DONE, ep, getattr(stage, "last_qag_epoch", 0),
+            self.default_ctas if ctas is None else ctas, self._stream())
+        if rc != 0:
+            raise RuntimeError(f"symm all_gather_fp8 failed: {K.last_error()}")
+        K._LAUNCHES += 1
+        stage.last_qag_epoch = ep
         return ep
 
     def wait_rs_done(self, epoch):

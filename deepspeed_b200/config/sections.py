@@ -154,6 +154,7 @@ class DeepSpeedZeroConfig(DeepSpeedConfigModel):
     leaf_module: DeepSpeedZeroLeafModuleConfig = Field(default_factory=DeepSpeedZeroLeafModuleConfig)
     # ---- B200-native knobs (no reference counterpart) ----
     fused_collectives: Optional[bool] = None  # None -> on when symmetric memory is available on NVLink
+    fused_rs_adam: Optional[bool] = None  # None -> on when no clipping / loss scale / accumulation forces a late step
     unit_max_numel: int = Field(pp_int(1e9), ge=0)  # ZeRO-3 unit (flat shard) upper size in elements
     quantized_weights_format: str = "fp8_e4m3_block32"  # qwZ wire format: block-scaled fp8 or "int8"
     quantized_gradients_format: str = "fp8_e4m3_block32"

@@ -127,6 +127,12 @@ class UnitCoordinator:
             esz = src.element_size()
             self.z.symm.all_gather(st.lp_symm, u.shard_offset * esz, u.shard_numel * esz, full)
             return
+        if self.z.quantized_weights and self.z.symm is not None and u.dtype in (torch.bfloat16, torch.float16) \
+                and src.data_ptr() == u.param_shard.data_ptr() and u.shard_numel % 256 == 0 \
+                and group is u.dp_group:
+            # fused path 3 (qwZ): quantize -> NVLink pull of FP8 + scales -> dequantize, one kernel
+            self.z.symm.all_gather_fp8(src, self._fp8_stage(u), full)
+            return
         if self.z.quantized_weights and u.dtype in (torch.bfloat16, torch.float16) and full.is_cuda:
             from ...ops.quantizer import quantized_all_gather
             quantized_all_gather(full, src, group)
@@ -137,6 +143,18 @@ class UnitCoordinator:
             dist.all_gather_into_tensor(full, src, group=group)
         else:  # hpZ secondary gather: group is a subgroup holding replicated sub-shards
             dist.all_gather_into_tensor(full, src, group=group)
+
+    def _fp8_stage(self, u):
+        """Round-robin symmetric staging buffers for the FP8 payload + scales (the kernel itself waits for the peers
+        to be done with the buffer's previous use)."""
+        pool = getattr(self, "_fp8_pool", None)
+        if pool is None:
+            nbytes = self.z.symm.fp8_stage_bytes(max(x.shard_numel for x in self.z.units), 256)
+            pool = self._fp8_pool = [self.z.symm.alloc(nbytes, want_multicast=False) for _ in range(3)]
+            self._fp8_next = 0
+        stage = pool[self._fp8_next]
+        self._fp8_next = (self._fp8_next + 1) % len(pool)
+        return stage
 
     def _make_secondary(self, u):
         """hpZ: keep an intra-group replica so the backward re-gather stays inside the (smaller) group."""

@@ -71,7 +71,7 @@ class ZeroShardedOptimizer:
                  unit_max_numel=int(1e9), param_persistence_threshold=int(1e5), prefetch=True, mics_shard_size=-1,
                  hpz_size=1, quantized_weights=False, quantized_gradients=False, expert_groups=None,
                  leaf_modules=(), elastic_checkpoint=False, timers=None, fused_collectives=None,
-                 ignore_unused_parameters=True):
+                 ignore_unused_parameters=True, fused_rs_adam=None):
         self.module = module
         self.optimizer = optimizer
         self.stage = int(stage)
@@ -188,6 +188,7 @@ class ZeroShardedOptimizer:
                     logger.warning(f"symmetric-memory collectives unavailable ({e}); using NCCL")
                     self.symm, self._grad_pool = None, None
         self._allocate_and_link()
+        self._setup_fused_rs_adam(fused_rs_adam)
         self._register_grad_hooks()
         self.coordinator = None
         if self.partition_params:
@@ -307,6 +308,77 @@ class ZeroShardedOptimizer:
         for g, views in zip(self.optimizer.param_groups, self._views_by_group):
             g["params"] = views
         self.param_groups = self.optimizer.param_groups
+
+    # ------------------------------------------------------------------ fused RS + Adam --------
+    def _setup_fused_rs_adam(self, want):
+        """Update-in-backward (north-star path 1): when nothing forces the step to wait for a global quantity
+        (no clipping, no fp16 loss scale, gas == 1) each bucket's reduce-scatter kernel also applies AdamW to the
+        owner shard, so reduced gradients never reach HBM and ``step()`` has no optimizer kernel left to run.
+        The moments are carved from flat per-storage tensors so that a unit's shard is contiguous."""
+        self._fused_adam = False
+        self._fused_iter = False
+        if want is False or self.symm is None or self._grad_pool is None:
+            if want is True:
+                raise RuntimeError("fused_rs_adam needs the symmetric-memory collectives (NVLink, world <= 16)")
+            return
+        from ...ops.optimizers import FusedAdam
+        ok = (type(self.optimizer) is FusedAdam and self.master_dtype == torch.float32 and self.clip_grad == 0.0
+              and self.lp_dtype != torch.float16 and not self.offload_optimizer and self.gas == 1
+              and all(g.get("state_dtype") in (None, torch.float32) for g in self.optimizer.param_groups))
+        per_unit = {}
+        for (key, a, b, gi, u, v) in self._segments:
+            per_unit.setdefault(u.uid, []).append((a - u.shard_offset, b - u.shard_offset, gi))
+        for u in self.units:
+            segs = per_unit.get(u.uid, [])
+            ok = ok and u.world > 1 and len(segs) <= 8 and all(x % 8 == 0 and y % 8 == 0 for x, y, _ in segs)
+        if not ok:
+            if want is True:
+                raise RuntimeError("fused_rs_adam requested but its preconditions do not hold (FusedAdam, fp32 master, "
+                                   "no clipping, no fp16, gas == 1, <= 8 aligned group runs per unit)")
+            return
+        for key, st in self.storages.items():
+            st.exp_avg = torch.zeros(st.numel, dtype=torch.float32, device=st.device)
+            st.exp_avg_sq = torch.zeros(st.numel, dtype=torch.float32, device=st.device)
+        for (key, a, b, gi, u, v) in self._segments:
+            st = self.storages[key]
+            self.optimizer.state[v] = {"step": 0, "exp_avg": st.exp_avg[a:b], "exp_avg_sq": st.exp_avg_sq[a:b]}
+        self._unit_segs = per_unit
+        self._fused_sumsq = torch.zeros((), dtype=torch.float32, device=self.units[0].device)
+        self._fused_adam = True
+        log_dist("ZeRO: fused reduce-scatter + AdamW (update in backward) enabled", [0])
+
+    def _rs_adam_unit(self, u: FlatUnit, div):
+        if not self._fused_iter:  # first bucket of this iteration: advance the step counters (bias correction)
+            self._fused_iter = True
+            self._fused_sumsq.zero_()
+            for g in self.optimizer.param_groups:
+                g["step"] = g.get("step", 0) + 1
+                for v in g["params"]:
+                    self.optimizer.state[v]["step"] = g["step"]
+        st = self.storages[(u.group_key, u.dtype)]
+        a, b = u.shard_offset, u.shard_offset + u.shard_numel
+        segs = sorted(self._unit_segs.get(u.uid, []))
+        if not segs:
+            segs = [(0, 0, 0)]
+        bounds, hyper = [segs[0][0]], []
+        # the kernel wants a gap-free cover: a (frozen / padding) gap becomes a zero-lr segment
+        for x, y, gi in segs:
+            if x != bounds[-1]:
+                hyper.append([0.0, 0.0, 0.0, 1.0, 0.0, 1.0, 1.0, 1.0])
+                bounds.append(x)
+            h = self.optimizer._hyper(self.optimizer.param_groups[gi])
+            hyper.append([h["lr"], h["beta1"], h["beta2"], h["eps"], h["wd"], h["bc1"], h["bc2"], h["mode"]])
+            bounds.append(y)
+        if bounds[0] != 0:
+            bounds.insert(0, 0)
+            hyper.insert(0, [0.0, 0.0, 0.0, 1.0, 0.0, 1.0, 1.0, 1.0])
+        lp = st.lp[a:b] if self.partition_params else u.param_shard
+        _, grid = self.symm.rs_adam(u._slot, u.full_grad.dtype, u.shard_numel, 1.0 / div, st.master[a:b],
+                                    st.exp_avg[a:b], st.exp_avg_sq[a:b], lp if lp.dtype == torch.bfloat16 else None,
+                                    bounds, hyper, want_sumsq=True)
+        self._fused_sumsq.add_(self.symm.partials[:grid].sum())
+        if lp.dtype != torch.bfloat16:
+            lp.copy_(st.master[a:b])
 
     @torch.no_grad()
     def _flatten_unit(self, u: FlatUnit, st, a, b):
@@ -456,7 +528,11 @@ class ZeroShardedOptimizer:
             stream_ctx = torch.cuda.stream(self.rs_stream)
             stream_ctx.__enter__()
         try:
-            if getattr(u, "_slot", None) is not None and self.symm is not None:
+            if getattr(u, "_slot", None) is not None and self.symm is not None and self._fused_adam and first:
+                # ONE kernel: NVLink loads + fp32 sum + average + AdamW on the owner shard + bf16 weight write
+                self._rs_adam_unit(u, div)
+                u._slot = None
+            elif getattr(u, "_slot", None) is not None and self.symm is not None:
                 # ONE kernel: NVLink loads from every peer's bucket + fp32 sum + average + cast + accumulate
                 self.symm.reduce_scatter(u._slot, full.dtype, u.shard_numel, u.grad_shard, accumulate=not first,
                                          scale=1.0 / div)
@@ -590,6 +666,8 @@ class ZeroShardedOptimizer:
         return sq
 
     def get_global_grad_norm(self):
+        if self._global_grad_norm is None and getattr(self, "_global_grad_norm_t", None) is not None:
+            self._global_grad_norm = float(self._global_grad_norm_t)
         return self._global_grad_norm
 
     # ------------------------------------------------------------------ step -------------------
@@ -609,6 +687,19 @@ class ZeroShardedOptimizer:
         if self._use_streams and self.overlap_comm:
             torch.cuda.current_stream().wait_stream(self.rs_stream)
 
+        if self._fused_iter:
+            # every bucket was updated by its reduce-scatter kernel during backward; only bookkeeping is left
+            self._fused_iter = False
+            sq = self._fused_sumsq.clone()
+            dist.all_reduce(sq, group=self._shard_group)
+            self._global_grad_norm_t = sq.sqrt_()  # device scalar; materialised lazily by get_global_grad_norm
+            self._global_grad_norm = None
+            self.overflow = False
+            self._lp_written_by_step = True
+            self._sync_lp_from_master()
+            self._zero_grad_shards()
+            self._post_step_gather()
+            return
         self._zero_stale_shards()
         norm_sq = self._global_grad_norm_sq()
         scale = float(self.cur_scale)
@@ -873,7 +964,11 @@ class ZeroShardedOptimizer:
                 stt = self.optimizer.state[v]
                 for k, d in tens.items():
                     src = d[_skey_str(skey)][a:b]
-                    stt[k] = src.to(v.device).clone().view_as(v)
+                    cur = stt.get(k)
+                    if torch.is_tensor(cur) and cur.numel() == b - a:
+                        cur.copy_(src.view_as(cur))  # keeps views into flat moment storage (fused RS+Adam) intact
+                    else:
+                        stt[k] = src.to(v.device).clone().view_as(v)
                 for k, val in scalars.get(gi, scalars.get(str(gi), {})).items():
                     stt[k] = torch.tensor(float(val)) if k == "step" and _step_is_tensor(self.optimizer) else val
             if hasattr(self.optimizer, "on_state_loaded"):
@@ -907,6 +1002,9 @@ class ZeroShardedOptimizer:
                 for k, t in list(stt.items()):
                     if torch.is_tensor(t) and t.numel() > 1:
                         stt[k] = t.to(dev)
+            if getattr(self, "_fused_adam", False):  # the flat moment storage is re-created on reload
+                for st in self.storages.values():
+                    st.exp_avg = st.exp_avg_sq = None
             self._offloaded_states.add("optim_states")
         if torch.cuda.is_available():
             torch.cuda.synchronize()
@@ -924,6 +1022,16 @@ class ZeroShardedOptimizer:
                 for k, t in list(stt.items()):
                     if torch.is_tensor(t) and t.numel() > 1:
                         stt[k] = t.to(v.device)
+            if getattr(self, "_fused_adam", False):
+                for st in self.storages.values():
+                    st.exp_avg = torch.zeros(st.numel, dtype=torch.float32, device=st.device)
+                    st.exp_avg_sq = torch.zeros(st.numel, dtype=torch.float32, device=st.device)
+                for (skey, a, b, gi, u, v) in self._segments:
+                    st, stt = self.storages[skey], self.optimizer.state[v]
+                    for k in ("exp_avg", "exp_avg_sq"):
+                        flat = getattr(st, k)[a:b]
+                        flat.copy_(stt[k].view(-1))
+                        stt[k] = flat
         self._offloaded_states.clear()
 
     def _move_flat(self, st, attr, dev, pin):

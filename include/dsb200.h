@@ -92,6 +92,24 @@ int dsb200_swiglu_bwd(const void* dy, const void* gate, const void* up, void* dg
 int dsb200_ce_fwd(void* logits, const int64_t* target, float* loss, float* lse, int rows, int vocab, int64_t row_stride,
                   int ignore_index, int write_grad, float grad_scale, int dt, cudaStream_t stream);
 
+/* ---------------------------------------------------------------- fused collective + compute (symm_fused.cu) */
+/* Reduce-scatter my gradient shard out of every peer's bucket and apply AdamW to the fp32 master / moments (+ bf16
+ * copy) in the same kernel. seg_bounds[nseg+1]: element offsets (multiples of 8) of the parameter-group runs inside the
+ * shard; hyper[nseg][8] = {lr, beta1, beta2, eps, wd, bias_corr1, bias_corr2, mode (1 = AdamW)}. Returns the grid size.
+ * Reference: reduce_scatter_coalesced + a separate FusedAdam launch (coalesced_collectives.py:158, fused_adam.py:195). */
+int dsb200_symm_rs_adam(const uint64_t* peer_bufs, const uint64_t* peer_flags, int rank, int world,
+                        int64_t shard_numel, int in_dt, float grad_scale, float* p, float* m, float* v, void* lp,
+                        int nseg, const int64_t* seg_bounds, const float* hyper, float* sumsq_partials,
+                        unsigned int* ticket, int ch_ready, int ch_done, unsigned int epoch, int ctas,
+                        cudaStream_t stream);
+/* ZeRO++ qwZ all-gather in one kernel: block-scaled e4m3 quantize into the symmetric staging buffer, NVLink pull of the
+ * peers' payload + scales, dequantize into `full`. Reference: partition_parameters.py:1248 + CUDAQuantizer. */
+int64_t dsb200_symm_fp8_stage_bytes(int64_t shard_elems, int block);
+int dsb200_symm_all_gather_fp8(const void* my_shard, int dt, const uint64_t* peer_stage, const uint64_t* peer_flags,
+                               int rank, int world, int64_t shard_elems, int block, void* full,
+                               unsigned int* tickets, int ch_ready, int ch_done, unsigned int epoch,
+                               unsigned int reuse_epoch, int ctas, cudaStream_t stream);
+
 /* ---------------------------------------------------------------- token movement ------------------------- */
 /* scatter == 0: dst[i,:] = src[idx[i],:]; scatter != 0: dst[idx[i],:] = src[i,:]. idx is int32 (idx_bytes 4) or int64
  * (8); rows and strides are multiples of 16 bytes; indices outside [0, bound) are skipped.

@@ -82,7 +82,7 @@ def test_symm_collectives_match_nccl(world):
             assert err <= 2e-2 * max(mag, 1.0), (k, o[k])
 
 
-def _train(fused, steps):
+def _train(fused, steps, extra=None, clip=1.0, stage=3):
     import deepspeed_b200 as ds
     from deepspeed_b200.models import LlamaConfig, LlamaForCausalLM
     dev = torch.device("cuda", torch.cuda.current_device())
@@ -91,10 +91,13 @@ def _train(fused, steps):
                       num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=256)
     model = LlamaForCausalLM(cfg, device=dev)
     eng, _, _, _ = ds.initialize(model=model, config={
-        "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True}, "gradient_clipping": 1.0,
-        "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}},
-        "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 1000, "fused_collectives": fused}})
+        "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True}, "gradient_clipping": clip,
+        "optimizer": {"type": "AdamW", "params": {"lr": 1e-3, "weight_decay": 0.1}},
+        "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 1000, "fused_collectives": fused,
+                              **(extra or {})}})
     assert (eng.optimizer.symm is not None) == fused
+    if extra and extra.get("fused_rs_adam"):
+        assert eng.optimizer._fused_adam
     torch.manual_seed(1 + ds.comm.get_rank())
     losses = []
     for _ in range(steps):
@@ -103,6 +106,8 @@ def _train(fused, steps):
         eng.backward(loss)
         eng.step()
         losses.append(float(loss.detach()))
+    if fused and extra and extra.get("zero_quantized_weights"):
+        assert getattr(eng.optimizer.coordinator, "_fp8_pool", None) is not None, "fused FP8 all-gather not used"
     return losses
 
 
@@ -113,3 +118,111 @@ def test_zero3_fused_collectives_match_nccl_path():
     for la, lb in zip(a[0], b[0]):
         assert abs(la - lb) < 5e-2, (a[0], b[0])
     assert a[0][-1] < a[0][0]
+
+
+@needs2
+@pytest.mark.parametrize("stage", [2, 3])
+def test_update_in_backward_matches_late_step(stage):
+    """fused reduce-scatter+AdamW (no optimizer kernel in step()) vs reduce-scatter then fused Adam in step()."""
+    a = run_distributed(_train, 2, args=(True, 6, {"fused_rs_adam": True}, 0.0, stage))
+    b = run_distributed(_train, 2, args=(True, 6, {"fused_rs_adam": False}, 0.0, stage))
+    c = run_distributed(_train, 2, args=(False, 6, None, 0.0, stage))
+    for la, lb, lc in zip(a[0], b[0], c[0]):
+        assert abs(la - lb) < 3e-2 and abs(la - lc) < 5e-2, (a[0], b[0], c[0])
+    assert a[0][-1] < a[0][0]
+
+
+@needs2
+def test_qwz_fused_fp8_all_gather_trains():
+    """ZeRO++ qwZ through the fused FP8 all-gather kernel: same trajectory as the NCCL qwZ path (identical
+    quantization), close to the unquantized one."""
+    a = run_distributed(_train, 2, args=(True, 6, {"zero_quantized_weights": True}))
+    b = run_distributed(_train, 2, args=(False, 6, {"zero_quantized_weights": True}))
+    c = run_distributed(_train, 2, args=(True, 6, None))
+    for la, lb, lc in zip(a[0], b[0], c[0]):
+        assert abs(la - lb) < 5e-2 and abs(la - lc) < 0.25, (a[0], b[0], c[0])
+    assert a[0][-1] < a[0][0]
+
+
+def _fused_v2(world):
+    """rs_adam vs (NCCL reduce-scatter + torch AdamW); all_gather_fp8 vs (quantize -> NCCL all-gather -> dequantize)."""
+    import torch.distributed as dist
+    from deepspeed_b200.comm import symm
+    from deepspeed_b200.ops.quantizer import fp8_block_dequantize, fp8_block_quantize
+    rank = dist.get_rank()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    ctx = symm.SymmContext.get(dist.group.WORLD)
+    out = {}
+    # ---- (A) reduce-scatter + AdamW, two parameter-group segments, two consecutive steps ----
+    shard = 64 * 1024 + 512
+    n = shard * world
+    buf = ctx.alloc(n * 2)
+    torch.manual_seed(5)
+    p0 = torch.randn(shard, device=dev)
+    p, m, v = p0.clone(), torch.zeros(shard, device=dev), torch.zeros(shard, device=dev)
+    lp = torch.empty(shard, dtype=torch.bfloat16, device=dev)
+    ref_p = torch.nn.Parameter(p0.clone())
+    cut = 40 * 1024
+    opt = torch.optim.AdamW([{"params": [ref_p], "lr": 1e-2, "betas": (0.9, 0.95), "eps": 1e-8, "weight_decay": 0.0}])
+    # reference with per-segment weight decay: emulate with two tensors
+    ra, rb = torch.nn.Parameter(p0[:cut].clone()), torch.nn.Parameter(p0[cut:].clone())
+    opt = torch.optim.AdamW([{"params": [ra], "weight_decay": 0.1}, {"params": [rb], "weight_decay": 0.0}], lr=1e-2,
+                            betas=(0.9, 0.95), eps=1e-8)
+    errs = []
+    for step in (1, 2):
+        torch.manual_seed(100 * step + rank)
+        g = torch.randn(n, device=dev).to(torch.bfloat16)
+        ctx.wait_rs_done(buf.last_rs_epoch)
+        buf.view(n, torch.bfloat16).copy_(g)
+        hyper = [[1e-2, 0.9, 0.95, 1e-8, wd, 1 - 0.9**step, 1 - 0.95**step, 1.0] for wd in (0.1, 0.0)]
+        _, grid = ctx.rs_adam(buf, torch.bfloat16, shard, 1.0 / world, p, m, v, lp, [0, cut, shard], hyper,
+                              want_sumsq=True)
+        gref = torch.empty(shard, device=dev)
+        dist.reduce_scatter_tensor(gref, g.float())
+        gref /= world
+        ra.grad, rb.grad = gref[:cut].clone(), gref[cut:].clone()
+        opt.step()
+        torch.cuda.synchronize()
+        want = torch.cat([ra.detach(), rb.detach()])
+        errs.append((p - want).abs().max().item())
+        errs.append((lp.float() - want.to(torch.bfloat16).float()).abs().max().item())
+        ss = ctx.partials[:grid].sum().item()
+        errs.append(abs(ss - gref.pow(2).sum().item()) / gref.pow(2).sum().item())
+    out["rs_adam"] = errs
+    # ---- (B) fp8 all-gather ----
+    block = 256
+    sh = 128 * 1024
+    torch.manual_seed(11 + rank)
+    mine = (torch.randn(sh, device=dev) * (1 + rank)).to(torch.bfloat16)
+    stage = ctx.alloc(ctx.fp8_stage_bytes(sh, block), want_multicast=False)
+    full = torch.empty(sh * world, dtype=torch.bfloat16, device=dev)
+    ok = True
+    for it in range(3):  # reuse of the staging buffer exercises the DONE wait
+        mine = mine * 1.5
+        ctx.all_gather_fp8(mine, stage, full, block)
+        q, s = fp8_block_quantize(mine, block)
+        qa = torch.empty(world * q.numel(), dtype=torch.uint8, device=dev)
+        sa = torch.empty(world * s.numel(), dtype=torch.float32, device=dev)
+        dist.all_gather_into_tensor(qa, q)
+        dist.all_gather_into_tensor(sa, s)
+        ref = fp8_block_dequantize(qa, sa, torch.bfloat16, block)
+        torch.cuda.synchronize()
+        ok = ok and bool(torch.equal(full, ref.view(-1)))
+    out["ag_fp8"] = ok
+    rel = ((full[rank * sh:(rank + 1) * sh].float() - mine.float()).abs().max() / mine.float().abs().max()).item()
+    out["ag_fp8_relerr"] = rel
+    dist.barrier()
+    return out
+
+
+@needs2
+def test_fused_rs_adam_and_fp8_all_gather():
+    world = min(2, _ngpu())
+    outs = run_distributed(_fused_v2, world, args=(world, ))
+    for o in outs:
+        assert o["ag_fp8"], o
+        assert o["ag_fp8_relerr"] < 0.07, o
+        e = o["rs_adam"]
+        assert max(e[0], e[3]) < 2e-5, o      # fp32 master vs torch AdamW
+        assert max(e[1], e[4]) < 1e-2, o      # bf16 copy
+        assert max(e[2], e[5]) < 1e-4, o      # fused sum of squares
