@@ -15,7 +15,6 @@ import deepspeed_b200 as _impl
 
 _ALIASES = {
     "deepspeed.runtime.fp16.loss_scaler": "deepspeed_b200.runtime.loss_scaler",
-    "deepspeed.runtime.fp16": "deepspeed_b200.runtime",
     "deepspeed.runtime.config": "deepspeed_b200.config.config",
     "deepspeed.runtime.config_utils": "deepspeed_b200.config.base",
     "deepspeed.runtime.zero.config": "deepspeed_b200.config.sections",

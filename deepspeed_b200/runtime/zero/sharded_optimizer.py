@@ -520,7 +520,9 @@ class ZeroShardedOptimizer:
         u.reduced_this_pass = True
         self._zero_unwritten(u)
         full = u.full_grad
-        div = self._grad_divisor(u)
+        # 1-bit optimizers past their warm-up keep gradients local (they all-reduce a compressed momentum instead)
+        local_only = getattr(self.optimizer, "compression_active", False) and not self.partition_optimizer
+        div = 1.0 if local_only else self._grad_divisor(u)
         first = not getattr(u, "_shard_has_data", False)
         stream_ctx = None
         if self._use_streams and self.overlap_comm:
@@ -562,7 +564,8 @@ class ZeroShardedOptimizer:
             dist.reduce_scatter_tensor(out, full, group=u.dp_group)
         else:
             out = full
-        if u.replica_world > 1:
+        if u.replica_world > 1 and not (getattr(self.optimizer, "compression_active", False)
+                                        and not self.partition_optimizer):
             dist.all_reduce(out, group=u.replica_group)
         if first:
             if post != 1.0:
@@ -727,10 +730,48 @@ class ZeroShardedOptimizer:
                 combined = clip * scale
         inv = 1.0 / combined
 
+        if getattr(self.optimizer, "needs_full_matrix_update", False):
+            self._apply_muon(inv)
         self._inner_step(inv)
         self._sync_lp_from_master()
         self._zero_grad_shards()
         self._post_step_gather()
+
+    @torch.no_grad()
+    def _apply_muon(self, grad_scale):
+        """Muon under ZeRO: the orthogonalised update needs whole matrices, the shards hold flat slices. Gather the
+        reduced gradient of every unit that has muon parameters, run momentum + Newton-Schulz on the matrices that
+        overlap my shard (their momentum lives here as full matrices) and write my slice of the update back into the
+        gradient shard; the inner optimizer then only applies ``p -= lr * (update + wd * p)``
+        (reference stage_1_and_2.py:2138-2160)."""
+        from ...ops.muon import muon_update
+        opt = self.optimizer
+        opt.zero_mode = True
+        mom = self.__dict__.setdefault("_muon_momentum", {})
+        ngroups = len(opt.param_groups)
+        for u in self.units:
+            ids = [i for i, gi in enumerate(u.param_group_ids)
+                   if gi < ngroups and opt.param_groups[gi].get("use_muon", False)]
+            if not ids:
+                continue
+            full = self._gather_shard_tensor(u, u.grad_shard)
+            s, e = u.shard_range()
+            for i in ids:
+                o, n = u.offsets[i], u.numels[i]
+                lo, hi = max(o, s), min(o + n, e)
+                if lo >= hi:
+                    continue
+                group = opt.param_groups[u.param_group_ids[i]]
+                g = full[o:o + n].view(u.shapes[i]).float()
+                if grad_scale != 1.0:
+                    g = g * grad_scale
+                buf = mom.get(u.names[i])
+                if buf is None:
+                    buf = mom[u.names[i]] = torch.zeros_like(g)
+                upd = muon_update(g, buf, beta=group["momentum"], ns_method=group["ns_method"],
+                                  is_expert_group=(g.ndim == 3)).reshape(-1)
+                piece = upd[lo - o:hi - o]
+                u.grad_shard[lo - s:hi - s].copy_(piece / grad_scale if grad_scale != 1.0 else piece)
 
     def _inner_step(self, grad_scale):
         opt = self.optimizer
@@ -926,6 +967,8 @@ class ZeroShardedOptimizer:
             "param_groups": pg,
             UNIT_LAYOUT: self.layout_metadata(),
         }
+        if getattr(self, "_muon_momentum", None):
+            sd["muon_momentum"] = {k: v.detach().cpu() for k, v in self._muon_momentum.items()}
         return sd
 
     def layout_metadata(self):
@@ -973,6 +1016,9 @@ class ZeroShardedOptimizer:
                     stt[k] = torch.tensor(float(val)) if k == "step" and _step_is_tensor(self.optimizer) else val
             if hasattr(self.optimizer, "on_state_loaded"):
                 self.optimizer.on_state_loaded()
+            if "muon_momentum" in sd:
+                dev = self.units[0].device
+                self._muon_momentum = {k: v.to(dev) for k, v in sd["muon_momentum"].items()}
 
     def refresh_lp_from_params(self):
         """After module weights were loaded directly into the lp params: rebuild master shards."""
