@@ -117,6 +117,8 @@ def _zero_optimizer_state(engine):
         for k, v in stt.items():
             if torch.is_tensor(v) and v.numel() > 1:
                 state_keys.add(k)
+    if getattr(z, "_nvme", None) is not None:  # moments swapped out to NVMe are not in optimizer.state
+        state_keys.update(z._nvme_names)
     exported = {k: lay.export(lambda u, k=k: z._state_shard(u, k)) for k in sorted(state_keys)}
     # per-group scalar state (step)
     base_state = {}

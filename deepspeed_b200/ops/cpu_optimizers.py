@@ -52,13 +52,15 @@ class _CPUOptimizer(torch.optim.Optimizer):
         return loss
 
     @torch.no_grad()
-    def step_flat(self, grads, lp_params=None, grad_scale=1.0):
+    def step_flat(self, grads, lp_params=None, grad_scale=1.0, advance_step=True):
+        """``advance_step=False``: a further slice of the same optimizer step (sub-group stepping for NVMe swapping)."""
         lp_params = lp_params or {}
         for group in self.param_groups:
             used = [p for p in group["params"] if p in grads]
             if not used:
                 continue
-            group["step"] = group.get("step", 0) + 1
+            if advance_step or "step" not in group:
+                group["step"] = group.get("step", 0) + 1
             for p in used:
                 assert p.device.type == "cpu" and p.dtype == torch.float32 and p.is_contiguous(), \
                     "CPU optimizers operate on contiguous fp32 host tensors"

@@ -71,7 +71,7 @@ class ZeroShardedOptimizer:
                  unit_max_numel=int(1e9), param_persistence_threshold=int(1e5), prefetch=True, mics_shard_size=-1,
                  hpz_size=1, quantized_weights=False, quantized_gradients=False, expert_groups=None,
                  leaf_modules=(), elastic_checkpoint=False, timers=None, fused_collectives=None,
-                 ignore_unused_parameters=True, fused_rs_adam=None):
+                 ignore_unused_parameters=True, fused_rs_adam=None, aio_config=None):
         self.module = module
         self.optimizer = optimizer
         self.stage = int(stage)
@@ -94,6 +94,9 @@ class ZeroShardedOptimizer:
         self.ignore_unused_parameters = ignore_unused_parameters
         self.offload_optimizer = bool(offload_optimizer and str(getattr(offload_optimizer, "device", "none")) != "none")
         self.offload_cfg = offload_optimizer
+        self.offload_nvme = self.offload_optimizer and "nvme" in str(getattr(offload_optimizer, "device", ""))
+        self._aio_config = aio_config
+        self._nvme = None
         self.offload_param_cfg = offload_param
         self.lp_dtype = dtype
         self.master_dtype = dtype if master_weights_in_lp else torch.float32
@@ -773,6 +776,80 @@ class ZeroShardedOptimizer:
                 piece = upd[lo - o:hi - o]
                 u.grad_shard[lo - s:hi - s].copy_(piece / grad_scale if grad_scale != 1.0 else piece)
 
+    # ------------------------------------------------------------------ NVMe (ZeRO-Infinity) ---
+    def _nvme_swapper(self):
+        """Optimizer moments live in per-unit swap files on ``offload_optimizer.nvme_path``; a pipelined swapper keeps
+        ``buffer_count`` unit state sets in pinned memory (reference stage3.py:2420-2507 + swap_tensor/*). The fp32
+        master shard stays in pinned host memory."""
+        if self._nvme is None:
+            from ..swap_tensor.pipelined_optimizer_swapper import PipelinedOptimizerSwapper
+            aio = self._aio_config
+            aio = dict(block_size=aio.block_size, queue_depth=aio.queue_depth, single_submit=aio.single_submit,
+                       overlap_events=aio.overlap_events, intra_op_parallelism=aio.intra_op_parallelism) \
+                if aio is not None and not isinstance(aio, dict) else (aio or dict(
+                    block_size=1048576, queue_depth=8, single_submit=False, overlap_events=True,
+                    intra_op_parallelism=1))
+            assert getattr(self.optimizer, "supports_flat_step", False), \
+                "NVMe offload needs a DeepSpeedCPU* optimizer (sub-group stepping)"
+            names = tuple(self.optimizer._state_names())
+            self._nvme_names = names
+            largest = max(u.shard_numel for u in self.units)
+            count = max(3, int(getattr(self.offload_cfg, "buffer_count", 4)))
+            self._nvme = PipelinedOptimizerSwapper(self.offload_cfg, aio, self.offload_cfg.nvme_path, largest,
+                                                   len(names), torch.float32, sets_in_flight=count)
+            for u in self.units:
+                self._nvme.register(f"unit{u.uid}", u.shard_numel)
+        return self._nvme
+
+    def _inner_step_nvme(self, grad_scale):
+        sw = self._nvme_swapper()
+        opt = self.optimizer
+        by_unit = OrderedDict()
+        for seg in self._segments:
+            by_unit.setdefault(seg[4].uid, []).append(seg)
+        # moments put into optimizer.state from outside (checkpoint load) are adopted into the swap files first
+        for uid, segs in by_unit.items():
+            if any(n in opt.state.get(seg[5], {}) for seg in segs for n in self._nvme_names):
+                bufs = sw.acquire(f"unit{uid}")
+                for (skey, a, b, gi, u, v) in segs:
+                    off = a - u.shard_offset
+                    for name, buf in zip(self._nvme_names, bufs):
+                        t = opt.state[v].pop(name, None)
+                        if t is not None:
+                            buf[off:off + (b - a)].copy_(t.view(-1))
+                sw.release(f"unit{uid}", dirty=True)
+        order = list(by_unit)
+        if order:
+            sw.prefetch(f"unit{order[0]}")
+        for idx, uid in enumerate(order):
+            key = f"unit{uid}"
+            bufs = sw.acquire(key)
+            if idx + 1 < len(order):
+                sw.prefetch(f"unit{order[idx + 1]}")  # overlaps this unit's CPU optimizer step
+            grads, lp_map = {}, {}
+            for (skey, a, b, gi, u, v) in by_unit[uid]:
+                st = self.storages[skey]
+                off = a - u.shard_offset
+                stt = opt.state[v]
+                stt.setdefault("step", 0)
+                for name, buf in zip(self._nvme_names, bufs):
+                    stt[name] = buf[off:off + (b - a)]
+                grads[v] = st.grad_host[a:b]
+                lp_map[v] = st.lp_host[a:b]
+            opt.step_flat(grads=grads, lp_params=lp_map, grad_scale=grad_scale, advance_step=(idx == 0))
+            sw.release(key, dirty=True)
+        sw.flush()
+        for (skey, a, b, gi, u, v) in self._segments:  # nothing may keep pointing into recycled swap buffers
+            for name in self._nvme_names:
+                opt.state[v].pop(name, None)
+        for key, st in self.storages.items():
+            if self.partition_params:
+                st.lp.copy_(st.lp_host, non_blocking=True)
+            else:
+                for u in st.units:
+                    u.param_shard.copy_(st.lp_host[u.shard_offset:u.shard_offset + u.shard_numel], non_blocking=True)
+        self._lp_written_by_step = True
+
     def _inner_step(self, grad_scale):
         opt = self.optimizer
         fused = getattr(opt, "supports_flat_step", False) and not self.offload_optimizer
@@ -782,6 +859,8 @@ class ZeroShardedOptimizer:
                     st.grad_host.copy_(st.grad.float(), non_blocking=True)
             if torch.cuda.is_available():
                 torch.cuda.current_stream().synchronize()
+        if self.offload_nvme:
+            return self._inner_step_nvme(grad_scale)
         if fused:
             lp_map, grads = {}, {}
             for (key, a, b, gi, u, v) in self._segments:
@@ -920,6 +999,8 @@ class ZeroShardedOptimizer:
 
     def _state_shard(self, u, key):
         """Assemble the optimizer-state shard of a unit from the per-run views held by the inner optimizer."""
+        if self._nvme is not None and key in self._nvme_names:
+            return self._nvme.read_all(f"unit{u.uid}")[self._nvme_names.index(key)]
         out = torch.zeros(u.shard_numel, dtype=torch.float32, device=u.master_shard.device)
         found = False
         for (skey, a, b, gi, uu, v) in self._segments:
@@ -945,6 +1026,13 @@ class ZeroShardedOptimizer:
                     flat[a:b].copy_(val.view(-1))
                 else:
                     scalars.setdefault(gi, {})[k] = val.item() if torch.is_tensor(val) else val
+        if self._nvme is not None:  # moments are on NVMe: read every unit's state set back
+            for u in self.units:
+                st = self.storages[(u.group_key, u.dtype)]
+                for name, t in zip(self._nvme_names, self._nvme.read_all(f"unit{u.uid}")):
+                    flat = tens.setdefault(name, {}).setdefault(
+                        _skey_str((u.group_key, u.dtype)), torch.zeros(st.numel, dtype=torch.float32))
+                    flat[u.shard_offset:u.shard_offset + u.shard_numel].copy_(t)
         return tens, scalars
 
     def state_dict(self):
@@ -1003,6 +1091,13 @@ class ZeroShardedOptimizer:
             for g, saved in zip(self.optimizer.param_groups, sd.get("param_groups", [])):
                 g.update(saved)
             tens, scalars = sd.get("state_flat", {}), sd.get("state_scalars", {})
+            if self.offload_nvme and tens:
+                sw = self._nvme_swapper()
+                for u in self.units:
+                    sk = _skey_str((u.group_key, u.dtype))
+                    a, b = u.shard_offset, u.shard_offset + u.shard_numel
+                    sw.write_all(f"unit{u.uid}", [tens[n][sk][a:b].float() for n in self._nvme_names])
+                tens = {}
             for (skey, a, b, gi, u, v) in self._segments:
                 stt = self.optimizer.state[v]
                 for k, d in tens.items():
