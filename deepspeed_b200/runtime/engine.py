@@ -294,7 +294,7 @@ class DeepSpeedEngine(Module):
             quantized_weights=zc.zero_quantized_weights, quantized_gradients=zc.zero_quantized_gradients,
             leaf_modules=self._leaf_module_classes(), elastic_checkpoint=zc.elastic_checkpoint, timers=self.timers,
             fused_collectives=fused, ignore_unused_parameters=zc.ignore_unused_parameters,
-            fused_rs_adam=zc.fused_rs_adam, aio_config=self._config.aio_config)
+            fused_rs_adam=zc.fused_rs_adam, aio_config=self._config.aio_config, zenflow=zc.zenflow)
 
     def _configure_zero_inference(self, model_parameters):
         dummy = torch.optim.SGD([p for p in self.module.parameters()], lr=0.0)

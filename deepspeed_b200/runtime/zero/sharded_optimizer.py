@@ -71,7 +71,7 @@ class ZeroShardedOptimizer:
                  unit_max_numel=int(1e9), param_persistence_threshold=int(1e5), prefetch=True, mics_shard_size=-1,
                  hpz_size=1, quantized_weights=False, quantized_gradients=False, expert_groups=None,
                  leaf_modules=(), elastic_checkpoint=False, timers=None, fused_collectives=None,
-                 ignore_unused_parameters=True, fused_rs_adam=None, aio_config=None):
+                 ignore_unused_parameters=True, fused_rs_adam=None, aio_config=None, zenflow=None):
         self.module = module
         self.optimizer = optimizer
         self.stage = int(stage)
@@ -192,6 +192,23 @@ class ZeroShardedOptimizer:
                     self.symm, self._grad_pool = None, None
         self._allocate_and_link()
         self._setup_fused_rs_adam(fused_rs_adam)
+        self._zenflow = None
+        if zenflow is not None and self.offload_optimizer and not self.offload_nvme:
+            from ..zenflow.zenflow_utils import ZenFlowController
+            self._zenflow = ZenFlowController(self, zenflow)
+            log_dist(f"ZenFlow: top-{zenflow.topk_ratio:.0%} of the shard updated on GPU every step, CPU update every "
+                     f"{self._zenflow.update_interval} steps (overlap={self._zenflow.overlap_step})", [0])
+        self._super = None
+        if self.offload_optimizer and not self.offload_nvme and getattr(self.offload_cfg, "super_offload", False) \
+                and self._zenflow is None and self.gas == 1 and self.lp_dtype != torch.float16 \
+                and hasattr(self.optimizer, "rollback"):
+            from ..superoffload.superoffload_utils import SuperOffloadCPUOptimizer
+            self._super = SuperOffloadCPUOptimizer(self.optimizer,
+                                                   getattr(self.offload_cfg, "cpuadam_cores_perc", 0.8))
+            self._segs_of_unit = {}
+            for seg in self._segments:
+                self._segs_of_unit.setdefault(seg[4].uid, []).append(seg)
+            log_dist("SuperOffload: speculative CPU optimizer steps overlap the backward pass", [0])
         self._register_grad_hooks()
         self.coordinator = None
         if self.partition_params:
@@ -545,6 +562,8 @@ class ZeroShardedOptimizer:
             else:
                 self._reduce_unit_nccl(u, full, div, first)
             u._shard_has_data = True
+            if self._super is not None and first:
+                self._speculate_unit(u)
         finally:
             if stream_ctx is not None:
                 stream_ctx.__exit__(None, None, None)
@@ -733,6 +752,17 @@ class ZeroShardedOptimizer:
                 combined = clip * scale
         inv = 1.0 / combined
 
+        if self._super is not None and self._super.speculated:
+            self._finish_super_step(inv, skip=False)
+            self._sync_lp_from_master()
+            self._zero_grad_shards()
+            self._post_step_gather()
+            return
+        if self._zenflow is not None:
+            self._zenflow.step(inv)
+            self._zero_grad_shards()
+            self._post_step_gather()
+            return
         if getattr(self.optimizer, "needs_full_matrix_update", False):
             self._apply_muon(inv)
         self._inner_step(inv)
@@ -775,6 +805,40 @@ class ZeroShardedOptimizer:
                                   is_expert_group=(g.ndim == 3)).reshape(-1)
                 piece = upd[lo - o:hi - o]
                 u.grad_shard[lo - s:hi - s].copy_(piece / grad_scale if grad_scale != 1.0 else piece)
+
+    # ------------------------------------------------------------------ SuperOffload -----------
+    def _speculate_unit(self, u):
+        """Right after a unit's reduce-scatter (same stream): copy its gradient shard to pinned host memory and let the
+        CPU worker apply the optimizer to it while the backward pass continues (assumes no clipping will be needed)."""
+        st = self.storages[(u.group_key, u.dtype)]
+        a, b = u.shard_offset, u.shard_offset + u.shard_numel
+        if st.grad.dtype == torch.float32:
+            st.grad_host[a:b].copy_(st.grad[a:b], non_blocking=True)
+        else:
+            st.grad_host[a:b].copy_(st.grad[a:b].float(), non_blocking=True)
+        event = None
+        if torch.cuda.is_available() and st.grad.is_cuda:
+            event = torch.cuda.Event()
+            event.record(torch.cuda.current_stream())
+        grads, lp = {}, {}
+        for (key, sa, sb, gi, uu, v) in self._segs_of_unit.get(u.uid, []):
+            grads[v] = st.grad_host[sa:sb]
+            lp[v] = st.lp_host[sa:sb]
+        if grads:
+            self._super.async_step(grads, lp, event, 1.0)
+
+    def _finish_super_step(self, inv, skip):
+        if skip or inv != 1.0:
+            self._super.rollback_and_redo(inv, skip=skip)  # the speculation was wrong: undo, redo with the real scale
+        else:
+            self._super.commit()
+        for key, st in self.storages.items():
+            if self.partition_params:
+                st.lp.copy_(st.lp_host, non_blocking=True)
+            else:
+                for u in st.units:
+                    u.param_shard.copy_(st.lp_host[u.shard_offset:u.shard_offset + u.shard_numel], non_blocking=True)
+        self._lp_written_by_step = True
 
     # ------------------------------------------------------------------ NVMe (ZeRO-Infinity) ---
     def _nvme_swapper(self):
