@@ -201,6 +201,15 @@ def main(args=None):
         active = collections.OrderedDict(list(active.items())[:args.num_nodes])
     if args.num_gpus > 0:
         active = collections.OrderedDict((h, list(range(args.num_gpus))) for h in active)
+    if args.autotuning:
+        # `deepspeed --autotuning tune|run script.py --deepspeed_config ds.json` (reference runner.py:run_autotuning)
+        from ..autotuning import Autotuner
+        tuner = Autotuner(args, active)
+        tuner.tune()
+        tuner.print_tuning_results()
+        if args.autotuning == "run":
+            tuner.run_after_tuning()
+        return
     multi_node = args.force_multi or len(active) > 1
     if not args.master_addr:
         first = list(active.keys())[0]

@@ -818,6 +818,48 @@ class DeepSpeedEngine(Module):
             self._report_progress(self.global_steps + 1)
         self.global_steps += 1
         self.global_samples += self.train_batch_size()
+        if self._config.autotuning_config.get("enabled", False):
+            self._autotuning_step()
+
+    # ------------------------------------------------------------------ autotuning -------------
+    def autotuning_enabled(self):
+        return bool(self._config.autotuning_config.get("enabled", False))
+
+    def _autotuning_step(self):
+        """Experiment mode of the autotuner (reference engine.py:1122-1170, 2812-2850): time the steps between
+        ``start_profile_step`` and ``end_profile_step``, write the metric file (and model info) and exit."""
+        import json
+        import sys
+        import time
+        ac = self._config.autotuning_config
+        start, end = int(ac.get("start_profile_step", 3)), int(ac.get("end_profile_step", 5))
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+        if self.global_steps == start:
+            self._autotuning_t0 = time.time()
+        if self.global_steps < end:
+            return
+        steps = max(1, end - start)
+        latency = (time.time() - getattr(self, "_autotuning_t0", time.time())) / steps
+        n_params = sum(getattr(p, "ds_numel", p.numel()) for p in self.module.parameters())
+        metrics = {"latency": latency * 1e3, "throughput": self.train_batch_size() / max(latency, 1e-9),
+                   "flops": 0.0, "num_params": n_params}
+        if self.flops_profiler is not None and getattr(self.flops_profiler, "total_flops", None):
+            metrics["flops"] = float(self.flops_profiler.total_flops) / max(latency, 1e-9)
+        if self.global_rank == 0:
+            path = ac.get("metric_path") or os.path.join(os.getcwd(), "autotuning_metric.json")
+            with open(path, "w") as f:
+                json.dump(metrics, f)
+            if (ac.get("model_info") or {}).get("profile", False) or ac.get("model_info_path"):
+                info = {"num_params": n_params, "trainable_num_params": sum(
+                    getattr(p, "ds_numel", p.numel()) for p in self.module.parameters() if p.requires_grad),
+                    "activation_mem_per_gpu": int(torch.cuda.max_memory_allocated()) if torch.cuda.is_available() else 0}
+                with open(ac.get("model_info_path") or os.path.join(os.getcwd(), "autotuning_model_info.json"),
+                          "w") as f:
+                    json.dump(info, f)
+        dist.barrier()
+        log_dist("autotuning: metrics written, exiting the experiment", [0])
+        sys.exit(0)
 
     @instrument_w_nvtx
     def step(self, lr_kwargs=None):
