@@ -23,7 +23,9 @@ from ..utils.logging import log_dist, logger
 from . import comm as dist
 
 CH_RS_READY, CH_RS_DONE, CH_AG_READY, CH_AG_DONE, CH_A2A_READY, CH_A2A_DONE, CH_USER = 0, 1, 2, 3, 4, 5, 6
-CH_QAG_READY, CH_QAG_DONE, CH_GEMM_READY, CH_GEMM_DONE = 7, 8, 9, 10
+CH_QAG_READY, CH_QAG_DONE, CH_GIN_READY, CH_GIN_DONE = 7, 8, 9, 10
+CH_GA2A_READY, CH_GA2A_DONE, CH_GRS_READY, CH_GRS_DONE = 11, 12, 13, 14
+GEMM_AG_A, GEMM_AG_B, GEMM_SCATTER_N, GEMM_RS_M = 1, 2, 4, 8
 _CONTEXTS = {}
 
 
@@ -42,6 +44,8 @@ def _declare(L):
     L.dsb200_symm_fp8_stage_bytes.restype = L64
     L.dsb200_symm_all_gather_fp8.argtypes = [P, I, P, P, I, I, L64, I, P, P, I, I, U, U, I, P]
     L.dsb200_symm_all_gather_fp8.restype = I
+    L.dsb200_gemm_comm_bf16_nt.argtypes = [I, P, P, P, P, P, I, I, I, L64, L64, L64, P, I, I, I, I, I, I, U, U, P, I, P]
+    L.dsb200_gemm_comm_bf16_nt.restype = I
     L.dsb200_symm_wait.argtypes = [P, I, I, I, U, P]
     L.dsb200_symm_wait.restype = I
     L.dsb200_symm_signal.argtypes = [P, I, I, I, U, P]
@@ -189,6 +193,94 @@ class SymmContext:
         K._LAUNCHES += 1
         stage.last_qag_epoch = ep
         return ep
+
+    # ---- tcgen05 GEMM fused with a collective (csrc/gemm_comm.cu) -------------------------------------
+    def _signal(self, channel, epoch):
+        self.lib.dsb200_symm_signal(self.flags.ptrs, self.rank, self.world, channel, epoch, self._stream())
+        K._LAUNCHES += 1
+
+    def _wait(self, channel, epoch):
+        if epoch > 0:
+            self.lib.dsb200_symm_wait(self.flags.ptrs, self.rank, self.world, channel, epoch, self._stream())
+            K._LAUNCHES += 1
+
+    def _gemm_comm(self, mode, a_ptrs, b_ptrs, out, c_ptrs, rs_out, M, N, Kd, lda, ldb, ldc, chans, epoch, reuse,
+                   max_ctas=0):
+        null = ctypes.c_void_p(0)
+        bn = self.lib.dsb200_gemm_comm_bf16_nt(
+            mode, a_ptrs, b_ptrs, ctypes.c_void_p(out.data_ptr()) if out is not None else null,
+            c_ptrs if c_ptrs is not None else null, ctypes.c_void_p(rs_out.data_ptr()) if rs_out is not None else null,
+            M, N, Kd, lda, ldb, ldc, self.flags.ptrs, self.rank, self.world, chans[0], chans[1], chans[2], chans[3],
+            epoch, reuse, ctypes.c_void_p(self.tickets.data_ptr() + 32), max_ctas, self._stream())
+        if bn < 0:
+            raise RuntimeError(f"gemm_comm failed: {K.last_error()}")
+        K._LAUNCHES += 1
+        return bn
+
+    @staticmethod
+    def _one(t):
+        return (ctypes.c_uint64 * 16)(*([t.data_ptr()] + [0] * 15))
+
+    def all_gather_gemm(self, x, w_buf: SymmBuffer, n_total, out=None, gathered="b", max_ctas=0):
+        """Fused path 2. ``gathered="b"``: ``out[M, n_total] = x[M, K] @ W^T`` where rank p holds rows
+        ``[p*n_total/world, ...)`` of ``W`` in ``w_buf`` - the ZeRO-3 weight all-gather happens tile by tile inside the
+        GEMM. ``gathered="a"``: ``out[m_total, N] = X @ w^T`` with the rows of ``X`` spread over the ranks' ``w_buf``
+        (sequence-parallel input of an AutoTP column-parallel linear); then ``x`` is the local weight [N, K]."""
+        Kd = x.shape[1]
+        ep = self._next(CH_GIN_READY)
+        self._signal(CH_GIN_READY, ep)  # stream order: my shard is final before peers may read it
+        if gathered == "b":
+            M, N = x.shape[0], n_total
+            a_ptrs, b_ptrs, mode = self._one(x), w_buf.ptrs, GEMM_AG_B
+        else:
+            M, N = n_total, x.shape[0]
+            a_ptrs, b_ptrs, mode = w_buf.ptrs, self._one(x), GEMM_AG_A
+        if out is None:
+            out = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+        self._gemm_comm(mode, a_ptrs, b_ptrs, out, None, None, M, N, Kd, Kd if gathered == "a" else x.stride(0),
+                        Kd if gathered == "b" else x.stride(0), out.stride(0),
+                        (CH_GIN_READY, CH_GIN_DONE, 0, 0), ep, 0, max_ctas)
+        w_buf.last_gin_epoch = ep
+        return out
+
+    def wait_gemm_readers(self, buf: SymmBuffer):
+        """Before overwriting a shard that fused GEMMs read: wait until every peer's kernel finished reading it."""
+        self._wait(CH_GIN_DONE, getattr(buf, "last_gin_epoch", 0))
+
+    def gemm_all_to_all(self, x, w, out_buf: SymmBuffer, max_ctas=0):
+        """Fused path 4. ``Y = x[M, K] @ w[N, K]^T`` with column block j of ``Y`` delivered to rank j: afterwards
+        ``out_buf`` on every rank holds ``[world * M, N / world]`` (rows ordered by source rank) - the Ulysses
+        sequence-sharded -> head-sharded re-layout done by the GEMM epilogue. Call :meth:`release_a2a_out` once the
+        consumer has read ``out_buf``."""
+        M, Kd = x.shape
+        N = w.shape[0]
+        ep = self._next(CH_GA2A_READY)
+        self._gemm_comm(GEMM_SCATTER_N, self._one(x), self._one(w), None, out_buf.ptrs, None, M, N, Kd, x.stride(0),
+                        w.stride(0), N // self.world, (0, 0, CH_GA2A_READY, CH_GA2A_DONE), ep,
+                        getattr(out_buf, "last_ga2a_done", 0), max_ctas)
+        out_buf.last_ga2a_epoch = ep
+        return out_buf.view(self.world * M * (N // self.world), torch.bfloat16).view(self.world * M, N // self.world)
+
+    def release_a2a_out(self, out_buf: SymmBuffer):
+        ep = getattr(out_buf, "last_ga2a_epoch", 0)
+        if ep:
+            self._signal(CH_GA2A_DONE, ep)
+            out_buf.last_ga2a_done = ep
+
+    def gemm_reduce_scatter(self, x, w, stage_buf: SymmBuffer, out=None, max_ctas=0):
+        """Fused AutoTP row-parallel linear: every rank computes the partial ``x[M, K_local] @ w[N, K_local]^T``;
+        row block j goes to rank j's staging slot while the GEMM runs, then each rank sums its ``world`` slots:
+        ``out[M / world, N] = sum_p partial_p[rank rows]``. ``stage_buf`` needs ``M * N * 2`` bytes."""
+        M, Kd = x.shape
+        N = w.shape[0]
+        if out is None:
+            out = torch.empty((M // self.world, N), dtype=torch.bfloat16, device=x.device)
+        ep = self._next(CH_GRS_READY)
+        self._gemm_comm(GEMM_RS_M, self._one(x), self._one(w), None, stage_buf.ptrs, out, M, N, Kd, x.stride(0),
+                        w.stride(0), out.stride(0), (0, 0, CH_GRS_READY, CH_GRS_DONE), ep,
+                        getattr(stage_buf, "last_grs_epoch", 0), max_ctas)
+        stage_buf.last_grs_epoch = ep
+        return out
 
     def wait_rs_done(self, epoch):
         """Enqueue (current stream) a wait until every peer finished reading my buffer in RS ``epoch``."""

@@ -226,3 +226,69 @@ def test_fused_rs_adam_and_fp8_all_gather():
         assert max(e[0], e[3]) < 2e-5, o      # fp32 master vs torch AdamW
         assert max(e[1], e[4]) < 1e-2, o      # bf16 copy
         assert max(e[2], e[5]) < 1e-4, o      # fused sum of squares
+
+
+def _gemm_comm(world):
+    """tcgen05 GEMM fused with all-gather (A or B), all-to-all scatter and reduce-scatter vs NCCL + torch.matmul."""
+    import torch.distributed as dist
+    from deepspeed_b200.comm import symm
+    rank = dist.get_rank()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    ctx = symm.SymmContext.get(dist.group.WORLD)
+    out = {}
+    M, N, Kd = 512, 1024, 768
+    g = torch.Generator(device="cpu").manual_seed(3)
+    Wfull = (torch.randn(N, Kd, generator=g) * 0.05).to(torch.bfloat16).to(dev)
+    Xfull = torch.randn(world * M, Kd, generator=g).to(torch.bfloat16).to(dev)
+    x = Xfull[rank * M:(rank + 1) * M].contiguous()
+
+    def rel(a, b):
+        return ((a.float() - b.float()).abs().max() / b.float().abs().max()).item()
+
+    # ---- AG_B: weight rows sharded over ranks ----
+    nb = N // world
+    wbuf = ctx.alloc(nb * Kd * 2, want_multicast=False)
+    wbuf.view(nb * Kd, torch.bfloat16).copy_(Wfull[rank * nb:(rank + 1) * nb].reshape(-1))
+    for it in range(2):
+        y = ctx.all_gather_gemm(x, wbuf, N, gathered="b")
+        torch.cuda.synchronize()
+        out[f"ag_b{it}"] = rel(y, x.float() @ Wfull.float().t())
+    # ---- AG_A: activation rows sharded over ranks ----
+    abuf = ctx.alloc(M * Kd * 2, want_multicast=False)
+    abuf.view(M * Kd, torch.bfloat16).copy_(x.reshape(-1))
+    y = ctx.all_gather_gemm(Wfull, abuf, world * M, gathered="a")
+    torch.cuda.synchronize()
+    out["ag_a"] = rel(y, Xfull.float() @ Wfull.float().t())
+    # ---- SCATTER_N: GEMM -> all-to-all ----
+    obuf = ctx.alloc(world * M * (N // world) * 2, want_multicast=False)
+    for it in range(2):
+        xi = (x * (it + 1)).contiguous()
+        got = ctx.gemm_all_to_all(xi, Wfull, obuf)
+        torch.cuda.synchronize()
+        full = (Xfull.float() * (it + 1)) @ Wfull.float().t()           # [world*M, N]
+        want = full[:, rank * (N // world):(rank + 1) * (N // world)]    # my column block from every source rank
+        out[f"a2a{it}"] = rel(got, want)
+        ctx.release_a2a_out(obuf)
+    # ---- RS_M: GEMM -> reduce-scatter ----
+    sbuf = ctx.alloc(M * N * 2, want_multicast=False)
+    torch.manual_seed(50 + rank)
+    xp = torch.randn(M, Kd, device=dev).to(torch.bfloat16)
+    wp = (torch.randn(N, Kd, device=dev) * 0.05).to(torch.bfloat16)
+    for it in range(2):
+        got = ctx.gemm_reduce_scatter(xp, wp, sbuf)
+        partial = (xp.float() @ wp.float().t())
+        ref = torch.empty(M // world, N, device=dev)
+        dist.reduce_scatter_tensor(ref, partial)
+        torch.cuda.synchronize()
+        out[f"rs{it}"] = rel(got, ref)
+    dist.barrier()
+    return out
+
+
+@needs2
+def test_gemm_fused_with_collectives():
+    world = min(2, _ngpu())
+    outs = run_distributed(_gemm_comm, world, args=(world, ))
+    for o in outs:
+        for k, v in o.items():
+            assert v < 2e-2, o
