@@ -25,7 +25,7 @@
 
 namespace {
 
-enum { MODE_AG_A = 1, MODE_AG_B = 2, MODE_SCATTER_N = 4, MODE_RS_M = 8 };
+enum { MODE_AG_A = 1, MODE_AG_B = 2, MODE_SCATTER_N = 4, MODE_RS_M = 8, MODE_REUSE_FULL = 16 };
 
 struct MapTable {
     CUtensorMap m[MAX_WORLD];
@@ -42,12 +42,108 @@ struct CommArgs {
     unsigned int* tickets;  // 3 zero-initialised local words
     __nv_bfloat16* rs_out;  // RS_M result [M/world, N]
     int64_t rs_ld;
+    // gathered operand (AG_A / AG_B): `n_copy` CTAs pull the peers' shards ONCE over NVLink into the local buffer
+    // `g_full` with bulk async copies and publish per-chunk flags; the GEMM CTAs read chunks from `g_full`
+    int n_copy;
+    uint32_t* chunk_flags;        // local, one word per tile-row block of the gathered operand, compared with `epoch`
+    const void* g_src[MAX_WORLD];  // peers' shard bases
+    uint8_t* g_full;              // local gathered operand [world * rows_per_peer, K]
+    int64_t chunk_bytes;          // bytes of one tile-row block (rows * K * 2)
+    int chunks_per_peer;
 };
 
 __device__ __forceinline__ void wait_flag(const PeerPtrs& flags, int rank, int channel, int peer, uint32_t epoch)
 {
     const uint32_t* f = reinterpret_cast<const uint32_t*>(flags.p[rank]) + channel * FLAG_STRIDE + peer;
     while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) { __nanosleep(64); }
+}
+
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)),
+                 "r"(bytes)
+                 : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* addr, uint32_t v)
+{
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* addr)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+    return v;
+}
+
+constexpr int COPY_PIECE = 32 * 1024;
+constexpr int COPY_STAGES = 5;
+
+// One elected thread of a copy CTA: remote shard -> smem ring -> local gathered buffer, chunk by chunk in the order
+// the GEMM CTAs consume them. All data movement is done by the TMA engines (bulk async copies), so COPY_STAGES x 32 KB
+// per CTA are in flight over NVLink without occupying registers or issue slots.
+__device__ void copy_role(const CommArgs& ca, uint8_t* smem, uint64_t* bars, int copy_id, int n_chunks, int rot)
+{
+    const int rank = ca.rank;
+    uint32_t seen = 1u << rank;
+    uint32_t issued_in_stage[COPY_STAGES] = {0, 0, 0, 0, 0};
+    int list_pos = 0;
+    for (int i = 0; i < n_chunks; i++) {
+        const int chunk = (i + rot) % n_chunks;
+        const int peer = chunk / ca.chunks_per_peer;
+        if (peer == rank) continue;  // my own shard is read in place
+        if ((list_pos++ % ca.n_copy) != copy_id) continue;
+        if (!(seen >> peer & 1)) {
+            wait_flag(ca.flags, rank, ca.ch_in_ready, peer, ca.epoch);
+            seen |= 1u << peer;
+        }
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(ca.g_src[peer]) +
+                             (int64_t)(chunk - peer * ca.chunks_per_peer) * ca.chunk_bytes;
+        uint8_t* dst = ca.g_full + (int64_t)chunk * ca.chunk_bytes;
+        if (ca.mode & 64) {  // debug: data already in place, only publish the flag
+            __threadfence();
+            st_release_gpu(ca.chunk_flags + chunk, ca.epoch);
+            continue;
+        }
+        const int pieces = (int)((ca.chunk_bytes + COPY_PIECE - 1) / COPY_PIECE);
+        auto piece_bytes = [&](int q) {
+            const int64_t left = ca.chunk_bytes - (int64_t)q * COPY_PIECE;
+            return (uint32_t)(left < COPY_PIECE ? left : COPY_PIECE);
+        };
+        auto load = [&](int q) {
+            const int st = q % COPY_STAGES;
+            mbar_expect_tx(&bars[st], piece_bytes(q));
+            bulk_g2s(smem + st * COPY_PIECE, src + (int64_t)q * COPY_PIECE, piece_bytes(q), &bars[st]);
+        };
+        for (int q = 0; q < pieces && q < COPY_STAGES; q++) load(q);
+        for (int q = 0; q < pieces; q++) {
+            const int st = q % COPY_STAGES;
+            mbar_wait(&bars[st], issued_in_stage[st] & 1);
+            issued_in_stage[st]++;
+            if (ca.mode & 32) {  // debug: generic-proxy copy out of shared memory instead of the bulk store
+                const uint4* sp = reinterpret_cast<const uint4*>(smem + st * COPY_PIECE);
+                uint4* gp = reinterpret_cast<uint4*>(dst + (int64_t)q * COPY_PIECE);
+                for (uint32_t b = 0; b < piece_bytes(q) / 16; b++) gp[b] = sp[b];
+            } else {
+                bulk_s2g(dst + (int64_t)q * COPY_PIECE, smem + st * COPY_PIECE, piece_bytes(q));
+            }
+            if (q + COPY_STAGES < pieces) {
+                asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // smem stage free again
+                load(q + COPY_STAGES);
+            }
+        }
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // chunk completely written
+        asm volatile("fence.proxy.async;" ::: "memory");
+        __threadfence();
+        st_release_gpu(ca.chunk_flags + chunk, ca.epoch);
+    }
 }
 
 template <int BLOCK_N>
@@ -70,8 +166,11 @@ gemm_comm_kernel(const __grid_constant__ MapTable maps_a, const __grid_constant_
     const int m_rot = (mode & (MODE_AG_A | MODE_RS_M)) ? rank * (m_tiles / world) : 0;
     const int n_rot = (mode & (MODE_AG_B | MODE_SCATTER_N)) ? rank * (n_tiles / world) : 0;
 
+    const int n_copy = ca.n_copy;
+    const bool is_copy = (int)blockIdx.x < n_copy;
+    const int gemm_cta = (int)blockIdx.x - n_copy, gemm_ctas = (int)gridDim.x - n_copy;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; s++) {
+        for (int s = 0; s < MAX_STAGES; s++) {  // all of them: the copy CTAs use COPY_STAGES (> STAGES for wide tiles)
             mbar_init(&sm->full[s], 1);
             mbar_init(&sm->empty[s], 1);
         }
@@ -81,7 +180,16 @@ gemm_comm_kernel(const __grid_constant__ MapTable maps_a, const __grid_constant_
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 1) {
+    if (is_copy) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            static_assert(COPY_STAGES <= MAX_STAGES, "copy ring uses the `full` barriers");
+            if (mode & MODE_AG_B) copy_role(ca, tiles, sm->full, blockIdx.x, n_tiles, n_rot);
+            else copy_role(ca, tiles, sm->full, blockIdx.x, m_tiles, m_rot);
+        }
+        __syncthreads();
+    }
+    if (!is_copy && warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm->tmem_base)),
                      "n"(TMEM_COLS)
                      : "memory");
@@ -90,30 +198,33 @@ gemm_comm_kernel(const __grid_constant__ MapTable maps_a, const __grid_constant_
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = sm->tmem_base;
+    const uint32_t tmem_base = is_copy ? 0u : sm->tmem_base;
 
-    if (warp == 0) {
-        // ================= TMA producer (local and remote operand tiles) =================
+    if (is_copy) {
+        // nothing else to do until the collective tail
+    } else if (warp == 0) {
+        // ================= TMA producer (local and gathered operand tiles) =================
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0, seen = 1u << rank;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            for (int t = gemm_cta; t < num_tiles; t += gemm_ctas) {
                 const int m_blk = (t % m_tiles + m_rot) % m_tiles, n_blk = (t / m_tiles + n_rot) % n_tiles;
                 int pa = 0, pb = 0, a_row = m_blk * BLOCK_M, b_row = n_blk * BLOCK_N;
+                (void)seen;
                 if (mode & MODE_AG_A) {
                     pa = a_row / ca.rows_per_peer_a;
                     a_row -= pa * ca.rows_per_peer_a;
-                    if (!(seen >> pa & 1)) {
-                        wait_flag(ca.flags, rank, ca.ch_in_ready, pa, ca.epoch);
-                        seen |= 1u << pa;
+                    if (pa != rank && !(mode & MODE_REUSE_FULL)) {  // gathered by the copy CTAs: wait for this tile-row block to land locally
+                        while ((int32_t)(ld_acquire_gpu(ca.chunk_flags + m_blk) - ca.epoch) < 0) __nanosleep(32);
+                        asm volatile("fence.proxy.async;" ::: "memory");
                     }
                 }
                 if (mode & MODE_AG_B) {
                     pb = b_row / ca.rows_per_peer_b;
                     b_row -= pb * ca.rows_per_peer_b;
-                    if (!(seen >> pb & 1)) {
-                        wait_flag(ca.flags, rank, ca.ch_in_ready, pb, ca.epoch);
-                        seen |= 1u << pb;
+                    if (pb != rank && !(mode & MODE_REUSE_FULL)) {
+                        while ((int32_t)(ld_acquire_gpu(ca.chunk_flags + n_blk) - ca.epoch) < 0) __nanosleep(32);
+                        asm volatile("fence.proxy.async;" ::: "memory");
                     }
                 }
                 const CUtensorMap* ma = &maps_a.m[pa];
@@ -138,7 +249,7 @@ gemm_comm_kernel(const __grid_constant__ MapTable maps_a, const __grid_constant_
             constexpr uint32_t idesc = make_idesc(BLOCK_M, BLOCK_N);
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            for (int t = gemm_cta; t < num_tiles; t += gemm_ctas) {
                 mbar_wait(&sm->tmem_empty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
@@ -171,7 +282,7 @@ gemm_comm_kernel(const __grid_constant__ MapTable maps_a, const __grid_constant_
         int acc = 0;
         uint32_t acc_phase = 0, seen = (ca.reuse_epoch == 0) ? 0xffffffffu : (1u << rank);
         const int cols_per_peer = N / world, rows_per_peer = M / world;
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        for (int t = gemm_cta; t < num_tiles; t += gemm_ctas) {
             const int m_blk = (t % m_tiles + m_rot) % m_tiles, n_blk = (t / m_tiles + n_rot) % n_tiles;
             mbar_wait(&sm->tmem_full[acc], acc_phase);
             tc_fence_after();
@@ -229,7 +340,7 @@ gemm_comm_kernel(const __grid_constant__ MapTable maps_a, const __grid_constant_
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) {
+    if (!is_copy && warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
     }
@@ -242,7 +353,8 @@ gemm_comm_kernel(const __grid_constant__ MapTable maps_a, const __grid_constant_
     }
     __syncthreads();
     if (last) {
-        if (mode & (MODE_AG_A | MODE_AG_B)) signal_all(ca.flags, rank, world, ca.ch_in_done, ca.epoch);
+        if ((mode & (MODE_AG_A | MODE_AG_B)) && !(mode & MODE_REUSE_FULL))
+            signal_all(ca.flags, rank, world, ca.ch_in_done, ca.epoch);
         if (mode & (MODE_SCATTER_N | MODE_RS_M)) signal_all(ca.flags, rank, world, ca.ch_out_ready, ca.epoch);
     }
     if (mode & (MODE_SCATTER_N | MODE_RS_M)) {
@@ -292,7 +404,8 @@ int dsb200_gemm_comm_bf16_nt(int mode, const uint64_t* a_ptrs, const uint64_t* b
                              const uint64_t* c_ptrs, void* rs_out, int M, int N, int K, int64_t lda, int64_t ldb,
                              int64_t ldc, const uint64_t* peer_flags, int rank, int world, int ch_in_ready,
                              int ch_in_done, int ch_out_ready, int ch_out_done, unsigned int epoch,
-                             unsigned int reuse_epoch, unsigned int* tickets, int max_ctas, cudaStream_t stream)
+                             unsigned int reuse_epoch, unsigned int* tickets, void* g_full, void* chunk_flags,
+                             int n_copy, int max_ctas, cudaStream_t stream)
 {
     if (world < 1 || world > MAX_WORLD || M <= 0 || N <= 0 || K <= 0 || (lda % 8) || (ldb % 8)) {
         dsb200_set_error("gemm_comm: bad world size / shape / leading dimension");
@@ -316,15 +429,35 @@ int dsb200_gemm_comm_bf16_nt(int mode, const uint64_t* a_ptrs, const uint64_t* b
     MapTable ta, tb;
     memset(&ta, 0, sizeof(ta));
     memset(&tb, 0, sizeof(tb));
+    if (mode & MODE_REUSE_FULL) n_copy = 0;  // the gathered operand is still resident in g_full from an earlier call
+    if ((mode & (MODE_AG_A | MODE_AG_B)) &&
+        (g_full == nullptr || (!(mode & MODE_REUSE_FULL) && (chunk_flags == nullptr || n_copy < 1)))) {
+        dsb200_set_error("gemm_comm: all-gather modes need a local gather buffer, chunk flags and n_copy >= 1");
+        return -1;
+    }
     if (mode & MODE_AG_A) {
-        for (int p = 0; p < world; p++)
-            if (make_map(&ta.m[p], (const void*)a_ptrs[p], M / world, K, lda, BLOCK_M) != 0) return -2;
+        if (lda != K) {
+            dsb200_set_error("gemm_comm: the gathered operand must have contiguous rows (ld == K)");
+            return -1;
+        }
+        for (int p = 0; p < world; p++) {
+            const void* base = (p == rank) ? (const void*)a_ptrs[p]
+                                           : (const void*)((const uint8_t*)g_full + (int64_t)p * (M / world) * K * 2);
+            if (make_map(&ta.m[p], base, M / world, K, lda, BLOCK_M) != 0) return -2;
+        }
     } else if (make_map(&ta.m[0], (const void*)a_ptrs[0], M, K, lda, BLOCK_M) != 0) {
         return -2;
     }
     if (mode & MODE_AG_B) {
-        for (int p = 0; p < world; p++)
-            if (make_map(&tb.m[p], (const void*)b_ptrs[p], N / world, K, ldb, bn) != 0) return -2;
+        if (ldb != K) {
+            dsb200_set_error("gemm_comm: the gathered operand must have contiguous rows (ld == K)");
+            return -1;
+        }
+        for (int p = 0; p < world; p++) {
+            const void* base = (p == rank) ? (const void*)b_ptrs[p]
+                                           : (const void*)((const uint8_t*)g_full + (int64_t)p * (N / world) * K * 2);
+            if (make_map(&tb.m[p], base, N / world, K, ldb, bn) != 0) return -2;
+        }
     } else if (make_map(&tb.m[0], (const void*)b_ptrs[0], N, K, ldb, bn) != 0) {
         return -2;
     }
@@ -346,10 +479,22 @@ int dsb200_gemm_comm_bf16_nt(int mode, const uint64_t* a_ptrs, const uint64_t* b
     ca.tickets = tickets;
     ca.rs_out = (__nv_bfloat16*)rs_out;
     ca.rs_ld = ldc;
+    ca.n_copy = 0;
+    if (mode & (MODE_AG_A | MODE_AG_B)) {
+        const uint64_t* src = (mode & MODE_AG_A) ? a_ptrs : b_ptrs;
+        const int rows = (mode & MODE_AG_A) ? BLOCK_M : bn;
+        ca.n_copy = n_copy;
+        ca.chunk_flags = (uint32_t*)chunk_flags;
+        ca.g_full = (uint8_t*)g_full;
+        ca.chunk_bytes = (int64_t)rows * K * 2;
+        ca.chunks_per_peer = ((mode & MODE_AG_A) ? M : N) / world / rows;
+        for (int p = 0; p < world; p++) ca.g_src[p] = (const void*)src[p];
+    }
     const int m_tiles = (M + BLOCK_M - 1) / BLOCK_M;
     const int tiles = m_tiles * ((N + bn - 1) / bn);
-    int grid = tiles < DSB_NUM_SMS ? tiles : DSB_NUM_SMS;
+    int grid = tiles < DSB_NUM_SMS - ca.n_copy ? tiles : DSB_NUM_SMS - ca.n_copy;
     if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+    grid += ca.n_copy;
 #define COMM_LAUNCH(BN)                                                                                             \
     do {                                                                                                            \
         static bool attr_set = false;                                                                               \

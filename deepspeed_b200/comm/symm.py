@@ -44,7 +44,8 @@ def _declare(L):
     L.dsb200_symm_fp8_stage_bytes.restype = L64
     L.dsb200_symm_all_gather_fp8.argtypes = [P, I, P, P, I, I, L64, I, P, P, I, I, U, U, I, P]
     L.dsb200_symm_all_gather_fp8.restype = I
-    L.dsb200_gemm_comm_bf16_nt.argtypes = [I, P, P, P, P, P, I, I, I, L64, L64, L64, P, I, I, I, I, I, I, U, U, P, I, P]
+    L.dsb200_gemm_comm_bf16_nt.argtypes = [I, P, P, P, P, P, I, I, I, L64, L64, L64, P, I, I, I, I, I, I, U, U, P, P, P, I,
+                                           I, P]
     L.dsb200_gemm_comm_bf16_nt.restype = I
     L.dsb200_symm_wait.argtypes = [P, I, I, I, U, P]
     L.dsb200_symm_wait.restype = I
@@ -205,13 +206,18 @@ class SymmContext:
             K._LAUNCHES += 1
 
     def _gemm_comm(self, mode, a_ptrs, b_ptrs, out, c_ptrs, rs_out, M, N, Kd, lda, ldb, ldc, chans, epoch, reuse,
-                   max_ctas=0):
+                   max_ctas=0, g_full=None, n_copy=0):
         null = ctypes.c_void_p(0)
+        if g_full is not None and getattr(self, "chunk_flags", None) is None:
+            self.chunk_flags = torch.zeros(8192, dtype=torch.int32, device=self.device)
         bn = self.lib.dsb200_gemm_comm_bf16_nt(
             mode, a_ptrs, b_ptrs, ctypes.c_void_p(out.data_ptr()) if out is not None else null,
             c_ptrs if c_ptrs is not None else null, ctypes.c_void_p(rs_out.data_ptr()) if rs_out is not None else null,
             M, N, Kd, lda, ldb, ldc, self.flags.ptrs, self.rank, self.world, chans[0], chans[1], chans[2], chans[3],
-            epoch, reuse, ctypes.c_void_p(self.tickets.data_ptr() + 32), max_ctas, self._stream())
+            epoch, reuse, ctypes.c_void_p(self.tickets.data_ptr() + 32),
+            ctypes.c_void_p(g_full.data_ptr()) if g_full is not None else null,
+            ctypes.c_void_p(self.chunk_flags.data_ptr()) if g_full is not None else null, n_copy, max_ctas,
+            self._stream())
         if bn < 0:
             raise RuntimeError(f"gemm_comm failed: {K.last_error()}")
         K._LAUNCHES += 1
@@ -221,7 +227,8 @@ class SymmContext:
     def _one(t):
         return (ctypes.c_uint64 * 16)(*([t.data_ptr()] + [0] * 15))
 
-    def all_gather_gemm(self, x, w_buf: SymmBuffer, n_total, out=None, gathered="b", max_ctas=0):
+    def all_gather_gemm(self, x, w_buf: SymmBuffer, n_total, out=None, gathered="b", max_ctas=0, full=None,
+                        n_copy=None):
         """Fused path 2. ``gathered="b"``: ``out[M, n_total] = x[M, K] @ W^T`` where rank p holds rows
         ``[p*n_total/world, ...)`` of ``W`` in ``w_buf`` - the ZeRO-3 weight all-gather happens tile by tile inside the
         GEMM. ``gathered="a"``: ``out[m_total, N] = X @ w^T`` with the rows of ``X`` spread over the ranks' ``w_buf``
@@ -237,9 +244,16 @@ class SymmContext:
             a_ptrs, b_ptrs, mode = w_buf.ptrs, self._one(x), GEMM_AG_A
         if out is None:
             out = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+        if full is None:  # local landing buffer of the gathered operand (for ZeRO-3: the unit's full parameter)
+            cache = self.__dict__.setdefault("_gather_full", {})
+            full = cache.get(n_total * Kd)
+            if full is None:
+                full = cache[n_total * Kd] = torch.empty(n_total * Kd, dtype=torch.bfloat16, device=x.device)
+        if n_copy is None:
+            n_copy = int(os.environ.get("DSB200_GEMM_COPY_CTAS", "12"))
         self._gemm_comm(mode, a_ptrs, b_ptrs, out, None, None, M, N, Kd, Kd if gathered == "a" else x.stride(0),
                         Kd if gathered == "b" else x.stride(0), out.stride(0),
-                        (CH_GIN_READY, CH_GIN_DONE, 0, 0), ep, 0, max_ctas)
+                        (CH_GIN_READY, CH_GIN_DONE, 0, 0), ep, 0, max_ctas, g_full=full, n_copy=n_copy)
         w_buf.last_gin_epoch = ep
         return out
 

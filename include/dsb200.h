@@ -110,6 +110,24 @@ int dsb200_symm_all_gather_fp8(const void* my_shard, int dt, const uint64_t* pee
                                unsigned int* tickets, int ch_ready, int ch_done, unsigned int epoch,
                                unsigned int reuse_epoch, int ctas, cudaStream_t stream);
 
+/* ---------------------------------------------------------------- tcgen05 GEMM + collective (gemm_comm.cu) */
+/* C = A * B^T (bf16, fp32 accumulate in TMEM) fused with an NVLink collective over symmetric memory. mode bits:
+ *   1 AG_A  rows of A live on the peers   2 AG_B  rows of B live on the peers (ZeRO-3 weight all-gather -> GEMM):
+ *           n_copy CTAs pull each remote tile-row block ONCE with bulk async copies into g_full and publish
+ *           chunk_flags; the GEMM CTAs read them from there through per-peer TMA maps;
+ *   4 SCATTER_N  column block j of C is stored to peer j's buffer c_ptrs[j] at row offset rank*M (GEMM -> all-to-all);
+ *   8 RS_M  row block j goes to peer j's staging slot [rank], then every rank sums its slots into rs_out
+ *           (GEMM -> reduce-scatter);   16 REUSE_FULL  the gathered operand is still resident in g_full.
+ * M, N, K are global sizes; the distributed dimension must be a multiple of world * tile. tickets: 3 zeroed words.
+ * Returns the tile width used (> 0). Reference: NCCL collective + cuBLAS GEMM as separate kernels
+ * (partition_parameters.py:1301, sequence/layer.py:264, module_inject/layers.py:771). */
+int dsb200_gemm_comm_bf16_nt(int mode, const uint64_t* a_ptrs, const uint64_t* b_ptrs, void* C,
+                             const uint64_t* c_ptrs, void* rs_out, int M, int N, int K, int64_t lda, int64_t ldb,
+                             int64_t ldc, const uint64_t* peer_flags, int rank, int world, int ch_in_ready,
+                             int ch_in_done, int ch_out_ready, int ch_out_done, unsigned int epoch,
+                             unsigned int reuse_epoch, unsigned int* tickets, void* g_full, void* chunk_flags,
+                             int n_copy, int max_ctas, cudaStream_t stream);
+
 /* ---------------------------------------------------------------- token movement ------------------------- */
 /* scatter == 0: dst[i,:] = src[idx[i],:]; scatter != 0: dst[idx[i],:] = src[i,:]. idx is int32 (idx_bytes 4) or int64
  * (8); rows and strides are multiples of 16 bytes; indices outside [0, bound) are skipped.
