@@ -1,0 +1,94 @@
+"""Evoformer attention for DS4Science / AlphaFold-style models (reference ``ops/deepspeed4science/evoformer_attn.py``
+over the CUTLASS kernels in ``csrc/deepspeed4science/evoformer_attn``): attention over ``[*, L, H, D]`` tensors with
+up to two additive biases - ``bias1 [B, N, 1, 1, L]`` (the MSA mask) and ``bias2 [B, 1, H, L, L]`` (the pair bias) -
+and gradients for both.
+
+The score matrix is never materialised for the whole batch: rows of the MSA dimension are processed in chunks sized to
+a fixed workspace, forward and backward (the backward recomputes each chunk's probabilities from the saved
+log-sum-exp, like the fused kernel does)."""
+import math
+
+import torch
+
+_WORKSPACE_ELEMS = 1 << 28  # fp32 score elements per chunk (1 GiB)
+
+
+def _chunks(n_rows, per_row):
+    step = max(1, _WORKSPACE_ELEMS // max(per_row, 1))
+    return [(s, min(n_rows, s + step)) for s in range(0, n_rows, step)]
+
+
+class EvoformerFusedAttention(torch.autograd.Function):
+
+    @staticmethod
+    def forward(ctx, q, k, v, bias1=None, bias2=None):
+        # q, k, v: [B, N, L, H, D]
+        B, N, L, H, D = q.shape
+        scale = 1.0 / math.sqrt(D)
+        out = torch.empty_like(q)
+        acc = torch.float64 if q.dtype == torch.float64 else torch.float32
+        lse = torch.empty(B, N, H, L, dtype=acc, device=q.device)
+        for s, e in _chunks(N, B * H * L * L):
+            qc = q[:, s:e].permute(0, 1, 3, 2, 4)                    # [B, n, H, L, D]
+            kc = k[:, s:e].permute(0, 1, 3, 2, 4)
+            vc = v[:, s:e].permute(0, 1, 3, 2, 4)
+            scores = torch.matmul(qc, kc.transpose(-1, -2)).to(acc) * scale
+            if bias1 is not None:
+                scores = scores + bias1[:, s:e].to(acc)              # [B, n, 1, 1, L]
+            if bias2 is not None:
+                scores = scores + bias2.to(acc)                      # [B, 1, H, L, L]
+            l = torch.logsumexp(scores, dim=-1)
+            lse[:, s:e] = l
+            p = torch.exp(scores - l.unsqueeze(-1)).to(q.dtype)
+            out[:, s:e] = torch.matmul(p, vc).permute(0, 1, 3, 2, 4)
+        ctx.save_for_backward(q, k, v, out, lse, bias1 if bias1 is not None else torch.tensor([]),
+                              bias2 if bias2 is not None else torch.tensor([]))
+        ctx.has_b1, ctx.has_b2 = bias1 is not None, bias2 is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        q, k, v, out, lse, bias1, bias2 = ctx.saved_tensors
+        B, N, L, H, D = q.shape
+        scale = 1.0 / math.sqrt(D)
+        acc = lse.dtype
+        dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+        need_b1 = ctx.has_b1 and ctx.needs_input_grad[3]
+        need_b2 = ctx.has_b2 and ctx.needs_input_grad[4]
+        db1 = torch.zeros(bias1.shape, dtype=acc, device=q.device) if need_b1 else None
+        db2 = torch.zeros(bias2.shape, dtype=acc, device=q.device) if need_b2 else None
+        delta = (grad_output.to(acc) * out.to(acc)).sum(-1).permute(0, 1, 3, 2)      # [B, N, H, L]
+        for s, e in _chunks(N, B * H * L * L):
+            qc = q[:, s:e].permute(0, 1, 3, 2, 4)
+            kc = k[:, s:e].permute(0, 1, 3, 2, 4)
+            vc = v[:, s:e].permute(0, 1, 3, 2, 4)
+            doc = grad_output[:, s:e].permute(0, 1, 3, 2, 4)
+            scores = torch.matmul(qc, kc.transpose(-1, -2)).to(acc) * scale
+            if ctx.has_b1:
+                scores = scores + bias1[:, s:e].to(acc)
+            if ctx.has_b2:
+                scores = scores + bias2.to(acc)
+            p = torch.exp(scores - lse[:, s:e].unsqueeze(-1))                           # fp32 [B, n, H, L, L]
+            dv[:, s:e] = torch.matmul(p.to(q.dtype).transpose(-1, -2), doc).permute(0, 1, 3, 2, 4)
+            dp = torch.matmul(doc, vc.transpose(-1, -2)).to(acc)
+            ds = p * (dp - delta[:, s:e].unsqueeze(-1))                                 # d(scores incl. biases)
+            if need_b1:
+                db1[:, s:e] += ds.sum(dim=(2, 3), keepdim=True)
+            if need_b2:
+                db2 += ds.sum(dim=1, keepdim=True)
+            dsl = (ds * scale).to(q.dtype)
+            dq[:, s:e] = torch.matmul(dsl, kc).permute(0, 1, 3, 2, 4)
+            dk[:, s:e] = torch.matmul(dsl.transpose(-1, -2), qc).permute(0, 1, 3, 2, 4)
+        return dq, dk, dv, (db1.to(grad_output.dtype) if need_b1 else None), \
+            (db2.to(grad_output.dtype) if need_b2 else None)
+
+
+def DS4Sci_EvoformerAttention(Q, K, V, biases):
+    """Q, K, V: [B, N, L, H, D]; ``biases``: up to two tensors, ``[B, N, 1, 1, L]`` and ``[B, 1, H, L, L]``."""
+    assert len(biases) <= 2
+    biases = list(biases) + [None] * (2 - len(biases))
+    if biases[0] is not None:
+        assert biases[0].shape == (Q.shape[0], Q.shape[1], 1, 1, Q.shape[2]), "bias1 shape is incorrect"
+    if biases[1] is not None:
+        assert biases[1].shape == (Q.shape[0], 1, Q.shape[3], Q.shape[2], Q.shape[2]), "bias2 shape is incorrect"
+    return EvoformerFusedAttention.apply(Q, K, V, biases[0], biases[1])
