@@ -39,5 +39,11 @@ TransformerBuilder = _mk("TransformerBuilder", "deepspeed_b200.ops.transformer")
 RandomLTDBuilder = _mk("RandomLTDBuilder", "deepspeed_b200.ops.random_ltd")
 SparseAttnBuilder = _mk("SparseAttnBuilder", "deepspeed_b200.ops.sparse_attention")
 EvoformerAttnBuilder = _mk("EvoformerAttnBuilder", "deepspeed_b200.ops.deepspeed4science")
-InferenceBuilder = _mk("InferenceBuilder", "deepspeed_b200.inference.kernels")
+InferenceBuilder = _mk("InferenceBuilder", "deepspeed_b200.inference.engine")
+SpatialInferenceBuilder = _mk("SpatialInferenceBuilder", "deepspeed_b200.ops.spatial")
+PinMemoryBuilder = _mk("PinMemoryBuilder", "deepspeed_b200.ops.pin_memory")
+GDSBuilder = _mk("GDSBuilder", "deepspeed_b200.ops.gds")
+StochasticTransformerBuilder = _mk("StochasticTransformerBuilder", "deepspeed_b200.ops.transformer")
+RaggedOpsBuilder = _mk("RaggedOpsBuilder", "deepspeed_b200.inference.v2.ragged")
+DeepCompileBuilder = _mk("DeepCompileBuilder", "deepspeed_b200.compile")
 ALL_OPS = {k: v for k, v in globals().items() if k.endswith("Builder") and k != "_Builder"}
