@@ -195,6 +195,49 @@ def all_to_all_quant_reduce(tensors, groups, bits=4):
     return outs
 
 
+_LOCO_STEP = 0
+
+
+def all_to_all_loco_quant_reduce(params, groups, loco_param=None):
+    """qgZ with LoCo error feedback (reference ``coalesced_collectives.py:81``): the quantization error of every
+    gradient is kept (int8-compressed) on the parameter and added back, damped by ``err_beta``, before the next
+    quantization; the buffers are reset every ``reset_T`` steps. One NVSwitch domain -> one all-to-all stage.
+    ``params``: parameters whose ``.grad`` is reduced; returns each rank's (mean) partition per parameter."""
+    global _LOCO_STEP
+    loco_param = loco_param or {"err_beta": 0.8, "reset_T": 1024}
+    beta, reset_t = loco_param["err_beta"], loco_param["reset_T"]
+    local = next((g for k, g in groups.items() if k.startswith("local")), None)
+    world = dist.get_world_size(local)
+    if _LOCO_STEP > reset_t:
+        _LOCO_STEP = 0
+    outs = []
+    for p in params:
+        g = p.grad
+        n = g.numel()
+        if g.dim() < 2 or n % (world * 256) != 0:
+            outs.extend(all_to_all_quant_reduce([g], groups))
+            continue
+        flat = g.contiguous().view(-1)
+        if _LOCO_STEP == 0 or not hasattr(p, "intra_ef_buf"):
+            err = torch.zeros_like(flat, dtype=torch.float32)
+        else:
+            eq, es = p.intra_ef_buf
+            err = dequantize(eq, es, es.numel(), 8, dtype=torch.bfloat16).float().view(-1)
+        comp = flat.float() + beta * err
+        group_elems = 256 if (n // world) % 512 else 512
+        ngroups = n // group_elems
+        q, s = quantize(comp.to(torch.bfloat16), ngroups, 4)
+        new_err = comp - dequantize(q, s, ngroups, 4, dtype=torch.bfloat16).float().view(-1)
+        p.intra_ef_buf = quantize(new_err.to(torch.bfloat16), ngroups, 8)
+        qr, sr = torch.empty_like(q), torch.empty_like(s)
+        dist.all_to_all_single(qr, q, group=local)
+        dist.all_to_all_single(sr, s, group=local)
+        outs.append(quantized_reduction(qr, sr, ngroups, ngroups // world, 4, world,
+                                        dtype=g.dtype if g.dtype != torch.float32 else torch.bfloat16).to(g.dtype))
+    _LOCO_STEP += 1
+    return outs
+
+
 class CUDAQuantizer:
     """Object API used by ZeRO-3 parameter all-gather in the reference (``partition_parameters.py:846``)."""
     async_flag = True

@@ -5,7 +5,7 @@ import math
 import torch
 
 from ... import comm as dist
-from ...ops.quantizer import all_to_all_quant_reduce  # noqa: F401
+from ...ops.quantizer import all_to_all_loco_quant_reduce, all_to_all_quant_reduce  # noqa: F401
 
 
 @torch.no_grad()

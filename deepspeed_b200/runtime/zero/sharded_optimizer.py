@@ -35,6 +35,9 @@ from ...utils.nvtx import instrument_w_nvtx
 from ..loss_scaler import CreateLossScaler
 from .units import FlatUnit, build_bucket_units, build_module_units
 
+import os as _os
+
+_SYMM_VERIFY = _os.environ.get("DSB200_SYMM_VERIFY", "0") == "1"
 ZERO_STAGE = "zero_stage"
 PARTITION_COUNT = "partition_count"
 BASE_OPTIMIZER_STATE = "base_optimizer_state"
@@ -556,8 +559,19 @@ class ZeroShardedOptimizer:
                 u._slot = None
             elif getattr(u, "_slot", None) is not None and self.symm is not None:
                 # ONE kernel: NVLink loads from every peer's bucket + fp32 sum + average + cast + accumulate
+                verify = _SYMM_VERIFY and first
+                if verify:  # debug mode: the NCCL collective is the oracle for the in-kernel one (race detection)
+                    want = torch.empty(u.shard_numel, dtype=torch.float32, device=full.device)
+                    dist.reduce_scatter_tensor(want, full.float(), group=u.dp_group)
+                    want.div_(div)
                 self.symm.reduce_scatter(u._slot, full.dtype, u.shard_numel, u.grad_shard, accumulate=not first,
                                          scale=1.0 / div)
+                if verify:
+                    err = float((u.grad_shard.float() - want).abs().max())
+                    tol = 2e-2 * max(1.0, float(want.abs().max()))
+                    if not err <= tol:
+                        raise RuntimeError(f"DSB200_SYMM_VERIFY: fused reduce-scatter of {u.name} differs from NCCL "
+                                           f"by {err} (tolerance {tol}): ordering bug in the flag protocol?")
                 u._slot = None
             else:
                 self._reduce_unit_nccl(u, full, div, first)
