@@ -190,8 +190,9 @@ class DeepSpeedEngine(Module):
                     _set_buffer(model, name, buf.to(self.device))
         # MoE discovery (reference engine.py:1775-1792)
         from ..moe.layer import MoE
+        from ..parallel.auto_ep import AutoEPMoELayer
         for m in model.modules():
-            if isinstance(m, MoE):
+            if isinstance(m, (MoE, AutoEPMoELayer)):
                 self.has_moe_layers = True
                 self.num_experts.append(m.num_experts)
                 self.moe_layers.append(m)
