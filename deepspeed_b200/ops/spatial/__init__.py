@@ -28,7 +28,6 @@ def _run(x, bias, other=None, other_bias=None):
         K._check(L.dsb200_nhwc_bias_add(K._ptr(x), K._ptr(bias), K._ptr(other) if other is not None else null,
                                         K._ptr(other_bias) if other_bias is not None else null, K._ptr(out),
                                         x.numel(), c, K._dt(x), K._stream()), "nhwc_bias_add")
-        K._LAUNCHES += 1
         return out
     shape = (1, c, 1, 1) if x.dim() == 4 else (c, )
     out = x + bias.view(shape)
