@@ -51,6 +51,11 @@ class ClockSampler:
 
     def __init__(self, gpu_index=0):
         self.rows, self.proc, self.gpu_index = [], None, gpu_index
+        self.t_region = 0.0
+
+    def mark_region_start(self):
+        """Samples before this moment (warm-up; nvidia-smi's own start-up) are discarded."""
+        self.t_region = time.time()
 
     def start(self):
         try:
@@ -64,7 +69,7 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
 
     def stop(self):
         if self.proc is None:
@@ -76,7 +81,9 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        for ts, r in self.rows:
+            if ts < self.t_region:
+                continue
             try:
                 sm.append(float(r[1]))
                 mx.append(float(r[2]))
@@ -264,14 +271,16 @@ def main():
         dist.barrier()
         torch.cuda.synchronize()
 
+    # the clock sampler is started BEFORE the warm-up so that spawning nvidia-smi (NVML start-up, device enumeration)
+    # cannot stall a timed step; only samples taken inside the timed regions are reported
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
     for i in range(W):
         loss = step(host[i].to(dev, non_blocking=True))
     float(loss)
     sync_all()
-
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
+    sampler.mark_region_start()
     # ---- region 1: device-timed ----
     l0 = launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
