@@ -35,8 +35,10 @@ class InferenceEngineV2:
         self.state_manager = DSStateManager(kv, self.config.max_tracked_sequences, self.config.max_ragged_batch_size,
                                             self.config.max_ragged_sequence_count)
         self.batch = RaggedBatchWrapper()
-        self.cos, self.sin = fused.rope_tables(c.max_position_embeddings, c.head_dim, c.rope_theta, self.device,
-                                               c.rope_scaling)
+        self.generic = hasattr(model, "forward_tokens")  # model_implementations.GenericDecoder (any HF family)
+        if not self.generic:
+            self.cos, self.sin = fused.rope_tables(c.max_position_embeddings, c.head_dim, c.rope_theta, self.device,
+                                                   c.rope_scaling)
 
     @property
     def free_blocks(self):
@@ -77,8 +79,30 @@ class InferenceEngineV2:
             seq.post_forward()
         return logits
 
+    def _attend(self, li, q, k, v):
+        """Blocked-KV attention for the current ragged batch: q/k/v are [T, heads, head_dim] with positions applied."""
+        nh, nkv = q.shape[1], k.shape[1]
+        outs = []
+        for (seq, start, n, seen) in self.batch.seq_meta:
+            self.state_manager.kv.write(li, seq, k[start:start + n], v[start:start + n], seen)
+            kk, vv = self.state_manager.kv.read(li, seq, seen + n)
+            qq = q[start:start + n].transpose(0, 1).unsqueeze(0)
+            kk = kk.transpose(0, 1).repeat_interleave(nh // nkv, 0).unsqueeze(0)
+            vv = vv.transpose(0, 1).repeat_interleave(nh // nkv, 0).unsqueeze(0)
+            mask = (torch.arange(seen + n, device=self.device)[None, :] <=
+                    (torch.arange(n, device=self.device) + seen)[:, None])
+            o = F.scaled_dot_product_attention(qq, kk, vv, attn_mask=mask)
+            outs.append(o[0].transpose(0, 1).reshape(n, -1))
+        return torch.cat(outs, 0)
+
     def _forward(self, ids):
         m = self.model
+        if self.generic:
+            pos = torch.cat([torch.arange(seen, seen + n, device=self.device)
+                             for (_, _, n, seen) in self.batch.seq_meta])
+            h = m.forward_tokens(ids, pos, self._attend)
+            last = torch.tensor([s + n - 1 for (_, s, n, _) in self.batch.seq_meta], device=self.device)
+            return m.lm_head(h.index_select(0, last))
         inner = getattr(m, "model", m)
         layers = inner.layers
         h = inner.embed_tokens(ids)  # [T, H]
