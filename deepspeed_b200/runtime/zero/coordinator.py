@@ -91,7 +91,15 @@ class UnitCoordinator:
             group = u.dp_group
             if z._hpz_group is not None and self._in_backward_pass and u.sec_shard is not None:
                 src, group = u.sec_shard, z._hpz_group
-            if use_side:
+            world = dist.get_world_size(group) if group is not None and dist.is_initialized() else 1
+            if world <= 1 and src.numel() == u.numel_padded and src.dtype == u.dtype:
+                # a single shard IS the full parameter: alias it instead of "gathering" through a copy
+                u.full_param = src
+                u.gather_work = True
+                use_side = None
+            if use_side is None:
+                pass
+            elif use_side:
                 with torch.cuda.stream(z.ag_stream):
                     full = torch.empty(u.numel_padded, dtype=u.dtype, device=u.device)
                     self._launch_gather(u, full, src, group)
@@ -100,8 +108,9 @@ class UnitCoordinator:
             else:
                 full = torch.empty(u.numel_padded, dtype=u.dtype, device=u.device)
                 self._launch_gather(u, full, src, group)
-            u.full_param = full
-            u.gather_work = True
+            if use_side is not None:
+                u.full_param = full
+                u.gather_work = True
         if wait and not u.gathered:
             if u.gather_event is not None:
                 torch.cuda.current_stream().wait_event(u.gather_event)

@@ -480,6 +480,12 @@ class ZeroShardedOptimizer:
             if self._grad_pool is not None and u.world > 1:
                 u._slot = self._grad_pool.acquire()  # waits (on this stream) until peers released the slot
                 u.full_grad = u._slot.view(u.numel_padded, self._full_grad_dtype())
+            elif (u.world == 1 and u.replica_world == 1 and not getattr(u, "_shard_has_data", False)
+                  and u.grad_shard.dtype == self._full_grad_dtype() and u.grad_shard.numel() == u.numel_padded
+                  and self.partition_grads):
+                # nothing to reduce and nothing accumulated yet: gradients are written straight into the shard
+                u._slot = None
+                u.full_grad = u.grad_shard
             else:
                 u._slot = None
                 u.full_grad = torch.empty(u.numel_padded, dtype=self._full_grad_dtype(), device=u.device)
@@ -603,7 +609,10 @@ class ZeroShardedOptimizer:
         if u.replica_world > 1 and not (getattr(self.optimizer, "compression_active", False)
                                         and not self.partition_optimizer):
             dist.all_reduce(out, group=u.replica_group)
-        if first:
+        if first and out.data_ptr() == u.grad_shard.data_ptr():
+            if post != 1.0:
+                u.grad_shard.mul_(1.0 / post)
+        elif first:
             if post != 1.0:
                 torch.mul(out, 1.0 / post, out=u.grad_shard) if out.dtype == u.grad_shard.dtype else \
                     u.grad_shard.copy_(out.to(u.grad_shard.dtype).mul_(1.0 / post))
