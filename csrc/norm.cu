@@ -119,17 +119,36 @@ __global__ void __launch_bounds__(max_threads_for(MAX_VPT)) norm_bwd_kernel(cons
         for (int i = 0; i < 8; i++) dg[k].v[i] = db[k].v[i] = 0.f;
         if (v < nvec) gam[k] = dsb::load8(gamma + v * 8);
     }
+    // software pipeline over rows: the 16-byte loads of the NEXT row are issued before the block reduction of the
+    // current one, so the DRAM latency of row r+1 hides behind the reduction + stores of row r
+    uint4 rx[MAX_VPT], rdy[MAX_VPT], rres[MAX_VPT];
+    auto fetch = [&](int row) {
+#pragma unroll
+        for (int k = 0; k < MAX_VPT; k++) {
+            const int v = threadIdx.x + k * blockDim.x;
+            if (v < nvec) {
+                rx[k] = dsb::ldg_stream(reinterpret_cast<const uint4*>(x + (int64_t)row * cols) + v);
+                rdy[k] = dsb::ldg_stream(reinterpret_cast<const uint4*>(dy + (int64_t)row * cols) + v);
+                if (dres != nullptr) rres[k] = dsb::ldg_stream(reinterpret_cast<const uint4*>(dres + (int64_t)row * cols) + v);
+            }
+        }
+    };
+    constexpr bool PIPE = MAX_VPT <= 2;  // wider rows would spill the extra row of registers
+    if (PIPE && (int)blockIdx.x < rows) fetch(blockIdx.x);
     for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+        if (!PIPE) fetch(row);
         const float mean = LAYERNORM ? stats[2 * row] : 0.f;
         const float rstd = LAYERNORM ? stats[2 * row + 1] : stats[row];
         dsb::f8 xh[MAX_VPT], dyg[MAX_VPT];
+        uint4 cres[MAX_VPT];
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
         for (int k = 0; k < MAX_VPT; k++) {
             const int v = threadIdx.x + k * blockDim.x;
             if (v < nvec) {
-                dsb::f8 a = dsb::load8(x + (int64_t)row * cols + v * 8);
-                dsb::f8 d = dsb::load8(dy + (int64_t)row * cols + v * 8);
+                dsb::f8 a = dsb::load8(reinterpret_cast<const T*>(&rx[k]));
+                dsb::f8 d = dsb::load8(reinterpret_cast<const T*>(&rdy[k]));
+                if (PIPE) cres[k] = rres[k];
 #pragma unroll
                 for (int i = 0; i < 8; i++) {
                     float h = (a.v[i] - mean) * rstd;
@@ -143,6 +162,7 @@ __global__ void __launch_bounds__(max_threads_for(MAX_VPT)) norm_bwd_kernel(cons
                 }
             }
         }
+        if (PIPE && row + (int)gridDim.x < rows) fetch(row + gridDim.x);
         s1 = dsb::block_sum(s1, red) / cols;
         s2 = LAYERNORM ? dsb::block_sum(s2, red) / cols : 0.f;
 #pragma unroll
@@ -153,7 +173,7 @@ __global__ void __launch_bounds__(max_threads_for(MAX_VPT)) norm_bwd_kernel(cons
 #pragma unroll
                 for (int i = 0; i < 8; i++) o.v[i] = rstd * (dyg[k].v[i] - xh[k].v[i] * s1 - s2);
                 if (dres != nullptr) {
-                    dsb::f8 r = dsb::load8(dres + (int64_t)row * cols + v * 8);
+                    dsb::f8 r = dsb::load8(reinterpret_cast<const T*>(PIPE ? &cres[k] : &rres[k]));
 #pragma unroll
                     for (int i = 0; i < 8; i++) o.v[i] += r.v[i];
                 }
@@ -179,15 +199,24 @@ __global__ void __launch_bounds__(max_threads_for(MAX_VPT)) norm_bwd_kernel(cons
 
 // out[c] (T or float, accumulate optional) = sum_b partial[b][c]
 template <typename T>
-__global__ void reduce_partials_kernel(const float* __restrict__ partial, int nparts, int cols, T* __restrict__ out,
-                                       int accumulate)
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ partial, int nparts, int cols,
+                                                              T* __restrict__ out, int accumulate)
 {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= cols) return;
+    // 32 columns x 8 row groups per block: every warp reads one 128-byte line per partial row
+    __shared__ float sm[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
     float s = 0.f;
-    for (int b = 0; b < nparts; b++) s += partial[(int64_t)b * cols + c];
-    if (accumulate) s += dsb::to_f<T>(out[c]);
-    out[c] = dsb::from_f<T>(s);
+    if (c < cols)
+        for (int b = ty; b < nparts; b += 8) s += partial[(int64_t)b * cols + c];
+    sm[ty][tx] = s;
+    __syncthreads();
+    if (ty == 0 && c < cols) {
+#pragma unroll
+        for (int j = 1; j < 8; j++) s += sm[j][tx];
+        if (accumulate) s += dsb::to_f<T>(out[c]);
+        out[c] = dsb::from_f<T>(s);
+    }
 }
 
 int pick_vpt(int cols)
@@ -250,10 +279,10 @@ int launch_bwd(bool ln, const void* dy, const void* x, const void* gamma, const 
                                                                (const T*)dres, (T*)dx, pdg, nullptr, rows, cols);
     });
     DSB_CHECK_LAUNCH("norm_bwd");
-    reduce_partials_kernel<T><<<(cols + 255) / 256, 256, 0, s>>>(pdg, grid, cols, (T*)dgamma, accumulate);
+    reduce_partials_kernel<T><<<(cols + 31) / 32, 256, 0, s>>>(pdg, grid, cols, (T*)dgamma, accumulate);
     DSB_CHECK_LAUNCH("norm_bwd_reduce_g");
     if (ln && dbeta != nullptr) {
-        reduce_partials_kernel<T><<<(cols + 255) / 256, 256, 0, s>>>(pdb, grid, cols, (T*)dbeta, accumulate);
+        reduce_partials_kernel<T><<<(cols + 31) / 32, 256, 0, s>>>(pdb, grid, cols, (T*)dbeta, accumulate);
         DSB_CHECK_LAUNCH("norm_bwd_reduce_b");
     }
     return 0;
