@@ -1,9 +1,9 @@
 // tcgen05 GEMM fused with NVLink collectives over symmetric memory: C = A * B^T (bf16, fp32 accumulate in TMEM), where
 //
-//   AG_A       the rows of A live on the peers (rows_per_peer each)          all-gather -> GEMM   (AutoTP sequence-
-//              and are fetched tile by tile with TMA straight over NVLink      parallel input, Ulysses gather)
+//   AG_A       the rows of A live on the peers (rows_per_peer each); copy      all-gather -> GEMM   (AutoTP sequence-
+//              CTAs pull them ONCE into the local buffer g_full              parallel input, Ulysses gather)
 //   AG_B       the rows of B (= output features of a sharded weight) live    ZeRO-3 parameter all-gather fused into
-//              on the peers and are fetched the same way                       the first GEMM that consumes it
+//              on the peers and are staged into g_full the same way            the first GEMM that consumes it
 //   SCATTER_N  column block j of C is stored into peer j's output buffer at   GEMM -> all-to-all (Ulysses QKV
 //              row offset rank*M (peer j ends up with [world*M, N/world])      projection -> head-sharded layout)
 //   RS_M       row block j of the partial product is stored into peer j's     GEMM -> reduce-scatter (AutoTP row-
@@ -12,9 +12,12 @@
 //
 // Reference baseline: separate NCCL collective + cuBLAS GEMM kernels (partition_parameters.py:1301 all-gather then
 // F.linear; sequence/layer.py:264 all-to-all after the QKV linear; module_inject/layers.py:771 linear then
-// all-reduce). Here the transfer of tile i overlaps the MMAs of tile i-1 inside ONE persistent kernel: remote operand
-// tiles arrive through the same TMA/mbarrier ring as local ones, remote output tiles leave from the epilogue warps
-// while the tensor cores work on the next accumulator stage.
+// all-reduce). Here the transfer of block i overlaps the MMAs of block i-1 inside ONE persistent kernel: dedicated
+// copy CTAs land each peer's tile-row block in the local g_full with plain bulk async copies (no multicast) and
+// publish a per-block flag; the GEMM CTAs wait on the flag and then load the block through the ordinary TMA/mbarrier
+// ring. Remote output tiles leave from the epilogue warps while the tensor cores work on the next accumulator stage.
+// Every tensor map in this file covers THIS GPU's memory only: a remote operand must cross NVLink once, and per-tile
+// TMA loads from peer memory re-fetched the same weight tile for every m-tile (7x slower than NCCL when measured).
 //
 // Ordering uses the epoch flags of symm.cu: IN_READY ("my shard may be read", raised by the host-enqueued signal
 // kernel before this launch), IN_DONE ("I finished reading your shard"), OUT_READY ("all my stores into your buffer are
@@ -497,11 +500,13 @@ int dsb200_gemm_comm_bf16_nt(int mode, const uint64_t* a_ptrs, const uint64_t* b
     grid += ca.n_copy;
 #define COMM_LAUNCH(BN)                                                                                             \
     do {                                                                                                            \
-        static bool attr_set = false;                                                                               \
-        if (!attr_set) {                                                                                            \
+        static bool attr_set[64] = {};                                                                               \
+        int dev_ = 0;                                                                               \
+        cudaGetDevice(&dev_);                                                                               \
+        if (!attr_set[dev_ & 63]) {                                                                                            \
             DSB_CHECK(cudaFuncSetAttribute(gemm_comm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,       \
                                            Cfg<BN>::SMEM_BYTES));                                                  \
-            attr_set = true;                                                                                        \
+            attr_set[dev_ & 63] = true;                                                                                        \
         }                                                                                                           \
         gemm_comm_kernel<BN><<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(ta, tb, ca, (__nv_bfloat16*)C, M, \
                                                                                  N, K, ldc);                       \

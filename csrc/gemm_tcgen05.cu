@@ -207,11 +207,13 @@ int dsb200_gemm_bf16_nt(const void* A, const void* B, void* C, int M, int N, int
     if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
 #define GEMM_LAUNCH(BN)                                                                                              \
     do {                                                                                                             \
-        static bool attr_set = false;                                                                                \
-        if (!attr_set) {                                                                                             \
+        static bool attr_set[64] = {};                                                                                \
+        int dev_ = 0;                                                                                \
+        cudaGetDevice(&dev_);                                                                                \
+        if (!attr_set[dev_ & 63]) {                                                                                             \
             DSB_CHECK(cudaFuncSetAttribute(gemm_bf16_nt_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
                                            Cfg<BN>::SMEM_BYTES));                                                   \
-            attr_set = true;                                                                                         \
+            attr_set[dev_ & 63] = true;                                                                                         \
         }                                                                                                            \
         gemm_bf16_nt_kernel<BN><<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(map_a, map_b, (__nv_bfloat16*)C, \
                                                                                     M, N, K, ldc);                  \

@@ -111,9 +111,11 @@ class ReferenceLayout:
         """``shard_of_unit(u) -> fp32 shard tensor``; returns list (per group) of this rank's reference partition."""
         outs = [torch.zeros(self.partition_size[gi], dtype=torch.float32) for gi in range(len(self.group_params))]
         for u in self.z.units:
+            if not any(id(p) in self.ref_offset for p in u.params):
+                continue  # nothing of this unit is exported (e.g. all parameters frozen); same decision on every rank
             shard = shard_of_unit(u)
-            if shard is None:
-                continue
+            if shard is None:  # this rank's shard holds no such state (only frozen runs here): peers still gather
+                shard = torch.zeros(u.shard_numel, dtype=torch.float32, device=u.master_shard.device)
             full = self._full_unit(u, shard.float())
             for i, p in enumerate(u.params):
                 if id(p) not in self.ref_offset:

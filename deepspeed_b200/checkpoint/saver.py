@@ -107,6 +107,107 @@ def _module_state_for_save(engine, exclude_frozen):
     return engine.module_state_dict(exclude_frozen_parameters=exclude_frozen)
 
 
+def _cdiv(a, b):
+    return (a + b - 1) // b
+
+
+@torch.no_grad()
+def _zero3_frozen_fragments(engine):
+    """ZeRO-3: this rank's fragment of every frozen parameter in the reference layout (``param.ds_tensor``:
+    ``ceil(numel/world)`` contiguous elements of the flat parameter, zero padded on the last ranks; reference
+    ``engine.py:5292-5306``), so that the reference ``zero_to_fp32._zero3_merge_frozen_params`` (cat + narrow)
+    rebuilds them. Collective: one all-gather per unit that holds frozen parameters."""
+    z = engine.optimizer
+    shapes, frags = OrderedDict(), OrderedDict()
+    by_id = {}
+    for u in z.units:
+        frozen = [i for i, p in enumerate(u.params) if not p.requires_grad]
+        if not frozen:
+            continue
+        if u.world > 1 and not u.persistent and u.param_shard is not None:
+            full = z._gather_shard_tensor(u, u.param_shard)
+        elif u.param_shard is not None and not u.persistent:
+            full = u.param_shard
+        else:
+            full = None
+        world, rank = max(u.world, 1), (z._rank_of(u.group_key) if u.world > 1 else 0)
+        for i in frozen:
+            p, n, o = u.params[i], u.numels[i], u.offsets[i]
+            flat = full[o:o + n] if full is not None else p.detach().reshape(-1)
+            per = _cdiv(n, world)
+            a, b = min(rank * per, n), min((rank + 1) * per, n)
+            frag = torch.zeros(per, dtype=flat.dtype)
+            if b > a:
+                frag[:b - a].copy_(flat[a:b])
+            by_id[id(p)] = (torch.Size(u.shapes[i]), frag)
+    for name, p in engine.module.named_parameters():
+        if not p.requires_grad:
+            if id(p) in by_id:
+                shapes[name], frags[name] = by_id[id(p)]
+            else:  # not managed by a unit (should not happen at stage 3): keep the tensor itself
+                shapes[name], frags[name] = torch.Size(p.shape), p.detach().cpu().clone()
+    return shapes, frags
+
+
+@torch.no_grad()
+def _zero3_load_persistent_from_module(engine, ckpt):
+    """No optimizer shard files: replicated (persistent) parameters are in ``ckpt['module']``; copy them into the
+    live tensors before the flat shards are refreshed from the parameters."""
+    z = engine.optimizer
+    module_sd = ckpt.get("module") or {}
+    names = {id(p): n for n, p in engine.module.named_parameters()}
+    for u in z.units:
+        if not u.persistent:
+            continue
+        for i, p in enumerate(u.params):
+            src = module_sd.get(names.get(id(p)))
+            if src is not None and src.numel() == u.numels[i] and p.numel() == u.numels[i]:
+                p.data.copy_(src.to(p.device).view_as(p))
+
+
+@torch.no_grad()
+def _zero3_load_frozen(engine, ckpt):
+    """Inverse of :func:`_zero3_frozen_fragments` (collective: one all-reduce per unit with frozen parameters).
+    Writes the fp32 master region, the low-precision shard and, for resident units, the gathered copy."""
+    z = engine.optimizer
+    frags = ckpt.get(FROZEN_PARAM_FRAGMENTS) or {}
+    if not frags:
+        return
+    names = {id(p): n for n, p in engine.module.named_parameters()}
+    for u in z.units:
+        frozen = [i for i, p in enumerate(u.params) if not p.requires_grad and names.get(id(p)) in frags]
+        if not frozen:
+            continue
+        world, rank = max(u.world, 1), (z._rank_of(u.group_key) if u.world > 1 else 0)
+        full = torch.zeros(u.numel_padded, dtype=torch.float32, device=u.device)
+        for i in frozen:
+            n, o = u.numels[i], u.offsets[i]
+            frag = frags[names[id(u.params[i])]].reshape(-1)
+            per = _cdiv(n, world)
+            a, b = min(rank * per, n), min((rank + 1) * per, n)
+            if frag.numel() == n and world > 1:  # unpartitioned fragment (saved by a persistent/replicated param)
+                if rank == 0:
+                    full[o:o + n].copy_(frag.to(u.device, torch.float32))
+            elif b > a and frag.numel() >= b - a:
+                full[o + a:o + b].copy_(frag[:b - a].to(u.device, torch.float32))
+        if u.world > 1:
+            dist.all_reduce(full, group=u.dp_group)
+        lo, hi = u.shard_range(rank if u.world > 1 else 0)
+        st = z.storages[(u.group_key, u.dtype)]
+        for i in frozen:
+            n, o = u.numels[i], u.offsets[i]
+            a, b = max(o, lo), min(o + n, hi)
+            if b > a:
+                if u.master_shard is not None:
+                    u.master_shard[a - lo:b - lo].copy_(full[a:b].to(u.master_shard.dtype))
+                if u.param_shard is not None:
+                    u.param_shard[a - lo:b - lo].copy_(full[a:b].to(u.param_shard.dtype))
+                if st.lp is not None:
+                    st.lp[u.shard_offset + a - lo:u.shard_offset + b - lo].copy_(full[a:b].to(st.lp.dtype))
+            if u.full_param is not None:
+                u.full_param[o:o + n].copy_(full[o:o + n].to(u.full_param.dtype))
+
+
 def _zero_optimizer_state(engine):
     """Reference-layout optimizer state dict for this rank."""
     z = engine.optimizer
@@ -119,6 +220,12 @@ def _zero_optimizer_state(engine):
                 state_keys.add(k)
     if getattr(z, "_nvme", None) is not None:  # moments swapped out to NVMe are not in optimizer.state
         state_keys.update(z._nvme_names)
+    if z._shard_world > 1 and dist.is_initialized():
+        # a rank whose shards hold only frozen runs has no state tensors: agree on the key set before the
+        # per-key collectives below
+        gathered = [None] * z._shard_world
+        dist.all_gather_object(gathered, sorted(state_keys), group=z._shard_group)
+        state_keys = set().union(*[set(g or ()) for g in gathered])
     exported = {k: lay.export(lambda u, k=k: z._state_shard(u, k)) for k in sorted(state_keys)}
     # per-group scalar state (step)
     base_state = {}
@@ -208,10 +315,16 @@ def save_engine_checkpoint(engine, save_dir, tag=None, client_state=None, save_l
             lay = ReferenceLayout(engine.optimizer)
         param_shapes = lay.param_shapes() if lay is not None else None
         frozen_shapes, frozen_frags = OrderedDict(), OrderedDict()
-        for n, p in engine.module.named_parameters():
-            if not p.requires_grad:
-                frozen_shapes[n] = torch.Size(getattr(p, "ds_shape", p.shape))
-                frozen_frags[n] = p.detach().cpu().clone() if p.numel() > 0 else torch.empty(0)
+        if exclude_frozen_parameters:
+            pass
+        elif engine.zero_optimization_partition_weights() and engine.optimizer is not None \
+                and hasattr(engine.optimizer, "units"):
+            frozen_shapes, frozen_frags = _zero3_frozen_fragments(engine)  # collective
+        else:
+            for n, p in engine.module.named_parameters():
+                if not p.requires_grad:
+                    frozen_shapes[n] = torch.Size(getattr(p, "ds_shape", p.shape))
+                    frozen_frags[n] = p.detach().cpu().clone()
         state = dict(module=module_sd, buffer_names=buffer_names, optimizer=None, param_shapes=param_shapes,
                      frozen_param_shapes=frozen_shapes or None, frozen_param_fragments=frozen_frags or None,
                      shared_params=_shared_params(engine.module),
@@ -307,6 +420,8 @@ def load_engine_checkpoint(engine, load_dir, tag=None, load_module_strict=True, 
         for name, val in sd.items():
             if name in bufs and bufs[name] is not None and val.numel() == bufs[name].numel():
                 bufs[name].data.copy_(val.to(bufs[name].device))
+        if engine.optimizer is not None and hasattr(engine.optimizer, "units") and not have_zero_files:
+            _zero3_load_persistent_from_module(engine, ckpt)
 
     engine.loaded_checkpoint_dp_world_size = ckpt.get("dp_world_size")
     engine.loaded_checkpoint_mp_world_size = ckpt.get("mp_world_size")
@@ -332,6 +447,8 @@ def load_engine_checkpoint(engine, load_dir, tag=None, load_module_strict=True, 
             engine.optimizer.refresh_lp_from_params() if not zero3 else None
         else:
             engine.optimizer.refresh_lp_from_params()
+        if zero3 and hasattr(engine.optimizer, "units"):
+            _zero3_load_frozen(engine, ckpt)
 
     reserved = {"module", "buffer_names", "optimizer", "param_shapes", "frozen_param_shapes", "frozen_param_fragments",
                 "shared_params", "lr_scheduler", "data_sampler", "random_ltd", "sparse_tensor_module_names",
@@ -363,8 +480,13 @@ def _load_zero_state(engine, zsd, load_optimizer_states, load_from_fp32=True):
         fp32 = _regroup_stage3(fp32, lay)
     if load_from_fp32:
 
+        n_opt_groups = len(z.optimizer.param_groups)
+
         def write_master(u, shard):
-            u.master_shard.copy_(shard.to(u.master_shard.dtype))
+            # only the regions of optimizer-managed parameters: frozen parameters are not in the fp32 flats
+            for run in u.runs_in_shard():
+                if run.group_idx < n_opt_groups:
+                    u.master_shard[run.start:run.end].copy_(shard[run.start:run.end].to(u.master_shard.dtype))
 
         lay.import_(fp32, write_master)
         z._lp_written_by_step = False

@@ -340,21 +340,44 @@ class SymmContext:
 
 
 class SymmSlotPool:
-    """Round-robin pool of symmetric buffers (gradient buckets / a2a staging). Before a slot is rewritten the
-    producer stream waits for the peers' DONE flag of the collective that last read it."""
+    """Pool of symmetric buffers (gradient buckets / a2a staging) with ownership tracking. A slot handed out by
+    ``acquire`` stays busy until ``release``; before a released slot is rewritten the producer stream waits for the
+    peers' DONE flag of the collective that last read it. ``acquire`` returns None when every slot is held (a unit
+    whose gradients are still incomplete keeps its slot until the backward epilogue): the caller then uses a private
+    buffer and the NCCL path. Every rank sees the same hook order, so every rank takes the same decision."""
 
     def __init__(self, ctx: SymmContext, slot_bytes, n_slots=3, kind="rs"):
         self.ctx, self.kind = ctx, kind
         self.slots = [ctx.alloc(slot_bytes) for _ in range(n_slots)]
+        self.busy = [False] * n_slots
         self.next = 0
         self.slot_bytes = self.slots[0].nbytes
 
     def acquire(self):
-        """Next slot; enqueues the DONE wait of its previous use on the current stream."""
-        s = self.slots[self.next]
-        self.next = (self.next + 1) % len(self.slots)
+        """Next free slot in round-robin order (None if all are held); enqueues the DONE wait of its previous use
+        on the current stream."""
+        n = len(self.slots)
+        for k in range(n):
+            i = (self.next + k) % n
+            if not self.busy[i]:
+                break
+        else:
+            return None
+        self.busy[i] = True
+        self.next = (i + 1) % n
+        s = self.slots[i]
         if self.kind == "rs":
             self.ctx.wait_rs_done(getattr(s, "last_rs_epoch", 0))
         else:
             self.ctx.wait_a2a_done(getattr(s, "last_a2a_epoch", 0))
         return s
+
+    def release(self, slot):
+        """The holder has enqueued the collective that consumes ``slot`` (or dropped it); it may be handed out again."""
+        for i, s in enumerate(self.slots):
+            if s is slot:
+                self.busy[i] = False
+                return
+
+    def n_free(self):
+        return self.busy.count(False)

@@ -139,8 +139,43 @@ def top1gating(logits, capacity_factor, min_capacity, used_token=None, noisy_gat
 
 
 def top2gating(logits, capacity_factor, min_capacity, drop_tokens=True, ep_group=None, top2_2nd_expert_sampling=True):
-    return topkgating(logits, 2, capacity_factor, min_capacity, drop_tokens, ep_group, "position",
-                      "RSample" if top2_2nd_expert_sampling else None, False, None, normalize=True)
+    """Top-2 gating with the reference's exact selection rules (``moe/sharded_moe.py:341-404``): expert 1 is the
+    noise-free argmax of the gates; expert 2 is the argmax of the (optionally Gumbel-perturbed) logits with expert 1
+    masked out; all second choices queue behind all first choices of the same expert
+    (``locations2 += sum(mask1)``); the balancing loss uses the first-choice mask only. Same return tuple as
+    :func:`topkgating`."""
+    S, E = logits.shape
+    logits = logits.float()
+    gates = F.softmax(logits, dim=1)
+    idx1 = torch.argmax(gates, dim=1)
+    mask1 = F.one_hot(idx1, num_classes=E)
+    sel = logits + gumbel_rsample(logits.shape, device=logits.device) if top2_2nd_expert_sampling else logits
+    idx2 = torch.argmax(sel.masked_fill(mask1.bool(), float("-inf")), dim=1)
+    mask2 = F.one_hot(idx2, num_classes=E)
+    loc1 = torch.cumsum(mask1, dim=0) - 1
+    loc2 = torch.cumsum(mask2, dim=0) - 1 + mask1.sum(dim=0, keepdim=True)
+    me = gates.mean(dim=0)
+    ce = mask1.float().mean(dim=0)
+    l_aux = torch.mean(me * ce) * E * E
+    exp_counts = (mask1 + mask2).sum(dim=0).detach()
+    if drop_tokens:
+        capacity = _capacity(S * 2, E, capacity_factor, min_capacity)
+    else:
+        new_cap = exp_counts.max()
+        if ep_group is not None and dist.is_initialized() and dist.get_world_size(ep_group) > 1:
+            dist.all_reduce(new_cap, op=dist.ReduceOp.MAX, group=ep_group)
+        capacity = int(new_cap)
+    slot1 = loc1.gather(1, idx1.view(-1, 1)).squeeze(1)
+    slot2 = loc2.gather(1, idx2.view(-1, 1)).squeeze(1)
+    ok1, ok2 = slot1 < capacity, slot2 < capacity
+    g1 = gates.gather(1, idx1.view(-1, 1)).squeeze(1) * ok1.to(gates.dtype)
+    g2 = gates.gather(1, idx2.view(-1, 1)).squeeze(1) * ok2.to(gates.dtype)
+    denom = (g1 + g2).clamp(min=torch.finfo(gates.dtype).eps)
+    top_idx = torch.stack([idx1, idx2], dim=1)
+    slot_idx = torch.stack([torch.where(ok1, slot1, torch.full_like(slot1, -1)),
+                            torch.where(ok2, slot2, torch.full_like(slot2, -1))], dim=1)
+    w = torch.stack([g1 / denom, g2 / denom], dim=1)
+    return l_aux, top_idx, slot_idx, w, capacity, exp_counts
 
 
 class TopKGate(nn.Module):

@@ -222,7 +222,7 @@ def lamb_step(p, g, m, v, lp, h, coeffs_out):
         lib().dsb200_lamb_step(_ptr(p), _ptr(g), _ptr(m), _ptr(v), _ptr(lp), p.numel(), (_dt(lp) if lp is not None else 0),
                                _ptr(scratch), _ptr(scratch[4096:]), h["lr"], h["beta1"], h["beta2"], h["eps"], h["wd"],
                                h["bc1"], h["bc2"], int(h["mode"]), h["max_coeff"], h["min_coeff"], _stream()), "lamb")
-    coeffs_out.append(scratch[4096 + 2])
+    coeffs_out.append(scratch[4096 + 2].clone())  # the scratch word is reused by the next launch
 
 
 # ---------------------------------------------------------------------------------------------------------

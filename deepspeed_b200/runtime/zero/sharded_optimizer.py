@@ -477,8 +477,12 @@ class ZeroShardedOptimizer:
         if u.full_grad is None:
             # no memset: every parameter overwrites its own region; alignment gaps / params that never produce a
             # gradient are zeroed just before the reduction (_zero_unwritten)
+            u._slot = None
             if self._grad_pool is not None and u.world > 1:
-                u._slot = self._grad_pool.acquire()  # waits (on this stream) until peers released the slot
+                # waits (on this stream) until peers released the slot; None when every slot is still held by a
+                # unit with incomplete gradients -> private buffer + NCCL reduction below
+                u._slot = self._grad_pool.acquire()
+            if u._slot is not None:
                 u.full_grad = u._slot.view(u.numel_padded, self._full_grad_dtype())
             elif (u.world == 1 and u.replica_world == 1 and not getattr(u, "_shard_has_data", False)
                   and u.grad_shard.dtype == self._full_grad_dtype() and u.grad_shard.numel() == u.numel_padded
@@ -562,7 +566,7 @@ class ZeroShardedOptimizer:
             if getattr(u, "_slot", None) is not None and self.symm is not None and self._fused_adam and first:
                 # ONE kernel: NVLink loads + fp32 sum + average + AdamW on the owner shard + bf16 weight write
                 self._rs_adam_unit(u, div)
-                u._slot = None
+                self._release_slot(u)
             elif getattr(u, "_slot", None) is not None and self.symm is not None:
                 # ONE kernel: NVLink loads from every peer's bucket + fp32 sum + average + cast + accumulate
                 verify = _SYMM_VERIFY and first
@@ -578,7 +582,7 @@ class ZeroShardedOptimizer:
                     if not err <= tol:
                         raise RuntimeError(f"DSB200_SYMM_VERIFY: fused reduce-scatter of {u.name} differs from NCCL "
                                            f"by {err} (tolerance {tol}): ordering bug in the flag protocol?")
-                u._slot = None
+                self._release_slot(u)
             else:
                 self._reduce_unit_nccl(u, full, div, first)
             u._shard_has_data = True
@@ -591,6 +595,11 @@ class ZeroShardedOptimizer:
             u.full_grad = None
             u.has_grad_data = False
             u._accumulated = set()
+
+    def _release_slot(self, u):
+        if getattr(u, "_slot", None) is not None and self._grad_pool is not None:
+            self._grad_pool.release(u._slot)
+        u._slot = None
 
     def _reduce_unit_nccl(self, u, full, div, first):
         """Baseline path: (pre-divide) -> NCCL reduce-scatter / all-reduce -> scale + cast + accumulate."""
@@ -1032,6 +1041,7 @@ class ZeroShardedOptimizer:
         for u in self.units:
             for p in u.params:
                 p.grad = None
+            self._release_slot(u)
             u.full_grad = None
             u.has_grad_data = False
             u._accumulated = set()

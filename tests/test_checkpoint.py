@@ -116,3 +116,86 @@ def test_universal_checkpoint_dp_reshape(stage, tmp_path):
     for n in full:
         torch.testing.assert_close(lfull[n], full[n], rtol=0, atol=0)
         torch.testing.assert_close(lm[n], m[n], rtol=0, atol=1e-7)
+
+
+def _frozen_model(seed):
+    torch.manual_seed(seed)
+    model = SimpleModel(HID, 3)
+    # frozen: one large (partitioned) weight and one small (persistent, replicated) bias -- LoRA-style fine-tuning
+    model.linears[1].weight.requires_grad_(False)
+    model.linears[0].bias.requires_grad_(False)
+    return model
+
+
+def _frozen_values(eng, model):
+    import deepspeed_b200 as ds
+    out = {}
+    for n, p in model.named_parameters():
+        with ds.zero.GatheredParameters([p]):
+            out[n] = p.detach().float().cpu().clone()
+    return out
+
+
+def _train_and_save_frozen(ckpt_dir):
+    import deepspeed_b200 as ds
+    model = _frozen_model(0)
+    eng, _, _, _ = ds.initialize(model=model, model_parameters=[p for p in model.parameters() if p.requires_grad],
+                                 config=_cfg(3))
+    rank, world = ds.comm.get_rank(), ds.comm.get_world_size()
+    batches = random_batches(3 * world, 4, HID, "cpu")
+    for i in range(3):
+        x, y = batches[i * world + rank]
+        loss = eng(x, y)
+        eng.backward(loss)
+        eng.step()
+    eng.save_checkpoint(ckpt_dir, tag="t1")
+    return _frozen_values(eng, model)
+
+
+def _load_frozen(ckpt_dir):
+    import deepspeed_b200 as ds
+    model = _frozen_model(321)  # different init, frozen weights included: everything must come from the checkpoint
+    eng, _, _, _ = ds.initialize(model=model, model_parameters=[p for p in model.parameters() if p.requires_grad],
+                                 config=_cfg(3))
+    path, _ = eng.load_checkpoint(ckpt_dir, tag="t1")
+    assert path is not None
+    vals = _frozen_values(eng, model)
+    x, y = random_batches(1, 4, HID, "cpu")[0]
+    loss = eng(x, y)  # the restored shards must also drive a forward/backward
+    eng.backward(loss)
+    eng.step()
+    return vals
+
+
+def test_zero3_frozen_params_roundtrip(tmp_path):
+    """ZeRO-3 with frozen parameters: fragments are saved in the reference layout (this rank's ceil(n/world) slice),
+    both zero_to_fp32 scripts rebuild them, and load restores them (reference engine.py:5292-5306,
+    zero_to_fp32.py _zero3_merge_frozen_params)."""
+    d = str(tmp_path / "ck")
+    want = run_distributed(_train_and_save_frozen, 2, args=(d, ))[0]
+    frozen = ["linears.1.weight", "linears.0.bias"]
+    ms = torch.load(os.path.join(d, "t1", "zero_pp_rank_0_mp_rank_00_model_states.pt"), weights_only=False)
+    assert set(ms["frozen_param_shapes"]) == set(frozen)
+    assert ms["frozen_param_fragments"]["linears.1.weight"].numel() == HID * HID // 2
+    for names in ms["param_shapes"]:
+        assert not set(names) & set(frozen)
+    got = run_distributed(_load_frozen, 2, args=(d, ))[0]
+    for n in want:
+        torch.testing.assert_close(got[n], want[n], rtol=0, atol=0)
+    out = str(tmp_path / "fp32.pt")
+    subprocess.check_call([sys.executable, os.path.join(d, "t1", "zero_to_fp32.py"), d, out], cwd=str(tmp_path),
+                          env=dict(os.environ, PYTHONPATH=""))
+    sd = torch.load(out, weights_only=False)
+    for n in frozen:
+        torch.testing.assert_close(sd[n], want[n], rtol=0, atol=0)
+    ref = os.path.join(REPO, "baseline", "_ref", "deepspeed", "utils", "zero_to_fp32.py")
+    if os.path.exists(ref):
+        out2 = str(tmp_path / "ref_out")
+        subprocess.check_call([sys.executable, "-m", "deepspeed.utils.zero_to_fp32", d, out2], cwd=str(tmp_path),
+                              env=dict(os.environ, PYTHONPATH=os.path.join(REPO, "baseline", "_ref")))
+        ref_sd = {}
+        for f in os.listdir(out2):
+            if f.endswith(".bin"):
+                ref_sd.update(torch.load(os.path.join(out2, f), weights_only=False))
+        for n in want:
+            torch.testing.assert_close(ref_sd[n].float(), want[n], rtol=0, atol=1e-6)

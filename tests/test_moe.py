@@ -1,5 +1,6 @@
 """MoE: capacity (DS-MoE ``MoE``) and dropless (AutoEP) layers; expert parallel (ep=2) matches ep=1
 (reference tests/unit/v1/moe/*)."""
+import pytest
 import torch
 
 from common import run_distributed
@@ -69,3 +70,57 @@ def test_autoep_expert_parallel_matches_single():
         # every rank saw the same batch, so each local expert accumulated both ranks' (identical) tokens: 2x
         torch.testing.assert_close(g, 2 * single[1][rank * nl:(rank + 1) * nl], rtol=1e-3, atol=1e-5)
         torch.testing.assert_close(gr, single[2], rtol=1e-3, atol=1e-5)
+
+
+def _dense_top2(logits, capacity_factor, min_capacity, noise):
+    """Dense restatement of the reference top-2 gate (moe/sharded_moe.py:341-432): combine weights [S, E, C]."""
+    import math
+    import torch.nn.functional as F
+    S, E = logits.shape
+    gates = F.softmax(logits, dim=1)
+    i1 = gates.argmax(1)
+    m1 = F.one_hot(i1, E)
+    noisy = logits + noise if noise is not None else logits
+    i2 = noisy.masked_fill(m1.bool(), float("-inf")).argmax(1)
+    m2 = F.one_hot(i2, E)
+    l1 = torch.cumsum(m1, 0) - 1
+    l2 = torch.cumsum(m2, 0) - 1 + m1.sum(0, keepdim=True)
+    l_aux = (gates.mean(0) * m1.float().mean(0)).mean() * E * E
+    cap = max(int(math.ceil(S / E * capacity_factor * 2)), min_capacity)
+    m1 = m1 * (l1 < cap)
+    m2 = m2 * (l2 < cap)
+    s1, s2 = (l1 * m1).sum(1), (l2 * m2).sum(1)
+    g1, g2 = (gates * m1).sum(1), (gates * m2).sum(1)
+    den = (g1 + g2).clamp(min=torch.finfo(gates.dtype).eps)
+    comb = torch.zeros(S, E, cap)
+    for s in range(S):
+        if m1[s].any():
+            comb[s, i1[s], s1[s]] += g1[s] / den[s]
+        if m2[s].any():
+            comb[s, i2[s], s2[s]] += g2[s] / den[s]
+    return l_aux, comb, cap
+
+
+@pytest.mark.parametrize("sampling", [False, True])
+def test_top2_gating_matches_reference_rules(sampling):
+    from deepspeed_b200.moe import sharded_moe as sm
+    torch.manual_seed(7)
+    S, E = 64, 4
+    logits = torch.randn(S, E) * 2.0
+    logits[:, 0] += 1.5  # skew towards expert 0 so that the capacity limit drops tokens
+    noise = None
+    if sampling:
+        torch.manual_seed(99)
+        noise = sm.gumbel_rsample(logits.shape, device=logits.device)
+        torch.manual_seed(99)  # top2gating draws the same noise
+    l_aux, idx, slot, w, cap, counts = sm.top2gating(logits.clone(), 0.5, 4, True, None, sampling)
+    want_aux, want, want_cap = _dense_top2(logits.clone(), 0.5, 4, noise)
+    assert cap == want_cap
+    torch.testing.assert_close(l_aux, want_aux)
+    got = torch.zeros(S, E, cap)
+    for s in range(S):
+        for j in range(2):
+            if slot[s, j] >= 0:
+                got[s, idx[s, j], slot[s, j]] += w[s, j]
+    assert (slot < 0).any(), "test must exercise dropped tokens"
+    torch.testing.assert_close(got, want)

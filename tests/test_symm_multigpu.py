@@ -111,6 +111,49 @@ def _train(fused, steps, extra=None, clip=1.0, stage=3):
     return losses
 
 
+def _train_unused(fused, steps):
+    """6 layers (> 3 pool slots) and a parameter in the LAST layer that never receives a gradient: that unit takes
+    its slot first in backward and holds it until the epilogue while the other units cycle through the pool."""
+    import deepspeed_b200 as ds
+    from deepspeed_b200.models import LlamaConfig, LlamaForCausalLM
+    dev = torch.device("cuda", torch.cuda.current_device())
+    torch.manual_seed(0)
+    cfg = LlamaConfig(vocab_size=2048, hidden_size=256, intermediate_size=512, num_hidden_layers=6,
+                      num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=256)
+    model = LlamaForCausalLM(cfg, device=dev)
+    model.model.layers[-1].never_used = torch.nn.Parameter(torch.ones(4096, device=dev, dtype=torch.bfloat16))
+    eng, _, _, _ = ds.initialize(model=model, config={
+        "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True}, "gradient_clipping": 1.0,
+        "optimizer": {"type": "AdamW", "params": {"lr": 1e-3, "weight_decay": 0.0}},
+        "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 1000, "fused_collectives": fused,
+                              "fused_rs_adam": False}})
+    assert (eng.optimizer.symm is not None) == fused
+    assert len(eng.optimizer.units) > 3
+    torch.manual_seed(1 + ds.comm.get_rank())
+    losses, held = [], 0
+    for _ in range(steps):
+        ids = torch.randint(0, 2048, (2, 128), device=dev)
+        loss = eng(ids, labels=ids)
+        eng.backward(loss)
+        if fused:
+            assert eng.optimizer._grad_pool.n_free() == 3, "a slot leaked past the backward epilogue"
+        eng.step()
+        losses.append(float(loss.detach()))
+    norm = float(eng.get_global_grad_norm() or 0.0)
+    return losses, norm
+
+
+@needs2
+def test_slot_pool_with_pending_unit_matches_nccl_path():
+    a = run_distributed(_train_unused, 2, args=(True, 6))
+    b = run_distributed(_train_unused, 2, args=(False, 6))
+    (la, na), (lb, nb) = a[0], b[0]
+    for x, y in zip(la, lb):
+        assert abs(x - y) < 5e-2, (la, lb)
+    assert abs(na - nb) <= 5e-2 * max(1.0, nb), (na, nb)
+    assert la[-1] < la[0]
+
+
 @needs2
 def test_zero3_fused_collectives_match_nccl_path():
     a = run_distributed(_train, 2, args=(True, 6))
