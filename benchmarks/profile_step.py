@@ -23,9 +23,10 @@ def main():
     os.environ.setdefault("PYTORCH_CUDA_ALLOC_CONF", "expandable_segments:True")
     for k, v in dict(RANK="0", WORLD_SIZE="1", LOCAL_RANK="0", MASTER_ADDR="127.0.0.1", MASTER_PORT="29519").items():
         os.environ.setdefault(k, v)
-    torch.cuda.set_device(0)
-    torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", 0))
-    step, _, _ = bench.build_ours(args, torch, 1)
+    world, rank, lr = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(lr)
+    torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", lr))
+    step, _, _ = bench.build_ours(args, torch, world)
     ids = torch.randint(0, 128256, (1, args.seq), device="cuda")
     for _ in range(3):
         step(ids)
@@ -36,15 +37,25 @@ def main():
             step(ids)
         torch.cuda.synchronize()
     agg = collections.defaultdict(lambda: [0.0, 0])
+    t_min, t_max = None, None
     for ev in prof.events():
         if ev.device_type == torch.autograd.DeviceType.CUDA:
             agg[ev.name][0] += ev.device_time_total / 2e3
             agg[ev.name][1] += 1
+            tr = ev.time_range
+            t_min = tr.start if t_min is None else min(t_min, tr.start)
+            t_max = tr.end if t_max is None else max(t_max, tr.end)
+    if rank != 0:
+        torch.distributed.barrier()
+        return
     rows = sorted(agg.items(), key=lambda kv: -kv[1][0])
     total = sum(v[0] for v in agg.values())
-    out = {"total_kernel_ms_per_step": round(total, 2),
+    out = {"world": world, "total_kernel_ms_per_step": round(total, 2),
+           "span_ms_per_step": round((t_max - t_min) / 2e3, 2) if t_min is not None else None,
            "top": [{"kernel": k[:110], "ms_per_step": round(v[0], 3), "launches_per_step": v[1] // 2} for k, v in rows[:40]]}
     print(json.dumps(out, indent=1))
+    if world > 1:
+        torch.distributed.barrier()
 
 
 if __name__ == "__main__":

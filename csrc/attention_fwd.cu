@@ -1,0 +1,477 @@
+// Flash-attention forward on the 5th-generation tensor cores (bf16, head_dim 128, optional causal mask, GQA).
+//
+//   O[b, i, h, :] = softmax_j(scale * Q[b, i, h, :] . K[b, j, h / (H/Hkv), :]) V[b, j, h / (H/Hkv), :]
+//   LSE[b, h, i]  = log sum_j exp(scale * q.k)
+//
+// Operands stay in the projection layout [batch, seq, heads, 128] with arbitrary row / batch strides (so the views of
+// a fused QKV projection are consumed in place); no transposes, no materialised scores.
+//
+// Reference: the reference has no attention kernel of its own for training; its models call the framework's SDPA /
+// flash-attn (runtime/sequence_parallel/ulysses_sp.py:50, sequence/fpdt_layer.py:238-269), and its own fused softmax
+// kernels (csrc/transformer/softmax_kernels.cu) materialise the [S, S] scores. This is the B200-native replacement.
+//
+// One CTA = one (batch, head) and TWO 128-row query tiles that ping-pong on the tensor pipe (while the softmax warps of
+// one tile run, the MMAs of the other tile execute). 320 threads:
+//   warp 0      TMA producer: Q tiles once, then K_j / V_j blocks (128 keys) through two 2-stage rings (3-D tensor
+//               maps [batch, seq, heads*128], 128-byte swizzle, OOB rows zero-filled)
+//   warp 1      MMA issuer (one elected lane): S_t = Q_t K_j^T (SS form, both operands K-major) into TMEM,
+//               O_t += P_t V_j with P read straight from TMEM (TS form) and V as an MN-major smem operand
+//   warps 2-5   softmax of tile 0, warps 6-9 softmax of tile 1: one thread per query row (TMEM lane == row, so row
+//               max / row sum need no shuffles): tcgen05.ld S -> online softmax in the log2 domain -> bf16 P written
+//               back over S with tcgen05.st -> lazy rescale of O in TMEM (only when the row max grew by > 2^8)
+// TMEM (512 columns): S0 | S1 | O0 | O1, 128 fp32 columns each; P_t aliases the first 64 columns of S_t.
+#include "gemm_common.cuh"
+
+namespace {
+
+constexpr int FA_D = 128;          // head dim
+constexpr int FA_BM = 128;         // query rows per tile
+constexpr int FA_BN = 128;         // keys per block
+constexpr int FA_THREADS = 320;
+constexpr int FA_TILE_BYTES = FA_BM * FA_D * 2;  // 32 KB: two 16 KB swizzle-128B boxes (d halves)
+constexpr int FA_HALF_BYTES = FA_TILE_BYTES / 2;
+constexpr int FA_KV_STAGES = 2;
+constexpr int FA_SMEM_BYTES = (2 + 2 * FA_KV_STAGES) * FA_TILE_BYTES + 1024 + 256;
+
+struct FaBars {
+    uint64_t q_full;
+    uint64_t k_full[FA_KV_STAGES], k_empty[FA_KV_STAGES];
+    uint64_t v_full[FA_KV_STAGES], v_empty[FA_KV_STAGES];
+    uint64_t s_full[2], p_full[2], o_full[2];
+    uint32_t tmem_base;
+};
+
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+
+// MN-major, 128B-swizzled operand: a [k rows x 64 elements] box per 64-element slab of the M/N extent; rows 128 B
+// apart, 8-row groups 1024 B apart (stride byte offset), slabs `slab_bytes` apart (leading byte offset).
+__device__ __forceinline__ uint64_t make_smem_desc_mn(uint32_t smem_addr, uint32_t slab_bytes)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((slab_bytes >> 4) & 0x3FFF) << 16;  // leading byte offset
+    d |= (uint64_t)(1024 >> 4) << 32;                   // stride byte offset
+    d |= (uint64_t)1 << 46;                             // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;                             // SWIZZLE_128B
+    return d;
+}
+
+// kind::f16, A = B = bf16, D = f32; b_mn: B operand is MN-major
+__host__ __device__ constexpr uint32_t make_idesc_ex(int m, int n, int a_mn, int b_mn)
+{
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+           ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+// D[tmem] (+)= A[tmem] * B[smem]
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                             uint32_t accumulate)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+__device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&r)[16])
+{
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+        "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&r)[32])
+{
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+        "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+        "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+        "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ float fast_exp2(float x)
+{
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+struct FaParams {
+    __nv_bfloat16* o;
+    float* lse;  // [B, H, Sq]
+    int B, Sq, Skv, H, Hkv;
+    int64_t o_row_stride, o_batch_stride;
+    float scale_log2;  // softmax scale * log2(e)
+    int causal;
+    int pairs;  // ceil(Sq / 256)
+};
+
+__global__ void __launch_bounds__(FA_THREADS, 1)
+flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
+                      const __grid_constant__ CUtensorMap map_v, const FaParams prm)
+{
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* q_smem = tiles;                                   // 2 tiles
+    uint8_t* k_smem = tiles + 2 * FA_TILE_BYTES;               // FA_KV_STAGES
+    uint8_t* v_smem = k_smem + FA_KV_STAGES * FA_TILE_BYTES;   // FA_KV_STAGES
+    FaBars* bars = reinterpret_cast<FaBars*>(v_smem + FA_KV_STAGES * FA_TILE_BYTES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    // work item: heavy (late) query tiles first; consecutive CTAs share a KV head (L2 reuse)
+    const int bh = prm.B * prm.H;
+    const int pair = prm.pairs - 1 - (int)(blockIdx.x / bh);
+    const int rem = (int)(blockIdx.x % bh);
+    const int b = rem / prm.H, h = rem % prm.H;
+    const int hk = h / (prm.H / prm.Hkv);
+    const int q0 = pair * 2 * FA_BM;  // first query row of tile 0
+    // number of key blocks per tile
+    const int nb_all = (prm.Skv + FA_BN - 1) / FA_BN;
+    int nb_t[2];
+#pragma unroll
+    for (int t = 0; t < 2; t++) {
+        const int row0 = q0 + t * FA_BM;
+        if (row0 >= prm.Sq) {
+            nb_t[t] = 0;
+        } else if (prm.causal) {
+            const int last_row = min(row0 + FA_BM, prm.Sq) - 1 + (prm.Skv - prm.Sq);  // bottom-right aligned
+            nb_t[t] = max(0, min(nb_all, last_row / FA_BN + 1));
+        } else {
+            nb_t[t] = nb_all;
+        }
+    }
+    const int nb = max(nb_t[0], nb_t[1]);
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bars->q_full, 1);
+        for (int s = 0; s < FA_KV_STAGES; s++) {
+            mbar_init(&bars->k_full[s], 1);
+            mbar_init(&bars->k_empty[s], 1);
+            mbar_init(&bars->v_full[s], 1);
+            mbar_init(&bars->v_empty[s], 1);
+        }
+        for (int t = 0; t < 2; t++) {
+            mbar_init(&bars->s_full[t], 1);
+            mbar_init(&bars->p_full[t], 4);  // one arrive per softmax warp
+            mbar_init(&bars->o_full[t], 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&bars->tmem_base)),
+                     "n"(512)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+    // column offsets
+    constexpr uint32_t COL_S0 = 0, COL_O0 = 256;
+
+    if (warp == 0) {
+        // ============================ TMA producer ============================
+        if (lane == 0 && nb > 0) {
+            mbar_expect_tx(&bars->q_full, 2 * FA_TILE_BYTES);
+#pragma unroll
+            for (int t = 0; t < 2; t++)
+#pragma unroll
+                for (int hf = 0; hf < 2; hf++)
+                    tma_load_3d(q_smem + t * FA_TILE_BYTES + hf * FA_HALF_BYTES, &map_q, &bars->q_full,
+                                h * FA_D + hf * 64, q0 + t * FA_BM, b);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int j = 0; j < nb; j++) {
+                mbar_wait(&bars->k_empty[stage], phase ^ 1);
+                mbar_expect_tx(&bars->k_full[stage], FA_TILE_BYTES);
+#pragma unroll
+                for (int hf = 0; hf < 2; hf++)
+                    tma_load_3d(k_smem + stage * FA_TILE_BYTES + hf * FA_HALF_BYTES, &map_k, &bars->k_full[stage],
+                                hk * FA_D + hf * 64, j * FA_BN, b);
+                mbar_wait(&bars->v_empty[stage], phase ^ 1);
+                mbar_expect_tx(&bars->v_full[stage], FA_TILE_BYTES);
+#pragma unroll
+                for (int hf = 0; hf < 2; hf++)
+                    tma_load_3d(v_smem + stage * FA_TILE_BYTES + hf * FA_HALF_BYTES, &map_v, &bars->v_full[stage],
+                                hk * FA_D + hf * 64, j * FA_BN, b);
+                if (++stage == FA_KV_STAGES) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ============================ MMA issuer ============================
+        if (lane == 0 && nb > 0) {
+            constexpr uint32_t idesc_qk = make_idesc_ex(FA_BM, FA_BN, 0, 0);  // S = Q K^T, both K-major
+            constexpr uint32_t idesc_pv = make_idesc_ex(FA_BM, FA_D, 0, 1);   // O += P V, V is MN-major
+            auto issue_qk = [&](int t, int kstage) {
+                const uint32_t qa = smem_u32(q_smem + t * FA_TILE_BYTES), ka = smem_u32(k_smem + kstage * FA_TILE_BYTES);
+#pragma unroll
+                for (int k = 0; k < FA_D / UMMA_K; k++) {
+                    const uint32_t off = (uint32_t)(k >> 2) * FA_HALF_BYTES + (uint32_t)(k & 3) * 32;
+                    umma_bf16(tmem_base + COL_S0 + t * 128, make_smem_desc(qa + off), make_smem_desc(ka + off), idesc_qk,
+                              k > 0 ? 1u : 0u);
+                }
+                umma_commit(&bars->s_full[t]);
+            };
+            auto issue_pv = [&](int t, int vstage, bool first) {
+                const uint32_t va = smem_u32(v_smem + vstage * FA_TILE_BYTES);
+#pragma unroll
+                for (int k = 0; k < FA_BN / UMMA_K; k++) {
+                    // A: 16 bf16 of P per row = 8 TMEM columns per k step; B: 16 key rows = 2048 bytes per k step
+                    umma_bf16_ts(tmem_base + COL_O0 + t * 128, tmem_base + COL_S0 + t * 128 + k * 8,
+                                 make_smem_desc_mn(va + k * 2048, FA_HALF_BYTES), idesc_pv, (!first || k > 0) ? 1u : 0u);
+                }
+            };
+            mbar_wait(&bars->q_full, 0);
+            mbar_wait(&bars->k_full[0], 0);
+            tc_fence_after();
+            for (int t = 0; t < 2; t++)
+                if (nb_t[t] > 0) issue_qk(t, 0);
+            umma_commit(&bars->k_empty[0]);
+            int vstage = 0;
+            uint32_t vphase = 0;
+            int kstage = 1 % FA_KV_STAGES;
+            uint32_t kphase = (FA_KV_STAGES == 1) ? 1 : 0;
+            for (int j = 0; j < nb; j++) {
+                mbar_wait(&bars->v_full[vstage], vphase);
+                const bool more = (j + 1 < nb);
+                if (more) mbar_wait(&bars->k_full[kstage], kphase);
+                tc_fence_after();
+                for (int t = 0; t < 2; t++) {
+                    if (j < nb_t[t]) {
+                        mbar_wait(&bars->p_full[t], (uint32_t)(j & 1));
+                        tc_fence_after();
+                        issue_pv(t, vstage, j == 0);
+                        if (j == nb_t[t] - 1) umma_commit(&bars->o_full[t]);
+                        if (j + 1 < nb_t[t]) issue_qk(t, kstage);
+                    }
+                }
+                umma_commit(&bars->v_empty[vstage]);
+                if (++vstage == FA_KV_STAGES) {
+                    vstage = 0;
+                    vphase ^= 1;
+                }
+                if (more) {
+                    umma_commit(&bars->k_empty[kstage]);
+                    if (++kstage == FA_KV_STAGES) {
+                        kstage = 0;
+                        kphase ^= 1;
+                    }
+                }
+            }
+        }
+    } else {
+        // ============================ softmax / correction / epilogue ============================
+        const int t = (warp - 2) >> 2;           // tile handled by this warp group
+        const int lane_base = (warp & 3) * 32;   // TMEM lanes this warp may access
+        const int row_in_tile = lane_base + lane;
+        const int row = q0 + t * FA_BM + row_in_tile;  // query index
+        const uint32_t lane_addr = (uint32_t)lane_base << 16;
+        const uint32_t s_addr = tmem_base + lane_addr + COL_S0 + t * 128;
+        const uint32_t o_addr = tmem_base + lane_addr + COL_O0 + t * 128;
+        const int my_nb = nb_t[t];
+        const int causal_off = prm.Skv - prm.Sq;
+        float m_run = -INFINITY, l_run = 0.f;
+        for (int j = 0; j < my_nb; j++) {
+            mbar_wait(&bars->s_full[t], (uint32_t)(j & 1));
+            tc_fence_after();
+            const int col0 = j * FA_BN;
+            // does this block need masking (diagonal block of the causal mask, or the tail of the key sequence)?
+            const bool need_mask = (prm.causal && (col0 + FA_BN - 1 > q0 + t * FA_BM + causal_off)) || (col0 + FA_BN > prm.Skv);
+            const int col_limit = prm.causal ? min(prm.Skv, row + causal_off + 1) : prm.Skv;  // valid keys: col < col_limit
+            // ---- pass 1: row max ----
+            float mx = -INFINITY;
+#pragma unroll 1
+            for (int c = 0; c < 4; c++) {
+                uint32_t r[32];
+                tmem_ld_32x32(s_addr + c * 32, r);
+                tmem_wait_ld();
+                if (need_mask) {
+#pragma unroll
+                    for (int i = 0; i < 32; i++)
+                        if (col0 + c * 32 + i < col_limit) mx = fmaxf(mx, __uint_as_float(r[i]));
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; i++) mx = fmaxf(mx, __uint_as_float(r[i]));
+                }
+            }
+            mx *= prm.scale_log2;  // scale > 0: max commutes with the scaling
+            float m_new = fmaxf(m_run, mx);
+            // lazy rescale: keep the stale max while the new one is within 2^8 of it (p stays <= 256)
+            if (m_run != -INFINITY && m_new - m_run <= 8.f) m_new = m_run;
+            const float alpha = (m_run == -INFINITY) ? 0.f : fast_exp2(m_run - m_new);
+            const float m_use = (m_new == -INFINITY) ? 0.f : m_new;  // fully masked row so far: avoid inf - inf
+            // ---- pass 2: p = exp2(s * scale - m), bf16 P over the S columns ----
+            float rowsum = 0.f;
+#pragma unroll 1
+            for (int c = 0; c < 4; c++) {
+                uint32_t r[32];
+                tmem_ld_32x32(s_addr + c * 32, r);
+                tmem_wait_ld();
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 16; i++) {
+                    float p0 = fast_exp2(fmaf(__uint_as_float(r[2 * i]), prm.scale_log2, -m_use));
+                    float p1 = fast_exp2(fmaf(__uint_as_float(r[2 * i + 1]), prm.scale_log2, -m_use));
+                    if (need_mask) {
+                        if (col0 + c * 32 + 2 * i >= col_limit) p0 = 0.f;
+                        if (col0 + c * 32 + 2 * i + 1 >= col_limit) p1 = 0.f;
+                    }
+                    rowsum += p0 + p1;
+                    __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
+                    pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+                }
+                tmem_st_32x16(s_addr + c * 16, pk);
+            }
+            l_run = l_run * alpha + rowsum;
+            m_run = m_new;
+            // ---- rescale O (the previous P V has completed: s_full of this block was committed after it) ----
+            if (j > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
+#pragma unroll 1
+                for (int c = 0; c < 4; c++) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(o_addr + c * 32, r);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int i = 0; i < 32; i++) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+                    tmem_st_32x32(o_addr + c * 32, r);
+                }
+            }
+            tmem_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars->p_full[t]);
+        }
+        // ---- epilogue: O / l -> bf16 -> global, LSE ----
+        if (my_nb > 0) {
+            mbar_wait(&bars->o_full[t], 0);
+            tc_fence_after();
+            const float inv_l = (l_run > 0.f) ? 1.f / l_run : 0.f;
+            const bool valid = row < prm.Sq;
+            __nv_bfloat16* orow = prm.o + (int64_t)b * prm.o_batch_stride + (int64_t)row * prm.o_row_stride + h * FA_D;
+#pragma unroll 1
+            for (int c = 0; c < 4; c++) {
+                uint32_t r[32];
+                tmem_ld_32x32(o_addr + c * 32, r);
+                tmem_wait_ld();
+                if (valid) {
+#pragma unroll
+                    for (int v4 = 0; v4 < 4; v4++) {
+                        uint4 pk;
+                        __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+                        for (int i = 0; i < 4; i++)
+                            hh[i] = __floats2bfloat162_rn(__uint_as_float(r[v4 * 8 + 2 * i]) * inv_l,
+                                                          __uint_as_float(r[v4 * 8 + 2 * i + 1]) * inv_l);
+                        *reinterpret_cast<uint4*>(orow + c * 32 + v4 * 8) = pk;
+                    }
+                }
+            }
+            if (valid && prm.lse != nullptr) {
+                const float lse = (l_run > 0.f) ? (m_run + log2f(l_run)) * 0.6931471805599453f : -INFINITY;
+                prm.lse[((int64_t)b * prm.H + h) * prm.Sq + row] = lse;
+            }
+        } else if (row < prm.Sq && q0 + t * FA_BM < prm.Sq) {
+            // no visible key at all (causal with Skv < Sq): zeros
+            __nv_bfloat16* orow = prm.o + (int64_t)b * prm.o_batch_stride + (int64_t)row * prm.o_row_stride + h * FA_D;
+            for (int i = 0; i < FA_D; i += 8) *reinterpret_cast<uint4*>(orow + i) = make_uint4(0, 0, 0, 0);
+            if (prm.lse != nullptr) prm.lse[((int64_t)b * prm.H + h) * prm.Sq + row] = -INFINITY;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+    }
+}
+
+// 3-D bf16 tensor [batch, seq, cols] (cols contiguous), box = [1, box_rows, 64], 128-byte swizzle, OOB -> zeros
+int make_map_3d(CUtensorMap* map, const void* ptr, int64_t batch, int64_t seq, int64_t cols, int64_t row_stride,
+                int64_t batch_stride, int box_rows)
+{
+    EncodeTiledFn enc = get_encode();
+    if (enc == nullptr) {
+        dsb200_set_error("cuTensorMapEncodeTiled entry point unavailable");
+        return -1;
+    }
+    cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)seq, (cuuint64_t)batch};
+    cuuint64_t strides[2] = {(cuuint64_t)row_stride * 2, (cuuint64_t)batch_stride * 2};
+    cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        dsb200_set_error("flash_attn: cuTensorMapEncodeTiled failed (16-byte aligned base, strides multiple of 8 elements)");
+        return -2;
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+// q [B, Sq, H, 128], k / v [B, Skv, Hkv, 128], o [B, Sq, H, 128] (all bf16; strides in elements, last dim contiguous,
+// heads packed 128 apart), lse [B, H, Sq] fp32 (may be null). causal: bottom-right aligned when Skv != Sq.
+int dsb200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int Sq, int Skv,
+                          int H, int Hkv, int64_t q_row_stride, int64_t q_batch_stride, int64_t k_row_stride,
+                          int64_t k_batch_stride, int64_t v_row_stride, int64_t v_batch_stride, int64_t o_row_stride,
+                          int64_t o_batch_stride, float scale, int causal, cudaStream_t stream)
+{
+    if (B <= 0 || Sq <= 0 || Skv <= 0) return 0;
+    if (H % Hkv != 0 || (o_row_stride % 8) || (o_batch_stride % 8) || ((uintptr_t)o & 15)) {
+        dsb200_set_error("flash_attn_fwd: H must be a multiple of Hkv; output must be 16-byte aligned");
+        return -1;
+    }
+    CUtensorMap mq, mk, mv;
+    if (make_map_3d(&mq, q, B, Sq, (int64_t)H * FA_D, q_row_stride, q_batch_stride, FA_BM) != 0) return -2;
+    if (make_map_3d(&mk, k, B, Skv, (int64_t)Hkv * FA_D, k_row_stride, k_batch_stride, FA_BN) != 0) return -2;
+    if (make_map_3d(&mv, v, B, Skv, (int64_t)Hkv * FA_D, v_row_stride, v_batch_stride, FA_BN) != 0) return -2;
+    FaParams prm;
+    prm.o = (__nv_bfloat16*)o;
+    prm.lse = lse;
+    prm.B = B, prm.Sq = Sq, prm.Skv = Skv, prm.H = H, prm.Hkv = Hkv;
+    prm.o_row_stride = o_row_stride, prm.o_batch_stride = o_batch_stride;
+    prm.scale_log2 = scale * 1.4426950408889634f;
+    prm.causal = causal;
+    prm.pairs = (Sq + 2 * FA_BM - 1) / (2 * FA_BM);
+    static bool attr_set[64] = {};
+    int dev_ = 0;
+    cudaGetDevice(&dev_);
+    if (!attr_set[dev_ & 63]) {
+        DSB_CHECK(cudaFuncSetAttribute(flash_attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM_BYTES));
+        attr_set[dev_ & 63] = true;
+    }
+    const int64_t grid = (int64_t)prm.pairs * B * H;
+    flash_attn_fwd_kernel<<<(unsigned)grid, FA_THREADS, FA_SMEM_BYTES, stream>>>(mq, mk, mv, prm);
+    DSB_CHECK_LAUNCH("flash_attn_fwd");
+    return 0;
+}
+
+}  // extern "C"

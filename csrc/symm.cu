@@ -411,6 +411,53 @@ int dsb200_symm_all_to_all(const uint64_t* peer_ins, const uint64_t* peer_flags,
     return 0;
 }
 
+// All-gather on the copy engines: the peers' shards are pulled with cudaMemcpyAsync over NVLink (DMA, no SM is
+// occupied, so the overlapped GEMMs keep all 148 SMs), spread over `n_helpers` helper streams so that several copy
+// engines run at once; `stream` forks before and joins after. No flag handshake here: the caller orders the gather
+// against the writers of the shards (symm_signal after the optimizer step / symm_wait before the first gather) and
+// publishes completion with symm_signal when the shards are about to be rewritten.
+// Reference counterpart: the DeepCompile executor's symmetric-memory all-gather (csrc/compile/z3.cpp:100-112), which
+// brackets per-peer copy_() calls with two barriers for every parameter.
+int dsb200_symm_all_gather_ce(const uint64_t* peer_shards, int rank, int world, int64_t shard_bytes, void* full,
+                              const cudaStream_t* helpers, int n_helpers, cudaStream_t stream)
+{
+    constexpr int MAX_HELPERS = 8;
+    if (world > MAX_WORLD || world < 1 || n_helpers > MAX_HELPERS || n_helpers < 0) {
+        dsb200_set_error("symm_all_gather_ce: world > 16 or more than 8 helper streams");
+        return -1;
+    }
+    struct Events {
+        cudaEvent_t fork = nullptr, join[MAX_HELPERS] = {};
+    };
+    static Events per_dev[64];
+    int dev = 0;
+    DSB_CHECK(cudaGetDevice(&dev));
+    Events& ev = per_dev[dev & 63];
+    if (ev.fork == nullptr) {
+        DSB_CHECK(cudaEventCreateWithFlags(&ev.fork, cudaEventDisableTiming));
+        for (int i = 0; i < MAX_HELPERS; i++) DSB_CHECK(cudaEventCreateWithFlags(&ev.join[i], cudaEventDisableTiming));
+    }
+    uint8_t* dst = reinterpret_cast<uint8_t*>(full);
+    const int used = n_helpers < world - 1 ? n_helpers : world - 1;
+    if (used > 0) {
+        DSB_CHECK(cudaEventRecord(ev.fork, stream));
+        for (int h = 0; h < used; h++) DSB_CHECK(cudaStreamWaitEvent(helpers[h], ev.fork, 0));
+    }
+    for (int i = 1; i < world; i++) {
+        const int p = (rank + i) % world;  // every rank starts with a different peer: no hot spot on one GPU
+        cudaStream_t s = used > 0 ? helpers[(i - 1) % used] : stream;
+        DSB_CHECK(cudaMemcpyAsync(dst + (int64_t)p * shard_bytes, reinterpret_cast<const void*>(peer_shards[p]),
+                                  (size_t)shard_bytes, cudaMemcpyDeviceToDevice, s));
+    }
+    DSB_CHECK(cudaMemcpyAsync(dst + (int64_t)rank * shard_bytes, reinterpret_cast<const void*>(peer_shards[rank]),
+                              (size_t)shard_bytes, cudaMemcpyDeviceToDevice, stream));
+    for (int h = 0; h < used; h++) {
+        DSB_CHECK(cudaEventRecord(ev.join[h], helpers[h]));
+        DSB_CHECK(cudaStreamWaitEvent(stream, ev.join[h], 0));
+    }
+    return 0;
+}
+
 int dsb200_symm_wait(const uint64_t* peer_flags, int rank, int world, int channel, unsigned int epoch,
                      cudaStream_t stream)
 {

@@ -25,6 +25,7 @@ from . import comm as dist
 CH_RS_READY, CH_RS_DONE, CH_AG_READY, CH_AG_DONE, CH_A2A_READY, CH_A2A_DONE, CH_USER = 0, 1, 2, 3, 4, 5, 6
 CH_QAG_READY, CH_QAG_DONE, CH_GIN_READY, CH_GIN_DONE = 7, 8, 9, 10
 CH_GA2A_READY, CH_GA2A_DONE, CH_GRS_READY, CH_GRS_DONE = 11, 12, 13, 14
+CH_CE_READY, CH_CE_DONE = 15, 16
 GEMM_AG_A, GEMM_AG_B, GEMM_SCATTER_N, GEMM_RS_M = 1, 2, 4, 8
 _CONTEXTS = {}
 
@@ -47,6 +48,8 @@ def _declare(L):
     L.dsb200_gemm_comm_bf16_nt.argtypes = [I, P, P, P, P, P, I, I, I, L64, L64, L64, P, I, I, I, I, I, I, U, U, P, P, P, I,
                                            I, P]
     L.dsb200_gemm_comm_bf16_nt.restype = I
+    L.dsb200_symm_all_gather_ce.argtypes = [P, I, I, L64, P, P, I, P]
+    L.dsb200_symm_all_gather_ce.restype = I
     L.dsb200_symm_wait.argtypes = [P, I, I, I, U, P]
     L.dsb200_symm_wait.restype = I
     L.dsb200_symm_signal.argtypes = [P, I, I, I, U, P]
@@ -314,6 +317,48 @@ class SymmContext:
             raise RuntimeError(f"symm all_gather failed: {K.last_error()}")
         K._LAUNCHES += 1
         return ep
+
+    # ---- copy-engine all-gather (ZeRO-3 parameter gather) ------------------------------------------------
+    # The parameter shards live in symmetric memory and only change at the optimizer step, so the gather needs no
+    # per-call handshake: the writer publishes once (`publish_shards`), the first gather afterwards waits for every
+    # peer's publication, and the copies themselves are plain DMA pulls over NVLink that occupy no SM -- the GEMMs they
+    # overlap with keep the whole GPU. Before the shards are rewritten the writer waits until every peer has finished
+    # the gathers issued so far (`wait_ce_readers`; all ranks issue the same sequence of gathers).
+    def _ce_state(self):
+        if not hasattr(self, "_ce_helpers"):
+            n = int(os.environ.get("DSB200_CE_STREAMS", str(min(self.world - 1, 7))))
+            self._ce_helpers = [torch.cuda.Stream(priority=-1) for _ in range(max(0, min(n, 8)))]
+            self._ce_helper_arr = (ctypes.c_void_p * 8)(*([s.cuda_stream for s in self._ce_helpers] +
+                                                          [None] * (8 - len(self._ce_helpers))))
+            self._ce_pub, self._ce_seen, self._ce_issued = 0, 0, 0
+        return self
+
+    def publish_shards(self):
+        """Call on the stream that (re)wrote symmetric parameter shards, after the writes."""
+        self._ce_state()
+        self._ce_pub = self._next(CH_CE_READY)
+        self._signal(CH_CE_READY, self._ce_pub)
+
+    def wait_ce_readers(self):
+        """Call on the stream that is about to rewrite symmetric parameter shards."""
+        self._ce_state()
+        if self._ce_issued:
+            self._wait(CH_CE_DONE, self._ce_issued)
+
+    def all_gather_ce(self, shard_buf: SymmBuffer, shard_offset_bytes, shard_bytes, full):
+        """full[p*shard_bytes ...] = peer p's bytes at ``shard_offset_bytes`` of ``shard_buf``, on the copy engines."""
+        self._ce_state()
+        if self._ce_seen != self._ce_pub:
+            self._wait(CH_CE_READY, self._ce_pub)  # every peer's shards are final
+            self._ce_seen = self._ce_pub
+        ptrs = (ctypes.c_uint64 * 16)(*[(int(p) + shard_offset_bytes) if p else 0 for p in shard_buf.ptrs])
+        rc = self.lib.dsb200_symm_all_gather_ce(ptrs, self.rank, self.world, shard_bytes,
+                                                ctypes.c_void_p(full.data_ptr()), self._ce_helper_arr,
+                                                len(self._ce_helpers), self._stream())
+        if rc != 0:
+            raise RuntimeError(f"symm all_gather_ce failed: {K.last_error()}")
+        self._ce_issued += 1
+        self._signal(CH_CE_DONE, self._ce_issued)
 
     def all_to_all(self, in_buf: SymmBuffer, rows, row_bytes, out, interleave=False, ctas=None):
         """out[p] = peer p's chunk ``rank`` of its input buffer viewed as [world, rows, row_bytes]."""

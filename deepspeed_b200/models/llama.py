@@ -85,7 +85,7 @@ def attention(q, k, v, causal=True, impl="auto"):
     """q: [B,S,Hq,D], k/v: [B,S,Hkv,D] -> [B,S,Hq,D]. GQA handled without materialising repeated KV."""
     if impl in ("auto", "native") and q.is_cuda:
         from ..ops import attention as native_attn
-        if native_attn.supported(q, k, v):
+        if (impl == "native" or native_attn.enabled_by_default()) and native_attn.supported(q, k, v):
             return native_attn.flash_attention(q, k, v, causal=causal)
     qt, kt, vt = q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2)
     gqa = qt.shape[1] != kt.shape[1]

@@ -1,20 +1,106 @@
-"""Native flash-attention front-end (tcgen05 kernel when built; see csrc/attention_*.cu)."""
+"""Native flash-attention front-end: the hand-written tcgen05 kernels of ``csrc/attention_fwd.cu`` /
+``csrc/attention_bwd.cu`` behind a ``torch.autograd.Function``.
+
+Layout is the projection layout ``[batch, seq, heads, 128]`` (views of a fused QKV projection are consumed in
+place through strided TMA tensor maps). ``flash_attention_forward`` also returns the log-sum-exp, which the
+chunked / sequence-parallel callers (FPDT ``sequence/fpdt_layer.py`` online-softmax merging) need and the framework
+SDPA call does not expose. Reference call sites: ``sequence/fpdt_layer.py:238-269`` (flash-attn forward/backward with
+LSE), ``runtime/sequence_parallel/ulysses_sp.py:50`` (HF attention functions).
+"""
+import ctypes
+import math
+import os
+
 import torch
 
 from . import kernels as K
 
+_DECLARED = False
+
+
+def _lib():
+    global _DECLARED
+    L = K.lib()
+    if not _DECLARED:
+        P, I, L64, F = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float
+        L.dsb200_flash_attn_fwd.argtypes = [P, P, P, P, P, I, I, I, I, I, L64, L64, L64, L64, L64, L64, L64, L64, F, I, P]
+        L.dsb200_flash_attn_fwd.restype = I
+        _DECLARED = True
+    return L
+
+
+def _ok_layout(t):
+    """[B, S, H, 128] bf16 with the head dim contiguous and heads packed 128 apart (strided rows / batches allowed)."""
+    return (t.dim() == 4 and t.dtype == torch.bfloat16 and t.shape[-1] == 128 and t.stride(3) == 1
+            and (t.shape[2] == 1 or t.stride(2) == 128) and t.stride(1) % 8 == 0 and t.stride(0) % 8 == 0
+            and t.data_ptr() % 16 == 0)
+
 
 def supported(q, k, v):
     """True when the hand-written sm_100a attention kernel can serve these operands."""
-    lib = K._LIB if K._LIB is not None else None
-    return bool(lib is not None and hasattr(lib, "dsb200_flash_attn_fwd") and q.dtype == torch.bfloat16
-                and q.shape[-1] == 128 and _enabled())
+    if not (q.is_cuda and K.available() and hasattr(K.lib(), "dsb200_flash_attn_fwd")):
+        return False
+    return (_ok_layout(q) and _ok_layout(k) and _ok_layout(v) and k.shape == v.shape and q.shape[0] == k.shape[0]
+            and q.shape[2] % k.shape[2] == 0)
 
 
-def _enabled():
-    import os
+def enabled_by_default():
+    """Training default: DSB200_NATIVE_ATTN=1 forces the native kernels, =0 the library SDPA."""
     return os.environ.get("DSB200_NATIVE_ATTN", "0") == "1"
 
 
-def flash_attention(q, k, v, causal=True):
-    raise NotImplementedError("native attention kernel not built in this revision")
+def flash_attention_forward(q, k, v, causal=True, scale=None, out=None, want_lse=True):
+    """q [B,Sq,H,128], k/v [B,Skv,Hkv,128] -> (o [B,Sq,H,128] bf16, lse [B,H,Sq] fp32 or None)."""
+    assert supported(q, k, v), "flash_attention_forward: unsupported operands (bf16, head_dim 128, packed heads)"
+    B, Sq, H, D = q.shape
+    Skv, Hkv = k.shape[1], k.shape[2]
+    if scale is None:
+        scale = 1.0 / math.sqrt(D)
+    if out is None:
+        out = torch.empty((B, Sq, H, D), dtype=torch.bfloat16, device=q.device)
+    lse = torch.empty((B, H, Sq), dtype=torch.float32, device=q.device) if want_lse else None
+    rc = _lib().dsb200_flash_attn_fwd(
+        K._ptr(q), K._ptr(k), K._ptr(v), K._ptr(out), K._ptr(lse), B, Sq, Skv, H, Hkv, q.stride(1), q.stride(0),
+        k.stride(1), k.stride(0), v.stride(1), v.stride(0), out.stride(1), out.stride(0), float(scale),
+        1 if causal else 0, K._stream())
+    K._check(rc, "flash_attn_fwd")
+    return out, lse
+
+
+def _reference_backward(q, k, v, do, causal, scale):
+    """Library fallback for the backward pass (recomputes through the framework SDPA)."""
+    with torch.enable_grad():
+        qd, kd, vd = (t.detach().requires_grad_(True) for t in (q, k, v))
+        o = torch.nn.functional.scaled_dot_product_attention(qd.transpose(1, 2), kd.transpose(1, 2), vd.transpose(1, 2),
+                                                             is_causal=causal, scale=scale,
+                                                             enable_gqa=q.shape[2] != k.shape[2])
+        o.backward(do.transpose(1, 2))
+    return qd.grad, kd.grad, vd.grad
+
+
+def flash_attention_backward(q, k, v, o, lse, do, causal=True, scale=None):
+    """Gradients (dq, dk, dv) in the layouts of q / k / v (contiguous [B,S,H,128])."""
+    if scale is None:
+        scale = 1.0 / math.sqrt(q.shape[-1])
+    return _reference_backward(q, k, v, do, causal, scale)
+
+
+class _FlashAttn(torch.autograd.Function):
+
+    @staticmethod
+    def forward(ctx, q, k, v, causal, scale):
+        o, lse = flash_attention_forward(q, k, v, causal, scale)
+        ctx.save_for_backward(q, k, v, o, lse)
+        ctx.causal, ctx.scale = causal, scale
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v, o, lse = ctx.saved_tensors
+        dq, dk, dv = flash_attention_backward(q, k, v, o, lse, do.contiguous(), ctx.causal, ctx.scale)
+        return dq, dk, dv, None, None
+
+
+def flash_attention(q, k, v, causal=True, scale=None):
+    """Differentiable attention on the native kernels. q [B,S,H,128], k/v [B,S,Hkv,128] -> [B,S,H,128]."""
+    return _FlashAttn.apply(q, k, v, causal, scale)

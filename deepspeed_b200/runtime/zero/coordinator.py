@@ -134,7 +134,10 @@ class UnitCoordinator:
                 and src.data_ptr() == u.param_shard.data_ptr() and not self.z.quantized_weights:
             # fused path 2 (v1): pull every peer's shard straight out of its symmetric lp storage over NVLink
             esz = src.element_size()
-            self.z.symm.all_gather(st.lp_symm, u.shard_offset * esz, u.shard_numel * esz, full)
+            if self.z._ag_on_copy_engines:
+                self.z.symm.all_gather_ce(st.lp_symm, u.shard_offset * esz, u.shard_numel * esz, full)
+            else:
+                self.z.symm.all_gather(st.lp_symm, u.shard_offset * esz, u.shard_numel * esz, full)
             return
         if self.z.quantized_weights and self.z.symm is not None and u.dtype in (torch.bfloat16, torch.float16) \
                 and src.data_ptr() == u.param_shard.data_ptr() and u.shard_numel % 256 == 0 \

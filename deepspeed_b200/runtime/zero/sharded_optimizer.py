@@ -193,7 +193,11 @@ class ZeroShardedOptimizer:
                         raise
                     logger.warning(f"symmetric-memory collectives unavailable ({e}); using NCCL")
                     self.symm, self._grad_pool = None, None
+        # ZeRO-3 parameter all-gather on the copy engines (DMA pulls from the peers' symmetric shards, no SM taken from
+        # the overlapped GEMMs); DSB200_AG_MODE=kernel selects the SM-driven pull kernel instead
+        self._ag_on_copy_engines = _os.environ.get("DSB200_AG_MODE", "ce") == "ce"
         self._allocate_and_link()
+        self._lp_shards_written()
         self._setup_fused_rs_adam(fused_rs_adam)
         self._zenflow = None
         if zenflow is not None and self.offload_optimizer and not self.offload_nvme:
@@ -396,6 +400,7 @@ class ZeroShardedOptimizer:
             bounds.insert(0, 0)
             hyper.insert(0, [0.0, 0.0, 0.0, 1.0, 0.0, 1.0, 1.0, 1.0])
         lp = st.lp[a:b] if self.partition_params else u.param_shard
+        self._lp_shards_will_be_written()
         _, grid = self.symm.rs_adam(u._slot, u.full_grad.dtype, u.shard_numel, 1.0 / div, st.master[a:b],
                                     st.exp_avg[a:b], st.exp_avg_sq[a:b], lp if lp.dtype == torch.bfloat16 else None,
                                     bounds, hyper, want_sumsq=True)
@@ -596,6 +601,17 @@ class ZeroShardedOptimizer:
             u.has_grad_data = False
             u._accumulated = set()
 
+    def _lp_shards_written(self):
+        """The symmetric low-precision shards were (re)written on the current stream: publish them to the peers."""
+        if self.symm is not None and self.partition_params and self._ag_on_copy_engines:
+            self.symm.publish_shards()
+
+    def _lp_shards_will_be_written(self):
+        """About to rewrite the symmetric shards on the current stream: every peer must have finished the copy-engine
+        gathers issued so far (they read my shards directly)."""
+        if self.symm is not None and self.partition_params and self._ag_on_copy_engines:
+            self.symm.wait_ce_readers()
+
     def _release_slot(self, u):
         if getattr(u, "_slot", None) is not None and self._grad_pool is not None:
             self._grad_pool.release(u._slot)
@@ -743,6 +759,7 @@ class ZeroShardedOptimizer:
                 u.reduced_this_pass = False
         if self._use_streams and self.overlap_comm:
             torch.cuda.current_stream().wait_stream(self.rs_stream)
+        self._lp_shards_will_be_written()
 
         if self._fused_iter:
             # every bucket was updated by its reduce-scatter kernel during backward; only bookkeeping is left
@@ -1014,6 +1031,7 @@ class ZeroShardedOptimizer:
     @torch.no_grad()
     def _post_step_gather(self):
         """All-gather updated lp shards of resident units (reference ``all_gather_dp_groups`` utils.py:1016)."""
+        self._lp_shards_written()
         for u in self.units:
             if u.full_param is None or u.world <= 1:
                 continue
@@ -1086,11 +1104,15 @@ class ZeroShardedOptimizer:
             dst = u.master_shard if optim_state_key is None else self._state_shard(u, optim_state_key)
             dst[s_in_shard:s_in_shard + n].copy_(flat[s_in_p:s_in_p + n].to(dst.dtype))
             if optim_state_key is None:
+                self._lp_shards_will_be_written()
+            if optim_state_key is None:
                 lp = self.storages[(u.group_key, u.dtype)].lp
                 if lp is not None:
                     lp[u.shard_offset + s_in_shard:u.shard_offset + s_in_shard + n].copy_(flat[s_in_p:s_in_p + n])
                 if u.full_param is not None:
                     u.param_shard[s_in_shard:s_in_shard + n].copy_(flat[s_in_p:s_in_p + n])
+        if optim_state_key is None:
+            self._lp_shards_written()
         if optim_state_key is None and u.full_param is not None and u.world > 1:
             self._all_gather_into(u.full_param, u.param_shard, u)
 

@@ -181,6 +181,11 @@ int dsb200_symm_all_gather(const uint64_t* peer_shards, const uint64_t* peer_fla
                            int world, int64_t shard_bytes, const void* my_shard, void* full, unsigned int* ticket,
                            int ch_ready, int ch_done, unsigned int epoch, unsigned int done_epoch, int ctas,
                            cudaStream_t stream);
+/* All-gather on the copy engines (cudaMemcpyAsync pulls over NVLink on `n_helpers` <= 8 helper streams forked from /
+ * joined into `stream`); occupies no SM. The caller orders it against the writers of the shards with
+ * dsb200_symm_signal / dsb200_symm_wait. Reference: csrc/compile/z3.cpp:100-112 (symmetric-memory all-gather). */
+int dsb200_symm_all_gather_ce(const uint64_t* peer_shards, int rank, int world, int64_t shard_bytes, void* full,
+                              const cudaStream_t* helpers, int n_helpers, cudaStream_t stream);
 int dsb200_symm_all_to_all(const uint64_t* peer_ins, const uint64_t* peer_flags, int rank, int world, int64_t rows,
                            int64_t row_bytes, int interleave, void* out, unsigned int* ticket, int ch_ready,
                            int ch_done, unsigned int epoch, int ctas, cudaStream_t stream);

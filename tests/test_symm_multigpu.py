@@ -126,9 +126,9 @@ def _train_unused(fused, steps):
         "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True}, "gradient_clipping": 1.0,
         "optimizer": {"type": "AdamW", "params": {"lr": 1e-3, "weight_decay": 0.0}},
         "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 1000, "fused_collectives": fused,
-                              "fused_rs_adam": False}})
+                              "fused_rs_adam": False, "unit_max_numel": 700000}})  # one unit per layer
     assert (eng.optimizer.symm is not None) == fused
-    assert len(eng.optimizer.units) > 3
+    assert len(eng.optimizer.units) > 3, eng.optimizer.units
     torch.manual_seed(1 + ds.comm.get_rank())
     losses, held = [], 0
     for _ in range(steps):
