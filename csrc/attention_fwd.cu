@@ -21,6 +21,7 @@
 //               back over S with tcgen05.st -> lazy rescale of O in TMEM (only when the row max grew by > 2^8)
 // TMEM (512 columns): S0 | S1 | O0 | O1, 128 fp32 columns each; P_t aliases the first 64 columns of S_t.
 #include "gemm_common.cuh"
+#include <cstdlib>
 
 namespace {
 
@@ -114,6 +115,25 @@ __device__ __forceinline__ float fast_exp2(float x)
     return y;
 }
 
+// 2^x on the FMA/ALU pipes (Cody-Waite split + cubic minimax polynomial, relative error ~1e-4, far below the bf16
+// rounding of P): the MUFU unit delivers 16 ex2/clk/SM, exactly the rate at which the tensor pipe consumes scores for
+// head_dim 128, so a share of the exponentials is moved off it to give the softmax warps slack.
+__device__ __forceinline__ float exp2_emu(float x)
+{
+    x = fmaxf(x, -126.f);
+    const float t = __fadd_rd(x, 12582912.f);  // 1.5 * 2^23: floor(x) lands in the low mantissa bits
+    const float f = x - (t - 12582912.f);      // fractional part in [0, 1)
+    const float p = fmaf(fmaf(fmaf(0.077119f, f, 0.227564f), f, 0.695146f), f, 1.0f);
+    return __uint_as_float(__float_as_uint(p) + (__float_as_uint(t) << 23));
+}
+// EMU_MASK: which of every 8 consecutive scores use exp2_emu (e.g. 0xA8 = positions 3, 5, 7 = 37.5 %)
+template <unsigned EMU_MASK, int I>
+__device__ __forceinline__ float exp2_sel(float x)
+{
+    if constexpr ((EMU_MASK >> (I & 7)) & 1u) return exp2_emu(x);
+    else return fast_exp2(x);
+}
+
 struct FaParams {
     __nv_bfloat16* o;
     float* lse;  // [B, H, Sq]
@@ -124,6 +144,7 @@ struct FaParams {
     int pairs;  // ceil(Sq / 256)
 };
 
+template <unsigned EMU_MASK>
 __global__ void __launch_bounds__(FA_THREADS, 1)
 flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                       const __grid_constant__ CUtensorMap map_v, const FaParams prm)
@@ -303,21 +324,26 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
             // does this block need masking (diagonal block of the causal mask, or the tail of the key sequence)?
             const bool need_mask = (prm.causal && (col0 + FA_BN - 1 > q0 + t * FA_BM + causal_off)) || (col0 + FA_BN > prm.Skv);
             const int col_limit = prm.causal ? min(prm.Skv, row + causal_off + 1) : prm.Skv;  // valid keys: col < col_limit
-            // ---- pass 1: row max ----
+            // ---- the whole score row lives in registers: one TMEM round trip ----
+            uint32_t r[4][32];
+#pragma unroll
+            for (int c = 0; c < 4; c++) tmem_ld_32x32(s_addr + c * 32, r[c]);
+            tmem_wait_ld();
             float mx = -INFINITY;
-#pragma unroll 1
-            for (int c = 0; c < 4; c++) {
-                uint32_t r[32];
-                tmem_ld_32x32(s_addr + c * 32, r);
-                tmem_wait_ld();
-                if (need_mask) {
+            if (need_mask) {
+#pragma unroll
+                for (int c = 0; c < 4; c++)
 #pragma unroll
                     for (int i = 0; i < 32; i++)
-                        if (col0 + c * 32 + i < col_limit) mx = fmaxf(mx, __uint_as_float(r[i]));
-                } else {
+                        if (col0 + c * 32 + i >= col_limit) r[c][i] = 0xff800000u;  // -inf
+            }
+            {
+                float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // 4 independent chains
 #pragma unroll
-                    for (int i = 0; i < 32; i++) mx = fmaxf(mx, __uint_as_float(r[i]));
-                }
+                for (int c = 0; c < 4; c++)
+#pragma unroll
+                    for (int i = 0; i < 32; i++) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(r[c][i]));
+                mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
             }
             mx *= prm.scale_log2;  // scale > 0: max commutes with the scaling
             float m_new = fmaxf(m_run, mx);
@@ -325,28 +351,40 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
             if (m_run != -INFINITY && m_new - m_run <= 8.f) m_new = m_run;
             const float alpha = (m_run == -INFINITY) ? 0.f : fast_exp2(m_run - m_new);
             const float m_use = (m_new == -INFINITY) ? 0.f : m_new;  // fully masked row so far: avoid inf - inf
-            // ---- pass 2: p = exp2(s * scale - m), bf16 P over the S columns ----
-            float rowsum = 0.f;
-#pragma unroll 1
+            // ---- p = exp2(s * scale - m) (masked entries: exp2(-inf) = 0), bf16 P over the S columns ----
+            float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
             for (int c = 0; c < 4; c++) {
-                uint32_t r[32];
-                tmem_ld_32x32(s_addr + c * 32, r);
-                tmem_wait_ld();
                 uint32_t pk[16];
 #pragma unroll
-                for (int i = 0; i < 16; i++) {
-                    float p0 = fast_exp2(fmaf(__uint_as_float(r[2 * i]), prm.scale_log2, -m_use));
-                    float p1 = fast_exp2(fmaf(__uint_as_float(r[2 * i + 1]), prm.scale_log2, -m_use));
-                    if (need_mask) {
-                        if (col0 + c * 32 + 2 * i >= col_limit) p0 = 0.f;
-                        if (col0 + c * 32 + 2 * i + 1 >= col_limit) p1 = 0.f;
-                    }
-                    rowsum += p0 + p1;
-                    __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
-                    pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+                for (int i = 0; i < 16; i += 4) {
+                    // 8 scores per step: compile-time choice of MUFU vs FMA-pipe exponential per position
+                    const float x0 = fmaf(__uint_as_float(r[c][2 * i + 0]), prm.scale_log2, -m_use);
+                    const float x1 = fmaf(__uint_as_float(r[c][2 * i + 1]), prm.scale_log2, -m_use);
+                    const float x2 = fmaf(__uint_as_float(r[c][2 * i + 2]), prm.scale_log2, -m_use);
+                    const float x3 = fmaf(__uint_as_float(r[c][2 * i + 3]), prm.scale_log2, -m_use);
+                    const float x4 = fmaf(__uint_as_float(r[c][2 * i + 4]), prm.scale_log2, -m_use);
+                    const float x5 = fmaf(__uint_as_float(r[c][2 * i + 5]), prm.scale_log2, -m_use);
+                    const float x6 = fmaf(__uint_as_float(r[c][2 * i + 6]), prm.scale_log2, -m_use);
+                    const float x7 = fmaf(__uint_as_float(r[c][2 * i + 7]), prm.scale_log2, -m_use);
+                    const float p0 = exp2_sel<EMU_MASK, 0>(x0), p1 = exp2_sel<EMU_MASK, 1>(x1);
+                    const float p2 = exp2_sel<EMU_MASK, 2>(x2), p3 = exp2_sel<EMU_MASK, 3>(x3);
+                    const float p4 = exp2_sel<EMU_MASK, 4>(x4), p5 = exp2_sel<EMU_MASK, 5>(x5);
+                    const float p6 = exp2_sel<EMU_MASK, 6>(x6), p7 = exp2_sel<EMU_MASK, 7>(x7);
+                    rs4[0] += p0 + p1;
+                    rs4[1] += p2 + p3;
+                    rs4[2] += p4 + p5;
+                    rs4[3] += p6 + p7;
+                    __nv_bfloat162 h0 = __floats2bfloat162_rn(p0, p1), h1 = __floats2bfloat162_rn(p2, p3);
+                    __nv_bfloat162 h2 = __floats2bfloat162_rn(p4, p5), h3 = __floats2bfloat162_rn(p6, p7);
+                    pk[i + 0] = *reinterpret_cast<uint32_t*>(&h0);
+                    pk[i + 1] = *reinterpret_cast<uint32_t*>(&h1);
+                    pk[i + 2] = *reinterpret_cast<uint32_t*>(&h2);
+                    pk[i + 3] = *reinterpret_cast<uint32_t*>(&h3);
                 }
                 tmem_st_32x16(s_addr + c * 16, pk);
             }
+            const float rowsum = (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
             l_run = l_run * alpha + rowsum;
             m_run = m_new;
             // ---- rescale O (the previous P V has completed: s_full of this block was committed after it) ----
@@ -461,15 +499,37 @@ int dsb200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, 
     prm.scale_log2 = scale * 1.4426950408889634f;
     prm.causal = causal;
     prm.pairs = (Sq + 2 * FA_BM - 1) / (2 * FA_BM);
-    static bool attr_set[64] = {};
-    int dev_ = 0;
-    cudaGetDevice(&dev_);
-    if (!attr_set[dev_ & 63]) {
-        DSB_CHECK(cudaFuncSetAttribute(flash_attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM_BYTES));
-        attr_set[dev_ & 63] = true;
+    // share of exponentials computed on the FMA pipes instead of the MUFU (tuning knob DSB200_FA_EMU = 0..3 ->
+    // 0 / 25 / 37.5 / 50 %). Measured on B200 (S = 4096..8192): 0 % is fastest (1.24 PFLOP/s non-causal at 8192; every
+    // extra 12.5 % costs ~3 %), the softmax warps are issue-bound before they are MUFU-bound, so the default is 0.
+    static int emu = -1;
+    if (emu < 0) {
+        const char* e = getenv("DSB200_FA_EMU");
+        emu = e ? atoi(e) : 0;
+        if (emu < 0 || emu > 3) emu = 0;
     }
     const int64_t grid = (int64_t)prm.pairs * B * H;
-    flash_attn_fwd_kernel<<<(unsigned)grid, FA_THREADS, FA_SMEM_BYTES, stream>>>(mq, mk, mv, prm);
+    int dev_ = 0;
+    cudaGetDevice(&dev_);
+#define FA_LAUNCH(MASK)                                                                                             \
+    do {                                                                                                            \
+        static bool attr_set[64] = {};                                                                              \
+        if (!attr_set[dev_ & 63]) {                                                                                 \
+            DSB_CHECK(cudaFuncSetAttribute(flash_attn_fwd_kernel<MASK>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                           FA_SMEM_BYTES));                                                         \
+            attr_set[dev_ & 63] = true;                                                                             \
+        }                                                                                                           \
+        flash_attn_fwd_kernel<MASK><<<(unsigned)grid, FA_THREADS, FA_SMEM_BYTES, stream>>>(mq, mk, mv, prm);        \
+    } while (0)
+    if (emu == 0)
+        FA_LAUNCH(0x00u);
+    else if (emu == 1)
+        FA_LAUNCH(0x88u);  // 25 %
+    else if (emu == 2)
+        FA_LAUNCH(0xA8u);  // 37.5 %
+    else
+        FA_LAUNCH(0xAAu);  // 50 %
+#undef FA_LAUNCH
     DSB_CHECK_LAUNCH("flash_attn_fwd");
     return 0;
 }
