@@ -124,18 +124,16 @@ class LlamaAttention(nn.Module):
         self.cfg = cfg
         self.nh, self.nkv, self.hd = cfg.num_attention_heads, cfg.num_key_value_heads, cfg.head_dim
         qkv_out = (self.nh + 2 * self.nkv) * self.hd
-        self.qkv_proj = nn.Linear(cfg.hidden_size, qkv_out, bias=False, dtype=cfg.dtype, device=device)
-        self.o_proj = nn.Linear(self.nh * self.hd, cfg.hidden_size, bias=False, dtype=cfg.dtype, device=device)
+        self.qkv_proj = fused.Linear(cfg.hidden_size, qkv_out, bias=False, dtype=cfg.dtype, device=device)
+        self.o_proj = fused.Linear(self.nh * self.hd, cfg.hidden_size, bias=False, dtype=cfg.dtype, device=device)
 
     def forward(self, x, cos, sin, position_ids=None, sp_attention=None):
         B, S, _ = x.shape
         qkv = self.qkv_proj(x)
-        q, k, v = qkv.split([self.nh * self.hd, self.nkv * self.hd, self.nkv * self.hd], dim=-1)
-        q = fused.apply_rope(q.reshape(B, S, self.nh, self.hd), cos, sin, position_ids)
-        k = fused.apply_rope(k.reshape(B, S, self.nkv, self.hd), cos, sin, position_ids)
-        v = v.reshape(B, S, self.nkv, self.hd)
+        # RoPE in place on the q and k heads of the fused projection; q / k / v stay views of it
+        q, k, v = fused.apply_rope_qkv(qkv, cos, sin, position_ids, self.nh, self.nkv, self.hd)
         if sp_attention is not None:
-            o = sp_attention(q, k, v)
+            o = sp_attention(q.contiguous(), k.contiguous(), v.contiguous())
         else:
             o = attention(q, k, v, causal=True, impl=self.cfg.attn_impl)
         return self.o_proj(o.reshape(B, S, self.nh * self.hd))
@@ -145,9 +143,10 @@ class LlamaMLP(nn.Module):
 
     def __init__(self, cfg: LlamaConfig, device=None):
         super().__init__()
-        self.gate_up_proj = nn.Linear(cfg.hidden_size, 2 * cfg.intermediate_size, bias=False, dtype=cfg.dtype,
+        self.gate_up_proj = fused.Linear(cfg.hidden_size, 2 * cfg.intermediate_size, bias=False, dtype=cfg.dtype,
+                                         device=device)
+        self.down_proj = fused.Linear(cfg.intermediate_size, cfg.hidden_size, bias=False, dtype=cfg.dtype,
                                       device=device)
-        self.down_proj = nn.Linear(cfg.intermediate_size, cfg.hidden_size, bias=False, dtype=cfg.dtype, device=device)
 
     def forward(self, x):
         return self.down_proj(fused.swiglu(self.gate_up_proj(x)))

@@ -284,6 +284,15 @@ def rope_(x, cos, sin, pos, seq_len, backward=False):
     return x
 
 
+def rope_strided_(x, cos, sin, pos, rows, n_heads, head_dim, row_stride, seq_len, backward=False):
+    """In-place half-rotation RoPE on the first ``n_heads`` heads of every row of ``x`` (rows ``row_stride``
+    elements apart): the q and k heads of a fused QKV projection in one launch."""
+    assert x.is_contiguous() and cos.dtype == torch.float32 and cos.shape[-1] == head_dim // 2
+    _check(lib().dsb200_rope(_ptr(x), _ptr(cos), _ptr(sin), _ptr(pos), rows, n_heads, head_dim, row_stride, seq_len,
+                             1 if backward else 0, _dt(x), _stream()), "rope")
+    return x
+
+
 def swiglu_fwd(gate_up):
     inter = gate_up.shape[-1] // 2
     rows = gate_up.numel() // (2 * inter)

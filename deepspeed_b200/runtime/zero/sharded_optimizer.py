@@ -196,6 +196,8 @@ class ZeroShardedOptimizer:
         # ZeRO-3 parameter all-gather on the copy engines (DMA pulls from the peers' symmetric shards, no SM taken from
         # the overlapped GEMMs); DSB200_AG_MODE=kernel selects the SM-driven pull kernel instead
         self._ag_on_copy_engines = _os.environ.get("DSB200_AG_MODE", "ce") == "ce"
+        # weight-gradient GEMMs of ops.fused.Linear write straight into the flat gradient buffers
+        self._direct_wgrad = _os.environ.get("DSB200_DIRECT_WGRAD", "1") == "1"
         self._allocate_and_link()
         self._lp_shards_written()
         self._setup_fused_rs_adam(fused_rs_adam)
@@ -473,44 +475,88 @@ class ZeroShardedOptimizer:
         self._epilogue_queued = False
         self.backward_epilogue()
 
+    def _ensure_full_grad(self, u: FlatUnit):
+        """Give the unit its flat gradient buffer for this backward pass (symmetric slot, the shard itself at world 1,
+        or a private buffer)."""
+        if u.full_grad is not None:
+            return
+        # no memset: every parameter overwrites its own region; alignment gaps / params that never produce a
+        # gradient are zeroed just before the reduction (_zero_unwritten)
+        u._slot = None
+        if self._grad_pool is not None and u.world > 1:
+            # waits (on this stream) until peers released the slot; None when every slot is still held by a
+            # unit with incomplete gradients -> private buffer + NCCL reduction below
+            u._slot = self._grad_pool.acquire()
+        if u._slot is not None:
+            u.full_grad = u._slot.view(u.numel_padded, self._full_grad_dtype())
+        elif (u.world == 1 and u.replica_world == 1 and not getattr(u, "_shard_has_data", False)
+              and u.grad_shard.dtype == self._full_grad_dtype() and u.grad_shard.numel() == u.numel_padded
+              and self.partition_grads):
+            # nothing to reduce and nothing accumulated yet: gradients are written straight into the shard
+            u._slot = None
+            u.full_grad = u.grad_shard
+        else:
+            u._slot = None
+            u.full_grad = torch.empty(u.numel_padded, dtype=self._full_grad_dtype(), device=u.device)
+        u.has_grad_data = False
+        u._written = set()
+
     @torch.no_grad()
     def _on_grad_ready(self, u: FlatUnit, i, param):
         g = param.grad
         if g is None:
             return
         self._ensure_epilogue()
-        if u.full_grad is None:
-            # no memset: every parameter overwrites its own region; alignment gaps / params that never produce a
-            # gradient are zeroed just before the reduction (_zero_unwritten)
-            u._slot = None
-            if self._grad_pool is not None and u.world > 1:
-                # waits (on this stream) until peers released the slot; None when every slot is still held by a
-                # unit with incomplete gradients -> private buffer + NCCL reduction below
-                u._slot = self._grad_pool.acquire()
-            if u._slot is not None:
-                u.full_grad = u._slot.view(u.numel_padded, self._full_grad_dtype())
-            elif (u.world == 1 and u.replica_world == 1 and not getattr(u, "_shard_has_data", False)
-                  and u.grad_shard.dtype == self._full_grad_dtype() and u.grad_shard.numel() == u.numel_padded
-                  and self.partition_grads):
-                # nothing to reduce and nothing accumulated yet: gradients are written straight into the shard
-                u._slot = None
-                u.full_grad = u.grad_shard
-            else:
-                u._slot = None
-                u.full_grad = torch.empty(u.numel_padded, dtype=self._full_grad_dtype(), device=u.device)
-            u.has_grad_data = False
-            u._written = set()
-        u._written.add(i)
+        self._ensure_full_grad(u)
         o, n = u.offsets[i], u.numels[i]
         view = u.full_grad[o:o + n]
-        if u.has_grad_data and not self.partition_grads and i in getattr(u, "_accumulated", ()):
+        if self._accumulates(u, i):
             view.add_(g.reshape(-1))
         else:
             view.copy_(g.reshape(-1))
         param.grad = None
-        u.grads_ready += 1
-        if u.grads_ready >= u.grads_expected:
-            self._unit_backward_done(u)
+        self._grad_landed(u, i)
+
+    def _accumulates(self, u, i):
+        """Must a new gradient of parameter ``i`` be added to the flat buffer (instead of overwriting its region)?
+        Yes for a second contribution inside the same backward pass (direct path, shared weights) and, when the flat
+        buffer is kept across micro-batches (stage <= 1), for every contribution after the first micro-batch."""
+        return i in getattr(u, "_pass_seen", ()) or (u.has_grad_data and not self.partition_grads
+                                                   and i in getattr(u, "_accumulated", ()))
+
+    def _grad_landed(self, u, i):
+        seen = u.__dict__.setdefault("_pass_seen", set())
+        first_time = i not in seen
+        seen.add(i)
+        u._written.add(i)
+        if first_time:
+            u.grads_ready += 1
+            if u.grads_ready >= u.grads_expected:
+                self._unit_backward_done(u)
+
+    # ---- direct weight-gradient path (ops/fused.py::linear) ------------------------------------
+    @torch.no_grad()
+    def grad_target(self, param, dtype):
+        """Where the weight-gradient GEMM of ``param`` may write directly: ``(flat view, accumulate)`` -- the
+        parameter's region of the unit's flat gradient buffer -- or None when the caller must hand the gradient to
+        autograd (dtype mismatch, reductions disabled, parameter not managed). Saves the grad -> flat-buffer copy
+        (reference: the same idea as Megatron's gradient-accumulation fusion that DeepSpeed's engine supports via
+        ``main_grad``). Follow with :meth:`grad_written`."""
+        ent = self._unit_of_param.get(id(param))
+        if ent is None or not self._direct_wgrad or dtype != self._full_grad_dtype() or not param.requires_grad:
+            return None
+        u, i = ent
+        if u.reduced_this_pass:  # a second use after the unit was already reduced: let the hook path deal with it
+            return None
+        self._ensure_epilogue()
+        self._ensure_full_grad(u)
+        o, n = u.offsets[i], u.numels[i]
+        return u.full_grad[o:o + n], self._accumulates(u, i)
+
+    @torch.no_grad()
+    def grad_written(self, param):
+        u, i = self._unit_of_param[id(param)]
+        self._grad_landed(u, i)
 
     def _full_grad_dtype(self):
         # stage<=1 accumulates micro-batches in the full buffer -> use the accumulation dtype there
@@ -667,6 +713,7 @@ class ZeroShardedOptimizer:
         for u in self.units:
             u.grads_ready = 0
             u.reduced_this_pass = False
+            u._pass_seen = set()
             if u.full_grad is not None:
                 if len(getattr(u, "_accumulated", ())) != len(u.params):
                     self._zero_unwritten(u)

@@ -78,3 +78,44 @@ def test_fused_path_matches_torch_path_fp32_master():
         # of that on average (fast-math division/sqrt + bf16 re-rounding of the weights between steps)
         assert diff <= 3.0 * noise + 2e-5, f"{n}: fused-vs-torch {diff:.3e} exceeds run-to-run noise {noise:.3e}"
         assert (fused[n] - ref[n]).abs().max().item() < 3 * 3 * 1e-3
+
+
+@pytest.mark.parametrize("stage", [1, 3])
+def test_direct_wgrad_matches_hook_path(stage):
+    """Weight-gradient GEMMs writing straight into the flat gradient buffer (ops.fused.Linear +
+    ZeroShardedOptimizer.grad_target) vs the grad-hook copy path: same losses and gradient norms, with gradient
+    accumulation (stage 1 keeps the flat buffer across micro-batches -> the accumulate branch)."""
+    _env()
+    import deepspeed_b200 as ds
+    from deepspeed_b200.models import LlamaConfig, LlamaForCausalLM
+    dev = torch.device("cuda", 0)
+    cfg = LlamaConfig(vocab_size=1024, hidden_size=128, intermediate_size=256, num_hidden_layers=2,
+                      num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=128)
+    out = []
+    for direct in (True, False):
+        torch.manual_seed(0)
+        model = LlamaForCausalLM(cfg, device=dev)
+        eng, _, _, _ = ds.initialize(model=model, config={
+            "train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 2, "bf16": {"enabled": True},
+            "gradient_clipping": 1.0, "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}},
+            "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 1000}})
+        eng.optimizer._direct_wgrad = direct
+        torch.manual_seed(1)
+        losses, norms = [], []
+        for it in range(8):
+            ids = torch.randint(0, 1024, (2, 64), device=dev)
+            loss = eng(ids, labels=ids)
+            eng.backward(loss)
+            eng.step()
+            losses.append(float(loss.detach()))
+            gn = eng.get_global_grad_norm()
+            if it % 2 == 1 and gn is not None:
+                norms.append(float(gn))
+        out.append((losses, norms))
+        eng.destroy()
+    (la, na), (lb, nb) = out
+    assert len(na) == len(nb) == 4, (na, nb)
+    for x, y in zip(la, lb):
+        assert abs(x - y) < 3e-2, (la, lb)
+    for x, y in zip(na, nb):
+        assert abs(x - y) <= 3e-2 * max(1.0, y), (na, nb)

@@ -228,3 +228,29 @@ def test_sumsq_not_disturbed_by_kernels_sharing_scratch(K):
         got = float(K.sumsq(t))
         ref = float(t.double().pow(2).sum())
         assert abs(got - ref) <= 2e-4 * ref
+
+
+@pytest.mark.parametrize("with_pos", [False, True])
+def test_rope_qkv_inplace_fwd_bwd(K, with_pos):
+    """Fused in-place RoPE on the q / k heads of a QKV projection vs the per-tensor fp32 reference."""
+    from deepspeed_b200.ops import fused
+    torch.manual_seed(0)
+    B, S, Hq, Hkv, D = 2, 128, 4, 2, 128
+    src = torch.randn(B, S, (Hq + 2 * Hkv) * D, device=_dev(), dtype=torch.bfloat16)
+    cos, sin = fused.rope_tables(512, D, 10000.0, _dev())
+    pos = torch.randint(0, 512, (B, S), device=_dev()) if with_pos else None
+    leaf = src.clone().requires_grad_(True)
+    qkv = leaf * 1.0  # a non-leaf the function may modify in place
+    q, k, v = fused.apply_rope_qkv(qkv, cos, sin, pos, Hq, Hkv, D)
+    dq, dk, dv = torch.randn_like(q), torch.randn_like(k), torch.randn_like(v)
+    ((q.float() * dq.float()).sum() + (k.float() * dk.float()).sum() + (v.float() * dv.float()).sum()).backward()
+    ref = src.float().clone().requires_grad_(True)
+    rq, rk, rv = ref.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+    rq = fused._rope_torch(rq.reshape(B, S, Hq, D), cos, sin, pos, S)
+    rk = fused._rope_torch(rk.reshape(B, S, Hkv, D), cos, sin, pos, S)
+    rv = rv.reshape(B, S, Hkv, D)
+    ((rq * dq.float()).sum() + (rk * dk.float()).sum() + (rv * dv.float()).sum()).backward()
+    torch.testing.assert_close(q.float(), rq, rtol=1e-2, atol=1e-2)
+    torch.testing.assert_close(k.float(), rk, rtol=1e-2, atol=1e-2)
+    torch.testing.assert_close(v.float(), rv, rtol=0, atol=0)
+    torch.testing.assert_close(leaf.grad.float(), ref.grad, rtol=1e-2, atol=2e-2)
