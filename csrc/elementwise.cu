@@ -107,9 +107,10 @@ template <typename T>
 __global__ void __launch_bounds__(1024) ce_fwd_kernel(T* __restrict__ logits, const int64_t* __restrict__ target,
                                                       float* __restrict__ loss, float* __restrict__ lse_out, int rows,
                                                       int vocab, int64_t row_stride, int ignore_index, int write_grad,
-                                                      float grad_scale)
+                                                      float grad_scale, const float* __restrict__ grad_scale_dev)
 {
     __shared__ float red[33];
+    if (grad_scale_dev != nullptr) grad_scale *= *grad_scale_dev;  // e.g. 1 / (number of valid tokens), kept on device
     const int row = blockIdx.x;
     T* lr = logits + (int64_t)row * row_stride;
     const int64_t tgt = target[row];
@@ -159,6 +160,23 @@ __global__ void __launch_bounds__(1024) ce_fwd_kernel(T* __restrict__ logits, co
         const float a = dsb::to_f<T>(lr[i]);
         lr[i] = dsb::from_f<T>((__expf(a - lse) - ((i == tgt) ? 1.f : 0.f)) * gsc);
     }
+}
+
+// x[i] *= *scale (device scalar), vectorised; nothing is touched when *scale == 1
+template <typename T>
+__global__ void __launch_bounds__(256) scale_by_dev_kernel(T* __restrict__ x, int64_t n, const float* __restrict__ scale)
+{
+    const float s = *scale;
+    if (s == 1.0f) return;
+    const int64_t nvec = n >> 3;
+    for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
+        dsb::f8 a = dsb::load8(x + v * 8);
+#pragma unroll
+        for (int i = 0; i < 8; i++) a.v[i] *= s;
+        dsb::store8(x + v * 8, a);
+    }
+    if (blockIdx.x == 0)
+        for (int64_t i = (nvec << 3) + threadIdx.x; i < n; i += blockDim.x) x[i] = dsb::from_f<T>(dsb::to_f<T>(x[i]) * s);
 }
 
 int grid_for(int64_t work_items, int threads, int per_sm)
@@ -246,9 +264,39 @@ int dsb200_swiglu_bwd(const void* dy, const void* gate, const void* up, void* dg
     return 0;
 }
 
+int dsb200_ce_fwd_ex(void* logits, const int64_t* target, float* loss, float* lse, int rows, int vocab,
+                     int64_t row_stride, int ignore_index, int write_grad, float grad_scale, const float* grad_scale_dev,
+                     int dt, cudaStream_t stream);
+
 // logits: [rows, vocab] with row stride `row_stride` elements (16-byte aligned rows); target int64 [rows].
 int dsb200_ce_fwd(void* logits, const int64_t* target, float* loss, float* lse, int rows, int vocab, int64_t row_stride,
                   int ignore_index, int write_grad, float grad_scale, int dt, cudaStream_t stream)
+{
+    return dsb200_ce_fwd_ex(logits, target, loss, lse, rows, vocab, row_stride, ignore_index, write_grad, grad_scale,
+                            nullptr, dt, stream);
+}
+
+// x (fp16 / bf16, 16-byte aligned, contiguous) *= *scale_dev; a no-op kernel when the device scalar is 1.
+int dsb200_scale_by_dev(void* x, int64_t n, int dt, const float* scale_dev, cudaStream_t stream)
+{
+    if (n <= 0) return 0;
+    const int grid = grid_for(n / 8 + 1, 256, 8);
+    if (dt == DSB_DT_BF16)
+        scale_by_dev_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>((__nv_bfloat16*)x, n, scale_dev);
+    else if (dt == DSB_DT_F16)
+        scale_by_dev_kernel<__half><<<grid, 256, 0, stream>>>((__half*)x, n, scale_dev);
+    else {
+        dsb200_set_error("scale_by_dev: dtype must be fp16/bf16");
+        return -1;
+    }
+    DSB_CHECK_LAUNCH("scale_by_dev");
+    return 0;
+}
+
+// as dsb200_ce_fwd; the gradient scale is grad_scale * (*grad_scale_dev) when the device pointer is given
+int dsb200_ce_fwd_ex(void* logits, const int64_t* target, float* loss, float* lse, int rows, int vocab,
+                     int64_t row_stride, int ignore_index, int write_grad, float grad_scale, const float* grad_scale_dev,
+                     int dt, cudaStream_t stream)
 {
     if (rows <= 0) return 0;
     if (row_stride % 8 != 0) {
@@ -258,10 +306,11 @@ int dsb200_ce_fwd(void* logits, const int64_t* target, float* loss, float* lse, 
     const int threads = vocab >= 16384 ? 1024 : (vocab >= 2048 ? 256 : 128);
     if (dt == DSB_DT_BF16)
         ce_fwd_kernel<__nv_bfloat16><<<rows, threads, 0, stream>>>((__nv_bfloat16*)logits, target, loss, lse, rows, vocab,
-                                                                   row_stride, ignore_index, write_grad, grad_scale);
+                                                                   row_stride, ignore_index, write_grad, grad_scale,
+                                                                   grad_scale_dev);
     else if (dt == DSB_DT_F16)
         ce_fwd_kernel<__half><<<rows, threads, 0, stream>>>((__half*)logits, target, loss, lse, rows, vocab, row_stride,
-                                                            ignore_index, write_grad, grad_scale);
+                                                            ignore_index, write_grad, grad_scale, grad_scale_dev);
     else {
         dsb200_set_error("cross_entropy: dtype must be fp16/bf16");
         return -1;

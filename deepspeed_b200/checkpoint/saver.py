@@ -286,6 +286,8 @@ def save_engine_checkpoint(engine, save_dir, tag=None, client_state=None, save_l
     if tag is None:
         tag = f"global_step{engine.global_steps}"
     tag = str(tag)
+    if hasattr(engine.optimizer, "_join_step"):
+        engine.optimizer._join_step()  # a pipelined optimizer step may still be running on its side stream
     ce = engine.checkpoint_engine
     from ..runtime.checkpoint_engine import CheckpointCommitInfo
     info = CheckpointCommitInfo(tag=tag, save_dir=save_dir, save_latest=save_latest)
@@ -460,6 +462,8 @@ def load_engine_checkpoint(engine, load_dir, tag=None, load_module_strict=True, 
 
 def _load_zero_state(engine, zsd, load_optimizer_states, load_from_fp32=True):
     z = engine.optimizer
+    if hasattr(z, "_join_step"):
+        z._join_step()
     saved_world = zsd.get("partition_count", z._shard_world)
     if isinstance(saved_world, (list, tuple)):
         saved_world = max(saved_world)

@@ -345,12 +345,15 @@ class SymmContext:
         if self._ce_issued:
             self._wait(CH_CE_DONE, self._ce_issued)
 
-    def all_gather_ce(self, shard_buf: SymmBuffer, shard_offset_bytes, shard_bytes, full):
-        """full[p*shard_bytes ...] = peer p's bytes at ``shard_offset_bytes`` of ``shard_buf``, on the copy engines."""
+    def all_gather_ce(self, shard_buf: SymmBuffer, shard_offset_bytes, shard_bytes, full, need_epoch=0):
+        """full[p*shard_bytes ...] = peer p's bytes at ``shard_offset_bytes`` of ``shard_buf``, on the copy engines.
+        ``need_epoch``: publication after which this shard is final on every peer (a pipelined optimizer step
+        publishes unit by unit); 0 = the latest publication."""
         self._ce_state()
-        if self._ce_seen != self._ce_pub:
-            self._wait(CH_CE_READY, self._ce_pub)  # every peer's shards are final
-            self._ce_seen = self._ce_pub
+        need = need_epoch if 0 < need_epoch <= self._ce_pub else self._ce_pub
+        if need > self._ce_seen:
+            self._wait(CH_CE_READY, need)  # every peer's copy of this shard is final
+            self._ce_seen = need
         ptrs = (ctypes.c_uint64 * 16)(*[(int(p) + shard_offset_bytes) if p else 0 for p in shard_buf.ptrs])
         rc = self.lib.dsb200_symm_all_gather_ce(ptrs, self.rank, self.world, shard_bytes,
                                                 ctypes.c_void_p(full.data_ptr()), self._ce_helper_arr,

@@ -284,14 +284,14 @@ class _LinearCrossEntropyFn(torch.autograd.Function):
             dw = torch.zeros(V, H, dtype=torch.float32, device=h.device)
         loss_sum = torch.zeros((), dtype=torch.float32, device=h.device)
         inv_f = float(inv) if not torch.is_tensor(inv) else None
+        inv_dev = inv.to(torch.float32).reshape(()).contiguous() if inv_f is None else None
         for s in range(0, N, chunk_tokens):
             e = min(N, s + chunk_tokens)
             logits = torch.matmul(h[s:e], weight.t())
             scale = inv_f if inv_f is not None else 1.0
-            loss_rows = K.cross_entropy_inplace_grad(logits, target[s:e], ignore_index, scale)
+            loss_rows = K.cross_entropy_inplace_grad(logits, target[s:e], ignore_index, scale,
+                                                     None if inv_f is not None else inv_dev)
             loss_sum += loss_rows.sum()
-            if inv_f is None:
-                logits.mul_(inv.to(logits.dtype))
             if need_h:
                 torch.matmul(logits, weight, out=dh[s:e])
             if need_w:
@@ -309,17 +309,18 @@ class _LinearCrossEntropyFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, gloss):
         dh, dw = ctx.saved_tensors
-        # the saved gradients are rescaled in place with the vectorised multi-tensor kernel (a broadcast multiply by a
-        # 0-dim device tensor takes the slow strided elementwise path: 2.1 ms for the 128k x 4k lm_head gradient)
+        # the saved gradients are rescaled in place by a vectorised kernel that exits at once when the incoming gradient
+        # is 1 (a broadcast multiply by a 0-dim device tensor takes the slow strided elementwise path: 2.1 ms for the
+        # 128k x 4k lm_head gradient)
         if getattr(ctx, "_consumed", False):
             raise RuntimeError("linear_cross_entropy: backward called twice (gradients were rescaled in place)")
         ctx._consumed = True
         gh = gw = None
+        g32 = gloss.to(torch.float32).reshape(()).contiguous()
         if ctx.need_h:
-            torch._foreach_mul_([dh], gloss.to(torch.float32))
-            gh = dh
+            gh = K.scale_by_device_scalar_(dh, g32) if dh.dtype != torch.float32 else dh.mul_(g32)
         if ctx.need_w:
-            torch._foreach_mul_([dw], gloss.to(torch.float32))
+            dw = K.scale_by_device_scalar_(dw, g32) if dw.dtype != torch.float32 else dw.mul_(g32)
             gw = dw if dw.dtype == ctx.w_dtype else dw.to(ctx.w_dtype)
         return gh, gw, None, None, None, None
 

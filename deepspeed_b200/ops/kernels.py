@@ -120,6 +120,8 @@ def _declare(L):
     sig("dsb200_swiglu_fwd", P, P, P, L64, I, L64, I, P)
     sig("dsb200_swiglu_bwd", P, P, P, P, P, L64, I, L64, I, P)
     sig("dsb200_ce_fwd", P, P, P, P, I, I, L64, I, I, F, I, P)
+    sig("dsb200_ce_fwd_ex", P, P, P, P, I, I, L64, I, I, F, P, I, P)
+    sig("dsb200_scale_by_dev", P, L64, I, P, P)
     sig("dsb200_move_rows", P, P, P, I, L64, L64, L64, L64, L64, I, P)
     sig("dsb200_scatter_add_rows", P, P, P, I, P, L64, I, L64, L64, L64, I, I, P)
     sig("dsb200_sort_rows_i32", P, L64, I, P)
@@ -314,14 +316,23 @@ def swiglu_bwd(dy, gate_up):
     return dgu
 
 
-def cross_entropy_inplace_grad(logits, target, ignore_index, grad_scale):
-    """Per-row loss (fp32); ``logits`` is overwritten with ``(softmax - onehot) * grad_scale``."""
+def cross_entropy_inplace_grad(logits, target, ignore_index, grad_scale, grad_scale_dev=None):
+    """Per-row loss (fp32); ``logits`` is overwritten with ``(softmax - onehot) * grad_scale`` (times the fp32 device
+    scalar ``grad_scale_dev`` when given)."""
     rows, vocab = logits.shape
     assert logits.stride(1) == 1
     loss = torch.empty(rows, dtype=torch.float32, device=logits.device)
-    _check(lib().dsb200_ce_fwd(_ptr(logits), _ptr(target), _ptr(loss), c_void_p(0), rows, vocab, logits.stride(0),
-                               int(ignore_index), 1, float(grad_scale), _dt(logits), _stream()), "ce_fwd")
+    _check(lib().dsb200_ce_fwd_ex(_ptr(logits), _ptr(target), _ptr(loss), c_void_p(0), rows, vocab, logits.stride(0),
+                                  int(ignore_index), 1, float(grad_scale), _ptr(grad_scale_dev), _dt(logits), _stream()),
+           "ce_fwd")
     return loss
+
+
+def scale_by_device_scalar_(x, scale_dev):
+    """``x *= scale_dev`` (0-dim fp32 device tensor) without a host sync; nothing is touched when the scalar is 1."""
+    assert x.is_contiguous() and scale_dev.dtype == torch.float32
+    _check(lib().dsb200_scale_by_dev(_ptr(x), x.numel(), _dt(x), _ptr(scale_dev), _stream()), "scale_by_dev")
+    return x
 
 
 def cross_entropy_fwd(logits, target, ignore_index):

@@ -65,8 +65,9 @@ class _FusedBase(torch.optim.Optimizer):
         return loss
 
     @torch.no_grad()
-    def step_flat(self, grads, lp_params=None, grad_scale=1.0):
-        """``grads``: {param: grad tensor (any float dtype)}; ``lp_params``: {param: low-precision copy to write}."""
+    def step_flat(self, grads, lp_params=None, grad_scale=1.0, advance_step=True):
+        """``grads``: {param: grad tensor (any float dtype)}; ``lp_params``: {param: low-precision copy to write}.
+        ``advance_step=False``: a further slice of the same optimizer step (the ZeRO wrapper steps unit by unit)."""
         lp_params = lp_params or {}
         items = []  # (group_idx, p, g, lp)
         for gi, group in enumerate(self.param_groups):
@@ -79,10 +80,11 @@ class _FusedBase(torch.optim.Optimizer):
                 any_p = True
                 items.append((gi, p, g, lp_params.get(p)))
             if any_p:
-                group["step"] = group.get("step", 0) + 1
+                if advance_step:
+                    group["step"] = group.get("step", 0) + 1
                 for p in group["params"]:
                     if p in grads:
-                        self.state[p]["step"] = group["step"]
+                        self.state[p]["step"] = group.get("step", 1)
         if not items:
             return
         if all(_on_cuda(p) for _, p, _, _ in items):
@@ -100,7 +102,8 @@ class _FusedBase(torch.optim.Optimizer):
                     for gi, p, g, lp in items)
         table = self._table_cache.get(key)
         if table is None:
-            self._table_cache.clear()
+            if len(self._table_cache) >= 512:  # one entry per (unit-sized) slice of the model; stale ones are dropped
+                self._table_cache.clear()
             # kernel slots: [first moment (exp_avg / momentum_buffer) or None, second moment (exp_avg_sq) or None]
             states = [[next((self.state[p][n] for n in ("exp_avg", "momentum_buffer") if n in self.state[p]), None),
                        self.state[p].get("exp_avg_sq")] for _, p, _, _ in items]

@@ -92,6 +92,10 @@ class UnitCoordinator:
             if z._hpz_group is not None and self._in_backward_pass and u.sec_shard is not None:
                 src, group = u.sec_shard, z._hpz_group
             world = dist.get_world_size(group) if group is not None and dist.is_initialized() else 1
+            ev = u.opt_event
+            if ev is not None:  # this unit's slice of a pipelined optimizer step must have landed
+                (z.ag_stream if (use_side and world > 1) else torch.cuda.current_stream()).wait_event(ev)
+                u.opt_event = None
             if world <= 1 and src.numel() == u.numel_padded and src.dtype == u.dtype:
                 # a single shard IS the full parameter: alias it instead of "gathering" through a copy
                 u.full_param = src
@@ -135,7 +139,8 @@ class UnitCoordinator:
             # fused path 2 (v1): pull every peer's shard straight out of its symmetric lp storage over NVLink
             esz = src.element_size()
             if self.z._ag_on_copy_engines:
-                self.z.symm.all_gather_ce(st.lp_symm, u.shard_offset * esz, u.shard_numel * esz, full)
+                self.z.symm.all_gather_ce(st.lp_symm, u.shard_offset * esz, u.shard_numel * esz, full,
+                                          need_epoch=getattr(u, "_ready_epoch", 0))
             else:
                 self.z.symm.all_gather(st.lp_symm, u.shard_offset * esz, u.shard_numel * esz, full)
             return

@@ -196,6 +196,14 @@ class ZeroShardedOptimizer:
         # ZeRO-3 parameter all-gather on the copy engines (DMA pulls from the peers' symmetric shards, no SM taken from
         # the overlapped GEMMs); DSB200_AG_MODE=kernel selects the SM-driven pull kernel instead
         self._ag_on_copy_engines = _os.environ.get("DSB200_AG_MODE", "ce") == "ce"
+        # ZeRO-3 (opt-in, DSB200_PIPELINED_STEP=1): the fused optimizer runs unit by unit in forward order on a side
+        # stream, so the (HBM-bound) update of later layers overlaps the (tensor-core-bound) forward of earlier layers of
+        # the next step. Measured on the 1000 W power-capped B200 of this pool: 213.3 vs 213.8 ms/step for Llama-3-8B
+        # at one GPU -- the step is energy-bound there (SM clock ~1.5 of 1.965 GHz), overlap buys nothing, so it is off
+        # by default; bitwise-identical results (tests/test_engine_gpu.py).
+        self._pipelined_step = _os.environ.get("DSB200_PIPELINED_STEP", "0") == "1"
+        self._opt_stream = None
+        self._step_in_flight = False
         # weight-gradient GEMMs of ops.fused.Linear write straight into the flat gradient buffers
         self._direct_wgrad = _os.environ.get("DSB200_DIRECT_WGRAD", "1") == "1"
         self._allocate_and_link()
@@ -795,6 +803,7 @@ class ZeroShardedOptimizer:
     @torch.no_grad()
     def step(self, closure=None):
         """Partitioned optimizer step. Returns nothing; sets ``self.overflow`` when the step was skipped."""
+        self._join_step()
         if self._use_streams and self.overlap_comm:
             torch.cuda.current_stream().wait_stream(self.rs_stream)
         # any unit still holding unreduced grads (stage<=1 boundary without hooks, no_sync exit)
@@ -1021,6 +1030,8 @@ class ZeroShardedOptimizer:
                 torch.cuda.current_stream().synchronize()
         if self.offload_nvme:
             return self._inner_step_nvme(grad_scale)
+        if fused and self._can_pipeline_step():
+            return self._inner_step_pipelined(grad_scale)
         if fused:
             lp_map, grads = {}, {}
             for (key, a, b, gi, u, v) in self._segments:
@@ -1041,6 +1052,68 @@ class ZeroShardedOptimizer:
         opt.step()
         for (_, _, _, _, _, v) in self._segments:
             v.grad = None
+
+    # ------------------------------------------------------------------ pipelined step ---------
+    def _can_pipeline_step(self):
+        c = self.coordinator
+        return (self._pipelined_step and self.partition_params and c is not None and c._trace_done and c.fwd_order
+                and self._use_streams and not self.offload_optimizer and self._super is None and self._zenflow is None
+                and not getattr(self.optimizer, "needs_full_matrix_update", False)
+                and (self.symm is None or self._ag_on_copy_engines) and self.hpz_size == 1
+                and not self.quantized_weights)
+
+    @torch.no_grad()
+    def _inner_step_pipelined(self, grad_scale):
+        """One fused-optimizer launch per unit instead of one for the whole model: replicated (persistent) units and
+        units outside the recorded forward order first, on the current stream; then the partitioned units in forward
+        order on ``_opt_stream``, each followed by an event (and, with peers, by a publication of its shard). The
+        gather of a unit waits for its event only, so the next forward starts while the tail of the update is still
+        streaming through HBM. Anything else that reads optimizer state calls :meth:`_join_step` first."""
+        opt = self.optimizer
+        if self._opt_stream is None:
+            self._opt_stream = torch.cuda.Stream()
+        by_unit = {}
+        for seg in self._segments:
+            by_unit.setdefault(seg[4].uid, []).append(seg)
+        for g in opt.param_groups:  # every group advances once, whichever unit its parameters sit in
+            g["step"] = g.get("step", 0) + 1
+
+        def step_unit(u):
+            segs = by_unit.get(u.uid)
+            if not segs:
+                return
+            grads, lp_map = {}, {}
+            for (key, a, b, gi, uu, v) in segs:
+                st = self.storages[key]
+                grads[v] = st.grad[a:b]
+                lp_map[v] = self._lp_view(st, uu, a, b)
+            opt.step_flat(grads=grads, lp_params=lp_map, grad_scale=grad_scale, advance_step=False)
+
+        order = [self.units[uid] for uid in self.coordinator.fwd_order if not self.units[uid].persistent]
+        in_order = {u.uid for u in order}
+        for u in self.units:
+            if u.uid not in in_order:
+                step_unit(u)
+        main = torch.cuda.current_stream()
+        self._opt_stream.wait_stream(main)
+        with torch.cuda.stream(self._opt_stream):
+            for u in order:
+                step_unit(u)
+                if self.symm is not None:
+                    self.symm.publish_shards()
+                    u._ready_epoch = self.symm._ce_pub
+                u.opt_event = torch.cuda.Event()
+                u.opt_event.record(self._opt_stream)
+        self._lp_written_by_step = True
+        self._step_in_flight = True
+
+    def _join_step(self):
+        """Wait (stream order) for a pipelined optimizer step still running on the side stream."""
+        if self._step_in_flight:
+            torch.cuda.current_stream().wait_stream(self._opt_stream)
+            self._step_in_flight = False
+            for u in self.units:
+                u.opt_event = None
 
     def _lp_view(self, st, u, a, b):
         if self.partition_params:
@@ -1078,7 +1151,8 @@ class ZeroShardedOptimizer:
     @torch.no_grad()
     def _post_step_gather(self):
         """All-gather updated lp shards of resident units (reference ``all_gather_dp_groups`` utils.py:1016)."""
-        self._lp_shards_written()
+        if not self._step_in_flight:  # the pipelined step publishes unit by unit on its own stream
+            self._lp_shards_written()
         for u in self.units:
             if u.full_param is None or u.world <= 1:
                 continue
@@ -1115,6 +1189,7 @@ class ZeroShardedOptimizer:
     # ------------------------------------------------------------------ fragment / debug API ---
     def _gather_shard_tensor(self, u, shard):
         """Full flat tensor (all ranks' shards) for a unit from the given per-rank shard tensor."""
+        self._join_step()
         if u.world <= 1:
             return shard.clone()
         dev = u.device
@@ -1143,6 +1218,7 @@ class ZeroShardedOptimizer:
         return full[o:o + n].view(u.shapes[i]).float() / float(self.cur_scale)
 
     def set_full_hp_param(self, value, param, optim_state_key=None):
+        self._join_step()
         u, i = self._unit_of_param[id(param)]
         flat = value.reshape(-1)
         for (pi, s_in_p, s_in_shard, n) in u.param_fragments():
@@ -1165,6 +1241,7 @@ class ZeroShardedOptimizer:
 
     def _state_shard(self, u, key):
         """Assemble the optimizer-state shard of a unit from the per-run views held by the inner optimizer."""
+        self._join_step()
         if self._nvme is not None and key in self._nvme_names:
             return self._nvme.read_all(f"unit{u.uid}")[self._nvme_names.index(key)]
         out = torch.zeros(u.shard_numel, dtype=torch.float32, device=u.master_shard.device)
@@ -1202,6 +1279,7 @@ class ZeroShardedOptimizer:
         return tens, scalars
 
     def state_dict(self):
+        self._join_step()
         tens, scalars = self._inner_state_flat()
         pg = []
         for g in self.optimizer.param_groups:
@@ -1237,6 +1315,7 @@ class ZeroShardedOptimizer:
         return dict(units=units, stage=self.stage, shard_world=self._shard_world, shard_rank=self._shard_rank)
 
     def load_state_dict(self, sd, load_optimizer_states=True, load_from_fp32_weights=True, **kw):
+        self._join_step()
         if isinstance(sd, (list, tuple)):  # list of per-rank dicts (reference passes all ranks' states)
             sd = sd[self._shard_rank] if len(sd) > 1 else sd[0]
         self.loss_scaler = sd.get(LOSS_SCALER, self.loss_scaler)
@@ -1283,6 +1362,7 @@ class ZeroShardedOptimizer:
 
     def refresh_lp_from_params(self):
         """After module weights were loaded directly into the lp params: rebuild master shards."""
+        self._join_step()
         with torch.no_grad():
             for u in self.units:
                 if u.full_param is None:
@@ -1293,6 +1373,7 @@ class ZeroShardedOptimizer:
     # ------------------------------------------------------------------ offload_states ---------
     def offload_states(self, include=None, device="cpu", pin_memory=True, non_blocking=False):
         """Move optimizer-side state to host to free HBM between phases (reference stage_1_and_2.py:2915)."""
+        self._join_step()
         include = set(include) if include is not None else {"optim_states", "hp_params", "lp_grads"}
         include = {getattr(i, "value", i) for i in include}
         dev = torch.device(device)

@@ -84,6 +84,8 @@ class FlatUnit:
         self.reduced_this_pass = False
         self.has_grad_data = False
         self.sec_shard = None  # hpZ secondary (intra-group) replica shard
+        self.opt_event = None  # pipelined optimizer step: recorded after this unit's update on the side stream
+        self._ready_epoch = 0  # ... and the symmetric-memory epoch at which every peer has published its shard
 
     # ---- geometry helpers --------------------------------------------------------------------
     def shard_range(self, rank=None):

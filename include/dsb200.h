@@ -91,6 +91,12 @@ int dsb200_swiglu_bwd(const void* dy, const void* gate, const void* up, void* dg
  * Reference: TiledFusedLogitsLoss (runtime/sequence_parallel/ulysses_sp.py:1065). */
 int dsb200_ce_fwd(void* logits, const int64_t* target, float* loss, float* lse, int rows, int vocab, int64_t row_stride,
                   int ignore_index, int write_grad, float grad_scale, int dt, cudaStream_t stream);
+/* as dsb200_ce_fwd with the gradient scale multiplied by a device scalar (e.g. 1 / #valid tokens without a host sync) */
+int dsb200_ce_fwd_ex(void* logits, const int64_t* target, float* loss, float* lse, int rows, int vocab,
+                     int64_t row_stride, int ignore_index, int write_grad, float grad_scale, const float* grad_scale_dev,
+                     int dt, cudaStream_t stream);
+/* x (fp16/bf16) *= *scale_dev, vectorised; a no-op when the device scalar is 1 (incoming loss gradient of 1) */
+int dsb200_scale_by_dev(void* x, int64_t n, int dt, const float* scale_dev, cudaStream_t stream);
 
 /* ---------------------------------------------------------------- fused collective + compute (symm_fused.cu) */
 /* Reduce-scatter my gradient shard out of every peer's bucket and apply AdamW to the fp32 master / moments (+ bf16

@@ -119,3 +119,42 @@ def test_direct_wgrad_matches_hook_path(stage):
         assert abs(x - y) < 3e-2, (la, lb)
     for x, y in zip(na, nb):
         assert abs(x - y) <= 3e-2 * max(1.0, y), (na, nb)
+
+
+def test_pipelined_step_matches_single_launch_step():
+    """ZeRO-3 optimizer step issued unit by unit in forward order on a side stream (overlapping the next forward)
+    vs one launch for the whole model: identical parameters after several steps, and state reads join first."""
+    _env()
+    import deepspeed_b200 as ds
+    from deepspeed_b200.models import LlamaConfig, LlamaForCausalLM
+    from deepspeed_b200.utils.tensor_fragment import safe_get_full_fp32_param
+    dev = torch.device("cuda", 0)
+    cfg = LlamaConfig(vocab_size=1024, hidden_size=128, intermediate_size=256, num_hidden_layers=4,
+                      num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=128)
+    out = []
+    for pipelined in (True, False):
+        torch.manual_seed(0)
+        model = LlamaForCausalLM(cfg, device=dev)
+        eng, _, _, _ = ds.initialize(model=model, config={
+            "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True}, "gradient_clipping": 1.0,
+            "optimizer": {"type": "AdamW", "params": {"lr": 1e-3, "weight_decay": 0.1}},
+            "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 1000, "unit_max_numel": 300000}})
+        assert len(eng.optimizer.units) >= 5
+        eng.optimizer._pipelined_step = pipelined
+        torch.manual_seed(1)
+        losses = []
+        for _ in range(6):
+            ids = torch.randint(0, 1024, (2, 64), device=dev)
+            loss = eng(ids, labels=ids)
+            eng.backward(loss)
+            eng.step()
+            losses.append(float(loss.detach()))
+        if pipelined:
+            assert eng.optimizer._opt_stream is not None, "pipelined step was not taken"
+        params = {n: safe_get_full_fp32_param(p).clone() for n, p in model.named_parameters()}
+        out.append((losses, params))
+        eng.destroy()
+    (la, pa), (lb, pb) = out
+    assert la == lb, (la, lb)
+    for n in pa:
+        torch.testing.assert_close(pa[n], pb[n], rtol=0, atol=0)
