@@ -44,56 +44,106 @@ def parse():
 
 
 class ClockSampler:
-    """Samples SM clocks / throttle reasons with nvidia-smi while the timed region runs."""
+    """Samples SM clocks / throttle reasons of THIS rank's GPU while the timed region runs.
+
+    NVML is queried in-process (pynvml, one device handle) from a background thread. Spawning ``nvidia-smi -lms``
+    instead attaches every GPU of the box (persistence mode is off on the bench boxes) and stalled one or two timed
+    steps by 0.2-1 s, seconds after the spawn (measured: a 950 ms and a 795 ms step inside a 10-step region at 2 GPUs);
+    it is kept only as the fallback when pynvml is missing."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, gpu_index=0):
-        self.rows, self.proc, self.gpu_index = [], None, gpu_index
+    def __init__(self, gpu_index=0, period_s=None):
+        if period_s is None:
+            period_s = float(os.environ.get("DSB200_BENCH_SAMPLE_PERIOD", "0.5"))
+        self.rows, self.proc, self.gpu_index, self.period = [], None, gpu_index, period_s
         self.t_region = 0.0
+        self.nvml, self.handle, self._stop = None, None, False
+        self.t = None
 
     def mark_region_start(self):
-        """Samples before this moment (warm-up; nvidia-smi's own start-up) are discarded."""
+        """Samples before this moment (warm-up; start-up of the sampler) are discarded."""
         self.t_region = time.time()
 
+    def _physical_index(self):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            try:
+                return int(vis.split(",")[self.gpu_index])
+            except Exception:
+                return self.gpu_index
+        return self.gpu_index
+
     def start(self):
+        if os.environ.get("DSB200_BENCH_NO_SAMPLER", "0") == "1":
+            return
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index())
+            self.max_sm = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200", "-i", str(self.gpu_index)], stdout=subprocess.PIPE,
+                                          "-lms", "200", "-i", str(self._physical_index())], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
             self.proc = None
 
+    def _poll(self):
+        n = self.nvml
+        bits = [n.nvmlClocksEventReasonHwSlowdown, n.nvmlClocksEventReasonHwThermalSlowdown,
+                n.nvmlClocksEventReasonSwThermalSlowdown, n.nvmlClocksEventReasonSwPowerCap]
+        while not self._stop:
+            try:
+                sm = float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
+                mask = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+                self.rows.append((time.time(), [self.gpu_index, sm, self.max_sm, 0.0, mask] +
+                                  ["Active" if mask & b else "Not Active" for b in bits]))
+            except Exception:
+                pass
+            time.sleep(self.period)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
+        if self.nvml is not None:
+            self._stop = True
+            self.t.join(timeout=2)
+        elif self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        else:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["clock sampler unavailable"]}
         sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for ts, r in self.rows:
             if ts < self.t_region:
                 continue
             try:
                 sm.append(float(r[1]))
                 mx.append(float(r[2]))
-                for n, v in zip(names, r[5:9]):
-                    if v.lower().startswith("active"):
+                for n, v in zip(self.NAMES, r[5:9]):
+                    if str(v).lower().startswith("active"):
                         reasons.add(n)
             except Exception:
                 continue
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm),
+                "source": "nvml (in-process)" if self.nvml is not None else "nvidia-smi -lms 200"}
 
 
 def model_dims(args):
@@ -293,12 +343,15 @@ def main():
     l0 = launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     e0.record()
     for i in range(K):
         loss = step(dev_inputs[i])
+        marks[i].record()
     e1.record()
     sync_all()
     dev_ms = e0.elapsed_time(e1)
+    step_ms = [round((e0 if i == 0 else marks[i - 1]).elapsed_time(marks[i]), 2) for i in range(K)]
     n_launch = launches() - l0
     last_loss = float(loss)
     # ---- region 2: end to end (pinned H2D each step + loss D2H each step) ----
@@ -350,6 +403,7 @@ def main():
                     "h2d_bytes_per_step": B * S * 8, "d2h_bytes_per_step": 4},
             "gpu_launches": n_launch,
             "clocks": clocks,
+            "step_ms": step_ms,
             "final_loss": last_loss,
             "peak_mem_gib": round(peak_mem, 2),
         }

@@ -3,12 +3,18 @@ a blocked KV cache and returns next-token logits per sequence.
 
 Reference: ``inference/v2/engine_v2.py:30`` (``InferenceEngineV2.put/query/flush``), model implementations
 ``inference/v2/model_implementations/llama_v2`` (here: the framework's own Llama/Mixtral weights), ragged kernels
-``inference/v2/kernels/ragged_ops`` (blocked rotary + KV copy, blocked flash). Attention per sequence uses the
-library SDPA over the gathered blocks; the linear layers / norms / RoPE are the fused ops of this framework."""
+``inference/v2/kernels/ragged_ops`` (blocked rotary + KV copy, blocked flash). On a GPU the attention of the whole
+ragged batch is two launches of ``csrc/ragged_ops.cu`` (RoPE + KV append, paged attention with split-KV); the
+per-sequence SDPA over gathered blocks remains as the CPU / unsupported-shape path. Linear layers / norms are the
+fused ops of this framework."""
+import math
+import os
+
 import torch
 import torch.nn.functional as F
 
 from ...ops import fused
+from ...ops import kernels as K
 from .ragged import BlockedKVCache, DSStateManager, RaggedBatchWrapper
 
 
@@ -35,6 +41,7 @@ class InferenceEngineV2:
         self.state_manager = DSStateManager(kv, self.config.max_tracked_sequences, self.config.max_ragged_batch_size,
                                             self.config.max_ragged_sequence_count)
         self.batch = RaggedBatchWrapper()
+        self._meta = None
         self.generic = hasattr(model, "forward_tokens")  # model_implementations.GenericDecoder (any HF family)
         if not self.generic:
             self.cos, self.sin = fused.rope_tables(c.max_position_embeddings, c.head_dim, c.rope_theta, self.device,
@@ -74,14 +81,37 @@ class InferenceEngineV2:
             seq.pre_forward(len(toks))
             self.batch.insert_sequence(seq, toks)
         ids = self.batch.finalize(self.device)
+        self._meta = None
         logits = self._forward(ids)
         for seq, _, _, _ in self.batch.seq_meta:
             seq.post_forward()
         return logits
 
+    # ---- native ragged kernels --------------------------------------------------------------------
+    def _native(self, q, nh, nkv, hd):
+        return (os.environ.get("DSB200_RAGGED_NATIVE", "1") == "1" and q.is_cuda
+                and K.ragged_attention_supported(q, hd, nh, nkv))
+
+    def _batch_meta(self):
+        if self._meta is None:
+            tok_seq, tok_pos, table = self.batch.device_metadata(self.device)
+            max_ctx = max(seen + n for (_, _, n, seen) in self.batch.seq_meta)
+            self._meta = (tok_seq, tok_pos, table, max_ctx)
+        return self._meta
+
+    def _attend_native(self, li, q, k, v, cos=None, sin=None, rotary_dim=0):
+        """q [T, Hq, D] (rotated in place when ``rotary_dim``), k / v [T, Hkv, D] -> [T, Hq * D]."""
+        tok_seq, tok_pos, table, max_ctx = self._batch_meta()
+        kv_layer = self.state_manager.kv.cache[li]
+        K.ragged_kv_append_rope(q, k, v, kv_layer, cos, sin, tok_seq, tok_pos, table, rotary_dim)
+        o = K.ragged_paged_attention(q, kv_layer, tok_seq, tok_pos, table, 1.0 / math.sqrt(q.shape[-1]), max_ctx)
+        return o.reshape(q.shape[0], -1)
+
     def _attend(self, li, q, k, v):
         """Blocked-KV attention for the current ragged batch: q/k/v are [T, heads, head_dim] with positions applied."""
         nh, nkv = q.shape[1], k.shape[1]
+        if self._native(q, nh, nkv, q.shape[2]):
+            return self._attend_native(li, q, k, v)
         outs = []
         for (seq, start, n, seen) in self.batch.seq_meta:
             self.state_manager.kv.write(li, seq, k[start:start + n], v[start:start + n], seen)
@@ -114,6 +144,14 @@ class InferenceEngineV2:
             qkv = attn.qkv_proj(x)
             lnh, lnkv = attn.nh, attn.nkv
             q, k, v = qkv.split([lnh * hd, lnkv * hd, lnkv * hd], dim=-1)
+            if self._native(qkv, lnh, lnkv, hd):
+                T = qkv.shape[0]
+                a = attn.o_proj(self._attend_native(li, q.view(T, lnh, hd), k.view(T, lnkv, hd), v.view(T, lnkv, hd),
+                                                    self.cos, self.sin, hd))
+                x2, h = layer.post_attention_layernorm(a, residual=h)
+                ffn = layer.mlp if hasattr(layer, "mlp") else layer.block_sparse_moe
+                h = h + ffn(x2.unsqueeze(0))[0] if not hasattr(layer, "mlp") else h + ffn(x2)
+                continue
             q = fused.apply_rope(q.reshape(1, -1, lnh, hd), self.cos, self.sin, pos.view(1, -1))[0]
             k = fused.apply_rope(k.reshape(1, -1, lnkv, hd), self.cos, self.sin, pos.view(1, -1))[0]
             v = v.reshape(-1, lnkv, hd)

@@ -68,11 +68,12 @@ class DSSequenceDescriptor:
 
 
 class BlockedKVCache:
-    """[layers, num_blocks, block_size, 2, kv_heads, head_dim]"""
+    """[layers, num_blocks, 2 (K | V), block_size, kv_heads, head_dim]: the K (or V) plane of a block is one contiguous
+    [block_size, kv_heads * head_dim] matrix (what the paged-attention kernels of ``csrc/ragged_ops.cu`` stream)."""
 
     def __init__(self, num_layers, num_blocks, block_size, kv_heads, head_dim, dtype, device):
         self.block_size = block_size
-        self.cache = torch.zeros(num_layers, num_blocks, block_size, 2, kv_heads, head_dim, dtype=dtype, device=device)
+        self.cache = torch.zeros(num_layers, num_blocks, 2, block_size, kv_heads, head_dim, dtype=dtype, device=device)
         self.allocator = BlockedAllocator(num_blocks)
 
     def write(self, layer, seq: DSSequenceDescriptor, k, v, start):
@@ -81,13 +82,14 @@ class BlockedKVCache:
         pos = torch.arange(start, start + n, device=k.device)
         blk = torch.tensor(seq.blocks, device=k.device)[pos // self.block_size]
         off = pos % self.block_size
-        self.cache[layer, blk, off, 0] = k
-        self.cache[layer, blk, off, 1] = v
+        self.cache[layer, blk, 0, off] = k
+        self.cache[layer, blk, 1, off] = v
 
     def read(self, layer, seq: DSSequenceDescriptor, length):
         blk = torch.tensor(seq.blocks, device=self.cache.device)
-        kv = self.cache[layer, blk].reshape(-1, 2, self.cache.shape[-2], self.cache.shape[-1])[:length]
-        return kv[:, 0], kv[:, 1]
+        kv = self.cache[layer, blk]  # [n_blocks, 2, block_size, heads, dim]
+        heads, dim = self.cache.shape[-2], self.cache.shape[-1]
+        return kv[:, 0].reshape(-1, heads, dim)[:length], kv[:, 1].reshape(-1, heads, dim)[:length]
 
 
 class DSStateManager:
@@ -150,6 +152,22 @@ class RaggedBatchWrapper:
 
     def finalize(self, device):
         return torch.cat(self.tokens).to(device)
+
+    def device_metadata(self, device, max_blocks=None):
+        """Per-token (sequence row, absolute position) and the block table of the batch, as int32 device tensors:
+        the inputs of the ragged kernels (reference ``ragged_wrapper.py`` inflight descriptors + ``kv_ptrs``)."""
+        tok_seq, tok_pos = [], []
+        for row, (seq, start, n, seen) in enumerate(self.seq_meta):
+            tok_seq += [row] * n
+            tok_pos += list(range(seen, seen + n))
+        width = max_blocks or max(1, max(len(seq.blocks) for seq, _, _, _ in self.seq_meta))
+        table = torch.zeros(len(self.seq_meta), width, dtype=torch.int32)
+        for row, (seq, _, _, _) in enumerate(self.seq_meta):
+            if seq.blocks:
+                table[row, :len(seq.blocks)] = torch.tensor(seq.blocks, dtype=torch.int32)
+        host = torch.tensor([tok_seq, tok_pos], dtype=torch.int32)
+        dev = host.to(device, non_blocking=True)
+        return dev[0].contiguous(), dev[1].contiguous(), table.to(device, non_blocking=True)
 
     @property
     def current_tokens(self):

@@ -122,6 +122,8 @@ def _declare(L):
     sig("dsb200_ce_fwd", P, P, P, P, I, I, L64, I, I, F, I, P)
     sig("dsb200_ce_fwd_ex", P, P, P, P, I, I, L64, I, I, F, P, I, P)
     sig("dsb200_scale_by_dev", P, L64, I, P, P)
+    sig("dsb200_ragged_kv_append_rope", P, P, P, P, P, P, P, P, P, I, L64, L64, L64, I, I, I, I, I, I, I, P)
+    sig("dsb200_ragged_paged_attention", P, P, P, P, P, P, P, P, I, L64, I, I, I, I, I, I, F, P)
     sig("dsb200_move_rows", P, P, P, I, L64, L64, L64, L64, L64, I, P)
     sig("dsb200_scatter_add_rows", P, P, P, I, P, L64, I, L64, L64, L64, I, I, P)
     sig("dsb200_sort_rows_i32", P, L64, I, P)
@@ -416,3 +418,56 @@ def gemm_bf16_nt(a, b, out=None, max_ctas=0, block_n=0):
     _check(L.dsb200_gemm_bf16_nt(_ptr(a), _ptr(b), _ptr(out), M, N, Kd, a.stride(0), b.stride(0), out.stride(0),
                                  int(max_ctas), int(block_n), _stream()), "gemm_bf16_nt")
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# FastGen ragged ops (csrc/ragged_ops.cu)
+# ---------------------------------------------------------------------------------------------------------
+def ragged_kv_append_rope(q, k, v, kv_layer, cos, sin, tok_seq, tok_pos, block_table, rotary_dim):
+    """RoPE on q [T, Hq, D] in place and on k, then k / v [T, Hkv, D] are appended to the blocked cache of one layer
+    ``kv_layer`` [num_blocks, 2, block_size, Hkv, D]. ``rotary_dim`` 0: positions are not rotary."""
+    T, Hq, D = q.shape
+    Hkv = k.shape[1]
+    assert q.stride(2) == 1 and q.stride(1) == D and k.stride(1) == D and v.stride(1) == D and kv_layer.is_contiguous()
+    _check(lib().dsb200_ragged_kv_append_rope(
+        _ptr(q), _ptr(k), _ptr(v), _ptr(kv_layer), _ptr(cos), _ptr(sin), _ptr(tok_seq), _ptr(tok_pos), _ptr(block_table),
+        T, q.stride(0), k.stride(0), v.stride(0), Hq, Hkv, D, int(rotary_dim), kv_layer.shape[2], block_table.shape[1],
+        _dt(q), _stream()), "ragged_kv_append_rope")
+
+
+_PA_SCRATCH = {}
+
+
+def ragged_paged_attention(q, kv_layer, tok_seq, tok_pos, block_table, scale, max_context, out=None):
+    """Every token of the ragged batch attends to keys [0, pos] of its sequence in the blocked cache.
+    q [T, Hq, D] (bf16, D in {64, 128}) -> out [T, Hq, D]. The key range is split over several CTAs (flash-decoding)
+    when the batch alone cannot fill the GPU."""
+    T, Hq, D = q.shape
+    Hkv = kv_layer.shape[3]
+    if out is None:
+        out = torch.empty((T, Hq, D), dtype=q.dtype, device=q.device)
+    tiles = max(1, (int(max_context) + 31) // 32)
+    splits = 1
+    if T * Hkv < 2 * 148:
+        splits = max(1, min(tiles // 4, (4 * 148) // max(1, T * Hkv), 32))
+    pa = pm = None
+    if splits > 1:
+        key = (q.device, T * Hq * splits * (D + 2))
+        buf = _PA_SCRATCH.get(key)
+        if buf is None:
+            _PA_SCRATCH.clear()
+            buf = _PA_SCRATCH[key] = torch.empty(T * Hq * splits * (D + 2), dtype=torch.float32, device=q.device)
+        pa, pm = buf[:T * Hq * splits * D], buf[T * Hq * splits * D:]
+    rc = lib().dsb200_ragged_paged_attention(_ptr(q), _ptr(kv_layer), _ptr(out), _ptr(tok_seq), _ptr(tok_pos),
+                                             _ptr(block_table), _ptr(pa), _ptr(pm), T, q.stride(0), Hq, Hkv, D,
+                                             kv_layer.shape[2], block_table.shape[1], splits, float(scale), _stream())
+    if rc < 0:
+        raise RuntimeError(f"ragged_paged_attention failed: {last_error()}")
+    global _LAUNCHES
+    _LAUNCHES += 1
+    return out
+
+
+def ragged_attention_supported(q, head_dim, n_heads, n_kv_heads):
+    return (available() and q.is_cuda and q.dtype == torch.bfloat16 and head_dim in (64, 128)
+            and n_heads % n_kv_heads == 0 and n_heads // n_kv_heads in (1, 2, 4, 8))
