@@ -142,6 +142,14 @@ struct FaParams {
     float scale_log2;  // softmax scale * log2(e)
     int causal;
     int pairs;  // ceil(Sq / 256)
+    // ragged / paged mode (FastGen prefill): `B` sequences packed back to back in q / o ([T_total, H, 128]); keys and
+    // values come from a blocked cache [num_blocks, 2, 128, Hkv, 128] through a block table. Null in dense mode.
+    const int* cu_q;         // [B] first packed row of each sequence
+    const int* q_len;        // [B] query rows of each sequence in this batch
+    const int* kv_len;       // [B] keys visible to the last query row (tokens already cached + q_len)
+    const int* block_table;  // [B, max_blocks]
+    int max_blocks;
+    int lse_stride;          // elements between heads in lse (Sq dense, T_total ragged)
 };
 
 template <unsigned EMU_MASK>
@@ -163,17 +171,22 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     const int rem = (int)(blockIdx.x % bh);
     const int b = rem / prm.H, h = rem % prm.H;
     const int hk = h / (prm.H / prm.Hkv);
-    const int q0 = pair * 2 * FA_BM;  // first query row of tile 0
+    const int q0 = pair * 2 * FA_BM;  // first query row of tile 0 (relative to the sequence)
+    const bool ragged = prm.cu_q != nullptr;
+    const int Sq = ragged ? prm.q_len[b] : prm.Sq;
+    const int Skv = ragged ? prm.kv_len[b] : prm.Skv;
+    const int row_base = ragged ? prm.cu_q[b] : 0;  // packed row of the sequence's first query
+    if (q0 >= Sq) return;                           // ragged batches are launched for the longest sequence
     // number of key blocks per tile
-    const int nb_all = (prm.Skv + FA_BN - 1) / FA_BN;
+    const int nb_all = (Skv + FA_BN - 1) / FA_BN;
     int nb_t[2];
 #pragma unroll
     for (int t = 0; t < 2; t++) {
         const int row0 = q0 + t * FA_BM;
-        if (row0 >= prm.Sq) {
+        if (row0 >= Sq) {
             nb_t[t] = 0;
         } else if (prm.causal) {
-            const int last_row = min(row0 + FA_BM, prm.Sq) - 1 + (prm.Skv - prm.Sq);  // bottom-right aligned
+            const int last_row = min(row0 + FA_BM, Sq) - 1 + (Skv - Sq);  // bottom-right aligned
             nb_t[t] = max(0, min(nb_all, last_row / FA_BN + 1));
         } else {
             nb_t[t] = nb_all;
@@ -221,22 +234,25 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
 #pragma unroll
                 for (int hf = 0; hf < 2; hf++)
                     tma_load_3d(q_smem + t * FA_TILE_BYTES + hf * FA_HALF_BYTES, &map_q, &bars->q_full,
-                                h * FA_D + hf * 64, q0 + t * FA_BM, b);
+                                h * FA_D + hf * 64, row_base + q0 + t * FA_BM, ragged ? 0 : b);
             int stage = 0;
             uint32_t phase = 0;
             for (int j = 0; j < nb; j++) {
+                // dense: rows [j*128, +128) of batch b; paged: plane (block*2 + {K,V}) of the cache, rows [0, 128)
+                const int blk = ragged ? prm.block_table[(int64_t)b * prm.max_blocks + j] : 0;
+                const int krow = ragged ? 0 : j * FA_BN, kz = ragged ? blk * 2 : b, vz = ragged ? blk * 2 + 1 : b;
                 mbar_wait(&bars->k_empty[stage], phase ^ 1);
                 mbar_expect_tx(&bars->k_full[stage], FA_TILE_BYTES);
 #pragma unroll
                 for (int hf = 0; hf < 2; hf++)
                     tma_load_3d(k_smem + stage * FA_TILE_BYTES + hf * FA_HALF_BYTES, &map_k, &bars->k_full[stage],
-                                hk * FA_D + hf * 64, j * FA_BN, b);
+                                hk * FA_D + hf * 64, krow, kz);
                 mbar_wait(&bars->v_empty[stage], phase ^ 1);
                 mbar_expect_tx(&bars->v_full[stage], FA_TILE_BYTES);
 #pragma unroll
                 for (int hf = 0; hf < 2; hf++)
                     tma_load_3d(v_smem + stage * FA_TILE_BYTES + hf * FA_HALF_BYTES, &map_v, &bars->v_full[stage],
-                                hk * FA_D + hf * 64, j * FA_BN, b);
+                                hk * FA_D + hf * 64, krow, vz);
                 if (++stage == FA_KV_STAGES) {
                     stage = 0;
                     phase ^= 1;
@@ -315,15 +331,15 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
         const uint32_t s_addr = tmem_base + lane_addr + COL_S0 + t * 128;
         const uint32_t o_addr = tmem_base + lane_addr + COL_O0 + t * 128;
         const int my_nb = nb_t[t];
-        const int causal_off = prm.Skv - prm.Sq;
+        const int causal_off = Skv - Sq;
         float m_run = -INFINITY, l_run = 0.f;
         for (int j = 0; j < my_nb; j++) {
             mbar_wait(&bars->s_full[t], (uint32_t)(j & 1));
             tc_fence_after();
             const int col0 = j * FA_BN;
             // does this block need masking (diagonal block of the causal mask, or the tail of the key sequence)?
-            const bool need_mask = (prm.causal && (col0 + FA_BN - 1 > q0 + t * FA_BM + causal_off)) || (col0 + FA_BN > prm.Skv);
-            const int col_limit = prm.causal ? min(prm.Skv, row + causal_off + 1) : prm.Skv;  // valid keys: col < col_limit
+            const bool need_mask = (prm.causal && (col0 + FA_BN - 1 > q0 + t * FA_BM + causal_off)) || (col0 + FA_BN > Skv);
+            const int col_limit = prm.causal ? min(Skv, row + causal_off + 1) : Skv;  // valid keys: col < col_limit
             // ---- the whole score row lives in registers: one TMEM round trip ----
             uint32_t r[4][32];
 #pragma unroll
@@ -409,8 +425,9 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
             mbar_wait(&bars->o_full[t], 0);
             tc_fence_after();
             const float inv_l = (l_run > 0.f) ? 1.f / l_run : 0.f;
-            const bool valid = row < prm.Sq;
-            __nv_bfloat16* orow = prm.o + (int64_t)b * prm.o_batch_stride + (int64_t)row * prm.o_row_stride + h * FA_D;
+            const bool valid = row < Sq;
+            __nv_bfloat16* orow = prm.o + (ragged ? 0 : (int64_t)b * prm.o_batch_stride) +
+                                  (int64_t)(row_base + row) * prm.o_row_stride + h * FA_D;
 #pragma unroll 1
             for (int c = 0; c < 4; c++) {
                 uint32_t r[32];
@@ -431,13 +448,15 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
             }
             if (valid && prm.lse != nullptr) {
                 const float lse = (l_run > 0.f) ? (m_run + log2f(l_run)) * 0.6931471805599453f : -INFINITY;
-                prm.lse[((int64_t)b * prm.H + h) * prm.Sq + row] = lse;
+                prm.lse[((int64_t)(ragged ? 0 : b) * prm.H + h) * prm.lse_stride + row_base + row] = lse;
             }
-        } else if (row < prm.Sq && q0 + t * FA_BM < prm.Sq) {
+        } else if (row < Sq && q0 + t * FA_BM < Sq) {
             // no visible key at all (causal with Skv < Sq): zeros
-            __nv_bfloat16* orow = prm.o + (int64_t)b * prm.o_batch_stride + (int64_t)row * prm.o_row_stride + h * FA_D;
+            __nv_bfloat16* orow = prm.o + (ragged ? 0 : (int64_t)b * prm.o_batch_stride) +
+                                  (int64_t)(row_base + row) * prm.o_row_stride + h * FA_D;
             for (int i = 0; i < FA_D; i += 8) *reinterpret_cast<uint4*>(orow + i) = make_uint4(0, 0, 0, 0);
-            if (prm.lse != nullptr) prm.lse[((int64_t)b * prm.H + h) * prm.Sq + row] = -INFINITY;
+            if (prm.lse != nullptr)
+                prm.lse[((int64_t)(ragged ? 0 : b) * prm.H + h) * prm.lse_stride + row_base + row] = -INFINITY;
         }
     }
     tc_fence_before();
@@ -473,32 +492,11 @@ int make_map_3d(CUtensorMap* map, const void* ptr, int64_t batch, int64_t seq, i
 
 }  // namespace
 
-extern "C" {
+namespace {
 
-// q [B, Sq, H, 128], k / v [B, Skv, Hkv, 128], o [B, Sq, H, 128] (all bf16; strides in elements, last dim contiguous,
-// heads packed 128 apart), lse [B, H, Sq] fp32 (may be null). causal: bottom-right aligned when Skv != Sq.
-int dsb200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int Sq, int Skv,
-                          int H, int Hkv, int64_t q_row_stride, int64_t q_batch_stride, int64_t k_row_stride,
-                          int64_t k_batch_stride, int64_t v_row_stride, int64_t v_batch_stride, int64_t o_row_stride,
-                          int64_t o_batch_stride, float scale, int causal, cudaStream_t stream)
+int launch_flash_fwd(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const FaParams& prm,
+                     cudaStream_t stream)
 {
-    if (B <= 0 || Sq <= 0 || Skv <= 0) return 0;
-    if (H % Hkv != 0 || (o_row_stride % 8) || (o_batch_stride % 8) || ((uintptr_t)o & 15)) {
-        dsb200_set_error("flash_attn_fwd: H must be a multiple of Hkv; output must be 16-byte aligned");
-        return -1;
-    }
-    CUtensorMap mq, mk, mv;
-    if (make_map_3d(&mq, q, B, Sq, (int64_t)H * FA_D, q_row_stride, q_batch_stride, FA_BM) != 0) return -2;
-    if (make_map_3d(&mk, k, B, Skv, (int64_t)Hkv * FA_D, k_row_stride, k_batch_stride, FA_BN) != 0) return -2;
-    if (make_map_3d(&mv, v, B, Skv, (int64_t)Hkv * FA_D, v_row_stride, v_batch_stride, FA_BN) != 0) return -2;
-    FaParams prm;
-    prm.o = (__nv_bfloat16*)o;
-    prm.lse = lse;
-    prm.B = B, prm.Sq = Sq, prm.Skv = Skv, prm.H = H, prm.Hkv = Hkv;
-    prm.o_row_stride = o_row_stride, prm.o_batch_stride = o_batch_stride;
-    prm.scale_log2 = scale * 1.4426950408889634f;
-    prm.causal = causal;
-    prm.pairs = (Sq + 2 * FA_BM - 1) / (2 * FA_BM);
     // share of exponentials computed on the FMA pipes instead of the MUFU (tuning knob DSB200_FA_EMU = 0..3 ->
     // 0 / 25 / 37.5 / 50 %). Measured on B200 (S = 4096..8192): 0 % is fastest (1.24 PFLOP/s non-causal at 8192; every
     // extra 12.5 % costs ~3 %), the softmax warps are issue-bound before they are MUFU-bound, so the default is 0.
@@ -508,7 +506,7 @@ int dsb200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, 
         emu = e ? atoi(e) : 0;
         if (emu < 0 || emu > 3) emu = 0;
     }
-    const int64_t grid = (int64_t)prm.pairs * B * H;
+    const int64_t grid = (int64_t)prm.pairs * prm.B * prm.H;
     int dev_ = 0;
     cudaGetDevice(&dev_);
 #define FA_LAUNCH(MASK)                                                                                             \
@@ -532,6 +530,75 @@ int dsb200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, 
 #undef FA_LAUNCH
     DSB_CHECK_LAUNCH("flash_attn_fwd");
     return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+// q [B, Sq, H, 128], k / v [B, Skv, Hkv, 128], o [B, Sq, H, 128] (all bf16; strides in elements, last dim contiguous,
+// heads packed 128 apart), lse [B, H, Sq] fp32 (may be null). causal: bottom-right aligned when Skv != Sq.
+int dsb200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int Sq, int Skv,
+                          int H, int Hkv, int64_t q_row_stride, int64_t q_batch_stride, int64_t k_row_stride,
+                          int64_t k_batch_stride, int64_t v_row_stride, int64_t v_batch_stride, int64_t o_row_stride,
+                          int64_t o_batch_stride, float scale, int causal, cudaStream_t stream)
+{
+    if (B <= 0 || Sq <= 0 || Skv <= 0) return 0;
+    if (H % Hkv != 0 || (o_row_stride % 8) || (o_batch_stride % 8) || ((uintptr_t)o & 15)) {
+        dsb200_set_error("flash_attn_fwd: H must be a multiple of Hkv; output must be 16-byte aligned");
+        return -1;
+    }
+    CUtensorMap mq, mk, mv;
+    if (make_map_3d(&mq, q, B, Sq, (int64_t)H * FA_D, q_row_stride, q_batch_stride, FA_BM) != 0) return -2;
+    if (make_map_3d(&mk, k, B, Skv, (int64_t)Hkv * FA_D, k_row_stride, k_batch_stride, FA_BN) != 0) return -2;
+    if (make_map_3d(&mv, v, B, Skv, (int64_t)Hkv * FA_D, v_row_stride, v_batch_stride, FA_BN) != 0) return -2;
+    FaParams prm = {};
+    prm.o = (__nv_bfloat16*)o;
+    prm.lse = lse;
+    prm.B = B, prm.Sq = Sq, prm.Skv = Skv, prm.H = H, prm.Hkv = Hkv;
+    prm.o_row_stride = o_row_stride, prm.o_batch_stride = o_batch_stride;
+    prm.scale_log2 = scale * 1.4426950408889634f;
+    prm.causal = causal;
+    prm.pairs = (Sq + 2 * FA_BM - 1) / (2 * FA_BM);
+    prm.lse_stride = Sq;
+    return launch_flash_fwd(mq, mk, mv, prm, stream);
+}
+
+// Ragged prefill over a blocked KV cache (FastGen): `n_seqs` sequences packed back to back in q / o [T_total, H, 128]
+// (row stride in elements); sequence s owns rows [cu_q[s], cu_q[s] + q_len[s]) and attends causally to the first
+// kv_len[s] keys of its blocks (kv_len - q_len of them were cached by earlier chunks). `kv` is one layer of the cache,
+// [num_blocks, 2, 128, Hkv, 128] -- the block size must equal the kernel's key block (128). cu_q / q_len / kv_len /
+// block_table are device int32 arrays; max_q_len is the host-side maximum of q_len. lse [H, T_total] may be null.
+// Reference: inference/v2/kernels/ragged_ops/blocked_flash (paged FA2 fork).
+int dsb200_flash_attn_fwd_paged(const void* q, const void* kv, void* o, float* lse, const int* cu_q, const int* q_len,
+                                const int* kv_len, const int* block_table, int n_seqs, int T_total, int max_q_len,
+                                int H, int Hkv, int num_blocks, int max_blocks, int64_t q_row_stride,
+                                int64_t o_row_stride, float scale, cudaStream_t stream)
+{
+    if (n_seqs <= 0 || T_total <= 0 || max_q_len <= 0) return 0;
+    if (H % Hkv != 0 || (o_row_stride % 8) || ((uintptr_t)o & 15)) {
+        dsb200_set_error("flash_attn_fwd_paged: H must be a multiple of Hkv; output must be 16-byte aligned");
+        return -1;
+    }
+    CUtensorMap mq, mk;
+    if (make_map_3d(&mq, q, 1, T_total, (int64_t)H * FA_D, q_row_stride, (int64_t)T_total * q_row_stride, FA_BM) != 0)
+        return -2;
+    // the cache as [num_blocks * 2 planes, 128 rows, Hkv * 128]
+    const int64_t plane = (int64_t)FA_BN * Hkv * FA_D;
+    if (make_map_3d(&mk, kv, (int64_t)num_blocks * 2, FA_BN, (int64_t)Hkv * FA_D, (int64_t)Hkv * FA_D, plane, FA_BN) != 0)
+        return -2;
+    FaParams prm = {};
+    prm.o = (__nv_bfloat16*)o;
+    prm.lse = lse;
+    prm.B = n_seqs, prm.Sq = max_q_len, prm.Skv = 0, prm.H = H, prm.Hkv = Hkv;
+    prm.o_row_stride = o_row_stride, prm.o_batch_stride = 0;
+    prm.scale_log2 = scale * 1.4426950408889634f;
+    prm.causal = 1;
+    prm.pairs = (max_q_len + 2 * FA_BM - 1) / (2 * FA_BM);
+    prm.cu_q = cu_q, prm.q_len = q_len, prm.kv_len = kv_len, prm.block_table = block_table;
+    prm.max_blocks = max_blocks;
+    prm.lse_stride = T_total;
+    return launch_flash_fwd(mq, mk, mk, prm, stream);
 }
 
 }  // extern "C"

@@ -30,6 +30,7 @@ struct PagedArgs {
     const int* tok_seq;       // [T] sequence slot of each token (row of block_table)
     const int* tok_pos;       // [T] absolute position of each token inside its sequence
     const int* block_table;   // [n_seqs, max_blocks]
+    const int* tok_row;       // [T] row of q / out for each listed token (null: row == index)
     float* part_acc;          // [T, Hq, splits, D] (splits > 1)
     float* part_ml;           // [T, Hq, splits, 2]
     int64_t q_stride;
@@ -61,9 +62,10 @@ __global__ void __launch_bounds__(PA_THREADS) paged_attention_kernel(const Paged
     __shared__ float s_m[PA_WARPS][G], s_l[PA_WARPS][G];
     static_assert(G * D * 4 <= PA_TILE * ROW * 2, "partial output must fit in the tile buffer");
 
-    const int t = blockIdx.x, hk = blockIdx.y, split = blockIdx.z;
+    const int ti = blockIdx.x, hk = blockIdx.y, split = blockIdx.z;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int seq = a.tok_seq[t], pos = a.tok_pos[t];
+    const int seq = a.tok_seq[ti], pos = a.tok_pos[ti];
+    const int t = a.tok_row != nullptr ? a.tok_row[ti] : ti;  // row of q / out
     const int n_keys = pos + 1;
     const int n_tiles = (n_keys + PA_TILE - 1) / PA_TILE;
     // this split's tile range
@@ -221,7 +223,7 @@ __global__ void __launch_bounds__(PA_THREADS) paged_attention_kernel(const Paged
         if (a.splits == 1) {
             a.out[((int64_t)t * a.Hq + hq) * D + d] = __float2bfloat16_rn(ll > 0.f ? o / ll : 0.f);
         } else {
-            const int64_t base = ((int64_t)t * a.Hq + hq) * a.splits + split;
+            const int64_t base = ((int64_t)ti * a.Hq + hq) * a.splits + split;
             a.part_acc[base * D + d] = o;
             if (d == 0) {
                 a.part_ml[base * 2] = mm;
@@ -234,10 +236,12 @@ __global__ void __launch_bounds__(PA_THREADS) paged_attention_kernel(const Paged
 template <int D>
 __global__ void __launch_bounds__(D) paged_attention_merge_kernel(const float* __restrict__ part_acc,
                                                                   const float* __restrict__ part_ml,
-                                                                  __nv_bfloat16* __restrict__ out, int splits)
+                                                                  __nv_bfloat16* __restrict__ out, int splits, int Hq,
+                                                                  const int* __restrict__ tok_row)
 {
-    const int64_t row = blockIdx.x;  // token * Hq + head
+    const int64_t row = blockIdx.x;  // listed token * Hq + head
     const int d = threadIdx.x;
+    const int64_t out_row = tok_row != nullptr ? (int64_t)tok_row[row / Hq] * Hq + row % Hq : row;
     float mm = -INFINITY;
     for (int s = 0; s < splits; s++) mm = fmaxf(mm, part_ml[(row * splits + s) * 2]);
     float ll = 0.f, o = 0.f;
@@ -247,7 +251,7 @@ __global__ void __launch_bounds__(D) paged_attention_merge_kernel(const float* _
         ll += part_ml[(row * splits + s) * 2 + 1] * f;
         o += part_acc[(row * splits + s) * D + d] * f;
     }
-    out[row * D + d] = __float2bfloat16_rn(ll > 0.f ? o / ll : 0.f);
+    out[out_row * D + d] = __float2bfloat16_rn(ll > 0.f ? o / ll : 0.f);
 }
 
 // one CTA per token; threads sweep (head, rotary pair)
@@ -328,10 +332,12 @@ int dsb200_ragged_kv_append_rope(void* q, const void* k, const void* v, void* kv
     return 0;
 }
 
+// The T listed tokens are rows tok_row[i] of q / out (tok_row null: row i), so a subset of a ragged batch can be served.
 // Scratch needed for `splits` > 1: part_acc T*Hq*splits*D floats, part_ml T*Hq*splits*2 floats.
 // Supported: bf16, head_dim 64 / 128, Hq / Hkv in {1, 2, 4, 8}. Returns the number of splits used (>= 1) or < 0.
 int dsb200_ragged_paged_attention(const void* q, const void* kv, void* out, const int* tok_seq, const int* tok_pos,
-                                  const int* block_table, float* part_acc, float* part_ml, int T, int64_t q_stride,
+                                  const int* block_table, const int* tok_row, float* part_acc, float* part_ml, int T,
+                                  int64_t q_stride,
                                   int Hq, int Hkv, int D, int block_size, int max_blocks, int splits, float scale,
                                   cudaStream_t stream)
 {
@@ -348,7 +354,7 @@ int dsb200_ragged_paged_attention(const void* q, const void* kv, void* out, cons
     }
     PagedArgs a;
     a.q = (const __nv_bfloat16*)q, a.kv = (const __nv_bfloat16*)kv, a.out = (__nv_bfloat16*)out;
-    a.tok_seq = tok_seq, a.tok_pos = tok_pos, a.block_table = block_table;
+    a.tok_seq = tok_seq, a.tok_pos = tok_pos, a.block_table = block_table, a.tok_row = tok_row;
     a.part_acc = part_acc, a.part_ml = part_ml;
     a.q_stride = q_stride;
     a.T = T, a.Hq = Hq, a.Hkv = Hkv, a.block_size = block_size, a.max_blocks = max_blocks, a.splits = splits;
@@ -371,9 +377,11 @@ int dsb200_ragged_paged_attention(const void* q, const void* kv, void* out, cons
     DSB_CHECK_LAUNCH("ragged_paged_attention");
     if (splits > 1) {
         if (D == 128)
-            paged_attention_merge_kernel<128><<<T * Hq, 128, 0, stream>>>(part_acc, part_ml, (__nv_bfloat16*)out, splits);
+            paged_attention_merge_kernel<128><<<T * Hq, 128, 0, stream>>>(part_acc, part_ml, (__nv_bfloat16*)out, splits, Hq,
+                                                                          tok_row);
         else
-            paged_attention_merge_kernel<64><<<T * Hq, 64, 0, stream>>>(part_acc, part_ml, (__nv_bfloat16*)out, splits);
+            paged_attention_merge_kernel<64><<<T * Hq, 64, 0, stream>>>(part_acc, part_ml, (__nv_bfloat16*)out, splits, Hq,
+                                                                        tok_row);
         DSB_CHECK_LAUNCH("ragged_paged_attention_merge");
     }
     return splits;

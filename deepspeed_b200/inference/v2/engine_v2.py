@@ -92,19 +92,58 @@ class InferenceEngineV2:
         return (os.environ.get("DSB200_RAGGED_NATIVE", "1") == "1" and q.is_cuda
                 and K.ragged_attention_supported(q, hd, nh, nkv))
 
+    # chunks of at least this many tokens go to the tcgen05 prefill kernel (needs head_dim 128 and 128-token blocks);
+    # shorter chunks and decode tokens are HBM-bound and go to the SIMT paged kernel
+    PREFILL_MIN_TOKENS = 128
+
     def _batch_meta(self):
         if self._meta is None:
-            tok_seq, tok_pos, table = self.batch.device_metadata(self.device)
-            max_ctx = max(seen + n for (_, _, n, seen) in self.batch.seq_meta)
-            self._meta = (tok_seq, tok_pos, table, max_ctx)
+            dev = self.device
+            tok_seq, tok_pos, table = self.batch.device_metadata(dev)
+            meta = dict(tok_seq=tok_seq, tok_pos=tok_pos, table=table, prefill=None, rest=None,
+                        max_ctx=max(seen + n for (_, _, n, seen) in self.batch.seq_meta))
+            long_rows = [r for r, (_, _, n, _) in enumerate(self.batch.seq_meta) if n >= self.PREFILL_MIN_TOKENS]
+            if long_rows and self.config.kv_block_size == 128:
+                sm = self.batch.seq_meta
+                ints = torch.tensor([[sm[r][1] for r in long_rows], [sm[r][2] for r in long_rows],
+                                     [sm[r][3] + sm[r][2] for r in long_rows]], dtype=torch.int32).to(dev)
+                meta["prefill"] = dict(cu_q=ints[0].contiguous(), q_len=ints[1].contiguous(), kv_len=ints[2].contiguous(),
+                                       table=table[torch.tensor(long_rows, device=dev)].contiguous(),
+                                       max_q=max(sm[r][2] for r in long_rows))
+                rest = [r for r in range(len(sm)) if r not in set(long_rows)]
+                if rest:
+                    rows, rseq, rpos = [], [], []
+                    for r in rest:
+                        _, start, n, seen = sm[r]
+                        rows += list(range(start, start + n))
+                        rseq += [r] * n
+                        rpos += list(range(seen, seen + n))
+                    t = torch.tensor([rows, rseq, rpos], dtype=torch.int32).to(dev)
+                    meta["rest"] = dict(rows=t[0].contiguous(), seq=t[1].contiguous(), pos=t[2].contiguous(),
+                                        max_ctx=max(sm[r][3] + sm[r][2] for r in rest))
+                else:
+                    meta["rest"] = "none"
+            self._meta = meta
         return self._meta
 
     def _attend_native(self, li, q, k, v, cos=None, sin=None, rotary_dim=0):
         """q [T, Hq, D] (rotated in place when ``rotary_dim``), k / v [T, Hkv, D] -> [T, Hq * D]."""
-        tok_seq, tok_pos, table, max_ctx = self._batch_meta()
+        from ...ops import attention as A
+        m = self._batch_meta()
         kv_layer = self.state_manager.kv.cache[li]
-        K.ragged_kv_append_rope(q, k, v, kv_layer, cos, sin, tok_seq, tok_pos, table, rotary_dim)
-        o = K.ragged_paged_attention(q, kv_layer, tok_seq, tok_pos, table, 1.0 / math.sqrt(q.shape[-1]), max_ctx)
+        scale = 1.0 / math.sqrt(q.shape[-1])
+        K.ragged_kv_append_rope(q, k, v, kv_layer, cos, sin, m["tok_seq"], m["tok_pos"], m["table"], rotary_dim)
+        pf = m["prefill"]
+        if pf is not None and A.paged_prefill_supported(q, kv_layer):
+            o = torch.empty((q.shape[0], q.shape[1], q.shape[2]), dtype=q.dtype, device=q.device)
+            A.flash_attention_paged_prefill(q, kv_layer, pf["cu_q"], pf["q_len"], pf["kv_len"], pf["table"], pf["max_q"],
+                                            scale, out=o)
+            rest = m["rest"]
+            if rest != "none":
+                K.ragged_paged_attention(q, kv_layer, rest["seq"], rest["pos"], m["table"], scale, rest["max_ctx"],
+                                         out=o, tok_row=rest["rows"])
+        else:
+            o = K.ragged_paged_attention(q, kv_layer, m["tok_seq"], m["tok_pos"], m["table"], scale, m["max_ctx"])
         return o.reshape(q.shape[0], -1)
 
     def _attend(self, li, q, k, v):

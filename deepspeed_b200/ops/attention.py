@@ -25,6 +25,8 @@ def _lib():
         P, I, L64, F = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float
         L.dsb200_flash_attn_fwd.argtypes = [P, P, P, P, P, I, I, I, I, I, L64, L64, L64, L64, L64, L64, L64, L64, F, I, P]
         L.dsb200_flash_attn_fwd.restype = I
+        L.dsb200_flash_attn_fwd_paged.argtypes = [P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, L64, L64, F, P]
+        L.dsb200_flash_attn_fwd_paged.restype = I
         _DECLARED = True
     return L
 
@@ -65,6 +67,35 @@ def flash_attention_forward(q, k, v, causal=True, scale=None, out=None, want_lse
         1 if causal else 0, K._stream())
     K._check(rc, "flash_attn_fwd")
     return out, lse
+
+
+def paged_prefill_supported(q, kv_layer):
+    """q [T, H, 128] bf16 (heads packed), kv_layer [num_blocks, 2, 128, Hkv, 128] contiguous bf16."""
+    return (q.is_cuda and K.available() and hasattr(K.lib(), "dsb200_flash_attn_fwd_paged") and q.dtype == torch.bfloat16
+            and q.dim() == 3 and q.shape[-1] == 128 and q.stride(2) == 1 and q.stride(1) == 128 and q.stride(0) % 8 == 0
+            and q.data_ptr() % 16 == 0 and kv_layer.dim() == 5 and kv_layer.shape[2] == 128 and kv_layer.shape[4] == 128
+            and kv_layer.is_contiguous() and q.shape[1] % kv_layer.shape[3] == 0)
+
+
+def flash_attention_paged_prefill(q, kv_layer, cu_q, q_len, kv_len, block_table, max_q_len, scale=None, out=None):
+    """Causal attention of a ragged prefill batch over a blocked KV cache on the tcgen05 kernel.
+
+    ``q`` [T_total, H, 128]: sequences packed back to back, sequence s = rows [cu_q[s], cu_q[s] + q_len[s]); its keys
+    and values (including this chunk's, already appended) are the first kv_len[s] positions of blocks
+    ``block_table[s]`` of ``kv_layer`` [num_blocks, 2, 128, Hkv, 128]. ``cu_q`` / ``q_len`` / ``kv_len`` /
+    ``block_table`` are int32 device tensors. Rows of ``out`` outside the listed sequences are left untouched."""
+    assert paged_prefill_supported(q, kv_layer)
+    T, H, D = q.shape
+    if scale is None:
+        scale = 1.0 / math.sqrt(D)
+    if out is None:
+        out = torch.empty((T, H, D), dtype=torch.bfloat16, device=q.device)
+    rc = _lib().dsb200_flash_attn_fwd_paged(
+        K._ptr(q), K._ptr(kv_layer), K._ptr(out), None, K._ptr(cu_q), K._ptr(q_len), K._ptr(kv_len), K._ptr(block_table),
+        cu_q.numel(), T, int(max_q_len), H, kv_layer.shape[3], kv_layer.shape[0], block_table.shape[1], q.stride(0),
+        out.stride(0), float(scale), K._stream())
+    K._check(rc, "flash_attn_fwd_paged")
+    return out
 
 
 def _reference_backward(q, k, v, do, causal, scale):

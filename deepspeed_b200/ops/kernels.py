@@ -123,7 +123,7 @@ def _declare(L):
     sig("dsb200_ce_fwd_ex", P, P, P, P, I, I, L64, I, I, F, P, I, P)
     sig("dsb200_scale_by_dev", P, L64, I, P, P)
     sig("dsb200_ragged_kv_append_rope", P, P, P, P, P, P, P, P, P, I, L64, L64, L64, I, I, I, I, I, I, I, P)
-    sig("dsb200_ragged_paged_attention", P, P, P, P, P, P, P, P, I, L64, I, I, I, I, I, I, F, P)
+    sig("dsb200_ragged_paged_attention", P, P, P, P, P, P, P, P, P, I, L64, I, I, I, I, I, I, F, P)
     sig("dsb200_move_rows", P, P, P, I, L64, L64, L64, L64, L64, I, P)
     sig("dsb200_scatter_add_rows", P, P, P, I, P, L64, I, L64, L64, L64, I, I, P)
     sig("dsb200_sort_rows_i32", P, L64, I, P)
@@ -438,14 +438,16 @@ def ragged_kv_append_rope(q, k, v, kv_layer, cos, sin, tok_seq, tok_pos, block_t
 _PA_SCRATCH = {}
 
 
-def ragged_paged_attention(q, kv_layer, tok_seq, tok_pos, block_table, scale, max_context, out=None):
-    """Every token of the ragged batch attends to keys [0, pos] of its sequence in the blocked cache.
-    q [T, Hq, D] (bf16, D in {64, 128}) -> out [T, Hq, D]. The key range is split over several CTAs (flash-decoding)
-    when the batch alone cannot fill the GPU."""
-    T, Hq, D = q.shape
+def ragged_paged_attention(q, kv_layer, tok_seq, tok_pos, block_table, scale, max_context, out=None, tok_row=None):
+    """Every listed token attends to keys [0, pos] of its sequence in the blocked cache.
+    q [T, Hq, D] (bf16, D in {64, 128}) -> out [T, Hq, D]. ``tok_row`` (int32) restricts the launch to a subset of the
+    rows of q / out (``tok_seq`` / ``tok_pos`` then describe that subset). The key range is split over several CTAs
+    (flash-decoding) when the batch alone cannot fill the GPU."""
+    Hq, D = q.shape[1], q.shape[2]
+    T = q.shape[0] if tok_row is None else tok_row.numel()
     Hkv = kv_layer.shape[3]
     if out is None:
-        out = torch.empty((T, Hq, D), dtype=q.dtype, device=q.device)
+        out = torch.empty((q.shape[0], Hq, D), dtype=q.dtype, device=q.device)
     tiles = max(1, (int(max_context) + 31) // 32)
     splits = 1
     if T * Hkv < 2 * 148:
@@ -459,7 +461,8 @@ def ragged_paged_attention(q, kv_layer, tok_seq, tok_pos, block_table, scale, ma
             buf = _PA_SCRATCH[key] = torch.empty(T * Hq * splits * (D + 2), dtype=torch.float32, device=q.device)
         pa, pm = buf[:T * Hq * splits * D], buf[T * Hq * splits * D:]
     rc = lib().dsb200_ragged_paged_attention(_ptr(q), _ptr(kv_layer), _ptr(out), _ptr(tok_seq), _ptr(tok_pos),
-                                             _ptr(block_table), _ptr(pa), _ptr(pm), T, q.stride(0), Hq, Hkv, D,
+                                             _ptr(block_table), _ptr(tok_row), _ptr(pa), _ptr(pm), T, q.stride(0), Hq,
+                                             Hkv, D,
                                              kv_layer.shape[2], block_table.shape[1], splits, float(scale), _stream())
     if rc < 0:
         raise RuntimeError(f"ragged_paged_attention failed: {last_error()}")

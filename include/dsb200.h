@@ -224,6 +224,29 @@ int64_t dsb200_aio_wait(void* h);
 void* dsb200_aligned_alloc(int64_t nbytes, int64_t alignment);
 void dsb200_aligned_free(void* p);
 
+/* ---- flash attention on tcgen05 (csrc/attention_fwd.cu): bf16, head_dim 128, layout [batch, seq, heads, 128] with
+ * element strides; lse [B, H, Sq] fp32 or null. Reference call sites: sequence/fpdt_layer.py:238-269 (flash-attn with
+ * LSE), runtime/sequence_parallel/ulysses_sp.py:50. ---- */
+int dsb200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int Sq, int Skv,
+                          int H, int Hkv, int64_t q_row_stride, int64_t q_batch_stride, int64_t k_row_stride,
+                          int64_t k_batch_stride, int64_t v_row_stride, int64_t v_batch_stride, int64_t o_row_stride,
+                          int64_t o_batch_stride, float scale, int causal, cudaStream_t stream);
+/* ragged prefill over a blocked KV cache [num_blocks, 2, 128, Hkv, 128] (reference: ragged_ops/blocked_flash) */
+int dsb200_flash_attn_fwd_paged(const void* q, const void* kv, void* o, float* lse, const int* cu_q, const int* q_len,
+                                const int* kv_len, const int* block_table, int n_seqs, int T_total, int max_q_len,
+                                int H, int Hkv, int num_blocks, int max_blocks, int64_t q_row_stride,
+                                int64_t o_row_stride, float scale, cudaStream_t stream);
+/* ---- FastGen ragged ops (csrc/ragged_ops.cu); reference: inference/v2/kernels/ragged_ops/{linear_blocked_kv_rotary,
+ * blocked_flash,atom_builder} ---- */
+int dsb200_ragged_kv_append_rope(void* q, const void* k, const void* v, void* kv, const float* cos_tab,
+                                 const float* sin_tab, const int* tok_seq, const int* tok_pos, const int* block_table,
+                                 int T, int64_t q_stride, int64_t k_stride, int64_t v_stride, int Hq, int Hkv, int D,
+                                 int rotary_dim, int block_size, int max_blocks, int dt, cudaStream_t stream);
+int dsb200_ragged_paged_attention(const void* q, const void* kv, void* out, const int* tok_seq, const int* tok_pos,
+                                  const int* block_table, const int* tok_row, float* part_acc, float* part_ml, int T,
+                                  int64_t q_stride, int Hq, int Hkv, int D, int block_size, int max_blocks, int splits,
+                                  float scale, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -142,3 +142,65 @@ def test_ragged_engine_native_matches_fallback():
     # bf16 ties may flip a late token; the prompts and the first generated tokens must agree
     assert torch.equal(a[:, :74], b[:, :74]), (a[:, 70:], b[:, 70:])
     assert (a == b).float().mean().item() > 0.95
+
+
+def test_paged_prefill_tcgen05_matches_simt_kernel():
+    """Ragged prefill (two long chunks, one of them continuing a cached prefix) on the tcgen05 kernel with the block
+    table vs the SIMT paged kernel; decode tokens of the same batch are served by the SIMT kernel through tok_row."""
+    from deepspeed_b200.ops import attention as A, kernels as K
+    torch.manual_seed(3)
+    dev = torch.device("cuda")
+    D, Hq, Hkv, bs = 128, 8, 2, 128
+    spec = [(0, 300), (200, 1), (384, 257), (0, 130), (77, 3)]  # (cached, new)
+    tok_seq, tok_pos, table, blocks, n_blocks = _make_batch(spec, bs, dev)
+    T = tok_seq.numel()
+    cache = torch.randn(n_blocks, 2, bs, Hkv, D, device=dev, dtype=torch.bfloat16)  # history + this chunk's keys
+    q = torch.randn(T, Hq, D, device=dev, dtype=torch.bfloat16)
+    scale = 1.0 / math.sqrt(D)
+    want = K.ragged_paged_attention(q, cache, tok_seq, tok_pos, table, scale, max(s + n for s, n in spec))
+    assert A.paged_prefill_supported(q, cache)
+    starts, it = [], 0
+    for _, n in spec:
+        starts.append(it)
+        it += n
+    long_rows = [r for r, (_, n) in enumerate(spec) if n >= 128]
+    cu_q = torch.tensor([starts[r] for r in long_rows], dtype=torch.int32, device=dev)
+    q_len = torch.tensor([spec[r][1] for r in long_rows], dtype=torch.int32, device=dev)
+    kv_len = torch.tensor([sum(spec[r]) for r in long_rows], dtype=torch.int32, device=dev)
+    out = torch.zeros(T, Hq, D, device=dev, dtype=torch.bfloat16)
+    A.flash_attention_paged_prefill(q, cache, cu_q, q_len, kv_len, table[torch.tensor(long_rows, device=dev)].contiguous(),
+                                    max(spec[r][1] for r in long_rows), scale, out=out)
+    rest = [r for r in range(len(spec)) if r not in long_rows]
+    rows = torch.tensor([starts[r] + i for r in rest for i in range(spec[r][1])], dtype=torch.int32, device=dev)
+    rseq = torch.tensor([r for r in rest for _ in range(spec[r][1])], dtype=torch.int32, device=dev)
+    rpos = torch.tensor([spec[r][0] + i for r in rest for i in range(spec[r][1])], dtype=torch.int32, device=dev)
+    K.ragged_paged_attention(q, cache, rseq, rpos, table, scale, max(sum(spec[r]) for r in rest), out=out, tok_row=rows)
+    torch.cuda.synchronize()
+    assert (out.float() - want.float()).abs().max().item() < 2e-2
+
+
+def test_ragged_engine_long_prompt_uses_tcgen05_prefill():
+    from deepspeed_b200.inference.v2.engine_v2 import InferenceEngineV2, RaggedInferenceEngineConfig
+    from deepspeed_b200.models import LlamaConfig, LlamaForCausalLM
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    cfg = LlamaConfig(vocab_size=512, hidden_size=512, intermediate_size=1024, num_hidden_layers=2,
+                      num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=1024)
+    model = LlamaForCausalLM(cfg, device=dev).eval()
+    with torch.no_grad():
+        for p in model.parameters():
+            if p.dim() >= 2:
+                p.normal_(0.0, 0.05)
+    prompts = [torch.randint(0, 512, (400, )), torch.randint(0, 512, (5, )), torch.randint(0, 512, (150, ))]
+    logits = {}
+    for bs in (128, 64):  # 128-token blocks: tcgen05 prefill for the long chunks; 64: SIMT kernel for everything
+        eng = InferenceEngineV2(model, RaggedInferenceEngineConfig(kv_block_size=bs, num_kv_blocks=64,
+                                                                   max_ragged_batch_size=1024))
+        a = eng.put([0, 1, 2], prompts)
+        b = eng.put([0, 1, 2], [torch.tensor([7]), torch.tensor([8]), torch.tensor([9])])  # decode on top of it
+        if bs == 128:
+            assert eng._meta is not None
+        logits[bs] = (a.float(), b.float())
+    for x, y in zip(logits[128], logits[64]):
+        assert (x - y).abs().max().item() < 0.15 * max(1.0, y.abs().max().item()), (x - y).abs().max()
+        assert (x.argmax(-1) == y.argmax(-1)).all()
