@@ -150,6 +150,13 @@ struct FaParams {
     const int* block_table;  // [B, max_blocks]
     int max_blocks;
     int lse_stride;          // elements between heads in lse (Sq dense, T_total ragged)
+    // decode mode (one query token per "sequence", FastGen decode): the G = Hq / Hkv query heads that share a KV head
+    // are the ROWS of the query tile (a [G, 128] box, zero-filled to 128 rows by TMA), the kernel's head index is the
+    // KV head, and the key range is split over `pairs` CTAs whose normalised partial outputs + LSE are merged afterwards.
+    int decode;              // 0 / 1
+    int G;                   // query heads per KV head
+    float* part_o;           // [T * Hq, splits, 128] fp32 (splits > 1)
+    float* part_lse;         // [T * Hq, splits]
 };
 
 template <unsigned EMU_MASK>
@@ -171,19 +178,25 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     const int rem = (int)(blockIdx.x % bh);
     const int b = rem / prm.H, h = rem % prm.H;
     const int hk = h / (prm.H / prm.Hkv);
-    const int q0 = pair * 2 * FA_BM;  // first query row of tile 0 (relative to the sequence)
-    const bool ragged = prm.cu_q != nullptr;
-    const int Sq = ragged ? prm.q_len[b] : prm.Sq;
+    const bool decode = prm.decode != 0;
+    const int q0 = decode ? 0 : pair * 2 * FA_BM;  // first query row of tile 0 (relative to the sequence)
+    const bool ragged = prm.cu_q != nullptr || decode;
+    const int Sq = decode ? prm.G : (ragged ? prm.q_len[b] : prm.Sq);
     const int Skv = ragged ? prm.kv_len[b] : prm.Skv;
-    const int row_base = ragged ? prm.cu_q[b] : 0;  // packed row of the sequence's first query
+    const int row_base = decode ? 0 : (ragged ? prm.cu_q[b] : 0);  // packed row of the sequence's first query
     if (q0 >= Sq) return;                           // ragged batches are launched for the longest sequence
     // number of key blocks per tile
     const int nb_all = (Skv + FA_BN - 1) / FA_BN;
+    // decode: this CTA's share of the key blocks (split index = pair)
+    const int split_per = decode ? (nb_all + prm.pairs - 1) / prm.pairs : 0;
+    const int jbase = decode ? min(nb_all, pair * split_per) : 0;
     int nb_t[2];
 #pragma unroll
     for (int t = 0; t < 2; t++) {
         const int row0 = q0 + t * FA_BM;
-        if (row0 >= Sq) {
+        if (decode) {
+            nb_t[t] = t == 0 ? min(nb_all, jbase + split_per) - jbase : 0;
+        } else if (row0 >= Sq) {
             nb_t[t] = 0;
         } else if (prm.causal) {
             const int last_row = min(row0 + FA_BM, Sq) - 1 + (Skv - Sq);  // bottom-right aligned
@@ -233,13 +246,17 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
             for (int t = 0; t < 2; t++)
 #pragma unroll
                 for (int hf = 0; hf < 2; hf++)
-                    tma_load_3d(q_smem + t * FA_TILE_BYTES + hf * FA_HALF_BYTES, &map_q, &bars->q_full,
-                                h * FA_D + hf * 64, row_base + q0 + t * FA_BM, ragged ? 0 : b);
+                    if (decode)  // q viewed as [T * Hkv, G, 128]: rows >= G of the box are zero-filled
+                        tma_load_3d(q_smem + t * FA_TILE_BYTES + hf * FA_HALF_BYTES, &map_q, &bars->q_full, hf * 64,
+                                    t * FA_BM, b * prm.H + h);
+                    else
+                        tma_load_3d(q_smem + t * FA_TILE_BYTES + hf * FA_HALF_BYTES, &map_q, &bars->q_full,
+                                    h * FA_D + hf * 64, row_base + q0 + t * FA_BM, ragged ? 0 : b);
             int stage = 0;
             uint32_t phase = 0;
             for (int j = 0; j < nb; j++) {
                 // dense: rows [j*128, +128) of batch b; paged: plane (block*2 + {K,V}) of the cache, rows [0, 128)
-                const int blk = ragged ? prm.block_table[(int64_t)b * prm.max_blocks + j] : 0;
+                const int blk = ragged ? prm.block_table[(int64_t)b * prm.max_blocks + jbase + j] : 0;
                 const int krow = ragged ? 0 : j * FA_BN, kz = ragged ? blk * 2 : b, vz = ragged ? blk * 2 + 1 : b;
                 mbar_wait(&bars->k_empty[stage], phase ^ 1);
                 mbar_expect_tx(&bars->k_full[stage], FA_TILE_BYTES);
@@ -336,7 +353,7 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
         for (int j = 0; j < my_nb; j++) {
             mbar_wait(&bars->s_full[t], (uint32_t)(j & 1));
             tc_fence_after();
-            const int col0 = j * FA_BN;
+            const int col0 = (jbase + j) * FA_BN;
             // does this block need masking (diagonal block of the causal mask, or the tail of the key sequence)?
             const bool need_mask = (prm.causal && (col0 + FA_BN - 1 > q0 + t * FA_BM + causal_off)) || (col0 + FA_BN > Skv);
             const int col_limit = prm.causal ? min(Skv, row + causal_off + 1) : Skv;  // valid keys: col < col_limit
@@ -426,14 +443,25 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
             tc_fence_after();
             const float inv_l = (l_run > 0.f) ? 1.f / l_run : 0.f;
             const bool valid = row < Sq;
-            __nv_bfloat16* orow = prm.o + (ragged ? 0 : (int64_t)b * prm.o_batch_stride) +
-                                  (int64_t)(row_base + row) * prm.o_row_stride + h * FA_D;
+            // decode: row = query head inside the KV-head group; o is [T, Hq, 128] and the kernel's H is Hkv
+            const int64_t head_row = decode ? ((int64_t)b * prm.H + h) * prm.G + row : 0;
+            __nv_bfloat16* orow = decode ? prm.o + head_row * FA_D
+                                         : prm.o + (ragged ? 0 : (int64_t)b * prm.o_batch_stride) +
+                                               (int64_t)(row_base + row) * prm.o_row_stride + h * FA_D;
+            const bool partial = decode && prm.pairs > 1;
+            float* prow = partial ? prm.part_o + (head_row * prm.pairs + pair) * FA_D : nullptr;
 #pragma unroll 1
             for (int c = 0; c < 4; c++) {
                 uint32_t r[32];
                 tmem_ld_32x32(o_addr + c * 32, r);
                 tmem_wait_ld();
-                if (valid) {
+                if (valid && partial) {
+#pragma unroll
+                    for (int v4 = 0; v4 < 8; v4++)
+                        *reinterpret_cast<float4*>(prow + c * 32 + v4 * 4) =
+                            make_float4(__uint_as_float(r[v4 * 4]) * inv_l, __uint_as_float(r[v4 * 4 + 1]) * inv_l,
+                                        __uint_as_float(r[v4 * 4 + 2]) * inv_l, __uint_as_float(r[v4 * 4 + 3]) * inv_l);
+                } else if (valid) {
 #pragma unroll
                     for (int v4 = 0; v4 < 4; v4++) {
                         uint4 pk;
@@ -446,10 +474,16 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
                     }
                 }
             }
-            if (valid && prm.lse != nullptr) {
+            if (valid && partial) {
+                prm.part_lse[head_row * prm.pairs + pair] = (l_run > 0.f) ? (m_run + log2f(l_run)) : -INFINITY;  // log2
+            } else if (valid && prm.lse != nullptr && !decode) {
                 const float lse = (l_run > 0.f) ? (m_run + log2f(l_run)) * 0.6931471805599453f : -INFINITY;
                 prm.lse[((int64_t)(ragged ? 0 : b) * prm.H + h) * prm.lse_stride + row_base + row] = lse;
             }
+        } else if (decode) {
+            // a split beyond the end of this sequence's keys: an empty partial (weight 0 in the merge)
+            if (t == 0 && row < Sq && prm.pairs > 1)
+                prm.part_lse[(((int64_t)b * prm.H + h) * prm.G + row) * prm.pairs + pair] = -INFINITY;
         } else if (row < Sq && q0 + t * FA_BM < Sq) {
             // no visible key at all (causal with Skv < Sq): zeros
             __nv_bfloat16* orow = prm.o + (ragged ? 0 : (int64_t)b * prm.o_batch_stride) +
@@ -465,6 +499,26 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
     }
+}
+
+// decode split-KV merge: out[row] = sum_s w_s * part_o[row, s] with w_s = 2^(lse_s - max) / sum 2^(lse - max)
+__global__ void __launch_bounds__(128) flash_decode_merge_kernel(const float* __restrict__ part_o,
+                                                                 const float* __restrict__ part_lse,
+                                                                 __nv_bfloat16* __restrict__ out, int splits)
+{
+    const int64_t row = blockIdx.x;
+    const int d = threadIdx.x;
+    float mx = -INFINITY;
+    for (int s = 0; s < splits; s++) mx = fmaxf(mx, part_lse[row * splits + s]);
+    float den = 0.f, acc = 0.f;
+    for (int s = 0; s < splits; s++) {
+        const float l = part_lse[row * splits + s];
+        if (l == -INFINITY) continue;
+        const float w = exp2f(l - mx);
+        den += w;
+        acc += w * part_o[(row * splits + s) * FA_D + d];
+    }
+    out[row * FA_D + d] = __float2bfloat16_rn(den > 0.f ? acc / den : 0.f);
 }
 
 // 3-D bf16 tensor [batch, seq, cols] (cols contiguous), box = [1, box_rows, 64], 128-byte swizzle, OOB -> zeros
@@ -599,6 +653,51 @@ int dsb200_flash_attn_fwd_paged(const void* q, const void* kv, void* o, float* l
     prm.max_blocks = max_blocks;
     prm.lse_stride = T_total;
     return launch_flash_fwd(mq, mk, mk, prm, stream);
+}
+
+
+// Decode over a blocked KV cache on the tcgen05 kernel: T tokens (one per sequence), q [T, Hq, 128] contiguous,
+// kv one cache layer [num_blocks, 2, 128, Hkv, 128], kv_len[T] keys visible to each token, block_table [T, max_blocks].
+// splits > 1 needs part_o (T*Hq*splits*128 floats) and part_lse (T*Hq*splits floats). o [T, Hq, 128] bf16.
+// Reference: inference/v2/kernels/ragged_ops/blocked_flash (decode path).
+int dsb200_flash_decode_paged(const void* q, const void* kv, void* o, const int* kv_len, const int* block_table,
+                              float* part_o, float* part_lse, int T, int Hq, int Hkv, int num_blocks, int max_blocks,
+                              int splits, float scale, cudaStream_t stream)
+{
+    if (T <= 0) return 0;
+    const int G = Hkv > 0 ? Hq / Hkv : 0;
+    if (Hkv <= 0 || Hq % Hkv != 0 || G > FA_BM) {
+        dsb200_set_error("flash_decode_paged: Hq must be a multiple of Hkv (at most 128 query heads per KV head)");
+        return -1;
+    }
+    if (splits < 1) splits = 1;
+    if (splits > 1 && (part_o == nullptr || part_lse == nullptr)) {
+        dsb200_set_error("flash_decode_paged: split-KV needs the partial-result buffers");
+        return -1;
+    }
+    CUtensorMap mq, mk;
+    // q as [T * Hkv, G, 128]: one [G, 128] box per (token, KV head); rows G..127 of the 128-row box are OOB -> zeros
+    if (make_map_3d(&mq, q, (int64_t)T * Hkv, G, FA_D, FA_D, (int64_t)G * FA_D, FA_BM) != 0) return -2;
+    const int64_t plane = (int64_t)FA_BN * Hkv * FA_D;
+    if (make_map_3d(&mk, kv, (int64_t)num_blocks * 2, FA_BN, (int64_t)Hkv * FA_D, (int64_t)Hkv * FA_D, plane, FA_BN) != 0)
+        return -2;
+    FaParams prm = {};
+    prm.o = (__nv_bfloat16*)o;
+    prm.B = T, prm.Sq = G, prm.Skv = 0, prm.H = Hkv, prm.Hkv = Hkv;
+    prm.o_row_stride = FA_D, prm.o_batch_stride = 0;
+    prm.scale_log2 = scale * 1.4426950408889634f;
+    prm.causal = 0;
+    prm.pairs = splits;
+    prm.kv_len = kv_len, prm.block_table = block_table, prm.max_blocks = max_blocks;
+    prm.decode = 1, prm.G = G;
+    prm.part_o = part_o, prm.part_lse = part_lse;
+    int rc = launch_flash_fwd(mq, mk, mk, prm, stream);
+    if (rc != 0) return rc;
+    if (splits > 1) {
+        flash_decode_merge_kernel<<<T * Hq, 128, 0, stream>>>(part_o, part_lse, (__nv_bfloat16*)o, splits);
+        DSB_CHECK_LAUNCH("flash_decode_merge");
+    }
+    return 0;
 }
 
 }  // extern "C"

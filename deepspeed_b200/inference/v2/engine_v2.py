@@ -92,26 +92,36 @@ class InferenceEngineV2:
         return (os.environ.get("DSB200_RAGGED_NATIVE", "1") == "1" and q.is_cuda
                 and K.ragged_attention_supported(q, hd, nh, nkv))
 
-    # chunks of at least this many tokens go to the tcgen05 prefill kernel (needs head_dim 128 and 128-token blocks);
-    # shorter chunks and decode tokens are HBM-bound and go to the SIMT paged kernel
+    # With head_dim 128 and 128-token KV blocks the attention of a ragged batch runs on the tcgen05 kernel: single-token
+    # (decode) sequences through its split-KV decode mode, chunks of at least PREFILL_MIN_TOKENS tokens through its
+    # paged prefill mode; what is left (short chunks, other head dims / block sizes) goes to the SIMT paged kernel.
     PREFILL_MIN_TOKENS = 128
 
     def _batch_meta(self):
         if self._meta is None:
             dev = self.device
+            sm = self.batch.seq_meta
             tok_seq, tok_pos, table = self.batch.device_metadata(dev)
-            meta = dict(tok_seq=tok_seq, tok_pos=tok_pos, table=table, prefill=None, rest=None,
-                        max_ctx=max(seen + n for (_, _, n, seen) in self.batch.seq_meta))
-            long_rows = [r for r, (_, _, n, _) in enumerate(self.batch.seq_meta) if n >= self.PREFILL_MIN_TOKENS]
-            if long_rows and self.config.kv_block_size == 128:
-                sm = self.batch.seq_meta
-                ints = torch.tensor([[sm[r][1] for r in long_rows], [sm[r][2] for r in long_rows],
-                                     [sm[r][3] + sm[r][2] for r in long_rows]], dtype=torch.int32).to(dev)
-                meta["prefill"] = dict(cu_q=ints[0].contiguous(), q_len=ints[1].contiguous(), kv_len=ints[2].contiguous(),
-                                       table=table[torch.tensor(long_rows, device=dev)].contiguous(),
-                                       max_q=max(sm[r][2] for r in long_rows))
-                rest = [r for r in range(len(sm)) if r not in set(long_rows)]
-                if rest:
+            meta = dict(tok_seq=tok_seq, tok_pos=tok_pos, table=table, prefill=None, decode=None, rest=None,
+                        max_ctx=max(seen + n for (_, _, n, seen) in sm))
+            if self.config.kv_block_size == 128:
+                long_rows = [r for r, (_, _, n, _) in enumerate(sm) if n >= self.PREFILL_MIN_TOKENS]
+                dec_rows = [r for r, (_, _, n, _) in enumerate(sm) if n == 1]
+                rest = [r for r, (_, _, n, _) in enumerate(sm) if 1 < n < self.PREFILL_MIN_TOKENS]
+                if long_rows:
+                    ints = torch.tensor([[sm[r][1] for r in long_rows], [sm[r][2] for r in long_rows],
+                                         [sm[r][3] + sm[r][2] for r in long_rows]], dtype=torch.int32).to(dev)
+                    meta["prefill"] = dict(cu_q=ints[0].contiguous(), q_len=ints[1].contiguous(),
+                                           kv_len=ints[2].contiguous(),
+                                           table=table[torch.tensor(long_rows, device=dev)].contiguous(),
+                                           max_q=max(sm[r][2] for r in long_rows))
+                if dec_rows:
+                    ints = torch.tensor([[sm[r][1] for r in dec_rows], [sm[r][3] + 1 for r in dec_rows]],
+                                        dtype=torch.int32).to(dev)
+                    meta["decode"] = dict(rows=ints[0].long(), kv_len=ints[1].contiguous(),
+                                          table=table[torch.tensor(dec_rows, device=dev)].contiguous(),
+                                          max_ctx=max(sm[r][3] + 1 for r in dec_rows), all=len(dec_rows) == len(sm))
+                if rest and (long_rows or dec_rows):
                     rows, rseq, rpos = [], [], []
                     for r in rest:
                         _, start, n, seen = sm[r]
@@ -121,8 +131,6 @@ class InferenceEngineV2:
                     t = torch.tensor([rows, rseq, rpos], dtype=torch.int32).to(dev)
                     meta["rest"] = dict(rows=t[0].contiguous(), seq=t[1].contiguous(), pos=t[2].contiguous(),
                                         max_ctx=max(sm[r][3] + sm[r][2] for r in rest))
-                else:
-                    meta["rest"] = "none"
             self._meta = meta
         return self._meta
 
@@ -133,17 +141,23 @@ class InferenceEngineV2:
         kv_layer = self.state_manager.kv.cache[li]
         scale = 1.0 / math.sqrt(q.shape[-1])
         K.ragged_kv_append_rope(q, k, v, kv_layer, cos, sin, m["tok_seq"], m["tok_pos"], m["table"], rotary_dim)
-        pf = m["prefill"]
-        if pf is not None and A.paged_prefill_supported(q, kv_layer):
-            o = torch.empty((q.shape[0], q.shape[1], q.shape[2]), dtype=q.dtype, device=q.device)
+        pf, dc, rest = m["prefill"], m["decode"], m["rest"]
+        if (pf is None and dc is None) or not A.paged_prefill_supported(q, kv_layer):
+            o = K.ragged_paged_attention(q, kv_layer, m["tok_seq"], m["tok_pos"], m["table"], scale, m["max_ctx"])
+            return o.reshape(q.shape[0], -1)
+        o = torch.empty((q.shape[0], q.shape[1], q.shape[2]), dtype=q.dtype, device=q.device)
+        if pf is not None:
             A.flash_attention_paged_prefill(q, kv_layer, pf["cu_q"], pf["q_len"], pf["kv_len"], pf["table"], pf["max_q"],
                                             scale, out=o)
-            rest = m["rest"]
-            if rest != "none":
-                K.ragged_paged_attention(q, kv_layer, rest["seq"], rest["pos"], m["table"], scale, rest["max_ctx"],
-                                         out=o, tok_row=rest["rows"])
-        else:
-            o = K.ragged_paged_attention(q, kv_layer, m["tok_seq"], m["tok_pos"], m["table"], scale, m["max_ctx"])
+        if dc is not None:
+            qd = q.contiguous() if dc["all"] else q.index_select(0, dc["rows"])
+            od = A.flash_decode_paged(qd, kv_layer, dc["kv_len"], dc["table"], dc["max_ctx"], scale,
+                                      out=o if dc["all"] else None)
+            if not dc["all"]:
+                o.index_copy_(0, dc["rows"], od)
+        if rest is not None:
+            K.ragged_paged_attention(q, kv_layer, rest["seq"], rest["pos"], m["table"], scale, rest["max_ctx"], out=o,
+                                     tok_row=rest["rows"])
         return o.reshape(q.shape[0], -1)
 
     def _attend(self, li, q, k, v):

@@ -27,6 +27,8 @@ def _lib():
         L.dsb200_flash_attn_fwd.restype = I
         L.dsb200_flash_attn_fwd_paged.argtypes = [P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, L64, L64, F, P]
         L.dsb200_flash_attn_fwd_paged.restype = I
+        L.dsb200_flash_decode_paged.argtypes = [P, P, P, P, P, P, P, I, I, I, I, I, I, F, P]
+        L.dsb200_flash_decode_paged.restype = I
         _DECLARED = True
     return L
 
@@ -95,6 +97,40 @@ def flash_attention_paged_prefill(q, kv_layer, cu_q, q_len, kv_len, block_table,
         cu_q.numel(), T, int(max_q_len), H, kv_layer.shape[3], kv_layer.shape[0], block_table.shape[1], q.stride(0),
         out.stride(0), float(scale), K._stream())
     K._check(rc, "flash_attn_fwd_paged")
+    return out
+
+
+_DECODE_SCRATCH = {}
+
+
+def flash_decode_paged(q, kv_layer, kv_len, block_table, max_context, scale=None, out=None, splits=None):
+    """Decode attention (one query token per sequence) over a blocked KV cache on the tcgen05 kernel: the query heads
+    that share a KV head form the rows of the MMA tile, K / V blocks arrive by TMA through the block table and the key
+    range is split over CTAs (flash-decoding) so that small batches still cover all SMs.
+
+    ``q`` [T, Hq, 128] contiguous bf16; ``kv_layer`` [num_blocks, 2, 128, Hkv, 128]; ``kv_len`` [T] int32 (keys visible
+    to each token, its own included); ``block_table`` [T, max_blocks] int32. Returns ``out`` [T, Hq, 128]."""
+    assert paged_prefill_supported(q, kv_layer) and q.is_contiguous()
+    T, Hq, D = q.shape
+    Hkv = kv_layer.shape[3]
+    if scale is None:
+        scale = 1.0 / math.sqrt(D)
+    if out is None:
+        out = torch.empty((T, Hq, D), dtype=torch.bfloat16, device=q.device)
+    n_blocks_max = max(1, (int(max_context) + 127) // 128)
+    if splits is None:
+        splits = max(1, min(n_blocks_max, -(-2 * 148 // max(1, T * Hkv)), 64))
+    po = pl = None
+    if splits > 1:
+        need = T * Hq * splits * (D + 1)
+        buf = _DECODE_SCRATCH.get(q.device)
+        if buf is None or buf.numel() < need:
+            buf = _DECODE_SCRATCH[q.device] = torch.empty(need, dtype=torch.float32, device=q.device)
+        po, pl = buf[:T * Hq * splits * D], buf[T * Hq * splits * D:need]
+    rc = _lib().dsb200_flash_decode_paged(K._ptr(q), K._ptr(kv_layer), K._ptr(out), K._ptr(kv_len), K._ptr(block_table),
+                                          K._ptr(po), K._ptr(pl), T, Hq, Hkv, kv_layer.shape[0], block_table.shape[1],
+                                          int(splits), float(scale), K._stream())
+    K._check(rc, "flash_decode_paged")
     return out
 
 

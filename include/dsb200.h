@@ -236,6 +236,11 @@ int dsb200_flash_attn_fwd_paged(const void* q, const void* kv, void* o, float* l
                                 const int* kv_len, const int* block_table, int n_seqs, int T_total, int max_q_len,
                                 int H, int Hkv, int num_blocks, int max_blocks, int64_t q_row_stride,
                                 int64_t o_row_stride, float scale, cudaStream_t stream);
+/* decode (one token per sequence) over the blocked cache on the same kernel: query heads of a KV head are the tile rows,
+ * split-KV partials merged by a second kernel (reference: ragged_ops/blocked_flash decode path) */
+int dsb200_flash_decode_paged(const void* q, const void* kv, void* o, const int* kv_len, const int* block_table,
+                              float* part_o, float* part_lse, int T, int Hq, int Hkv, int num_blocks, int max_blocks,
+                              int splits, float scale, cudaStream_t stream);
 /* ---- FastGen ragged ops (csrc/ragged_ops.cu); reference: inference/v2/kernels/ragged_ops/{linear_blocked_kv_rotary,
  * blocked_flash,atom_builder} ---- */
 int dsb200_ragged_kv_append_rope(void* q, const void* k, const void* v, void* kv, const float* cos_tab,

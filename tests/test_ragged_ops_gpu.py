@@ -191,16 +191,41 @@ def test_ragged_engine_long_prompt_uses_tcgen05_prefill():
         for p in model.parameters():
             if p.dim() >= 2:
                 p.normal_(0.0, 0.05)
-    prompts = [torch.randint(0, 512, (400, )), torch.randint(0, 512, (5, )), torch.randint(0, 512, (150, ))]
+    # a long prompt (tcgen05 prefill), a short chunk (SIMT), another long one, and a single token (tcgen05 decode)
+    prompts = [torch.randint(0, 512, (400, )), torch.randint(0, 512, (5, )), torch.randint(0, 512, (150, )),
+               torch.randint(0, 512, (1, ))]
     logits = {}
     for bs in (128, 64):  # 128-token blocks: tcgen05 prefill for the long chunks; 64: SIMT kernel for everything
         eng = InferenceEngineV2(model, RaggedInferenceEngineConfig(kv_block_size=bs, num_kv_blocks=64,
                                                                    max_ragged_batch_size=1024))
-        a = eng.put([0, 1, 2], prompts)
-        b = eng.put([0, 1, 2], [torch.tensor([7]), torch.tensor([8]), torch.tensor([9])])  # decode on top of it
+        a = eng.put([0, 1, 2, 3], prompts)
+        # all-decode batch on top of it
+        b = eng.put([0, 1, 2, 3], [torch.tensor([7]), torch.tensor([8]), torch.tensor([9]), torch.tensor([3])])
         if bs == 128:
             assert eng._meta is not None
         logits[bs] = (a.float(), b.float())
     for x, y in zip(logits[128], logits[64]):
         assert (x - y).abs().max().item() < 0.15 * max(1.0, y.abs().max().item()), (x - y).abs().max()
         assert (x.argmax(-1) == y.argmax(-1)).all()
+
+
+@pytest.mark.parametrize("Hq,Hkv,n_seq,ctx", [(32, 8, 5, 1000), (8, 8, 3, 260), (16, 2, 2, 4097), (32, 8, 70, 129)])
+def test_flash_decode_paged_tcgen05_matches_simt(Hq, Hkv, n_seq, ctx):
+    """Decode attention on the tcgen05 kernel (heads as tile rows, split-KV + merge) vs the SIMT paged kernel."""
+    from deepspeed_b200.ops import attention as A, kernels as K
+    torch.manual_seed(4)
+    dev = torch.device("cuda")
+    D, bs = 128, 128
+    lens = [max(1, ctx - 37 * i) for i in range(n_seq)]
+    spec = [(n - 1, 1) for n in lens]
+    tok_seq, tok_pos, table, blocks, n_blocks = _make_batch(spec, bs, dev)
+    cache = torch.randn(n_blocks, 2, bs, Hkv, D, device=dev, dtype=torch.bfloat16)
+    q = torch.randn(n_seq, Hq, D, device=dev, dtype=torch.bfloat16)
+    scale = 1.0 / math.sqrt(D)
+    want = K.ragged_paged_attention(q, cache, tok_seq, tok_pos, table, scale, max(lens))
+    kv_len = torch.tensor(lens, dtype=torch.int32, device=dev)
+    for splits in (None, 1, 3):
+        got = A.flash_decode_paged(q, cache, kv_len, table, max(lens), scale, splits=splits)
+        torch.cuda.synchronize()
+        err = (got.float() - want.float()).abs().max().item()
+        assert err < 2e-2, (splits, err)
