@@ -107,6 +107,18 @@ class AutoEPMoELayer(nn.Module):
         self.ep_group = None
         self.ep_rank = 0
 
+    def _use_fused(self, x):
+        import os
+        if os.environ.get("DSB200_FUSED_MOE", "1") != "1" or not x.is_cuda:
+            return False
+        if not hasattr(self, "_fused_ok"):
+            from ..moe import fused_dispatch as FD
+            try:
+                self._fused_ok = FD.supported(self.ep_group, self.hidden, self.top_k, x.dtype)
+            except Exception:  # noqa: BLE001
+                self._fused_ok = False
+        return self._fused_ok
+
     def set_deepspeed_parallelism(self, use_data_before_expert_parallel_=False):
         if self.group_name not in groups._get_expert_parallel_group_dict():
             groups._create_expert_and_data_parallel(self.ep_size, use_data_before_expert_parallel_)
@@ -123,9 +135,21 @@ class AutoEPMoELayer(nn.Module):
         tok = order // self.top_k
         routed = x.index_select(0, tok)                         # [T*k, H] expert-sorted
         counts = torch.bincount(flat_e, minlength=self.num_experts)
+        if self.ep_size > 1 and self.ep_group is None:
+            self.set_deepspeed_parallelism()
+        if self.ep_size > 1 and self._use_fused(x):
+            # ONE NVLink kernel per direction (csrc/moe_comm.cu): pull-dispatch into expert-contiguous rows, experts,
+            # pull-combine with the router weights -- no index_select / all-to-all-v / permute / index_add passes
+            from ..moe import fused_dispatch as FD
+            comm = FD.FusedMoEComm.get(self.ep_group, self.hidden)
+            plan = FD.build_plan(top_i, self.num_experts, self.ep_size, self.ep_rank, self.ep_group)
+            expert_in = FD.fused_dispatch(x, comm, plan)
+            expert_out = self.experts(expert_in, plan.local_counts)
+            out = FD.fused_combine(expert_out, top_w, comm, plan).reshape(shape)
+            if self.return_router_logits:
+                return out, None
+            return out
         if self.ep_size > 1:
-            if self.ep_group is None:
-                self.set_deepspeed_parallelism()
             # split plan: counts [ep, E_local] exchanged so every rank knows what it receives (one host sync,
             # same as the reference; the fused NVLink dispatch removes it)
             recv_counts = torch.empty_like(counts)
