@@ -113,5 +113,32 @@ class QuantizedLinear(nn.Linear):
         assert dtype == torch.bfloat16, "currently only supports bfloat16 dtype"
         self.weight = QuantizedParameter(self.weight.data, quantization_config=quantization_config)
 
+    def _apply(self, fn, recurse=True):
+        # nn.Module._apply assigns ``param.data = fn(param)``, which would drop the quantization metadata (and, for a
+        # weight still waiting to be quantized on its first CUDA residency, skip the quantization): convert the weight
+        # through QuantizedParameter.to instead
+        w = self._parameters.pop("weight")
+        try:
+            super()._apply(fn)
+            with torch.no_grad():
+                nw = fn(w)
+        finally:
+            self._parameters["weight"] = w
+        if not isinstance(nw, QuantizedParameter):
+            nw = QuantizedParameter(nw.data, quantization_config=w.quantization_config, quantizer=w.quantizer)
+        self._parameters["weight"] = nw
+        return self
+
     def forward(self, input):
+        w = self.weight
+        q = getattr(w, "_q", None)
+        if q is not None and input.is_cuda and not torch.is_grad_enabled():
+            # decode-sized inputs: the quantized weights cross HBM once and are expanded in registers
+            # (csrc/wo_gemm.cu); nothing is dequantized to memory
+            from ..ops import kernels as K
+            x2 = input.reshape(-1, input.shape[-1])
+            N, Kd = w._orig_shape[0], w._orig_shape[1]
+            if K.wo_gemm_supported(x2, w.data, q.group_size, q.q_bits, Kd) and q.scale.is_cuda:
+                y = K.wo_gemm(x2, w.data, q.scale, N, Kd, q.group_size, q.q_bits, self.bias)
+                return y.view(*input.shape[:-1], N)
         return F.linear(input, self.weight.dequantized(), self.bias)

@@ -122,6 +122,8 @@ def _declare(L):
     sig("dsb200_ce_fwd", P, P, P, P, I, I, L64, I, I, F, I, P)
     sig("dsb200_ce_fwd_ex", P, P, P, P, I, I, L64, I, I, F, P, I, P)
     sig("dsb200_scale_by_dev", P, L64, I, P, P)
+    sig("dsb200_wo_gemv", P, P, P, P, P, P, I, I, I, I, I, L64, L64, P)
+    sig("dsb200_wo_gemm_tc", P, P, P, P, P, P, I, I, I, I, I, L64, L64, P)
     sig("dsb200_ragged_kv_append_rope", P, P, P, P, P, P, P, P, P, I, L64, L64, L64, I, I, I, I, I, I, I, P)
     sig("dsb200_ragged_paged_attention", P, P, P, P, P, P, P, P, P, I, L64, I, I, I, I, I, I, F, P)
     sig("dsb200_move_rows", P, P, P, I, L64, L64, L64, L64, L64, I, P)
@@ -474,3 +476,50 @@ def ragged_paged_attention(q, kv_layer, tok_seq, tok_pos, block_table, scale, ma
 def ragged_attention_supported(q, head_dim, n_heads, n_kv_heads):
     return (available() and q.is_cuda and q.dtype == torch.bfloat16 and head_dim in (64, 128)
             and n_heads % n_kv_heads == 0 and n_heads // n_kv_heads in (1, 2, 4, 8))
+
+
+# ---------------------------------------------------------------------------------------------------------
+# weight-only quantized decode GEMM (csrc/wo_gemm.cu)
+# ---------------------------------------------------------------------------------------------------------
+_WO_SCRATCH = {}
+
+
+def wo_gemv_supported(x2, payload, group, q_bits, K_dim):
+    return (available() and x2.is_cuda and x2.dtype == torch.bfloat16 and x2.shape[0] <= 8 and q_bits in (4, 8)
+            and payload.dtype == torch.uint8 and K_dim % 256 == 0 and group % 16 == 0 and K_dim % group == 0
+            and x2.stride(1) == 1 and x2.stride(0) % 8 == 0)
+
+
+def wo_gemm_supported(x2, payload, group, q_bits, K_dim):
+    """Shapes the tcgen05 weight-only GEMM serves: up to 64 tokens."""
+    return (available() and x2.is_cuda and x2.dtype == torch.bfloat16 and 0 < x2.shape[0] <= 64 and q_bits in (4, 8)
+            and payload.dtype == torch.uint8 and K_dim % 64 == 0 and group % 16 == 0 and K_dim % group == 0
+            and x2.stride(1) == 1 and x2.stride(0) % 8 == 0 and x2.data_ptr() % 16 == 0 and payload.data_ptr() % 16 == 0
+            and (K_dim * q_bits // 8) % 16 == 0)
+
+
+def wo_gemm(x2, payload, scales, N, K_dim, group, q_bits, bias=None):
+    """``x2 [T <= 64, K] @ dequant(W [N, K])^T`` on the tensor cores (csrc/wo_gemm.cu, tcgen05 version): the quantized
+    weights are streamed once by TMA, dequantised into the swizzled operand layout in shared memory and multiplied with
+    the tokens as the N extent of the MMA. Returns bf16 [T, N]."""
+    T = x2.shape[0]
+    y = torch.empty((T, N), dtype=torch.bfloat16, device=x2.device)
+    buf = _WO_SCRATCH.get(x2.device)
+    if buf is None or buf.numel() < T * N:
+        buf = _WO_SCRATCH[x2.device] = torch.empty(max(T * N, 64 * 32768), dtype=torch.float32, device=x2.device)
+    _check(lib().dsb200_wo_gemm_tc(_ptr(x2), _ptr(payload), _ptr(scales), _ptr(bias), _ptr(y), _ptr(buf), T, N, K_dim,
+                                   int(group), int(q_bits), x2.stride(0), y.stride(0), _stream()), "wo_gemm_tc")
+    return y
+
+
+def wo_gemv(x2, payload, scales, N, K_dim, group, q_bits, bias=None):
+    """``x2 [M <= 8, K] @ dequant(W [N, K])^T`` with W as FP8 (e4m3 bytes) / FP4 (e2m1 nibble pairs) + fp32 group
+    scales; the weights are read once in their quantized form. Returns bf16 [M, N]."""
+    M = x2.shape[0]
+    y = torch.empty((M, N), dtype=torch.bfloat16, device=x2.device)
+    buf = _WO_SCRATCH.get(x2.device)
+    if buf is None or buf.numel() < M * N:
+        buf = _WO_SCRATCH[x2.device] = torch.empty(max(M * N, 8 * 32768), dtype=torch.float32, device=x2.device)
+    _check(lib().dsb200_wo_gemv(_ptr(x2), _ptr(payload), _ptr(scales), _ptr(bias), _ptr(y), _ptr(buf), M, N, K_dim,
+                                int(group), int(q_bits), x2.stride(0), y.stride(0), _stream()), "wo_gemv")
+    return y
