@@ -29,6 +29,9 @@ def _lib():
         L.dsb200_flash_attn_fwd_paged.restype = I
         L.dsb200_flash_decode_paged.argtypes = [P, P, P, P, P, P, P, I, I, I, I, I, I, F, P]
         L.dsb200_flash_decode_paged.restype = I
+        if hasattr(L, "dsb200_flash_attn_bwd"):
+            L.dsb200_flash_attn_bwd.argtypes = [P] * 10 + [I, I, I, I] + [L64] * 16 + [F, I, P]
+            L.dsb200_flash_attn_bwd.restype = I
         _DECLARED = True
     return L
 
@@ -145,11 +148,32 @@ def _reference_backward(q, k, v, do, causal, scale):
     return qd.grad, kd.grad, vd.grad
 
 
+def _native_backward_available():
+    return K.available() and hasattr(K.lib(), "dsb200_flash_attn_bwd") and os.environ.get("DSB200_NATIVE_ATTN_BWD", "1") == "1"
+
+
 def flash_attention_backward(q, k, v, o, lse, do, causal=True, scale=None):
-    """Gradients (dq, dk, dv) in the layouts of q / k / v (contiguous [B,S,H,128])."""
+    """Gradients (dq, dk, dv), contiguous [B,S,H,128] / [B,S,Hkv,128], on the tcgen05 backward kernels
+    (``csrc/attention_bwd.cu``) for self-attention with S a multiple of 128; otherwise through the library SDPA."""
+    B, Sq, H, D = q.shape
+    Skv, Hkv = k.shape[1], k.shape[2]
     if scale is None:
-        scale = 1.0 / math.sqrt(q.shape[-1])
-    return _reference_backward(q, k, v, do, causal, scale)
+        scale = 1.0 / math.sqrt(D)
+    if not (_native_backward_available() and Sq == Skv and Sq % 128 == 0 and lse is not None and _ok_layout(o)
+            and _ok_layout(do) and supported(q, k, v)):
+        return _reference_backward(q, k, v, do, causal, scale)
+    L = _lib()
+    dq = torch.empty((B, Sq, H, D), dtype=torch.bfloat16, device=q.device)
+    dk = torch.empty((B, Skv, Hkv, D), dtype=torch.bfloat16, device=q.device)
+    dv = torch.empty((B, Skv, Hkv, D), dtype=torch.bfloat16, device=q.device)
+    delta = torch.empty((B, H, Sq), dtype=torch.float32, device=q.device)
+    rc = L.dsb200_flash_attn_bwd(
+        K._ptr(q), K._ptr(k), K._ptr(v), K._ptr(o), K._ptr(do), K._ptr(lse), K._ptr(delta), K._ptr(dq), K._ptr(dk),
+        K._ptr(dv), B, Sq, H, Hkv, q.stride(1), q.stride(0), k.stride(1), k.stride(0), v.stride(1), v.stride(0),
+        o.stride(1), o.stride(0), do.stride(1), do.stride(0), dq.stride(1), dq.stride(0), dk.stride(1), dk.stride(0),
+        dv.stride(1), dv.stride(0), float(scale), 1 if causal else 0, K._stream())
+    K._check(rc, "flash_attn_bwd")
+    return dq, dk, dv
 
 
 class _FlashAttn(torch.autograd.Function):
