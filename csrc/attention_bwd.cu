@@ -40,6 +40,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int n) { asm volatile("ba
 // ------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) fa_bwd_delta_kernel(const __nv_bfloat16* __restrict__ o,
                                                            const __nv_bfloat16* __restrict__ dout,
+                                                           const float* __restrict__ dlse,
                                                            float* __restrict__ delta, int B, int S, int H,
                                                            int64_t o_row, int64_t o_batch, int64_t do_row,
                                                            int64_t do_batch)
@@ -58,7 +59,12 @@ __global__ void __launch_bounds__(256) fa_bwd_delta_kernel(const __nv_bfloat16* 
     const float2 g1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&g.y));
     float v = a0.x * g0.x + a0.y * g0.y + a1.x * g1.x + a1.y * g1.y;
     v = dsb::warp_sum(v);
-    if (lane == 0) delta[((int64_t)b * H + h) * S + i] = v;
+    // a gradient flowing into the log-sum-exp output (chunked / ring attention merges partial results through it) enters
+    // dS = P o (dP - delta) as an extra P o dLSE term, i.e. as a shift of delta
+    if (lane == 0) {
+        const int64_t idx = ((int64_t)b * H + h) * S + i;
+        delta[idx] = v - (dlse != nullptr ? dlse[idx] : 0.f);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -483,9 +489,11 @@ fa_bwd_dkv_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
 extern "C" {
 
 // All tensors bf16 [B, S, heads, 128] with element strides (last dim contiguous, heads packed 128 apart); lse [B, H, S]
-// fp32 from the forward; delta: fp32 scratch [B, H, S]. S must be a multiple of 128 (self-attention, Sq == Skv).
+// fp32 from the forward; dlse: gradient w.r.t. that log-sum-exp output ([B, H, S] fp32) or null; delta: fp32 scratch
+// [B, H, S]. S must be a multiple of 128 (Sq == Skv; causal or full).
 int dsb200_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout, const float* lse,
-                          float* delta, void* dq, void* dk, void* dv, int B, int S, int H, int Hkv, int64_t q_row,
+                          const float* dlse, float* delta, void* dq, void* dk, void* dv, int B, int S, int H, int Hkv,
+                          int64_t q_row,
                           int64_t q_batch, int64_t k_row, int64_t k_batch, int64_t v_row, int64_t v_batch, int64_t o_row,
                           int64_t o_batch, int64_t do_row, int64_t do_batch, int64_t dq_row, int64_t dq_batch,
                           int64_t dk_row, int64_t dk_batch, int64_t dv_row, int64_t dv_batch, float scale, int causal,
@@ -498,7 +506,8 @@ int dsb200_flash_attn_bwd(const void* q, const void* k, const void* v, const voi
     }
     const int64_t rows = (int64_t)B * S * H;
     fa_bwd_delta_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, stream>>>((const __nv_bfloat16*)o, (const __nv_bfloat16*)dout,
-                                                                        delta, B, S, H, o_row, o_batch, do_row, do_batch);
+                                                                        dlse, delta, B, S, H, o_row, o_batch, do_row,
+                                                                        do_batch);
     DSB_CHECK_LAUNCH("fa_bwd_delta");
     CUtensorMap mq, mdo, mk, mv;
     if (make_map_3d(&mq, q, B, S, (int64_t)H * FA_D, q_row, q_batch, 128) != 0) return -2;

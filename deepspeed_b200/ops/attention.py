@@ -30,7 +30,7 @@ def _lib():
         L.dsb200_flash_decode_paged.argtypes = [P, P, P, P, P, P, P, I, I, I, I, I, I, F, P]
         L.dsb200_flash_decode_paged.restype = I
         if hasattr(L, "dsb200_flash_attn_bwd"):
-            L.dsb200_flash_attn_bwd.argtypes = [P] * 10 + [I, I, I, I] + [L64] * 16 + [F, I, P]
+            L.dsb200_flash_attn_bwd.argtypes = [P] * 11 + [I, I, I, I] + [L64] * 16 + [F, I, P]
             L.dsb200_flash_attn_bwd.restype = I
         _DECLARED = True
     return L
@@ -152,15 +152,23 @@ def _native_backward_available():
     return K.available() and hasattr(K.lib(), "dsb200_flash_attn_bwd") and os.environ.get("DSB200_NATIVE_ATTN_BWD", "1") == "1"
 
 
-def flash_attention_backward(q, k, v, o, lse, do, causal=True, scale=None):
+def native_backward_supported(q, k, v, o, do, lse):
+    return (_native_backward_available() and q.shape[1] == k.shape[1] and q.shape[1] % 128 == 0 and lse is not None
+            and _ok_layout(o) and _ok_layout(do) and supported(q, k, v))
+
+
+def flash_attention_backward(q, k, v, o, lse, do, causal=True, scale=None, dlse=None):
     """Gradients (dq, dk, dv), contiguous [B,S,H,128] / [B,S,Hkv,128], on the tcgen05 backward kernels
-    (``csrc/attention_bwd.cu``) for self-attention with S a multiple of 128; otherwise through the library SDPA."""
+    (``csrc/attention_bwd.cu``) for Sq == Skv a multiple of 128; otherwise through the library SDPA. ``dlse``: gradient
+    w.r.t. the log-sum-exp output [B,H,S] (chunked attention merges partial results through it) or None."""
     B, Sq, H, D = q.shape
     Skv, Hkv = k.shape[1], k.shape[2]
     if scale is None:
         scale = 1.0 / math.sqrt(D)
-    if not (_native_backward_available() and Sq == Skv and Sq % 128 == 0 and lse is not None and _ok_layout(o)
-            and _ok_layout(do) and supported(q, k, v)):
+    if not native_backward_supported(q, k, v, o, do, lse):
+        if dlse is not None:
+            raise RuntimeError("flash_attention_backward: a gradient w.r.t. the LSE output needs the native kernels "
+                               "(bf16, head_dim 128, Sq == Skv multiple of 128)")
         return _reference_backward(q, k, v, do, causal, scale)
     L = _lib()
     dq = torch.empty((B, Sq, H, D), dtype=torch.bfloat16, device=q.device)
@@ -168,7 +176,8 @@ def flash_attention_backward(q, k, v, o, lse, do, causal=True, scale=None):
     dv = torch.empty((B, Skv, Hkv, D), dtype=torch.bfloat16, device=q.device)
     delta = torch.empty((B, H, Sq), dtype=torch.float32, device=q.device)
     rc = L.dsb200_flash_attn_bwd(
-        K._ptr(q), K._ptr(k), K._ptr(v), K._ptr(o), K._ptr(do), K._ptr(lse), K._ptr(delta), K._ptr(dq), K._ptr(dk),
+        K._ptr(q), K._ptr(k), K._ptr(v), K._ptr(o), K._ptr(do), K._ptr(lse),
+        K._ptr(dlse.contiguous().float() if dlse is not None else None), K._ptr(delta), K._ptr(dq), K._ptr(dk),
         K._ptr(dv), B, Sq, H, Hkv, q.stride(1), q.stride(0), k.stride(1), k.stride(0), v.stride(1), v.stride(0),
         o.stride(1), o.stride(0), do.stride(1), do.stride(0), dq.stride(1), dq.stride(0), dk.stride(1), dk.stride(0),
         dv.stride(1), dv.stride(0), float(scale), 1 if causal else 0, K._stream())
@@ -190,6 +199,33 @@ class _FlashAttn(torch.autograd.Function):
         q, k, v, o, lse = ctx.saved_tensors
         dq, dk, dv = flash_attention_backward(q, k, v, o, lse, do.contiguous(), ctx.causal, ctx.scale)
         return dq, dk, dv, None, None
+
+
+class _FlashAttnLSE(torch.autograd.Function):
+    """(out, lse) with gradients through both (partial-attention building block of chunked / blockwise schemes)."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, causal, scale):
+        o, lse = flash_attention_forward(q, k, v, causal, scale)
+        ctx.save_for_backward(q, k, v, o, lse)
+        ctx.causal, ctx.scale = causal, scale
+        return o, lse
+
+    @staticmethod
+    def backward(ctx, do, dlse):
+        q, k, v, o, lse = ctx.saved_tensors
+        dq, dk, dv = flash_attention_backward(q, k, v, o, lse, do.contiguous(), ctx.causal, ctx.scale, dlse=dlse)
+        return dq, dk, dv, None, None
+
+
+def lse_attention_supported(q, k, v):
+    """Can :func:`flash_attention_with_lse` serve these operands forward AND backward on the native kernels?"""
+    return supported(q, k, v) and _native_backward_available() and q.shape[1] == k.shape[1] and q.shape[1] % 128 == 0
+
+
+def flash_attention_with_lse(q, k, v, causal=True, scale=None):
+    """-> (out [B,S,H,128] bf16, lse [B,H,S] fp32), differentiable through both outputs."""
+    return _FlashAttnLSE.apply(q, k, v, causal, scale)
 
 
 def flash_attention(q, k, v, causal=True, scale=None):

@@ -25,7 +25,15 @@ def update_out_and_lse(out, lse, block_out, block_lse):
 
 
 def _attn_with_lse(q, k, v, causal):
-    """q,k,v: [B,S,H,D] -> (out [B,S,H,D], lse [B,H,Sq]) in fp32 math (chunk-sized, so materialising scores is fine)."""
+    """q,k,v: [B,S,H,D] -> (out [B,S,H,D], lse [B,H,Sq]). On a GPU (bf16, head_dim 128, chunk a multiple of 128) this is
+    the tcgen05 flash-attention forward/backward pair with the log-sum-exp as a differentiable output
+    (``ops/attention.py``; reference: flash-attn ``_flash_attn_forward/_backward``, fpdt_layer.py:238-269); otherwise
+    fp32 math that materialises the chunk's scores."""
+    if q.is_cuda:
+        from ..ops import attention as _A
+        qc, kc, vc = (t if t.stride(-1) == 1 and t.stride(2) == t.shape[-1] else t.contiguous() for t in (q, k, v))
+        if _A.lse_attention_supported(qc, kc, vc):
+            return _A.flash_attention_with_lse(qc, kc, vc, causal=causal)
     qt, kt, vt = q.transpose(1, 2).float(), k.transpose(1, 2).float(), v.transpose(1, 2).float()
     if kt.shape[1] != qt.shape[1]:
         rep = qt.shape[1] // kt.shape[1]

@@ -236,6 +236,14 @@ int dsb200_flash_attn_fwd_paged(const void* q, const void* kv, void* o, float* l
                                 const int* kv_len, const int* block_table, int n_seqs, int T_total, int max_q_len,
                                 int H, int Hkv, int num_blocks, int max_blocks, int64_t q_row_stride,
                                 int64_t o_row_stride, float scale, cudaStream_t stream);
+/* backward (csrc/attention_bwd.cu): delta preprocess + transposed dK/dV kernel + dQ kernel, Sq == Skv multiple of 128;
+ * dlse = gradient w.r.t. the LSE output or null; delta = fp32 scratch [B, H, S] */
+int dsb200_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout, const float* lse,
+                          const float* dlse, float* delta, void* dq, void* dk, void* dv, int B, int S, int H, int Hkv,
+                          int64_t q_row, int64_t q_batch, int64_t k_row, int64_t k_batch, int64_t v_row, int64_t v_batch,
+                          int64_t o_row, int64_t o_batch, int64_t do_row, int64_t do_batch, int64_t dq_row,
+                          int64_t dq_batch, int64_t dk_row, int64_t dk_batch, int64_t dv_row, int64_t dv_batch,
+                          float scale, int causal, cudaStream_t stream);
 /* decode (one token per sequence) over the blocked cache on the same kernel: query heads of a KV head are the tile rows,
  * split-KV partials merged by a second kernel (reference: ragged_ops/blocked_flash decode path) */
 int dsb200_flash_decode_paged(const void* q, const void* kv, void* o, const int* kv_len, const int* block_table,
