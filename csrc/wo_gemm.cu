@@ -214,78 +214,111 @@ int dsb200_wo_gemv(const void* x, const void* wq, const float* scales, const voi
 // tcgen05 version: Y[T, N] = X[T, K] * dequant(Wq[N, K])^T for T <= 64 tokens, computed as D = W * X^T so that the
 // (large) weight matrix is the M operand of the MMA and the few tokens are its N extent (16 / 32 / 64).
 //
-//   warp 0     TMA: raw quantized weight tile (128 rows x 64 elements: 8 KB FP8 / 4 KB FP4, unswizzled) and the
-//              activation tile (TN tokens x 64, bf16, 128-byte swizzle) of every k-block into a 4-stage ring
-//   warps 2-5  dequantise: raw bytes -> (hardware cvt / table) -> * group scale -> bf16, written straight into the
-//              128-byte-swizzled K-major layout the tensor core reads (two buffers), then fence.proxy.async
-//   warp 1     one lane issues 4 x tcgen05.mma (M128 x N{16,32,64} x K16) per k-block, accumulator in TMEM
-//   warps 2-5  epilogue: tcgen05.ld, fp32 atomics into y32[T, N] (split-K CTAs add up), converted by wo_finish_kernel
+//   warp 0      TMA: raw quantized weight tile (128 rows x 64 elements: 8 KB FP8 / 4 KB FP4, unswizzled) and the
+//               activation tile (TN tokens x 64, bf16, 128-byte swizzle) of every k-block into a 4-stage ring
+//   warps 6-13  expand: raw codes -> f16 with ONE hardware cvt per two elements (cvt.f16x2.e4m3x2 / .e2m1x2, exact),
+//               written straight into the 128-byte-swizzled K-major layout the tensor core reads; no scale here
+//   warp 1      one lane issues 4 x tcgen05.mma (A = f16 weights, B = activations converted to f16, M128 x N{16,32,64} x K16) per
+//               k-block; each scale group (`group` elements of K) accumulates into its own TMEM buffer (two alternate)
+//   warps 2-5   per group: tcgen05.ld the group's partial sums, multiply by the fp32 group scale of the row, add into
+//               fp32 registers; at the end bf16 store (+ bias), or fp32 atomics when split-K CTAs share an output
 //
-// The weights cross HBM once in quantized form; SIMT work per weight element is ~3 instructions (the first version
-// above spends 3 + M and loses to the bf16 library GEMM). Grid = (N / 128) x split-K so that all SMs stream.
+// The weights cross HBM once in quantized form and cost ~0.7 SIMT instructions per element (the scale is applied to
+// the per-group partial sums in fp32, which is also more accurate than scaling the weights to bf16 first).
+// Grid = (N / 128) x split-K so that all SMs stream.
 // =========================================================================================================
 #include "gemm_common.cuh"
 
 namespace {
 
-constexpr int WT_STAGES = 4;
+// ~48 KB of raw weights in flight per CTA (two CTAs per SM): HBM latency x bandwidth needs ~90 KB per SM; ncu showed the
+// 4-stage version waiting on the ring (37 % of DRAM peak, long-scoreboard stalls)
+constexpr int WT_RING_BYTES = 48 * 1024;
+constexpr int WT_MAX_STAGES = 12;
+constexpr int WT_ABUFS = 2;  // expanded weight tiles in flight between the expand warps and the MMA
 constexpr int WT_BM = 128, WT_BK = 64;
+constexpr int WT_THREADS = 64 + 128 + 256;  // TMA warp, MMA warp, 4 accumulate / epilogue warps, 8 expand warps
 
 struct WtBars {
-    uint64_t raw_full[WT_STAGES], raw_empty[WT_STAGES];
-    uint64_t a_full[2], a_empty[2];
-    uint64_t d_full;
+    uint64_t raw_full[WT_MAX_STAGES], raw_empty[WT_MAX_STAGES];
+    uint64_t a_full[WT_ABUFS], a_empty[WT_ABUFS];
+    uint64_t acc_full[2], acc_empty[2];
     uint32_t tmem_base;
 };
 
-constexpr int WT_THREADS = 64 + 256;  // TMA warp, MMA warp, 8 dequantise / epilogue warps
+// kind::f16 with A = B = f16, D = f32, both K-major (mixing an f16 with a bf16 operand is an illegal instruction)
+__host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n)
+{
+    return (1u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
 
-template <int BITS>
+// activations bf16 -> f16 (saturating at +-65504), so that both MMA operands are f16
+__global__ void __launch_bounds__(256) wo_x_to_f16_kernel(const __nv_bfloat16* __restrict__ x, __half* __restrict__ x16, int T,
+                                                          int K, int64_t x_stride)
+{
+    const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+    if (i >= (int64_t)T * K) return;
+    const int t = (int)(i / K), k = (int)(i % K);
+    const uint4 raw = *reinterpret_cast<const uint4*>(x + (int64_t)t * x_stride + k);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+    uint4 out;
+    __half2* o = reinterpret_cast<__half2*>(&out);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        float2 f = __bfloat1622float2(h[j]);
+        f.x = fminf(fmaxf(f.x, -65504.f), 65504.f);
+        f.y = fminf(fmaxf(f.y, -65504.f), 65504.f);
+        o[j] = __floats2half2_rn(f.x, f.y);
+    }
+    *reinterpret_cast<uint4*>(x16 + i) = out;
+}
+
+template <int BITS, int TN>
 __global__ void __launch_bounds__(WT_THREADS, 2)
 wo_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x,
                   const float* __restrict__ scales, float* __restrict__ y32, const __nv_bfloat16* __restrict__ bias,
-                  __nv_bfloat16* __restrict__ y, int64_t y_stride, int T, int N, int K, int group, int TN,
-                  int kb_per_split)
+                  __nv_bfloat16* __restrict__ y, int64_t y_stride, int T, int N, int K, int group, int kb_per_split)
 {
     constexpr int RAW_BYTES = WT_BM * WT_BK * BITS / 8;  // 8 KB / 4 KB
-    constexpr int X_BYTES_MAX = 64 * WT_BK * 2;          // 8 KB
+    constexpr int WT_STAGES = WT_RING_BYTES / RAW_BYTES;  // 6 / 12
+    constexpr int X_BYTES_MAX = (TN * WT_BK * 2 + 1023) / 1024 * 1024;  // 2 / 4 / 8 KB
     constexpr int A_BYTES_T = WT_BM * WT_BK * 2;         // 16 KB
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* a_smem = base;                                   // 2 x 16 KB (swizzled bf16 weight tiles)
-    uint8_t* x_smem = a_smem + 2 * A_BYTES_T;                 // WT_STAGES x 8 KB
+    uint8_t* a_smem = base;                                   // WT_ABUFS x 16 KB (swizzled f16 weight tiles)
+    uint8_t* x_smem = a_smem + WT_ABUFS * A_BYTES_T;          // WT_STAGES x X_BYTES_MAX
     uint8_t* r_smem = x_smem + WT_STAGES * X_BYTES_MAX;       // WT_STAGES x RAW_BYTES
     WtBars* bars = reinterpret_cast<WtBars*>(r_smem + WT_STAGES * RAW_BYTES);
-    __shared__ __nv_bfloat16 lut4[16];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n0 = blockIdx.x * WT_BM;
     const int kb0 = blockIdx.y * kb_per_split;
     const int kb_total = K / WT_BK;
     const int nkb = min(kb_per_split, kb_total - kb0);
     if (nkb <= 0) return;
+    const int kbg = group / WT_BK;  // k-blocks per scale group (group is a multiple of 64)
+    // groups touched by this CTA: absolute group index of k-block kb is (kb0 + kb) / kbg
+    const int g_first = kb0 / kbg, g_last = (kb0 + nkb - 1) / kbg;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < WT_STAGES; s++) {
             mbar_init(&bars->raw_full[s], 1);
             mbar_init(&bars->raw_empty[s], 1);
         }
-        for (int s = 0; s < 2; s++) {
+        for (int s = 0; s < WT_ABUFS; s++) {
             mbar_init(&bars->a_full[s], 8);
             mbar_init(&bars->a_empty[s], 1);
         }
-        mbar_init(&bars->d_full, 1);
+        for (int s = 0; s < 2; s++) {
+            mbar_init(&bars->acc_full[s], 1);
+            mbar_init(&bars->acc_empty[s], 4);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
     }
-    if (threadIdx.x < 16) {
-        const int mag = threadIdx.x & 7;
-        const float v = (mag < 2) ? 0.5f * mag : (float)(2 | (mag & 1)) * (float)(1 << ((mag >> 1) - 1)) * 0.5f;
-        lut4[threadIdx.x] = __float2bfloat16_rn((threadIdx.x & 8) ? -v : v);
-    }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&bars->tmem_base)),
-                     "n"(64)
+                     "n"(128)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -313,19 +346,32 @@ wo_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_consta
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            const uint32_t idesc = make_idesc(WT_BM, TN);
+            const uint32_t idesc = make_idesc_f16(WT_BM, TN);
             int stage = 0;
             uint32_t phase = 0;
+            int cur_g = -1, gi = -1;
             for (int kb = 0; kb < nkb; kb++) {
-                const int a = kb & 1;
-                mbar_wait(&bars->raw_full[stage], phase);       // activation tile landed
-                mbar_wait(&bars->a_full[a], (uint32_t)((kb >> 1) & 1));  // weight tile dequantised
+                const int a = kb % WT_ABUFS;
+                const int g = (kb0 + kb) / kbg;
+                bool first_of_group = false;
+                if (g != cur_g) {  // a new scale group starts: switch accumulator buffer
+                    if (cur_g >= 0) umma_commit(&bars->acc_full[gi & 1]);
+                    cur_g = g;
+                    gi++;
+                    mbar_wait(&bars->acc_empty[gi & 1], (uint32_t)(((gi >> 1) & 1) ^ 1));
+                    tc_fence_after();
+                    first_of_group = true;
+                }
+                mbar_wait(&bars->raw_full[stage], phase);                        // activation tile landed
+                mbar_wait(&bars->a_full[a], (uint32_t)((kb / WT_ABUFS) & 1));    // weight tile expanded
                 tc_fence_after();
                 const uint64_t adesc = make_smem_desc(smem_u32(a_smem + a * A_BYTES_T));
                 const uint64_t bdesc = make_smem_desc(smem_u32(x_smem + stage * X_BYTES_MAX));
+                const uint32_t d_addr = tmem_base + (uint32_t)((gi & 1) * 64);
 #pragma unroll
                 for (int k = 0; k < WT_BK / UMMA_K; k++)
-                    umma_bf16(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                    umma_bf16(d_addr, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
+                              (!first_of_group || k > 0) ? 1u : 0u);
                 umma_commit(&bars->raw_empty[stage]);
                 umma_commit(&bars->a_empty[a]);
                 if (++stage == WT_STAGES) {
@@ -333,62 +379,46 @@ wo_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_consta
                     phase ^= 1;
                 }
             }
-            umma_commit(&bars->d_full);
+            umma_commit(&bars->acc_full[gi & 1]);
         }
-    } else {
-        // ---------------- dequantise (and later: epilogue) ----------------
-        const int tq = threadIdx.x - 64;  // 0..255: two (row, 16-element chunk) units per k-block
+    } else if (warp >= 6) {
+        // ---------------- expand raw codes to f16 (8 warps: two (row, 16-element chunk) units per thread) ----------------
+        const int tq = threadIdx.x - 192;  // 0..255
         int stage = 0;
         uint32_t phase = 0;
-        float sc[2] = {0.f, 0.f};
-        int sc_group[2] = {-1, -1};
         for (int kb = 0; kb < nkb; kb++) {
-            const int a = kb & 1;
-            const int kglob = (kb0 + kb) * WT_BK;
-            // group scales change every `group` elements along K (>= 16): reload only then, before waiting for data
-#pragma unroll
-            for (int i = 0; i < 2; i++) {
-                const int row = i * 64 + (tq >> 2), c4 = tq & 3;
-                const int n = n0 + row;
-                const int64_t g = ((int64_t)n * K + kglob + c4 * 16) / group;
-                if (n < N && (int)(g & 0x7fffffff) != sc_group[i]) {
-                    sc[i] = __ldg(scales + g);
-                    sc_group[i] = (int)(g & 0x7fffffff);
-                }
-            }
+            const int a = kb % WT_ABUFS;
             mbar_wait(&bars->raw_full[stage], phase);
-            mbar_wait(&bars->a_empty[a], (uint32_t)(((kb >> 1) & 1) ^ 1));
+            mbar_wait(&bars->a_empty[a], (uint32_t)(((kb / WT_ABUFS) & 1) ^ 1));
             const uint8_t* raw = r_smem + stage * RAW_BYTES;
             uint8_t* dst = a_smem + a * A_BYTES_T;
 #pragma unroll
             for (int i = 0; i < 2; i++) {
                 const int row = i * 64 + (tq >> 2), c4 = tq & 3;  // 16 elements: logical 16-byte chunks 2*c4, 2*c4+1
-                const float scv = sc[i];
                 uint32_t out[8];
                 if constexpr (BITS == 8) {
                     const uint4 rv = *reinterpret_cast<const uint4*>(raw + row * 64 + c4 * 16);
                     const uint32_t words[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
                     for (int w = 0; w < 4; w++) {
-                        float f[4];
-                        cvt_e4m3x4(words[w], f);
-                        __nv_bfloat162 p0 = __floats2bfloat162_rn(f[0] * scv, f[1] * scv);
-                        __nv_bfloat162 p1 = __floats2bfloat162_rn(f[2] * scv, f[3] * scv);
-                        out[2 * w] = *reinterpret_cast<uint32_t*>(&p0);
-                        out[2 * w + 1] = *reinterpret_cast<uint32_t*>(&p1);
+                        const __half2_raw lo = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)(words[w] & 0xFFFF), __NV_E4M3);
+                        const __half2_raw hi = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)(words[w] >> 16), __NV_E4M3);
+                        out[2 * w] = *reinterpret_cast<const uint32_t*>(&lo);
+                        out[2 * w + 1] = *reinterpret_cast<const uint32_t*>(&hi);
                     }
                 } else {
+#ifdef DSB_HAVE_FP4
                     const uint2 rv = *reinterpret_cast<const uint2*>(raw + row * 32 + c4 * 8);
                     const uint32_t words[2] = {rv.x, rv.y};
 #pragma unroll
                     for (int w = 0; w < 2; w++)
 #pragma unroll
                         for (int p = 0; p < 4; p++) {
-                            const float f0 = __bfloat162float(lut4[(words[w] >> (8 * p)) & 0xF]) * scv;
-                            const float f1 = __bfloat162float(lut4[(words[w] >> (8 * p + 4)) & 0xF]) * scv;
-                            __nv_bfloat162 pr = __floats2bfloat162_rn(f0, f1);
-                            out[w * 4 + p] = *reinterpret_cast<uint32_t*>(&pr);
+                            const __half2_raw h2 =
+                                __nv_cvt_fp4x2_to_halfraw2((__nv_fp4x2_storage_t)((words[w] >> (8 * p)) & 0xFF), __NV_E2M1);
+                            out[w * 4 + p] = *reinterpret_cast<const uint32_t*>(&h2);
                         }
+#endif
                 }
                 // 128-byte swizzle of the K-major tile: 16-byte chunk c of row r lives at chunk (c ^ (r & 7))
                 const int sw = row & 7;
@@ -403,34 +433,50 @@ wo_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_consta
                 phase ^= 1;
             }
         }
-        // ---------------- epilogue (warps 2-5 own the four TMEM lane groups) ----------------
-        if (warp < 6) {
-            mbar_wait(&bars->d_full, 0);
-            tc_fence_after();
-            const int lane_group = warp & 3;
-            const int n = n0 + lane_group * 32 + lane;
-            const bool direct = gridDim.y == 1;  // no split-K: write bf16 (+ bias) straight to y
-            const float bv = (direct && bias != nullptr && n < N) ? __bfloat162float(bias[n]) : 0.f;
-            for (int c = 0; c < TN; c += 16) {
-                uint32_t r[16];
-                const uint32_t taddr = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)c;
-                asm volatile(
-                    "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-                    : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-                      "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-                    : "r"(taddr)
-                    : "memory");
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (n < N) {
+    } else {
+        // ---------------- per-group accumulate + epilogue (warps 2-5 own the four TMEM lane groups) ----------------
+        const int lane_group = warp & 3;
+        const int n = n0 + lane_group * 32 + lane;
+        float acc[TN];
 #pragma unroll
-                    for (int j = 0; j < 16; j++) {
-                        if (c + j >= T) break;
-                        if (direct)
-                            y[(int64_t)(c + j) * y_stride + n] = __float2bfloat16_rn(__uint_as_float(r[j]) + bv);
-                        else
-                            atomicAdd(&y32[(int64_t)(c + j) * N + n], __uint_as_float(r[j]));
-                    }
+        for (int j = 0; j < TN; j++) acc[j] = 0.f;
+        int gi = 0;
+        for (int g = g_first; g <= g_last; g++, gi++) {
+            const float sc = (n < N) ? __ldg(scales + (int64_t)n * (K / group) + g) : 0.f;
+            mbar_wait(&bars->acc_full[gi & 1], (uint32_t)((gi >> 1) & 1));
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)((gi & 1) * 64);
+#pragma unroll
+            for (int c = 0; c < TN; c += 16) {
+                {
+                    uint32_t r[16];
+                    asm volatile(
+                        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+                        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
+                          "=r"(r[15])
+                        : "r"(taddr + c)
+                        : "memory");
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                    for (int j = 0; j < 16; j++) acc[c + j] = fmaf(sc, __uint_as_float(r[j]), acc[c + j]);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars->acc_empty[gi & 1]);
+        }
+        if (n < N) {
+            const bool direct = gridDim.y == 1;  // no split-K: write bf16 (+ bias) straight to y
+            const float bv = (direct && bias != nullptr) ? __bfloat162float(bias[n]) : 0.f;
+#pragma unroll
+            for (int j = 0; j < TN; j++) {
+                if (j < T) {
+                    if (direct)
+                        y[(int64_t)j * y_stride + n] = __float2bfloat16_rn(acc[j] + bv);
+                    else
+                        atomicAdd(&y32[(int64_t)j * N + n], acc[j]);
                 }
             }
         }
@@ -439,7 +485,7 @@ wo_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_consta
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(64) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(128) : "memory");
     }
 }
 
@@ -469,20 +515,31 @@ int make_map_bytes(CUtensorMap* map, const void* ptr, int64_t rows, int64_t row_
 
 extern "C" {
 
-// As dsb200_wo_gemv, on the tensor cores, for T <= 64 tokens. K a multiple of 64, group a multiple of 16 dividing K.
-int dsb200_wo_gemm_tc(const void* x, const void* wq, const float* scales, const void* bias, void* y, float* y32, int T,
-                      int N, int K, int group, int bits, int64_t x_stride, int64_t y_stride, cudaStream_t stream)
+// As dsb200_wo_gemv, on the tensor cores, for T <= 64 tokens. K a multiple of 64; the scale group a multiple of 64 that
+// divides K (scales laid out [N, K / group]).
+// x16: scratch of T * K halves (the activations as f16); y32: T * N floats (used when split-K is taken).
+int dsb200_wo_gemm_tc(const void* x, const void* wq, const float* scales, const void* bias, void* y, float* y32, void* x16,
+                      int T, int N, int K, int group, int bits, int64_t x_stride, int64_t y_stride, cudaStream_t stream)
 {
     if (T <= 0 || N <= 0) return 0;
-    if (T > 64 || K % WT_BK != 0 || group % 16 != 0 || K % group != 0 || (bits != 8 && bits != 4) || (x_stride % 8) ||
+    if (T > 64 || K % WT_BK != 0 || group % WT_BK != 0 || K % group != 0 || (bits != 8 && bits != 4) || (x_stride % 8) ||
         ((uintptr_t)x & 15) || ((uintptr_t)wq & 15)) {
-        dsb200_set_error("wo_gemm_tc: needs T <= 64, K % 64 == 0, group % 16 == 0 dividing K, bits in {4, 8}, aligned operands");
+        dsb200_set_error("wo_gemm_tc: needs T <= 64, K % 64 == 0, group % 64 == 0 dividing K, bits in {4, 8}, aligned operands");
         return -1;
     }
+#ifndef DSB_HAVE_FP4
+    if (bits == 4) {
+        dsb200_set_error("wo_gemm_tc: built without cuda_fp4.h");
+        return -1;
+    }
+#endif
     const int TN = T <= 16 ? 16 : (T <= 32 ? 32 : 64);
     CUtensorMap mw, mx;
     if (make_map_bytes(&mw, wq, N, (int64_t)K * bits / 8, WT_BK * bits / 8, WT_BM) != 0) return -2;
-    if (make_map(&mx, x, T, K, x_stride, TN) != 0) return -2;
+    wo_x_to_f16_kernel<<<(unsigned)(((int64_t)T * K / 8 + 255) / 256), 256, 0, stream>>>((const __nv_bfloat16*)x, (__half*)x16,
+                                                                                        T, K, x_stride);
+    DSB_CHECK_LAUNCH("wo_x_to_f16");
+    if (make_map(&mx, x16, T, K, K, TN) != 0) return -2;  // same element size / swizzle as a bf16 map
     const int n_blocks = (N + WT_BM - 1) / WT_BM, kb_total = K / WT_BK;
     int splits = (2 * DSB_NUM_SMS) / n_blocks;  // aim at ~2 CTAs per SM in total; none when N alone fills the GPU
     if (splits > kb_total / 4) splits = kb_total / 4 > 0 ? kb_total / 4 : 1;
@@ -492,25 +549,41 @@ int dsb200_wo_gemm_tc(const void* x, const void* wq, const float* scales, const 
     if (splits > 1) DSB_CHECK(cudaMemsetAsync(y32, 0, (size_t)T * N * sizeof(float), stream));
     dim3 grid(n_blocks, splits);
     const int raw_bytes = WT_BM * WT_BK * bits / 8;
-    const int smem = 2 * WT_BM * WT_BK * 2 + WT_STAGES * 64 * WT_BK * 2 + WT_STAGES * raw_bytes + 1024 + 256;
+    const int x_stage = (TN * WT_BK * 2 + 1023) / 1024 * 1024;
+    const int n_stages = WT_RING_BYTES / raw_bytes;
+    const int smem = WT_ABUFS * WT_BM * WT_BK * 2 + n_stages * x_stage + n_stages * raw_bytes + 1024 + 512;
     int dev_ = 0;
     cudaGetDevice(&dev_);
-#define WT_LAUNCH(BB)                                                                                                  \
+#define WT_LAUNCH_(BB, TT)                                                                                             \
     do {                                                                                                               \
         static bool attr_set[64] = {};                                                                                 \
         if (!attr_set[dev_ & 63]) {                                                                                    \
-            DSB_CHECK(cudaFuncSetAttribute(wo_gemm_tc_kernel<BB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
+            DSB_CHECK(cudaFuncSetAttribute(wo_gemm_tc_kernel<BB, TT>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                           smem));                                                                     \
             attr_set[dev_ & 63] = true;                                                                                \
         }                                                                                                              \
-        wo_gemm_tc_kernel<BB><<<grid, WT_THREADS, smem, stream>>>(mw, mx, scales, y32, (const __nv_bfloat16*)bias,    \
-                                                                  (__nv_bfloat16*)y, y_stride, T, N, K, group, TN,     \
-                                                                  kb_per_split);                                       \
+        wo_gemm_tc_kernel<BB, TT><<<grid, WT_THREADS, smem, stream>>>(mw, mx, scales, y32, (const __nv_bfloat16*)bias, \
+                                                                      (__nv_bfloat16*)y, y_stride, T, N, K, group,      \
+                                                                      kb_per_split);                                   \
     } while (0)
-    if (bits == 8)
-        WT_LAUNCH(8);
+#define WT_BITS(TT)            \
+    do {                       \
+        if (bits == 8) {       \
+            constexpr int BB = 8; \
+            WT_LAUNCH_(BB, TT); \
+        } else {               \
+            constexpr int BB = 4; \
+            WT_LAUNCH_(BB, TT); \
+        }                      \
+    } while (0)
+    if (TN == 16)
+        WT_BITS(16);
+    else if (TN == 32)
+        WT_BITS(32);
     else
-        WT_LAUNCH(4);
-#undef WT_LAUNCH
+        WT_BITS(64);
+#undef WT_BITS
+#undef WT_LAUNCH_
     DSB_CHECK_LAUNCH("wo_gemm_tc");
     if (splits > 1) {
         const int64_t total = (int64_t)T * N;

@@ -123,7 +123,7 @@ def _declare(L):
     sig("dsb200_ce_fwd_ex", P, P, P, P, I, I, L64, I, I, F, P, I, P)
     sig("dsb200_scale_by_dev", P, L64, I, P, P)
     sig("dsb200_wo_gemv", P, P, P, P, P, P, I, I, I, I, I, L64, L64, P)
-    sig("dsb200_wo_gemm_tc", P, P, P, P, P, P, I, I, I, I, I, L64, L64, P)
+    sig("dsb200_wo_gemm_tc", P, P, P, P, P, P, P, I, I, I, I, I, L64, L64, P)
     sig("dsb200_ragged_kv_append_rope", P, P, P, P, P, P, P, P, P, I, L64, L64, L64, I, I, I, I, I, I, I, P)
     sig("dsb200_ragged_paged_attention", P, P, P, P, P, P, P, P, P, I, L64, I, I, I, I, I, I, F, P)
     sig("dsb200_move_rows", P, P, P, I, L64, L64, L64, L64, L64, I, P)
@@ -493,7 +493,7 @@ def wo_gemv_supported(x2, payload, group, q_bits, K_dim):
 def wo_gemm_supported(x2, payload, group, q_bits, K_dim):
     """Shapes the tcgen05 weight-only GEMM serves: up to 64 tokens."""
     return (available() and x2.is_cuda and x2.dtype == torch.bfloat16 and 0 < x2.shape[0] <= 64 and q_bits in (4, 8)
-            and payload.dtype == torch.uint8 and K_dim % 64 == 0 and group % 16 == 0 and K_dim % group == 0
+            and payload.dtype == torch.uint8 and K_dim % 64 == 0 and group % 64 == 0 and K_dim % group == 0
             and x2.stride(1) == 1 and x2.stride(0) % 8 == 0 and x2.data_ptr() % 16 == 0 and payload.data_ptr() % 16 == 0
             and (K_dim * q_bits // 8) % 16 == 0)
 
@@ -504,11 +504,13 @@ def wo_gemm(x2, payload, scales, N, K_dim, group, q_bits, bias=None):
     the tokens as the N extent of the MMA. Returns bf16 [T, N]."""
     T = x2.shape[0]
     y = torch.empty((T, N), dtype=torch.bfloat16, device=x2.device)
+    need = T * N + (T * K_dim + 1) // 2 + 64
     buf = _WO_SCRATCH.get(x2.device)
-    if buf is None or buf.numel() < T * N:
-        buf = _WO_SCRATCH[x2.device] = torch.empty(max(T * N, 64 * 32768), dtype=torch.float32, device=x2.device)
-    _check(lib().dsb200_wo_gemm_tc(_ptr(x2), _ptr(payload), _ptr(scales), _ptr(bias), _ptr(y), _ptr(buf), T, N, K_dim,
-                                   int(group), int(q_bits), x2.stride(0), y.stride(0), _stream()), "wo_gemm_tc")
+    if buf is None or buf.numel() < need:
+        buf = _WO_SCRATCH[x2.device] = torch.empty(max(need, 64 * 32768), dtype=torch.float32, device=x2.device)
+    y32, x16 = buf[:T * N], buf[(T * N + 3) // 4 * 4:]
+    _check(lib().dsb200_wo_gemm_tc(_ptr(x2), _ptr(payload), _ptr(scales), _ptr(bias), _ptr(y), _ptr(y32), _ptr(x16), T, N,
+                                   K_dim, int(group), int(q_bits), x2.stride(0), y.stride(0), _stream()), "wo_gemm_tc")
     return y
 
 
