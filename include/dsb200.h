@@ -260,6 +260,27 @@ int dsb200_ragged_paged_attention(const void* q, const void* kv, void* out, cons
                                   int64_t q_stride, int Hq, int Hkv, int D, int block_size, int max_blocks, int splits,
                                   float scale, cudaStream_t stream);
 
+/* ---- weight-only quantized GEMM for decode (csrc/wo_gemm.cu): y[T, N] = x[T, K] * dequant(Wq[N, K])^T with Wq as
+ * e4m3 bytes (bits 8) or e2m1 nibble pairs (bits 4) + fp32 scales per `group` elements of K ([N, K / group]).
+ * Reference: inference/v2/kernels/core_ops/cuda_linear (FP6-LLM), cutlass_ops/mixed_gemm, csrc/fp_quantizer. ---- */
+/* tcgen05 version, T <= 64, K % 64 == 0, group % 64 == 0; x16: scratch of T*K halves; y32: T*N floats (split-K) */
+int dsb200_wo_gemm_tc(const void* x, const void* wq, const float* scales, const void* bias, void* y, float* y32, void* x16,
+                      int T, int N, int K, int group, int bits, int64_t x_stride, int64_t y_stride, cudaStream_t stream);
+/* SIMT reference version, M <= 8, K % 256 == 0, group % 16 == 0; y32: M*N floats */
+int dsb200_wo_gemv(const void* x, const void* wq, const float* scales, const void* bias, void* y, float* y32, int M,
+                   int N, int K, int group, int bits, int64_t x_stride, int64_t y_stride, cudaStream_t stream);
+/* ---- expert-parallel MoE dispatch / combine over NVLink peer memory (csrc/moe_comm.cu); reference:
+ * module_inject/auto_ep_layer.py:184-350,575-730 (_AllToAllV + permute / unpermute + weighted combine). segs: device
+ * array of nseg {src_rank, src_start, dst_start, n} int32 records sorted by dst_start. ---- */
+int dsb200_moe_dispatch(const uint64_t* peer_x, const uint64_t* peer_idx, const uint64_t* peer_scale,
+                        const uint64_t* peer_flags, int rank, int world, const void* segs, int nseg, int n_rows,
+                        int hidden, void* out, unsigned int* ticket, int ch_ready, int ch_done, unsigned int epoch,
+                        int ctas, cudaStream_t stream);
+int dsb200_moe_combine(const uint64_t* peer_y, const uint64_t* peer_flags, int rank, int world, const int* slot_rank,
+                       const int* slot_row, const float* weights, int T, int k, int hidden, void* out, void* rows_out,
+                       unsigned int* ticket, int ch_ready, int ch_done, unsigned int epoch, int ctas,
+                       cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
