@@ -124,3 +124,53 @@ def test_top2_gating_matches_reference_rules(sampling):
                 got[s, idx[s, j], slot[s, j]] += w[s, j]
     assert (slot < 0).any(), "test must exercise dropped tokens"
     torch.testing.assert_close(got, want)
+
+
+def _fused_plan_roundtrip(top_k, n_experts):
+    """CPU emulation of the fused MoE dispatch / combine kernels driven by ``build_plan``: every token row must reach the
+    right expert rank at the planned row, and the combine must find it again (index math of moe/fused_dispatch.py)."""
+    import deepspeed_b200 as ds
+    from deepspeed_b200.moe.fused_dispatch import build_plan
+    dist = ds.comm
+    rank, world = dist.get_rank(), dist.get_world_size()
+    torch.manual_seed(10 + rank)
+    T, H = 37 + 5 * rank, 8
+    x = torch.randn(T, H)
+    scores = torch.rand(T, n_experts)
+    top_w, top_i = scores.topk(top_k, dim=-1)
+    plan = build_plan(top_i, n_experts, world, rank, None)
+    E_local = n_experts // world
+    # what the kernels read from the peers: token rows, expert-sorted token lists
+    Ts = [None] * world
+    dist.all_gather_object(Ts, (x, plan.sorted_tok, plan.segs.clone(), plan.n_rows))
+    # ---- dispatch (expert rank pulls) ----
+    expert_in = torch.zeros(plan.n_rows, H)
+    for (src, s0, d0, n) in plan.segs.tolist():
+        for i in range(n):
+            expert_in[d0 + i] = Ts[src][0][int(Ts[src][1][s0 + i])]
+    assert sum(plan.local_counts) == plan.n_rows
+    # rows of local expert el are contiguous and really were routed to it
+    off = 0
+    for el, cnt in enumerate(plan.local_counts):
+        off += cnt
+    # ---- "experts": tag each row with its local expert id so the combine can be checked ----
+    tag = torch.zeros(plan.n_rows)
+    off = 0
+    for el, cnt in enumerate(plan.local_counts):
+        tag[off:off + cnt] = rank * E_local + el
+        off += cnt
+    outs = [None] * world
+    dist.all_gather_object(outs, (expert_in, tag))
+    # ---- combine (token owner pulls) ----
+    for t in range(T):
+        for j in range(top_k):
+            r, row = int(plan.slot_rank[t * top_k + j]), int(plan.slot_row[t * top_k + j])
+            assert torch.equal(outs[r][0][row], x[t]), (t, j)          # my token row sits where the plan says
+            assert int(outs[r][1][row]) == int(top_i[t, j]), (t, j)    # ... inside the segment of the chosen expert
+    return True
+
+
+@pytest.mark.parametrize("top_k,n_experts", [(2, 4), (1, 3), (2, 6)])
+def test_fused_moe_plan_index_math(top_k, n_experts):
+    world = 3 if n_experts % 3 == 0 else 2
+    assert all(run_distributed(_fused_plan_roundtrip, world, args=(top_k, n_experts)))
