@@ -257,9 +257,17 @@ class GatheredParameters:
         if not self.enabled:
             return False
         with torch.no_grad():
+            written = []
             for u in self._units:
                 z = _zopt_of(u)
                 if self.modifier_rank is not None and u.full_param is not None:
+                    if z is not None and z not in written:
+                        # the shards are about to change under the peers' copy-engine gathers: wait for their reads,
+                        # publish the new contents afterwards (ZeroShardedOptimizer._lp_shards_*)
+                        if hasattr(z, "_join_step"):
+                            z._join_step()
+                        z._lp_shards_will_be_written()
+                        written.append(z)
                     if u.world > 1:
                         src = dist.get_global_rank(u.dp_group, self.modifier_rank)
                         dist.broadcast(u.full_param, src, group=u.dp_group)
@@ -273,6 +281,8 @@ class GatheredParameters:
                 if z is not None and z.coordinator is not None and not u.persistent \
                         and not self._was_gathered.get(u.uid, False):
                     z.coordinator.release(u)
+            for z in written:
+                z._lp_shards_written()
             for p in self.params:
                 if hasattr(p, "ds_init_shard") and not hasattr(p, "ds_unit"):
                     if self.modifier_rank is not None:
