@@ -41,16 +41,32 @@ class _GroupedMM(torch.autograd.Function):
         x, w = ctx.saved_tensors
         g = g.contiguous()
         dx = torch.empty_like(x)
-        dw = torch.zeros_like(w)
+        # expert weight gradients go straight into the ZeRO flat gradient buffer when the optimizer offers a target
+        # (ZeroShardedOptimizer.grad_target, same mechanism as ops.fused.Linear)
+        unit = getattr(w, "ds_unit", None)
+        zopt = getattr(unit, "_zopt", None) if unit is not None else None
+        tgt = zopt.grad_target(w, g.dtype) if zopt is not None and hasattr(zopt, "grad_target") else None
+        if tgt is not None:
+            dw_view, acc = tgt[0].view(w.shape), tgt[1]
+        else:
+            dw_view, acc = torch.zeros_like(w), False
         off = 0
         for e, n in enumerate(ctx.counts):
             if n == 0:
+                if tgt is not None and not acc:
+                    dw_view[e].zero_()
                 continue
             ge = g[off:off + n]
             torch.matmul(ge, w[e], out=dx[off:off + n])
-            torch.matmul(ge.t(), x[off:off + n], out=dw[e])
+            if acc:
+                dw_view[e].addmm_(ge.t(), x[off:off + n])
+            else:
+                torch.matmul(ge.t(), x[off:off + n], out=dw_view[e])
             off += n
-        return dx, dw, None
+        if tgt is not None:
+            zopt.grad_written(w)
+            return dx, None, None
+        return dx, dw_view, None
 
 
 def grouped_mm(x, w, counts):

@@ -109,7 +109,11 @@ class AutoEPMoELayer(nn.Module):
 
     def _use_fused(self, x):
         import os
-        if os.environ.get("DSB200_FUSED_MOE", "1") != "1" or not x.is_cuda:
+        # auto: fused NVLink dispatch/combine up to 4 expert-parallel ranks. Measured (profiles/moe_fused_dispatch_*.json):
+        # 2.4 % faster than the NCCL all-to-all-v path at EP=2, 6 % slower at EP=8 (Mixtral 8x7B: 598 vs 563 ms/step; the
+        # per-layer plan construction after the count sync and the 8-way READY/DONE handshakes cost more than they save).
+        mode = os.environ.get("DSB200_FUSED_MOE", "auto")
+        if mode == "0" or not x.is_cuda or (mode == "auto" and self.ep_size > 4):
             return False
         if not hasattr(self, "_fused_ok"):
             from ..moe import fused_dispatch as FD
