@@ -197,6 +197,9 @@ class _LinearFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight):
         ctx.save_for_backward(x, weight)
+        # the parameter OBJECT (for the ZeRO bookkeeping): under non-reentrant activation checkpointing the saved tensors
+        # come back as detached aliases without the parameter's attributes
+        ctx.weight_param = weight
         return F.linear(x, weight)
 
     @staticmethod
@@ -207,6 +210,7 @@ class _LinearFn(torch.autograd.Function):
             dx = torch.matmul(dy, weight)
         if ctx.needs_input_grad[1]:
             dy2, x2 = dy.reshape(-1, dy.shape[-1]), x.reshape(-1, x.shape[-1])
+            weight = ctx.weight_param
             unit = getattr(weight, "ds_unit", None)
             zopt = getattr(unit, "_zopt", None) if unit is not None else None
             tgt = zopt.grad_target(weight, dy2.dtype) if zopt is not None and hasattr(zopt, "grad_target") else None
@@ -224,7 +228,7 @@ class _LinearFn(torch.autograd.Function):
 
 
 def linear(x, weight, bias=None):
-    if bias is None and x.is_cuda and weight.requires_grad and torch.is_grad_enabled() \
+    if bias is None and weight.requires_grad and torch.is_grad_enabled() \
             and getattr(weight, "ds_unit", None) is not None:
         return _LinearFn.apply(x, weight)
     return F.linear(x, weight, bias)

@@ -20,6 +20,7 @@ class _GroupedMM(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, counts):
         ctx.counts = counts
+        ctx.w_param = w  # parameter object for the ZeRO bookkeeping (saved tensors may come back as detached aliases)
         ctx.save_for_backward(x, w)
         N = w.shape[1]
         out = x.new_empty(x.shape[0], N)
@@ -43,9 +44,10 @@ class _GroupedMM(torch.autograd.Function):
         dx = torch.empty_like(x)
         # expert weight gradients go straight into the ZeRO flat gradient buffer when the optimizer offers a target
         # (ZeroShardedOptimizer.grad_target, same mechanism as ops.fused.Linear)
-        unit = getattr(w, "ds_unit", None)
+        wp = ctx.w_param
+        unit = getattr(wp, "ds_unit", None)
         zopt = getattr(unit, "_zopt", None) if unit is not None else None
-        tgt = zopt.grad_target(w, g.dtype) if zopt is not None and hasattr(zopt, "grad_target") else None
+        tgt = zopt.grad_target(wp, g.dtype) if zopt is not None and hasattr(zopt, "grad_target") else None
         if tgt is not None:
             dw_view, acc = tgt[0].view(w.shape), tgt[1]
         else:
@@ -64,7 +66,7 @@ class _GroupedMM(torch.autograd.Function):
                 torch.matmul(ge.t(), x[off:off + n], out=dw_view[e])
             off += n
         if tgt is not None:
-            zopt.grad_written(w)
+            zopt.grad_written(wp)
             return dx, None, None
         return dx, dw_view, None
 

@@ -77,3 +77,47 @@ def test_zero_bf16_tracks_fp32(stage):
     # both ranks agree exactly on the master weights
     for n in full:
         torch.testing.assert_close(outs[0][1][n], outs[1][1][n], rtol=0, atol=0)
+
+
+def _llama_direct_wgrad(stage, direct):
+    """Tiny Llama under ZeRO (gloo, fp32): weight gradients written straight into the flat gradient buffers
+    (ops.fused.Linear + ZeroShardedOptimizer.grad_target) vs the grad-hook copy path."""
+    import deepspeed_b200 as ds
+    from deepspeed_b200.models import LlamaConfig, LlamaForCausalLM
+    torch.manual_seed(0)
+    cfg = LlamaConfig(vocab_size=128, hidden_size=32, intermediate_size=64, num_hidden_layers=2, num_attention_heads=4,
+                      num_key_value_heads=2, max_position_embeddings=64, dtype=torch.float32)
+    model = LlamaForCausalLM(cfg)
+    eng, _, _, _ = ds.initialize(model=model, config={
+        "train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 2, "gradient_clipping": 1.0,
+        "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}},
+        "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 10, "unit_max_numel": 6000,
+                              "reduce_bucket_size": 5000}})
+    eng.optimizer._direct_wgrad = direct
+    calls = {"n": 0}
+    orig = eng.optimizer.grad_written
+
+    def counted(p):
+        calls["n"] += 1
+        return orig(p)
+
+    eng.optimizer.grad_written = counted
+    torch.manual_seed(1 + ds.comm.get_rank())
+    losses = []
+    for _ in range(6):
+        ids = torch.randint(0, 128, (2, 16))
+        loss = eng(ids, labels=ids)
+        eng.backward(loss)
+        eng.step()
+        losses.append(float(loss.detach()))
+    return losses, calls["n"]
+
+
+@pytest.mark.parametrize("stage", [1, 2, 3])
+def test_direct_weight_gradients_match_hook_path(stage):
+    a = run_distributed(_llama_direct_wgrad, 2, args=(stage, True))
+    b = run_distributed(_llama_direct_wgrad, 2, args=(stage, False))
+    (la, na), (lb, nb) = a[0], b[0]
+    assert na > 0 and nb == 0, (na, nb)   # the direct path really ran (and only when enabled)
+    for x, y in zip(la, lb):
+        assert abs(x - y) < 1e-5, (la, lb)
