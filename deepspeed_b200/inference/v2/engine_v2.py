@@ -15,7 +15,7 @@ import torch.nn.functional as F
 
 from ...ops import fused
 from ...ops import kernels as K
-from .ragged import BlockedKVCache, DSStateManager, RaggedBatchWrapper
+from .ragged import BlockedKVCache, DSStateManager, NativeRaggedState, RaggedBatchWrapper
 
 
 class RaggedInferenceEngineConfig:
@@ -42,31 +42,46 @@ class InferenceEngineV2:
                                             self.config.max_ragged_sequence_count)
         self.batch = RaggedBatchWrapper()
         self._meta = None
+        # C++ host runtime (allocator + sequence table + batch descriptors) whenever the native kernels serve this model
+        self.native_state = None
+        probe = torch.empty(0, dtype=self.dtype, device=self.device)
+        if self._native(probe, c.num_attention_heads, c.num_key_value_heads, c.head_dim):
+            try:
+                self.native_state = NativeRaggedState(self.config.num_kv_blocks, self.config.kv_block_size,
+                                                      self.config.max_tracked_sequences,
+                                                      self.config.max_ragged_batch_size,
+                                                      self.config.max_ragged_sequence_count)
+            except Exception:  # noqa: BLE001 - host library unavailable: Python bookkeeping
+                self.native_state = None
         self.generic = hasattr(model, "forward_tokens")  # model_implementations.GenericDecoder (any HF family)
         if not self.generic:
             self.cos, self.sin = fused.rope_tables(c.max_position_embeddings, c.head_dim, c.rope_theta, self.device,
                                                    c.rope_scaling)
 
     @property
+    def _sm(self):
+        return self.native_state if self.native_state is not None else self.state_manager
+
+    @property
     def free_blocks(self):
-        return self.state_manager.free_blocks
+        return self._sm.free_blocks
 
     def query(self, uid, max_request_tokens, max_request_blocks=None):
-        return self.state_manager.query(uid, max_request_tokens)
+        return self._sm.query(uid, max_request_tokens)
 
     def can_schedule(self, uids, lengths):
         total_blocks = 0
         if sum(lengths) > self.config.max_ragged_batch_size or len(uids) > self.config.max_ragged_sequence_count:
             return False
         for uid, n in zip(uids, lengths):
-            ok, need = self.state_manager.query(uid, n)
+            ok, need = self._sm.query(uid, n)
             if ok == 0:
                 return False
             total_blocks += need
         return total_blocks <= self.free_blocks
 
     def flush(self, uid):
-        self.state_manager.flush_sequence(uid)
+        self._sm.flush_sequence(uid)
 
     @torch.no_grad()
     def put(self, batch_uids, batch_tokens, do_checks=True):
@@ -74,6 +89,31 @@ class InferenceEngineV2:
         if do_checks and not self.can_schedule(batch_uids, [len(t) for t in batch_tokens]):
             raise RuntimeError("ragged batch cannot be scheduled (KV blocks / batch limits)")
         self.batch.clear()
+        if self.native_state is not None:
+            # one C++ call builds every descriptor of this forward; one pinned copy ships them
+            toks = [torch.as_tensor(t, dtype=torch.long) for t in batch_tokens]
+            lens = [int(t.numel()) for t in toks]
+            pmin = self.PREFILL_MIN_TOKENS if self.config.kv_block_size == 128 else (1 << 30)
+            dmax = 1 if self.config.kv_block_size == 128 else 0  # decode class only with 128-token blocks
+            meta = self.native_state.schedule(batch_uids, lens, pmin, self.device)
+            if dmax == 0 and meta["decode"] is not None:  # fold single-token sequences into the SIMT group
+                meta["decode"] = None
+                meta["rest"] = None
+            for grp in ("prefill", "decode"):
+                if meta[grp] is not None:
+                    meta[grp]["table"] = meta["table"].index_select(0, meta[grp]["seq_rows"].long()).contiguous()
+            if meta["decode"] is not None:
+                meta["decode"]["rows"] = meta["decode"]["rows"].long()
+            if meta["prefill"] is None and meta["decode"] is None:
+                meta["rest"] = None  # everything goes through the SIMT kernel with the whole-batch arrays
+            self._meta = meta
+            ids = torch.cat(toks).to(self.device, non_blocking=True)
+            ends, acc = [], 0
+            for n in lens:
+                acc += n
+                ends.append(acc - 1)
+            last = torch.tensor(ends, device=self.device)
+            return self._forward(ids, meta["tok_pos"].long(), last)
         for uid, toks in zip(batch_uids, batch_tokens):
             seq = self.state_manager.get_or_create_sequence(uid)
             toks = torch.as_tensor(toks, dtype=torch.long)
@@ -82,7 +122,9 @@ class InferenceEngineV2:
             self.batch.insert_sequence(seq, toks)
         ids = self.batch.finalize(self.device)
         self._meta = None
-        logits = self._forward(ids)
+        pos = torch.cat([torch.arange(seen, seen + n, device=self.device) for (_, _, n, seen) in self.batch.seq_meta])
+        last = torch.tensor([s + n - 1 for (_, s, n, _) in self.batch.seq_meta], device=self.device)
+        logits = self._forward(ids, pos, last)
         for seq, _, _, _ in self.batch.seq_meta:
             seq.post_forward()
         return logits
@@ -178,18 +220,14 @@ class InferenceEngineV2:
             outs.append(o[0].transpose(0, 1).reshape(n, -1))
         return torch.cat(outs, 0)
 
-    def _forward(self, ids):
+    def _forward(self, ids, pos, last):
         m = self.model
         if self.generic:
-            pos = torch.cat([torch.arange(seen, seen + n, device=self.device)
-                             for (_, _, n, seen) in self.batch.seq_meta])
             h = m.forward_tokens(ids, pos, self._attend)
-            last = torch.tensor([s + n - 1 for (_, s, n, _) in self.batch.seq_meta], device=self.device)
             return m.lm_head(h.index_select(0, last))
         inner = getattr(m, "model", m)
         layers = inner.layers
         h = inner.embed_tokens(ids)  # [T, H]
-        pos = torch.cat([torch.arange(seen, seen + n, device=self.device) for (_, _, n, seen) in self.batch.seq_meta])
         nh, nkv, hd = self.cfg.num_attention_heads, self.cfg.num_key_value_heads, self.cfg.head_dim
         for li, layer in enumerate(layers):
             x = layer.input_layernorm(h)
@@ -225,7 +263,6 @@ class InferenceEngineV2:
             ffn = layer.mlp if hasattr(layer, "mlp") else layer.block_sparse_moe
             h = h + ffn(x2.unsqueeze(0))[0] if not hasattr(layer, "mlp") else h + ffn(x2)
         h = inner.norm(h)
-        last = torch.tensor([s + n - 1 for (_, s, n, _) in self.batch.seq_meta], device=self.device)
         head = m.lm_head
         return head(h.index_select(0, last))
 

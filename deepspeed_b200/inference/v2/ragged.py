@@ -176,3 +176,89 @@ class RaggedBatchWrapper:
     @property
     def current_sequences(self):
         return len(self.seq_meta)
+
+
+class NativeRaggedState:
+    """Blocked-KV allocator + sequence table + batch descriptor builder in C++ (``csrc/cpu/ragged_host.cpp``): one call
+    per forward produces every integer array the ragged kernels consume, in one pinned buffer -> one host-to-device copy.
+    Reference: ``ragged/manager.py`` + ``ragged_wrapper.py`` + ``ragged/csrc/fast_host_buffer.cu`` +
+    ``kernels/ragged_ops/atom_builder``."""
+
+    def __init__(self, num_blocks, block_size, max_tracked_sequences=2048, max_tokens=768, max_sequences=512,
+                 max_blocks_per_seq=None):
+        import ctypes
+        from ...ops import cpu_lib
+        self.L = cpu_lib.lib()
+        if not hasattr(self.L, "dsb200_ragged_create"):
+            raise RuntimeError("libdsb200_cpu.so was built without the ragged host runtime")
+        self.h = ctypes.c_void_p(self.L.dsb200_ragged_create(num_blocks, block_size, max_tracked_sequences))
+        self.block_size, self.num_blocks = block_size, num_blocks
+        width = max_blocks_per_seq or num_blocks
+        self.cap = 5 * max_tokens + max_sequences * (width + 8) + 64
+        self.buf = torch.empty(self.cap, dtype=torch.int32)
+        if torch.cuda.is_available():
+            self.buf = self.buf.pin_memory()
+        self.header = torch.zeros(16, dtype=torch.int32)
+        self._ct = ctypes
+
+    def __del__(self):
+        try:
+            self.L.dsb200_ragged_destroy(self.h)
+        except Exception:  # noqa: BLE001
+            pass
+
+    @property
+    def free_blocks(self):
+        return int(self.L.dsb200_ragged_free_blocks(self.h))
+
+    @property
+    def n_tracked_sequences(self):
+        return int(self.L.dsb200_ragged_tracked(self.h))
+
+    def seen_tokens(self, uid):
+        return int(self.L.dsb200_ragged_seen(self.h, int(uid)))
+
+    def query(self, uid, new_tokens):
+        need = int(self.L.dsb200_ragged_blocks_needed(self.h, int(uid), int(new_tokens)))
+        return (new_tokens if need <= self.free_blocks else 0), need
+
+    def blocks(self, uid):
+        out = torch.empty(self.num_blocks, dtype=torch.int32)
+        n = int(self.L.dsb200_ragged_blocks(self.h, int(uid), self._ct.c_void_p(out.data_ptr()), out.numel()))
+        return out[:max(n, 0)].tolist()
+
+    def flush_sequence(self, uid):
+        rc = int(self.L.dsb200_ragged_flush(self.h, int(uid)))
+        if rc != 0:
+            raise ValueError(f"KV block bookkeeping corrupted while flushing sequence {uid} (code {rc})")
+
+    def schedule(self, uids, lengths, prefill_min_tokens, device, commit=True):
+        """-> dict of int32 device tensors + host scalars describing this forward (see ragged_host.cpp)."""
+        n = len(uids)
+        u = torch.tensor([int(x) for x in uids], dtype=torch.int64)
+        ln = torch.tensor([int(x) for x in lengths], dtype=torch.int32)
+        P = self._ct.c_void_p
+        rc = int(self.L.dsb200_ragged_schedule(self.h, n, P(u.data_ptr()), P(ln.data_ptr()), int(prefill_min_tokens),
+                                               P(self.buf.data_ptr()), self.cap, P(self.header.data_ptr()),
+                                               1 if commit else 0))
+        if rc == -1:
+            raise ValueError("Not enough free blocks in the KV-cache for this ragged batch")
+        if rc == -2:
+            raise RuntimeError("too many tracked sequences")
+        if rc == -3:
+            raise RuntimeError("ragged batch larger than the descriptor buffer (raise max_ragged_batch_size)")
+        hd = self.header.tolist()
+        T, n_seq, width, n_p, max_q, n_d, ctx_d, T_r, ctx_r, max_ctx, o_p, o_d, o_r, total = hd[:14]
+        dev = self.buf[:total].to(device, non_blocking=True)
+        meta = dict(T=T, tok_seq=dev[:T], tok_pos=dev[T:2 * T], table=dev[2 * T:2 * T + n_seq * width].view(n_seq, width),
+                    max_ctx=max_ctx, prefill=None, decode=None, rest=None)
+        if n_p:
+            pf = dev[o_p:o_p + 4 * n_p].view(4, n_p)
+            meta["prefill"] = dict(cu_q=pf[0], q_len=pf[1], kv_len=pf[2], seq_rows=pf[3], max_q=max_q)
+        if n_d:
+            dc = dev[o_d:o_d + 3 * n_d].view(3, n_d)
+            meta["decode"] = dict(rows=dc[0], kv_len=dc[1], seq_rows=dc[2], max_ctx=ctx_d, all=(n_d == n_seq and T == n_d))
+        if T_r:
+            rs = dev[o_r:o_r + 3 * T_r].view(3, T_r)
+            meta["rest"] = dict(rows=rs[0], seq=rs[1], pos=rs[2], max_ctx=ctx_r)
+        return meta

@@ -31,6 +31,24 @@ def lib():
                 L.dsb200_cpu_sumsq.argtypes = [P, L64]
                 L.dsb200_cpu_sumsq.restype = ctypes.c_double
                 L.dsb200_cpu_num_threads.restype = I
+                if hasattr(L, "dsb200_ragged_create"):
+                    L.dsb200_ragged_create.argtypes = [I, I, I]
+                    L.dsb200_ragged_create.restype = P
+                    L.dsb200_ragged_destroy.argtypes = [P]
+                    L.dsb200_ragged_free_blocks.argtypes = [P]
+                    L.dsb200_ragged_free_blocks.restype = I
+                    L.dsb200_ragged_tracked.argtypes = [P]
+                    L.dsb200_ragged_tracked.restype = I
+                    L.dsb200_ragged_seen.argtypes = [P, L64]
+                    L.dsb200_ragged_seen.restype = L64
+                    L.dsb200_ragged_blocks_needed.argtypes = [P, L64, I]
+                    L.dsb200_ragged_blocks_needed.restype = I
+                    L.dsb200_ragged_blocks.argtypes = [P, L64, P, I]
+                    L.dsb200_ragged_blocks.restype = I
+                    L.dsb200_ragged_flush.argtypes = [P, L64]
+                    L.dsb200_ragged_flush.restype = I
+                    L.dsb200_ragged_schedule.argtypes = [P, I, P, P, I, P, L64, P, I]
+                    L.dsb200_ragged_schedule.restype = I
                 L.dsb200_aio_create.argtypes = [L64, I, I, I]
                 L.dsb200_aio_create.restype = P
                 L.dsb200_aio_destroy.argtypes = [P]

@@ -281,6 +281,21 @@ int dsb200_moe_combine(const uint64_t* peer_y, const uint64_t* peer_flags, int r
                        unsigned int* ticket, int ch_ready, int ch_done, unsigned int epoch, int ctas,
                        cudaStream_t stream);
 
+/* ---- libdsb200_cpu.so: FastGen host runtime (csrc/cpu/ragged_host.cpp): blocked-KV allocator, sequence table and
+ * the per-forward batch descriptor builder; reference: inference/v2/ragged/{blocked_allocator,manager,ragged_wrapper}.py,
+ * ragged/csrc/fast_host_buffer.cu, kernels/ragged_ops/atom_builder ---- */
+void* dsb200_ragged_create(int num_blocks, int block_size, int max_tracked_sequences);
+void dsb200_ragged_destroy(void* h);
+int dsb200_ragged_free_blocks(void* h);
+int dsb200_ragged_tracked(void* h);
+int64_t dsb200_ragged_seen(void* h, int64_t uid);
+int dsb200_ragged_blocks_needed(void* h, int64_t uid, int new_tokens);
+int dsb200_ragged_blocks(void* h, int64_t uid, int* out, int cap);
+int dsb200_ragged_flush(void* h, int64_t uid);
+/* buf layout and header fields: see ragged_host.cpp; 0 ok, -1 out of KV blocks, -2 too many sequences, -3 buffer small */
+int dsb200_ragged_schedule(void* h, int n_seq, const int64_t* uids, const int* n_tokens, int prefill_min, int* buf,
+                           int64_t cap, int* header, int commit);
+
 #ifdef __cplusplus
 }
 #endif

@@ -50,3 +50,59 @@ def test_init_inference_wrapper_and_generate():
     with torch.no_grad():
         nxt = model(ids)[:, -1].argmax(-1)
     assert torch.equal(out[:, 5], nxt)
+
+
+def test_native_ragged_state_matches_python_bookkeeping():
+    """C++ host runtime (csrc/cpu/ragged_host.cpp) vs the Python allocator / batch wrapper: same block tables, token
+    descriptors and free-block accounting over a prefill + decode + flush scenario."""
+    import random
+    from deepspeed_b200.inference.v2.ragged import (BlockedKVCache, DSStateManager, NativeRaggedState,
+                                                    RaggedBatchWrapper)
+    bs, nb = 4, 40
+    nat = NativeRaggedState(nb, bs, max_tokens=256, max_sequences=16)
+    py = DSStateManager(BlockedKVCache(1, nb, bs, 1, 8, torch.float32, "cpu"))
+    rng = random.Random(0)
+    live = []
+    for step in range(12):
+        uids, lens = [], []
+        for uid in list(live):
+            if rng.random() < 0.7:
+                uids.append(uid)
+                lens.append(1 if rng.random() < 0.6 else rng.randint(2, 5))
+        if step % 3 == 0:
+            uids.append(100 + step)
+            lens.append(rng.randint(5, 11))
+            live.append(100 + step)
+        if not uids:
+            continue
+        meta = nat.schedule(uids, lens, prefill_min_tokens=6, device=torch.device("cpu"))
+        batch = RaggedBatchWrapper()
+        for uid, n in zip(uids, lens):
+            seq = py.get_or_create_sequence(uid)
+            py.ensure_capacity(seq, n)
+            seq.pre_forward(n)
+            batch.insert_sequence(seq, torch.zeros(n, dtype=torch.long))
+        tok_seq, tok_pos, table = batch.device_metadata(torch.device("cpu"))
+        assert meta["tok_seq"].tolist() == tok_seq.tolist() and meta["tok_pos"].tolist() == tok_pos.tolist()
+        # block tables agree up to the (equal) free-list order: compare block COUNTS and ownership disjointness
+        for row, (seq, _, _, _) in enumerate(batch.seq_meta):
+            got = [b for b in meta["table"][row].tolist()[:len(seq.blocks)]]
+            assert len(got) == len(seq.blocks) == len(nat.blocks(seq.uid))
+        for seq, _, _, _ in batch.seq_meta:
+            seq.post_forward()
+        assert nat.free_blocks == py.free_blocks
+        n_p = sum(1 for n in lens if n >= 6)
+        n_d = sum(1 for n in lens if n == 1)
+        assert (meta["prefill"] is None) == (n_p == 0) and (meta["decode"] is None) == (n_d == 0)
+        if meta["decode"] is not None:
+            assert meta["decode"]["kv_len"].tolist() == [nat.seen_tokens(u) for u, n in zip(uids, lens) if n == 1]
+        if step % 4 == 3 and live:
+            gone = live.pop(0)
+            nat.flush_sequence(gone)
+            py.flush_sequence(gone)
+            assert nat.free_blocks == py.free_blocks and nat.n_tracked_sequences == py.n_tracked_sequences
+    all_blocks = [b for u in live for b in nat.blocks(u)]
+    assert len(all_blocks) == len(set(all_blocks)) == nb - nat.free_blocks
+    with pytest.raises(ValueError):
+        nat.schedule([999], [bs * nb + 1], 6, torch.device("cpu"))
+    assert nat.n_tracked_sequences == len(live)  # a refused batch changes nothing
