@@ -291,6 +291,8 @@ class DeepSpeedEngine(Module):
                                   or self._config.fp16_master_weights_and_gradients),
             offload_optimizer=zc.offload_optimizer, offload_param=zc.offload_param, unit_max_numel=zc.unit_max_numel,
             param_persistence_threshold=zc.param_persistence_threshold, prefetch=zc.prefetch_bucket_size > 0,
+            prefetch_bucket_size=zc.prefetch_bucket_size, max_live_parameters=zc.max_live_parameters,
+            max_reuse_distance=zc.max_reuse_distance,
             mics_shard_size=zc.mics_shard_size, hpz_size=zc.zero_hpz_partition_size,
             quantized_weights=zc.zero_quantized_weights, quantized_gradients=zc.zero_quantized_gradients,
             leaf_modules=self._leaf_module_classes(), elastic_checkpoint=zc.elastic_checkpoint, timers=self.timers,

@@ -19,9 +19,16 @@ from .units import FlatUnit
 
 class UnitCoordinator:
 
-    def __init__(self, zopt, prefetch=True):
+    def __init__(self, zopt, prefetch=True, prefetch_bucket_size=None, max_live_parameters=None,
+                 max_reuse_distance=None):
         self.z = zopt
         self.prefetch = prefetch
+        # reference knobs (partitioned_param_coordinator.py:73-690): elements that may be gathered ahead of use, cap on
+        # gathered elements alive at once, and "do not release what is needed again within this many elements"
+        self.prefetch_bucket_size = int(prefetch_bucket_size) if prefetch_bucket_size else 0
+        self.max_live_parameters = int(max_live_parameters) if max_live_parameters else 0
+        self.max_reuse_distance = int(max_reuse_distance) if max_reuse_distance else 0
+        self.gathers_launched = 0  # statistics (tests, tuning)
         self.handles = []
         self.fwd_order = []  # unit ids in first-forward order
         self._trace_done = False
@@ -86,6 +93,7 @@ class UnitCoordinator:
         """Launch (if needed) and optionally complete the all-gather of a unit's parameters."""
         z = self.z
         if not u.gathered and u.gather_work is None:
+            self.gathers_launched += 1
             use_side = z._use_streams and z.overlap_comm
             src = u.param_shard
             group = u.dp_group
@@ -198,11 +206,45 @@ class UnitCoordinator:
             self.gather(u, wait=False)
         if self.prefetch and self._trace_done and need and not self._in_backward_pass:
             pos = max(self._fwd_pos.get(u.uid, -1) for u in need) + 1
-            if 0 <= pos < len(self.fwd_order):
-                self.gather(self.z.units[self.fwd_order[pos]], wait=False)
+            self._prefetch_from(pos, +1)
         for u in need:
             self.gather(u, wait=True)
         return None
+
+    def _live_numel(self):
+        return sum(u.numel_padded for u in self.z.units if not u.persistent and (u.gathered or u.gather_work))
+
+    def _prefetch_from(self, pos, step):
+        """Launch gathers of the units that follow in execution order (``step`` +1 forward, -1 backward): always the
+        next one, further ones while the elements in flight stay within ``stage3_prefetch_bucket_size`` and the live
+        elements within ``stage3_max_live_parameters``."""
+        budget, first = self.prefetch_bucket_size, True
+        while 0 <= pos < len(self.fwd_order):
+            nxt = self.z.units[self.fwd_order[pos]]
+            if step < 0 and nxt.reduced_this_pass:
+                break
+            if not (nxt.gathered or nxt.gather_work):
+                if not first:
+                    if nxt.numel_padded > budget:
+                        break
+                    if self.max_live_parameters and self._live_numel() + nxt.numel_padded > self.max_live_parameters:
+                        break
+                self.gather(nxt, wait=False)
+                budget -= nxt.numel_padded
+            first = False
+            pos += step
+
+    def _keep_for_backward(self, u):
+        """Forward is done with ``u``: skip the release when its backward use is closer than
+        ``stage3_max_reuse_distance`` elements away (the units after it run forward and backward in between) and the
+        live set stays under ``stage3_max_live_parameters`` (reference ``__params_to_release``)."""
+        if not (self.max_reuse_distance and self._trace_done and torch.is_grad_enabled()) or u.uid not in self._fwd_pos:
+            return False
+        pos = self._fwd_pos[u.uid]
+        dist = 2 * sum(self.z.units[uid].numel_padded for uid in self.fwd_order[pos + 1:])
+        if dist > self.max_reuse_distance:
+            return False
+        return not self.max_live_parameters or self._live_numel() <= self.max_live_parameters
 
     def _post_forward(self, module, args, output):
         need = self._needed_units(module)
@@ -212,6 +254,8 @@ class UnitCoordinator:
         if not self._in_backward_pass:
             for u in need:
                 if self._still_needed_by_parent(module, u):
+                    continue
+                if grad_mode and self._keep_for_backward(u):
                     continue
                 self.release(u)
         return None
@@ -245,10 +289,7 @@ class UnitCoordinator:
             self.gather(u, wait=False)
         if self.prefetch and need:
             pos = min(self._fwd_pos.get(u.uid, 1 << 30) for u in need) - 1
-            if 0 <= pos < len(self.fwd_order):
-                nxt = self.z.units[self.fwd_order[pos]]
-                if not nxt.reduced_this_pass:
-                    self.gather(nxt, wait=False)
+            self._prefetch_from(pos, -1)
         for u in need:
             self.gather(u, wait=True)
 

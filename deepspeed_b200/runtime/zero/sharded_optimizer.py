@@ -74,7 +74,8 @@ class ZeroShardedOptimizer:
                  unit_max_numel=int(1e9), param_persistence_threshold=int(1e5), prefetch=True, mics_shard_size=-1,
                  hpz_size=1, quantized_weights=False, quantized_gradients=False, expert_groups=None,
                  leaf_modules=(), elastic_checkpoint=False, timers=None, fused_collectives=None,
-                 ignore_unused_parameters=True, fused_rs_adam=None, aio_config=None, zenflow=None):
+                 ignore_unused_parameters=True, fused_rs_adam=None, aio_config=None, zenflow=None,
+                 prefetch_bucket_size=None, max_live_parameters=None, max_reuse_distance=None):
         self.module = module
         self.optimizer = optimizer
         self.stage = int(stage)
@@ -230,7 +231,9 @@ class ZeroShardedOptimizer:
         self.coordinator = None
         if self.partition_params:
             from .coordinator import UnitCoordinator
-            self.coordinator = UnitCoordinator(self, prefetch=prefetch)
+            self.coordinator = UnitCoordinator(self, prefetch=prefetch, prefetch_bucket_size=prefetch_bucket_size,
+                                               max_live_parameters=max_live_parameters,
+                                               max_reuse_distance=max_reuse_distance)
         log_dist(
             f"ZeRO stage {self.stage}: {len(self.units)} units, shard_world={self._shard_world}, "
             f"replica_world={self._replica_world}, lp={self.lp_dtype}, master={self.master_dtype}, "

@@ -121,3 +121,41 @@ def test_direct_weight_gradients_match_hook_path(stage):
     assert na > 0 and nb == 0, (na, nb)   # the direct path really ran (and only when enabled)
     for x, y in zip(la, lb):
         assert abs(x - y) < 1e-5, (la, lb)
+
+
+def _coordinator_knobs(reuse, bucket):
+    """ZeRO-3 coordinator knobs: stage3_max_reuse_distance keeps the last units gathered from forward into backward,
+    stage3_prefetch_bucket_size bounds how far ahead gathers are launched."""
+    import deepspeed_b200 as ds
+    torch.manual_seed(0)
+    model = SimpleModel(16, 6)
+    eng, _, _, _ = ds.initialize(model=model, config={
+        "train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}},
+        "zero_optimization": {"stage": 3, "unit_max_numel": 300, "stage3_param_persistence_threshold": 0,
+                              "stage3_max_reuse_distance": reuse, "stage3_prefetch_bucket_size": bucket,
+                              "stage3_max_live_parameters": 10**9}})
+    co = eng.optimizer.coordinator
+    batches = random_batches(8, 4, 16, "cpu")
+    losses, per_step = [], []
+    for i in range(4):
+        g0 = co.gathers_launched
+        x, y = batches[2 * i + ds.comm.get_rank()]
+        loss = eng(x, y)
+        eng.backward(loss)
+        eng.step()
+        losses.append(float(loss.detach()))
+        per_step.append(co.gathers_launched - g0)
+    n_units = len([u for u in eng.optimizer.units if not u.persistent])
+    return losses, per_step, n_units
+
+
+def test_zero3_reuse_distance_and_prefetch_bucket():
+    base = run_distributed(_coordinator_knobs, 2, args=(0, 1))[0]
+    keep = run_distributed(_coordinator_knobs, 2, args=(10**9, 10**9))[0]
+    some = run_distributed(_coordinator_knobs, 2, args=(700, 1))[0]
+    n = base[2]
+    assert base[1][-1] == 2 * n                       # every unit gathered for forward and again for backward
+    assert keep[1][-1] == n                           # everything within reuse distance: one gather per step
+    assert n < some[1][-1] < 2 * n                    # only the last units stay gathered
+    for a, b, c in zip(base[0], keep[0], some[0]):    # scheduling does not change the math
+        assert abs(a - b) < 1e-6 and abs(a - c) < 1e-6
