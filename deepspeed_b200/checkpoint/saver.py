@@ -522,6 +522,8 @@ def _load_zero_state(engine, zsd, load_optimizer_states, load_from_fp32=True):
                     z.optimizer.state[v][k] = val
         if hasattr(z.optimizer, "on_state_loaded"):
             z.optimizer.on_state_loaded()
+    if getattr(z, "coordinator", None) is not None:
+        z.coordinator.release_all()  # units a plan keeps gathered hold pre-load contents
 
 
 def _state_dtype(z, v):

@@ -393,7 +393,9 @@ class CheckpointConfig(DeepSpeedConfigModel):
 class CompileConfig(DeepSpeedConfigModel):
     deepcompile: bool = False
     free_activation: bool = False
+    free_activation_threshold: int = 10 * 1024 * 1024
     offload_activation: bool = False
+    offload_activation_pin_memory: bool = True
     offload_opt_states: bool = False
     double_buffer: bool = True
     symmetric_memory: bool = False
@@ -405,6 +407,7 @@ class CompileConfig(DeepSpeedConfigModel):
     sync_after_allgather: bool = False
     keep_int_input_tensors: bool = True
     keep_all_input_tensors: bool = False
+    passes: Optional[List[str]] = None
     model_config = dict(DeepSpeedConfigModel.model_config, extra="allow")
 
 

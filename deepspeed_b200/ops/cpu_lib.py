@@ -49,6 +49,12 @@ def lib():
                     L.dsb200_ragged_flush.restype = I
                     L.dsb200_ragged_schedule.argtypes = [P, I, P, P, I, P, L64, P, I]
                     L.dsb200_ragged_schedule.restype = I
+                if hasattr(L, "dsb200_dc_plan"):
+                    D = ctypes.c_double
+                    L.dsb200_dc_fit_comm.argtypes = [I, P, P, P]
+                    L.dsb200_dc_fit_comm.restype = I
+                    L.dsb200_dc_plan.argtypes = [I, P, P, I, P, P, P, D, D, L64, L64, L64, D, D, P, P, P, P]
+                    L.dsb200_dc_plan.restype = I
                 L.dsb200_aio_create.argtypes = [L64, I, I, I]
                 L.dsb200_aio_create.restype = P
                 L.dsb200_aio_destroy.argtypes = [P]

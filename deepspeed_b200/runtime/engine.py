@@ -879,6 +879,8 @@ class DeepSpeedEngine(Module):
             if self.eigenvalue is not None and self.global_steps % self.eigenvalue.gas_boundary_resolution == 0:
                 self.block_eigenvalue = self.eigenvalue.compute_eigenvalue(self.module, self.device)
             self._take_model_step(lr_kwargs)
+            if getattr(self, "_dc_driver", None) is not None:
+                self._dc_driver.tick()
         self.tput_timer.stop(global_step=boundary)
         for t in self.engine_timers.step_timers:
             self.timers(t).stop()
@@ -931,8 +933,22 @@ class DeepSpeedEngine(Module):
         self.optimizer.reload_states(non_blocking=non_blocking)
 
     def compile(self, backend=None, compile_kwargs=None, schedule=None, compiled_autograd_enabled=False):
-        """No tracing compiler on the hot path by design: kept as a passthrough for API compatibility."""
-        log_dist("engine.compile(): passthrough (B200 path uses hand-written kernels + CUDA graphs)", [0])
+        """Reference ``engine.compile`` (``runtime/engine.py:5706``). No tracing compiler sits on the hot path here; with
+        ``compile.deepcompile`` the ZeRO scheduling the reference obtains from graph passes is installed instead:
+        stage 3 profiles a step at unit granularity and follows the native planner's gather schedule
+        (``compile/backend.py::UnitScheduleDriver``), stages 1/2 apply the state-offload passes of ``schedule``."""
+        if self.is_compiled:
+            return
+        cc = self._config.compile_config
+        if getattr(cc, "deepcompile", False) and self.optimizer is not None and hasattr(self.optimizer, "units"):
+            from ..compile import backend as dc
+            if self.zero_optimization_stage() >= 3:
+                dc.init_z3(self, backend="eager", compile_config=cc, compile_kwargs=compile_kwargs, schedule=schedule)
+            else:
+                dc.init_z1(self, backend="eager", compile_config=cc, compile_kwargs=compile_kwargs, schedule=schedule,
+                           use_z2=self.zero_optimization_stage() == 2)
+        else:
+            log_dist("engine.compile(): hand-written kernels + CUDA graphs are the compiled path; nothing to trace", [0])
         self._is_compiled = True
 
     @property

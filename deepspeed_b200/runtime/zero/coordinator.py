@@ -29,6 +29,8 @@ class UnitCoordinator:
         self.max_live_parameters = int(max_live_parameters) if max_live_parameters else 0
         self.max_reuse_distance = int(max_reuse_distance) if max_reuse_distance else 0
         self.gathers_launched = 0  # statistics (tests, tuning)
+        self._plan = None  # profile-guided schedule (compile/planner.py); None = the heuristics below
+        self._prof = None  # active UnitProfiler (compile/profiler.py)
         self.handles = []
         self.fwd_order = []  # unit ids in first-forward order
         self._trace_done = False
@@ -109,17 +111,24 @@ class UnitCoordinator:
                 u.full_param = src
                 u.gather_work = True
                 use_side = None
+            prof = self._prof if use_side is not None else None
             if use_side is None:
                 pass
             elif use_side:
                 with torch.cuda.stream(z.ag_stream):
                     full = torch.empty(u.numel_padded, dtype=u.dtype, device=u.device)
+                    tok = prof.gather_begin(u, z.ag_stream) if prof is not None else None
                     self._launch_gather(u, full, src, group)
+                    if prof is not None:
+                        prof.gather_end(tok, z.ag_stream)
                     u.gather_event = torch.cuda.Event()
                     u.gather_event.record(z.ag_stream)
             else:
                 full = torch.empty(u.numel_padded, dtype=u.dtype, device=u.device)
+                tok = prof.gather_begin(u, None) if prof is not None else None
                 self._launch_gather(u, full, src, group)
+                if prof is not None:
+                    prof.gather_end(tok, None)
             if use_side is not None:
                 u.full_param = full
                 u.gather_work = True
@@ -189,9 +198,11 @@ class UnitCoordinator:
         r = dist.get_rank(z._hpz_group)
         u.sec_shard = u.full_param[r * n:(r + 1) * n].clone()
 
-    def release(self, u: FlatUnit):
+    def release(self, u: FlatUnit, force=False):
         if u.persistent or not (u.gathered or u.gather_work):
             return
+        if getattr(u, "resident", False) and not force:
+            return  # planned to stay gathered until the optimizer step rewrites the shards (on_step_done)
         if u.gather_work and not u.gathered:
             self.gather(u, wait=True)
         self.z._release_params(u)
@@ -204,12 +215,38 @@ class UnitCoordinator:
                 self._fwd_pos[u.uid] = len(self.fwd_order)
                 self.fwd_order.append(u.uid)
             self.gather(u, wait=False)
+        if self._prof is not None and need and not self._in_backward_pass:
+            self._prof.step_begin("fwd", need)
         if self.prefetch and self._trace_done and need and not self._in_backward_pass:
-            pos = max(self._fwd_pos.get(u.uid, -1) for u in need) + 1
-            self._prefetch_from(pos, +1)
+            if self._plan is not None:
+                self._launch_planned([self._fwd_pos.get(u.uid, -1) for u in need])
+            else:
+                pos = max(self._fwd_pos.get(u.uid, -1) for u in need) + 1
+                self._prefetch_from(pos, +1)
         for u in need:
             self.gather(u, wait=True)
         return None
+
+    # ---- profile-guided plan (DeepCompile counterpart, compile/planner.py) -----------------------
+    def set_plan(self, plan):
+        """``plan``: :class:`compile.planner.UnitPlan` over the timeline [forward positions, backward positions] of
+        ``fwd_order``, or None to go back to the heuristics. Resident units stay gathered across micro-steps."""
+        for u in self.z.units:
+            u.resident = False
+        self._plan = plan
+        if plan is not None:
+            for uid in plan.resident:
+                self.z.units[uid].resident = True
+
+    def _launch_planned(self, steps):
+        n = len(self.fwd_order)
+        for s in steps:
+            for t in self._plan.launch_at.get(s, ()):
+                pos = t if t < n else 2 * n - 1 - t
+                u = self.z.units[self.fwd_order[pos]]
+                if t >= n and u.reduced_this_pass:
+                    continue
+                self.gather(u, wait=False)
 
     def _live_numel(self):
         return sum(u.numel_padded for u in self.z.units if not u.persistent and (u.gathered or u.gather_work))
@@ -238,6 +275,8 @@ class UnitCoordinator:
         """Forward is done with ``u``: skip the release when its backward use is closer than
         ``stage3_max_reuse_distance`` elements away (the units after it run forward and backward in between) and the
         live set stays under ``stage3_max_live_parameters`` (reference ``__params_to_release``)."""
+        if self._plan is not None and self._trace_done and u.uid in self._fwd_pos:
+            return torch.is_grad_enabled() and self._fwd_pos[u.uid] in self._plan.keep
         if not (self.max_reuse_distance and self._trace_done and torch.is_grad_enabled()) or u.uid not in self._fwd_pos:
             return False
         pos = self._fwd_pos[u.uid]
@@ -287,7 +326,12 @@ class UnitCoordinator:
         need = self._needed_units(module)
         for u in need:
             self.gather(u, wait=False)
-        if self.prefetch and need:
+        if self._prof is not None and need:
+            self._prof.step_begin("bwd", need)
+        if self.prefetch and need and self._plan is not None and self._trace_done:
+            n = len(self.fwd_order)
+            self._launch_planned([2 * n - 1 - self._fwd_pos[u.uid] for u in need if u.uid in self._fwd_pos])
+        elif self.prefetch and need:
             pos = min(self._fwd_pos.get(u.uid, 1 << 30) for u in need) - 1
             self._prefetch_from(pos, -1)
         for u in need:
@@ -300,6 +344,8 @@ class UnitCoordinator:
 
     def on_backward_end(self):
         self._in_backward_pass = False
+        if self._prof is not None:
+            self._prof.pass_end()
         if self.fwd_order:
             self._trace_done = True
         for u in self.z.units:
@@ -312,11 +358,19 @@ class UnitCoordinator:
             z.ag_stream.wait_stream(torch.cuda.current_stream())  # shards were rewritten by the step
         for u in self.z.units:
             u.sec_shard = None  # hpZ replicas are stale after the update (reference stage3.py:706)
+        if self._plan is not None:
+            # resident units: the gathered copy is stale now; refresh it once per optimizer step (in first-use
+            # order, every rank the same), overlapping whatever runs before the next forward needs them
+            for uid in self.fwd_order:
+                u = self.z.units[uid]
+                if getattr(u, "resident", False) and not u.persistent:
+                    self.release(u, force=True)
+                    self.gather(u, wait=False)
 
     def release_all(self):
         for u in self.z.units:
             if not u.persistent:
-                self.release(u)
+                self.release(u, force=True)
 
     def gather_all(self):
         for u in self.z.units:

@@ -296,6 +296,17 @@ int dsb200_ragged_flush(void* h, int64_t uid);
 int dsb200_ragged_schedule(void* h, int n_seq, const int64_t* uids, const int* n_tokens, int prefill_min, int* buf,
                            int64_t cap, int* header, int commit);
 
+/* ---- ZeRO-3 unit-timeline planner (csrc/cpu/dc_planner.cpp; libdsb200_cpu) -----------------------------------
+ * fit_comm: least squares of us = latency + bytes / bandwidth; out[0] latency_us, out[1] bytes_per_us.
+ * plan: see the comment above dsb200_dc_plan in dc_planner.cpp for every argument; outputs persist_out[n_units],
+ * launch_step[n_steps], keep_after[n_steps], sim[8]. Returns 0, -1 empty input, -2 step_unit out of range. */
+int dsb200_dc_fit_comm(int n, const int64_t* bytes, const double* us, double* out);
+int dsb200_dc_plan(int n_units, const int64_t* unit_bytes, const uint8_t* persistent_in, int n_steps,
+                   const int* step_unit, const double* step_us, const int64_t* step_peak, double latency_us,
+                   double bytes_per_us, int64_t mem_budget, int64_t max_inflight, int64_t persist_headroom,
+                   double reuse_window_us, double safety, uint8_t* persist_out, int* launch_step, int* keep_after,
+                   double* sim);
+
 #ifdef __cplusplus
 }
 #endif

@@ -158,3 +158,40 @@ def test_pipelined_step_matches_single_launch_step():
     assert la == lb, (la, lb)
     for n in pa:
         torch.testing.assert_close(pa[n], pb[n], rtol=0, atol=0)
+
+
+def test_engine_compile_unit_plan_single_gpu():
+    """engine.compile() with compile.deepcompile: profile (CUDA events + allocator peaks) -> native plan -> same losses."""
+    import deepspeed_b200 as ds
+    from deepspeed_b200.models import LlamaConfig, LlamaForCausalLM
+    _env()
+    dev = torch.device("cuda", 0)
+
+    def run(compiled):
+        torch.manual_seed(0)
+        cfg = LlamaConfig(vocab_size=2048, hidden_size=256, intermediate_size=512, num_hidden_layers=4,
+                          num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=256)
+        model = LlamaForCausalLM(cfg, device=dev)
+        eng, _, _, _ = ds.initialize(model=model, config={
+            "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True},
+            "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}},
+            "zero_optimization": {"stage": 3, "unit_max_numel": 700000},
+            "compile": {"deepcompile": compiled}})
+        if compiled:
+            eng.compile()
+        torch.manual_seed(1)
+        losses = []
+        for _ in range(6):
+            ids = torch.randint(0, 2048, (2, 128), device=dev)
+            loss = eng(ids, labels=ids)
+            eng.backward(loss)
+            eng.step()
+            losses.append(float(loss.detach()))
+        if compiled:
+            d = eng._dc_driver
+            assert d.plan is not None and d.profile.total_memory > 0 and min(d.profile.step_us) > 0
+        eng.destroy()
+        return losses
+
+    a, b = run(True), run(False)
+    assert a == b, (a, b)

@@ -154,6 +154,59 @@ def test_slot_pool_with_pending_unit_matches_nccl_path():
     assert la[-1] < la[0]
 
 
+def _train_dc(compiled, steps, headroom):
+    """ZeRO-3 on the fused collectives with the profile-guided unit plan (engine.compile) vs the default heuristics."""
+    import deepspeed_b200 as ds
+    from deepspeed_b200.models import LlamaConfig, LlamaForCausalLM
+    dev = torch.device("cuda", torch.cuda.current_device())
+    torch.manual_seed(0)
+    cfg = LlamaConfig(vocab_size=2048, hidden_size=256, intermediate_size=512, num_hidden_layers=6,
+                      num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=256)
+    model = LlamaForCausalLM(cfg, device=dev)
+    eng, _, _, _ = ds.initialize(model=model, config={
+        "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True}, "gradient_clipping": 1.0,
+        "optimizer": {"type": "AdamW", "params": {"lr": 1e-3, "weight_decay": 0.0}},
+        "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 1000, "fused_collectives": True,
+                              "fused_rs_adam": False, "unit_max_numel": 700000},
+        "compile": {"deepcompile": compiled, "persist_headroom_bytes": headroom}})
+    if compiled:
+        eng.compile()
+    co = eng.optimizer.coordinator
+    torch.manual_seed(1 + ds.comm.get_rank())
+    losses, gathers = [], []
+    for _ in range(steps):
+        g0 = co.gathers_launched
+        ids = torch.randint(0, 2048, (2, 128), device=dev)
+        loss = eng(ids, labels=ids)
+        eng.backward(loss)
+        eng.step()
+        losses.append(float(loss.detach()))
+        gathers.append(co.gathers_launched - g0)
+    info = None
+    if compiled:
+        d = eng._dc_driver
+        assert d.plan is not None and d.profile.total_memory > 0
+        assert all(t > 0 for t in d.profile.step_us) and max(d.profile.step_peak) > 0
+        assert d.profile.comm_bytes_per_us > 0
+        info = (len(d.plan.resident), sorted(d.plan.keep), len(co.fwd_order), d.plan.predicted["feasible"])
+    return losses, gathers, info
+
+
+@needs2
+@pytest.mark.parametrize("headroom", [0, 1 << 30])
+def test_deepcompile_unit_plan_matches_default_schedule(headroom):
+    a = run_distributed(_train_dc, 2, args=(True, 8, headroom))
+    b = run_distributed(_train_dc, 2, args=(False, 8, headroom))
+    for la, lb in zip(a[0][0], b[0][0]):
+        assert abs(la - lb) < 5e-2, (a[0][0], b[0][0])
+    n_res, keep, n, feasible = a[0][2]
+    assert feasible == 1.0 and a[1][2] == a[0][2]
+    if headroom:
+        assert n_res == n and a[0][1][-1] == n  # everything resident: one gather per unit per optimizer step
+    else:
+        assert n_res == 0 and n <= a[0][1][-1] <= 2 * n
+
+
 @needs2
 def test_zero3_fused_collectives_match_nccl_path():
     a = run_distributed(_train, 2, args=(True, 6))
