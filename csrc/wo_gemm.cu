@@ -19,6 +19,10 @@
 #include <cuda_fp4.h>
 #define DSB_HAVE_FP4 1
 #endif
+#if __has_include(<cuda_fp6.h>)
+#include <cuda_fp6.h>
+#define DSB_HAVE_FP6 1
+#endif
 
 namespace {
 
@@ -214,9 +218,9 @@ int dsb200_wo_gemv(const void* x, const void* wq, const float* scales, const voi
 // tcgen05 version: Y[T, N] = X[T, K] * dequant(Wq[N, K])^T for T <= 64 tokens, computed as D = W * X^T so that the
 // (large) weight matrix is the M operand of the MMA and the few tokens are its N extent (16 / 32 / 64).
 //
-//   warp 0      TMA: raw quantized weight tile (128 rows x 64 elements: 8 KB FP8 / 4 KB FP4, unswizzled) and the
+//   warp 0      TMA: raw quantized weight tile (128 rows x 64 elements: 8 KB FP8 / 6 KB FP6 / 4 KB FP4, unswizzled) and the
 //               activation tile (TN tokens x 64, bf16, 128-byte swizzle) of every k-block into a 4-stage ring
-//   warps 6-13  expand: raw codes -> f16 with ONE hardware cvt per two elements (cvt.f16x2.e4m3x2 / .e2m1x2, exact),
+//   warps 6-13  expand: raw codes -> f16 with ONE hardware cvt per two elements (cvt.f16x2.e4m3x2 / .e3m2x2 / .e2m1x2, exact),
 //               written straight into the 128-byte-swizzled K-major layout the tensor core reads; no scale here
 //   warp 1      one lane issues 4 x tcgen05.mma (A = f16 weights, B = activations converted to f16, M128 x N{16,32,64} x K16) per
 //               k-block; each scale group (`group` elements of K) accumulates into its own TMEM buffer (two alternate)
@@ -279,8 +283,8 @@ wo_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_consta
                   const float* __restrict__ scales, float* __restrict__ y32, const __nv_bfloat16* __restrict__ bias,
                   __nv_bfloat16* __restrict__ y, int64_t y_stride, int T, int N, int K, int group, int kb_per_split)
 {
-    constexpr int RAW_BYTES = WT_BM * WT_BK * BITS / 8;  // 8 KB / 4 KB
-    constexpr int WT_STAGES = WT_RING_BYTES / RAW_BYTES;  // 6 / 12
+    constexpr int RAW_BYTES = WT_BM * WT_BK * BITS / 8;  // 8 KB / 6 KB / 4 KB
+    constexpr int WT_STAGES = WT_RING_BYTES / RAW_BYTES;  // 6 / 8 / 12
     constexpr int X_BYTES_MAX = (TN * WT_BK * 2 + 1023) / 1024 * 1024;  // 2 / 4 / 8 KB
     constexpr int A_BYTES_T = WT_BM * WT_BK * 2;         // 16 KB
     extern __shared__ uint8_t smem_raw[];
@@ -406,6 +410,28 @@ wo_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_consta
                         out[2 * w] = *reinterpret_cast<const uint32_t*>(&lo);
                         out[2 * w + 1] = *reinterpret_cast<const uint32_t*>(&hi);
                     }
+                } else if constexpr (BITS == 6) {
+#ifdef DSB_HAVE_FP6
+                    // 16 e3m2 codes = 96 bits (code i at bits [6i, 6i+6) of the row's little-endian bit stream): each
+                    // 12-bit pair is spread to two bytes and converted by one cvt.rn.f16x2.e3m2x2
+                    const uint32_t* rp = reinterpret_cast<const uint32_t*>(raw + row * 48 + c4 * 12);
+                    const uint32_t w0 = rp[0], w1 = rp[1], w2 = rp[2];
+                    const uint32_t pr[8] = {w0,
+                                            w0 >> 12,
+                                            __funnelshift_r(w0, w1, 24),
+                                            w1 >> 4,
+                                            w1 >> 16,
+                                            __funnelshift_r(w1, w2, 28),
+                                            w2 >> 8,
+                                            w2 >> 20};
+#pragma unroll
+                    for (int p = 0; p < 8; p++) {
+                        const uint32_t v = pr[p];
+                        const __half2_raw h2 =
+                            __nv_cvt_fp6x2_to_halfraw2((__nv_fp6x2_storage_t)((v & 0x3F) | ((v & 0xFC0) << 2)), __NV_E3M2);
+                        out[p] = *reinterpret_cast<const uint32_t*>(&h2);
+                    }
+#endif
                 } else {
 #ifdef DSB_HAVE_FP4
                     const uint2 rv = *reinterpret_cast<const uint2*>(raw + row * 32 + c4 * 8);
@@ -522,11 +548,17 @@ int dsb200_wo_gemm_tc(const void* x, const void* wq, const float* scales, const 
                       int T, int N, int K, int group, int bits, int64_t x_stride, int64_t y_stride, cudaStream_t stream)
 {
     if (T <= 0 || N <= 0) return 0;
-    if (T > 64 || K % WT_BK != 0 || group % WT_BK != 0 || K % group != 0 || (bits != 8 && bits != 4) || (x_stride % 8) ||
-        ((uintptr_t)x & 15) || ((uintptr_t)wq & 15)) {
-        dsb200_set_error("wo_gemm_tc: needs T <= 64, K % 64 == 0, group % 64 == 0 dividing K, bits in {4, 8}, aligned operands");
+    if (T > 64 || K % WT_BK != 0 || group % WT_BK != 0 || K % group != 0 || (bits != 8 && bits != 6 && bits != 4) ||
+        (x_stride % 8) || ((uintptr_t)x & 15) || ((uintptr_t)wq & 15)) {
+        dsb200_set_error("wo_gemm_tc: needs T <= 64, K % 64 == 0, group % 64 == 0 dividing K, bits in {4, 6, 8}, aligned operands");
         return -1;
     }
+#ifndef DSB_HAVE_FP6
+    if (bits == 6) {
+        dsb200_set_error("wo_gemm_tc: built without cuda_fp6.h");
+        return -1;
+    }
+#endif
 #ifndef DSB_HAVE_FP4
     if (bits == 4) {
         dsb200_set_error("wo_gemm_tc: built without cuda_fp4.h");
@@ -570,6 +602,9 @@ int dsb200_wo_gemm_tc(const void* x, const void* wq, const float* scales, const 
     do {                       \
         if (bits == 8) {       \
             constexpr int BB = 8; \
+            WT_LAUNCH_(BB, TT); \
+        } else if (bits == 6) { \
+            constexpr int BB = 6; \
             WT_LAUNCH_(BB, TT); \
         } else {               \
             constexpr int BB = 4; \

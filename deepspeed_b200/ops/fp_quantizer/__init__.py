@@ -2,8 +2,10 @@
 minifloat quantization, q_bits in {8: e4m3, 6: e3m2, 4: e2m1, 12: e4m7}, per-group fp32 scale, optional stochastic
 rounding, ``dequantize`` / ``selective_dequantize`` / ``get_scales``.
 
-Storage: 8-bit -> e4m3 bytes (hardware cvt); 4-bit -> two e2m1 codes per byte; 6/12-bit -> the rounded value kept in
-bf16 (bit-packing of 6/12-bit payloads is a storage-only optimisation that the kernels do not need).
+Storage: 8-bit -> e4m3 bytes (hardware cvt); 4-bit -> two e2m1 codes per byte; 6-bit -> four e3m2 codes in three bytes
+(little-endian bit stream: code i occupies bits [6i, 6i+6), the layout ``csrc/wo_gemm.cu`` unpacks in shared memory);
+12-bit -> two e4m7 codes in three bytes. The reference appends each group's fp32 scale to the group's bytes; here
+the scales are a separate tensor.
 """
 import ctypes
 
@@ -14,6 +16,57 @@ from ..quantizer import _lib
 
 _FORMATS = {8: (4, 3, 448.0), 6: (3, 2, 28.0), 4: (2, 1, 6.0), 12: (4, 7, 510.0)}
 _E2M1_VALUES = torch.tensor([0.0, 0.5, 1.0, 1.5, 2.0, 3.0, 4.0, 6.0])
+
+
+def encode_minifloat(vals, eb, mb):
+    """Exactly representable values -> sign/exponent/mantissa codes (uint8 for <= 8 bits, int16 otherwise).
+    No inf/nan encodings (e3m2 / e2m1 / e4m7 use every exponent for finite values)."""
+    bias = (1 << (eb - 1)) - 1
+    a = vals.float().abs()
+    _, ex = torch.frexp(a)  # a = m * 2^ex, m in [0.5, 1)
+    e_unb = (ex - 1).clamp(min=1 - bias)
+    e_unb = torch.where(a > 0, e_unb, torch.full_like(e_unb, 1 - bias))
+    frac = a * torch.pow(2.0, -e_unb.float())  # [0, 2): >= 1 normal, < 1 subnormal
+    normal = frac >= 1.0
+    e_field = torch.where(normal, e_unb + bias, torch.zeros_like(e_unb))
+    m_field = torch.round(torch.where(normal, frac - 1.0, frac) * (1 << mb)).to(torch.int32)
+    code = (e_field.to(torch.int32) << mb) | m_field
+    code = code | ((vals < 0).to(torch.int32) << (eb + mb))
+    return code.to(torch.uint8 if eb + mb + 1 <= 8 else torch.int16)
+
+
+def decode_minifloat(code, eb, mb):
+    bias = (1 << (eb - 1)) - 1
+    c = code.to(torch.int32)
+    m = (c & ((1 << mb) - 1)).float() / (1 << mb)
+    e = (c >> mb) & ((1 << eb) - 1)
+    mag = torch.where(e > 0, (1.0 + m) * torch.pow(2.0, (e - bias).float()), m * (2.0**(1 - bias)))
+    return torch.where(((c >> (eb + mb)) & 1) > 0, -mag, mag)
+
+
+def pack_6bit(code):
+    """uint8 codes (6 significant bits), numel % 4 == 0 -> 3 bytes per 4 codes."""
+    c = code.view(-1, 4).to(torch.int32)
+    w = c[:, 0] | (c[:, 1] << 6) | (c[:, 2] << 12) | (c[:, 3] << 18)
+    return torch.stack([w & 0xFF, (w >> 8) & 0xFF, (w >> 16) & 0xFF], dim=1).to(torch.uint8).view(-1)
+
+
+def unpack_6bit(packed):
+    b = packed.view(-1, 3).to(torch.int32)
+    w = b[:, 0] | (b[:, 1] << 8) | (b[:, 2] << 16)
+    return torch.stack([w & 0x3F, (w >> 6) & 0x3F, (w >> 12) & 0x3F, (w >> 18) & 0x3F], dim=1).to(torch.uint8).view(-1)
+
+
+def pack_12bit(code):
+    c = code.view(-1, 2).to(torch.int32) & 0xFFF
+    w = c[:, 0] | (c[:, 1] << 12)
+    return torch.stack([w & 0xFF, (w >> 8) & 0xFF, (w >> 16) & 0xFF], dim=1).to(torch.uint8).view(-1)
+
+
+def unpack_12bit(packed):
+    b = packed.view(-1, 3).to(torch.int32)
+    w = b[:, 0] | (b[:, 1] << 8) | (b[:, 2] << 16)
+    return torch.stack([w & 0xFFF, (w >> 12) & 0xFFF], dim=1).to(torch.int16).view(-1)
 
 
 class Quantizer:
@@ -74,8 +127,12 @@ class FP_Quantize(Quantizer):
             idx = torch.bucketize(vals.abs(), (table[:-1] + table[1:]) / 2).to(torch.uint8)
             code = idx | ((vals < 0).to(torch.uint8) << 3)
             payload = code[0::2] | (code[1::2] << 4)
+        elif q_bits == 6:
+            assert vals.numel() % 4 == 0, "6-bit packing needs numel % 4 == 0"
+            payload = pack_6bit(encode_minifloat(vals, 3, 2))
         else:
-            payload = vals.to(torch.bfloat16)
+            assert vals.numel() % 2 == 0, "12-bit packing needs an even numel"
+            payload = pack_12bit(encode_minifloat(vals, 4, 7))
         if return_meta_tensor:
             return payload, scale
         return _QTensor(payload, scale, q_bits, self.group_size, input.shape, input.dtype)
@@ -89,7 +146,11 @@ class FP_Quantize(Quantizer):
             codes = torch.stack([lo, hi], dim=1).view(-1)
             vals = table[(codes & 7).long()]
             return torch.where((codes & 8) > 0, -vals, vals)
-        return payload.float()
+        if payload.dtype != torch.uint8:  # payloads of older checkpoints: rounded values kept in bf16
+            return payload.float()
+        if q_bits == 6:
+            return decode_minifloat(unpack_6bit(payload), 3, 2)
+        return decode_minifloat(unpack_12bit(payload), 4, 7)
 
     def dequantize(self, input_q, fp_out=None, q_bits=8, q_mantisa_bits=3, scale=None):
         if isinstance(input_q, _QTensor):

@@ -492,7 +492,7 @@ def wo_gemv_supported(x2, payload, group, q_bits, K_dim):
 
 def wo_gemm_supported(x2, payload, group, q_bits, K_dim):
     """Shapes the tcgen05 weight-only GEMM serves: up to 64 tokens."""
-    return (available() and x2.is_cuda and x2.dtype == torch.bfloat16 and 0 < x2.shape[0] <= 64 and q_bits in (4, 8)
+    return (available() and x2.is_cuda and x2.dtype == torch.bfloat16 and 0 < x2.shape[0] <= 64 and q_bits in (4, 6, 8)
             and payload.dtype == torch.uint8 and K_dim % 64 == 0 and group % 64 == 0 and K_dim % group == 0
             and x2.stride(1) == 1 and x2.stride(0) % 8 == 0 and x2.data_ptr() % 16 == 0 and payload.data_ptr() % 16 == 0
             and (K_dim * q_bits // 8) % 16 == 0)

@@ -60,3 +60,34 @@ def test_fp_selective_dequantize():
     sel = fq.selective_dequantize(qt, torch.tensor([2, 0]))
     full = fq.dequantize(qt)
     torch.testing.assert_close(sel, full[[2, 0]])
+
+
+@pytest.mark.parametrize("eb,mb,fmax", [(3, 2, 28.0), (2, 1, 6.0), (4, 7, 510.0)])
+def test_minifloat_codes_roundtrip_exhaustively(eb, mb, fmax):
+    from deepspeed_b200.ops.fp_quantizer import decode_minifloat, encode_minifloat
+    n = 1 << (eb + mb + 1)
+    codes = torch.arange(n, dtype=torch.int32)
+    vals = decode_minifloat(codes, eb, mb)
+    assert vals.abs().max().item() == fmax
+    back = encode_minifloat(vals, eb, mb).to(torch.int32) & (n - 1)
+    assert bool(((back == codes) | (vals == 0)).all())  # -0 is stored as +0
+
+
+def test_fp6_and_fp12_payloads_are_bit_packed():
+    """6-bit: four e3m2 codes in three bytes, code i at bits [6i, 6i+6) (the layout csrc/wo_gemm.cu unpacks)."""
+    from deepspeed_b200.ops.fp_quantizer import FP_Quantize, pack_6bit, unpack_6bit, pack_12bit, unpack_12bit
+    codes = torch.tensor([0x01, 0x3F, 0x2A, 0x15], dtype=torch.uint8)
+    packed = pack_6bit(codes)
+    word = 0x01 | (0x3F << 6) | (0x2A << 12) | (0x15 << 18)
+    assert packed.tolist() == [word & 0xFF, (word >> 8) & 0xFF, (word >> 16) & 0xFF]
+    assert unpack_6bit(packed).tolist() == codes.tolist()
+    c12 = torch.tensor([0xABC, 0x123], dtype=torch.int16)
+    assert unpack_12bit(pack_12bit(c12)).tolist() == c12.tolist()
+    x = torch.randn(16, 256, dtype=torch.bfloat16)
+    for bits, tol in ((6, 0.13), (12, 0.004)):
+        fq = FP_Quantize(group_size=128)
+        q = fq.quantize(x, q_bits=bits)
+        assert q.payload.dtype == torch.uint8 and q.payload.numel() == x.numel() * bits // 8
+        y = fq.dequantize(q)
+        rel = ((y.float() - x.float()).abs().amax() / x.float().abs().amax()).item()
+        assert rel < tol, (bits, rel)

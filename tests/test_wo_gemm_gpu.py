@@ -26,7 +26,7 @@ def test_wo_gemv_matches_dequant_matmul(q_bits, M, N, K, group):
     assert err <= 2e-2 * max(1.0, want.abs().max().item()), err
 
 
-@pytest.mark.parametrize("q_bits", [8, 4])
+@pytest.mark.parametrize("q_bits", [8, 6, 4])
 @pytest.mark.parametrize("T,N,K,group", [(1, 512, 1024, 256), (5, 1000, 4096, 512), (16, 200, 14336, 512),
                                          (33, 4096, 4096, 128), (64, 640, 2048, 64), (7, 384, 1536, 1536)])
 def test_wo_gemm_tcgen05_matches_dequant_matmul(q_bits, T, N, K, group):
