@@ -253,6 +253,17 @@ def all_reduce(tensor, op=ReduceOp.SUM, group=None, async_op=False):
 
 @timed_op
 def inference_all_reduce(tensor, op=ReduceOp.SUM, group=None):
+    """Reference ``comm/torch.py:186``: CPU tensors of a single-host job go through the shared-memory all-reduce
+    (``comm/shm.py``, ``csrc/cpu/shm_comm.cpp``); everything else is a plain all-reduce."""
+    if is_initialized() and op == ReduceOp.SUM and group is None and tensor.device.type == "cpu":
+        from .shm import shm_all_reduce
+        if shm_all_reduce(tensor):
+            return None
+    if not tensor.is_contiguous():  # the backends reduce a contiguous buffer: go through one and copy back
+        buf = tensor.contiguous()
+        all_reduce.__wrapped__(buf, op=op, group=group)
+        tensor.copy_(buf)
+        return None
     return all_reduce.__wrapped__(tensor, op=op, group=group)
 
 

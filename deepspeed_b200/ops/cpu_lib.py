@@ -55,6 +55,12 @@ def lib():
                     L.dsb200_dc_fit_comm.restype = I
                     L.dsb200_dc_plan.argtypes = [I, P, P, I, P, P, P, D, D, L64, L64, L64, D, D, P, P, P, P]
                     L.dsb200_dc_plan.restype = I
+                if hasattr(L, "dsb200_shm_create"):
+                    L.dsb200_shm_create.argtypes = [ctypes.c_char_p, I, I, L64, I, ctypes.c_double]
+                    L.dsb200_shm_create.restype = P
+                    L.dsb200_shm_destroy.argtypes = [P]
+                    L.dsb200_shm_all_reduce.argtypes = [P, P, L64, I]
+                    L.dsb200_shm_all_reduce.restype = I
                 L.dsb200_aio_create.argtypes = [L64, I, I, I]
                 L.dsb200_aio_create.restype = P
                 L.dsb200_aio_destroy.argtypes = [P]

@@ -296,6 +296,13 @@ int dsb200_ragged_flush(void* h, int64_t uid);
 int dsb200_ragged_schedule(void* h, int n_seq, const int64_t* uids, const int* n_tokens, int prefill_min, int* buf,
                            int64_t cap, int* header, int commit);
 
+/* ---- shared-memory all-reduce between the ranks of one host (csrc/cpu/shm_comm.cpp; libdsb200_cpu) ---------------
+ * create: rank 0 passes create != 0 first, the others attach afterwards (order them with a barrier); buf_bytes is the
+ * chunk capacity. all_reduce: in-place sum, dtype 0 fp32 / 1 bf16 / 2 fp16; 0 ok, -1 bad argument, -2 peer timeout. */
+void* dsb200_shm_create(const char* name, int rank, int world, int64_t buf_bytes, int create, double timeout_s);
+void dsb200_shm_destroy(void* h);
+int dsb200_shm_all_reduce(void* h, void* data, int64_t numel, int dtype);
+
 /* ---- ZeRO-3 unit-timeline planner (csrc/cpu/dc_planner.cpp; libdsb200_cpu) -----------------------------------
  * fit_comm: least squares of us = latency + bytes / bandwidth; out[0] latency_us, out[1] bytes_per_us.
  * plan: see the comment above dsb200_dc_plan in dc_planner.cpp for every argument; outputs persist_out[n_units],
