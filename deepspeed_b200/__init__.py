@@ -22,11 +22,14 @@ from .runtime import lr_schedules
 from .runtime.lr_schedules import add_tuning_arguments
 from .utils import groups, logging
 from .utils.logging import log_dist, logger
-from .version import __version__
+from .version import __version__, __reference_api__ as _reference_api
 
 __version_major__, __version_minor__, __version_patch__ = (int(x) for x in __version__.split(".")[:3])
 __git_hash__ = None
 __git_branch__ = None
+git_hash, git_branch = __git_hash__, __git_branch__
+version = __version__
+TORCH_DISTRIBUTED_DEFAULT_PORT = 29500
 _TP_MODEL_INIT_ARGS = None
 
 
@@ -59,6 +62,26 @@ def __getattr__(name):
         return _lazy("runtime.hybrid_engine").DeepSpeedHybridEngine
     if name == "get_accelerator":
         return _lazy("accelerator").get_accelerator
+    late = {
+        "OnDevice": ("utils.init_on_device", "OnDevice"),
+        "DeepSpeedDataLoader": ("runtime.dataloader", "DeepSpeedDataLoader"),
+        "DeepSpeedInferenceConfig": ("inference.config", "DeepSpeedInferenceConfig"),
+        "DeepSpeedOptimizer": ("runtime.base_optimizer", "DeepSpeedOptimizer"),
+        "replace_transformer_layer": ("parallel.replace_module", "replace_transformer_layer"),
+        "revert_transformer_layer": ("parallel.replace_module", "revert_transformer_layer"),
+        "set_autotp_mode": ("parallel.layers", "set_autotp_mode"),
+        "is_compile_supported": ("runtime.compiler", "is_compile_supported"),
+        "ADAM_OPTIMIZER": ("config.config", "ADAM_OPTIMIZER"),
+        "LAMB_OPTIMIZER": ("config.config", "LAMB_OPTIMIZER"),
+        "MUON_OPTIMIZER": ("config.config", "MUON_OPTIMIZER"),
+    }
+    if name in late:
+        mod, attr = late[name]
+        return getattr(_lazy(mod), attr)
+    if name == "domino":
+        return _lazy("runtime.domino")
+    if name == "constants":
+        return _lazy("constants")
     raise AttributeError(f"module {__name__!r} has no attribute {name!r}")
 
 
@@ -76,7 +99,7 @@ def initialize(args=None,
                mesh_param=None,
                config_params=None):
     """Build the engine. Returns ``(engine, optimizer, training_dataloader, lr_scheduler)``."""
-    log_dist(f"DeepSpeed-B200 info: version={__version__} (reference API {__import__(__name__).version.__reference_api__})",
+    log_dist(f"DeepSpeed-B200 info: version={__version__} (reference API {_reference_api})",
              ranks=[0])
     assert model is not None, "deepspeed.initialize requires a model"
     zero.shutdown_init_context()
@@ -99,9 +122,7 @@ def initialize(args=None,
             cfg_dict.setdefault("sequence_parallel_size", mesh_param[1])
         elif "sequence_parallel_size" in cfg_dict and "data_parallel_size" in cfg_dict:
             cfg_dict.setdefault("sequence_parallel_size", cfg_dict["sequence_parallel_size"])
-        if _TP_MODEL_INIT_ARGS is not None:
-            tp = cfg_dict.setdefault("tensor_parallel", {})
-            tp.setdefault("autotp_size", _TP_MODEL_INIT_ARGS["tp_size"])
+        merge_tp_model_init_into_config(cfg_dict, mpu, mesh_param, dist)
         config_class = DeepSpeedConfig(cfg_dict, mpu, mesh_device)
         from .runtime.pipe.module import PipelineModule
         if isinstance(model, PipelineModule):
@@ -180,6 +201,36 @@ def tp_model_init(model, tp_size, dtype, config=None, **kwargs):
     apply_autotp(model, TPTrainingConfig(autotp_size=tp_size, dtype=dtype), groups._get_model_parallel_group())
     model.ds_autotp_parsed = True
     return model
+
+
+def merge_tp_model_init_into_config(config_dict, mpu, mesh_param, dist_module):
+    """Fold the arguments recorded by :func:`tp_model_init` into the ``tensor_parallel`` section; conflicting values
+    raise (reference ``runtime/tensor_parallel/init_utils.py:79``)."""
+    if _TP_MODEL_INIT_ARGS is None:
+        return
+    tp_size, dtype = _TP_MODEL_INIT_ARGS["tp_size"], _TP_MODEL_INIT_ARGS.get("dtype")
+    tp_group = _TP_MODEL_INIT_ARGS.get("tp_group")
+    if tp_group is not None and mpu is not None:
+        raise ValueError("tp_model_init provided tp_group; deepspeed.initialize must not receive mpu.")
+    section = config_dict.setdefault("tensor_parallel", {})
+    have = section.get("autotp_size")
+    if have is not None and have != tp_size:
+        raise ValueError(f"Conflicting tensor_parallel.autotp_size in config ({have}) and tp_model_init ({tp_size}).")
+    section["autotp_size"] = tp_size
+    inner = section.get("tp") or {}
+    if not isinstance(inner, dict):
+        raise ValueError("tensor_parallel.tp must be a dict when provided.")
+    if inner.get("tp_size") not in (None, tp_size):
+        raise ValueError(f"Conflicting tensor_parallel.tp.tp_size in config ({inner['tp_size']}) and tp_model_init "
+                         f"({tp_size}).")
+    inner["tp_size"] = tp_size
+    if tp_group is not None:
+        if inner.get("tp_group") not in (None, tp_group):
+            raise ValueError("Conflicting tensor_parallel.tp.tp_group in config and tp_model_init.")
+        inner["tp_group"] = tp_group
+    section["tp"] = inner
+    if dtype is not None and "dtype" not in section:
+        section["dtype"] = str(dtype).replace("torch.", "")
 
 
 def set_optimizer_flags(config_class, model):

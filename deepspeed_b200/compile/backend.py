@@ -44,6 +44,17 @@ def _apply_passes(engine, compile_config, schedule):
     return did
 
 
+_CUSTOM_PASSES = {}  # name -> fn(profile, plan) -> plan | None
+
+
+def register_compile_pass(pass_name, pass_fn, contract=None):
+    """Reference ``compile/passes/__init__.py:register_compile_pass``. Here a pass edits the :class:`UnitPlan` that the
+    built-in planner produced (launch points, kept units, resident units) given the :class:`UnitProfile`."""
+    if not callable(pass_fn):
+        raise TypeError("pass_fn must be callable: pass_fn(profile, plan) -> plan or None")
+    _CUSTOM_PASSES[pass_name] = pass_fn
+
+
 class UnitScheduleDriver:
     """Profile -> plan -> execute loop of the ZeRO-3 unit executor (the reference's ``launch_compile_passes`` schedule,
     ``compile/backend.py:200-280``, at unit granularity): the first optimizer step traces the unit order, the next
@@ -63,6 +74,7 @@ class UnitScheduleDriver:
         self.profiler = UnitProfiler(self.coord)
         self.plan = None
         self.profile = None
+        self.pass_times = {}
         self._seen = 0
 
     def tick(self):
@@ -77,14 +89,26 @@ class UnitScheduleDriver:
         self._seen += 1
         if self._seen < self.profile_steps:
             return
+        import time
         from .planner import plan_units
         c._prof = None
+        t0 = time.perf_counter()
         self.profile = self.profiler.result()
+        t1 = time.perf_counter()
         self.plan = plan_units(self.profile, mem_margin=self.mem_margin, max_inflight=self.max_inflight,
                                persist="selective_gather" in self.passes, persist_headroom=self.persist_headroom)
         if "prefetch" not in self.passes:
             self.plan.launch_at = {}
             self.plan.keep = set()
+        self.pass_times = {"profile": t1 - t0, "plan": time.perf_counter() - t1}
+        for name in self.passes:
+            fn = _CUSTOM_PASSES.get(name)
+            if fn is not None:
+                t2 = time.perf_counter()
+                out = fn(self.profile, self.plan)
+                if out is not None:
+                    self.plan = out
+                self.pass_times[name] = time.perf_counter() - t2
         c.set_plan(self.plan)
         pr = self.plan.predicted
         log_dist(f"DeepCompile(z3): unit plan installed: {len(self.plan.resident)} resident units "
@@ -107,7 +131,7 @@ def init_z3(engine, backend="inductor", compile_config=None, compile_kwargs=None
     did = _apply_passes(engine, compile_config, [(0, n, {}) for n in names if n.startswith("offload")])
     coord = getattr(engine.optimizer, "coordinator", None)
     if coord is not None:
-        unit_passes = [n for n in names if n in ("prefetch", "selective_gather")]
+        unit_passes = [n for n in names if n in ("prefetch", "selective_gather") or n in _CUSTOM_PASSES]
         extra = lambda k, d: getattr(compile_config, k, d) if compile_config is not None else d  # noqa: E731
         engine._dc_driver = UnitScheduleDriver(engine, passes=unit_passes, profile_steps=extra("profile_steps", 2),
                                                mem_margin=extra("mem_margin", 0.1),

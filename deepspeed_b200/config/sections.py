@@ -80,10 +80,38 @@ class ZenFlowConfig(DeepSpeedConfigModel):
     pt_reserved_cores_perc: float = Field(0.5, ge=0.0, le=1.0)
 
 
+DEFAULT_LEAF_MODULE_CLASSES = [
+    "transformers.models.mixtral.modeling_mixtral.MixtralSparseMoeBlock",
+    "transformers.models.qwen2_moe.modeling_qwen2_moe.Qwen2MoeSparseMoeBlock",
+    "transformers.models.qwen3_moe.modeling_qwen3_moe.Qwen3MoeSparseMoeBlock",
+]
+
+
 class DeepSpeedZeroLeafModuleConfig(DeepSpeedConfigModel):
-    classes: List[str] = Field(default_factory=list)
+    """``zero_optimization.leaf_module`` (reference ``runtime/zero/leaf_module_config.py``): HF sparse-MoE blocks are
+    leaves by default; a bare string is accepted for each list; duplicates are dropped."""
+    classes: List[str] = Field(default_factory=lambda: list(DEFAULT_LEAF_MODULE_CLASSES))
     names: List[str] = Field(default_factory=list)
     name_suffixes: List[str] = Field(default_factory=list)
+
+    @model_validator(mode="before")
+    @classmethod
+    def _coerce(cls, values):
+        if values is None:
+            return {}
+        if not isinstance(values, dict):
+            raise TypeError("leaf_module configuration must be a mapping of fields to values")
+        out = dict(values)
+        for key in ("classes", "names", "name_suffixes"):
+            if isinstance(out.get(key), str):
+                out[key] = [out[key]]
+        return out
+
+    @model_validator(mode="after")
+    def _dedupe(self):
+        for key in ("classes", "names", "name_suffixes"):
+            object.__setattr__(self, key, list(dict.fromkeys(str(v) for v in getattr(self, key))))
+        return self
 
 
 class DeepSpeedZeroConfig(DeepSpeedConfigModel):

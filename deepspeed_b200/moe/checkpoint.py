@@ -59,3 +59,42 @@ def load_moe_experts(engine, load_dir, tag, module_sd):
             sd = engine.checkpoint_engine.load(path, map_location="cpu")
             for k, v in sd.items():
                 module_sd[k.replace(f"{prefix}{global_id}.", f"{prefix}{local_id}.")] = v
+
+
+def load_expert_files(checkpoint_path, tag, state_dict, model=None, mpu=None, num_experts=1, old_moe_load=False):
+    """Static form used by ``DeepSpeedEngine.load_moe_state_dict`` (reference ``engine.py:3994``): merge the files of
+    this rank's experts into ``state_dict``, renaming global expert ids to local ones. ``old_moe_load`` reads the
+    layer-agnostic legacy names (``layer_id`` -1 in the reference's naming)."""
+    from .layer import MoE
+    from .saver_names import expert_ckpt_name
+    mp_rank = 0 if mpu is None else mpu.get_model_parallel_rank()
+    if old_moe_load:
+        gname = groups._get_max_expert_size_name()
+        ep_rank = groups._get_expert_data_parallel_rank(gname)
+        n_exp = max(num_experts) if isinstance(num_experts, (list, tuple)) else int(num_experts)
+        n_local = n_exp // groups._get_expert_parallel_world_size(gname)
+        marker = ".deepspeed_moe.experts.deepspeed_experts."
+        for local_id in range(n_local):
+            global_id = ep_rank * n_local + local_id
+            sd = torch.load(expert_ckpt_name(checkpoint_path, -1, global_id, tag, mp_rank), map_location="cpu",
+                            weights_only=False)
+            for k, v in sd.items():
+                state_dict[k.replace(f"{marker}{global_id}", f"{marker}{local_id}")] = v
+        return state_dict
+    assert model is not None, "load_moe_state_dict needs the model to enumerate its MoE layers"
+    layer_id = 0
+    for name, m in model.named_modules():
+        if not isinstance(m, MoE):
+            continue
+        gname = m.expert_group_name
+        ep_rank = groups._get_expert_parallel_rank(gname)
+        prefix = _expert_prefix(name)
+        for local_id in range(m.num_local_experts):
+            global_id = ep_rank * m.num_local_experts + local_id
+            path = expert_ckpt_name(checkpoint_path, layer_id, global_id, tag, mp_rank)
+            if os.path.exists(path):
+                sd = torch.load(path, map_location="cpu", weights_only=False)
+                for k, v in sd.items():
+                    state_dict[k.replace(f"{prefix}{global_id}.", f"{prefix}{local_id}.")] = v
+        layer_id += 1
+    return state_dict

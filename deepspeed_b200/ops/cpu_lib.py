@@ -55,6 +55,12 @@ def lib():
                     L.dsb200_dc_fit_comm.restype = I
                     L.dsb200_dc_plan.argtypes = [I, P, P, I, P, P, P, D, D, L64, L64, L64, D, D, P, P, P, P]
                     L.dsb200_dc_plan.restype = I
+                if hasattr(L, "dsb200_locked_alloc"):
+                    L.dsb200_locked_alloc.argtypes = [L64, P]
+                    L.dsb200_locked_alloc.restype = P
+                    L.dsb200_locked_free.argtypes = [P]
+                    L.dsb200_locked_free.restype = I
+                    L.dsb200_locked_bytes.restype = L64
                 if hasattr(L, "dsb200_shm_create"):
                     L.dsb200_shm_create.argtypes = [ctypes.c_char_p, I, I, L64, I, ctypes.c_double]
                     L.dsb200_shm_create.restype = P

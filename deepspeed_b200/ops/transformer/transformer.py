@@ -139,7 +139,7 @@ class DeepSpeedTransformerLayer(nn.Module):
 
     def forward(self, hidden_states, attention_mask=None, head_mask=None, layer_head_mask=None,
                 encoder_hidden_states=None, encoder_attention_mask=None, past_key_value=None, output_attentions=False,
-                grads=None):
+                grads=None, **unused_hf_kwargs):
         self.config.is_grad_enabled = torch.is_grad_enabled()
         cfg = self.config
         eps = cfg.layer_norm_eps

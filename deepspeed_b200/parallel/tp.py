@@ -265,14 +265,38 @@ def _fused_sub_params(name, module, model):
     return None, 1
 
 
+def _allreduce_grad(g, group):
+    g = g.contiguous().clone()
+    dist.all_reduce(g, group=group)
+    return g
+
+
 class AutoTP:
     """Walk a model and replace linears/embeddings with their tensor-parallel versions."""
 
     def __init__(self, model, mp_group, config=None, partition_config=None, mode="allreduce"):
         self.model, self.mp_group, self.config, self.mode = model, mp_group, config, mode
         self.partition_config = partition_config or {}
-        self.row = [re.compile(p) for p in ROW_PARALLEL_PATTERNS + list(self.partition_config.get("row_parallel", []))]
-        self.col = [re.compile(p) for p in COLUMN_PARALLEL_PATTERNS + list(self.partition_config.get("column_parallel", []))]
+        # reference schema (module_inject/autotp_config.py): an AutoTPConfig, or a dict with layer_specs / preset
+        self.specs = None
+        from .autotp_config import AutoTPConfig, AutoTPPresets, merge_autotp_configs
+        pc = self.partition_config
+        if isinstance(pc, AutoTPConfig):
+            self.specs, pc = pc, {}
+        elif isinstance(pc, dict) and ("layer_specs" in pc or "use_default_specs" in pc):
+            self.specs, pc = AutoTPConfig.from_dict(pc), {}
+        preset = getattr(config, "preset_model", None)
+        if preset:
+            base = AutoTPPresets.get_preset(preset)
+            if base is None:
+                raise ValueError(f"unknown tensor_parallel.preset_model {preset!r}")
+            self.specs = merge_autotp_configs(base, self.specs) if self.specs is not None else base
+        self.partition_config = pc
+        use_defaults = self.specs is None or self.specs.use_default_specs
+        self.row = [re.compile(p) for p in (ROW_PARALLEL_PATTERNS if use_defaults else []) +
+                    list(pc.get("row_parallel", []))]
+        self.col = [re.compile(p) for p in (COLUMN_PARALLEL_PATTERNS if use_defaults else []) +
+                    list(pc.get("column_parallel", []))]
         self.replaced = {}
 
     @staticmethod
@@ -299,12 +323,37 @@ class AutoTP:
         for name, module in list(self.model.named_modules()):
             if not isinstance(module, nn.Linear):
                 continue
-            kind = self._kind("." + name)
+            spec = None
+            if self.specs is not None:
+                mtype = getattr(getattr(self.model, "config", None), "model_type", None)
+                spec = self.specs.find_matching_spec(name + ".weight", mtype)
+            if spec is not None:
+                kind = spec.partition_type.value
+                if kind == "skip":
+                    if spec.grad_allreduce:  # replicated weight fed by rank-local activations: sum its gradient
+                        group = self.mp_group
+                        for p in module.parameters():
+                            p.ds_tp_grad_allreduce = True
+                            if p.requires_grad:
+                                p.register_hook(lambda g, group=group: _allreduce_grad(g, group))
+                    self.replaced[name] = "skip"
+                    continue
+            else:
+                kind = self._kind("." + name)
             if kind is None:
+                if self.specs is not None and self.specs.strict_mode:
+                    raise ValueError(f"AutoTP strict_mode: no partition spec matches linear layer {name!r}")
                 continue
             parent, attr = self._parent(name)
             if kind == "row":
                 new = LinearAllreduce(module, self.mp_group, mode=self.mode)
+            elif spec is not None:
+                sub = spec.sub_param_sizes_for(module.weight.shape[0])
+                grain = 1
+                if sub is None:
+                    sub, grain = _fused_sub_params(name, module, self.model)
+                new = LinearLayer(module, self.mp_group, sub_params=sub, gather_output=spec.gather_output,
+                                  mode=self.mode, grain=grain)
             else:
                 sub, grain = _fused_sub_params(name, module, self.model)
                 new = LinearLayer(module, self.mp_group, sub_params=sub, mode=self.mode, grain=grain)

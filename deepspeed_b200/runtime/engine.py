@@ -27,6 +27,7 @@ from ..utils.timer import (BACKWARD_GLOBAL_TIMER, BACKWARD_INNER_GLOBAL_TIMER, B
                            SynchronizedWallClockTimer, ThroughputTimer)
 from . import lr_schedules
 from .dataloader import DeepSpeedDataLoader
+from .engine_accessors import EngineAccessorsMixin
 from .zero.sharded_optimizer import ZeroShardedOptimizer
 
 MEMORY_OPT_ALLREDUCE_SIZE = 500000000
@@ -63,7 +64,7 @@ def _split_half_float_double(tensors):
     return list(buckets.values())
 
 
-class DeepSpeedEngine(Module):
+class DeepSpeedEngine(EngineAccessorsMixin, Module):
 
     def __init__(self, args=None, model=None, optimizer=None, model_parameters=None, training_data=None,
                  lr_scheduler=None, mpu=None, dist_init_required=None, collate_fn=None, config=None,
@@ -305,15 +306,11 @@ class DeepSpeedEngine(Module):
         self._zero_inference = True
 
     def _leaf_module_classes(self):
-        zc = self._config.zero_config.leaf_module
-        names = set(zc.classes)
-        out = []
-        for m in self.module.modules():
-            if getattr(m, "_z3_leaf", False) or f"{type(m).__module__}.{type(m).__name__}" in names \
-                    or type(m).__name__ in names:
-                if type(m) not in out:
-                    out.append(type(m))
-        return tuple(out)
+        """Flags the modules the ``leaf_module`` config section names (classes / names / suffixes); user calls to
+        ``set_z3_leaf_modules*`` have flagged theirs already. The unit builder reads the per-instance flag."""
+        from ..utils.z3_leaf_module import apply_zero_leaf_module_config
+        apply_zero_leaf_module_config(self.module, self._config.zero_config.leaf_module)
+        return ()
 
     def _grad_accum_dtype(self):
         name = self._config.grad_accum_dtype
@@ -722,11 +719,18 @@ class DeepSpeedEngine(Module):
 
     # ------------------------------------------------------------------ backward ---------------
     def is_gradient_accumulation_boundary(self):
+        """Managed mode (default): driven by the micro-step counter. With ``managed_gradient_accumulation: false`` the
+        caller owns the boundary: it is True only while ``step()`` runs (reference ``engine.py:3262``)."""
         if self._is_gradient_accumulation_boundary is None:
+            if not self.managed_gradient_accumulation():
+                return getattr(self, "_running_engine_step", False)
             return (self.micro_steps + 1) % self.gradient_accumulation_steps() == 0
         return self._is_gradient_accumulation_boundary
 
     def set_gradient_accumulation_boundary(self, is_boundary):
+        assert self.managed_gradient_accumulation(), \
+            "set_gradient_accumulation_boundary() is not supported with managed_gradient_accumulation=False; " \
+            "the caller owns the boundary by calling step()"
         self._is_gradient_accumulation_boundary = is_boundary
         if self.optimizer is not None:
             self.optimizer.is_gradient_accumulation_boundary = is_boundary
@@ -748,6 +752,37 @@ class DeepSpeedEngine(Module):
             if self.optimizer is not None:
                 self.optimizer._require_reduce = True
 
+    @contextlib.contextmanager
+    def coalesce_grad_reduction(self):
+        """One with-block == one optimizer step: every ``backward()`` inside only accumulates gradients locally (full
+        unit gradient buffers), the exit issues a single reduction pass (reference ``engine.py:3053``). ZeRO 1/2/3."""
+        assert self.managed_gradient_accumulation(), \
+            "coalesce_grad_reduction is not supported with managed_gradient_accumulation=False; " \
+            "the caller already owns the accumulation boundary via step()"
+        stage = self.zero_optimization_stage()
+        if stage not in (1, 2, 3):
+            raise NotImplementedError(f"coalesce_grad_reduction requires ZeRO stage 1/2/3, got stage {int(stage)}")
+        if getattr(self, "pipeline_parallelism", False):
+            raise NotImplementedError("coalesce_grad_reduction is not supported under pipeline parallelism")
+        if not hasattr(self.optimizer, "reduce_gradients") or not hasattr(self.optimizer, "_require_reduce"):
+            raise NotImplementedError(
+                f"coalesce_grad_reduction does not yet support optimizer wrapper {type(self.optimizer).__name__}")
+        assert not self.inside_no_sync_ctxt, "coalesce_grad_reduction cannot be nested inside another no_sync context"
+        saved = self._is_gradient_accumulation_boundary
+        self.inside_no_sync_ctxt = True
+        self.optimizer._require_reduce = False
+        try:
+            yield
+        finally:
+            self.optimizer._require_reduce = True
+            self.inside_no_sync_ctxt = False
+            self._is_gradient_accumulation_boundary = True
+            self.optimizer.is_gradient_accumulation_boundary = True
+            try:
+                self.optimizer.reduce_gradients()
+            finally:
+                self._is_gradient_accumulation_boundary = saved
+
     def _scale_loss_by_gas(self, loss):
         if torch.is_tensor(loss):
             return loss / self.gradient_accumulation_steps()
@@ -767,8 +802,8 @@ class DeepSpeedEngine(Module):
     @instrument_w_nvtx
     def backward(self, loss, retain_graph=False, scale_wrt_gas=True):
         assert self.optimizer is not None, "must provide optimizer during init in order to use backward"
-        if self.inside_no_sync_ctxt:
-            pass
+        if not self.managed_gradient_accumulation():
+            self._unmanaged_backward_count = getattr(self, "_unmanaged_backward_count", 0) + 1
         for t in self.engine_timers.backward_timers:
             self.timers(t).start()
         if self.gradient_accumulation_steps() > 1 and scale_wrt_gas:
@@ -820,7 +855,13 @@ class DeepSpeedEngine(Module):
         if self.steps_per_print() and (self.global_steps + 1) % self.steps_per_print() == 0 and self.global_rank == 0:
             self._report_progress(self.global_steps + 1)
         self.global_steps += 1
-        self.global_samples += self.train_batch_size()
+        if not self.managed_gradient_accumulation():
+            # count the micro-batches actually seen since the last step(), not the configured train_batch_size
+            per_micro = self.train_batch_size() // self.gradient_accumulation_steps()
+            self.global_samples += per_micro * getattr(self, "_unmanaged_backward_count", 0)
+            self._unmanaged_backward_count = 0
+        else:
+            self.global_samples += self.train_batch_size()
         if self._config.autotuning_config.get("enabled", False):
             self._autotuning_step()
 
@@ -867,8 +908,15 @@ class DeepSpeedEngine(Module):
     @instrument_w_nvtx
     def step(self, lr_kwargs=None):
         assert self.optimizer is not None, "must provide optimizer during init in order to use step"
+        assert not self.inside_no_sync_ctxt, "It is illegal to call Engine.step() inside no_sync context manager"
         for t in self.engine_timers.step_timers:
             self.timers(t).start()
+        self._running_engine_step = True
+        if not self.managed_gradient_accumulation():
+            # the caller owns the boundary: stages 2/3 reduced every backward already, stages 0/1 reduce now
+            self.optimizer.is_gradient_accumulation_boundary = True
+            if not self.zero_optimization_partition_gradients():
+                self.optimizer.reduce_gradients()
         boundary = self.is_gradient_accumulation_boundary()
         self._step_applied = False
         if boundary:
@@ -902,6 +950,7 @@ class DeepSpeedEngine(Module):
                                                     top_modules=fc.top_modules, detailed=fc.detailed,
                                                     output_file=fc.output_file)
             self.flops_profiler.end_profile()
+        self._running_engine_step = False
         self.micro_steps += 1
 
     def was_step_applied(self):

@@ -13,28 +13,10 @@ class MiCS_Init(Init):
     pass
 
 
-def set_z3_leaf_modules(model, leaf_module_classes):
-    """Mark module classes whose children must not become separate units (reference utils/z3_leaf_module.py)."""
-    found = []
-    for m in model.modules():
-        if isinstance(m, tuple(leaf_module_classes)):
-            m._z3_leaf = True
-            found.append(m)
-    return found
+from ...utils.z3_leaf_module import (set_z3_leaf_modules, unset_z3_leaf_modules, z3_leaf_module,  # noqa: F401,E402
+                                      get_z3_leaf_modules, set_z3_leaf_module, set_z3_leaf_modules_by_name,
+                                      set_z3_leaf_modules_by_suffix, z3_leaf_parameter)
 
-
-def unset_z3_leaf_modules(model, leaf_module_classes):
-    out = []
-    for m in model.modules():
-        if isinstance(m, tuple(leaf_module_classes)) and getattr(m, "_z3_leaf", False):
-            m._z3_leaf = False
-            out.append(m)
-    return out
-
-
-def z3_leaf_module(model):
-    return getattr(model, "_z3_leaf", False)
-
-
-def get_z3_leaf_modules(model):
-    return [m for m in model.modules() if getattr(m, "_z3_leaf", False)]
+from .tiling import TiledLinear, TiledLinearReturnBias  # noqa: F401,E402
+from .param_status import (DeepSpeedTensorOverride, DeepSpeedZeRoOffload, ZeroParamStatus, ZeroParamType,  # noqa: F401,E402
+                           unwrap_model_for_generation)

@@ -33,6 +33,7 @@ from ... import comm as dist
 from ...utils.logging import log_dist, logger
 from ...utils.nvtx import instrument_w_nvtx
 from ..loss_scaler import CreateLossScaler
+from ..base_optimizer import ZeROOptimizer
 from .units import FlatUnit, build_bucket_units, build_module_units
 
 import os as _os
@@ -63,7 +64,7 @@ class _Storage:
         self.lp = None
 
 
-class ZeroShardedOptimizer:
+class ZeroShardedOptimizer(ZeROOptimizer):
     """See module docstring. ``optimizer`` is any ``torch.optim.Optimizer`` built over the model's params."""
 
     def __init__(self, module, optimizer, *, stage=1, dp_group=None, dp_world=1, dp_rank=0, sp_size=1,
@@ -531,9 +532,10 @@ class ZeroShardedOptimizer:
     def _accumulates(self, u, i):
         """Must a new gradient of parameter ``i`` be added to the flat buffer (instead of overwriting its region)?
         Yes for a second contribution inside the same backward pass (direct path, shared weights) and, when the flat
-        buffer is kept across micro-batches (stage <= 1), for every contribution after the first micro-batch."""
-        return i in getattr(u, "_pass_seen", ()) or (u.has_grad_data and not self.partition_grads
-                                                   and i in getattr(u, "_accumulated", ()))
+        buffer is kept across micro-batches (stage <= 1, or any stage while reductions are held back by
+        ``engine.coalesce_grad_reduction``), for every contribution after the first micro-batch."""
+        kept = not self.partition_grads or not self._require_reduce
+        return i in getattr(u, "_pass_seen", ()) or (u.has_grad_data and kept and i in getattr(u, "_accumulated", ()))
 
     def _grad_landed(self, u, i):
         seen = u.__dict__.setdefault("_pass_seen", set())
@@ -1229,6 +1231,8 @@ class ZeroShardedOptimizer:
                 continue
             dst = u.master_shard if optim_state_key is None else self._state_shard(u, optim_state_key)
             dst[s_in_shard:s_in_shard + n].copy_(flat[s_in_p:s_in_p + n].to(dst.dtype))
+            if optim_state_key is not None:  # _state_shard assembles a copy: scatter it back into the state tensors
+                self._write_state_shard(u, optim_state_key, dst)
             if optim_state_key is None:
                 self._lp_shards_will_be_written()
             if optim_state_key is None:
@@ -1257,6 +1261,18 @@ class ZeroShardedOptimizer:
                 out[a - u.shard_offset:b - u.shard_offset].copy_(stt[key].view(-1))
                 found = True
         return out if found else None
+
+    def _write_state_shard(self, u, key, shard):
+        """Inverse of :meth:`_state_shard`: scatter a unit-shard-shaped tensor back into the per-run state tensors."""
+        self._join_step()
+        if self._nvme is not None and key in self._nvme_names:
+            raise NotImplementedError("optimizer state on NVMe cannot be set element-wise; reload it first")
+        for (skey, a, b, gi, uu, v) in self._segments:
+            if uu is not u:
+                continue
+            stt = self.optimizer.state.get(v, {})
+            if key in stt and torch.is_tensor(stt[key]) and stt[key].numel() == b - a:
+                stt[key].view(-1).copy_(shard[a - u.shard_offset:b - u.shard_offset].to(stt[key].dtype))
 
     # ------------------------------------------------------------------ state dict -------------
     def _inner_state_flat(self):

@@ -209,7 +209,11 @@ def build_module_units(model, param_groups, unit_max_numel, persistence_threshol
             return
         total = sum(numel_of(p) for p in ps)
         children = list(module.children())
-        leaf = isinstance(module, tuple(leaf_modules)) if leaf_modules else False
+        leaf = bool(getattr(module, "_z3_leaf", False)) or (isinstance(module, tuple(leaf_modules))
+                                                           if leaf_modules else False)
+        if leaf:
+            for p in module.parameters():
+                p.ds_z3_leaf_module = module
         container = isinstance(module, (torch.nn.ModuleList, torch.nn.ModuleDict))  # no forward(): hooks never fire
         if container:
             for c in children:

@@ -63,6 +63,25 @@ def log_dist(message, ranks=None, level=logging.INFO):
         logger.log(level, f"[Rank {_rank()}] {message}")
 
 
+@functools.lru_cache(None)
+def log_dist_once(message, ranks=None, level=logging.INFO):
+    """``log_dist`` that emits a given (message, ranks, level) only the first time."""
+    log_dist(message, ranks=tuple(ranks) if ranks is not None else None, level=level)
+
+
+def set_log_level_from_string(log_level_str, custom_logger=None):
+    """Reference ``utils/logging.py``: 'debug' | 'info' | 'warning' | 'error' | 'critical'."""
+    key = str(log_level_str).lower()
+    if key not in LOG_LEVELS:
+        raise ValueError(f"{log_level_str} is not one of the valid logging levels. Valid log levels are "
+                         f"{list(LOG_LEVELS)}.")
+    (custom_logger or logger).setLevel(LOG_LEVELS[key])
+
+
+def get_current_level():
+    return logger.getEffectiveLevel()
+
+
 def print_json_dist(message, ranks=None, path=None):
     """Dump a dict as JSON from the listed ranks, optionally to ``path``."""
     if should_log(ranks):

@@ -296,6 +296,12 @@ int dsb200_ragged_flush(void* h, int64_t uid);
 int dsb200_ragged_schedule(void* h, int n_seq, const int64_t* uids, const int* n_tokens, int prefill_min, int* buf,
                            int64_t cap, int* header, int commit);
 
+/* ---- page-locked host allocations (csrc/cpu/pin_memory.cpp; libdsb200_cpu) --------------------------------------
+ * page-aligned + mlock; *locked_out = 0 when RLIMIT_MEMLOCK refused the lock (memory still usable). */
+void* dsb200_locked_alloc(int64_t bytes, int* locked_out);
+int dsb200_locked_free(void* p);
+int64_t dsb200_locked_bytes(void);
+
 /* ---- shared-memory all-reduce between the ranks of one host (csrc/cpu/shm_comm.cpp; libdsb200_cpu) ---------------
  * create: rank 0 passes create != 0 first, the others attach afterwards (order them with a barrier); buf_bytes is the
  * chunk capacity. all_reduce: in-place sum, dtype 0 fp32 / 1 bf16 / 2 fp16; 0 ok, -1 bad argument, -2 peer timeout. */
