@@ -163,10 +163,94 @@ class B200Accelerator:
         return ["CUDA_VISIBLE_DEVICES"]
 
     def get_compile_backend(self):
-        return "inductor"
+        return getattr(self, "_compile_backend", "inductor")
 
+    def set_compile_backend(self, backend):
+        import torch._dynamo as dynamo
+        if backend not in dynamo.list_backends(exclude_tags=()):
+            raise ValueError(f"{backend} not supported by {self.device_name()}. Supported Backends are "
+                             f"{dynamo.list_backends(exclude_tags=())}")
+        self._compile_backend = backend
+
+    def set_visible_devices_envs(self, current_env, local_accelerator_ids):
+        for env in self.visible_devices_envs():
+            current_env[env] = ",".join(map(str, local_accelerator_ids))
+
+    # ---- RNG ---------------------------------------------------------------------------------
+    @property
+    def random(self):
+        return torch.cuda.random if torch.cuda.is_available() else torch.random
+
+    def initial_seed(self):
+        return torch.cuda.initial_seed() if torch.cuda.is_available() else torch.initial_seed()
+
+    def default_generator(self, device_index):
+        return torch.cuda.default_generators[device_index] if torch.cuda.is_available() else torch.default_generator
+
+    # ---- memory statistics (older spellings included) -------------------------------------------
+    def _cuda_stat(self, fn, device_index=None, default=0):
+        return getattr(torch.cuda, fn)(device_index) if torch.cuda.is_available() else default
+
+    def reset_max_memory_allocated(self, device_index=None):
+        if torch.cuda.is_available():
+            torch.cuda.reset_peak_memory_stats(device_index)
+
+    def memory_cached(self, device_index=None):
+        return self._cuda_stat("memory_reserved", device_index)
+
+    def max_memory_cached(self, device_index=None):
+        return self._cuda_stat("max_memory_reserved", device_index)
+
+    def reset_max_memory_cached(self, device_index=None):
+        self.reset_max_memory_allocated(device_index)
+
+    def max_memory_reserved(self, device_index=None):
+        return self._cuda_stat("max_memory_reserved", device_index)
+
+    def memory_stats(self, device_index=None):
+        return torch.cuda.memory_stats(device_index) if torch.cuda.is_available() else {}
+
+    # ---- CUDA graphs ---------------------------------------------------------------------------
+    def create_graph(self):
+        return torch.cuda.CUDAGraph()
+
+    def capture_to_graph(self, graph, pool=None, stream=None):
+        return torch.cuda.graph(graph, pool=pool, stream=stream)
+
+    def replay_graph(self, graph):
+        graph.replay()
+
+    def prefer_triton_grouped_mm(self):
+        return False  # the grouped GEMM is the tcgen05 kernel (ops/grouped_gemm.py)
+
+    # ---- typed tensor constructors on the device -----------------------------------------------
+    def _typed(self, dtype):
+        from functools import partial
+        return partial(torch.tensor, dtype=dtype, device=self.current_device_name())
+
+    BFloat16Tensor = property(lambda self: self._typed(torch.bfloat16))
+    ByteTensor = property(lambda self: self._typed(torch.uint8))
+    DoubleTensor = property(lambda self: self._typed(torch.double))
+    FloatTensor = property(lambda self: self._typed(torch.float))
+    HalfTensor = property(lambda self: self._typed(torch.half))
+    IntTensor = property(lambda self: self._typed(torch.int))
+    LongTensor = property(lambda self: self._typed(torch.long))
+
+    def unpin_memory(self, tensor):
+        """Release a tensor pinned through the native backend (``DS_PIN_MEMORY_BACKEND=native``); torch-pinned tensors
+        are freed by their storage."""
+        from ..utils.pin_memory import get_active_native_pinned_memory
+        mgr = get_active_native_pinned_memory()
+        return mgr.unpin(tensor) if mgr is not None and mgr.is_pinned(tensor) else False
+
+
+DeepSpeedAccelerator = B200Accelerator  # the reference's abstract base; one concrete device family here
 
 _ACC = None
+
+
+def is_current_accelerator_supported():
+    return True
 
 
 def get_accelerator():

@@ -122,3 +122,47 @@ def load_universal_into_engine(engine, load_dir, tag, load_optimizer_states=True
         logger.warning(f"universal checkpoint is missing {len(missing)} parameters, e.g. {missing[:3]}")
     log_dist(f"loaded universal checkpoint from {folder}", [0])
     return folder, client_state
+
+
+# ---- reference module-level API (``checkpoint/universal_checkpoint.py``) ----------------------------
+from dataclasses import dataclass  # noqa: E402
+from typing import List, Tuple, Union  # noqa: E402
+
+
+@dataclass
+class SubparamShape:
+    """Parameters matching ``patterns`` are made of fused sub-parameters: ``shape`` is the logical view whose entry at
+    ``partition_dim`` lists the sub-parameter sizes (or their count); used by ``ds_to_universal`` to merge / slice the
+    tensor-parallel shards of fused QKV or gate-up weights."""
+    patterns: List[str]
+    shape: Tuple[Union[Tuple[int], int]]
+    partition_dim: int
+
+
+def load_hp_checkpoint_state(self, folder, tp_rank, tp_world_size):
+    """Bound onto a parameter by :func:`enable_universal_checkpoint`: read ``<folder>/fp32.pt`` (+ optimizer state
+    files next to it), cut this tensor-parallel rank's slice, and write it into the parameter's master weights /
+    optimizer state through the fragment API. Returns the step recorded in the files (or None)."""
+    from ..utils import tensor_fragment as tf
+    step = None
+    for fname in sorted(os.listdir(folder)):
+        if not fname.endswith(".pt"):
+            continue
+        key = fname[:-3]
+        ckpt = torch.load(os.path.join(folder, fname), map_location="cpu", weights_only=False)
+        if key == "step":
+            step = ckpt
+            continue
+        full = _tp_slice(ckpt, tuple(getattr(self, "ds_shape", self.shape)), tp_rank, tp_world_size)
+        full = full.reshape(tuple(getattr(self, "ds_shape", self.shape)))
+        if key == "fp32":
+            tf.safe_set_full_fp32_param(self, full)
+        else:
+            tf.safe_set_full_optimizer_state(self, full, key)
+    return step
+
+
+def enable_universal_checkpoint(param_list):
+    import types
+    for param in param_list:
+        param.load_hp_checkpoint_state = types.MethodType(load_hp_checkpoint_state, param)

@@ -19,12 +19,35 @@ from .ragged import BlockedKVCache, DSStateManager, NativeRaggedState, RaggedBat
 
 
 class RaggedInferenceEngineConfig:
+    """Flat keyword form, or the reference's nested form (``config_v2.py:30``): ``tensor_parallel`` / ``tp``
+    ``{"tp_size": n}``, ``state_manager`` / ``manager`` ``{"max_tracked_sequences", "max_ragged_batch_size",
+    "max_ragged_sequence_count", "max_context", "memory_config": {"mode": "reserve"|"allocate", "size": ...}}``,
+    ``quantization`` ``{"quantization_mode": ...}``."""
 
     def __init__(self, kv_block_size=64, num_kv_blocks=1024, max_ragged_batch_size=768, max_ragged_sequence_count=512,
-                 max_tracked_sequences=2048):
+                 max_tracked_sequences=2048, tensor_parallel=None, tp=None, state_manager=None, manager=None,
+                 quantization=None, dtype=None):
+        from types import SimpleNamespace
+        sm = dict(state_manager or manager or {})
         self.kv_block_size, self.num_kv_blocks = kv_block_size, num_kv_blocks
-        self.max_ragged_batch_size, self.max_ragged_sequence_count = max_ragged_batch_size, max_ragged_sequence_count
-        self.max_tracked_sequences = max_tracked_sequences
+        self.max_ragged_batch_size = sm.get("max_ragged_batch_size", max_ragged_batch_size)
+        self.max_ragged_sequence_count = sm.get("max_ragged_sequence_count", max_ragged_sequence_count)
+        self.max_tracked_sequences = sm.get("max_tracked_sequences", max_tracked_sequences)
+        self.max_context = sm.get("max_context", 8192)
+        mem = dict(sm.get("memory_config", {}) or {})
+        if str(mem.get("mode", "")).lower().endswith("allocate") and "size" in mem:
+            self.num_kv_blocks = int(mem["size"])  # ALLOCATE mode: size is the number of KV blocks
+        self.memory_config = SimpleNamespace(mode=mem.get("mode", "reserve"), size=mem.get("size", 1_000_000_000))
+        tpd = tensor_parallel if tensor_parallel is not None else tp
+        tp_size = tpd.get("tp_size", 1) if isinstance(tpd, dict) else getattr(tpd, "tp_size", 1) if tpd else 1
+        self.tensor_parallel = SimpleNamespace(tp_size=int(tp_size))
+        q = dict(quantization or {})
+        self.quantization = SimpleNamespace(quantization_mode=q.get("quantization_mode"))
+        self.state_manager = SimpleNamespace(max_tracked_sequences=self.max_tracked_sequences,
+                                             max_ragged_batch_size=self.max_ragged_batch_size,
+                                             max_ragged_sequence_count=self.max_ragged_sequence_count,
+                                             max_context=self.max_context, memory_config=self.memory_config)
+        self.dtype = dtype
 
 
 class InferenceEngineV2:
@@ -61,6 +84,26 @@ class InferenceEngineV2:
     @property
     def _sm(self):
         return self.native_state if self.native_state is not None else self.state_manager
+
+    def serialize(self, save_path):
+        """Write the model so that ``build_engine_from_ds_checkpoint`` can rebuild the engine without the original
+        HuggingFace files (reference ``engine_v2.py:251``): parameters, metadata naming the policy, pickled config."""
+        import json
+        import os
+        import pickle
+        from .engine_factory import DS_MODEL_CONFIG, make_metadata_filename, make_param_filename
+        hf_config = getattr(self.model, "hf_config", None)
+        if hf_config is None:
+            raise RuntimeError("serialize() needs a model built from a HuggingFace config (build_hf_engine)")
+        os.makedirs(save_path, exist_ok=True)
+        tp = self.config.tensor_parallel.tp_size
+        torch.save({k: v.detach().cpu() for k, v in self.model.state_dict().items()},
+                   make_param_filename(save_path, 0, tp))
+        meta = {"policy": hf_config.model_type,
+                "params": {k: list(v.shape) for k, v in self.model.state_dict().items()}}
+        json.dump(meta, open(make_metadata_filename(save_path, 0, tp), "w"))
+        with open(os.path.join(save_path, DS_MODEL_CONFIG), "wb") as f:
+            pickle.dump(hf_config, f)
 
     @property
     def free_blocks(self):

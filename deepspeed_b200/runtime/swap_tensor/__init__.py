@@ -6,3 +6,6 @@ from .optimizer_utils import OptimizerSwapper  # noqa: F401
 from .partitioned_optimizer_swapper import PartitionedOptimizerSwapper  # noqa: F401
 from .pipelined_optimizer_swapper import PipelinedOptimizerSwapper  # noqa: F401
 from .partitioned_param_swapper import AsyncPartitionedParameterSwapper, PartitionedParamStatus  # noqa: F401
+
+MIN_AIO_BYTES = 1024**2
+MIN_SWAPPABLE_BYTES = MIN_AIO_BYTES  # tensors below this stay in memory (reference swap_tensor/utils.py:16)

@@ -106,3 +106,31 @@ def test_native_ragged_state_matches_python_bookkeeping():
     with pytest.raises(ValueError):
         nat.schedule([999], [bs * nb + 1], 6, torch.device("cpu"))
     assert nat.n_tracked_sequences == len(live)  # a refused batch changes nothing
+
+
+def test_build_hf_engine_from_directory_and_serialized_checkpoint(tmp_path):
+    """engine_factory: local HF directory -> engine; serialize() -> build_engine_from_ds_checkpoint round trip."""
+    import os
+    from transformers import LlamaConfig, LlamaForCausalLM
+    from deepspeed_b200.inference import RaggedInferenceEngineConfig, build_hf_engine
+    torch.manual_seed(0)
+    cfg = LlamaConfig(vocab_size=128, hidden_size=64, intermediate_size=128, num_hidden_layers=2,
+                      num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=64)
+    hf = LlamaForCausalLM(cfg).eval()
+    hf_dir, ds_dir = str(tmp_path / "hf"), str(tmp_path / "ds")
+    hf.save_pretrained(hf_dir)
+    ec = RaggedInferenceEngineConfig(state_manager={"max_ragged_batch_size": 64,
+                                                    "memory_config": {"mode": "allocate", "size": 32}},
+                                     tp={"tp_size": 1}, dtype=torch.float32)
+    assert ec.num_kv_blocks == 32 and ec.state_manager.max_ragged_batch_size == 64 and ec.tensor_parallel.tp_size == 1
+    eng = build_hf_engine(hf_dir, ec)
+    ids = torch.randint(0, 128, (1, 9))
+    with torch.no_grad():
+        want = hf(ids).logits[0, -1]
+    assert (eng.put([7], [ids[0]])[0].float().cpu() - want).abs().max() < 1e-4
+    eng.serialize(ds_dir)
+    assert sorted(os.listdir(ds_dir)) == ["ds_model_config.pkl", "metadata_rank_0_of_1.json", "params_rank_0_of_1.pt"]
+    eng2 = build_hf_engine(ds_dir, RaggedInferenceEngineConfig(dtype=torch.float32))
+    assert (eng2.put([1], [ids[0]])[0].float().cpu() - want).abs().max() < 1e-4
+    with pytest.raises(FileNotFoundError):
+        build_hf_engine(str(tmp_path / "missing"), ec)
