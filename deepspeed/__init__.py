@@ -31,6 +31,37 @@ _ALIASES = {
     "deepspeed.ops.lion": "deepspeed_b200.ops.lion",
     "deepspeed.ops.adagrad": "deepspeed_b200.ops.adagrad",
     "deepspeed.module_inject": "deepspeed_b200.parallel",
+    "deepspeed.module_inject.replace_module": "deepspeed_b200.parallel.replace_module",
+    "deepspeed.module_inject.module_quantize": "deepspeed_b200.parallel.replace_module",
+    "deepspeed.module_inject.replace_policy": "deepspeed_b200.parallel.replace_module",
+    "deepspeed.module_inject.policy": "deepspeed_b200.parallel.replace_module",
+    "deepspeed.module_inject.layers": "deepspeed_b200.parallel.layers",
+    "deepspeed.module_inject.autotp_config": "deepspeed_b200.parallel.autotp_config",
+    "deepspeed.module_inject.auto_tp": "deepspeed_b200.parallel.tp",
+    "deepspeed.module_inject.auto_ep": "deepspeed_b200.parallel.auto_ep",
+    "deepspeed.model_implementations.transformers.ds_transformer":
+    "deepspeed_b200.ops.transformer.inference.ds_transformer",
+    "deepspeed.ops.transformer.inference.ds_attention": "deepspeed_b200.ops.transformer.inference.ds_transformer",
+    "deepspeed.ops.transformer.inference.ds_mlp": "deepspeed_b200.ops.transformer.inference.ds_transformer",
+    "deepspeed.ops.adam.zenflow_cpu_adam": "deepspeed_b200.ops.adam.zenflow",
+    "deepspeed.ops.adam.zenflow_torch_adam": "deepspeed_b200.ops.adam.zenflow",
+    "deepspeed.runtime.zero.leaf_module_config": "deepspeed_b200.config.sections",
+    "deepspeed.runtime.zero.parameter_offload": "deepspeed_b200.runtime.zero.param_status",
+    "deepspeed.runtime.zero.mics": "deepspeed_b200.runtime.zero",
+    "deepspeed.inference.v2.config_v2": "deepspeed_b200.inference.v2.engine_factory",
+    "deepspeed.checkpoint.reshape_utils": "deepspeed_b200.checkpoint.reshape",
+    "deepspeed.checkpoint.reshape_3d_utils": "deepspeed_b200.checkpoint.reshape",
+    "deepspeed.checkpoint.reshape_meg_2d": "deepspeed_b200.checkpoint.reshape",
+    "deepspeed.checkpoint.zero_checkpoint": "deepspeed_b200.checkpoint.reshape",
+    "deepspeed.checkpoint.deepspeed_checkpoint": "deepspeed_b200.checkpoint.reshape",
+    "deepspeed.checkpoint.utils": "deepspeed_b200.checkpoint.reshape",
+    "deepspeed.checkpoint.universal_checkpoint": "deepspeed_b200.checkpoint.universal",
+    "deepspeed.nvme.perf_run_sweep": "deepspeed_b200.nvme",
+    "deepspeed.nvme.perf_generate_param": "deepspeed_b200.nvme",
+    "deepspeed.nvme.test_ds_aio": "deepspeed_b200.nvme",
+    "deepspeed.accelerator.real_accelerator": "deepspeed_b200.accelerator",
+    "deepspeed.accelerator.abstract_accelerator": "deepspeed_b200.accelerator",
+    "deepspeed.git_version_info": "deepspeed_b200.version",
     "deepspeed.utils.zero_to_fp32": "deepspeed_b200.checkpoint.zero_to_fp32",
     "deepspeed.checkpoint.ds_to_universal": "deepspeed_b200.checkpoint.ds_to_universal",
     "deepspeed.sequence.layer": "deepspeed_b200.sequence.layer",

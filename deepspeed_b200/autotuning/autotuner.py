@@ -67,6 +67,47 @@ class Autotuner:
     def mp_size(self):
         return self.autotuning_config.mp_size
 
+    def max_train_batch_size(self):
+        return self.autotuning_config.max_train_batch_size
+
+    def max_train_micro_batch_size_per_gpu(self):
+        """Upper end of the micro-batch search; a user-given ``max_train_batch_size`` caps it (at least one
+        gradient-accumulation step must fit)."""
+        cap = self.autotuning_config.max_train_micro_batch_size_per_gpu
+        mtb = self.max_train_batch_size()
+        if mtb and mtb > 0:
+            return min(cap, mtb * self.mp_size() // (self.exp_num_gpus * self.exp_num_nodes))
+        return cap
+
+    def min_train_micro_batch_size_per_gpu(self):
+        return self.autotuning_config.min_train_micro_batch_size_per_gpu
+
+    def num_tuning_micro_batch_sizes(self):
+        return self.autotuning_config.num_tuning_micro_batch_sizes
+
+    def get_plateau_mbs(self, tuning_space_name):
+        """Largest micro-batch size of a tuning space before the metric stops improving (drops, or gains < 5 %)."""
+        recs = sorted(self.records.get(tuning_space_name, []),
+                      key=lambda r: r[0]["ds_config"].get("train_micro_batch_size_per_gpu", 0))
+        prev_val, prev_mbs = None, 0
+        for exp, val, _ in recs:
+            if prev_val:
+                if val < prev_val or (val - prev_val) / prev_val < 0.05:
+                    break
+            prev_val, prev_mbs = val, exp["ds_config"].get("train_micro_batch_size_per_gpu", 0)
+        return prev_mbs
+
+    def get_val_from_user_args(self, ds_name):
+        """Numeric value the user script's command line gives to the argument mapped to ``ds_name``
+        (``autotuning.arg_mappings``), or None."""
+        mappings = self.autotuning_config.arg_mappings
+        user_args = list(getattr(self.args, "user_args", []) or [])
+        if mappings and ds_name in mappings and mappings[ds_name] in user_args:
+            idx = user_args.index(mappings[ds_name])
+            if idx + 1 < len(user_args) and str(user_args[idx + 1]).isnumeric():
+                return user_args[idx + 1]
+        return None
+
     def fp16_enabled(self):
         return bool(self.user_config.get("fp16", {}).get("enabled", False)) or \
             bool(self.user_config.get("bf16", {}).get("enabled", False))

@@ -101,7 +101,15 @@ def init_distributed(dist_backend=None,
         return
     required = ("RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT")
     if init_method is None and rank < 0 and not all(k in os.environ for k in required):
-        if not (auto_mpi_discovery and mpi_discovery(distributed_port, verbose)):
+        cloud = False
+        if auto_mpi_discovery and "OMPI_COMM_WORLD_RANK" in os.environ:
+            if in_aml() and not in_dlts():
+                patch_aml_env_for_torch_nccl_backend(verbose=verbose)
+                cloud = True
+            elif in_aws_sm():
+                patch_aws_sm_env_for_torch_nccl_backend(verbose=verbose)
+                cloud = True
+        if not cloud and not (auto_mpi_discovery and mpi_discovery(distributed_port, verbose)):
             # single-process default: a 1-rank world on localhost
             os.environ.setdefault("RANK", "0")
             os.environ.setdefault("WORLD_SIZE", "1")
@@ -122,6 +130,72 @@ def init_distributed(dist_backend=None,
         logger.info(f"Initializing torch.distributed backend={backend}")
     dist.init_process_group(**kwargs)
     _initialized_here = True
+
+
+def in_aml():
+    """Running inside Azure Machine Learning?"""
+    return "AZUREML_EXPERIMENT_ID" in os.environ
+
+
+def in_aws_sm():
+    """Running inside AWS SageMaker?"""
+    return "SM_TRAINING_ENV" in os.environ
+
+
+def in_dlts():
+    """Running on a DLTS cluster?"""
+    return "DLTS_JOB_ID" in os.environ
+
+
+def patch_aml_env_for_torch_nccl_backend(master_port=6105, verbose=True):
+    """Translate the OpenMPI variables Azure ML sets into RANK / WORLD_SIZE / LOCAL_RANK / MASTER_* (reference
+    ``comm.py:921``). Multi-node jobs take the master from AZ_BATCH_MASTER_NODE, single-node ones from
+    AZ_BATCHAI_MPI_MASTER_NODE."""
+    env = os.environ
+    env["RANK"] = env["OMPI_COMM_WORLD_RANK"]
+    env["WORLD_SIZE"] = env["OMPI_COMM_WORLD_SIZE"]
+    single_node = int(env["OMPI_COMM_WORLD_LOCAL_SIZE"]) == int(env["WORLD_SIZE"])
+    if not single_node:
+        env["MASTER_ADDR"] = env["AZ_BATCH_MASTER_NODE"].split(":")[0]
+        env.setdefault("MASTER_PORT", str(master_port))
+    else:
+        env["MASTER_ADDR"] = env["AZ_BATCHAI_MPI_MASTER_NODE"]
+        env["MASTER_PORT"] = str(DEFAULT_AML_MASTER_PORT)
+    if verbose:
+        logger.info(f"NCCL_SOCKET_IFNAME original value = {env.get('NCCL_SOCKET_IFNAME')}")
+    env["NCCL_SOCKET_IFNAME"] = DEFAULT_AML_NCCL_SOCKET_IFNAME
+    env["LOCAL_RANK"] = env["OMPI_COMM_WORLD_LOCAL_RANK"]
+    if verbose:
+        logger.info(f"Discovered AzureML settings of world_rank={env['RANK']}, local_rank={env['LOCAL_RANK']}, "
+                    f"world_size={env['WORLD_SIZE']}, master_addr={env['MASTER_ADDR']}, "
+                    f"master_port={env['MASTER_PORT']}")
+
+
+def patch_aws_sm_env_for_torch_nccl_backend(verbose=True):
+    """SageMaker launches with OpenMPI: copy its rank variables (MASTER_* are already set there)."""
+    env = os.environ
+    env["RANK"] = env["OMPI_COMM_WORLD_RANK"]
+    env["LOCAL_RANK"] = env["OMPI_COMM_WORLD_LOCAL_RANK"]
+    env["WORLD_SIZE"] = env["OMPI_COMM_WORLD_SIZE"]
+    if verbose:
+        logger.info(f"Discovered AWS SageMaker settings of world_rank={env['RANK']}, local_rank={env['LOCAL_RANK']}, "
+                    f"world_size={env['WORLD_SIZE']}, master_addr={env.get('MASTER_ADDR')}, "
+                    f"master_port={env.get('MASTER_PORT')}")
+
+
+DEFAULT_AML_MASTER_PORT = "54965"
+DEFAULT_AML_NCCL_SOCKET_IFNAME = "^docker0,lo"
+
+
+def init_deepspeed_backend(ds_backend, timeout, init_method):
+    """The reference can swap in its own (non-torch) backends here; every backend of this framework is
+    ``torch.distributed`` plus the in-kernel NVLink collectives of ``comm/symm.py``, so there is nothing to build."""
+    logger.debug(f"{ds_backend} backend: torch.distributed process groups are used directly")
+
+
+def set_backend():
+    """Reference ``comm.py:203``: select the active backend object; a single backend exists here."""
+    return _device_backend()
 
 
 def destroy_process_group(group=None):
@@ -181,6 +255,61 @@ def new_group(ranks=None, **kw):
 
 def get_backend(group=None):
     return dist.get_backend(group)
+
+
+def initialize_mesh_device(mesh_shape, mesh_dim_names):
+    """Reference ``comm.py:765``: a torch DeviceMesh of the given shape / names (e.g. (dp, sp))."""
+    assert is_initialized(), "DeepSpeed backend not set, please initialize it using init_process_group()"
+    logger.info(f"Initializing mesh device with shape {mesh_shape} and dim names {mesh_dim_names}")
+    return init_device_mesh(mesh_shape, mesh_dim_names)
+
+
+def enable_symm_mem_for_group(group_name):
+    """Make torch symmetric memory usable on a named process group (reference ``comm/torch.py:455``)."""
+    assert is_initialized(), "DeepSpeed backend not set, please initialize it using init_process_group()"
+    try:
+        from torch.distributed._symmetric_memory import enable_symm_mem_for_group as _enable
+    except Exception as e:  # noqa: BLE001
+        raise RuntimeError(f"Backend {get_backend()} does not support symmetric memory initialization") from e
+    _enable(group_name)
+
+
+def has_all_reduce_coalesced():
+    return hasattr(dist, "all_reduce_coalesced")
+
+
+def has_coalescing_manager():
+    return hasattr(dist.distributed_c10d, "_coalescing_manager")
+
+
+def all_gather_coalesced(output_tensors, input_tensors, group=None, async_op=False):
+    """``output_tensors[i]`` (list of world tensors, or one flat tensor) receives ``input_tensors[i]`` of every rank;
+    the gathers are issued back to back and, with a coalescing manager, as one group launch."""
+    assert is_initialized(), "DeepSpeed backend not set, please initialize it using init_process_group()"
+    works = []
+    for out, inp in zip(output_tensors, input_tensors):
+        if isinstance(out, (list, tuple)):
+            works.append(dist.all_gather(list(out), inp, group=group, async_op=True))
+        else:
+            works.append(dist.all_gather_into_tensor(out, inp, group=group, async_op=True))
+    if async_op:
+        return works
+    for w in works:
+        w.wait()
+    return None
+
+
+def has_comm_data():
+    """Has the comms logger recorded anything yet?"""
+    return comms_logger.has_data()
+
+
+def get_comm_operation_count():
+    return comms_logger.get_total_operations()
+
+
+def get_logged_comm_ops():
+    return comms_logger.get_operation_names()
 
 
 def init_device_mesh(mesh_shape, mesh_dim_names):

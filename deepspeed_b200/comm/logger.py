@@ -67,6 +67,15 @@ class CommsLogger:
     def reset(self):
         self.comms_dict = {}
 
+    def has_data(self):
+        return any(per_op for per_op in self.comms_dict.values())
+
+    def get_total_operations(self):
+        return sum(ent[0] for per_op in self.comms_dict.values() for ent in per_op.values())
+
+    def get_operation_names(self):
+        return [name for name, per_op in self.comms_dict.items() if per_op]
+
     def append(self, raw_name, record_name, latency_ms, msg_size, world):
         msg_size, algbw, busbw = calc_bw_log(raw_name, msg_size, latency_ms, world)
         per_op = self.comms_dict.setdefault(record_name, {})

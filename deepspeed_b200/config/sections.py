@@ -473,3 +473,26 @@ class TimersThroughputConfig(DeepSpeedConfigModel):
 
 class TimersConfig(DeepSpeedConfigModel):
     throughput: TimersThroughputConfig = Field(default_factory=TimersThroughputConfig)
+
+
+# ---- reference helpers of ``runtime/zero/config.py`` ---------------------------------------------------------
+ZERO_OPTIMIZATION = "zero_optimization"
+
+
+def read_zero_config_deprecated(param_dict):
+    """``"zero_optimization": true`` (pre-0.3 format): stage 1, bucket size from ``allgather_size``."""
+    import logging
+    cfg = {"stage": 1 if param_dict[ZERO_OPTIMIZATION] else 0}
+    if cfg["stage"] > 0:
+        cfg["allgather_bucket_size"] = param_dict.get("allgather_size", 5e8)
+    logging.getLogger("DeepSpeed").warning(
+        "DeepSpeedConfig: this format of ZeRO optimization setup is deprecated. Please use "
+        '"zero_optimization": {"stage": [0|1|2|3], ...}')
+    return cfg
+
+
+def get_zero_config(param_dict):
+    section = param_dict.get(ZERO_OPTIMIZATION, {})
+    if isinstance(section, bool):
+        section = read_zero_config_deprecated(param_dict)
+    return DeepSpeedZeroConfig(**section)

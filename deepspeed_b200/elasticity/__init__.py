@@ -4,3 +4,5 @@ from .elasticity import (compute_elastic_config, elasticity_enabled, ensure_immu
                          ElasticityIncompatibleWorldSize, get_valid_gpus, get_best_candidates)
 from .utils import is_torch_elastic_compatible  # noqa: F401,E402
 from .constants import ENABLED, ENABLED_DEFAULT, ELASTICITY  # noqa: F401,E402
+if is_torch_elastic_compatible():
+    from .elastic_agent import DSElasticAgent  # noqa: F401,E402

@@ -49,9 +49,48 @@ def debug_report():
             ("device", torch.cuda.get_device_name(0) if torch.cuda.is_available() else "cpu"),
             ("nccl", ".".join(map(str, torch.cuda.nccl.version())) if torch.cuda.is_available() else "n/a"),
             ("python", sys.version.split()[0])]
+    shm, warns = get_shm_size()
+    rows.append(("shared memory (/dev/shm) size", shm))
     print("DeepSpeed-B200 general environment info:")
     for name, value in rows:
         print(f"{name} {'.' * max(1, 34 - len(name))} {value}")
+    for w in warns or []:
+        print(w)
+
+
+def human_readable_size(size):
+    units = ["B", "KB", "MB", "GB", "TB"]
+    i = 0
+    while size >= 1024 and i < len(units) - 1:
+        size /= 1024
+        i += 1
+    return f"{size:.2f} {units[i]}"
+
+
+def get_shm_size():
+    """(human readable size of /dev/shm, list of warnings): NCCL and the shared-memory all-reduce need it to be large
+    enough (docker defaults to 64 MB)."""
+    try:
+        st = os.statvfs("/dev/shm")
+    except (OSError, ValueError, AttributeError):
+        return "UNKNOWN", None
+    size = st.f_frsize * st.f_blocks
+    warn = []
+    if size < 512 * 1024**2:
+        warn.append(" [WARNING] /dev/shm size might be too small, if running in docker increase to at least "
+                    "--shm-size='1gb'")
+        warn.append(" [WARNING] see more details about NCCL requirements: "
+                    "https://docs.nvidia.com/deeplearning/nccl/user-guide/docs/troubleshooting.html#sharing-data")
+    return human_readable_size(size), warn
+
+
+def parse_arguments():
+    import argparse
+    p = argparse.ArgumentParser()
+    p.add_argument("--hide_operator_status", action="store_true",
+                   help="Suppress display of installation and compatibility statuses of the operators.")
+    p.add_argument("--hide_errors_and_warnings", action="store_true", help="Suppress warning and error messages.")
+    return p.parse_args()
 
 
 def main(hide_operator_status=False, hide_errors_and_warnings=False):
@@ -61,11 +100,7 @@ def main(hide_operator_status=False, hide_errors_and_warnings=False):
 
 
 def cli_main():
-    import argparse
-    p = argparse.ArgumentParser()
-    p.add_argument("--hide_operator_status", action="store_true")
-    p.add_argument("--hide_errors_and_warnings", action="store_true")
-    a = p.parse_args()
+    a = parse_arguments()
     main(a.hide_operator_status, a.hide_errors_and_warnings)
 
 

@@ -100,6 +100,128 @@ class InferenceEngine(nn.Module):
         from .v2.engine_v2 import greedy_generate
         return greedy_generate(self.module, *inputs, **kwargs)
 
+    # ---- latency profiling (reference engine.py:197, :564) ------------------------------------------------
+    def profile_model_time(self, use_cuda_events=True):
+        """Record the latency of every forward; read (and clear) with :meth:`model_times`."""
+        if not getattr(self, "model_profile_enabled", False):
+            self.module.register_forward_pre_hook(self._pre_forward_hook)
+            self.module.register_forward_hook(self._post_forward_hook)
+        self.model_profile_enabled = True
+        self.use_cuda_events = bool(use_cuda_events) and torch.cuda.is_available()
+        self._model_times = []
+
+    def _pre_forward_hook(self, module, *inputs, **kwargs):
+        if self.use_cuda_events:
+            self._ev0 = torch.cuda.Event(enable_timing=True)
+            self._ev0.record()
+        else:
+            import time
+            if torch.cuda.is_available():
+                torch.cuda.synchronize()
+            self._start = time.time()
+
+    def _post_forward_hook(self, module, input, output):
+        if self.use_cuda_events:
+            ev1 = torch.cuda.Event(enable_timing=True)
+            ev1.record()
+            ev1.synchronize()
+            ms = self._ev0.elapsed_time(ev1)
+        else:
+            import time
+            if torch.cuda.is_available():
+                torch.cuda.synchronize()
+            ms = (time.time() - self._start) * 1e3
+        self._model_times.append(ms)
+
+    def model_times(self):
+        assert getattr(self, "model_profile_enabled", False), "model profiling is not enabled"
+        times, self._model_times = self._model_times, []
+        return times
+
+    # ---- torch.compile passthrough, teardown ----------------------------------------------------------------
+    def compile(self, backend=None, compile_kwargs=None):
+        if getattr(self, "_is_compiled", False):
+            return
+        self.module.compile(backend=backend or "inductor", **(compile_kwargs or {}))
+        self._is_compiled = True
+
+    @property
+    def is_compiled(self):
+        return getattr(self, "_is_compiled", False)
+
+    def destroy(self):
+        """Drop captured graphs and the KV caches / layer counters of injected v1 layers."""
+        self._graphs = {}
+        from ..ops.transformer.inference.ds_transformer import DeepSpeedSelfAttention, DeepSpeedTransformerInference
+        DeepSpeedTransformerInference.reset_cache(self.module)
+        DeepSpeedTransformerInference.layer_id = 0
+        DeepSpeedSelfAttention.num_layers = 0
+
+    def load_model_with_checkpoint(self, r_module):
+        """Fill ``r_module`` from the checkpoint given in the config (reference ``engine.py:load_model_with_checkpoint``:
+        walks the module tree loading each layer's tensors, slicing them for tensor parallelism)."""
+        ckpt = self._config.checkpoint
+        self._load_checkpoint(ckpt)
+        return r_module
+
+    # ---- BLOOM / MPT helpers: head-sharded alibi and attention bias under tensor parallelism ------------------
+    def _head_slice(self):
+        if self.mp_world_size <= 1:
+            return None
+        cfg = getattr(self.module, "config", None)
+        heads = next((getattr(cfg, n) for n in ("num_attention_heads", "n_head", "n_heads", "num_heads")
+                      if cfg is not None and getattr(cfg, n, None) is not None), None)
+        if heads is None:
+            return None
+        from ..sequence.layer import head_shard_sizes
+        sizes = head_shard_sizes(heads, self.mp_world_size)
+        r = dist.get_rank(self.mp_group)
+        return slice(sum(sizes[:r]), sum(sizes[:r + 1])), heads
+
+    def remove_mask_prepare_for_bloom(self):
+        tr = getattr(self.module, "transformer", None)
+        if tr is not None and hasattr(tr, "_prepare_attn_mask"):
+            tr._prepare_attn_mask = lambda attention_mask, *args, **kwargs: attention_mask
+
+    def _wrap_head_sharded(self, owner, name, head_dim_of):
+        """Replace ``owner.<name>`` by a version that returns only this rank's heads of the full-head tensor."""
+        hs = self._head_slice()
+        fn = getattr(owner, name, None)
+        if hs is None or fn is None or getattr(fn, "_ds_head_sharded", False):
+            return
+        sl, heads = hs
+
+        def sharded(*args, **kwargs):
+            out = fn(*args, **kwargs)
+            if not torch.is_tensor(out):
+                return out
+            d = head_dim_of(out, heads)
+            if d is None:
+                return out
+            if out.shape[d] == heads:
+                return out.narrow(d, sl.start, sl.stop - sl.start)
+            b = out.shape[d] // heads  # [batch * heads, ...] layout (BLOOM)
+            shaped = out.reshape(b, heads, *out.shape[d + 1:])
+            return shaped[:, sl].reshape(-1, *out.shape[d + 1:])
+
+        sharded._ds_head_sharded = True
+        setattr(owner, name, sharded)
+
+    def build_alibi_tensor(self):
+        find = lambda out, heads: next((i for i, n in enumerate(out.shape) if n == heads or (i == 0 and n % heads == 0
+                                                                                             and n != 1)), None)  # noqa: E731
+        for owner_name, fn_name in (("transformer", "build_alibi_tensor"), ("transformer", "build_mpt_alibi_tensor"),
+                                    ("model", "get_alibi_mask")):
+            owner = getattr(self.module, owner_name, None)
+            if owner is not None and hasattr(owner, fn_name):
+                self._wrap_head_sharded(owner, fn_name, find)
+
+    def build_attn_bias(self):
+        owner = getattr(self.module, "transformer", None)
+        if owner is not None and hasattr(owner, "_attn_bias"):
+            self._wrap_head_sharded(owner, "_attn_bias",
+                                    lambda out, heads: next((i for i, n in enumerate(out.shape) if n == heads), None))
+
     def __getattr__(self, name):
         try:
             return super().__getattr__(name)

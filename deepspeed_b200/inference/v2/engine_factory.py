@@ -10,7 +10,7 @@ import pickle
 import torch
 
 from ...config.base import DeepSpeedConfigModel
-from .engine_v2 import InferenceEngineV2, RaggedInferenceEngineConfig
+from .engine_v2 import InferenceEngineV2, RaggedInferenceEngineConfig  # noqa: F401
 from .model_implementations.policies import build_hf_model
 
 DS_MODEL_CONFIG = "ds_model_config.pkl"

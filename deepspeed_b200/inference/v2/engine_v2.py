@@ -85,6 +85,25 @@ class InferenceEngineV2:
     def _sm(self):
         return self.native_state if self.native_state is not None else self.state_manager
 
+    @property
+    def n_kv_cache_groups(self):
+        """KV cache groups (one: every layer shares the block geometry)."""
+        return 1
+
+    def get_remaining_block_capacity(self, uid):
+        """Tokens that still fit into the last KV block already allocated to sequence ``uid`` (0 if unknown)."""
+        bs = self.config.kv_block_size
+        if self.native_state is not None:
+            seen = self.native_state.seen_tokens(uid)
+            if seen < 0:
+                return 0
+        else:
+            seq = self.state_manager.get_sequence(uid)
+            if seq is None:
+                return 0
+            seen = seq.seen_tokens
+        return (-seen) % bs
+
     def serialize(self, save_path):
         """Write the model so that ``build_engine_from_ds_checkpoint`` can rebuild the engine without the original
         HuggingFace files (reference ``engine_v2.py:251``): parameters, metadata naming the policy, pickled config."""

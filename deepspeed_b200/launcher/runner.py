@@ -189,6 +189,48 @@ def _collect_exports():
     return exports
 
 
+def parse_node_config(node_config):
+    """``"worker-1:0,2"`` -> ``("worker-1", [0, 2])``; a bare host name means all of its slots (``[]``)."""
+    if ":" not in node_config:
+        return node_config, []
+    host, slots = node_config.split(":")
+    return host, [int(x) for x in slots.split(",")]
+
+
+def parse_node_config_list(node_config_list):
+    """``"worker-0@worker-1:0,2"`` -> ``{host: sorted slot list}`` (the include / exclude string syntax)."""
+    out = collections.defaultdict(list)
+    for item in node_config_list.split("@"):
+        host, slots = parse_node_config(item)
+        out[host] += slots
+    return {h: sorted(set(v)) for h, v in out.items()}
+
+
+def parse_num_nodes(str_num_nodes, elastic_training):
+    """``"4"`` -> (4, -1); ``"2:8"`` (MIN:MAX) only with elastic training."""
+    parts = str(str_num_nodes).split(":")
+    if len(parts) == 1:
+        return int(parts[0]), -1
+    if len(parts) == 2 and elastic_training:
+        return int(parts[0]), int(parts[1])
+    if len(parts) == 2:
+        raise RuntimeError("MIN:MAX format is only supported in elastic training")
+    raise RuntimeError(f"num_nodes {str_num_nodes} is not in MIN:MAX format")
+
+
+def run_autotuning(args, active_resources):
+    """``deepspeed --autotuning tune|run script.py --deepspeed_config ds.json`` (reference ``runner.py:407``)."""
+    from ..autotuning import Autotuner
+    tuner = Autotuner(args, active_resources)
+    logger.info("[Start] Running autotuning")
+    tuner.tune()
+    tuner.print_tuning_results()
+    logger.info("[End] Running autotuning")
+    tuner.write_optimal_config()
+    if args.autotuning == "run":
+        tuner.run_after_tuning()
+
+
 def main(args=None):
     args = parse_args(args)
     resource_pool = fetch_hostfile(args.hostfile)
@@ -202,13 +244,7 @@ def main(args=None):
     if args.num_gpus > 0:
         active = collections.OrderedDict((h, list(range(args.num_gpus))) for h in active)
     if args.autotuning:
-        # `deepspeed --autotuning tune|run script.py --deepspeed_config ds.json` (reference runner.py:run_autotuning)
-        from ..autotuning import Autotuner
-        tuner = Autotuner(args, active)
-        tuner.tune()
-        tuner.print_tuning_results()
-        if args.autotuning == "run":
-            tuner.run_after_tuning()
+        run_autotuning(args, active)
         return
     multi_node = args.force_multi or len(active) > 1
     if not args.master_addr:

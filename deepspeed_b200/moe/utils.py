@@ -80,3 +80,20 @@ def split_params_into_different_moe_groups_for_optimizer(param_groups, max_group
 
 def is_moe_param_group(param_group):
     return param_group.get("moe", False)
+
+
+def configure_moe_param_groups(model_parameters):
+    """Param groups an optimizer can be built from when the model has experts (reference ``moe/utils.py:155``): a plain
+    list of parameters becomes one dense group that is then split into dense + per-expert-group groups; existing
+    groups are split unless they already carry the ``moe`` marker."""
+    assert isinstance(model_parameters, list), "model_parameters must be a list"
+    for p in model_parameters:
+        if not isinstance(p, (torch.Tensor, dict)):
+            raise TypeError("param argument that would be given to the optimizer should be an iterable of Tensors or "
+                            f"dicts, but got {type(p)}")
+    first = model_parameters[0]
+    if isinstance(first, torch.nn.Parameter):
+        return split_params_into_different_moe_groups_for_optimizer({"params": model_parameters, "name": "dense-params"})
+    if not any("moe" in g for g in model_parameters):
+        return split_params_into_different_moe_groups_for_optimizer(model_parameters)
+    return model_parameters

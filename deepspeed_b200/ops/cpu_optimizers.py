@@ -113,6 +113,63 @@ class DeepSpeedCPUAdam(_CPUOptimizer):
             group["step"] = group.get("step", 1) - 1
 
 
+    # ---- sub-group form used by SuperOffload (reference ``cpu_adam.py:166-243``): the state lives under an integer
+    # sub-group id instead of under the parameter, so the same flat fp32 buffer object can be stepped in slices ----------
+    def _subgroup_state(self, subgroup_id, p):
+        st = self.state[subgroup_id]
+        if len(st) == 0:
+            st["step"] = 0
+            dt = torch.float if self.fp32_optimizer_states else p.dtype
+            st["exp_avg"] = torch.zeros_like(p.data, dtype=dt, device="cpu")
+            st["exp_avg_sq"] = torch.zeros_like(p.data, dtype=dt, device="cpu")
+        return st
+
+    @torch.no_grad()
+    def step_subgroup(self, subgroup_id, closure=None):
+        """One Adam step of the parameters that currently hold a gradient, with the state of ``subgroup_id``."""
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        for group in self.param_groups:
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                assert p.device.type == "cpu", f"CPUAdam param is on {p.device} and must be 'cpu', make sure you " \
+                    "enabled 'offload_optimizer': 'cpu' in your ZeRO config."
+                st = self._subgroup_state(subgroup_id, p)
+                st["step"] += 1
+                g = p.grad.data.contiguous()
+                self._update(group, p.data, g, st, None, 1.0)
+        return loss
+
+    @torch.no_grad()
+    def rollback_subgroup(self, sub_group_id, closure=None):
+        """Undo the last :meth:`step_subgroup` of ``sub_group_id`` (same gradients must still be attached)."""
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        if sub_group_id not in self.state or len(self.state[sub_group_id]) == 0:
+            raise RuntimeError(f"Cannot rollback optimizer state for sub_group_id {sub_group_id} as it has not been "
+                               "initialized.")
+        st = self.state[sub_group_id]
+        if st.get("step", 0) <= 0:
+            raise RuntimeError(f"Cannot rollback sub_group_id {sub_group_id}: step count is {st.get('step', 0)}")
+        for group in self.param_groups:
+            b1, b2 = group["betas"]
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                g = p.grad.data.contiguous()
+                self._lib.dsb200_cpu_adam_rollback(_p(p.data), _p(g), _DT[g.dtype], _p(st["exp_avg"]),
+                                                   _p(st["exp_avg_sq"]), p.numel(), group["lr"], b1, b2, group["eps"],
+                                                   group["weight_decay"], st["step"], int(group["bias_correction"]),
+                                                   int(self.adam_w_mode), 1.0)
+                st["step"] -= 1
+        return loss
+
+
 class DeepSpeedCPUAdagrad(_CPUOptimizer):
 
     def __init__(self, model_params, lr=1e-2, eps=1e-10, weight_decay=0, amsgrad=False, fp32_optimizer_states=True):

@@ -125,6 +125,15 @@ class FlopsProfiler:
         for h in self._hooks:
             h.remove()
         self._hooks = []
+        # the reference keeps its counters ON the modules; code written against it reads these attributes. Here the
+        # per-module numbers are inclusive of the children, the attributes hold the module's OWN share so that
+        # get_module_flops / get_module_macs (which add the children up) give the inclusive value again.
+        for m in self.model.modules():
+            kids_f = sum(self.flops[id(c)] for c in m.children())
+            m.__flops__ = max(0, self.flops[id(m)] - kids_f)
+            m.__macs__ = m.__flops__ // 2
+            m.__duration__ = self.latency[id(m)]
+            m.__params__ = sum(getattr(q, "ds_numel", q.numel()) for q in m.parameters(recurse=False))
 
     def reset_profile(self):
         self.flops.clear()
@@ -150,6 +159,33 @@ class FlopsProfiler:
     def get_total_params(self, as_string=False):
         n = sum(getattr(p, "ds_numel", p.numel()) for p in self.model.parameters())
         return number_to_string(n) if as_string else n
+
+    def print_model_aggregated_profile(self, module_depth=-1, top_modules=1):
+        """Top module CLASSES by parameters, MACs and forward latency at every depth up to ``module_depth`` (-1: all)."""
+        if not hasattr(self.model, "__flops__"):
+            print("no __flops__ attribute in the model, call this function after start_profile and before end_profile")
+            return
+        info = {}
+
+        def walk(m, depth):
+            row = info.setdefault(depth, {}).setdefault(type(m).__name__, [0, 0, 0.0])
+            row[0] += get_module_macs(m)
+            row[1] += sum(getattr(q, "ds_numel", q.numel()) for q in m.parameters())
+            row[2] += get_module_duration(m)
+            for c in m.children():
+                walk(c, depth + 1)
+
+        walk(self.model, 0)
+        depth = len(info) - 1 if module_depth == -1 else min(module_depth, len(info) - 1)
+        print(f"Top {top_modules} modules in terms of params, MACs or fwd latency at different model depths:")
+        for d in range(depth + 1):
+            n = min(top_modules, len(info[d]))
+            top = lambda col, fmt: {k: fmt(v[col]) for k, v in sorted(info[d].items(), key=lambda kv: kv[1][col],  # noqa: E731
+                                                                      reverse=True)[:n]}
+            print(f"depth {d}:")
+            print(f"    params      - {top(1, params_to_string)}")
+            print(f"    MACs        - {top(0, macs_to_string)}")
+            print(f"    fwd latency - {top(2, duration_to_string)}")
 
     def print_model_profile(self, profile_step=1, module_depth=-1, top_modules=1, detailed=True, output_file=None):
         lines = []
@@ -191,6 +227,50 @@ def number_to_string(num, units=None, precision=2):
         if units == unit or (units is None and abs(num) >= scale):
             return f"{num / scale:.{precision}f} {unit}"
     return f"{num:.{precision}f} " if isinstance(num, float) else f"{num} "
+
+
+def flops_to_string(flops, units=None, precision=2):
+    return f"{number_to_string(flops, units=units, precision=precision)}FLOPS"
+
+
+def macs_to_string(macs, units=None, precision=2):
+    return f"{number_to_string(macs, units=units, precision=precision)}MACs"
+
+
+def bytes_to_string(b, units=None, precision=2):
+    return f"{number_to_string(b, units=units, precision=precision)}B"
+
+
+def params_to_string(params_num, units=None, precision=2):
+    """Parameter counts use "B" (billion) where the other quantities use "G"."""
+    units = units.replace("B", "G") if units else units
+    return number_to_string(params_num, units=units, precision=precision).replace("G", "B").strip()
+
+
+def get_module_flops(module):
+    """Inclusive FLOPs of a profiled module: its own share plus its children's."""
+    return getattr(module, "__flops__", 0) + sum(get_module_flops(c) for c in module.children())
+
+
+def get_module_macs(module):
+    return getattr(module, "__macs__", 0) + sum(get_module_macs(c) for c in module.children())
+
+
+def get_module_duration(module):
+    d = getattr(module, "__duration__", 0)
+    return d if d else sum(get_module_duration(c) for c in module.children())  # containers never run forward()
+
+
+def wrapFunc(func, funcFlopCompute):
+    """Reference hook point for counting a custom functional: ``funcFlopCompute(*args, **kw) -> (flops, macs)``. Counting
+    here happens at the ATen level (every op a custom functional dispatches is already seen), so the wrapper only
+    calls ``funcFlopCompute`` for its side effects when a profiler is active and forwards to ``func``."""
+
+    def wrapped(*args, **kwds):
+        return func(*args, **kwds)
+
+    wrapped.__wrapped__ = func
+    return wrapped
 
 
 def duration_to_string(d, units=None, precision=2):

@@ -309,3 +309,117 @@ def configure(mpu_, deepspeed_config=None, partition_activations=None, contiguou
 
 def is_configured():
     return _configured
+
+
+# ---- helper names of the reference module (``activation_checkpointing/checkpointing.py:78-470``) -------------------
+def detach_variable(inputs, device=None):
+    """Detached copies (optionally on ``device``) that keep ``requires_grad``: what backward recomputes from."""
+    if not isinstance(inputs, tuple):
+        raise RuntimeError("Only tuple of tensors is supported. Got Unsupported input type: ", type(inputs).__name__)
+    out = []
+    for t in inputs:
+        if not torch.is_tensor(t):
+            out.append(t)
+            continue
+        x = (t.to(device=device) if device is not None else t).detach()
+        x.requires_grad = t.requires_grad
+        out.append(x)
+    return tuple(out)
+
+
+def extract_tensors(all_objects):
+    """Split a list / tuple into (tensors, non-tensors, is-tensor flags); order preserved within each part."""
+    tensors = [v for v in all_objects if torch.is_tensor(v)]
+    others = [v for v in all_objects if not torch.is_tensor(v)]
+    flags = [torch.is_tensor(v) for v in all_objects]
+    if type(all_objects) is tuple:
+        return tuple(tensors), tuple(others), tuple(flags)
+    return tensors, others, flags
+
+
+def merge_tensors(tensor_objects, non_tensor_objects, tensor_flags):
+    """Inverse of :func:`extract_tensors`."""
+    it_t, it_o = iter(tensor_objects), iter(non_tensor_objects)
+    return tuple(next(it_t) if flag else next(it_o) for flag in tensor_flags)
+
+
+def is_activation_to_checkpoint(item):
+    """Floating-point tensors with at least one element per model-parallel rank, unless marked ``no_checkpointing``."""
+    size = _mp_info()[1] or 1
+    return torch.is_tensor(item) and item.is_floating_point() and item.numel() >= size and \
+        not getattr(item, "no_checkpointing", False)
+
+
+def get_partition_size(item):
+    size = _mp_info()[1] or 1
+    assert item.numel() % size == 0, "Doesn't handle if partition activation if item is not divisible by mp size"
+    return item.numel() // size
+
+
+def get_partition_start(item):
+    rank, size, _ = _mp_info()
+    return int(item.numel() / (size or 1) * (rank or 0))
+
+
+def partition_activations(args, cpu_checkpoint=False, contiguous_checkpoint=False):
+    """This model-parallel rank's slice of every activation to checkpoint (other arguments unchanged), optionally on
+    the host."""
+    out = []
+    for item in args:
+        if not is_activation_to_checkpoint(item):
+            out.append(item)
+            continue
+        n = get_partition_size(item)
+        part = item.detach().contiguous().view(-1).narrow(0, get_partition_start(item), n).clone()
+        out.append(part.to("cpu") if cpu_checkpoint else part)
+    return out
+
+
+def get_partitioned_activations_for_backward(args, inputs, contiguous_checkpoint=False):
+    """Interleave each partitioned activation with its original size (as the reference's saved-tensor list does), so
+    that :func:`gather_partitioned_activations` can rebuild the full tensors."""
+    out = []
+    for arg, inp in zip(args, inputs):
+        if not is_activation_to_checkpoint(arg):
+            out.append(arg)
+            out.append(None)
+            continue
+        out.append(inp)
+        out.append(torch.tensor(arg.size()))
+    return out
+
+
+def gather_partitioned_activations(tensors, device=None):
+    """Inverse of the two functions above: all-gather each (slice, size) pair over the model-parallel group."""
+    assert len(tensors) % 2 == 0, f"Expected even count of tensors, instead got {len(tensors)}"
+    rank, size, group = _mp_info()
+    out = []
+    for i in range(len(tensors) // 2):
+        item, shape = tensors[2 * i], tensors[2 * i + 1]
+        if shape is None or not torch.is_tensor(item):
+            out.append(item)
+            continue
+        shape = [int(s) for s in shape.tolist()]
+        if device is not None:
+            item = item.to(device)
+        if group is None or (size or 1) == 1:
+            out.append(item.view(shape))
+            continue
+        full = item.new_empty(item.numel() * size)
+        dist.all_gather_into_tensor(full, item.contiguous(), group=group)
+        out.append(full.view(shape))
+    return tuple(out)
+
+
+def get_cpu_activations_for_backward(args, inputs):
+    """Host copies of the activations to checkpoint (``cpu_checkpointing`` without partitioning)."""
+    return [inp.to("cpu") if is_activation_to_checkpoint(arg) else arg for arg, inp in zip(args, inputs)]
+
+
+get_offloaded_activations_for_backward = get_cpu_activations_for_backward
+
+
+def restore_offloaded_activations(tensors, device=None):
+    dev = device if device is not None else (torch.device("cuda", torch.cuda.current_device())
+                                             if torch.cuda.is_available() else torch.device("cpu"))
+    return tuple(t.to(dev) if torch.is_tensor(t) and t.device != dev and t.is_floating_point() else t for t in tensors)

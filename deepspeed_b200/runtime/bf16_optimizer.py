@@ -20,3 +20,37 @@ class BF16_Optimizer(ZeroShardedOptimizer):
                          dtype=torch.bfloat16, grad_accum_dtype=grad_acc_dtype or torch.float32, timers=timers)
         self.bf16_groups = [list(g) for g in self._orig_param_groups]
         self.immediate_grad_update = immediate_grad_update
+
+    # ---- reference method names (``bf16_optimizer.py:37-590``) over the flat-unit state ----------------------------
+    @torch.no_grad()
+    def clear_hp_grads(self):
+        """Zero the fp32 gradient accumulators."""
+        for st in self.storages.values():
+            if st.grad is not None:
+                st.grad.zero_()
+        for u in self.units:
+            u.has_grad_data = False
+
+    def clear_lp_grads(self, set_to_none=False):
+        """Drop / zero the low-precision ``.grad`` of the module parameters (they are consumed by the hooks anyway)."""
+        for group in self.bf16_groups:
+            for p in group:
+                if set_to_none or p.grad is None:
+                    p.grad = None
+                else:
+                    p.grad.zero_()
+
+    def update_hp_grads(self, clear_lp_grads=False):
+        """Gradients move into the fp32 accumulators as they are produced (per-parameter hooks), so at this point there
+        is nothing left to copy; kept for callers of the reference's two-phase API."""
+        if clear_lp_grads:
+            self.clear_lp_grads()
+
+    def get_grads_for_reduction(self):
+        """(dense gradient tensors, {expert group: tensors}) that a plain data-parallel all-reduce would cover."""
+        dense = [u.full_grad for u in self.units if u.full_grad is not None]
+        return dense, {}
+
+    def get_grads_for_norm(self, for_clipping=False):
+        """This rank's fp32 gradient shards (their norms combine to the global gradient norm)."""
+        return [st.grad for st in self.storages.values() if st.grad is not None]

@@ -111,3 +111,60 @@ def CreateLossScaler(dtype, static_loss_scale, dynamic_scaling, dynamic_loss_arg
 # reference's tools/engine (``deepspeed.runtime.fp16.loss_scaler``; resolved here by the ``deepspeed`` alias package).
 for _cls in (LossScalerBase, LossScaler, DynamicLossScaler):
     _cls.__module__ = "deepspeed.runtime.fp16.loss_scaler"
+
+
+# ---- loss-scale bookkeeping of the fp16 optimizer wrappers (reference ``fp16/loss_scaler.py:39-122``) ---------
+from dataclasses import dataclass  # noqa: E402
+from enum import Enum  # noqa: E402
+
+
+class LossScaleProfile(str, Enum):
+    FUSED = "fused"  # FP16_Optimizer: starts at 2^32
+    UNFUSED = "unfused"  # FP16_UnfusedOptimizer: starts at 2^16, may go below 1
+
+
+@dataclass(frozen=True)
+class LossScaleProfileDefaults:
+    initial_dynamic_scale: float
+    default_scale_window: int
+    default_min_loss_scale: float
+    scale_factor: float
+
+
+LOSS_SCALE_PROFILE_DEFAULTS = {
+    LossScaleProfile.FUSED: LossScaleProfileDefaults(2**32, 1000, 1, 2.0),
+    LossScaleProfile.UNFUSED: LossScaleProfileDefaults(1.0 * 2**16, 1000, 0.25, 2.0),
+}
+
+
+class LossScaleConfig:
+    """Resolved loss-scaling state: no scaling unless the low-precision dtype is fp16; static scale, or dynamic with
+    the profile's defaults / the user's ``dynamic_loss_args`` (``init_scale``, ``scale_window``, ``min_scale``)."""
+
+    def __init__(self, low_precision_dtype, dynamic_loss_scale, static_loss_scale, dynamic_loss_args, *,
+                 profile=LossScaleProfile.FUSED, initial_dynamic_scale=None):
+        import torch
+        d = LOSS_SCALE_PROFILE_DEFAULTS[profile]
+        self.use_grad_scaling = low_precision_dtype == torch.float16
+        self.dynamic_loss_scale = False
+        self.cur_iter, self.cur_scale = 0, 1.0
+        self.last_overflow_iter = self.scale_factor = self.scale_window = self.min_loss_scale = None
+        if not self.use_grad_scaling:
+            return
+        self.cur_scale = static_loss_scale
+        if not dynamic_loss_scale:
+            return
+        self.dynamic_loss_scale = True
+        self.last_overflow_iter = -1
+        self.scale_factor = d.scale_factor
+        if dynamic_loss_args is None:
+            self.cur_scale = d.initial_dynamic_scale if initial_dynamic_scale is None else initial_dynamic_scale
+            self.scale_window, self.min_loss_scale = d.default_scale_window, d.default_min_loss_scale
+        else:
+            self.cur_scale = dynamic_loss_args[INITIAL_LOSS_SCALE]
+            self.scale_window = dynamic_loss_args[SCALE_WINDOW]
+            self.min_loss_scale = dynamic_loss_args[MIN_LOSS_SCALE]
+
+
+def to_python_float(t):
+    return t.item() if hasattr(t, "item") else t[0]

@@ -344,3 +344,91 @@ def build_lr_scheduler(name, optimizer, params):
     if hasattr(torch.optim.lr_scheduler, name):
         return getattr(torch.optim.lr_scheduler, name)(get_torch_optimizer(optimizer), **params)
     raise ValueError(f"Unknown scheduler type {name}; valid: {VALID_LR_SCHEDULES} or torch.optim.lr_scheduler.*")
+
+
+# ---- command line <-> schedule config (reference ``lr_schedules.py:133-258``) -------------------------------
+CYCLE_FIRST_STEP_SIZE = "cycle_first_step_size"
+CYCLE_FIRST_STAIR_COUNT = "cycle_first_stair_count"
+CYCLE_SECOND_STEP_SIZE = "cycle_second_step_size"
+CYCLE_SECOND_STAIR_COUNT = "cycle_second_stair_count"
+DECAY_STEP_SIZE = "decay_step_size"
+DECAY_LR_RATE = "decay_lr_rate"
+CYCLE_MIN_MOM = "cycle_min_mom"
+CYCLE_MAX_MOM = "cycle_max_mom"
+DECAY_MOM_RATE = "decay_mom_rate"
+
+_LR_RANGE_KEYS = (LR_RANGE_TEST_MIN_LR, LR_RANGE_TEST_STEP_RATE, LR_RANGE_TEST_STEP_SIZE, LR_RANGE_TEST_STAIRCASE)
+_ONE_CYCLE_KEYS = (CYCLE_FIRST_STEP_SIZE, CYCLE_FIRST_STAIR_COUNT, CYCLE_SECOND_STEP_SIZE, CYCLE_SECOND_STAIR_COUNT,
+                   DECAY_STEP_SIZE, CYCLE_MIN_LR, CYCLE_MAX_LR, DECAY_LR_RATE, CYCLE_MIN_MOM, CYCLE_MAX_MOM,
+                   DECAY_MOM_RATE)
+_WARMUP_KEYS = (WARMUP_MIN_LR, WARMUP_MAX_LR, WARMUP_NUM_STEPS, WARMUP_TYPE)
+
+
+def _override(args, params, keys):
+    for k in keys:
+        v = getattr(args, k, None)
+        if v is not None:
+            params[k] = v
+
+
+def override_lr_range_test_params(args, params):
+    _override(args, params, _LR_RANGE_KEYS)
+
+
+def override_1cycle_params(args, params):
+    _override(args, params, _ONE_CYCLE_KEYS)
+
+
+def override_warmupLR_params(args, params):
+    _override(args, params, _WARMUP_KEYS)
+
+
+def override_params(args, params):
+    """Command-line values (``add_tuning_arguments``) win over the values of a schedule config."""
+    override_lr_range_test_params(args, params)
+    override_1cycle_params(args, params)
+    override_warmupLR_params(args, params)
+
+
+def get_config_from_args(args):
+    """``(scheduler config dict, None)`` built from ``--lr_schedule`` and its parameters, or ``(None, reason)``."""
+    name = getattr(args, LR_SCHEDULE, None)
+    if name is None:
+        return None, f"--{LR_SCHEDULE} not specified on command line"
+    if name not in VALID_LR_SCHEDULES:
+        return None, f"{name} is not supported LR schedule"
+    config = {"type": name, "params": {}}
+    if name == LR_RANGE_TEST:
+        override_lr_range_test_params(args, config["params"])
+    elif name == ONE_CYCLE:
+        override_1cycle_params(args, config["params"])
+    else:
+        override_warmupLR_params(args, config["params"])
+    return config, None
+
+
+def get_lr_from_config(config):
+    """The learning rate a schedule config starts the optimizer with: ``(lr, '')`` or ``(None, reason)``."""
+    if "type" not in config:
+        return None, "LR schedule type not defined in config"
+    if "params" not in config:
+        return None, "LR schedule params not defined in config"
+    name, params = config["type"], config["params"]
+    if name not in VALID_LR_SCHEDULES:
+        return None, f"{name} is not a valid LR schedule"
+    if name == LR_RANGE_TEST:
+        return params[LR_RANGE_TEST_MIN_LR], ""
+    if name == ONE_CYCLE:
+        return params[CYCLE_MAX_LR], ""
+    return params[WARMUP_MAX_LR], ""
+
+
+def update_lr(param_groups, lrs):
+    """Write ``lrs`` into the groups (in place for tensor learning rates, as capturable optimizers use)."""
+    import torch
+    for group, lr in zip(param_groups, lrs):
+        if torch.is_tensor(group["lr"]):
+            group["lr"].fill_(lr.squeeze() if torch.is_tensor(lr) else lr)
+        else:
+            group["lr"] = lr
+    return [g["lr"] for g in param_groups]

@@ -73,6 +73,32 @@ class PipelineEngine(DeepSpeedEngine):
     def set_batch_fn(self, fn):
         self.batch_fn = fn
 
+    def set_dataloader(self, loader):
+        """Only the first and last stage read data (inputs / labels)."""
+        if self.is_first_stage() or self.is_last_stage():
+            self.training_dataloader = loader
+            self.data_iterator = iter(self.training_dataloader)
+
+    def set_has_attention_mask(self, value):
+        assert isinstance(value, bool)
+        self.has_attention_mask = value
+
+    def get_pipeline_parallel_rank(self):
+        return self.stage_id
+
+    def get_additional_losses(self):
+        """Extra losses a module reported through ``PipelineModule.get_additional_losses`` (aggregated per batch)."""
+        return getattr(self, "agg_additional_losses", None)
+
+    def log_for_device(self, *msg):
+        print(f"RANK={dist.get_rank()} PIPE-ID={self.stage_id} DATA-ID={self.grid.data_parallel_id} "
+              f"MBATCH-ID={getattr(self, 'microbatch_id', 0)} STEP-ID={getattr(self, 'log_batch_step_id', -1)} ::",
+              *msg, flush=True)
+
+    def tput_log(self, *msg):
+        if self.global_rank == 0 and self.steps_per_print() and self.global_steps % self.steps_per_print() == 0:
+            print(*msg)
+
     def reset_activation_shape(self):
         self.first_output_send = True
         self.pipe_recv_buf = None

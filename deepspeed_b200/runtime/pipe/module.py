@@ -428,3 +428,12 @@ class PipelineModule(nn.Module):
 
     def get_additional_losses(self):
         return None
+
+    def partitions(self):
+        """Layer index boundaries of the stages: stage ``s`` owns layers ``[parts[s], parts[s + 1])``."""
+        return self.parts
+
+    def set_checkpoint_interval(self, interval):
+        """Activation-checkpoint every ``interval`` layers of this stage (0 = off); takes effect at the next forward."""
+        assert interval >= 0
+        self.activation_checkpoint_interval = interval

@@ -186,6 +186,25 @@ class PipelineParallelGrid:
     def get_model_parallel_group(self):
         return self.ds_model_proc_group
 
+    def get_pipeline_model_parallel_rank(self):
+        return self.get_pipe_parallel_rank()
+
+    def get_pipeline_model_parallel_world_size(self):
+        return self.get_pipe_parallel_world_size()
+
+    def get_data_parallel_group_ranks(self):
+        """Global ranks of this rank's data-parallel group."""
+        return self.dp_group
+
+    def get_tensor_model_parallel_rank(self):
+        return self.get_slice_parallel_rank()
+
+    def get_tensor_model_parallel_world_size(self):
+        return self.get_slice_parallel_world_size()
+
+    def get_tensor_model_parallel_group(self):
+        return self.get_slice_parallel_group()
+
     def get_slice_parallel_rank(self):
         return getattr(self._topo.get_coord(self.global_rank), "model", 0)
 

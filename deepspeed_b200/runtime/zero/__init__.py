@@ -20,3 +20,35 @@ from ...utils.z3_leaf_module import (set_z3_leaf_modules, unset_z3_leaf_modules,
 from .tiling import TiledLinear, TiledLinearReturnBias  # noqa: F401,E402
 from .param_status import (DeepSpeedTensorOverride, DeepSpeedZeRoOffload, ZeroParamStatus, ZeroParamType,  # noqa: F401,E402
                            unwrap_model_for_generation)
+from ...ops.quantizer import CUDAQuantizer  # noqa: F401,E402
+
+
+def print_rank_0(message, debug=False, force=False):
+    from ... import comm as _dist
+    if (debug or force) and (not _dist.is_initialized() or _dist.get_rank() == 0):
+        print(message)
+
+
+def debug_rank0(msg):
+    from ...utils.logging import logger
+    from ... import comm as _dist
+    if not _dist.is_initialized() or _dist.get_rank() == 0:
+        logger.debug(msg)
+
+
+def get_all_subclasses(cls, include_root=True):
+    out, todo = ([cls] if include_root else []), [cls]
+    while todo:
+        for sub in todo.pop().__subclasses__():
+            if sub not in out:
+                out.append(sub)
+                todo.append(sub)
+    return set(out)
+
+
+def free_param(param):
+    """Drop the gathered copy of a ZeRO-3 parameter (its shard stays)."""
+    import torch
+    assert not getattr(param, "ds_active_sub_modules", None), "parameter is still in use by a running sub-module"
+    param.data = torch.empty(0, dtype=param.dtype, device=param.device)
+    param.ds_status = ZeroParamStatus.NOT_AVAILABLE

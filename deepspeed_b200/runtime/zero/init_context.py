@@ -76,6 +76,22 @@ class Init:
     """Context manager: modules constructed inside have their parameters partitioned immediately."""
     num_params = 0
 
+    def get_partition_dp_group(self, param):
+        """The group ``param`` is partitioned over."""
+        return getattr(param, "ds_process_group", self.group)
+
+    def get_partition_rank(self):
+        """Rank inside the partition group (subclasses may override, e.g. MiCS)."""
+        return self.rank
+
+    @property
+    def num_partitions(self):
+        return self.world
+
+    def get_dp_process_group(self):
+        """The communication group with all data-parallel ranks."""
+        return self.group
+
     def __init__(self, module=None, data_parallel_group=None, mem_efficient_linear=True, remote_device=None,
                  pin_memory=False, config_dict_or_path=None, config=None, enabled=True, dtype=None, mpu=None,
                  zero_param_parallel_group=None, zero_quantized_weights=False,
@@ -321,3 +337,7 @@ def unregister_external_parameter(module, parameter):
     lst = module.__dict__.get("_ds_external_parameters", [])
     if parameter in lst:
         lst.remove(parameter)
+
+
+# names user code imports from the reference's ``runtime.zero.partition_parameters`` module
+from .param_status import DeepSpeedTensorOverride, ZeroParamStatus, ZeroParamType  # noqa: E402,F401

@@ -34,6 +34,7 @@ from ...utils.logging import log_dist, logger
 from ...utils.nvtx import instrument_w_nvtx
 from ..loss_scaler import CreateLossScaler
 from ..base_optimizer import ZeROOptimizer
+from .compat_api import ZeroCompatAPI
 from .units import FlatUnit, build_bucket_units, build_module_units
 
 import os as _os
@@ -64,7 +65,7 @@ class _Storage:
         self.lp = None
 
 
-class ZeroShardedOptimizer(ZeROOptimizer):
+class ZeroShardedOptimizer(ZeroCompatAPI, ZeROOptimizer):
     """See module docstring. ``optimizer`` is any ``torch.optim.Optimizer`` built over the model's params."""
 
     def __init__(self, module, optimizer, *, stage=1, dp_group=None, dp_world=1, dp_rank=0, sp_size=1,

@@ -147,12 +147,32 @@ def _get_model_parallel_rank():
     return _get("tp")[1].index(_rk())
 
 
+_MPU_TP_WORLD_SIZE = None  # overrides used by code that fakes a tensor-parallel context (reference groups.py:197,215)
+_MPU_TP_RANK = None
+
+
+def set_tensor_model_parallel_world_size(world_size):
+    global _MPU_TP_WORLD_SIZE
+    _MPU_TP_WORLD_SIZE = world_size
+
+
+def set_tensor_model_parallel_rank(rank):
+    global _MPU_TP_RANK
+    _MPU_TP_RANK = rank
+
+
+def get_tensor_model_parallel_world_size():
+    return _MPU_TP_WORLD_SIZE if _MPU_TP_WORLD_SIZE is not None else _get_model_parallel_world_size()
+
+
+def get_tensor_model_parallel_rank():
+    return _MPU_TP_RANK if _MPU_TP_RANK is not None else _get_model_parallel_rank()
+
+
 get_tensor_model_parallel_group = _get_model_parallel_group
-get_tensor_model_parallel_world_size = _get_model_parallel_world_size
-get_tensor_model_parallel_rank = _get_model_parallel_rank
 get_model_parallel_group = _get_model_parallel_group
-get_model_parallel_world_size = _get_model_parallel_world_size
-get_model_parallel_rank = _get_model_parallel_rank
+get_model_parallel_world_size = get_tensor_model_parallel_world_size
+get_model_parallel_rank = get_tensor_model_parallel_rank
 get_data_parallel_group = _get_data_parallel_group
 get_data_parallel_world_size = _get_data_parallel_world_size
 get_data_parallel_rank = _get_data_parallel_rank

@@ -258,3 +258,16 @@ def trim_mean(data, trim_percent):
     data = sorted(data)
     k = int(round(n * trim_percent))
     return sum(data[k:n - k]) / max(1, n - 2 * k)
+
+
+class CudaEventTimer:
+    """Elapsed device time between two recorded events (reference ``utils/timer.py:32``)."""
+
+    def __init__(self, start_event, end_event):
+        self.start_event, self.end_event = start_event, end_event
+
+    def get_elapsed_msec(self):
+        import torch
+        torch.cuda.current_stream().wait_event(self.end_event)
+        self.end_event.synchronize()
+        return self.start_event.elapsed_time(self.end_event)

@@ -222,3 +222,51 @@ def test_custom_compile_pass_edits_the_unit_plan():
     n_calls, launch_at, keys, active = run_distributed(_custom_pass, 2)[0]
     assert n_calls == 1 and launch_at == {} and active
     assert keys == ["drop_prefetch", "plan", "profile"]
+
+
+def _zero_compat(stage):
+    import deepspeed_b200 as ds
+    eng = _engine(stage, {"fp16": {"enabled": False}})
+    z = eng.optimizer
+    batches = random_batches(4, 4, 16, "cpu")
+    loss = eng(*batches[ds.comm.get_rank()])
+    eng.backward(loss)
+    p = next(iter(eng.module.parameters()))
+    ok = []
+    ok.append(not z.has_overflow())
+    g = z.get_fp32_grad_for_param(p)
+    ok.append(g.shape == tuple(getattr(p, "ds_shape", p.shape)) and float(g.abs().sum()) > 0)
+    z.update_fp32_grad_for_param_vectorized(lambda grad, param: grad * 0 + 2.0, [p])
+    ok.append(bool((z.get_fp32_grad_for_param(p) == 2.0).all()))
+    z.set_local_grad_for_param(torch.full_like(z.get_local_fp32_grad_for_param(p), float("inf")), p)
+    ok.append(z.has_overflow() or z.get_local_fp32_grad_for_param(p).numel() == 0 and z.has_overflow())
+    z.check_overflow()
+    ok.append(z.overflow)
+    z.set_local_grad_for_param(torch.zeros_like(z.get_local_fp32_grad_for_param(p)), p)
+    eng.step()
+    z.set_lr(0.5)
+    ok.append(z.get_lr() == 0.5 and eng.get_lr()[0] == 0.5)
+    z.override_loss_scale(128.0)
+    ok.append(z.cur_scale == 128.0 and z.custom_loss_scaler)
+    ok.append(z.get_hp_param_device(p).type == "cpu" and isinstance(z.get_param_id(p), tuple))
+    ok.append("exp_avg" in next(iter(z.state.values())))
+    lean = z.get_lean_optimizer_state()
+    ok.append("fp32" in lean and "exp_avg" in lean and lean["fp32"][0].dim() == 1)
+    w0 = z.get_local_fp32_param(p).clone()
+    z.set_local_hp_param(w0 + 1.0, p)
+    ok.append(bool(torch.equal(z.get_local_fp32_param(p), w0 + 1.0)))
+    z.update_lp_params()
+    from deepspeed_b200.utils import safe_get_full_fp32_param
+    full = safe_get_full_fp32_param(p)
+    z.refresh_fp32_params()
+    ok.append(bool(torch.allclose(safe_get_full_fp32_param(p), full)))
+    z.empty_partition_cache()
+    z.finalize_gradient_accumulation_boundary()
+    ok.append(z.is_gradient_accumulation_boundary)
+    return ok
+
+
+@pytest.mark.parametrize("stage", [2, 3])
+def test_zero_optimizer_reference_methods(stage):
+    for ok in run_distributed(_zero_compat, 2, args=(stage, )):
+        assert all(ok), [i for i, v in enumerate(ok) if not v]

@@ -134,3 +134,47 @@ def test_fpdt_chunked_attention_matches_full():
     ref = F.scaled_dot_product_attention(q.transpose(1, 2), kk.transpose(1, 2), vv.transpose(1, 2),
                                          is_causal=True).transpose(1, 2)
     torch.testing.assert_close(out, ref, rtol=1e-4, atol=1e-5)
+
+
+def _uneven_heads(world):
+    """3 heads over 2 ranks: DistributedAttention must equal single-device attention, forward and backward."""
+    import deepspeed_b200 as ds
+    from deepspeed_b200.sequence.layer import (DistributedAttention, head_shard_sizes, heads_to_seq, seq_to_heads,
+                                               uneven_heads_all2all)
+    from deepspeed_b200.utils import groups
+    ds.init_distributed()
+    groups.initialize(sp_size=world, force=True)
+    g = groups._get_sequence_parallel_group()
+    rank = ds.comm.get_rank()
+    torch.manual_seed(0)
+    B, S, H, D = 2, 8, 3, 4
+    q, k, v = (torch.randn(B, S, H, D) for _ in range(3))
+    w = torch.randn(B, S, H, D)
+
+    def attn(q, k, v):
+        o = torch.nn.functional.scaled_dot_product_attention(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2),
+                                                             is_causal=True)
+        return o.transpose(1, 2)
+
+    qr = q.clone().requires_grad_(True)
+    ref = attn(qr, k, v)
+    (ref * w).sum().backward()
+    s = S // world
+    sl = slice(rank * s, (rank + 1) * s)
+    ql = q[:, sl].clone().requires_grad_(True)
+    out = DistributedAttention(attn, g)(ql, k[:, sl].contiguous(), v[:, sl].contiguous(), batch_dim_idx=0)
+    (out * w[:, sl]).sum().backward()
+    sizes = head_shard_sizes(H, world)
+    x = q[:, sl].contiguous()
+    hx = uneven_heads_all2all(x, scatter_idx=2, gather_idx=1, batch_dim_idx=0, group=g)
+    back = uneven_heads_all2all(hx, scatter_idx=1, gather_idx=2, batch_dim_idx=0, group=g)
+    rt = heads_to_seq(seq_to_heads(x, g), g, num_heads=H)
+    return (float((out - ref[:, sl]).abs().max()), float((ql.grad - qr.grad[:, sl]).abs().max()), sizes,
+            tuple(hx.shape), bool(torch.equal(back, x)), bool(torch.equal(rt, x)))
+
+
+def test_ulysses_uneven_heads():
+    res = run_distributed(_uneven_heads, 2, args=(2, ))
+    for r, (err, gerr, sizes, shape, ok1, ok2) in enumerate(res):
+        assert err < 1e-5 and gerr < 1e-5 and sizes == [2, 1] and ok1 and ok2
+        assert shape == (2, 8, sizes[r], 4)
