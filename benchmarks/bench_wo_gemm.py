@@ -24,13 +24,16 @@ def timeit(fn, iters=50, warm=5):
     return e0.elapsed_time(e1) / iters
 
 
+BITS = tuple(int(b) for b in os.environ.get("WO_BITS", "8,6,4").split(","))
+
+
 def main():
     dev = torch.device("cuda")
     rows = []
     flush = torch.empty(256 * 2**20, dtype=torch.uint8, device=dev)  # > L2: evict the weights between iterations
     for (N, Kd) in [(6144, 4096), (28672, 4096), (4096, 14336)]:
         w = torch.randn(N, Kd, device=dev, dtype=torch.bfloat16) * 0.05
-        for bits in (8, 4):
+        for bits in BITS:
             fq = FP_Quantize(group_size=512)
             q = fq.quantize(w, q_bits=bits)
             payload = q.payload.view(torch.uint8)

@@ -39,7 +39,18 @@ def _worker(rank, world_size, port, fn, args, kwargs, backend, q):
 
 
 def run_distributed(fn, world_size=2, args=(), kwargs=None, backend=None, timeout=DEFAULT_TIMEOUT):
-    """Run ``fn(*args)`` on ``world_size`` ranks; returns list of per-rank return values (must be picklable)."""
+    """Run ``fn(*args)`` on ``world_size`` ranks; returns list of per-rank return values (must be picklable). The
+    rendezvous port is probed and released before the ranks start, so another socket can take it in between: that
+    (and only that) failure is retried with a fresh port."""
+    for attempt in range(3):
+        try:
+            return _run_distributed_once(fn, world_size, args, kwargs, backend, timeout)
+        except RuntimeError as e:
+            if "EADDRINUSE" not in str(e) or attempt == 2:
+                raise
+
+
+def _run_distributed_once(fn, world_size, args, kwargs, backend, timeout):
     kwargs = kwargs or {}
     if backend is None:
         backend = "nccl" if torch.cuda.is_available() and torch.cuda.device_count() >= world_size else "gloo"
