@@ -178,6 +178,14 @@ def ckpt_layers(args, world, impl, total_mem_bytes):
 
 
 def ds_config(args, world):
+    cfg = _ds_config(args, world)
+    if os.environ.get("DSB200_BENCH_DEEPCOMPILE", "0") == "1" and args.impl == "ours":
+        # extra (non-headline) configuration: profile-guided unit plan of the ZeRO-3 executor (needs warmup >= 4)
+        cfg["compile"] = {"deepcompile": True}
+    return cfg
+
+
+def _ds_config(args, world):
     return {
         "train_micro_batch_size_per_gpu": args.mbs,
         "gradient_accumulation_steps": 1,
@@ -202,6 +210,9 @@ def build_ours(args, torch, world):
     torch.manual_seed(1234)
     model = LlamaForCausalLM(cfg, device=dev)
     engine, _, _, _ = ds.initialize(model=model, config=ds_config(args, world))
+    if os.environ.get("DSB200_BENCH_DEEPCOMPILE", "0") == "1":
+        engine.compile()
+        args._dc_engine = engine
 
     def step(ids):
         loss = engine(ids, labels=ids)
@@ -407,6 +418,12 @@ def main():
             "final_loss": last_loss,
             "peak_mem_gib": round(peak_mem, 2),
         }
+        dc = getattr(getattr(args, "_dc_engine", None), "_dc_driver", None)
+        if dc is not None:
+            out["config"]["deepcompile"] = ("no plan yet (warmup too short)" if dc.plan is None else {
+                "resident_units": len(dc.plan.resident), "kept_forward_to_backward": len(dc.plan.keep),
+                "predicted_exposed_gather_ms": round(dc.plan.predicted["plan_exposed_us"] / 1e3, 2),
+                "comm_model": f"{dc.profile.comm_latency_us:.0f} us + {dc.profile.comm_bytes_per_us / 1e3:.0f} GB/s"})
         if args.layers != 32:
             out["INVALID"] = "reduced layer count (debug run)"
         print(json.dumps(out))

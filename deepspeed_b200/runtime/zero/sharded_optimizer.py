@@ -1162,6 +1162,8 @@ class ZeroShardedOptimizer(ZeroCompatAPI, ZeROOptimizer):
         for u in self.units:
             if u.full_param is None or u.world <= 1:
                 continue
+            if getattr(u, "resident", False) and self.coordinator is not None:
+                continue  # refreshed by the coordinator on the gather stream (on_step_done), not on this one
             self._all_gather_into(u.full_param, u.param_shard, u)
         if self.coordinator is not None:
             self.coordinator.on_step_done()
