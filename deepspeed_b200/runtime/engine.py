@@ -299,6 +299,12 @@ class DeepSpeedEngine(EngineAccessorsMixin, Module):
             leaf_modules=self._leaf_module_classes(), elastic_checkpoint=zc.elastic_checkpoint, timers=self.timers,
             fused_collectives=fused, ignore_unused_parameters=zc.ignore_unused_parameters,
             fused_rs_adam=zc.fused_rs_adam, aio_config=self._config.aio_config, zenflow=zc.zenflow)
+        co = getattr(self.optimizer, "coordinator", None)
+        if co is not None:
+            co.sanity_checks = bool(zc.enable_sanity_checks)
+            if self.wall_clock_breakdown() or zc.log_trace_cache_warnings:
+                from .zero.partitioned_param_profiler import PartitionedParameterProfiler
+                co.param_profiler = PartitionedParameterProfiler(self.timers if self.wall_clock_breakdown() else None)
 
     def _configure_zero_inference(self, model_parameters):
         dummy = torch.optim.SGD([p for p in self.module.parameters()], lr=0.0)

@@ -30,6 +30,12 @@ class UnitCoordinator:
         self.max_reuse_distance = int(max_reuse_distance) if max_reuse_distance else 0
         self.gathers_launched = 0  # statistics (tests, tuning)
         self._plan = None  # profile-guided schedule (compile/planner.py); None = the heuristics below
+        # reference aux subsystems: event counters (zero_optimization.log_trace_cache_warnings / wall_clock_breakdown)
+        # and the cross-rank sanity checks of "enable_sanity_checks" (every rank must gather the same units in the same
+        # order, or the collectives deadlock / corrupt)
+        self.param_profiler = None
+        self.sanity_checks = False
+        self._gather_log = []
         self._prof = None  # active UnitProfiler (compile/profiler.py)
         self.handles = []
         self.fwd_order = []  # unit ids in first-forward order
@@ -96,6 +102,15 @@ class UnitCoordinator:
         z = self.z
         if not u.gathered and u.gather_work is None:
             self.gathers_launched += 1
+            if self.sanity_checks:
+                self._gather_log.append(u.uid)
+            if self.param_profiler is not None:
+                from . import partitioned_param_profiler as pp
+                bwd = self._in_backward_pass
+                name = (pp.BACKWARD_FETCH_SUBMIT if bwd else pp.FORWARD_FETCH_SUBMIT) if wait else \
+                    (pp.BACKWARD_PREFETCH_SUBMIT if bwd else pp.FORWARD_PREFETCH_SUBMIT)
+                self.param_profiler.count(name, u.numel_padded)
+                self.param_profiler.count(pp.BACKWARD_ALL_GATHER if bwd else pp.FORWARD_ALL_GATHER, u.numel_padded)
             use_side = z._use_streams and z.overlap_comm
             src = u.param_shard
             group = u.dp_group
@@ -133,6 +148,10 @@ class UnitCoordinator:
                 u.full_param = full
                 u.gather_work = True
         if wait and not u.gathered:
+            if self.param_profiler is not None:
+                from . import partitioned_param_profiler as pp
+                self.param_profiler.count(pp.BACKWARD_FETCH_WAIT if self._in_backward_pass else pp.FORWARD_FETCH_WAIT,
+                                          u.numel_padded)
             if u.gather_event is not None:
                 torch.cuda.current_stream().wait_event(u.gather_event)
                 u.full_param.record_stream(torch.cuda.current_stream())
@@ -352,7 +371,16 @@ class UnitCoordinator:
             if not u.persistent and (u.gathered or u.gather_work):
                 self.release(u)
 
+    def check_gather_order(self):
+        """``enable_sanity_checks``: the unit ids gathered since the last check must be identical on every rank."""
+        from .utils import assert_ints_same_as_other_ranks
+        log, self._gather_log = self._gather_log, []
+        if dist.is_initialized() and dist.get_world_size() > 1:
+            assert_ints_same_as_other_ranks(log)
+
     def on_step_done(self):
+        if self.sanity_checks:
+            self.check_gather_order()
         z = self.z
         if z._use_streams and z.overlap_comm:
             z.ag_stream.wait_stream(torch.cuda.current_stream())  # shards were rewritten by the step

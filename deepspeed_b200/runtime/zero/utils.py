@@ -51,20 +51,37 @@ def get_lst_from_rank0(lst: List[int]) -> List[int]:
     return t.cpu().tolist()
 
 
+def _fingerprints(lst):
+    """(length, order-sensitive checksum) of every rank's list, gathered on all ranks in ONE collective: every rank
+    reaches the same verdict, so a disagreement raises everywhere instead of leaving the agreeing ranks stuck in the
+    next collective."""
+    h = 0
+    for i, v in enumerate(lst):
+        h = (h * 1000003 + int(v) + i) % 2147483629
+    mine = torch.tensor([len(lst), h], dtype=torch.int64, device=_device())
+    out = [torch.zeros_like(mine) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, mine)
+    return [tuple(int(x) for x in t.tolist()) for t in out]
+
+
 def assert_lst_len_same_as_other_ranks(lst: List[int]) -> None:
-    got = get_lst_from_rank0([len(lst)])[0]
-    if got != len(lst):
-        raise RuntimeError(f"disagreement between rank0 and rank{dist.get_rank()}: rank0: {got}, "
-                           f"rank{dist.get_rank()}: {len(lst)}")
+    fp = _fingerprints(lst)
+    bad = [r for r, f in enumerate(fp) if f[0] != fp[0][0]]
+    if bad:
+        raise RuntimeError(f"disagreement between rank0 and rank{bad[0]}: rank0: {fp[0][0]}, rank{bad[0]}: "
+                           f"{fp[bad[0]][0]} (list lengths)")
 
 
 def assert_ints_same_as_other_ranks(ints: List[int]) -> None:
     """Every rank must hold the same list as rank 0 (otherwise collectives would be issued in different orders)."""
-    assert_lst_len_same_as_other_ranks(ints)
-    r0 = get_lst_from_rank0(ints)
-    if r0 != list(ints):
-        raise RuntimeError(f"disagreement between rank0 and rank{dist.get_rank()}: rank0: {r0}, "
-                           f"rank{dist.get_rank()}: {ints}")
+    fp = _fingerprints(ints)
+    bad = [r for r, f in enumerate(fp) if f != fp[0]]
+    if bad:
+        r = bad[0]
+        what = "lengths" if fp[r][0] != fp[0][0] else "contents"
+        mine = list(ints) if len(ints) <= 32 else list(ints[:32]) + ["..."]
+        raise RuntimeError(f"disagreement between rank0 and rank{r} ({what}): rank0 (len, checksum) = {fp[0]}, "
+                           f"rank{r} = {fp[r]}; this rank ({dist.get_rank()}) holds {mine}")
 
 
 def is_builtin_type(obj):

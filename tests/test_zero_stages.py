@@ -159,3 +159,45 @@ def test_zero3_reuse_distance_and_prefetch_bucket():
     assert n < some[1][-1] < 2 * n                    # only the last units stay gathered
     for a, b, c in zip(base[0], keep[0], some[0]):    # scheduling does not change the math
         assert abs(a - b) < 1e-6 and abs(a - c) < 1e-6
+
+
+def _sanity_and_profiler():
+    import deepspeed_b200 as ds
+    from deepspeed_b200.runtime.zero import partitioned_param_profiler as pp
+    torch.manual_seed(0)
+    model = SimpleModel(16, 4)
+    eng, _, _, _ = ds.initialize(model=model, config={
+        "train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}},
+        "zero_optimization": {"stage": 3, "unit_max_numel": 300, "stage3_param_persistence_threshold": 0,
+                              "stage3_max_reuse_distance": 0, "enable_sanity_checks": True,
+                              "log_trace_cache_warnings": True}})
+    co = eng.optimizer.coordinator
+    assert co.sanity_checks and co.param_profiler is not None
+    batches = random_batches(8, 4, 16, "cpu")
+    for i in range(3):
+        loss = eng(*batches[2 * i + ds.comm.get_rank()])
+        eng.backward(loss)
+        eng.step()
+    ev = co.param_profiler.event_counters
+    n = len([u for u in eng.optimizer.units if not u.persistent])
+    counts = {k: v.count for k, v in ev.items()}
+    # a rank that gathers a different unit sequence is caught at the next step boundary
+    caught = False
+    if ds.comm.get_rank() == 1:
+        co._gather_log.append(12345)
+    try:
+        co.check_gather_order()
+    except RuntimeError as e:
+        caught = "disagreement" in str(e)
+    co.param_profiler.log_events()
+    return counts, n, caught
+
+
+def test_zero3_sanity_checks_and_param_profiler():
+    res = run_distributed(_sanity_and_profiler, 2)
+    counts, n, _ = res[0]
+    from deepspeed_b200.runtime.zero import partitioned_param_profiler as pp
+    assert counts[pp.FORWARD_ALL_GATHER] == 3 * n and counts[pp.BACKWARD_ALL_GATHER] == 3 * n
+    assert counts[pp.FORWARD_FETCH_WAIT] >= 3 * n
+    assert counts.get(pp.FORWARD_PREFETCH_SUBMIT, 0) > 0  # steps after the trace step prefetch one unit ahead
+    assert res[1][2] and res[0][2]  # the disagreement is raised on every rank (no rank is left in a collective)
