@@ -161,7 +161,116 @@ class DecoupledCheckpointEngine(CheckpointEngine):
             pass
 
 
+class NebulaCheckpointEngine(CheckpointEngine):
+    """Azure Nebula service (reference ``nebula_checkpoint_engine.py``): saves go to the service's tiered storage under the
+    checkpoint tag, a dummy file marks each partition on disk so that the usual file discovery keeps working. Needs the
+    external ``torch_nebula`` package."""
+
+    def __init__(self, config_params=None):
+        super().__init__(config_params)
+        try:
+            import torch_nebula
+        except ImportError as e:
+            raise RuntimeError("the nebula checkpoint engine needs the torch_nebula package (Azure ML images)") from e
+        self.nb = torch_nebula
+        self.name = "NebulaCheckpointEngine"
+        self.checkpoint, self.tag_flag = None, None
+        self.enable_nebula_load = config_params.enable_nebula_load
+        self.nebula_load_path = config_params.load_path or config_params.persistent_storage_path
+        self.nb.init(persistent_storage_path=config_params.persistent_storage_path,
+                     persistent_time_interval=config_params.persistent_time_interval,
+                     num_of_version_in_retention=config_params.num_of_version_in_retention)
+
+    @staticmethod
+    def _tag_of(path):
+        return os.path.basename(os.path.dirname(path))
+
+    def create(self, info):
+        log_dist(f"[Nebula] Start Checkpoint for tag:{info.tag}", [0])
+        self.checkpoint = self.nb.Checkpoint(info.tag, -2)  # -2: complete only on an explicit commit
+
+    def save(self, state_dict, path):
+        torch.save("", path)  # placeholder so that tag / file discovery works
+        self.checkpoint.save(os.path.basename(path), state_dict)
+
+    def load(self, path, map_location=None):
+        tag = self._tag_of(path)
+        if not self.enable_nebula_load and (self.tag_flag is None or self.tag_flag == tag):
+            self.tag_flag = tag
+            return torch.load(path, map_location=map_location, weights_only=False)
+        ck = self.nb.get_latest_checkpoint(persist_path=self.nebula_load_path) \
+            if tag in (None, "latest", "latest_universal") else \
+            self.nb.get_checkpoint(tag=tag, persist_path=self.nebula_load_path)
+        if ck is None or ck.tag == "":
+            ck = self.nb.get_latest_checkpoint(persist_path=self.nebula_load_path)
+        if ck is None or ck.tag == "":
+            logger.info(f"[Nebula] no checkpoint for tag {tag}; falling back to the file {path}")
+            return torch.load(path, map_location=map_location, weights_only=False)
+        self.tag_flag = ck.tag
+        return ck.load(os.path.basename(path), map_location=map_location)
+
+    def commit(self, info):
+        tag = getattr(info, "tag", info)
+        log_dist(f"[Nebula] all files for {tag} are saved in tier1; persisting to tier3 asynchronously", [0])
+        return self.checkpoint.commit()
+
+
+class DataStatesCheckpointEngine(CheckpointEngine):
+    """DataStates-LLM asynchronous multi-level checkpointing (reference ``datastates_checkpoint_engine.py``). Needs the
+    external ``datastates`` package."""
+
+    def __init__(self, deepspeed_config, rank):
+        super().__init__(deepspeed_config)
+        try:
+            from datastates import CheckpointEngine as _Engine
+        except ImportError as e:
+            raise RuntimeError("Please install DataStates from https://github.com/DataStates/datastates-llm.") from e
+        self.ckpt_engine = _Engine(deepspeed_config, rank)
+        self.commit_info = None
+
+    def create(self, info):
+        self.commit_info = info
+
+    def save(self, state_dict, path):
+        return self.ckpt_engine.save(state_dict, path)
+
+    def load(self, path, map_location=None):
+        return self.ckpt_engine.load(path, map_location)
+
+    def commit(self, info):
+        assert info == self.commit_info
+        self.ckpt_engine.wait(persist=True)
+        self.commit_info = None
+        return True
+
+    def cleanup(self):
+        if getattr(self, "ckpt_engine", None) is not None:
+            self.commit(self.commit_info)
+            del self.ckpt_engine
+            self.ckpt_engine = None
+
+    def is_decoupled(self):
+        return False
+
+    def preserves_storage_sharing(self):
+        return False
+
+
 def create_checkpoint_engine(config):
+    neb = getattr(config, "nebula_config", None) or {}
+    if isinstance(neb, dict) and neb.get("enabled", False):
+        from ...nebula.config import DeepSpeedNebulaConfig
+        try:
+            return NebulaCheckpointEngine(DeepSpeedNebulaConfig({"nebula": neb}))
+        except RuntimeError as e:
+            logger.warning(f"{e}; falling back to the torch checkpoint engine")
+    dst = getattr(config, "datastates_config", None) or {}
+    if isinstance(dst, dict) and dst.get("enabled", False):
+        try:
+            from ... import comm as _dist
+            return DataStatesCheckpointEngine(dst, _dist.get_rank() if _dist.is_initialized() else 0)
+        except RuntimeError as e:
+            logger.warning(f"{e}; falling back to the torch checkpoint engine")
     ck = getattr(config, "checkpoint_config", None)
     w = getattr(ck, "writer", None) if ck is not None else None
     kind = (getattr(w, "type", "torch") or "torch").lower() if w is not None else "torch"
