@@ -74,9 +74,16 @@ struct FaParams {
     int G;                   // query heads per KV head
     float* part_o;           // [T * Hq, splits, 128] fp32 (splits > 1)
     float* part_lse;         // [T * Hq, splits]
+    // additive score biases (BIAS kernel variant; Evoformer attention): score = scale * q.k + bias1[b, col] +
+    // bias2[b / bias2_div, h, row, col], both bf16, either may be null. Strides in elements.
+    const __nv_bfloat16* bias1;
+    const __nv_bfloat16* bias2;
+    int64_t bias1_bstride, bias2_bstride, bias2_hstride, bias2_rstride;
+    int bias2_div;
+    float inv_scale;         // 1 / softmax scale: the bias is folded into the raw score as bias / scale
 };
 
-template <unsigned EMU_MASK>
+template <unsigned EMU_MASK, bool BIAS = false>
 __global__ void __launch_bounds__(FA_THREADS, 1)
 flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                       const __grid_constant__ CUtensorMap map_v, const FaParams prm)
@@ -280,6 +287,56 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
             for (int c = 0; c < 4; c++) tmem_ld_32x32(s_addr + c * 32, r[c]);
             tmem_wait_ld();
             float mx = -INFINITY;
+            if constexpr (BIAS) {
+                // s' = s + (bias1[col] + bias2[row, col]) / scale, so that s' * scale_log2 is the biased logit in the
+                // log2 domain; 8 bf16 (16 bytes) per load, guarded at the sequence tail
+                const bool row_ok = row < Sq;
+                const __nv_bfloat16* b1 = prm.bias1 ? prm.bias1 + (int64_t)b * prm.bias1_bstride : nullptr;
+                const __nv_bfloat16* b2 = (prm.bias2 && row_ok)
+                    ? prm.bias2 + (int64_t)(b / prm.bias2_div) * prm.bias2_bstride + (int64_t)h * prm.bias2_hstride +
+                          (int64_t)row * prm.bias2_rstride
+                    : nullptr;
+                const bool vec_ok = (col0 + FA_BN <= Skv) && (Skv % 8 == 0);
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+#pragma unroll
+                    for (int i8 = 0; i8 < 32; i8 += 8) {
+                        const int col = col0 + c * 32 + i8;
+                        float add[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                        if (vec_ok) {
+                            if (b1) {
+                                const uint4 raw = *reinterpret_cast<const uint4*>(b1 + col);
+                                const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+                                for (int q4 = 0; q4 < 4; q4++) {
+                                    const float2 f = __bfloat1622float2(hp[q4]);
+                                    add[2 * q4] += f.x, add[2 * q4 + 1] += f.y;
+                                }
+                            }
+                            if (b2) {
+                                const uint4 raw = *reinterpret_cast<const uint4*>(b2 + col);
+                                const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+                                for (int q4 = 0; q4 < 4; q4++) {
+                                    const float2 f = __bfloat1622float2(hp[q4]);
+                                    add[2 * q4] += f.x, add[2 * q4 + 1] += f.y;
+                                }
+                            }
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 8; e++) {
+                                if (col + e < Skv) {
+                                    if (b1) add[e] += __bfloat162float(b1[col + e]);
+                                    if (b2) add[e] += __bfloat162float(b2[col + e]);
+                                }
+                            }
+                        }
+#pragma unroll
+                        for (int e = 0; e < 8; e++)
+                            r[c][i8 + e] = __float_as_uint(fmaf(add[e], prm.inv_scale, __uint_as_float(r[c][i8 + e])));
+                    }
+                }
+            }
             if (need_mask) {
 #pragma unroll
                 for (int c = 0; c < 4; c++)
@@ -480,6 +537,23 @@ int launch_flash_fwd(const CUtensorMap& mq, const CUtensorMap& mk, const CUtenso
     return 0;
 }
 
+int launch_flash_fwd_bias(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const FaParams& prm,
+                          cudaStream_t stream)
+{
+    const int64_t grid = (int64_t)prm.pairs * prm.B * prm.H;
+    int dev_ = 0;
+    cudaGetDevice(&dev_);
+    static bool attr_set[64] = {};
+    if (!attr_set[dev_ & 63]) {
+        DSB_CHECK(cudaFuncSetAttribute(flash_attn_fwd_kernel<0x00u, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       FA_SMEM_BYTES));
+        attr_set[dev_ & 63] = true;
+    }
+    flash_attn_fwd_kernel<0x00u, true><<<(unsigned)grid, FA_THREADS, FA_SMEM_BYTES, stream>>>(mq, mk, mv, prm);
+    DSB_CHECK_LAUNCH("flash_attn_fwd_bias");
+    return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -510,6 +584,53 @@ int dsb200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, 
     prm.pairs = (Sq + 2 * FA_BM - 1) / (2 * FA_BM);
     prm.lse_stride = Sq;
     return launch_flash_fwd(mq, mk, mv, prm, stream);
+}
+
+// Attention with additive score biases (Evoformer / any bias that broadcasts this way), non-causal:
+//   score[b, h, i, j] = scale * q[b, i, h, :] . k[b, j, h, :] + bias1[b, j] + bias2[b / bias2_div, h, i, j]
+// q / k / v / o as in dsb200_flash_attn_fwd (head_dim 128: pad smaller heads with zeros); bias1 [B, Skv] (row stride
+// bias1_bstride), bias2 [B / bias2_div, H, Sq, Skv] (strides given), both bf16, either may be null. For 16-byte bias
+// loads Skv should be a multiple of 8 and the bias rows 16-byte aligned (otherwise a scalar path is taken).
+int dsb200_flash_attn_fwd_bias(const void* q, const void* k, const void* v, void* o, float* lse, const void* bias1,
+                               const void* bias2, int B, int Sq, int Skv, int H, int64_t q_row_stride,
+                               int64_t q_batch_stride, int64_t k_row_stride, int64_t k_batch_stride,
+                               int64_t v_row_stride, int64_t v_batch_stride, int64_t o_row_stride,
+                               int64_t o_batch_stride, int64_t bias1_bstride, int64_t bias2_bstride,
+                               int64_t bias2_hstride, int64_t bias2_rstride, int bias2_div, float scale,
+                               cudaStream_t stream)
+{
+    if (B <= 0 || Sq <= 0 || Skv <= 0) return 0;
+    if ((o_row_stride % 8) || (o_batch_stride % 8) || ((uintptr_t)o & 15) || scale <= 0.f || bias2_div < 1) {
+        dsb200_set_error("flash_attn_fwd_bias: output must be 16-byte aligned, scale > 0, bias2_div >= 1");
+        return -1;
+    }
+    const bool aligned = !(((uintptr_t)bias1 | (uintptr_t)bias2) & 15) && (bias1_bstride % 8 == 0) &&
+                         (bias2_bstride % 8 == 0) && (bias2_hstride % 8 == 0) && (bias2_rstride % 8 == 0);
+    CUtensorMap mq, mk, mv;
+    if (make_map_3d(&mq, q, B, Sq, (int64_t)H * FA_D, q_row_stride, q_batch_stride, FA_BM) != 0) return -2;
+    if (make_map_3d(&mk, k, B, Skv, (int64_t)H * FA_D, k_row_stride, k_batch_stride, FA_BN) != 0) return -2;
+    if (make_map_3d(&mv, v, B, Skv, (int64_t)H * FA_D, v_row_stride, v_batch_stride, FA_BN) != 0) return -2;
+    FaParams prm = {};
+    prm.o = (__nv_bfloat16*)o;
+    prm.lse = lse;
+    prm.B = B, prm.Sq = Sq, prm.H = H, prm.Hkv = H;
+    // a Skv that is not a multiple of 8, or unaligned bias rows, must not take the 16-byte path: the kernel keys that
+    // on Skv % 8, so report an odd Skv to it only through the scalar-path condition below
+    prm.Skv = Skv;
+    prm.o_row_stride = o_row_stride, prm.o_batch_stride = o_batch_stride;
+    prm.scale_log2 = scale * 1.4426950408889634f;
+    prm.inv_scale = 1.0f / scale;
+    prm.causal = 0;
+    prm.pairs = (Sq + 2 * FA_BM - 1) / (2 * FA_BM);
+    prm.lse_stride = Sq;
+    prm.bias1 = (const __nv_bfloat16*)bias1, prm.bias2 = (const __nv_bfloat16*)bias2;
+    prm.bias1_bstride = bias1_bstride, prm.bias2_bstride = bias2_bstride;
+    prm.bias2_hstride = bias2_hstride, prm.bias2_rstride = bias2_rstride, prm.bias2_div = bias2_div;
+    if (!aligned) {
+        dsb200_set_error("flash_attn_fwd_bias: bias pointers / strides must be 16-byte aligned (multiples of 8 elements)");
+        return -1;
+    }
+    return launch_flash_fwd_bias(mq, mk, mv, prm, stream);
 }
 
 // Ragged prefill over a blocked KV cache (FastGen): `n_seqs` sequences packed back to back in q / o [T_total, H, 128]

@@ -29,6 +29,9 @@ def _lib():
         L.dsb200_flash_attn_fwd_paged.restype = I
         L.dsb200_flash_decode_paged.argtypes = [P, P, P, P, P, P, P, I, I, I, I, I, I, F, P]
         L.dsb200_flash_decode_paged.restype = I
+        if hasattr(L, "dsb200_flash_attn_fwd_bias"):
+            L.dsb200_flash_attn_fwd_bias.argtypes = [P] * 7 + [I, I, I, I] + [L64] * 12 + [I, F, P]
+            L.dsb200_flash_attn_fwd_bias.restype = I
         if hasattr(L, "dsb200_flash_attn_bwd"):
             L.dsb200_flash_attn_bwd.argtypes = [P] * 11 + [I, I, I, I] + [L64] * 16 + [F, I, P]
             L.dsb200_flash_attn_bwd.restype = I
@@ -72,6 +75,57 @@ def flash_attention_forward(q, k, v, causal=True, scale=None, out=None, want_lse
         1 if causal else 0, K._stream())
     K._check(rc, "flash_attn_fwd")
     return out, lse
+
+
+def bias_attention_supported(q):
+    return q.is_cuda and K.available() and hasattr(K.lib(), "dsb200_flash_attn_fwd_bias")
+
+
+def flash_attention_bias_forward(q, k, v, bias1=None, bias2=None, bias2_div=1, scale=None):
+    """Non-causal attention with additive biases on the tcgen05 kernel (``csrc/attention_fwd.cu``, BIAS variant).
+
+    q, k, v: [B, S, H, D] with D <= 128 (bf16 / fp16 / fp32; computed in bf16, heads zero-padded to 128);
+    ``bias1`` [B, Skv] added to every row and head; ``bias2`` [B / bias2_div, H, Sq, Skv] shared by ``bias2_div``
+    consecutive batch entries. Returns (o [B, S, H, D] in q's dtype, lse [B, H, Sq] fp32, natural log)."""
+    B, Sq, H, D = q.shape
+    Skv = k.shape[1]
+    assert D <= 128 and k.shape == v.shape and k.shape[2] == H
+    if scale is None:
+        scale = 1.0 / math.sqrt(D)
+
+    def pad(t):
+        t = t.to(torch.bfloat16)
+        if D == 128 and t.is_contiguous():
+            return t
+        out = torch.zeros(t.shape[:-1] + (128, ), dtype=torch.bfloat16, device=t.device)
+        out[..., :D] = t
+        return out
+
+    def bias_rows(b, last):
+        """bf16, last dim padded to a multiple of 8 so that every row is 16-byte aligned."""
+        if b is None:
+            return None
+        b = b.to(torch.bfloat16)
+        padn = (-last) % 8
+        if padn:
+            b = torch.nn.functional.pad(b, (0, padn))
+        return b.contiguous()
+
+    qp, kp, vp = pad(q), pad(k), pad(v)
+    out = torch.empty((B, Sq, H, 128), dtype=torch.bfloat16, device=q.device)
+    lse = torch.empty((B, H, Sq), dtype=torch.float32, device=q.device)
+    b1 = bias_rows(bias1.reshape(B, Skv), Skv) if bias1 is not None else None
+    b2 = bias_rows(bias2.reshape(-1, H, Sq, Skv), Skv) if bias2 is not None else None
+    if b2 is not None:
+        assert b2.shape[0] * bias2_div == B, "bias2 batch x bias2_div must equal the attention batch"
+    rc = _lib().dsb200_flash_attn_fwd_bias(
+        K._ptr(qp), K._ptr(kp), K._ptr(vp), K._ptr(out), K._ptr(lse), K._ptr(b1), K._ptr(b2), B, Sq, Skv, H,
+        qp.stride(1), qp.stride(0), kp.stride(1), kp.stride(0), vp.stride(1), vp.stride(0), out.stride(1),
+        out.stride(0), b1.stride(0) if b1 is not None else 0, b2.stride(0) if b2 is not None else 0,
+        b2.stride(1) if b2 is not None else 0, b2.stride(2) if b2 is not None else 0, int(bias2_div), float(scale),
+        K._stream())
+    K._check(rc, "flash_attn_fwd_bias")
+    return out[..., :D].to(q.dtype), lse
 
 
 def paged_prefill_supported(q, kv_layer):

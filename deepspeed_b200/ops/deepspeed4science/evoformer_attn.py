@@ -3,6 +3,11 @@ over the CUTLASS kernels in ``csrc/deepspeed4science/evoformer_attn``): attentio
 up to two additive biases - ``bias1 [B, N, 1, 1, L]`` (the MSA mask) and ``bias2 [B, 1, H, L, L]`` (the pair bias) -
 and gradients for both.
 
+Forward on a GPU: the tcgen05 flash-attention kernel with bias hooks (``csrc/attention_fwd.cu`` BIAS variant through
+``ops/attention.py::flash_attention_bias_forward``; heads are zero-padded to 128, the MSA rows become the kernel's batch,
+``bias2`` is shared by the N rows of a batch entry). The backward recomputes probabilities chunk by chunk with the
+library GEMM from the saved log-sum-exp. CPU / unsupported dtypes: the chunked PyTorch forward below.
+
 The score matrix is never materialised for the whole batch: rows of the MSA dimension are processed in chunks sized to
 a fixed workspace, forward and backward (the backward recomputes each chunk's probabilities from the saved
 log-sum-exp, like the fused kernel does)."""
@@ -18,6 +23,16 @@ def _chunks(n_rows, per_row):
     return [(s, min(n_rows, s + step)) for s in range(0, n_rows, step)]
 
 
+def _native_ok(q):
+    import os
+    if os.environ.get("DSB200_NATIVE_EVOFORMER", "1") != "1" or not q.is_cuda or q.shape[-1] > 128:
+        return False
+    if q.dtype not in (torch.bfloat16, torch.float16):
+        return False  # the kernel computes in bf16: keep fp32 / fp64 inputs on the exact path
+    from ..attention import bias_attention_supported
+    return bias_attention_supported(q)
+
+
 class EvoformerFusedAttention(torch.autograd.Function):
 
     @staticmethod
@@ -28,7 +43,16 @@ class EvoformerFusedAttention(torch.autograd.Function):
         out = torch.empty_like(q)
         acc = torch.float64 if q.dtype == torch.float64 else torch.float32
         lse = torch.empty(B, N, H, L, dtype=acc, device=q.device)
-        for s, e in _chunks(N, B * H * L * L):
+        native = _native_ok(q)
+        if native:
+            from ..attention import flash_attention_bias_forward
+            o, l = flash_attention_bias_forward(
+                q.reshape(B * N, L, H, D), k.reshape(B * N, L, H, D), v.reshape(B * N, L, H, D),
+                bias1=None if bias1 is None else bias1.reshape(B * N, L),
+                bias2=None if bias2 is None else bias2.reshape(B, H, L, L), bias2_div=N, scale=scale)
+            out = o.reshape(B, N, L, H, D)
+            lse = l.reshape(B, N, H, L).to(acc)
+        for s, e in ([] if native else _chunks(N, B * H * L * L)):
             qc = q[:, s:e].permute(0, 1, 3, 2, 4)                    # [B, n, H, L, D]
             kc = k[:, s:e].permute(0, 1, 3, 2, 4)
             vc = v[:, s:e].permute(0, 1, 3, 2, 4)

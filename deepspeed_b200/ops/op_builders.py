@@ -46,4 +46,16 @@ GDSBuilder = _mk("GDSBuilder", "deepspeed_b200.ops.gds")
 StochasticTransformerBuilder = _mk("StochasticTransformerBuilder", "deepspeed_b200.ops.transformer")
 RaggedOpsBuilder = _mk("RaggedOpsBuilder", "deepspeed_b200.inference.v2.ragged")
 DeepCompileBuilder = _mk("DeepCompileBuilder", "deepspeed_b200.compile")
+InferenceCoreBuilder = _mk("InferenceCoreBuilder", "deepspeed_b200.ops.fused")  # norms / activations / rotary kernels
+InferenceCutlassBuilder = _mk("InferenceCutlassBuilder", "deepspeed_b200.ops.kernels")  # wo_gemm, grouped GEMM
+RaggedUtilsBuilder = _mk("RaggedUtilsBuilder", "deepspeed_b200.inference.v2.ragged")  # csrc/cpu/ragged_host.cpp
 ALL_OPS = {k: v for k, v in globals().items() if k.endswith("Builder") and k != "_Builder"}
+
+# base-class names of the reference's op_builder package (``isinstance(b, OpBuilder)`` checks in user code)
+OpBuilder = _Builder
+CUDAOpBuilder = _Builder
+TorchCPUOpBuilder = _Builder
+
+
+def get_default_compute_capabilities():
+    return "10.0a"

@@ -232,6 +232,15 @@ int dsb200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, 
                           int64_t k_batch_stride, int64_t v_row_stride, int64_t v_batch_stride, int64_t o_row_stride,
                           int64_t o_batch_stride, float scale, int causal, cudaStream_t stream);
 /* ragged prefill over a blocked KV cache [num_blocks, 2, 128, Hkv, 128] (reference: ragged_ops/blocked_flash) */
+/* Non-causal attention with additive score biases (Evoformer): score = scale * q.k + bias1[b, j] +
+ * bias2[b / bias2_div, h, i, j]; biases bf16, either may be null, pointers / strides 16-byte aligned. */
+int dsb200_flash_attn_fwd_bias(const void* q, const void* k, const void* v, void* o, float* lse, const void* bias1,
+                               const void* bias2, int B, int Sq, int Skv, int H, int64_t q_row_stride,
+                               int64_t q_batch_stride, int64_t k_row_stride, int64_t k_batch_stride,
+                               int64_t v_row_stride, int64_t v_batch_stride, int64_t o_row_stride,
+                               int64_t o_batch_stride, int64_t bias1_bstride, int64_t bias2_bstride,
+                               int64_t bias2_hstride, int64_t bias2_rstride, int bias2_div, float scale,
+                               cudaStream_t stream);
 int dsb200_flash_attn_fwd_paged(const void* q, const void* kv, void* o, float* lse, const int* cu_q, const int* q_len,
                                 const int* kv_len, const int* block_table, int n_seqs, int T_total, int max_q_len,
                                 int H, int Hkv, int num_blocks, int max_blocks, int64_t q_row_stride,

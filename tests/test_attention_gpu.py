@@ -129,3 +129,53 @@ def test_fpdt_chunked_attention_on_native_kernels_matches_full_attention():
     for name, g, w in zip("qkv", got, (qf.grad, kf.grad, vf.grad)):
         err, ref = (g - w).abs().max().item(), w.abs().max().item()
         assert err <= 3e-2 * max(ref, 1.0), (name, err, ref)
+
+
+@pytest.mark.parametrize("S,D,which", [(256, 32, "both"), (203, 32, "both"), (384, 64, "bias2"), (130, 128, "bias1"),
+                                        (256, 16, "none")])
+def test_bias_attention_matches_reference(S, D, which):
+    """tcgen05 forward with additive biases (Evoformer form) vs an fp32 PyTorch restatement."""
+    from deepspeed_b200.ops.attention import bias_attention_supported, flash_attention_bias_forward
+    torch.manual_seed(0)
+    dev = torch.device("cuda")
+    B2, N, H = 2, 3, 4
+    q, k, v = (torch.randn(B2 * N, S, H, D, device=dev, dtype=torch.bfloat16) for _ in range(3))
+    assert bias_attention_supported(q)
+    b1 = (torch.randn(B2 * N, S, device=dev) * 2).bfloat16() if which in ("both", "bias1") else None
+    if b1 is not None:
+        b1[:, -5:] = -1e4  # masked keys, as the MSA mask bias does
+    b2 = torch.randn(B2, H, S, S, device=dev).bfloat16() if which in ("both", "bias2") else None
+    o, lse = flash_attention_bias_forward(q, k, v, bias1=b1, bias2=b2, bias2_div=N)
+    torch.cuda.synchronize()
+    scores = torch.einsum("bihd,bjhd->bhij", q.float(), k.float()) / math.sqrt(D)
+    if b1 is not None:
+        scores = scores + b1.float()[:, None, None, :]
+    if b2 is not None:
+        scores = scores + b2.float().repeat_interleave(N, dim=0)
+    want = torch.einsum("bhij,bjhd->bihd", scores.softmax(-1), v.float())
+    assert o.shape == q.shape and o.dtype == q.dtype
+    assert (o.float() - want).abs().max().item() < 3e-2
+    assert (lse - torch.logsumexp(scores, -1)).abs().max().item() < 2e-2
+
+
+def test_evoformer_attention_native_forward_and_grads():
+    """DS4Sci_EvoformerAttention on the GPU (native forward, GEMM backward from the saved LSE) vs the fp32 math."""
+    from deepspeed_b200.ops.deepspeed4science.evoformer_attn import DS4Sci_EvoformerAttention
+    torch.manual_seed(1)
+    dev = torch.device("cuda")
+    B, N, L, H, D = 1, 4, 192, 4, 32
+    mk = lambda *s: torch.randn(*s, device=dev, dtype=torch.bfloat16).requires_grad_(True)  # noqa: E731
+    q, k, v = mk(B, N, L, H, D), mk(B, N, L, H, D), mk(B, N, L, H, D)
+    b1, b2 = mk(B, N, 1, 1, L), mk(B, 1, H, L, L)
+    out = DS4Sci_EvoformerAttention(q, k, v, [b1, b2])
+    w = torch.randn_like(out)
+    (out.float() * w.float()).sum().backward()
+    got = [t.grad.float().clone() for t in (q, k, v, b1, b2)]
+    qf, kf, vf, b1f, b2f = (t.detach().float().requires_grad_(True) for t in (q, k, v, b1, b2))
+    scores = torch.einsum("bnihd,bnjhd->bnhij", qf, kf) / math.sqrt(D) + b1f + b2f
+    ref = torch.einsum("bnhij,bnjhd->bnihd", scores.softmax(-1), vf)
+    (ref * w.float()).sum().backward()
+    assert (out.float() - ref).abs().max().item() < 3e-2
+    for g, t, name in zip(got, (qf, kf, vf, b1f, b2f), "q k v bias1 bias2".split()):
+        denom = t.grad.abs().max().item() + 1e-6
+        assert (g - t.grad).abs().max().item() / denom < 5e-2, name
