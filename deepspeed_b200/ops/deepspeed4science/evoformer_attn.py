@@ -68,6 +68,7 @@ class EvoformerFusedAttention(torch.autograd.Function):
         ctx.save_for_backward(q, k, v, out, lse, bias1 if bias1 is not None else torch.tensor([]),
                               bias2 if bias2 is not None else torch.tensor([]))
         ctx.has_b1, ctx.has_b2 = bias1 is not None, bias2 is not None
+        ctx.native = native
         return out
 
     @staticmethod
@@ -76,6 +77,8 @@ class EvoformerFusedAttention(torch.autograd.Function):
         B, N, L, H, D = q.shape
         scale = 1.0 / math.sqrt(D)
         acc = lse.dtype
+        if ctx.native:
+            return _backward_low_precision(ctx, grad_output, q, k, v, out, lse, bias1, bias2, scale)
         dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
         need_b1 = ctx.has_b1 and ctx.needs_input_grad[3]
         need_b2 = ctx.has_b2 and ctx.needs_input_grad[4]
@@ -105,6 +108,64 @@ class EvoformerFusedAttention(torch.autograd.Function):
             dk[:, s:e] = torch.matmul(dsl.transpose(-1, -2), qc).permute(0, 1, 3, 2, 4)
         return dq, dk, dv, (db1.to(grad_output.dtype) if need_b1 else None), \
             (db2.to(grad_output.dtype) if need_b2 else None)
+
+
+def _backward_low_precision(ctx, grad_output, q, k, v, out, lse, bias1, bias2, scale):
+    """Backward for the bf16 / fp16 GPU path: every GEMM in the input dtype, the probabilities recomputed from the saved
+    log-sum-exp in fp32 one MSA chunk at a time, bias gradients accumulated in fp32. ``DSB200_EVO_BWD=sdpa`` instead
+    differentiates the library's fused attention with the broadcast bias as mask."""
+    import os
+    B, N, L, H, D = q.shape
+    need_b1 = ctx.has_b1 and ctx.needs_input_grad[3]
+    need_b2 = ctx.has_b2 and ctx.needs_input_grad[4]
+    if os.environ.get("DSB200_EVO_BWD", "gemm") == "sdpa":
+        with torch.enable_grad():
+            leaves = [t.detach().requires_grad_(True) for t in (q, k, v)]
+            b1 = bias1.detach().requires_grad_(need_b1) if ctx.has_b1 else None
+            b2 = bias2.detach().requires_grad_(need_b2) if ctx.has_b2 else None
+            mask = None
+            if b1 is not None or b2 is not None:
+                mask = (b1 if b1 is not None else 0) + (b2 if b2 is not None else 0)
+                mask = mask.expand(B, N, H, L, L)
+            o = torch.nn.functional.scaled_dot_product_attention(
+                leaves[0].transpose(2, 3), leaves[1].transpose(2, 3), leaves[2].transpose(2, 3), attn_mask=mask,
+                scale=scale).transpose(2, 3)
+            wanted = leaves + [t for t, need in ((b1, need_b1), (b2, need_b2)) if need]
+            grads = list(torch.autograd.grad(o, wanted, grad_output))
+        dq, dk, dv = grads[:3]
+        rest = grads[3:]
+        db1 = rest.pop(0) if need_b1 else None
+        db2 = rest.pop(0) if need_b2 else None
+        return dq, dk, dv, db1, db2
+    # every pass over the [B, n, H, L, L] score tensor is in the input dtype and fused where the library has a fused
+    # op (softmax, softmax backward); only the bias-gradient reductions accumulate in fp32
+    dt = q.dtype
+    dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    db1 = torch.zeros(B, N, L, dtype=torch.float32, device=q.device) if need_b1 else None
+    db2 = torch.zeros(B, H, L, L, dtype=torch.float32, device=q.device) if need_b2 else None
+    b2 = bias2.to(dt).reshape(B, 1, H, L, L) if ctx.has_b2 else None
+    for s, e in _chunks(N, B * H * L * L):
+        qc = (q[:, s:e] * scale).transpose(2, 3).contiguous()                                # [B, n, H, L, D]
+        kc, vc, doc = (t[:, s:e].transpose(2, 3).contiguous() for t in (k, v, grad_output))
+        x = torch.matmul(qc, kc.transpose(-1, -2))
+        if b2 is not None:
+            x.add_(b2)
+        if ctx.has_b1:
+            x.add_(bias1[:, s:e].to(dt))
+        p = torch.softmax(x, dim=-1)
+        del x
+        dv[:, s:e] = torch.matmul(p.transpose(-1, -2), doc).transpose(2, 3)
+        dp = torch.matmul(doc, vc.transpose(-1, -2))
+        ds = torch._softmax_backward_data(dp, p, -1, dt)                                     # p * (dp - sum(dp * p))
+        del dp, p
+        if need_b1:
+            db1[:, s:e] += ds.sum(dim=(2, 3), dtype=torch.float32)
+        if need_b2:
+            db2 += ds.sum(dim=1, dtype=torch.float32)
+        dq[:, s:e] = torch.matmul(ds, kc).mul_(scale).transpose(2, 3)
+        dk[:, s:e] = torch.matmul(ds.transpose(-1, -2), qc).transpose(2, 3)                   # qc carries the scale
+    return dq, dk, dv, (db1.reshape(bias1.shape).to(bias1.dtype) if need_b1 else None), \
+        (db2.reshape(bias2.shape).to(bias2.dtype) if need_b2 else None)
 
 
 def DS4Sci_EvoformerAttention(Q, K, V, biases):
