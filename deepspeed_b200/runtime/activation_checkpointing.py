@@ -163,18 +163,31 @@ def _pack(x):
     s.partitioned = PARTITION_ACTIVATIONS and x.is_floating_point() and _mp_info()[1] > 1 and x.numel() > 0
     data = _partition(x) if s.partitioned else x.detach()
     if CPU_CHECKPOINT and data.is_cuda:
-        host = torch.empty(data.shape, dtype=data.dtype, device="cpu", pin_memory=True)
-        host.copy_(data, non_blocking=True)
-        data = host
+        # asynchronous copy into a pooled pinned buffer on a side stream (runtime/offload_activations.py); a fresh
+        # pinned allocation per activation would cost more than the copy
+        data = _offload_engine().offload(data)
     s.data = data
     return s
+
+
+_OFFLOAD_ENGINE = None
+
+
+def _offload_engine():
+    global _OFFLOAD_ENGINE
+    if _OFFLOAD_ENGINE is None:
+        from .offload_activations import ActivationOffloadEngine
+        _OFFLOAD_ENGINE = ActivationOffloadEngine(min_offload_bytes=0, keep_last_count=0, max_in_flight=2)
+    return _OFFLOAD_ENGINE
 
 
 def _unpack(s):
     if not s.is_tensor:
         return s.data
     data = s.data
-    if data.device != s.device:
+    if not torch.is_tensor(data):  # ticket of the offload engine
+        data = _offload_engine().restore(data)
+    elif data.device != s.device:
         data = data.to(s.device, non_blocking=True)
     if s.partitioned:
         data = _gather(data, s.shape, s.numel)
