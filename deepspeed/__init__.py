@@ -39,6 +39,15 @@ _ALIASES = {
     "deepspeed.module_inject.autotp_config": "deepspeed_b200.parallel.autotp_config",
     "deepspeed.module_inject.auto_tp": "deepspeed_b200.parallel.tp",
     "deepspeed.module_inject.auto_ep": "deepspeed_b200.parallel.auto_ep",
+    "deepspeed.module_inject.auto_ep_layer": "deepspeed_b200.parallel.auto_ep",
+    "deepspeed.module_inject.auto_ep_config": "deepspeed_b200.parallel.auto_ep_presets",
+    "deepspeed.module_inject.auto_ep_folding": "deepspeed_b200.parallel.auto_ep_folding",
+    "deepspeed.module_inject.auto_ep_presets": "deepspeed_b200.parallel.auto_ep_presets",
+    "deepspeed.module_inject.auto_ep_presets.base": "deepspeed_b200.parallel.auto_ep_presets",
+    "deepspeed.module_inject.auto_ep_presets.registry": "deepspeed_b200.parallel.auto_ep_presets",
+    "deepspeed.moe.ep_router": "deepspeed_b200.parallel.auto_ep",
+    "deepspeed.moe.ep_experts": "deepspeed_b200.parallel.auto_ep",
+    "deepspeed.moe.fused_expert_layout": "deepspeed_b200.moe.fused_expert_layout",
     "deepspeed.model_implementations.transformers.ds_transformer":
     "deepspeed_b200.ops.transformer.inference.ds_transformer",
     "deepspeed.ops.transformer.inference.ds_attention": "deepspeed_b200.ops.transformer.inference.ds_transformer",

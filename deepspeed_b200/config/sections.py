@@ -287,17 +287,38 @@ class TPTrainingConfig(DeepSpeedConfigModel):
 
 
 class ExpertParallelConfig(DeepSpeedConfigModel):
+    """``expert_parallel`` section (reference ``module_inject/auto_ep_config.py::parse_autoep_config``); the keys the
+    user actually wrote are what ``parallel/auto_ep_presets.parse_autoep_config`` hands to AutoEP."""
     enabled: bool = False
     autoep_size: int = 1
+    expert_tensor_parallel_size: int = 1
+    validate_folding_routing: bool = False
     preset_model: Optional[str] = None
     moe_layer_pattern: Optional[str] = None
     router_pattern: Optional[str] = None
     expert_pattern: Optional[str] = None
     num_experts: Optional[int] = None
-    top_k: Optional[int] = None
     use_grouped_mm: bool = True
-    expert_tensor_parallel_size: int = 1
-    load_balance_coeff: float = 0.0
+    disable_triton_grouped_mm: bool = False
+    route_norm: Optional[bool] = None
+    route_scale: float = 1.0
+    score_apply: str = "auto"
+    combine_impl: str = "auto"
+    num_expert_groups: Optional[int] = None
+    num_limited_groups: Optional[int] = None
+    score_func: str = "auto"
+    top_k: Any = "auto"
+    load_balance_coeff: Optional[float] = None
+    routed_scaling_factor: Any = "auto"
+    expert_w1: Optional[str] = None
+    expert_w2: Optional[str] = None
+    expert_w3: Optional[str] = None
+    num_experts_attr: Optional[str] = None
+    top_k_attr: Optional[str] = None
+    has_shared_experts: Optional[bool] = None
+    shared_experts_pattern: Optional[str] = None
+    shared_experts_gate_pattern: Optional[str] = None
+    return_router_logits: Optional[bool] = None
     fused_dispatch: bool = True  # B200: in-kernel NVLink dispatch/combine
     model_config = dict(DeepSpeedConfigModel.model_config, extra="allow")
 

@@ -8,3 +8,6 @@ from .autotp_config import AutoTPConfig, AutoTPPresets, PartitionType, TPLayerSp
 from .replace_module import (DSPolicy, GroupQuantizer, HFBertLayerPolicy, ReplaceWithTensorSlicing,  # noqa: F401
                              generic_injection, quantize_transformer_layer, replace_transformer_layer,
                              revert_transformer_layer)
+from .auto_ep import AutoEP, AutoEPMoELayer, TokenChoiceTopKRouter, apply_autoep  # noqa: F401,E402
+from .auto_ep_presets import AutoEPConfig, MoELayerSpec, MoEModelPreset, parse_autoep_config  # noqa: F401,E402
+from .auto_ep_folding import ParallelFoldingSpec, build_folding_spec  # noqa: F401,E402

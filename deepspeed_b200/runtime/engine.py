@@ -177,7 +177,25 @@ class DeepSpeedEngine(EngineAccessorsMixin, Module):
             apply_autotp(model, self._config.tensor_parallel_config, groups._get_model_parallel_group())
         if self._config.expert_parallel_config.enabled:
             from ..parallel.auto_ep import apply_autoep
-            apply_autoep(model, self._config.expert_parallel_config)
+            from ..parallel.auto_ep_presets import parse_autoep_config, validate_autoep_config
+            ep_cfg = parse_autoep_config(self._config.expert_parallel_config)
+
+            def _offloads(section):
+                dev = getattr(section, "device", None)
+                return dev is not None and getattr(dev, "value", dev) != "none"
+
+            tp = int(self._config.tensor_parallel_config.autotp_size or 1)
+            zc = self._config.zero_config
+            validate_autoep_config(
+                ep_cfg, dist.get_world_size(), pp_size=int(groups._STATE.get("pp", 1) or 1),
+                tp_size=tp, sp_size=self.sequence_parallel_size, zero_stage=self._config.zero_optimization_stage,
+                deepcompile_enabled=bool(getattr(self._config.compile_config, "deepcompile", False)),
+                tp_preset_model=getattr(self._config.tensor_parallel_config, "preset_model", None),
+                use_data_before_expert_parallel=self._config.use_data_before_expert_parallel_, mpu=self.mpu,
+                zero_offload_optimizer=_offloads(getattr(zc, "offload_optimizer", None)),
+                zero_offload_param=_offloads(getattr(zc, "offload_param", None)))
+            # AutoEP folded over AutoTP: each lane routes its slice of the TP-replicated tokens
+            apply_autoep(model, ep_cfg, tp_group=groups._get_model_parallel_group() if tp > 1 else None)
         if not (self._config.torch_autocast_config.enabled):
             for p in model.parameters():
                 if p.is_floating_point() and p.dtype != dt and not hasattr(p, "ds_init_shard"):
