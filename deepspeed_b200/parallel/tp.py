@@ -384,10 +384,17 @@ class AutoTP:
 def apply_autotp(model, tp_config, mp_group):
     """Entry point used by the engine (``tensor_parallel.autotp_size > 1``) and ``deepspeed.tp_model_init``."""
     pc = getattr(tp_config, "partition_config", None) or {}
-    if not pc and hasattr(model, "config"):
-        pc = AutoTP.from_hf_tp_plan(model)
+    if not pc and not getattr(tp_config, "preset_model", None) and hasattr(model, "config"):
+        # priority: explicit partition_config / preset > the model's Hugging Face tp_plan > name heuristics
+        from .autotp_config import AutoTPConfig
+        from .tp_plan_converter import TPPlanConverter, get_hf_tp_plan
+        plan = get_hf_tp_plan(model)
+        specs = TPPlanConverter.convert(plan) if plan else None
+        if specs:
+            pc = AutoTPConfig(tp_size=_ws(mp_group), layer_specs=specs, use_default_specs=False)
     mode = "allreduce"
-    if getattr(tp_config, "fused_collectives", False) and pc.get("sequence_parallel_activations", False):
+    if getattr(tp_config, "fused_collectives", False) and isinstance(pc, dict) and \
+            pc.get("sequence_parallel_activations", False):
         mode = "rs_ag"
     return AutoTP(model, mp_group, tp_config, pc, mode=mode).apply()
 

@@ -125,3 +125,52 @@ def _two_ranks():
 
 def test_tp_layers_two_ranks():
     assert all(run_distributed(_two_ranks, 2))
+
+
+def test_tp_plan_converter_styles():
+    from deepspeed_b200.parallel.autotp_config import PartitionType
+    from deepspeed_b200.parallel.tp_plan_converter import TPPlanConverter
+    specs = TPPlanConverter.convert({"layers.*.self_attn.q_proj": "colwise", "layers.*.mlp.down_proj": "rowwise",
+                                     "lm_head": "colwise_gather_output", "layers.*.norm.weight":
+                                     "replicated_with_grad_allreduce"})
+    kinds = [(s.partition_type, s.gather_output, s.grad_allreduce) for s in specs]
+    assert kinds == [(PartitionType.COLUMN, False, False), (PartitionType.ROW, False, False),
+                     (PartitionType.COLUMN, True, False), (PartitionType.SKIP, False, True)]
+    assert specs[0].patterns == [r".*layers\..*\.self_attn\.q_proj\.weight$"]
+    assert specs[3].patterns == [r".*layers\..*\.norm\.weight$"]
+    assert TPPlanConverter.convert({}) is None
+    with pytest.raises(ValueError, match="unsupported partition style"):
+        TPPlanConverter.convert({"a": "colwise", "b": "local_packed_rowwise"})
+
+
+def _hf_plan():
+    """HF Llama sharded by its own tp_plan through TpTrainingManager equals the unsharded model; lanes share RNG."""
+    import transformers as T
+    import deepspeed_b200.comm as dist
+    from deepspeed_b200.parallel.tp import LinearAllreduce, LinearLayer
+    from deepspeed_b200.runtime.tensor_parallel import TpTrainingManager
+    torch.manual_seed(0)
+    cfg = T.LlamaConfig(vocab_size=64, hidden_size=32, intermediate_size=48, num_hidden_layers=2,
+                        num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=32)
+    m = T.LlamaForCausalLM(cfg).eval()
+    ids = torch.randint(0, 64, (2, 7))
+    with torch.no_grad():
+        want = m(ids).logits
+    torch.manual_seed(100 + dist.get_rank())  # lanes start with different generators
+    mgr = TpTrainingManager(m, tp_size=2, dtype=torch.float32)
+    draws = torch.rand(4)
+    both = [torch.empty(4) for _ in range(2)]
+    dist.all_gather(both, draws)
+    assert torch.equal(both[0], both[1])
+    layer = m.model.layers[0]
+    assert isinstance(layer.self_attn.q_proj, LinearLayer) and isinstance(layer.mlp.down_proj, LinearAllreduce)
+    assert layer.self_attn.q_proj.weight.shape == (16, 32) and layer.mlp.down_proj.weight.shape == (32, 24)
+    assert mgr.tp_config.tp_size == 2 and m.ds_autotp_parsed
+    with torch.no_grad():
+        got = m(ids).logits
+    torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+    return True
+
+
+def test_hf_tp_plan_through_training_manager():
+    assert all(run_distributed(_hf_plan, 2))
