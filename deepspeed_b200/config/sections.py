@@ -481,6 +481,7 @@ class HybridEngineConfig(DeepSpeedConfigModel):
     release_inference_cache: bool = False
     pin_parameters: bool = True
     tp_gather_partition_size: int = 8
+    enable_cuda_graph: bool = False  # replay the decode forward from CUDA graphs (runtime/hybrid_engine_graph.py)
 
 
 class GraphHarvestingConfig(DeepSpeedConfigModel):

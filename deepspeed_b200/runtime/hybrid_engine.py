@@ -10,7 +10,7 @@ import time
 
 import torch
 
-from ..utils.logging import log_dist
+from ..utils.logging import log_dist, logger
 from .engine import DeepSpeedEngine
 
 
@@ -48,6 +48,14 @@ class DeepSpeedHybridEngine(DeepSpeedEngine):
         self.is_lora_fused = False
         self._gather_ctx = None
         self._orig_generate = getattr(self.module, "generate", None)
+        self._decode_graphs = None
+        if getattr(cfg, "enable_cuda_graph", False):
+            from .hybrid_engine_graph import DecodeGraphCache, validate_cuda_graph_support
+            why = validate_cuda_graph_support(cfg, self.zero_optimization_stage())
+            if why is None:
+                self._decode_graphs = DecodeGraphCache(self.module.forward, self.max_out_tokens)
+            else:
+                logger.warning(f"hybrid_engine.enable_cuda_graph ignored: {why}")
         log_dist(f"DeepSpeedHybridEngine: ZeRO-3={self.Z3_enabled}, LoRA layers={len(_lora_pairs(self.module))}", [0])
 
     # ---- LoRA -----------------------------------------------------------------------------------
@@ -108,10 +116,19 @@ class DeepSpeedHybridEngine(DeepSpeedEngine):
         self._enter_generation()
         try:
             t0 = time.time()
-            if self._orig_generate is not None:
-                out = self._orig_generate(*inputs, **kwargs)
-            else:
-                out = self._greedy_generate(*inputs, **kwargs)
+            graphs = self._decode_graphs
+            if graphs is not None:
+                from .hybrid_engine_graph import decode_steps_from_generate_kwargs
+                graphs.begin_sequence(decode_steps_from_generate_kwargs(kwargs))
+                self.module.forward = graphs  # the decode forwards of this call go through the graph cache
+            try:
+                if self._orig_generate is not None:
+                    out = self._orig_generate(*inputs, **kwargs)
+                else:
+                    out = self._greedy_generate(*inputs, **kwargs)
+            finally:
+                if graphs is not None:
+                    del self.module.forward  # back to the class's forward
             if torch.cuda.is_available():
                 torch.cuda.synchronize()
             self._generate_latency += time.time() - t0
