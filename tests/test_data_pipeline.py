@@ -220,3 +220,50 @@ def test_random_ltd_layer_and_scheduler():
     assert sch.state["consumed_layer_tokens"] == 6 * (4 * 2 + S * 2) + 6 * (S * 2 + S * 2)
     sd = remove_random_ltd_state_dict(model.state_dict())
     assert "1.lin.weight" in sd and not any("random_ltd_layer" in k for k in sd)
+
+
+def test_legacy_indexed_dataset_lazy_and_cached(tmp_path):
+    """The fairseq / Megatron ``TNTIDX`` format (reference indexed_dataset.py:139-330): builder, lazy and cached
+    readers, merge, slices, implementation inference."""
+    import numpy as np
+    import torch
+    from deepspeed_b200.runtime.data_pipeline.data_sampling import indexed_dataset as I
+    items = [torch.arange(5), torch.arange(6).view(2, 3), torch.tensor([7]), torch.arange(4)]
+
+    def build(prefix, chunk):
+        b = I.make_builder(I.data_file_path(prefix), impl="lazy")
+        assert isinstance(b, I.IndexedDatasetBuilder)
+        for t in chunk:
+            b.add_item(t)
+            b.end_document()
+        b.finalize(I.index_file_path(prefix))
+
+    a, c = str(tmp_path / "a"), str(tmp_path / "c")
+    build(a, items[:2])
+    build(c, items[2:])
+    merged = str(tmp_path / "m")
+    b = I.IndexedDatasetBuilder(I.data_file_path(merged))
+    b.merge_file_(a)
+    b.merge_file_(c)
+    b.finalize(I.index_file_path(merged))
+    assert I.infer_dataset_impl(merged) == "cached" and I.dataset_exists(merged, "lazy")
+    lazy = I.make_dataset(merged, "lazy")
+    assert len(lazy) == 4 and lazy.dtype == np.int32
+    for got, want in zip((lazy[i] for i in range(4)), items):
+        assert got.shape == tuple(want.shape) and np.array_equal(got, want.numpy())
+    parts = lazy[1:4]
+    assert [p.tolist() for p in parts] == [list(range(6)), [7], [0, 1, 2, 3]]
+    assert lazy.doc_idx.tolist() == [0, 1, 3, 4, 5]  # size entries: the 2-D item contributes two
+    with pytest.raises(IndexError):
+        lazy[4]
+    with pytest.raises(ValueError):
+        lazy[0:4:2]
+    cached = I.make_dataset(merged, "cached")
+    assert cached.supports_prefetch and not lazy.supports_prefetch
+    cached.prefetch([3, 0, 1])
+    assert cached[0].tolist() == [0, 1, 2, 3, 4] and cached[1].shape == (2, 3) and cached[3].tolist() == [0, 1, 2, 3]
+    import pickle
+    again = pickle.loads(pickle.dumps(lazy))
+    assert again[2].tolist() == [7]
+    assert I.create_doc_idx([3, 0, 2, 0]) == [0, 2, 4] and set(I.get_available_dataset_impl()) == {"lazy", "cached", "mmap"}
+    assert I.make_dataset(str(tmp_path / "nothing"), "lazy") is None
