@@ -38,6 +38,9 @@ _ALIASES = {
     "deepspeed.module_inject.layers": "deepspeed_b200.parallel.layers",
     "deepspeed.module_inject.autotp_config": "deepspeed_b200.parallel.autotp_config",
     "deepspeed.module_inject.auto_tp": "deepspeed_b200.parallel.tp",
+    "deepspeed.comm.backend": "deepspeed_b200.comm.backend",
+    "deepspeed.comm.torch": "deepspeed_b200.comm.backend",
+    "deepspeed.comm.config": "deepspeed_b200.comm.config",
     "deepspeed.module_inject.tp_plan_converter": "deepspeed_b200.parallel.tp_plan_converter",
     "deepspeed.runtime.tensor_parallel": "deepspeed_b200.runtime.tensor_parallel",
     "deepspeed.runtime.tensor_parallel.tp_manager": "deepspeed_b200.runtime.tensor_parallel.tp_manager",

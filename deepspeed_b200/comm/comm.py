@@ -187,6 +187,9 @@ DEFAULT_AML_MASTER_PORT = "54965"
 DEFAULT_AML_NCCL_SOCKET_IFNAME = "^docker0,lo"
 
 
+cdb = None  # the backend object (reference ``comm.py`` global of the same name), built on demand
+
+
 def init_deepspeed_backend(ds_backend, timeout, init_method):
     """The reference can swap in its own (non-torch) backends here; every backend of this framework is
     ``torch.distributed`` plus the in-kernel NVLink collectives of ``comm/symm.py``, so there is nothing to build."""
@@ -195,6 +198,10 @@ def init_deepspeed_backend(ds_backend, timeout, init_method):
 
 def set_backend():
     """Reference ``comm.py:203``: select the active backend object; a single backend exists here."""
+    global cdb
+    if cdb is None and is_initialized():
+        from .backend import TorchBackend
+        cdb = TorchBackend(_device_backend())
     return _device_backend()
 
 
