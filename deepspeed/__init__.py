@@ -38,6 +38,17 @@ _ALIASES = {
     "deepspeed.module_inject.layers": "deepspeed_b200.parallel.layers",
     "deepspeed.module_inject.autotp_config": "deepspeed_b200.parallel.autotp_config",
     "deepspeed.module_inject.auto_tp": "deepspeed_b200.parallel.tp",
+    "deepspeed.runtime.model_checkpointing": "deepspeed_b200.runtime.model_checkpointing",
+    "deepspeed.runtime.model_checkpointing.constants": "deepspeed_b200.runtime.model_checkpointing.constants",
+    "deepspeed.runtime.model_checkpointing.config": "deepspeed_b200.runtime.model_checkpointing.config",
+    "deepspeed.runtime.model_checkpointing.utils": "deepspeed_b200.runtime.model_checkpointing.utils",
+    "deepspeed.runtime.model_checkpointing.writer_factory": "deepspeed_b200.runtime.model_checkpointing.writer_factory",
+    "deepspeed.runtime.model_checkpointing.data_parallel_writer_factory":
+    "deepspeed_b200.runtime.model_checkpointing.data_parallel_writer_factory",
+    "deepspeed.io.base_file_writer": "deepspeed_b200.io.base_file_writer",
+    "deepspeed.io.base_io_buffer": "deepspeed_b200.io.io_buffers",
+    "deepspeed.io.single_io_buffer": "deepspeed_b200.io.io_buffers",
+    "deepspeed.io.double_io_buffer": "deepspeed_b200.io.io_buffers",
     "deepspeed.comm.backend": "deepspeed_b200.comm.backend",
     "deepspeed.comm.torch": "deepspeed_b200.comm.backend",
     "deepspeed.comm.config": "deepspeed_b200.comm.config",

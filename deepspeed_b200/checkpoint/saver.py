@@ -344,12 +344,14 @@ def save_engine_checkpoint(engine, save_dir, tag=None, client_state=None, save_l
         if uc is not None:
             state[UNIVERSAL_CHECKPOINT_INFO] = uc() if callable(uc) else uc
         state.update(client_state or {})
-        if engine.seq_dp_rank == 0 or engine.zero_optimization_partition_weights():
+        if engine.zero_optimization_partition_weights() or ce.is_data_parallel_writer(engine.seq_dp_rank):
             ce.save(state, get_ckpt_name(engine, save_dir, tag))
 
     if zero_sd is not None:
-        ce.save({OPTIMIZER_STATE_DICT: zero_sd, "ds_config": engine.config, "ds_version": __version__},
-                get_zero_ckpt_name(engine, save_dir, tag))
+        zero_state = {OPTIMIZER_STATE_DICT: zero_sd, "ds_config": engine.config, "ds_version": __version__}
+        # this rank's own shard: never shared between data-parallel writers
+        kw = {"replicated": False} if getattr(ce, "supports_shared_write", False) else {}
+        ce.save(zero_state, get_zero_ckpt_name(engine, save_dir, tag), **kw)
         if engine.global_rank == 0:
             _copy_recovery_script(os.path.join(save_dir, tag))
 
@@ -404,9 +406,18 @@ def load_engine_checkpoint(engine, load_dir, tag=None, load_module_strict=True, 
         alt3 = os.path.join(load_dir, str(tag), f"zero_pp_rank_{engine.seq_dp_rank}_mp_rank_{_mp_rank(engine):02d}_model_states.pt")
         path = alt if os.path.exists(alt) else alt3
     if not os.path.exists(path):
-        logger.warning(f"Client provided checkpoint load path: {path} does not exist")
-        return None, None
-    ckpt = ce.load(path, map_location="cpu")
+        from ..io import find_striped_writers
+        if find_striped_writers(get_ckpt_name(engine, load_dir, tag)) is not None:
+            path = get_ckpt_name(engine, load_dir, tag)  # written in stripes by several data-parallel ranks
+        else:
+            logger.warning(f"Client provided checkpoint load path: {path} does not exist")
+            return None, None
+    if not os.path.exists(path):
+        from ..io import StripedReader
+        with StripedReader(path) as f:
+            ckpt = torch.load(f, map_location="cpu", weights_only=False)
+    else:
+        ckpt = ce.load(path, map_location="cpu")
     zero3 = engine.zero_optimization_partition_weights()
 
     have_zero_files = engine.optimizer is not None and os.path.exists(get_zero_ckpt_name(engine, load_dir, tag))

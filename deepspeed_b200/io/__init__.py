@@ -1,3 +1,6 @@
-from .fast_file_writer import FastFileWriter, FastFileWriterConfig
-from .mock_file_writer import MockFileWriter
-from .py_file_writer import PyFileWriter  # noqa: F401,E402
+from .base_file_writer import BaseFileWriter  # noqa: F401
+from .io_buffers import Base_IO_Buffer, Double_IO_Buffer, Single_IO_Buffer  # noqa: F401
+from .fast_file_writer import (FastFileWriter, FastFileWriterConfig, StripedReader, find_striped_writers,  # noqa: F401
+                               striped_file_path)
+from .mock_file_writer import MockFileWriter  # noqa: F401
+from .py_file_writer import PyFileWriter  # noqa: F401

@@ -1,9 +1,11 @@
 """Fake writer for tests of the fast writer path (reference ``deepspeed/io/mock_file_writer.py``)."""
+from .base_file_writer import WRITE_BYTES_KEY, WRITE_COUNT_KEY, BaseFileWriter
 
 
-class MockFileWriter:
+class MockFileWriter(BaseFileWriter):
 
     def __init__(self, file_path=None):
+        super().__init__(file_path)
         self.path = file_path
         self.bytes_written = 0
         self.calls = 0
@@ -11,10 +13,6 @@ class MockFileWriter:
     def write(self, data):
         self.bytes_written += len(data)
         self.calls += 1
+        self._incr_stats(WRITE_COUNT_KEY)
+        self._incr_stats(WRITE_BYTES_KEY, len(data))
         return len(data)
-
-    def flush(self):
-        pass
-
-    def close(self):
-        pass

@@ -2,42 +2,29 @@
 ``base_file_writer.py``): the baseline the checkpoint benchmarks compare ``FastFileWriter`` against."""
 import time
 
-INVALID_FD = -1
+from .base_file_writer import (CLOSE_COUNT_KEY, FLUSH_COUNT_KEY, INVALID_FD, WRITE_BYTES_KEY, WRITE_COUNT_KEY,  # noqa: F401
+                               WRITE_SEC_KEY, BaseFileWriter)
 
 
-class PyFileWriter:
+class PyFileWriter(BaseFileWriter):
 
     def __init__(self, file_path):
+        super().__init__(file_path)
         self.path = file_path
         self._fp = open(file_path, "wb")
-        self._stats = {"close": 0, "fileno": 0, "flush": 0, "write": 0, "write_bytes": 0, "write_sec": 0.0}
 
     def write(self, buffer):
         t0 = time.time()
         self._fp.write(buffer)
-        self._stats["write_sec"] += time.time() - t0
-        self._stats["write"] += 1
-        self._stats["write_bytes"] += len(buffer)
+        self._incr_stats(WRITE_SEC_KEY, time.time() - t0)
+        self._incr_stats(WRITE_COUNT_KEY)
+        self._incr_stats(WRITE_BYTES_KEY, len(buffer))
         return len(buffer)
 
     def flush(self):
-        self._stats["flush"] += 1
+        self._incr_stats(FLUSH_COUNT_KEY)
         self._fp.flush()
 
-    def fileno(self):
-        self._stats["fileno"] += 1
-        return INVALID_FD  # torch.save must not bypass write() through the descriptor
-
     def close(self):
-        self._stats["close"] += 1
+        self._incr_stats(CLOSE_COUNT_KEY)
         self._fp.close()
-
-    def get_stats(self):
-        return dict(self._stats)
-
-    def __enter__(self):
-        return self
-
-    def __exit__(self, *exc):
-        self.close()
-        return False

@@ -70,20 +70,62 @@ class TorchCheckpointEngine(CheckpointEngine):
 
 class FastCheckpointEngine(CheckpointEngine):
     """Serialises with torch's pickle protocol into a pinned double-buffered native writer
-    (:class:`deepspeed_b200.io.FastFileWriter`, O_DIRECT + worker threads)."""
+    (:class:`deepspeed_b200.io.FastFileWriter`, O_DIRECT + worker threads).
 
-    def __init__(self, config_params=None, dp_writer=True):
+    ``dp_writer_config`` (``runtime/model_checkpointing``): with a ``data_parallel`` unit in the writer section, the
+    ranks elected among those holding the same state each write a stripe set of the model-state file
+    (``<file>-<rank>.<N>``); ranks that were not elected write no replicated state at all. ``load`` accepts either
+    layout. ``optimize_dp_state`` is off when the weights themselves are partitioned (ZeRO-3): nothing is replicated."""
+
+    supports_shared_write = True
+
+    def __init__(self, config_params=None, dp_writer_config="rank0", optimize_dp_state=True):
         super().__init__(config_params)
-        from ...io.fast_file_writer import FastFileWriter, FastFileWriterConfig
-        self._writer_cls, self._cfg_cls = FastFileWriter, FastFileWriterConfig
+        from ..model_checkpointing import CheckpointWriterFactory, get_checkpoint_writer_config
+        self.name = "FastCheckpointEngine"
         w = getattr(config_params, "writer", None)
-        self.io_buffer_size = getattr(w, "io_buffer_size", 1 << 28) if w else 1 << 28
-        self.double = getattr(w, "io_buffer_double", True) if w else True
+        wd = w.model_dump() if hasattr(w, "model_dump") else dict(w or {})
+        wd["type"] = "fast"
+        if not wd.get("io_buffer_size"):
+            wd["io_buffer_size"] = 1 << 28
+        self._writer_cfg = get_checkpoint_writer_config({"writer": wd})
+        self.dp_writer_config = dp_writer_config
+        self.optimize_dp_state = optimize_dp_state
+        self.io_buffer_size = self._writer_cfg["io_buffer_size"]
+        self.double = self._writer_cfg["io_buffer_double"]
+        self._factory = None
+        self._factory_cls = CheckpointWriterFactory
+        self._aio = getattr(config_params, "aio_config", None)
 
-    def save(self, state_dict, path):
-        writer = self._writer_cls(path, self._cfg_cls(io_buffer_size=self.io_buffer_size, double_buffer=self.double))
-        torch.save(state_dict, writer, _use_new_zipfile_serialization=False)
-        writer.close()
+    def _shares(self):
+        dp = self.dp_writer_config
+        return self.optimize_dp_state and dp is not None and dp != "rank0" and dp.world_size > 1
+
+    def save(self, state_dict, path, replicated=True):
+        """``replicated``: the state is identical on the ranks of the data-parallel group (model states); per-rank
+        files (ZeRO shards) are always written whole."""
+        if self._factory is None:
+            dp = None if self.dp_writer_config == "rank0" else self.dp_writer_config
+            self._factory = self._factory_cls(self._writer_cfg, self._aio, dp)
+        writer = self._factory.create_writer(path, bool(replicated and self._shares()))
+        try:
+            torch.save(state_dict, writer, _use_new_zipfile_serialization=False)
+        finally:
+            self._factory.release_writer()
+
+    def load(self, path, map_location=None):
+        if not os.path.exists(path):
+            from ...io import StripedReader, find_striped_writers
+            n = find_striped_writers(path)
+            if n is not None:
+                with StripedReader(path, n) as f:
+                    return torch.load(f, map_location=map_location, weights_only=False)
+        return torch.load(path, map_location=map_location, weights_only=False)
+
+    def is_data_parallel_writer(self, dp_rank):
+        if self.dp_writer_config == "rank0":
+            return dp_rank == 0
+        return self.dp_writer_config is not None
 
 
 def _writer_main(q, done):
@@ -256,7 +298,7 @@ class DataStatesCheckpointEngine(CheckpointEngine):
         return False
 
 
-def create_checkpoint_engine(config):
+def create_checkpoint_engine(config, zero_stage=0, has_moe_layers=False):
     neb = getattr(config, "nebula_config", None) or {}
     if isinstance(neb, dict) and neb.get("enabled", False):
         from ...nebula.config import DeepSpeedNebulaConfig
@@ -278,7 +320,14 @@ def create_checkpoint_engine(config):
         kind = "decoupled"
     if kind == "fast":
         try:
-            return FastCheckpointEngine(ck)
+            dp_cfg = "rank0"
+            unit = getattr(w, "data_parallel", None)
+            from ... import comm as _dist
+            if unit and _dist.is_initialized():
+                from ...utils import groups as _groups
+                from ..model_checkpointing import create_data_parallel_writer_config
+                dp_cfg = create_data_parallel_writer_config(_groups, str(unit).upper(), zero_stage, has_moe_layers)
+            return FastCheckpointEngine(ck, dp_cfg, optimize_dp_state=int(zero_stage) != 3)
         except Exception as e:
             logger.warning(f"FastCheckpointEngine unavailable ({e}); falling back to torch")
             return TorchCheckpointEngine(ck)

@@ -356,10 +356,12 @@ class DeepSpeedEngine(EngineAccessorsMixin, Module):
 
     def _configure_checkpointing(self):
         from .checkpoint_engine import create_checkpoint_engine
-        self.checkpoint_engine = create_checkpoint_engine(self._config)
+        self.checkpoint_engine = create_checkpoint_engine(self._config, self._config.zero_optimization_stage,
+                                                          getattr(self, "has_moe_layers", False))
         dp_rank = self.seq_dp_rank
         # who writes what (reference engine.py:1574-1597)
-        self.save_non_zero_checkpoint = (dp_rank == 0) or self.zero_optimization_partition_weights()
+        self.save_non_zero_checkpoint = self.checkpoint_engine.is_data_parallel_writer(dp_rank) or \
+            self.zero_optimization_partition_weights()
         self.save_zero_checkpoint = self.zero_optimization() or self.bfloat16_enabled()
 
     def _configure_aux_features(self):
