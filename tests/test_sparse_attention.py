@@ -99,3 +99,56 @@ def test_bert_sparse_self_attention_shapes():
     x = torch.randn(2, 64, 64)
     mask = torch.zeros(2, 64)
     assert layer(x, mask).shape == (2, 64, 64)
+
+
+def test_block_sparse_matmul_modes_and_softmax_match_dense():
+    """The standalone block-sparse ops (reference ops/sparse_attention/matmul.py, softmax.py) against dense math with
+    the layout applied as a mask; an attention built from them equals SparseSelfAttention."""
+    import torch
+    from deepspeed_b200.ops.sparse_attention.matmul import MatMul, to_dense, to_sparse
+    from deepspeed_b200.ops.sparse_attention.softmax import Softmax
+    torch.manual_seed(0)
+    B, H, L, D, blk = 2, 3, 64, 16, 16
+    layout = (torch.rand(H, L // blk, L // blk) > 0.4).long()
+    layout[:, torch.arange(L // blk), torch.arange(L // blk)] = 1  # every row keeps its diagonal block
+    q, k, v = (torch.randn(B, H, L, D, requires_grad=True) for _ in range(3))
+    mask = layout.repeat_interleave(blk, 1).repeat_interleave(blk, 2).bool()  # [H, L, L]
+    # sdd: Q K^T on the pattern
+    sdd = MatMul(layout, blk, "sdd", trans_b=True)
+    w = sdd(q, k)
+    assert w.shape == (B, int(layout.sum()), blk, blk)
+    dense_w = torch.matmul(q, k.transpose(-1, -2))
+    torch.testing.assert_close(w, to_sparse(dense_w, layout, blk), rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(to_dense(w, layout, blk), dense_w * mask, rtol=1e-4, atol=1e-5)
+    # softmax with scale, rpe, masks
+    rpe = torch.randn(H, L, L)
+    kpm = torch.zeros(B, L)
+    kpm[:, -5:] = -1e4
+    am = torch.tril(torch.ones(L, L))
+    p = Softmax(layout, blk)(w, scale=D**-0.5, rpe=rpe, key_padding_mask=kpm, attn_mask=am,
+                             key_padding_mask_mode="add", attn_mask_mode="mul")
+    ref = dense_w * D**-0.5 + rpe + kpm[:, None, None, :] + (1 - am) * torch.finfo(torch.float32).min
+    ref = torch.softmax(ref.masked_fill(~mask, float("-inf")), -1)
+    torch.testing.assert_close(to_dense(p, layout, blk), ref, rtol=1e-4, atol=1e-6)
+    # dsd: P V ; gradients flow through all three ops
+    out = MatMul(layout, blk, "dsd")(p, v)
+    want = torch.matmul(ref, v)
+    torch.testing.assert_close(out, want, rtol=1e-4, atol=1e-5)
+    g = torch.randn_like(out)
+    got = torch.autograd.grad(out, (q, k, v), g, retain_graph=True)
+    exp = torch.autograd.grad(want, (q, k, v), g)
+    for a, b in zip(got, exp):
+        torch.testing.assert_close(a, b, rtol=1e-3, atol=1e-5)
+    # dds: dense x sparse, and the transposed variants
+    x = torch.randn(B, H, 32, L)
+    sp = to_sparse(dense_w.detach() * mask, layout, blk)
+    torch.testing.assert_close(MatMul(layout, blk, "dds")(x, sp), torch.matmul(x, dense_w.detach() * mask), rtol=1e-4,
+                               atol=1e-4)
+    torch.testing.assert_close(MatMul(layout, blk, "dds", trans_b=True)(x, sp),
+                               torch.matmul(x, (dense_w.detach() * mask).transpose(-1, -2)), rtol=1e-4, atol=1e-4)
+    y = torch.randn(B, H, L, 8)
+    torch.testing.assert_close(MatMul(layout, blk, "dsd", trans_a=True)(sp, y),
+                               torch.matmul((dense_w.detach() * mask).transpose(-1, -2), y), rtol=1e-4, atol=1e-4)
+    import pytest
+    with pytest.raises(NotImplementedError):
+        MatMul(layout, blk, "ddd")
