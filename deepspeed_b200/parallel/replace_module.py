@@ -247,14 +247,48 @@ class GroupQuantizer:
 
 
 def generic_injection(module, dtype=None, enable_cuda_graph=True):
-    """Reference: fused attention / CUDA-graph wrappers for diffusers pipelines (UNet, VAE, CLIP). Here the spatial
-    ops of ``ops/spatial`` (``csrc/spatial.cu``) are used by the models that call them; the pipeline itself is only cast
-    to ``dtype`` and optionally wrapped for CUDA-graph replay of its sub-models."""
+    """Reference ``module_inject/replace_module.py::generic_injection``: in a diffusers pipeline (or any module tree)
+    replace every attention module that looks like diffusers' ``Attention`` / ``CrossAttention`` (``to_q`` / ``to_k`` /
+    ``to_v`` / ``to_out``) by :class:`DeepSpeedDiffusersAttention` and every ``BasicTransformerBlock`` (``norm1..3``,
+    ``attn1``, ``attn2``, GEGLU ``ff``) by :class:`DeepSpeedDiffusersTransformerBlock`; the sub-models are cast to
+    ``dtype``. Returns the module; ``module.ds_injected`` counts what was replaced."""
+    from ..ops.transformer.inference.config import DeepSpeedInferenceConfig
+    from ..ops.transformer.inference.diffusers_2d_transformer import Diffusers2DTransformerConfig
+    from ..ops.transformer.inference.diffusers_attention import DeepSpeedDiffusersAttention
+    from ..ops.transformer.inference.diffusers_transformer_block import DeepSpeedDiffusersTransformerBlock
+    roots = [getattr(module, n) for n in ("unet", "vae", "text_encoder") if isinstance(getattr(module, n, None), nn.Module)]
+    if not roots and isinstance(module, nn.Module):
+        roots = [module]
     if dtype is not None:
-        for name in ("unet", "vae", "text_encoder"):
-            sub = getattr(module, name, None)
-            if isinstance(sub, nn.Module):
-                sub.to(dtype)
-    if enable_cuda_graph and torch.cuda.is_available():
-        from ..compile.graph_capture import CUDAGraphRunner  # noqa: F401  (callers wrap fixed-shape sub-models)
+        for r in roots:
+            r.to(dtype)
+
+    def is_attention(m):
+        return all(hasattr(m, n) for n in ("to_q", "to_k", "to_v", "to_out")) and hasattr(m, "heads") and \
+            isinstance(m.to_q, nn.Linear) and not isinstance(m, DeepSpeedDiffusersAttention)
+
+    def is_block(m):
+        ff = getattr(m, "ff", None)
+        return all(hasattr(m, n) for n in ("norm1", "norm2", "norm3", "attn1", "attn2")) and ff is not None and \
+            hasattr(ff, "net") and hasattr(ff.net[0], "proj") and getattr(m, "attn2", None) is not None and \
+            not isinstance(m, DeepSpeedDiffusersTransformerBlock)
+
+    n_attn = n_block = 0
+    for root in roots:
+        for parent in list(root.modules()):
+            for name, child in list(parent.named_children()):
+                if is_attention(child):
+                    w = child.to_q.weight
+                    cfg = DeepSpeedInferenceConfig(hidden_size=w.shape[0], heads=child.heads, dtype=w.dtype)
+                    setattr(parent, name, DeepSpeedDiffusersAttention.from_module(child, cfg))
+                    n_attn += 1
+        for parent in list(root.modules()):
+            for name, child in list(parent.named_children()):
+                if is_block(child):
+                    setattr(parent, name, DeepSpeedDiffusersTransformerBlock(child, Diffusers2DTransformerConfig()))
+                    n_block += 1
+    try:
+        module.ds_injected = {"attention": n_attn, "transformer_block": n_block}
+    except Exception:  # noqa: BLE001
+        pass
     return module
