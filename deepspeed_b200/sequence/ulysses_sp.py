@@ -296,3 +296,81 @@ class UlyssesSPFwdLossBwdWithLogits:
         loss = loss_sum / stats[1].clamp(min=1) * self.sp_world_size  # grads are averaged over sp by ZeRO
         self.model.backward(loss)
         return stats[0] / stats[1].clamp(min=1)
+
+
+class AutogradComputeMLP(torch.autograd.Function):
+    """``AutogradComputeMLP.apply(fn, module, x)``: run ``fn(module, x)`` without keeping its activations and recompute
+    them in backward - the un-tiled skeleton of :class:`TiledMLP` (reference
+    ``runtime/sequence_parallel/ulysses_sp.py:1218``)."""
+
+    @staticmethod
+    def forward(ctx, fn, self, x):
+        ctx.fn, ctx.self = fn, self
+        ctx.save_for_backward(x)
+        with torch.no_grad():
+            return fn(self, x)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        (x, ) = ctx.saved_tensors
+        x1 = x.detach().requires_grad_(x.requires_grad)
+        with torch.enable_grad():
+            out = ctx.fn(ctx.self, x1)
+        torch.autograd.backward(out, grads[0])
+        return None, None, x1.grad
+
+
+class TiledLoss(torch.autograd.Function):
+    """Loss over existing logits computed shard by shard along the sequence, so that the fp32 upcast / softmax
+    temporaries exist for one shard at a time (reference ``ulysses_sp.py:1269``; :class:`TiledFusedLogitsLoss` goes
+    further and never materialises the logits).
+
+    ``loss_fn(logits=, labels=None, vocab_size=, shift_labels=)`` returns the mean over the labels that are not
+    ``-100``. The shards' means are combined weighted by their number of such labels (a shard made only of ``-100`` is
+    skipped), and backward weights each shard's gradient the same way, so the result and its gradient equal the
+    un-tiled call whatever the distribution of ignored labels. (The reference divides the accumulated gradient by the
+    shard count instead, which is exact only when every shard holds the same number of valid labels.)"""
+
+    @staticmethod
+    def _steps(seqlen, shards):
+        step = -(-seqlen // shards)
+        return [(lo, min(seqlen, lo + step)) for lo in range(0, seqlen, step)]
+
+    @staticmethod
+    def forward(ctx, loss_fn, logits, vocab_size, shift_labels, shards):
+        ctx.save_for_backward(logits, shift_labels)
+        ctx.loss_fn, ctx.vocab_size, ctx.shards = loss_fn, vocab_size, shards
+        total = None
+        counts = []
+        with torch.no_grad():
+            for lo, hi in TiledLoss._steps(shift_labels.shape[1], shards):
+                lab = shift_labels[:, lo:hi]
+                n = int((lab != -100).sum())
+                counts.append(n)
+                if n == 0:
+                    continue
+                part = loss_fn(logits=logits[:, lo:hi, :], labels=None, vocab_size=vocab_size, shift_labels=lab) * n
+                total = part if total is None else total + part
+        ctx.counts = counts
+        n_all = sum(counts)
+        if n_all == 0:
+            return (logits.sum() * 0.0).float()
+        return total / n_all
+
+    @staticmethod
+    def backward(ctx, *grads):
+        logits, shift_labels = ctx.saved_tensors
+        g = grads[0]
+        n_all = sum(ctx.counts)
+        logits_grad = torch.zeros_like(logits)
+        if n_all > 0:
+            for (lo, hi), n in zip(TiledLoss._steps(shift_labels.shape[1], ctx.shards), ctx.counts):
+                if n == 0:
+                    continue
+                shard = logits[:, lo:hi, :].detach().requires_grad_(True)
+                with torch.enable_grad():
+                    loss = ctx.loss_fn(logits=shard, labels=None, vocab_size=ctx.vocab_size,
+                                       shift_labels=shift_labels[:, lo:hi])
+                (gs, ) = torch.autograd.grad(loss, shard, g * (n / n_all))
+                logits_grad[:, lo:hi, :] = gs
+        return None, logits_grad, None, None, None

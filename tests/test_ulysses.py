@@ -178,3 +178,38 @@ def test_ulysses_uneven_heads():
     for r, (err, gerr, sizes, shape, ok1, ok2) in enumerate(res):
         assert err < 1e-5 and gerr < 1e-5 and sizes == [2, 1] and ok1 and ok2
         assert shape == (2, 8, sizes[r], 4)
+
+
+def test_tiled_loss_and_autograd_compute_mlp_match_plain():
+    """TiledLoss (uneven shards, uneven -100 distribution, an all-ignored shard) and AutogradComputeMLP equal the
+    plain computation in value and gradient."""
+    import torch
+    import torch.nn.functional as F
+    from deepspeed_b200.sequence.ulysses_sp import AutogradComputeMLP, TiledLoss
+
+    def loss_fn(logits=None, labels=None, vocab_size=None, shift_labels=None):
+        return F.cross_entropy(logits.float().reshape(-1, vocab_size), shift_labels.reshape(-1), ignore_index=-100)
+
+    torch.manual_seed(0)
+    logits = torch.randn(2, 23, 11, requires_grad=True)
+    labels = torch.randint(0, 11, (2, 23))
+    labels[:, :6] = -100  # the first shard of 4 (6 tokens each) is ignored entirely
+    labels[0, 10:17] = -100
+    want = loss_fn(logits=logits, vocab_size=11, shift_labels=labels)
+    (gw, ) = torch.autograd.grad(want, logits)
+    got = TiledLoss.apply(loss_fn, logits, 11, labels, 4)
+    (gg, ) = torch.autograd.grad(got, logits)
+    torch.testing.assert_close(got, want)
+    torch.testing.assert_close(gg, gw, rtol=1e-5, atol=1e-7)
+    none = TiledLoss.apply(loss_fn, logits, 11, torch.full((2, 23), -100), 3)
+    assert float(none) == 0.0 and float(torch.autograd.grad(none, logits)[0].abs().sum()) == 0.0
+
+    mlp = torch.nn.Sequential(torch.nn.Linear(8, 32), torch.nn.GELU(), torch.nn.Linear(32, 8))
+    x = torch.randn(3, 5, 8, requires_grad=True)
+    y0 = mlp(x)
+    g0 = torch.autograd.grad(y0.square().sum(), [x] + list(mlp.parameters()))
+    y1 = AutogradComputeMLP.apply(lambda m, t: m(t), mlp, x)
+    y1.square().sum().backward()
+    torch.testing.assert_close(y1, y0)
+    for a, b in zip([x.grad] + [p.grad for p in mlp.parameters()], g0):
+        torch.testing.assert_close(a, b)
