@@ -49,6 +49,8 @@ _ALIASES = {
     "deepspeed.io.base_io_buffer": "deepspeed_b200.io.io_buffers",
     "deepspeed.io.single_io_buffer": "deepspeed_b200.io.io_buffers",
     "deepspeed.io.double_io_buffer": "deepspeed_b200.io.io_buffers",
+    "deepspeed.runtime.zero.mics": "deepspeed_b200.runtime.zero.mics",
+    "deepspeed.runtime.zero.mics_utils": "deepspeed_b200.runtime.zero.mics",
     "deepspeed.comm.backend": "deepspeed_b200.comm.backend",
     "deepspeed.comm.torch": "deepspeed_b200.comm.backend",
     "deepspeed.comm.config": "deepspeed_b200.comm.config",
@@ -73,7 +75,6 @@ _ALIASES = {
     "deepspeed.ops.adam.zenflow_torch_adam": "deepspeed_b200.ops.adam.zenflow",
     "deepspeed.runtime.zero.leaf_module_config": "deepspeed_b200.config.sections",
     "deepspeed.runtime.zero.parameter_offload": "deepspeed_b200.runtime.zero.param_status",
-    "deepspeed.runtime.zero.mics": "deepspeed_b200.runtime.zero",
     "deepspeed.inference.v2.config_v2": "deepspeed_b200.inference.v2.engine_factory",
     "deepspeed.checkpoint.reshape_utils": "deepspeed_b200.checkpoint.reshape",
     "deepspeed.checkpoint.reshape_3d_utils": "deepspeed_b200.checkpoint.reshape",

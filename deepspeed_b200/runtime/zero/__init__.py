@@ -17,6 +17,8 @@ from ...utils.z3_leaf_module import (set_z3_leaf_modules, unset_z3_leaf_modules,
                                       get_z3_leaf_modules, set_z3_leaf_module, set_z3_leaf_modules_by_name,
                                       set_z3_leaf_modules_by_suffix, z3_leaf_parameter)
 
+from .mics import (DeepSpeedZeroOptimizer, DeepSpeedZeroOptimizer_Stage3, MiCS_AllGatherCoalescedHandle,  # noqa: F401,E402
+                   MiCS_CommGroups, MiCS_Offload, MiCS_Optimizer, create_mics_comm_groups)
 from .tiling import TiledLinear, TiledLinearReturnBias  # noqa: F401,E402
 from .param_status import (DeepSpeedTensorOverride, DeepSpeedZeRoOffload, ZeroParamStatus, ZeroParamType,  # noqa: F401,E402
                            unwrap_model_for_generation)

@@ -1512,3 +1512,10 @@ def _step_is_tensor(opt):
         if "step" in stt:
             return torch.is_tensor(stt["step"])
     return False
+
+
+def __getattr__(name):  # the reference's class names for this optimizer live in ``mics.py`` (which imports this module)
+    if name in ("DeepSpeedZeroOptimizer", "DeepSpeedZeroOptimizer_Stage3", "MiCS_Optimizer"):
+        from . import mics
+        return getattr(mics, name)
+    raise AttributeError(f"module {__name__!r} has no attribute {name!r}")

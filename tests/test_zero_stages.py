@@ -201,3 +201,54 @@ def test_zero3_sanity_checks_and_param_profiler():
     assert counts[pp.FORWARD_FETCH_WAIT] >= 3 * n
     assert counts.get(pp.FORWARD_PREFETCH_SUBMIT, 0) > 0  # steps after the trace step prefetch one unit ahead
     assert res[1][2] and res[0][2]  # the disagreement is raised on every rank (no rank is left in a collective)
+
+
+def test_mics_rank_tables():
+    from deepspeed_b200.runtime.zero.mics import mics_rank_tables
+    t = mics_rank_tables(8, 4)
+    assert t["shard_groups"] == [[0, 1, 2, 3], [4, 5, 6, 7]]
+    assert t["replicate_groups"] == [[0, 4], [1, 5], [2, 6], [3, 7]] and t["span_nodes"] == 1
+    t = mics_rank_tables(16, 8, ndev_per_node=4)  # a shard group over two nodes of four devices
+    assert t["span_nodes"] == 2
+    assert t["intra_node_groups"][:2] == [[0, 1, 2, 3], [4, 5, 6, 7]]
+    assert t["inter_node_groups"][:4] == [[0, 4], [1, 5], [2, 6], [3, 7]]
+    import pytest
+    with pytest.raises(AssertionError):
+        mics_rank_tables(8, 3)
+
+
+def _mics_hier():
+    import torch
+    import deepspeed_b200.comm as dist
+    from deepspeed_b200.runtime.zero.mics import (MiCS_AllGatherCoalescedHandle, create_mics_comm_groups,
+                                                  hierarchical_all_gather)
+    rank = dist.get_rank()
+    g = create_mics_comm_groups(4, hierarchical_allgather=True, ndev_per_node=2)  # 4 ranks = 2 "nodes" x 2 devices
+    assert (g.param_shard_size, g.param_shard_rank, g.param_repli_size) == (4, rank, 1)
+    assert g.param_intra_node_group is not None and g.param_inter_node_shard_group is not None
+    out = torch.empty(4 * 3)
+    hierarchical_all_gather(out, torch.full((3, ), float(rank)), g)
+    assert out.tolist() == [0.0] * 3 + [1.0] * 3 + [2.0] * 3 + [3.0] * 3
+    g2 = create_mics_comm_groups(2)  # shard pairs, replicate across them
+    assert (g2.param_shard_size, g2.param_repli_size, g2.param_repli_rank) == (2, 2, rank // 2)
+    out2 = torch.empty(2)
+    hierarchical_all_gather(out2, torch.tensor([float(rank)]), g2)
+    assert out2.tolist() == ([0.0, 1.0] if rank < 2 else [2.0, 3.0])
+    h = MiCS_AllGatherCoalescedHandle(None, [])
+    h.wait()
+    return h.complete
+
+
+def test_mics_groups_and_hierarchical_gather_four_ranks():
+    assert all(run_distributed(_mics_hier, 4))
+
+
+def test_reference_zero_class_names():
+    import torch
+    from deepspeed_b200.runtime.zero.mics import DeepSpeedZeroOptimizer, DeepSpeedZeroOptimizer_Stage3, MiCS_Optimizer
+    from deepspeed_b200.runtime.zero import ZeroShardedOptimizer
+    m = torch.nn.Linear(8, 8)
+    z = DeepSpeedZeroOptimizer(m, torch.optim.AdamW(m.parameters(), lr=1e-3), partition_gradients=True,
+                               dtype=torch.float32)
+    assert isinstance(z, ZeroShardedOptimizer) and z.stage == 2
+    assert issubclass(MiCS_Optimizer, DeepSpeedZeroOptimizer_Stage3)
