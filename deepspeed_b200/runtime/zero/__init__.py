@@ -19,6 +19,12 @@ from ...utils.z3_leaf_module import (set_z3_leaf_modules, unset_z3_leaf_modules,
 
 from .mics import (DeepSpeedZeroOptimizer, DeepSpeedZeroOptimizer_Stage3, MiCS_AllGatherCoalescedHandle,  # noqa: F401,E402
                    MiCS_CommGroups, MiCS_Offload, MiCS_Optimizer, create_mics_comm_groups)
+from .handles import (AllGatherCoalescedHandle, AllGatherHandle, AllReduceCoalescedHandle, InflightParamRegistry,  # noqa: F401,E402
+                      MultipleAllGatherHandles, NoGatherCoalescedHandle, NoGatherHandle, QuantizationInfo,
+                      ZeROOrderedDict, ZeRoTraceMode)
+from .coordinator import UnitCoordinator  # noqa: F401,E402
+
+PartitionedParameterCoordinator = UnitCoordinator  # the reference's name for the fetch / release scheduler
 from .tiling import TiledLinear, TiledLinearReturnBias  # noqa: F401,E402
 from .param_status import (DeepSpeedTensorOverride, DeepSpeedZeRoOffload, ZeroParamStatus, ZeroParamType,  # noqa: F401,E402
                            unwrap_model_for_generation)

@@ -252,3 +252,59 @@ def test_reference_zero_class_names():
                                dtype=torch.float32)
     assert isinstance(z, ZeroShardedOptimizer) and z.stage == 2
     assert issubclass(MiCS_Optimizer, DeepSpeedZeroOptimizer_Stage3)
+
+
+def test_gather_handles_and_registry():
+    from deepspeed_b200.runtime.zero import (AllGatherCoalescedHandle, AllGatherHandle, InflightParamRegistry,
+                                             MultipleAllGatherHandles, NoGatherCoalescedHandle, NoGatherHandle,
+                                             PartitionedParameterCoordinator, ZeroParamStatus, ZeRoTraceMode,
+                                             ZeROOrderedDict)
+
+    class W:
+        waited = 0
+
+        def wait(self):
+            W.waited += 1
+
+    def param(numel=6, per=3):
+        p = torch.nn.Parameter(torch.empty(0))
+        p.ds_status, p.ds_numel, p.ds_shape, p.ds_id = ZeroParamStatus.INFLIGHT, numel, (2, 3), 0
+        p.ds_tensor = torch.empty(per)
+        p.ds_tensor.ds_numel = per
+        return p
+
+    p = param()
+    AllGatherHandle(W(), p).wait()
+    assert p.ds_status == ZeroParamStatus.AVAILABLE and W.waited == 1
+    with pytest.raises(RuntimeError):
+        AllGatherHandle(W(), p)  # not inflight any more
+    a, b = param(), param(4, 2)
+    b.ds_shape = (4, )
+    parts = [torch.tensor([0., 1, 2, 10, 11]), torch.tensor([3., 4, 5, 12, 13])]  # rank-major partitions of a then b
+    h = AllGatherCoalescedHandle(W(), [a, b], parts, 2)
+    MultipleAllGatherHandles([h]).wait()
+    assert a.data.tolist() == [[0, 1, 2], [3, 4, 5]] and b.data.tolist() == [10, 11, 12, 13] and h.complete
+    c = param()
+    NoGatherHandle(c).wait()
+    d = param()
+    NoGatherCoalescedHandle([d]).wait()
+    assert c.ds_status == d.ds_status == ZeroParamStatus.AVAILABLE
+    reg = InflightParamRegistry()
+    e = param()
+    reg[e] = h
+    with pytest.raises(RuntimeError):
+        reg[e] = h
+    with pytest.raises(RuntimeError):
+        reg[c] = h  # available, not inflight
+    assert ZeRoTraceMode.RECORD.value == 1 and PartitionedParameterCoordinator.__name__ == "UnitCoordinator"
+    mod = torch.nn.Linear(2, 2)
+    od = ZeROOrderedDict(mod, mod._parameters)
+    gathered = []
+    w = od["weight"]
+    w.ds_status = ZeroParamStatus.NOT_AVAILABLE
+    w.all_gather = lambda: gathered.append(1)
+    od["weight"]
+    assert not gathered  # outside forward nothing is fetched
+    od._in_forward = True
+    od["weight"]
+    assert gathered == [1]
