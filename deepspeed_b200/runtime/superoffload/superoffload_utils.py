@@ -77,3 +77,23 @@ class SuperOffloadCPUOptimizer:
 
     def close(self):
         self.tasks.put(None)
+
+
+class TaskKeys:
+    """Field names of a work item handed to the CPU optimizer worker (reference ``superoffload_utils.py:19``)."""
+    PARAM_DATA = "param_data"
+    PARAM_GRAD = "param_grad"
+    PARAM_GROUP_ID = "param_group_id"
+    SUB_GROUP_ID = "sub_group_id"
+    ROLLBACK = "rollback"
+    LR = "lr"
+
+
+class ResultKeys:
+    UPDATED_PARAM = "updated_param"
+    EVENT_TYPE = "event_type"
+
+
+class EventTypes:
+    ADAM_STEP = "adam_step"
+    ROLLBACK = "rollback"

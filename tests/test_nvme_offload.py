@@ -114,3 +114,42 @@ def test_param_swapper_and_async_swapper(tmp_path):
         back = torch.empty(1536)
         h.sync_pread(back, path)
         assert torch.equal(back[:1500], t)
+
+
+def test_nvme_benchmark_engines(tmp_path):
+    """The DeepNVMe benchmark engines (reference deepspeed/nvme/*_engine.py, ds_aio_job.py, perf_run_sweep.py)."""
+    import sys
+    from types import SimpleNamespace
+    from deepspeed_b200.nvme.engines import (AIOBasic_Engine, AIOHandle_Engine, Job, SweepConfig, Torch_FastIO_Engine,
+                                             TorchIO_Engine, run, run_job)
+    args = SimpleNamespace(folder=str(tmp_path), io_size=1 << 20, block_size=1 << 18, queue_depth=4,
+                           intra_op_parallelism=2, loops=2, warmup_loops=1, keep_files=True)
+    for cls in (AIOBasic_Engine, AIOHandle_Engine, TorchIO_Engine):
+        w = run(cls, args, read_op=False)
+        r = run(cls, args, read_op=True)
+        assert w["op"] == "write" and r["op"] == "read" and w["num_bytes"] == 1 << 20
+        assert r["gbps_best"] > 0 and w["loops"] == 2 and r["engine"] == cls.__name__
+    w = run(Torch_FastIO_Engine, args, read_op=False)
+    assert w["gbps_best"] > 0
+    import torch
+    f = [p for p in tmp_path.iterdir() if "write" in p.name][0]
+    # what the handle engine wrote is what it reads back
+    eng = AIOHandle_Engine(args, 7, read_op=False)
+    eng.ctxt["buffer"].copy_(torch.arange(1 << 20, dtype=torch.int64).to(torch.uint8))
+    eng.write()
+    path = eng.ctxt["file"]
+    want = eng.ctxt["buffer"].clone()
+    eng.fini()
+    back = AIOBasic_Engine(SimpleNamespace(**{**vars(args)}), 7, read_op=False)
+    back.ctxt["file"] = path
+    back.read()
+    assert torch.equal(back.ctxt["buffer"], want)
+    out = tmp_path / "job.log"
+    run_job(Job([sys.executable, "-c", "\"print('hello from job')\""], str(out)))
+    assert "hello from job" in out.read_text()
+    import pytest
+    with pytest.raises(AssertionError):
+        run_job(Job([sys.executable, "-c", "\"raise SystemExit(3)\""], str(out)))
+    sc = SweepConfig(SimpleNamespace(nvme_dir=[str(tmp_path)], sweep_config={"block_size": ["128K", "1M"],
+                                                                             "queue_depth": [4, 8]}, loops=2))
+    assert len(sc.combinations()) == 4 and sc.read and sc.write and "--loops 2" in sc.other_options

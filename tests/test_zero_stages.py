@@ -308,3 +308,28 @@ def test_gather_handles_and_registry():
     od._in_forward = True
     od["weight"]
     assert gathered == [1]
+
+
+def test_zenflow_and_superoffload_class_fronts():
+    from deepspeed_b200.ops.adam.multi_tensor_apply import MultiTensorApply
+    from deepspeed_b200.runtime.superoffload.superoffload_stage3 import SuperOffloadOptimizer_Stage3
+    from deepspeed_b200.runtime.superoffload.superoffload_utils import EventTypes, ResultKeys, TaskKeys
+    from deepspeed_b200.runtime.zenflow.zenflow_stage_1_and_2 import (ZenFlowZeroOptimizer,
+                                                                      ZenFlowZeroOptimizerParallel,
+                                                                      ZenFlowZeroOptimizerSequential)
+
+    class Z:
+        overlap_step = True
+
+    assert ZenFlowZeroOptimizer.create(Z()) is ZenFlowZeroOptimizerParallel
+    Z.overlap_step = False
+    assert ZenFlowZeroOptimizer.create(Z()) is ZenFlowZeroOptimizerSequential
+    m = torch.nn.Linear(4, 4)
+    with pytest.raises(AssertionError):
+        ZenFlowZeroOptimizer(m, None, zenflow=None, offload_optimizer=None)
+    with pytest.raises(AssertionError):
+        SuperOffloadOptimizer_Stage3(m, None, offload_optimizer=None)
+    assert (TaskKeys.PARAM_GRAD, ResultKeys.UPDATED_PARAM, EventTypes.ROLLBACK) == ("param_grad", "updated_param",
+                                                                                     "rollback")
+    got = MultiTensorApply(2048)(lambda chunk, flag, lists, lr: (chunk, len(lists), lr), None, [[1], [2]], 0.1)
+    assert got == (2048, 2, 0.1)
