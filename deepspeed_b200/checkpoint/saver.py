@@ -356,8 +356,11 @@ def save_engine_checkpoint(engine, save_dir, tag=None, client_state=None, save_l
             _copy_recovery_script(os.path.join(save_dir, tag))
 
     if ce.is_decoupled():
+        # every rank's writer process confirms its own files; only rank 0's also moves the ``latest`` marker
         if engine.global_rank == 0:
             ce.commit(info)
+        else:
+            ce.commit(type(info)(info.tag, info.save_dir, False))
     else:
         dist.barrier()
         ce.commit(info)

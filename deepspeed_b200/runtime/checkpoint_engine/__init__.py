@@ -4,6 +4,7 @@ Interface follows reference ``runtime/checkpoint_engine/checkpoint_engine.py:21-
 (``create/save/load/commit/makedirs/is_data_parallel_writer/is_decoupled``); factory ``utils.py:15``.
 """
 import multiprocessing as mp
+from enum import Enum
 import os
 import queue as _q
 
@@ -128,34 +129,102 @@ class FastCheckpointEngine(CheckpointEngine):
         return self.dp_writer_config is not None
 
 
-def _writer_main(q, done):
+class DecoupledEvent(Enum):
+    SAVE_EVENT = 1
+    COMMIT_EVENT = 2
+    EXIT_EVENT = 3
+
+
+class CheckpointSize:
+    """Bytes a checkpoint added to its directory (sizes before / after), in GiB."""
+
+    def __init__(self):
+        self._pre = self._post = self._gigabytes = None
+
+    def gb_size(self):
+        return self._gigabytes
+
+    def set_pre_size(self, size):
+        self._pre = size
+
+    def set_post_size(self, size):
+        self._post = size
+        self._gigabytes = (self._post - self._pre) / (1024**3)
+
+
+def _dir_bytes(path):
+    total = 0
+    for root, _, files in os.walk(path):
+        for f in files:
+            try:
+                total += os.path.getsize(os.path.join(root, f))
+            except OSError:
+                pass
+    return total
+
+
+class _WriterSection:  # picklable stand-in for the pydantic ``checkpoint`` section inside the writer process
+
+    def __init__(self, writer):
+        self.writer = writer
+
+
+def _writer_main(q, done, fast=None):
+    """Writer process. ``fast``: (writer section as a dict, data-parallel writer config, optimize_dp_state) - saves go
+    through :class:`FastCheckpointEngine` (pinned staging + native async writes, stripes shared with the other
+    data-parallel writers); without it plain ``torch.save``."""
+    engine = None
+    if fast is not None:
+        try:
+            engine = FastCheckpointEngine(_WriterSection(fast[0]), fast[1], fast[2])
+        except Exception as e:  # noqa: BLE001
+            print(f"[Decoupled] fast writer unavailable in the writer process ({e}); using torch.save", flush=True)
+    size = CheckpointSize()
     while True:
         item = q.get()
         if item is None:
             break
         kind, payload = item
-        if kind == "save":
-            sd, path = payload
-            torch.save(sd, path)
-        elif kind == "commit":
+        if kind in ("save", DecoupledEvent.SAVE_EVENT):
+            sd, path, replicated = (tuple(payload) + (True, ))[:3]
+            if size._pre is None:
+                size.set_pre_size(_dir_bytes(os.path.dirname(path)))
+            if engine is not None:
+                engine.save(sd, path, replicated=replicated)
+            else:
+                torch.save(sd, path)
+        elif kind in ("commit", DecoupledEvent.COMMIT_EVENT):
             save_dir, tag, save_latest = payload
             if save_latest:
                 with open(os.path.join(save_dir, "latest"), "w") as f:
                     f.write(tag)
+            size.set_post_size(_dir_bytes(os.path.join(save_dir, str(tag))))
+            size._pre = None
             done.put(tag)
 
 
 class DecoupledCheckpointEngine(CheckpointEngine):
     """Hands CPU copies of the state to a separate writer *process*; commit is confirmed at the next GAS
-    boundary (reference ``decoupled_checkpoint_engine.py``; engine.py:3452-3453)."""
+    boundary (reference ``decoupled_checkpoint_engine.py``; engine.py:3452-3453). With a ``fast`` writer section the
+    process writes through :class:`FastCheckpointEngine`, including the data-parallel shared write."""
+    supports_shared_write = True
 
-    def __init__(self, config_params=None):
+    def __init__(self, config_params=None, dp_writer_config="rank0", optimize_dp_state=True):
         super().__init__(config_params)
+        self.dp_writer_config = dp_writer_config
+        w = getattr(config_params, "writer", None)
+        wd = w.model_dump() if hasattr(w, "model_dump") else dict(w or {})
+        fast = (wd, dp_writer_config, optimize_dp_state) if str(wd.get("type", "")).lower() == "fast" else None
         ctx = mp.get_context("spawn")
         self.q, self.done = ctx.Queue(), ctx.Queue()
-        self.proc = ctx.Process(target=_writer_main, args=(self.q, self.done), daemon=True)
+        self.proc = ctx.Process(target=_writer_main, args=(self.q, self.done, fast), daemon=True)
         self.proc.start()
         self.pending = []
+
+    def is_data_parallel_writer(self, dp_rank):
+        if self.dp_writer_config == "rank0":
+            return dp_rank == 0
+        return self.dp_writer_config is not None
 
     def is_decoupled(self):
         return True
@@ -174,9 +243,9 @@ class DecoupledCheckpointEngine(CheckpointEngine):
             return type(obj)(DecoupledCheckpointEngine._to_cpu(v) for v in obj)
         return obj
 
-    def save(self, state_dict, path):
+    def save(self, state_dict, path, replicated=True):
         self._alive()
-        self.q.put(("save", (self._to_cpu(state_dict), path)))
+        self.q.put(("save", (self._to_cpu(state_dict), path, replicated)))
 
     def commit(self, info):
         self._alive()
@@ -332,5 +401,12 @@ def create_checkpoint_engine(config, zero_stage=0, has_moe_layers=False):
             logger.warning(f"FastCheckpointEngine unavailable ({e}); falling back to torch")
             return TorchCheckpointEngine(ck)
     if kind == "decoupled":
-        return DecoupledCheckpointEngine(ck)
+        dp_cfg = "rank0"
+        unit = getattr(w, "data_parallel", None)
+        from ... import comm as _dist
+        if unit and _dist.is_initialized() and (getattr(w, "type", "") or "").lower() == "fast":
+            from ...utils import groups as _groups
+            from ..model_checkpointing import create_data_parallel_writer_config
+            dp_cfg = create_data_parallel_writer_config(_groups, str(unit).upper(), zero_stage, has_moe_layers)
+        return DecoupledCheckpointEngine(ck, dp_cfg, optimize_dp_state=int(zero_stage) != 3)
     return TorchCheckpointEngine(ck)

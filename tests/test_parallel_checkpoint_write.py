@@ -155,3 +155,50 @@ def test_engine_shares_model_state_write_between_replicas(tmp_path, zero_stage):
     out = run_distributed(_engine_shared_write, 2, args=(str(tmp_path), zero_stage))
     if zero_stage == 1:
         assert sum("optim_states" in f for f in out[0]) == 2  # per-rank shards stay whole files
+
+
+def _engine_decoupled(tmp, fast):
+    """Decoupled writer process (plain and through the fast writer with a shared data-parallel write): training goes
+    on while the files are written, the checkpoint is committed at a later step and loads back."""
+    import deepspeed_b200 as ds
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(32, 64), torch.nn.ReLU(), torch.nn.Linear(64, 32))
+    writer = {"type": "fast", "decoupled": True, "data_parallel": "replica", "io_buffer_size": 65536} if fast else \
+        {"type": "python", "decoupled": True}
+    cfg = {"train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}},
+           "zero_optimization": {"stage": 1}, "checkpoint": {"writer": writer}}
+    engine, *_ = ds.initialize(model=model, config=cfg)
+    assert engine.checkpoint_engine.is_decoupled()
+    x = torch.randn(2, 32, device=engine.device)
+    engine.backward(engine(x).square().mean())
+    engine.step()
+    want = {k: v.clone() for k, v in engine.module.state_dict().items()}
+    engine.save_checkpoint(tmp, tag="d")
+    engine.backward(engine(x).square().mean())
+    engine.step()  # the commit is confirmed at a step boundary
+    engine.checkpoint_engine.commit_pending(block=True)
+    ds.comm.barrier()
+    files = sorted(os.listdir(os.path.join(tmp, "d")))
+    if fast:
+        assert "mp_rank_00_model_states.pt-0.2" in files and "mp_rank_00_model_states.pt-1.2" in files, files
+    else:
+        assert "mp_rank_00_model_states.pt" in files, files
+    assert open(os.path.join(tmp, "latest")).read() == "d"
+    engine.load_checkpoint(tmp, tag="d")
+    for k, v in engine.module.state_dict().items():
+        torch.testing.assert_close(v, want[k])
+    engine.destroy()
+    return True
+
+
+@pytest.mark.parametrize("fast", [False, True])
+def test_decoupled_writer_process(tmp_path, fast):
+    assert all(run_distributed(_engine_decoupled, 2, args=(str(tmp_path), fast)))
+
+
+def test_checkpoint_size_and_events():
+    from deepspeed_b200.runtime.checkpoint_engine import CheckpointSize, DecoupledEvent
+    s = CheckpointSize()
+    s.set_pre_size(1 << 30)
+    s.set_post_size(3 << 30)
+    assert s.gb_size() == 2.0 and DecoupledEvent.COMMIT_EVENT.value == 2
