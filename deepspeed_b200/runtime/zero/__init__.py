@@ -25,6 +25,10 @@ from .handles import (AllGatherCoalescedHandle, AllGatherHandle, AllReduceCoales
 from .coordinator import UnitCoordinator  # noqa: F401,E402
 
 PartitionedParameterCoordinator = UnitCoordinator  # the reference's name for the fetch / release scheduler
+from .mem_estimate import (estimate_zero2_model_states_mem_needs, estimate_zero2_model_states_mem_needs_all_cold,  # noqa: F401,E402
+                           estimate_zero2_model_states_mem_needs_all_live, estimate_zero3_model_states_mem_needs,
+                           estimate_zero3_model_states_mem_needs_all_cold,
+                           estimate_zero3_model_states_mem_needs_all_live)
 from .tiling import TiledLinear, TiledLinearReturnBias  # noqa: F401,E402
 from .param_status import (DeepSpeedTensorOverride, DeepSpeedZeRoOffload, ZeroParamStatus, ZeroParamType,  # noqa: F401,E402
                            unwrap_model_for_generation)

@@ -1518,4 +1518,7 @@ def __getattr__(name):  # the reference's class names for this optimizer live in
     if name in ("DeepSpeedZeroOptimizer", "DeepSpeedZeroOptimizer_Stage3", "MiCS_Optimizer"):
         from . import mics
         return getattr(mics, name)
+    if name.startswith("estimate_zero") or name == "model_to_params":
+        from . import mem_estimate
+        return getattr(mem_estimate, name)
     raise AttributeError(f"module {__name__!r} has no attribute {name!r}")

@@ -333,3 +333,32 @@ def test_zenflow_and_superoffload_class_fronts():
                                                                                      "rollback")
     got = MultiTensorApply(2048)(lambda chunk, flag, lists, lr: (chunk, len(lists), lr), None, [[1], [2]], 0.1)
     assert got == (2048, 2, 0.1)
+
+
+def test_memory_estimators(capsys):
+    """Values of the reference's documented examples (docs/code-docs/source/memory.rst)."""
+    from deepspeed_b200.runtime.zero import (estimate_zero2_model_states_mem_needs,
+                                             estimate_zero2_model_states_mem_needs_all_live,
+                                             estimate_zero3_model_states_mem_needs,
+                                             estimate_zero3_model_states_mem_needs_all_cold)
+    P = 2_851_000_000
+    cpu, gpu = estimate_zero2_model_states_mem_needs(P, 8, 1, cpu_offload=True)
+    assert gpu == 2 * P and cpu == int(P * 32 * 1.5)
+    cpu, gpu = estimate_zero2_model_states_mem_needs(P, 8, 1, cpu_offload=False)
+    assert gpu == 2 * P + int(18 * P / 8) and cpu == int(P * 4 * 8 * 1.5)
+    L = 32_000_000
+    cpu, gpu, big = estimate_zero3_model_states_mem_needs(P, L, 8, 1, True, True, True)
+    assert (gpu, big) == (4 * L, 4 * L) and cpu == int(P * 18 * 1.5)
+    cpu, gpu, _ = estimate_zero3_model_states_mem_needs(P, L, 8, 2, True, False, False)
+    assert gpu == 4 * L + int(2 * P / 16) and cpu == int(P * max(32, 8.0) * 1.5)
+    cpu, gpu, _ = estimate_zero3_model_states_mem_needs(P, L, 8, 1, False, False, True)
+    assert gpu == 4 * L + int(18 * P / 8) and cpu == int(L * 32 * 1.5)
+    rows = estimate_zero3_model_states_mem_needs_all_cold(P, L, 8, 1)
+    assert len(rows) == 6 and "offload_param=cpu , offload_optimizer=cpu , zero_init=1" in rows[0][2]
+    m = torch.nn.Sequential(torch.nn.Linear(10, 10), torch.nn.Linear(10, 10))
+    m[1].weight = m[0].weight  # shared: counted once
+    rows = estimate_zero2_model_states_mem_needs_all_live(m, 1, 1)
+    assert rows[0][1] == 2 * 120
+    out = capsys.readouterr().out
+    assert "per CPU  |  per GPU" in out and "2851M total params, 32M largest layer params" in out
+    from deepspeed_b200.runtime.zero.sharded_optimizer import estimate_zero3_model_states_mem_needs_all_live  # noqa: F401
