@@ -40,6 +40,7 @@ class MoE(nn.Module):
                                                min_capacity, noisy_gate_policy, drop_tokens, use_rts, None,
                                                top2_2nd_expert_sampling), experts, self.expert_group_name,
                                       self.ep_size, self.num_local_experts, use_tutel=use_tutel)
+        self.deepspeed_moe.enable_expert_tensor_parallelism = enable_expert_tensor_parallelism
         if self.use_residual:
             import copy
             self.mlp = copy.deepcopy(expert)

@@ -255,6 +255,18 @@ class MOELayer(nn.Module):
         rows_v, src_v = rows[vflat], src_tok[vflat]
         dispatched = torch.zeros(E * capacity, d_model, dtype=tokens.dtype, device=tokens.device)
         dispatched.index_copy_(0, rows_v, tokens.index_select(0, src_v))
+        # tensor-parallel ranks hold the same tokens: unless the experts are tensor-parallel themselves, each rank
+        # sends only its 1/tp slice of every expert's capacity through the all-to-all (reference sharded_moe.py:586)
+        full_capacity = capacity
+        tp_sliced = not getattr(self, "enable_expert_tensor_parallelism", False)
+        if tp_sliced:
+            from .mappings import drop_tokens as _drop, gather_tokens as _gather, _tp
+            tp_world = _tp()[0]
+            tp_sliced = tp_world > 1 and capacity % tp_world == 0
+        if tp_sliced:
+            dispatched = _drop(dispatched.view(E, capacity, d_model), dim=1)
+            capacity = capacity // tp_world
+            dispatched = dispatched.reshape(E * capacity, d_model)
         if self.ep_size > 1:
             dispatched = _AllToAll.apply(self.ep_group, dispatched)
         # [ep, E_local, C, M] -> [E_local, ep*C, M]
@@ -265,6 +277,9 @@ class MOELayer(nn.Module):
         expert_out = expert_out.reshape(E * capacity, d_model)
         if self.ep_size > 1:
             expert_out = _AllToAll.apply(self.ep_group, expert_out)
+        if tp_sliced:
+            expert_out = _gather(expert_out.view(E, capacity, d_model), dim=1).reshape(E * full_capacity, d_model)
+            capacity = full_capacity
         # ---- combine: out[s] = sum_j w[s,j] * expert_out[row(s,j)]
         picked = expert_out.index_select(0, rows_v) * gate_w.reshape(-1)[vflat].unsqueeze(1).to(expert_out.dtype)
         out = torch.zeros(S, d_model, dtype=expert_out.dtype, device=x.device)

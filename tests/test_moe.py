@@ -174,3 +174,49 @@ def _fused_plan_roundtrip(top_k, n_experts):
 def test_fused_moe_plan_index_math(top_k, n_experts):
     world = 3 if n_experts % 3 == 0 else 2
     assert all(run_distributed(_fused_plan_roundtrip, world, args=(top_k, n_experts)))
+
+
+def _moe_tp_drop():
+    """tp=2 (one replica): both ranks hold the same tokens; the DS-MoE layer sends half of every expert's capacity
+    through the experts on each rank and gathers the halves - the result and the gradients equal the tp=1 layer."""
+    import deepspeed_b200 as ds
+    from deepspeed_b200.moe import MoE
+    from deepspeed_b200.moe.mappings import drop_tokens, gather_tokens
+    from deepspeed_b200.utils import groups
+    torch.manual_seed(0)
+    expert = torch.nn.Sequential(torch.nn.Linear(16, 32), torch.nn.GELU(), torch.nn.Linear(32, 16))
+    moe = MoE(16, expert, num_experts=2, ep_size=1, k=1, capacity_factor=2.0, min_capacity=8, use_rts=False)
+    x = torch.randn(2, 8, 16)
+    moe.deepspeed_moe._set_ep_group(None)
+    xr = x.clone().requires_grad_(True)
+    want, _, _ = moe(xr)
+    want.square().sum().backward()
+    gw = [p.grad.clone() for p in moe.parameters()]
+    gx = xr.grad.clone()
+    for p in moe.parameters():
+        p.grad = None
+    groups.initialize(tp_size=2, force=True)
+    assert groups._get_model_parallel_world_size() == 2
+    t = torch.arange(8.0).view(1, 8, 1).requires_grad_(True)
+    half = drop_tokens(t, dim=1)
+    assert half.shape == (1, 4, 1) and float(half[0, 0, 0]) == 4.0 * ds.comm.get_rank()
+    back = gather_tokens(half, dim=1)
+    assert torch.equal(back, t)
+    back.sum().backward()
+    assert torch.equal(t.grad, torch.ones_like(t))
+    xt = x.clone().requires_grad_(True)
+    got, _, _ = moe(xt)
+    got.square().sum().backward()
+    torch.testing.assert_close(got, want, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(xt.grad, gx, rtol=1e-5, atol=1e-6)
+    # expert weights saw half of the tokens on each rank: the halves add up to the tp=1 gradient
+    for p, g in zip(moe.parameters(), gw):
+        if "experts" in [n for n, q in moe.named_parameters() if q is p][0]:
+            tot = p.grad.clone()
+            ds.comm.all_reduce(tot)
+            torch.testing.assert_close(tot, g, rtol=1e-4, atol=1e-6)
+    return True
+
+
+def test_ds_moe_drops_duplicate_tokens_across_tensor_parallel_ranks():
+    assert all(run_distributed(_moe_tp_drop, 2))
