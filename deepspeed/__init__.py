@@ -54,6 +54,10 @@ _ALIASES = {
     "deepspeed.comm.backend": "deepspeed_b200.comm.backend",
     "deepspeed.comm.torch": "deepspeed_b200.comm.backend",
     "deepspeed.comm.config": "deepspeed_b200.comm.config",
+    "deepspeed.module_inject.fusedqkv_utils": "deepspeed_b200.parallel.fusedqkv_utils",
+    "deepspeed.module_inject.tp_shard": "deepspeed_b200.parallel.fusedqkv_utils",
+    "deepspeed.module_inject.auto_tp_model_utils": "deepspeed_b200.parallel.auto_tp_model_utils",
+    "deepspeed.moe.mappings": "deepspeed_b200.moe.mappings",
     "deepspeed.module_inject.tp_plan_converter": "deepspeed_b200.parallel.tp_plan_converter",
     "deepspeed.runtime.tensor_parallel": "deepspeed_b200.runtime.tensor_parallel",
     "deepspeed.runtime.tensor_parallel.tp_manager": "deepspeed_b200.runtime.tensor_parallel.tp_manager",

@@ -152,17 +152,24 @@ def shard_tensor(w, dim, group, sub_params: Optional[List[int]] = None, grain=1)
 class LinearLayer(nn.Module):
     """Column-parallel linear: weight ``[out/tp, in]``. Input replicated (or sequence-sharded with ``mode='rs_ag'``)."""
 
-    def __init__(self, module: nn.Linear, mp_group, sub_params=None, gather_output=False, mode="allreduce", grain=1):
+    def __init__(self, module: nn.Linear, mp_group, sub_params=None, gather_output=False, mode="allreduce", grain=1,
+                 row_index=None):
         super().__init__()
         self.mp_group, self.gather_output, self.mode = mp_group, gather_output, mode
         self.tp_world, self.tp_rank = _ws(mp_group), _rk(mp_group)
         self.sub_params = sub_params
-        w = shard_tensor(module.weight.data, 0, mp_group, sub_params, grain)
+        self.row_index = row_index  # explicit rows of the full weight (fused-QKV layouts, parallel/fusedqkv_utils.py)
+        if row_index is not None and self.tp_world > 1:
+            idx = row_index.to(module.weight.device)
+            w = module.weight.data.index_select(0, idx).contiguous()
+            b = module.bias.data.index_select(0, idx).contiguous() if module.bias is not None else None
+        else:
+            w = shard_tensor(module.weight.data, 0, mp_group, sub_params, grain)
+            b = shard_tensor(module.bias.data, 0, mp_group, sub_params, grain) if module.bias is not None else None
         self.weight = nn.Parameter(w, requires_grad=module.weight.requires_grad)
         self.bias = None
-        if module.bias is not None:
-            self.bias = nn.Parameter(shard_tensor(module.bias.data, 0, mp_group, sub_params, grain),
-                                     requires_grad=module.bias.requires_grad)
+        if b is not None:
+            self.bias = nn.Parameter(b, requires_grad=module.bias.requires_grad)
         for p in self.parameters():
             p.tensor_model_parallel = True
             p.ds_tp_sharded = True
@@ -350,18 +357,60 @@ class AutoTP:
             elif spec is not None:
                 sub = spec.sub_param_sizes_for(module.weight.shape[0])
                 grain = 1
-                if sub is None:
+                rows = self._fused_qkv_rows(name, module, world) if sub is None else None
+                if sub is None and rows is None:
                     sub, grain = _fused_sub_params(name, module, self.model)
                 new = LinearLayer(module, self.mp_group, sub_params=sub, gather_output=spec.gather_output,
-                                  mode=self.mode, grain=grain)
+                                  mode=self.mode, grain=grain, row_index=rows)
             else:
-                sub, grain = _fused_sub_params(name, module, self.model)
-                new = LinearLayer(module, self.mp_group, sub_params=sub, mode=self.mode, grain=grain)
+                rows = self._fused_qkv_rows(name, module, world)
+                if rows is not None:
+                    new = LinearLayer(module, self.mp_group, mode=self.mode, row_index=rows)
+                else:
+                    sub, grain = _fused_sub_params(name, module, self.model)
+                    new = LinearLayer(module, self.mp_group, sub_params=sub, mode=self.mode, grain=grain)
             setattr(parent, attr, new)
             self.replaced[name] = kind
         self._fix_head_counts(world)
+        cfg = getattr(self.model, "config", None)
+        nh = getattr(cfg, "num_attention_heads", None) or getattr(cfg, "n_head", None) or getattr(cfg, "n_heads", None)
+        if nh and self.replaced:
+            from .auto_tp_model_utils import install_alibi_head_sharding
+            install_alibi_head_sharding(self.model, self.mp_group, nh)
         log_dist(f"AutoTP: replaced {len(self.replaced)} linear layers (tp={world}, mode={self.mode})", [0])
         return self.model
+
+    def _fused_qkv_rows(self, name, module, world):
+        """Row index for a fused QKV projection whose enclosing block belongs to a known layout family (Bloom / Falcon /
+        NeoX interleaved heads, CodeGen blocks, BigCode multi-query, Phi-3 / ChatGLM grouped KV); ``None`` for the
+        plain ``[q; k; v]`` layout handled by sub-parameter sharding."""
+        from . import fusedqkv_utils as Fq
+        if not Fq.require_tp_fused_qkvw(name, world):
+            return None
+        parts, node, ftype = name.split("."), self.model, None
+        for p in parts[:-1]:
+            node = getattr(node, p)
+            t = Fq.FUSED_QKV_TYPE_DICT.get(type(node).__name__)
+            if t is None:
+                hits = [k for k in Fq.FUSED_QKV_TYPE_DICT if k in type(node).__name__]
+                t = Fq.FUSED_QKV_TYPE_DICT[max(hits, key=len)] if hits else None
+            ftype = t or ftype
+        if ftype in (None, "qwentype"):
+            return None
+        cfg = getattr(self.model, "config", None) or getattr(self.model, "cfg", None)
+        nh = getattr(cfg, "num_attention_heads", None) or getattr(cfg, "n_head", None)
+        nkv = getattr(cfg, "num_key_value_heads", None) or getattr(cfg, "multi_query_group_num", None) or \
+            getattr(cfg, "num_kv_heads", None) or (1 if getattr(cfg, "multi_query", False) and
+                                                   ftype == "bigcodetype" else nh)
+        if ftype == "bloomtype" and getattr(cfg, "new_decoder_architecture", None) is False and \
+                getattr(cfg, "multi_query", False):
+            return None  # Falcon-7B style multi-query fused layout: not head-interleaved
+        n_embd = getattr(cfg, "hidden_size", None) or getattr(cfg, "n_embd", None)
+        if ftype == "glmtype" and nkv != 2:
+            return None  # plain [q; k; v]: the sub-parameter path shards it (also with grouped KV heads)
+        Fq.set_num_attention_heads(nh), Fq.set_num_kv_heads(nkv), Fq.set_n_embd(n_embd)
+        return Fq.fused_qkv_row_index(ftype, module.weight.shape[0], world, _rk(self.mp_group),
+                                      hidden_cols=module.weight.shape[1])
 
     def _parent(self, name):
         parts = name.split(".")
@@ -372,13 +421,27 @@ class AutoTP:
 
     def _fix_head_counts(self, world):
         """Attention modules keep per-rank head counts in attributes; divide them."""
+        heads = ("nh", "nkv", "num_heads", "num_key_value_heads", "num_attention_heads", "n_head", "n_heads",
+                 "num_kv_heads", "kv_n_heads", "num_attn_heads", "num_kv")
+        # widths an attention module derives its reshapes / splits from (reference auto_tp.py ``update_mp_params``)
+        widths = ("embed_dim", "all_head_size", "inner_dim", "split_size", "hidden_size", "d_model",
+                  "hidden_size_per_partition")
         for m in self.model.modules():
-            for attr in ("nh", "nkv", "num_heads", "num_key_value_heads", "num_attention_heads", "n_head"):
-                if hasattr(m, attr) and isinstance(getattr(m, attr), int) and not isinstance(m, type(self.model)):
-                    if any(isinstance(c, (LinearLayer, LinearAllreduce)) for c in m.children()):
-                        v = getattr(m, attr)
-                        if v % world == 0:
-                            setattr(m, attr, v // world)
+            if isinstance(m, type(self.model)) or \
+                    not any(isinstance(c, (LinearLayer, LinearAllreduce)) for c in m.children()):
+                continue
+            is_attention = False
+            for attr in heads:
+                v = getattr(m, attr, None)
+                if isinstance(v, int) and not isinstance(v, bool):
+                    is_attention = True
+                    if v % world == 0:
+                        setattr(m, attr, v // world)
+            if is_attention:
+                for attr in widths:
+                    v = getattr(m, attr, None)
+                    if isinstance(v, int) and not isinstance(v, bool) and v % world == 0 and attr in vars(m):
+                        setattr(m, attr, v // world)
 
 
 def apply_autotp(model, tp_config, mp_group):

@@ -174,3 +174,110 @@ def _hf_plan():
 
 def test_hf_tp_plan_through_training_manager():
     assert all(run_distributed(_hf_plan, 2))
+
+
+def test_fused_qkv_layouts_give_every_rank_whole_matching_heads():
+    """Rows are labelled (kind, head); each layout's shard must hold, for every head it owns, all of that head's q,
+    k and v rows (reference module_inject/fusedqkv_utils.py)."""
+    from deepspeed_b200.parallel import fusedqkv_utils as Fq
+    nh, hd, world = 8, 4, 2
+    H = nh * hd
+
+    def label(kinds_heads):  # list of (kind, head) per row block of hd rows
+        return [(k, h) for k, h in kinds_heads for _ in range(hd)]
+
+    def check(rows_by_rank, labels, replicated_kinds=()):
+        seen = []
+        for rows in rows_by_rank:
+            got = [labels[i] for i in rows.tolist()]
+            heads = {h for k, h in got if k == "q"}
+            for kind in "kv":
+                if kind in replicated_kinds:
+                    continue
+                assert {h for k, h in got if k == kind} == heads, (kind, heads)
+            seen += [g for g in got if g[0] not in replicated_kinds]
+        assert sorted(seen) == sorted(l for l in labels if l[0] not in replicated_kinds)  # a partition of the rows
+
+    Fq.set_num_kv_heads(nh), Fq.set_num_attention_heads(nh), Fq.set_n_embd(H)
+    bloom = label([(k, h) for h in range(nh) for k in "qkv"])
+    check([Fq.fused_qkv_row_index("bloomtype", 3 * H, world, r) for r in range(world)], bloom)
+    glm = label([(k, h) for k in "qkv" for h in range(nh)])
+    check([Fq.fused_qkv_row_index("glmtype", 3 * H, world, r) for r in range(world)], glm)
+    # codegen: 4 blocks of [q, v, k] sub-blocks, heads 2*blk, 2*blk+1 in block blk
+    cg = label([(k, 2 * blk + i) for blk in range(4) for k in "qvk" for i in range(2)])
+    rows = [Fq.fused_qkv_row_index("codegentype", 3 * H, world, r) for r in range(world)]
+    check(rows, cg)
+    assert all(len(r) == 3 * H // world for r in rows)
+    # phi3: grouped KV heads (8 q heads, 2 kv heads): rank r owns q heads 4r..4r+3 and kv head r
+    Fq.set_num_kv_heads(2)
+    phi = label([("q", h) for h in range(nh)] + [("k", h) for h in range(2)] + [("v", h) for h in range(2)])
+    for r in range(world):
+        got = [phi[i] for i in Fq.fused_qkv_row_index("phi3type", H + 4 * hd, world, r, hidden_cols=H).tolist()]
+        assert {h for k, h in got if k == "q"} == set(range(4 * r, 4 * r + 4))
+        assert {h for k, h in got if k == "k"} == {r} == {h for k, h in got if k == "v"}
+    # chatglm2: two KV groups behind n_embd q rows
+    got = Fq.fused_qkv_row_index("glmtype", H + 4 * hd, world, 1)
+    assert got.tolist() == list(range(16, 32)) + list(range(36, 40)) + list(range(44, 48))
+    assert Fq.fused_qkv_subparam_sizes(torch.nn.Identity(), (H + 4 * hd, H)) == (H + 4 * hd, )
+    # bigcode: q sharded, the single kv head replicated
+    Fq.set_num_kv_heads(1)
+    mq = label([("q", h) for h in range(nh)] + [("k", 0), ("v", 0)])
+    rows = [Fq.fused_qkv_row_index("bigcodetype", H + 2 * hd, world, r) for r in range(world)]
+    check(rows, mq, replicated_kinds=("k", "v"))
+    assert all(r[-2 * hd:].tolist() == list(range(H, H + 2 * hd)) for r in rows)
+
+    class FalconDecoderLayer(torch.nn.Module):
+
+        def __init__(self):
+            super().__init__()
+            self.query_key_value = torch.nn.Linear(H, 3 * H)
+
+    blk = FalconDecoderLayer()
+    assert Fq.get_fused_qkv_type(blk) == "bloomtype" and Fq.get_fused_qkv_type(torch.nn.Linear(2, 2)) is None
+    assert Fq.require_tp_fused_qkvw("h.0.self_attention.query_key_value", 2) and not Fq.require_tp_fused_qkvw("q", 2)
+    Fq.set_num_kv_heads(nh)
+    w = torch.arange(3 * H).float().view(-1, 1).expand(3 * H, 2)
+    assert Fq.prepare_tp_fused_qkvw(blk, w, 2, 1)[:, 0].tolist() == list(range(48, 96))
+    Fq.set_num_kv_heads(3)
+    assert Fq.get_shard_size_list(96, 2, "self_attn.qkv") == [64, 32]  # 3 heads over 2 ranks: 2 + 1
+    assert Fq.get_shard_size_list(96, 2, "mlp.up_proj") == [48, 48]
+    parts = Fq.split_by_qkvlist_and_refuse([torch.arange(4), torch.arange(4) + 10, torch.arange(4) + 20], 2)
+    assert parts[1].tolist() == [2, 3, 12, 13, 22, 23]
+    for f, v in ((Fq.set_num_kv_heads, None), (Fq.set_num_attention_heads, None), (Fq.set_n_embd, None)):
+        f(v)
+
+
+def _hf_interleaved_qkv(family):
+    """HF models with head-interleaved / blocked fused QKV sharded over two ranks reproduce the unsharded logits."""
+    import transformers as T
+    import deepspeed_b200.comm as dist
+    from deepspeed_b200.parallel.tp import LinearLayer, apply_autotp
+    from deepspeed_b200.config.sections import TPTrainingConfig
+    from deepspeed_b200.utils import groups
+    torch.manual_seed(0)
+    if family == "gpt_neox":
+        m = T.GPTNeoXForCausalLM(T.GPTNeoXConfig(vocab_size=64, hidden_size=32, intermediate_size=64,
+                                                 num_hidden_layers=2, num_attention_heads=4,
+                                                 max_position_embeddings=32))
+    elif family == "bloom":
+        m = T.BloomForCausalLM(T.BloomConfig(vocab_size=64, hidden_size=32, n_layer=2, n_head=4))
+    else:
+        m = T.GPTBigCodeForCausalLM(T.GPTBigCodeConfig(vocab_size=64, n_embd=32, n_layer=2, n_head=4, n_positions=32,
+                                                       multi_query=True))
+    m.eval()
+    ids = torch.randint(0, 64, (2, 7))
+    with torch.no_grad():
+        want = m(ids).logits
+    groups.initialize(tp_size=2, force=True)
+    apply_autotp(m, TPTrainingConfig(autotp_size=2, dtype=torch.float32), groups._get_model_parallel_group())
+    qkv = [x for n, x in m.named_modules() if n.endswith(("query_key_value", "c_attn"))][0]
+    assert isinstance(qkv, LinearLayer) and qkv.row_index is not None
+    with torch.no_grad():
+        got = m(ids).logits
+    torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-4)
+    return True
+
+
+@pytest.mark.parametrize("family", ["gpt_neox", "bloom", "gpt_bigcode"])
+def test_autotp_shards_family_specific_fused_qkv(family):
+    assert all(run_distributed(_hf_interleaved_qkv, 2, args=(family, )))
