@@ -30,6 +30,7 @@ class TPLayerSpec:
     model_types: Optional[List[str]] = None
     gather_output: bool = False  # COLUMN: all-gather the output so every rank sees the full result
     grad_allreduce: bool = False  # SKIP: replicated parameter whose gradient is summed over the TP ranks
+    split_input: bool = False  # ROW: the input arrives whole (after a gathered column layer) and is sliced locally
 
     def __post_init__(self):
         if isinstance(self.partition_type, str):

@@ -249,10 +249,10 @@ class VocabParallelEmbedding(nn.Module):
 
 # names of linears whose OUTPUT is reduced (row-parallel) in common architectures (reference auto_tp.py policy lists)
 ROW_PARALLEL_PATTERNS = [r"\.o_proj$", r"\.out_proj$", r"\.down_proj$", r"\.dense_4h_to_h$", r"\.c_proj$", r"\.wo$",
-                         r"\.w2$", r"attention\.dense$", r"\.fc2$", r"\.c_proj2$", r"self_attention\.dense$"]
+                         r"\.w2$", r"attention\.dense$", r"\.fc2$", r"\.c_proj2$", r"self_attention\.dense$", r"\.fc_out$"]
 COLUMN_PARALLEL_PATTERNS = [r"\.q_proj$", r"\.k_proj$", r"\.v_proj$", r"\.qkv_proj$", r"\.gate_proj$", r"\.up_proj$",
                             r"\.gate_up_proj$", r"\.query_key_value$", r"\.dense_h_to_4h$", r"\.c_attn$", r"\.c_fc$",
-                            r"\.wq$", r"\.wk$", r"\.wv$", r"\.w1$", r"\.w3$", r"\.fc1$", r"\.Wqkv$"]
+                            r"\.wq$", r"\.wk$", r"\.wv$", r"\.w1$", r"\.w3$", r"\.fc1$", r"\.Wqkv$", r"\.fc_in$"]
 
 
 def _fused_sub_params(name, module, model):
@@ -328,6 +328,9 @@ class AutoTP:
         if world == 1:
             return self.model
         for name, module in list(self.model.named_modules()):
+            if type(module).__name__ == "Conv1D" and getattr(module.weight, "dim", lambda: 0)() == 2:
+                self._replace_conv1d(name, module)  # GPT-2 style ``x @ w`` projections (weight ``[in, out]``)
+                continue
             if not isinstance(module, nn.Linear):
                 continue
             spec = None
@@ -353,13 +356,20 @@ class AutoTP:
                 continue
             parent, attr = self._parent(name)
             if kind == "row":
-                new = LinearAllreduce(module, self.mp_group, mode=self.mode)
+                if spec is not None and getattr(spec, "split_input", False):
+                    new = LmHeadLinearAllreduce(module, self.mp_group, mode=self.mode)
+                else:
+                    new = LinearAllreduce(module, self.mp_group, mode=self.mode)
             elif spec is not None:
                 sub = spec.sub_param_sizes_for(module.weight.shape[0])
                 grain = 1
-                rows = self._fused_qkv_rows(name, module, world) if sub is None else None
-                if sub is None and rows is None:
-                    sub, grain = _fused_sub_params(name, module, self.model)
+                rows = None
+                if spec.gather_output:
+                    pass  # contiguous shards: the all-gather of the outputs restores the original column order
+                elif sub is None:
+                    rows = self._fused_qkv_rows(name, module, world)
+                    if rows is None:
+                        sub, grain = _fused_sub_params(name, module, self.model)
                 new = LinearLayer(module, self.mp_group, sub_params=sub, gather_output=spec.gather_output,
                                   mode=self.mode, grain=grain, row_index=rows)
             else:
@@ -379,6 +389,21 @@ class AutoTP:
             install_alibi_head_sharding(self.model, self.mp_group, nh)
         log_dist(f"AutoTP: replaced {len(self.replaced)} linear layers (tp={world}, mode={self.mode})", [0])
         return self.model
+
+    def _replace_conv1d(self, name, module):
+        from .layers import Conv_LinearALlreduce, conv_LinearLayer
+        kind = self._kind("." + name)
+        if kind is None:
+            return
+        parent, attr = self._parent(name)
+        if kind == "row":
+            new = Conv_LinearALlreduce(module, self.mp_group, mode=self.mode)
+        else:
+            out = module.weight.shape[1]
+            sub = [out // 3] * 3 if re.search(r"c_attn$", name) and out % 3 == 0 else None
+            new = conv_LinearLayer(module, self.mp_group, sub_params=sub, mode=self.mode)
+        setattr(parent, attr, new)
+        self.replaced[name] = kind
 
     def _fused_qkv_rows(self, name, module, world):
         """Row index for a fused QKV projection whose enclosing block belongs to a known layout family (Bloom / Falcon /
@@ -404,7 +429,7 @@ class AutoTP:
                                                    ftype == "bigcodetype" else nh)
         if ftype == "bloomtype" and getattr(cfg, "new_decoder_architecture", None) is False and \
                 getattr(cfg, "multi_query", False):
-            return None  # Falcon-7B style multi-query fused layout: not head-interleaved
+            ftype, nkv = "bigcodetype", 1  # Falcon-7B multi-query layout [q heads; k; v]: shard q, replicate k / v
         n_embd = getattr(cfg, "hidden_size", None) or getattr(cfg, "n_embd", None)
         if ftype == "glmtype" and nkv != 2:
             return None  # plain [q; k; v]: the sub-parameter path shards it (also with grouped KV heads)
@@ -430,6 +455,9 @@ class AutoTP:
             if isinstance(m, type(self.model)) or \
                     not any(isinstance(c, (LinearLayer, LinearAllreduce)) for c in m.children()):
                 continue
+            cols = [c for c in m.children() if isinstance(c, LinearLayer)]
+            if cols and all(c.gather_output for c in cols):
+                continue  # the projections' outputs are gathered: the module works on all heads
             is_attention = False
             for attr in heads:
                 v = getattr(m, attr, None)

@@ -2,14 +2,16 @@
 ``runtime/tensor_parallel/config.py::_get_hf_tp_plan``).
 
 A plan maps wildcard module paths to a style: ``colwise`` (output-sharded), ``colwise_rep`` /
-``colwise_gather_output`` (output-sharded, result all-gathered), ``rowwise`` (input-sharded, result all-reduced),
+``colwise_gather_output`` (output-sharded, result all-gathered), ``rowwise`` (input-sharded, result all-reduced), ``rowwise_split_input`` (the same, the whole input is sliced
+locally first),
 ``replicated_with_grad_allreduce`` (kept whole, gradient summed over the group). A plan with any other style is
 rejected as a whole: applying half of a column/row pair would compute garbage."""
 from typing import Dict, List, Optional
 
 from .autotp_config import PartitionType, TPLayerSpec
 
-SUPPORTED_STYLES = {"colwise", "colwise_rep", "colwise_gather_output", "rowwise", "replicated_with_grad_allreduce"}
+SUPPORTED_STYLES = {"colwise", "colwise_rep", "colwise_gather_output", "rowwise", "rowwise_split_input",
+                    "replicated_with_grad_allreduce"}
 
 
 def get_hf_tp_plan(model) -> Optional[Dict[str, str]]:
@@ -40,6 +42,8 @@ class TPPlanConverter:
                 specs.append(TPLayerSpec([rx], PartitionType.COLUMN, gather_output=style != "colwise"))
             elif style == "rowwise":
                 specs.append(TPLayerSpec([rx], PartitionType.ROW))
+            elif style == "rowwise_split_input":  # follows a gathered column layer (fused QKV / gate-up projections)
+                specs.append(TPLayerSpec([rx], PartitionType.ROW, split_input=True))
             else:
                 specs.append(TPLayerSpec([rx], PartitionType.SKIP, grad_allreduce=True))
         return specs

@@ -247,37 +247,62 @@ def test_fused_qkv_layouts_give_every_rank_whole_matching_heads():
         f(v)
 
 
-def _hf_interleaved_qkv(family):
-    """HF models with head-interleaved / blocked fused QKV sharded over two ranks reproduce the unsharded logits."""
+def _hf_family_tp2(family):
+    """A Transformers model sharded over two ranks by AutoTP reproduces the unsharded logits. Covers the fused-QKV
+    layout families (interleaved heads, CodeGen blocks, multi-query, grouped KV), Conv1D projections, ALiBi models
+    and tp_plan styles with gathered outputs."""
     import transformers as T
-    import deepspeed_b200.comm as dist
-    from deepspeed_b200.parallel.tp import LinearLayer, apply_autotp
     from deepspeed_b200.config.sections import TPTrainingConfig
+    from deepspeed_b200.parallel.tp import LinearAllreduce, LinearLayer, apply_autotp
     from deepspeed_b200.utils import groups
     torch.manual_seed(0)
-    if family == "gpt_neox":
-        m = T.GPTNeoXForCausalLM(T.GPTNeoXConfig(vocab_size=64, hidden_size=32, intermediate_size=64,
-                                                 num_hidden_layers=2, num_attention_heads=4,
-                                                 max_position_embeddings=32))
-    elif family == "bloom":
-        m = T.BloomForCausalLM(T.BloomConfig(vocab_size=64, hidden_size=32, n_layer=2, n_head=4))
-    else:
-        m = T.GPTBigCodeForCausalLM(T.GPTBigCodeConfig(vocab_size=64, n_embd=32, n_layer=2, n_head=4, n_positions=32,
-                                                       multi_query=True))
-    m.eval()
+    c = dict(vocab_size=64)
+    small = dict(hidden_size=32, intermediate_size=64, num_hidden_layers=2, num_attention_heads=4,
+                 num_key_value_heads=2, max_position_embeddings=32)
+    build = {
+        "gpt_neox": lambda: T.GPTNeoXForCausalLM(T.GPTNeoXConfig(**c, hidden_size=32, intermediate_size=64,
+                                                                 num_hidden_layers=2, num_attention_heads=4,
+                                                                 max_position_embeddings=32)),
+        "bloom": lambda: T.BloomForCausalLM(T.BloomConfig(**c, hidden_size=32, n_layer=2, n_head=4)),
+        "gpt_bigcode": lambda: T.GPTBigCodeForCausalLM(T.GPTBigCodeConfig(**c, n_embd=32, n_layer=2, n_head=4,
+                                                                          n_positions=32, multi_query=True)),
+        "gpt2": lambda: T.GPT2LMHeadModel(T.GPT2Config(**c, n_embd=32, n_layer=2, n_head=4, n_positions=32)),
+        "opt": lambda: T.OPTForCausalLM(T.OPTConfig(**c, hidden_size=32, ffn_dim=64, num_hidden_layers=2,
+                                                    num_attention_heads=4, max_position_embeddings=32,
+                                                    word_embed_proj_dim=32)),
+        "gptj": lambda: T.GPTJForCausalLM(T.GPTJConfig(**c, n_embd=32, n_layer=2, n_head=4, n_positions=32,
+                                                       rotary_dim=4)),
+        "falcon_gqa": lambda: T.FalconForCausalLM(T.FalconConfig(**c, hidden_size=32, num_hidden_layers=2,
+                                                                 num_attention_heads=4, num_kv_heads=2,
+                                                                 new_decoder_architecture=True)),
+        "falcon_mqa": lambda: T.FalconForCausalLM(T.FalconConfig(**c, hidden_size=32, num_hidden_layers=2,
+                                                                 num_attention_heads=4, multi_query=True,
+                                                                 new_decoder_architecture=False, parallel_attn=True)),
+        "phi3": lambda: T.Phi3ForCausalLM(T.Phi3Config(**c, **small, pad_token_id=0)),
+        "qwen2": lambda: T.Qwen2ForCausalLM(T.Qwen2Config(**c, **small)),
+        "gemma": lambda: T.GemmaForCausalLM(T.GemmaConfig(**c, **small, head_dim=8)),
+        "mpt": lambda: T.MptForCausalLM(T.MptConfig(**c, d_model=32, n_heads=4, n_layers=2, max_seq_len=32)),
+        "codegen": lambda: T.CodeGenForCausalLM(T.CodeGenConfig(**c, n_embd=64, n_layer=2, n_head=8, n_positions=32,
+                                                                rotary_dim=4)),
+    }
+    m = build[family]().eval()
     ids = torch.randint(0, 64, (2, 7))
     with torch.no_grad():
         want = m(ids).logits
     groups.initialize(tp_size=2, force=True)
     apply_autotp(m, TPTrainingConfig(autotp_size=2, dtype=torch.float32), groups._get_model_parallel_group())
-    qkv = [x for n, x in m.named_modules() if n.endswith(("query_key_value", "c_attn"))][0]
-    assert isinstance(qkv, LinearLayer) and qkv.row_index is not None
+    n_tp = sum(isinstance(x, (LinearLayer, LinearAllreduce)) for x in m.modules())
+    assert n_tp >= 8, n_tp  # 2 layers x (qkv / out / mlp in / mlp out) at least
+    if family in ("gpt_neox", "bloom", "gpt_bigcode", "falcon_gqa", "falcon_mqa", "codegen"):
+        qkv = [x for n, x in m.named_modules() if n.endswith(("query_key_value", "c_attn", "qkv_proj"))][0]
+        assert qkv.row_index is not None
     with torch.no_grad():
         got = m(ids).logits
     torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-4)
     return True
 
 
-@pytest.mark.parametrize("family", ["gpt_neox", "bloom", "gpt_bigcode"])
-def test_autotp_shards_family_specific_fused_qkv(family):
-    assert all(run_distributed(_hf_interleaved_qkv, 2, args=(family, )))
+@pytest.mark.parametrize("family", ["gpt_neox", "bloom", "gpt_bigcode", "gpt2", "opt", "gptj", "falcon_gqa",
+                                    "falcon_mqa", "phi3", "qwen2", "gemma", "mpt", "codegen"])
+def test_autotp_hf_families_two_ranks(family):
+    assert all(run_distributed(_hf_family_tp2, 2, args=(family, )))
