@@ -61,3 +61,45 @@ def recv_meta(src_stage):
         specs.append((dt, tuple(shape), rg))
         pos += 3 + nd
     return bool(is_tuple), specs
+
+
+def can_send_recv() -> bool:
+    """Point-to-point send / recv is what the transport uses (no 2-rank-broadcast fallback needed)."""
+    return True
+
+
+def send_obj(msg, dest: int):
+    """Send an arbitrary msgpack-serialisable Python object to global rank ``dest`` (length first, then the bytes).
+    Reference ``runtime/pipe/p2p.py:96``. The payload travels through a device tensor: use sparingly."""
+    import msgpack
+    raw = msgpack.packb(msg)
+    payload = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(_dev())
+    dist.send(torch.tensor([payload.numel()], dtype=torch.long, device=_dev()), dest)
+    dist.send(payload, dest)
+
+
+def recv_obj(sender: int):
+    """Counterpart of :func:`send_obj`; tensors found in the object are moved to the current device."""
+    import msgpack
+    length = torch.zeros(1, dtype=torch.long, device=_dev())
+    dist.recv(length, sender)
+    payload = torch.empty(int(length.item()), dtype=torch.uint8, device=_dev())
+    dist.recv(payload, sender)
+    msg = msgpack.unpackb(payload.cpu().numpy().tobytes())
+
+    def to_device(x):
+        if torch.is_tensor(x):
+            return x.to(_dev())
+        if isinstance(x, (list, tuple)):
+            return type(x)(to_device(v) for v in x)
+        if isinstance(x, dict):
+            return {k: to_device(v) for k, v in x.items()}
+        return x
+
+    return to_device(msg)
+
+
+def wait():
+    """Block until the p2p operations issued so far have completed."""
+    if torch.cuda.is_available():
+        torch.cuda.current_stream().synchronize()

@@ -65,3 +65,20 @@ def test_pipeline_two_stages_matches_one():
         merged.update(params)
     for n, p in one[1].items():
         torch.testing.assert_close(merged[n], p, rtol=1e-5, atol=1e-6)
+
+
+def _p2p_objects():
+    import deepspeed_b200.comm as dist
+    from deepspeed_b200.runtime.pipe import p2p
+    msg = {"step": 3, "names": ["a", "b"], "lr": 0.5, "nested": {"k": [1, 2, 3]}}
+    if dist.get_rank() == 0:
+        p2p.send_obj(msg, 1)
+        return True
+    got = p2p.recv_obj(0)
+    p2p.wait()
+    return got == msg and p2p.can_send_recv()
+
+
+def test_p2p_send_and_receive_python_objects():
+    from common import run_distributed
+    assert all(run_distributed(_p2p_objects, 2))

@@ -91,3 +91,19 @@ def test_fp6_and_fp12_payloads_are_bit_packed():
         y = fq.dequantize(q)
         rel = ((y.float() - x.float()).abs().amax() / x.float().abs().amax()).item()
         assert rel < tol, (bits, rel)
+
+
+def test_matmul_fp8_matches_dequantised_matmul():
+    import torch
+    from deepspeed_b200.ops.fp_quantizer import FP_Quantize
+    from deepspeed_b200.ops.fp_quantizer.fp8_gemm import matmul_fp8, matmul_fp8_fallback
+    torch.manual_seed(0)
+    q = FP_Quantize(group_size=64)
+    w = torch.randn(128, 96, dtype=torch.bfloat16)
+    wq = q.quantize(w, q_bits=8)
+    scale = q.get_scales()
+    x = torch.randn(4, 128, dtype=torch.bfloat16)
+    want = x @ q.dequantize(wq, scale=scale)
+    torch.testing.assert_close(matmul_fp8(x, wq, scale, 64, q), want)
+    torch.testing.assert_close(matmul_fp8_fallback(x, wq, scale, 64, q), want)
+    assert (want.float() - x.float() @ w.float()).abs().max() < 0.1 * (x.float() @ w.float()).abs().max()
