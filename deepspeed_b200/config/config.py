@@ -365,3 +365,4 @@ class DeepSpeedConfigWriter:
 
 __all__ = ["DeepSpeedConfig", "DeepSpeedConfigError", "DeepSpeedConfigWriter", "load_ds_config", "get_scalar_param",
            "DeepSpeedConfigObject"]
+from .getters import *  # noqa: F401,F403,E402  (dictionary readers under the reference's names)

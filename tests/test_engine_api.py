@@ -270,3 +270,43 @@ def _zero_compat(stage):
 def test_zero_optimizer_reference_methods(stage):
     for ok in run_distributed(_zero_compat, 2, args=(stage, )):
         assert all(ok), [i for i, v in enumerate(ok) if not v]
+
+
+def test_config_dictionary_getters():
+    """``get_<field>(param_dict)`` readers with the reference's defaults (runtime/config.py and friends)."""
+    import torch
+    from deepspeed_b200.config import config as C
+    d = {"train_batch_size": 32, "gradient_clipping": 1.0,
+         "optimizer": {"type": "AdamW", "params": {"lr": 1e-3, "max_grad_norm": 2.0}},
+         "scheduler": {"type": "WarmupLR", "params": {"warmup_num_steps": 10}},
+         "sparse_attention": {"mode": "bigbird", "block": 32}, "fp16": {"enabled": True},
+         "checkpoint": {"tag_validation": "fail", "parallel_write": {"pipeline_stage": True}},
+         "data_efficiency": {"data_sampling": {"enabled": True, "curriculum_learning": {"enabled": True, "x": 1}},
+                             "data_routing": {"enabled": True, "random_ltd": {"enabled": True, "layers": 2}}},
+         "progressive_layer_drop": {"enabled": True, "theta": 0.5}, "communication_data_type": "bf16",
+         "tensorboard": {"enabled": True}, "amp": {"enabled": True, "opt_level": "O1"},
+         "torch_autocast": {"enabled": True, "dtype": "bfloat16"}}
+    assert (C.get_train_batch_size(d), C.get_gradient_clipping(d), C.get_optimizer_name(d)) == (32, 1.0, "adamw")
+    assert C.get_optimizer_gradient_clipping(d) == 2.0 and C.get_scheduler_params(d) == {"warmup_num_steps": 10}
+    sa = C.get_sparse_attention(d)
+    assert sa["mode"] == "bigbird" and sa["block"] == 32 and sa["num_sliding_window_blocks"] == 3
+    assert C.get_sparse_attention({}) is None and C.get_sparse_fixed_config({})["num_local_blocks"] == 4
+    assert C.get_float16_config(d).enabled and not C.get_bfloat16_config(d).enabled
+    ck = C.get_checkpoint_params(d)
+    assert C.get_checkpoint_tag_validation_mode(ck) == "FAIL" and C.get_checkpoint_parallel_write_pipeline(ck) is True
+    assert C.get_curriculum_learning_enabled(d) and C.get_curriculum_learning_params(d) == {"x": 1}
+    assert C.get_random_ltd_enabled(d) and C.get_random_ltd_params(d) == {"layers": 2}
+    assert C.get_pld_enabled(d) and C.get_pld_params(d) == {"theta": 0.5} and C.get_pld_params({}) is False
+    assert C.get_communication_data_type(d) is torch.bfloat16 and C.get_communication_data_type({}) is None
+    assert C.get_amp_enabled(d) and C.get_amp_params(d) == {"opt_level": "O1"}
+    assert C.get_torch_autocast_enabled(d) and C.get_torch_autocast_dtype(d) is torch.bfloat16
+    assert C.get_eigenvalue_config(d)[2] == 100 and C.get_pipeline_config(d)["partition"] == "best"
+    assert C.get_monitor_config(d).tensorboard.enabled and C.get_hybrid_engine_config(d).max_out_tokens == 512
+    assert C.get_gradient_allreduce_op({}) == "avg" and C.get_zero_force_ds_cpu_optimizer({}) is True
+    import pytest
+    with pytest.raises(ValueError):
+        C.get_gradient_allreduce_op({"gradient_allreduce_op": "max"})
+    with pytest.raises(ValueError):
+        C.get_checkpoint_tag_validation_mode({"tag_validation": "maybe"})
+    with pytest.raises(NotImplementedError):
+        C.get_sparse_attention({"sparse_attention": {"mode": "hexagonal"}})
