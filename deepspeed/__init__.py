@@ -7,6 +7,7 @@ objects (loss scaler, fragment addresses) under the reference's module names so 
 the reference's tools; this package is what makes those names importable here.
 """
 import importlib
+import types
 import importlib.abc
 import importlib.util
 import sys
@@ -101,14 +102,40 @@ _ALIASES = {
 }
 
 
+class _AliasModule(types.ModuleType):
+    """Stand-in for an aliased module: attribute reads go to the real module. It is a separate object so that the
+    import system, which binds every imported submodule as an attribute of its parent, writes those bindings here
+    and not into the real package (an alias whose leaf name equals a real attribute with a different target -
+    ``deepspeed.comm.torch``, ``deepspeed.runtime.activation_checkpointing`` - would otherwise overwrite it)."""
+
+    def __init__(self, name, real):
+        super().__init__(name, getattr(real, "__doc__", None))
+        object.__setattr__(self, "_ds_real", real)
+        if hasattr(real, "__path__"):
+            self.__dict__["__path__"] = []
+        self.__dict__["__all__"] = list(getattr(real, "__all__", None) or
+                                        [k for k in vars(real) if not k.startswith("_")])
+
+    def __getattr__(self, name):
+        return getattr(object.__getattribute__(self, "_ds_real"), name)
+
+    def __setattr__(self, name, value):
+        if isinstance(value, types.ModuleType) or name.startswith("__"):
+            self.__dict__[name] = value  # submodule binding made by the import system
+        else:
+            setattr(object.__getattribute__(self, "_ds_real"), name, value)  # a user patching a global
+
+    def __dir__(self):
+        return sorted(set(dir(object.__getattribute__(self, "_ds_real"))) | set(self.__dict__))
+
+
 class _AliasLoader(importlib.abc.Loader):
 
     def __init__(self, target):
         self.target = target
 
     def create_module(self, spec):
-        mod = importlib.import_module(self.target)
-        return mod
+        return _AliasModule(spec.name, importlib.import_module(self.target))
 
     def exec_module(self, module):
         pass
