@@ -45,6 +45,8 @@ class ReferenceLayout:
                 if ent is None:
                     continue
                 u, i = ent
+                if getattr(u, "group_key", "dp") != "dp":
+                    continue  # expert units: sharded over their own (expert-data-parallel) group, saved per unit
                 self.group_params[gi].append((u.names[i], p, u.numels[i], tuple(u.shapes[i])))
         # offsets of every param in the reference flat of its group
         self.ref_offset = {}
@@ -143,6 +145,8 @@ class ReferenceLayout:
         """Inverse of :meth:`export`. ``partitions``: list per group of this rank's reference partition;
         ``write_shard(u, fp32_shard_tensor)`` stores the unit shard."""
         for u in self.z.units:
+            if not any(id(p) in self.ref_offset for p in u.params):
+                continue  # not part of the reference flats (expert units, all-frozen units)
             full = torch.zeros(u.numel_padded, dtype=torch.float32, device=u.device)
             for i, p in enumerate(u.params):
                 if id(p) not in self.ref_offset:

@@ -255,6 +255,21 @@ def _zero_optimizer_state(engine):
         "zero_stage": z.stage,
         "ds_version": __version__,
     }
+    # expert units hold different parameters on every expert-parallel rank and are sharded over their own group: they
+    # do not fit the reference's data-parallel flats and are stored per unit (this rank's shard of master + moments)
+    experts = OrderedDict()
+    for u in z.units:
+        if getattr(u, "group_key", "dp") == "dp":
+            continue
+        entry = {"names": list(u.names), "world": u.world, "rank": u.rank,
+                 "fp32": u.master_shard.detach().float().cpu().clone(), "state": {}}
+        for k in sorted(state_keys):
+            st = z._state_shard(u, k)
+            if st is not None:
+                entry["state"][k] = st.detach().float().cpu().clone()
+        experts[u.name] = entry
+    if experts:
+        sd["expert_units"] = experts
     if z.stage >= 3:
         sd[OPTIMIZER_STATE_DICT] = base
         sd[FP32_FLAT_GROUPS] = fp32
@@ -304,8 +319,10 @@ def save_engine_checkpoint(engine, save_dir, tag=None, client_state=None, save_l
         zero_sd, lay = _zero_optimizer_state(engine)  # collective: every rank participates
 
     if engine.has_moe_layers:
-        from ..moe.checkpoint import save_moe_experts
+        from ..moe.checkpoint import save_expert_optimizer_state, save_moe_experts
         save_moe_experts(engine, save_dir, tag)
+        if not engine.save_zero_checkpoint:
+            save_expert_optimizer_state(engine, save_dir, tag)
 
     if engine.save_non_zero_checkpoint:
         module_sd = _module_state_for_save(engine, exclude_frozen_parameters)
@@ -458,8 +475,14 @@ def load_engine_checkpoint(engine, load_dir, tag=None, load_module_strict=True, 
             zsd = ce.load(get_zero_ckpt_name(engine, load_dir, tag), map_location="cpu")[OPTIMIZER_STATE_DICT]
             _load_zero_state(engine, zsd, load_optimizer_states and not load_module_only,
                              load_from_fp32=engine.zero_load_from_fp32_weights() or zero3)
-        elif ckpt.get("optimizer") is not None and load_optimizer_states and not load_module_only:
-            engine.optimizer.load_state_dict(ckpt["optimizer"])
+        elif load_optimizer_states and not load_module_only:
+            osd = None
+            if engine.has_moe_layers:
+                from ..moe.checkpoint import load_expert_optimizer_state
+                osd = load_expert_optimizer_state(engine, load_dir, tag)
+            osd = osd if osd is not None else ckpt.get("optimizer")
+            if osd is not None:
+                engine.optimizer.load_state_dict(osd)
             engine.optimizer.refresh_lp_from_params() if not zero3 else None
         else:
             engine.optimizer.refresh_lp_from_params()
@@ -472,6 +495,25 @@ def load_engine_checkpoint(engine, load_dir, tag=None, load_module_strict=True, 
                 "checkpoint_parallel_dimensions", "ds_config", "ds_version", UNIVERSAL_CHECKPOINT_INFO}
     client_state = {k: v for k, v in ckpt.items() if k not in reserved}
     return os.path.join(load_dir, str(tag)), client_state
+
+
+def _matching_expert_units(z, zsd):
+    """(unit, saved entry) for the expert units whose saved shard fits the current topology."""
+    saved = zsd.get("expert_units") or {}
+    out = []
+    for u in z.units:
+        if getattr(u, "group_key", "dp") == "dp":
+            continue
+        e = saved.get(u.name)
+        if e is None:
+            continue
+        if list(e["names"]) != list(u.names) or e["world"] != u.world or e["rank"] != u.rank or \
+                e["fp32"].numel() != u.master_shard.numel():
+            logger.warning(f"expert unit {u.name}: saved shard (world {e['world']}, rank {e['rank']}) does not match the "
+                           f"current topology (world {u.world}, rank {u.rank}); its optimizer state is not restored")
+            continue
+        out.append((u, e))
+    return out
 
 
 def _load_zero_state(engine, zsd, load_optimizer_states, load_from_fp32=True):
@@ -507,6 +549,8 @@ def _load_zero_state(engine, zsd, load_optimizer_states, load_from_fp32=True):
                     u.master_shard[run.start:run.end].copy_(shard[run.start:run.end].to(u.master_shard.dtype))
 
         lay.import_(fp32, write_master)
+        for u, entry in _matching_expert_units(z, zsd):
+            u.master_shard.copy_(entry["fp32"].to(u.master_shard.dtype))
         z._lp_written_by_step = False
         z._sync_lp_from_master()
         z._post_step_gather()
@@ -528,8 +572,15 @@ def _load_zero_state(engine, zsd, load_optimizer_states, load_from_fp32=True):
             shards = {}
             lay.import_(parts, lambda u, s: shards.__setitem__(u.uid, s.clone()))
             for (skey, a, b, gi, u, v) in z._segments:
+                if u.uid not in shards:
+                    continue  # expert units: restored from their per-unit entries below
                 src = shards[u.uid][a - u.shard_offset:b - u.shard_offset]
                 z.optimizer.state[v][k] = src.to(device=v.device, dtype=_state_dtype(z, v)).clone()
+        expert_state = {u.uid: entry["state"] for u, entry in _matching_expert_units(z, zsd)}
+        for (skey, a, b, gi, u, v) in z._segments:
+            for k, shard in expert_state.get(u.uid, {}).items():
+                z.optimizer.state[v][k] = shard[a - u.shard_offset:b - u.shard_offset].to(
+                    device=v.device, dtype=_state_dtype(z, v)).clone()
         for (skey, a, b, gi, u, v) in z._segments:
             for k, val in states.get(gi, {}).items():
                 if not (torch.is_tensor(val) and val.numel() > 1):

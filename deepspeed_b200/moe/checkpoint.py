@@ -22,9 +22,24 @@ def _expert_prefix(name):
     return f"{name}.deepspeed_moe.experts.deepspeed_experts." if name else "deepspeed_moe.experts.deepspeed_experts."
 
 
+def _autoep_layers(engine):
+    """AutoEP blocks (stacked expert weights ``experts.w13 [E_local, 2I, H]`` / ``experts.w2 [E_local, H, I]``)."""
+    from ..parallel.auto_ep import AutoEPMoELayer
+    return [(name, m) for name, m in engine.module.named_modules() if isinstance(m, AutoEPMoELayer)]
+
+
+_AUTOEP_KEYS = ("experts.w13", "experts.w2")
+
+
+def _autoep_key(name, key):
+    return f"{name}.{key}" if name else key
+
+
 def strip_expert_params(engine, module_sd):
     prefixes = [_expert_prefix(n) for n, _ in _moe_layers(engine)]
-    return OrderedDict((k, v) for k, v in module_sd.items() if not any(k.startswith(p) for p in prefixes))
+    stacked = {_autoep_key(n, k) for n, _ in _autoep_layers(engine) for k in _AUTOEP_KEYS}
+    return OrderedDict((k, v) for k, v in module_sd.items()
+                       if k not in stacked and not any(k.startswith(p) for p in prefixes))
 
 
 def save_moe_experts(engine, save_dir, tag):
@@ -43,6 +58,20 @@ def save_moe_experts(engine, save_dir, tag):
                 if k.startswith(f"{prefix}{local_id}."):
                     sd[k.replace(f"{prefix}{local_id}.", f"{prefix}{global_id}.")] = v.detach().cpu().clone()
             engine.checkpoint_engine.save(sd, expert_ckpt_name(save_dir, layer_id, global_id, tag))
+    # AutoEP blocks: one file per global expert as well, so a checkpoint loads at any expert-parallel degree. Layer
+    # ids continue after the DS-MoE layers.
+    base = len(_moe_layers(engine))
+    for i, (name, layer) in enumerate(_autoep_layers(engine)):
+        gname = layer.group_name
+        if layer.ep_size > 1 and groups._get_expert_data_parallel_rank(gname) != 0:
+            continue
+        if layer.ep_size == 1 and getattr(engine, "seq_dp_rank", 0) != 0:
+            continue
+        for local_id in range(layer.num_local_experts):
+            global_id = layer.ep_rank * layer.num_local_experts + local_id
+            sd = OrderedDict((_autoep_key(name, k), getattr(layer.experts, k.split(".")[1])[local_id].detach().cpu().clone())
+                             for k in _AUTOEP_KEYS)
+            engine.checkpoint_engine.save(sd, expert_ckpt_name(save_dir, base + i, global_id, tag))
 
 
 def load_moe_experts(engine, load_dir, tag, module_sd):
@@ -59,6 +88,56 @@ def load_moe_experts(engine, load_dir, tag, module_sd):
             sd = engine.checkpoint_engine.load(path, map_location="cpu")
             for k, v in sd.items():
                 module_sd[k.replace(f"{prefix}{global_id}.", f"{prefix}{local_id}.")] = v
+    base = len(_moe_layers(engine))
+    for i, (name, layer) in enumerate(_autoep_layers(engine)):
+        per_key = {k: [] for k in _AUTOEP_KEYS}
+        for local_id in range(layer.num_local_experts):
+            global_id = layer.ep_rank * layer.num_local_experts + local_id
+            path = expert_ckpt_name(load_dir, base + i, global_id, tag)
+            if not os.path.exists(path):
+                per_key = None  # a checkpoint from before per-expert files: the stacked tensors are in module_sd
+                break
+            sd = engine.checkpoint_engine.load(path, map_location="cpu")
+            for k in _AUTOEP_KEYS:
+                per_key[k].append(sd[_autoep_key(name, k)])
+        if per_key is not None:
+            for k in _AUTOEP_KEYS:
+                module_sd[_autoep_key(name, k)] = torch.stack(per_key[k])
+
+
+def expert_optimizer_ckpt_name(ckpt_dir, tag, ep_rank, mp_rank=0):
+    """Reference ``engine.py _get_optimizer_ckpt_name``: optimizer state of one expert-parallel rank when ZeRO does not
+    write per-rank files."""
+    return os.path.join(ckpt_dir, str(tag), f"expp_rank_{ep_rank}_mp_rank_{mp_rank:02d}_optim_states.pt")
+
+
+def _max_ep(engine):
+    sizes = [m.ep_size for _, m in _moe_layers(engine)] + [m.ep_size for _, m in _autoep_layers(engine)]
+    return max(sizes, default=1)
+
+
+def save_expert_optimizer_state(engine, save_dir, tag):
+    """Without ZeRO files the optimizer state sits in rank 0's model-state file; with expert parallelism every
+    expert-parallel rank owns different expert parameters, so each (first replica of it) writes its own."""
+    ep = _max_ep(engine)
+    if ep <= 1 or engine.optimizer is None:
+        return
+    gname = f"ep_size_{ep}"
+    if groups._get_expert_data_parallel_rank(gname) != 0:
+        return
+    path = expert_optimizer_ckpt_name(save_dir, tag, groups._get_expert_parallel_rank(gname))
+    engine.checkpoint_engine.save({"optimizer": engine.optimizer.state_dict()}, path)
+
+
+def load_expert_optimizer_state(engine, load_dir, tag):
+    """This rank's ``expp_rank_*`` optimizer state, or ``None``."""
+    ep = _max_ep(engine)
+    if ep <= 1:
+        return None
+    path = expert_optimizer_ckpt_name(load_dir, tag, groups._get_expert_parallel_rank(f"ep_size_{ep}"))
+    if not os.path.exists(path):
+        return None
+    return engine.checkpoint_engine.load(path, map_location="cpu")["optimizer"]
 
 
 def load_expert_files(checkpoint_path, tag, state_dict, model=None, mpu=None, num_experts=1, old_moe_load=False):

@@ -407,3 +407,59 @@ def _engine_rejects():
 
 def test_engine_rejects_bad_expert_parallel_section():
     assert run_distributed(_engine_rejects, 1)[0]
+
+
+def _autoep_checkpoint(tmp, zero_stage):
+    """Expert-parallel checkpoints: every expert-parallel rank's experts and their optimizer state survive a save /
+    load (per-expert files + per-rank optimizer state), training resumes bit-identically, and the per-expert files load
+    at another expert-parallel degree."""
+    import os
+    import deepspeed_b200 as ds
+    from deepspeed_b200.models.mixtral import MixtralConfig, MixtralForCausalLM
+
+    def build(ep):
+        torch.manual_seed(0)
+        cfg = MixtralConfig.tiny(dtype=torch.float32, gradient_checkpointing=False, ep_size=ep,
+                                 router_aux_loss_coef=0.0)
+        dcfg = {"train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}},
+                "zero_optimization": {"stage": zero_stage}}
+        return ds.initialize(model=MixtralForCausalLM(cfg), config=dcfg)[0]
+
+    engine = build(2)
+    rank = ds.comm.get_rank()
+    torch.manual_seed(5 + rank)
+    batches = [torch.randint(0, 512, (2, 16), device=engine.device) for _ in range(4)]
+
+    def step(e, ids):
+        loss = e(ids, labels=ids)
+        e.backward(loss)
+        e.step()
+        return float(loss)
+
+    for ids in batches[:2]:
+        step(engine, ids)
+    want = {k: v.clone() for k, v in engine.module.state_dict().items()}
+    engine.save_checkpoint(tmp, tag="t")
+    ref_losses = [step(engine, ids) for ids in batches[2:]]
+    files = sorted(os.listdir(os.path.join(tmp, "t")))
+    assert sum(f.startswith("layer_") and "_expert_" in f for f in files) == 2 * 4  # 2 MoE layers x 4 experts
+    if zero_stage == 0:
+        assert {"expp_rank_0_mp_rank_00_optim_states.pt", "expp_rank_1_mp_rank_00_optim_states.pt"} <= set(files)
+    resumed = build(2)
+    resumed.load_checkpoint(tmp, tag="t")
+    for k, v in resumed.module.state_dict().items():
+        assert torch.equal(v, want[k]), k
+    got_losses = [step(resumed, ids) for ids in batches[2:]]
+    assert got_losses == ref_losses, (got_losses, ref_losses)  # optimizer state came back too
+    if zero_stage == 0:  # the per-expert files at another expert-parallel degree (weights only)
+        single = build(1)
+        single.load_checkpoint(tmp, tag="t", load_optimizer_states=False, load_module_only=True)
+        sd = single.module.state_dict()
+        k = "layers.0.block_sparse_moe.experts.w13"
+        assert sd[k].shape[0] == 4 and torch.equal(sd[k][rank * 2:(rank + 1) * 2], want[k])
+    return True
+
+
+@pytest.mark.parametrize("zero_stage", [0, 1, 2])
+def test_expert_parallel_checkpoint_roundtrip_and_resume(tmp_path, zero_stage):
+    assert all(run_distributed(_autoep_checkpoint, 2, args=(str(tmp_path), zero_stage)))
