@@ -188,6 +188,142 @@ __global__ void __launch_bounds__(256) int_group_dequant_kernel(const int8_t* __
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// LoCo (error-feedback) variant of the group quantizer (reference swizzled_quantize.cu:200-316
+// loco_swizzled_quant_kernel): the value that is quantized is v = x + beta * err, and the error buffer is replaced by
+// what the quantization lost, err = v - dequant(q). `err` is fp32, laid out like x (unswizzled).
+// ---------------------------------------------------------------------------------------------------------
+template <typename T, int BITS>
+__global__ void __launch_bounds__(256) loco_group_quant_kernel(const T* __restrict__ x, float* __restrict__ err,
+                                                               int8_t* __restrict__ q, float* __restrict__ scales,
+                                                               int64_t ngroups, int group, float beta, int swz_nodes,
+                                                               int swz_devs)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    constexpr float qmax = BITS == 8 ? 127.f : 7.f;
+    const int iters = group / 256;
+    const int64_t parts = (int64_t)swz_nodes * swz_devs;
+    const int64_t groups_per_part = parts > 0 ? ngroups / parts : 0;
+    for (int64_t g = warp; g < ngroups; g += nwarps) {
+        const T* xg = x + g * group;
+        float* eg = err + g * group;
+        float amax = 0.f;
+        for (int it = 0; it < iters; it++) {
+            const int o = (it * 32 + lane) * 8;
+            dsb::f8 v = dsb::load8(xg + o);
+            const float4 e0 = *reinterpret_cast<const float4*>(eg + o), e1 = *reinterpret_cast<const float4*>(eg + o + 4);
+            const float ev[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+#pragma unroll
+            for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v.v[i] + beta * ev[i]));
+        }
+        amax = dsb::warp_max(amax);
+        const float scale = amax > 0.f ? amax / qmax : 1.f;
+        const float inv = 1.f / scale;
+        int64_t og = g;
+        if (parts > 0) {
+            const int64_t part = g / groups_per_part, j = g % groups_per_part;
+            const int64_t node = part / swz_devs, dev = part % swz_devs;
+            og = (dev * swz_nodes + node) * groups_per_part + j;
+        }
+        if (lane == 0) scales[og] = scale;
+        for (int it = 0; it < iters; it++) {
+            const int o = (it * 32 + lane) * 8;
+            dsb::f8 v = dsb::load8(xg + o);
+            const float4 e0 = *reinterpret_cast<const float4*>(eg + o), e1 = *reinterpret_cast<const float4*>(eg + o + 4);
+            const float ev[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+            int qi[8];
+            float ne[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const float t = v.v[i] + beta * ev[i];
+                qi[i] = max(-(int)qmax, min((int)qmax, __float2int_rn(t * inv)));
+                ne[i] = t - (float)qi[i] * scale;
+            }
+            *reinterpret_cast<float4*>(eg + o) = make_float4(ne[0], ne[1], ne[2], ne[3]);
+            *reinterpret_cast<float4*>(eg + o + 4) = make_float4(ne[4], ne[5], ne[6], ne[7]);
+            if (BITS == 8) {
+                uint2 out;
+                out.x = (qi[0] & 0xff) | ((qi[1] & 0xff) << 8) | ((qi[2] & 0xff) << 16) | ((uint32_t)(qi[3] & 0xff) << 24);
+                out.y = (qi[4] & 0xff) | ((qi[5] & 0xff) << 8) | ((qi[6] & 0xff) << 16) | ((uint32_t)(qi[7] & 0xff) << 24);
+                *reinterpret_cast<uint2*>(q + og * group + o) = out;
+            } else {
+                uint32_t out = 0;
+#pragma unroll
+                for (int i = 0; i < 8; i++) out |= (uint32_t)(qi[i] & 0xf) << (4 * i);
+                *reinterpret_cast<uint32_t*>(q + (og * group >> 1) + (it * 32 + lane) * 4) = out;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// MoQ fake quantization in place (reference fake_quantizer.cu: fake_quantize_kernel / _asym and the stochastic-rounding
+// sr_ variants): every group is snapped to its `bits`-bit grid and written back in the input dtype. One warp per group,
+// group size a multiple of 256. Symmetric: q in [-2^(b-1), 2^(b-1)-1], scale = amax / 2^(b-1); asymmetric: q in
+// [0, 2^b - 1] over [min, max]. Stochastic rounding adds a uniform draw in [0, 1) before the floor.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float uniform01(uint32_t seed, uint64_t idx)
+{
+    uint64_t z = idx + 0x9E3779B97F4A7C15ull * (uint64_t)(seed + 1);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return (float)(z >> 40) * (1.0f / 16777216.0f);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) fake_quant_kernel(T* __restrict__ x, int64_t ngroups, int group, int bits,
+                                                         int symmetric, int stochastic, uint32_t seed)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int iters = group / 256;
+    const float levels = (float)(1 << bits);
+    for (int64_t g = warp; g < ngroups; g += nwarps) {
+        T* xg = x + g * group;
+        float mx = -INFINITY, mn = INFINITY;
+        for (int it = 0; it < iters; it++) {
+            dsb::f8 v = dsb::load8(xg + (it * 32 + lane) * 8);
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                mx = fmaxf(mx, v.v[i]);
+                mn = fminf(mn, v.v[i]);
+            }
+        }
+        mx = dsb::warp_max(mx);
+        mn = -dsb::warp_max(-mn);
+        float scale, zero, lo, hi;
+        if (symmetric) {
+            const float amax = fmaxf(fabsf(mx), fabsf(mn));
+            scale = amax > 0.f ? 2.f * amax / levels : 1.f;
+            zero = 0.f;
+            lo = -levels * 0.5f;
+            hi = levels * 0.5f - 1.f;
+        } else {
+            scale = mx > mn ? (mx - mn) / (levels - 1.f) : 1.f;
+            zero = mn;
+            lo = 0.f;
+            hi = levels - 1.f;
+        }
+        const float inv = 1.f / scale;
+        for (int it = 0; it < iters; it++) {
+            const int o = (it * 32 + lane) * 8;
+            dsb::f8 v = dsb::load8(xg + o);
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const float t = (v.v[i] - zero) * inv;
+                float qv = stochastic ? floorf(t + uniform01(seed, (uint64_t)(g * group + o + i))) : rintf(t);
+                qv = fminf(hi, fmaxf(lo, qv));
+                v.v[i] = qv * scale + zero;
+            }
+            dsb::store8(xg + o, v);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // qgZ stage 2: out = sum_c dequant(q[c]) for `nchunks` received chunks of `chunk_elems` each (int8 or int4 groups
 // of size `group`), written as T (bf16/fp32-as-bf16 pairs) without re-quantization (single NVSwitch domain), or
 // re-quantized to int4 groups by the caller with int_group_quant.
@@ -384,6 +520,60 @@ int dsb200_int_group_quant(const void* x, int dt, void* q, float* scales, int64_
     }
 #undef IQ
     DSB_CHECK_LAUNCH("int_group_quant");
+    return 0;
+}
+
+// LoCo error-feedback quantization: q = Q(x + beta * err); err <- (x + beta * err) - DQ(q). err: fp32 [n].
+int dsb200_loco_group_quant(const void* x, int dt, float* err, void* q, float* scales, int64_t n, int group, int bits,
+                            float beta, int swz_nodes, int swz_devs, cudaStream_t stream)
+{
+    if (n <= 0) return 0;
+    if (group % 256 != 0 || n % group != 0 || (bits != 8 && bits != 4)) {
+        dsb200_set_error("loco_group_quant: group must be a multiple of 256 dividing n; bits in {4,8}");
+        return -1;
+    }
+    const int64_t ng = n / group;
+    if (swz_nodes * swz_devs > 0 && ng % ((int64_t)swz_nodes * swz_devs) != 0) {
+        dsb200_set_error("loco_group_quant: groups must divide evenly over nodes*devices for the swizzled layout");
+        return -1;
+    }
+#define LQ(T, B)                                                                                                      \
+    loco_group_quant_kernel<T, B><<<grid_warps(ng), 256, 0, stream>>>((const T*)x, err, (int8_t*)q, scales, ng, group, \
+                                                                      beta, swz_nodes, swz_devs)
+    if (dt == DSB_DT_BF16) {
+        if (bits == 8) LQ(__nv_bfloat16, 8); else LQ(__nv_bfloat16, 4);
+    } else if (dt == DSB_DT_F16) {
+        if (bits == 8) LQ(__half, 8); else LQ(__half, 4);
+    } else {
+        dsb200_set_error("loco_group_quant: input must be fp16/bf16");
+        return -1;
+    }
+#undef LQ
+    DSB_CHECK_LAUNCH("loco_group_quant");
+    return 0;
+}
+
+// In-place fake quantization (quantize-dequantize) of x [n] in groups; bits in [2, 16].
+int dsb200_fake_quant(void* x, int dt, int64_t n, int group, int bits, int symmetric, int stochastic, unsigned int seed,
+                      cudaStream_t stream)
+{
+    if (n <= 0) return 0;
+    if (group % 256 != 0 || n % group != 0 || bits < 2 || bits > 16) {
+        dsb200_set_error("fake_quant: group must be a multiple of 256 dividing n; bits in [2,16]");
+        return -1;
+    }
+    const int64_t ng = n / group;
+    if (dt == DSB_DT_BF16)
+        fake_quant_kernel<__nv_bfloat16><<<grid_warps(ng), 256, 0, stream>>>((__nv_bfloat16*)x, ng, group, bits, symmetric,
+                                                                             stochastic, seed);
+    else if (dt == DSB_DT_F16)
+        fake_quant_kernel<__half><<<grid_warps(ng), 256, 0, stream>>>((__half*)x, ng, group, bits, symmetric, stochastic,
+                                                                      seed);
+    else {
+        dsb200_set_error("fake_quant: input must be fp16/bf16");
+        return -1;
+    }
+    DSB_CHECK_LAUNCH("fake_quant");
     return 0;
 }
 

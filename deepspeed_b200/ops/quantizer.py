@@ -28,6 +28,9 @@ def _lib():
         L.dsb200_int_group_dequant.argtypes = [P, P, P, I, L64, I, I, P]
         L.dsb200_dequant_reduce.argtypes = [P, P, P, I, L64, I, I, I, F, P]
         L.dsb200_minifloat_quant.argtypes = [P, P, P, I, L64, I, I, I, F, I, U, P]
+        if hasattr(L, "dsb200_loco_group_quant"):
+            L.dsb200_loco_group_quant.argtypes = [P, I, P, P, P, L64, I, I, F, I, I, P]
+            L.dsb200_fake_quant.argtypes = [P, I, L64, I, I, I, I, U, P]
         _declared = True
     return L
 
@@ -120,6 +123,60 @@ def dequantize(q, s, groups, bits=8, dtype=torch.bfloat16, out=None):
         vals = q.float()
     out.copy_((vals.view(groups, group) * s[:, None]).view(-1).to(dtype))
     return out
+
+
+def loco_quantize(x, err, groups, bits=8, beta=0.8, swizzle=None):
+    """LoCo error-feedback group quantization (reference ``loco_swizzled_quant``): quantizes ``x + beta * err`` and
+    replaces ``err`` (fp32, shape of ``x``, updated in place) by what the quantization lost. Returns (q, scales)."""
+    x = x.contiguous().view(-1)
+    n = x.numel()
+    assert n % groups == 0 and err.numel() == n and err.dtype == torch.float32 and err.is_contiguous()
+    group = n // groups
+    nodes, devs = swizzle if swizzle else (0, 0)
+    if _cuda(x) and group % 256 == 0 and hasattr(_lib(), "dsb200_loco_group_quant"):
+        q = torch.empty(n * bits // 8, dtype=torch.int8, device=x.device)
+        s = torch.empty(groups, dtype=torch.float32, device=x.device)
+        K._check(_lib().dsb200_loco_group_quant(K._ptr(x), K._dt(x), K._ptr(err), K._ptr(q), K._ptr(s), n, group, bits,
+                                                float(beta), nodes, devs, K._stream()), "loco_group_quant")
+        return q, s
+    v = x.float() + beta * err.view(-1)
+    q, s = quantize(v, groups, bits, True, swizzle=None)
+    err.view(-1).copy_(v - dequantize(q, s, groups, bits, dtype=torch.float32))
+    if nodes * devs > 0:
+        q, s = quantize(v, groups, bits, True, swizzle=swizzle)
+    return q, s
+
+
+def fake_quantize(x, groups, bits=8, symmetric=True, stochastic=False, seed=0):
+    """MoQ quantize-dequantize of ``x`` in place (reference ``fake_quantizer.cu`` ``ds_quantize`` / ``ds_sr_quantize``
+    and the ``_asym`` variants). Returns ``x``."""
+    flat = x.view(-1)
+    n = flat.numel()
+    assert n % groups == 0
+    group = n // groups
+    if _cuda(x) and x.is_contiguous() and group % 256 == 0 and x.dtype in (torch.bfloat16, torch.float16) and \
+            hasattr(_lib(), "dsb200_fake_quant"):
+        K._check(_lib().dsb200_fake_quant(K._ptr(x), K._dt(x), n, group, int(bits), int(bool(symmetric)),
+                                          int(bool(stochastic)), int(seed) & 0xFFFFFFFF, K._stream()), "fake_quant")
+        return x
+    v = flat.float().view(groups, group)
+    levels = float(1 << bits)
+    if symmetric:
+        amax = v.abs().amax(dim=1, keepdim=True)
+        scale = torch.where(amax > 0, 2 * amax / levels, torch.ones_like(amax))
+        zero, lo, hi = torch.zeros_like(amax), -levels / 2, levels / 2 - 1
+    else:
+        mn, mx = v.amin(dim=1, keepdim=True), v.amax(dim=1, keepdim=True)
+        scale = torch.where(mx > mn, (mx - mn) / (levels - 1), torch.ones_like(mx))
+        zero, lo, hi = mn, 0.0, levels - 1
+    t = (v - zero) / scale
+    if stochastic:
+        g = torch.Generator(device=t.device).manual_seed(int(seed))
+        t = torch.floor(t + torch.rand(t.shape, generator=g, device=t.device))
+    else:
+        t = torch.round(t)
+    flat.copy_((t.clamp(lo, hi) * scale + zero).view(-1).to(x.dtype))
+    return x
 
 
 def swizzle_quant(x, groups, bits, nodes, devices_per_node):

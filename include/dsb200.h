@@ -329,6 +329,28 @@ int dsb200_dc_plan(int n_units, const int64_t* unit_bytes, const uint8_t* persis
                    double reuse_window_us, double safety, uint8_t* persist_out, int* launch_step, int* keep_after,
                    double* sim);
 
+/* LoCo error-feedback group quantization: q = Q(x + beta * err), err <- (x + beta * err) - DQ(q); err fp32 [n].
+ * Reference: csrc/quantization/swizzled_quantize.cu:200-316. */
+int dsb200_loco_group_quant(const void* x, int dt, float* err, void* q, float* scales, int64_t n, int group, int bits,
+                            float beta, int swz_nodes, int swz_devs, cudaStream_t stream);
+/* MoQ in-place fake quantization (sym / asym, nearest or stochastic rounding). Reference: fake_quantizer.cu. */
+int dsb200_fake_quant(void* x, int dt, int64_t n, int group, int bits, int symmetric, int stochastic, unsigned int seed,
+                      cudaStream_t stream);
+
+/* FastGen / inference row kernels (csrc/fastgen_ops.cu). Reference: inference/v2/kernels/ragged_ops/{embed,logits_gather,
+ * moe_scatter,moe_gather,top_k_gating}, core_ops/{bias_activations,gated_activations}. */
+int dsb200_embed_rows(const void* table, const int64_t* ids, const void* pos_table, const int64_t* pos, int pos_offset,
+                      void* out, int64_t rows, int cols, int dt, cudaStream_t stream);
+int dsb200_bias_act(const void* x, const void* bias, void* y, int64_t rows, int cols, int act, int dt,
+                    cudaStream_t stream);
+int dsb200_gated_act(const void* x, const void* bias, void* y, int64_t rows, int inter, int act, int dt,
+                     cudaStream_t stream);
+int dsb200_topk_gating(const float* logits, int T, int E, int k, int renorm, float* scores, int* experts, int* counts,
+                       int* slot, cudaStream_t stream);
+int dsb200_moe_scatter(const void* x, const int* dst, int T, int k, void* out, int cols, int dt, cudaStream_t stream);
+int dsb200_moe_gather(const void* expert_out, const int* src, const float* w, int T, int k, void* out, int cols, int dt,
+                      cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
