@@ -12,6 +12,8 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from ....ops import fastgen
+
 from ....ops import fused
 
 
@@ -88,13 +90,13 @@ class _MLP(nn.Module):
         self.down = nn.Linear(inter, h, bias=spec.mlp_bias, **kw)
 
     def forward(self, x):
-        u = self.up(x)
+        if self.gated and self.act_name == "silu" and self.up.bias is None:
+            return self.down(fused.swiglu(self.up(x)))
+        # bias add and (gated) activation in one pass over the projection's output (csrc/fastgen_ops.cu)
+        u = F.linear(x, self.up.weight)
         if self.gated:
-            if self.act_name == "silu":
-                return self.down(fused.swiglu(u))
-            g, v = u.chunk(2, dim=-1)
-            return self.down(_act(self.act_name)(g) * v)
-        return self.down(_act(self.act_name)(u))
+            return self.down(fastgen.gated_act(u, self.up.bias, self.act_name))
+        return self.down(fastgen.bias_act(u, self.up.bias, self.act_name))
 
 
 class _MoE(nn.Module):
@@ -112,9 +114,45 @@ class _MoE(nn.Module):
             self.shared = _MLP(spec, spec.shared_expert_intermediate_size, device)
             self.shared_gate = nn.Linear(spec.hidden_size, 1, bias=False, **kw)
 
+    def _stack_experts(self):
+        """Expert weights side by side for the grouped GEMM: ``w13 [E, 2I, H]`` / ``w2 [E, H, I]``. The per-expert
+        ``nn.Linear`` weights become views of the stacks, so nothing is held twice."""
+        w13 = torch.stack([e.up.weight.data for e in self.experts]).contiguous()
+        w2 = torch.stack([e.down.weight.data for e in self.experts]).contiguous()
+        for i, e in enumerate(self.experts):
+            e.up.weight.data, e.down.weight.data = w13[i], w2[i]
+        self._w13, self._w2 = w13, w2
+
+    def _grouped_ok(self, x):
+        import os
+        e0 = self.experts[0]
+        return (x.is_cuda and os.environ.get("DSB200_FASTGEN_GROUPED_MOE", "1") != "0" and e0.gated
+                and e0.act_name == "silu" and e0.up.bias is None and e0.down.bias is None
+                and x.dtype in (torch.bfloat16, torch.float16) and x.shape[-1] % 8 == 0 and fastgen._native(x))
+
+    def _forward_grouped(self, x):
+        """Gating kernel -> scatter to expert-contiguous rows -> two grouped GEMMs around SwiGLU -> weighted gather.
+        One host read (the expert counts) per layer instead of one ``nonzero`` per expert."""
+        from ....ops.grouped_gemm import grouped_mm
+        if getattr(self, "_w13", None) is None or self._w13.device != x.device:
+            self._stack_experts()
+        scores, experts, counts, slot = fastgen.topk_gating(self.gate(x), self.top_k, self.norm_topk, with_slots=True)
+        starts = torch.cumsum(counts, 0, dtype=torch.int32) - counts
+        rows = starts[experts.long()] + slot
+        n_rows = x.shape[0] * self.top_k
+        xs = fastgen.moe_scatter(x, rows, n_rows)
+        cl = counts.tolist()
+        h = fused.swiglu(grouped_mm(xs, self._w13, cl))
+        return fastgen.moe_gather(grouped_mm(h, self._w2, cl), rows, scores)
+
     def forward(self, x):
         shape = x.shape
         x = x.reshape(-1, shape[-1])
+        if self._grouped_ok(x):
+            out = self._forward_grouped(x.contiguous())
+            if self.shared is not None:
+                out = out + torch.sigmoid(self.shared_gate(x)) * self.shared(x)
+            return out.view(shape)
         probs = torch.softmax(self.gate(x).float(), dim=-1)
         w, idx = probs.topk(self.top_k, dim=-1)
         if self.norm_topk:
@@ -192,10 +230,10 @@ class GenericDecoder(nn.Module):
 
     def forward_tokens(self, ids, pos, attn_fn):
         spec = self.spec
-        h = self.embed_tokens(ids)
-        if spec.pos == "learned":
-            h = h + self.embed_positions(pos + spec.pos_offset)
+        if spec.pos == "learned":  # token + position lookup in one kernel (csrc/fastgen_ops.cu embed_rows)
+            h = fastgen.embed(ids, self.embed_tokens.weight, pos, self.embed_positions.weight, spec.pos_offset)
         else:
+            h = fastgen.embed(ids, self.embed_tokens.weight)
             cos, sin = self.rope(ids.device)
             rd = spec.rotary_dim or spec.head_dim
         for li, layer in enumerate(self.layers):

@@ -107,7 +107,7 @@ def test_loco_and_fake_quant_native_kernels():
         q, s = Q.loco_quantize(x, err, 16, bits, beta=0.8)
         qc, sc = Q.loco_quantize(x_cpu.float(), err_cpu, 16, bits, beta=0.8)
         torch.testing.assert_close(s.cpu(), sc, rtol=1e-5, atol=1e-7)
-        deq = Q.dequantize(q, s, 16, bits, dtype=torch.float32)
+        deq = Q.dequantize(q.cpu(), s.cpu(), 16, bits, dtype=torch.float32).to(dev)  # exact fp32 dequantisation
         torch.testing.assert_close(deq + err, x.float() + 0.8 * err_old, rtol=0, atol=1e-5)  # value = dequant + new error
         torch.testing.assert_close(err.cpu(), err_cpu, rtol=0, atol=float(sc.max()) * 1.01)
         assert (q.cpu().view(torch.uint8).long() - qc.view(torch.uint8).long()).abs().float().mean() < 0.02
@@ -123,3 +123,38 @@ def test_loco_and_fake_quant_native_kernels():
     x = torch.randn(8 * 256, device=dev).half()
     mean = torch.stack([Q.fake_quantize(x.clone(), 8, 3, True, True, seed=i).float() for i in range(200)]).mean(0)
     assert (mean - x.float()).abs().mean() < (Q.fake_quantize(x.clone(), 8, 3, True).float() - x.float()).abs().mean() * 0.5
+
+
+@pytest.mark.gpu
+def test_fastgen_decoder_blocks_use_the_kernels_and_match_the_loop_path(monkeypatch):
+    """FastGen MoE block: gating kernel + scatter + grouped GEMM + gather against the per-expert loop; MLP blocks with
+    bias / GeGLU through the fused activation kernels against plain PyTorch."""
+    from deepspeed_b200.inference.v2.model_implementations import arch as A
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    spec = A.ArchSpec(hidden_size=128, intermediate_size=256, num_experts=8, num_experts_per_tok=2,
+                      moe_intermediate_size=192, shared_expert_intermediate_size=64, dtype=torch.bfloat16)
+    moe = A._MoE(spec, device=dev)
+    for p in moe.parameters():
+        torch.nn.init.normal_(p, std=0.05)
+    x = torch.randn(3, 37, 128, device=dev, dtype=torch.bfloat16)
+    assert moe._grouped_ok(x.view(-1, 128))
+    with torch.no_grad():
+        fast = moe(x)
+        monkeypatch.setenv("DSB200_FASTGEN_GROUPED_MOE", "0")
+        slow = moe(x)  # the experts' weights are views of the stacks now: same numbers through the loop
+    torch.testing.assert_close(fast.float(), slow.float(), rtol=3e-2, atol=3e-2)
+    assert moe.experts[3].up.weight.data_ptr() == moe._w13[3].data_ptr()
+    for act, gated in (("gelu", True), ("gelu_tanh", False), ("relu", True)):
+        sp = A.ArchSpec(hidden_size=128, intermediate_size=256, act=act, gated_mlp=gated, mlp_bias=True,
+                        dtype=torch.bfloat16)
+        mlp = A._MLP(sp, 256, device=dev)
+        for p in mlp.parameters():
+            torch.nn.init.normal_(p, std=0.05)
+        with torch.no_grad():
+            got = mlp(x)
+            u = mlp.up(x).float()
+            f = A._act(act)
+            ref = (f(u[..., :256]) * u[..., 256:]) if gated else f(u)
+            want = torch.nn.functional.linear(ref.bfloat16(), mlp.down.weight, mlp.down.bias)
+        torch.testing.assert_close(got.float(), want.float(), rtol=3e-2, atol=3e-2)
