@@ -47,7 +47,14 @@ class Quantizer:
 
     @staticmethod
     def fake_quantize(x, bits, groups, symmetric=True, stochastic=False):
-        """Quantize-dequantize ``x`` group-wise to ``bits`` bits."""
+        """Quantize-dequantize ``x`` group-wise to ``bits`` bits. Half-precision CUDA tensors go through the in-place
+        kernel (``csrc/quant.cu`` ``fake_quant_kernel``: one read and one write of the tensor)."""
+        if x.is_cuda and x.dtype in (torch.bfloat16, torch.float16) and x.numel() % groups == 0 and \
+                (x.numel() // groups) % 256 == 0:
+            from ..ops import quantizer as Q
+            if Q._cuda(x) and hasattr(Q._lib(), "dsb200_fake_quant"):
+                seed = int(torch.randint(0, 2**31 - 1, (1, )).item()) if stochastic else 0
+                return Q.fake_quantize(x.contiguous().clone(), groups, bits, symmetric, stochastic, seed)
         flat = x.reshape(groups, -1).float()
         if symmetric:
             qmax = 2**(bits - 1) - 1
