@@ -261,7 +261,14 @@ def _zero_optimizer_state(engine):
     for u in z.units:
         if getattr(u, "group_key", "dp") == "dp":
             continue
-        entry = {"names": list(u.names), "world": u.world, "rank": u.rank,
+        from ..utils import groups as _groups
+        try:
+            ep_rank, ep_size = _groups._get_expert_parallel_rank(u.group_key), \
+                _groups._get_expert_parallel_world_size(u.group_key)
+        except Exception:  # noqa: BLE001
+            ep_rank, ep_size = 0, 1
+        entry = {"names": list(u.names), "world": u.world, "rank": u.rank, "shapes": [tuple(sh) for sh in u.shapes],
+                 "offsets": list(u.offsets), "numel_padded": u.numel_padded, "ep_rank": ep_rank, "ep_size": ep_size,
                  "fp32": u.master_shard.detach().float().cpu().clone(), "state": {}}
         for k in sorted(state_keys):
             st = z._state_shard(u, k)

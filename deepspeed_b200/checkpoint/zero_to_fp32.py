@@ -129,12 +129,54 @@ def _merge_stage3(flat_per_rank, param_shapes, world):
     return out
 
 
+def _merge_expert_units(optim_states, key="fp32"):
+    """Expert parameters are not in the data-parallel flats: every rank file carries its expert units (this rank's shard
+    of the unit's fp32 master, plus moments). Shards of a unit are concatenated over its expert-data-parallel ranks,
+    cut into parameters, and the expert-parallel ranks' tensors are put together: stacked experts (``[E_local, ...]``)
+    along dim 0, per-expert module names by renumbering the local expert index to the global one."""
+    import re
+    shards = {}  # (unit name, ep_rank) -> {edp rank: entry}
+    for o in optim_states:
+        for uname, e in (o.get("expert_units") or {}).items():
+            shards.setdefault((uname, e.get("ep_rank", 0)), {})[e["rank"]] = e
+    per_rank = {}  # param name -> {ep_rank: tensor}
+    ep_size = 1
+    for (uname, ep_rank), by_rank in shards.items():
+        first = by_rank[min(by_rank)]
+        if len(by_rank) != first["world"] or "shapes" not in first:
+            continue  # incomplete set of shards (or an old file without geometry): leave these parameters out
+        ep_size = max(ep_size, first.get("ep_size", 1))
+        pick = (lambda e: e["fp32"]) if key == "fp32" else (lambda e: e["state"][key])
+        if key != "fp32" and any(key not in e["state"] for e in by_rank.values()):
+            continue
+        flat = torch.cat([pick(by_rank[r]).float().reshape(-1) for r in sorted(by_rank)])
+        for name, shape, off in zip(first["names"], first["shapes"], first["offsets"]):
+            n = torch.Size(shape).numel()
+            per_rank.setdefault(name, {})[ep_rank] = flat[off:off + n].view(shape).clone()
+    out = {}
+    for name, by_ep in per_rank.items():
+        ranks = sorted(by_ep)
+        m = re.search(r"deepspeed_experts\.(\d+)\.", name)
+        if m is None:  # stacked experts: local slices along dim 0
+            out[name] = torch.cat([by_ep[r] for r in ranks], dim=0) if len(ranks) > 1 else by_ep[ranks[0]]
+        else:
+            prefix = name[:m.start()]
+            n_local = 1 + max(int(mm.group(1)) for nm in per_rank
+                              for mm in [re.search(r"deepspeed_experts\.(\d+)\.", nm)]
+                              if mm is not None and nm.startswith(prefix))
+            for r in ranks:
+                gid = r * n_local + int(m.group(1))
+                out[name[:m.start(1)] + str(gid) + name[m.end(1):]] = by_ep[r]
+    return out
+
+
 def get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir, tag=None, exclude_frozen_parameters=False,
                                              lazy_mode=False):
     """Return the consolidated fp32 state dict (parameters + buffers + shared-parameter aliases)."""
     ds_dir = _resolve_tag(checkpoint_dir, tag)
     optim_files = _files(ds_dir, "*_optim_states.pt")
-    model_files = _files(ds_dir, "*_model_states.pt")
+    model_files = [f for f in _files(ds_dir, "*_model_states.pt")
+                   if "_expert_" not in os.path.basename(f) and not os.path.basename(f).startswith("expert_")]
     optim = [_load(f)[OPTIMIZER_STATE_DICT] for f in optim_files]
     stage = optim[0][ZERO_STAGE]
     world = optim[0][PARTITION_COUNT]
@@ -154,6 +196,7 @@ def get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir, tag=None, exclude_f
         state = _merge_stage3(flats, param_shapes, world)
     else:
         raise ValueError(f"unknown zero stage {stage}")
+    state.update(_merge_expert_units(optim))
     # buffers (restored to fp32), frozen params, shared params
     buffers = {k: v.float() for k, v in model_state["module"].items() if k in set(model_state[BUFFER_NAMES])}
     state.update(buffers)

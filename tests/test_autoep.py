@@ -463,3 +463,36 @@ def _autoep_checkpoint(tmp, zero_stage):
 @pytest.mark.parametrize("zero_stage", [0, 1, 2])
 def test_expert_parallel_checkpoint_roundtrip_and_resume(tmp_path, zero_stage):
     assert all(run_distributed(_autoep_checkpoint, 2, args=(str(tmp_path), zero_stage)))
+
+
+def _autoep_zero_to_fp32(tmp):
+    """zero_to_fp32 puts the experts of all expert-parallel ranks back together (they live in per-rank expert units, not
+    in the data-parallel flats)."""
+    import deepspeed_b200 as ds
+    from deepspeed_b200.checkpoint.zero_to_fp32 import get_fp32_state_dict_from_zero_checkpoint
+    from deepspeed_b200.models.mixtral import MixtralConfig, MixtralForCausalLM
+    torch.manual_seed(0)
+    cfg = MixtralConfig.tiny(dtype=torch.float32, gradient_checkpointing=False, ep_size=2, router_aux_loss_coef=0.0)
+    engine = ds.initialize(model=MixtralForCausalLM(cfg),
+                           config={"train_micro_batch_size_per_gpu": 2,
+                                   "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}},
+                                   "zero_optimization": {"stage": 2}})[0]
+    rank = ds.comm.get_rank()
+    torch.manual_seed(5 + rank)
+    ids = torch.randint(0, 512, (2, 16), device=engine.device)
+    loss = engine(ids, labels=ids)
+    engine.backward(loss)
+    engine.step()
+    engine.save_checkpoint(tmp, tag="t")
+    mine = {k: v.clone() for k, v in engine.module.state_dict().items()}
+    ds.comm.barrier()
+    full = get_fp32_state_dict_from_zero_checkpoint(tmp, tag="t")
+    k = "layers.1.block_sparse_moe.experts.w2"
+    assert full[k].shape[0] == 4 and torch.equal(full[k][rank * 2:(rank + 1) * 2], mine[k])
+    dense = [n for n in mine if "experts" not in n and mine[n].dim() == 2][0]
+    torch.testing.assert_close(full[dense], mine[dense])
+    return True
+
+
+def test_zero_to_fp32_reassembles_expert_parallel_weights(tmp_path):
+    assert all(run_distributed(_autoep_zero_to_fp32, 2, args=(str(tmp_path), )))
