@@ -25,6 +25,8 @@ import torch
 
 UNIVERSAL_CHECKPOINT_INFO = "universal_checkpoint_info"
 PARAM = "param"
+EP_IS_EXPERT_PARAM = "is_expert_param"
+EP_NUM_EXPERTS = "ep_num_experts"
 CAT_DIM = "cat_dim"
 VOCAB_TENSOR = "vocab_tensor"
 PARAM_N_SUB_PARAMS = "param_n_sub_params"
@@ -74,7 +76,9 @@ def _rank_files(folder):
         m = re.search(r"zero_pp_rank_(\d+)_mp_rank_(\d+)_optim_states", os.path.basename(f))
         by_tp.setdefault(int(m.group(2)), {})[int(m.group(1))] = f
     model = {}
-    for f in glob.glob(os.path.join(folder, "*mp_rank_*_model_states.pt")):
+    for f in sorted(glob.glob(os.path.join(folder, "*mp_rank_*_model_states.pt"))):
+        if "_expert_" in os.path.basename(f) or os.path.basename(f).startswith("expert_"):
+            continue  # per-expert weight files of MoE layers
         m = re.search(r"mp_rank_(\d+)_model_states", os.path.basename(f))
         model.setdefault(int(m.group(1)), f)
     return {tp: [d[k] for k in sorted(d)] for tp, d in by_tp.items()}, model
@@ -245,6 +249,24 @@ def main(args=None):
     else:
         for j in mjobs:
             _merge_param(j)
+    # ---- 2b. expert-parallel parameters: every rank file carries its expert units; put the experts of all
+    # expert-parallel ranks together so the result loads at any expert-parallel degree (reference autoep_universal.py)
+    from .zero_to_fp32 import _merge_expert_units
+    all_optim = [_load(f)["optimizer_state_dict"] for tp in sorted(optim_by_tp) for f in optim_by_tp[tp]]
+    n_expert = 0
+    for state in ("fp32", "exp_avg", "exp_avg_sq"):
+        for name, tensor in _merge_expert_units(all_optim, key=state).items():
+            os.makedirs(os.path.join(out_zero, name), exist_ok=True)
+            torch.save({PARAM: tensor.clone(), EP_IS_EXPERT_PARAM: True, EP_NUM_EXPERTS: int(tensor.shape[0])},
+                       os.path.join(out_zero, name, f"{state}.pt"))
+            if state == "fp32":
+                n_expert += 1
+                base0 = all_optim[0].get("base_optimizer_state") or all_optim[0].get("optimizer_state_dict") or {}
+                step = next((st["step"] for st in (base0.get("state") or {}).values() if "step" in st), None)
+                if step is not None:
+                    torch.save(step, os.path.join(out_zero, name, "step.pt"))
+    if n_expert:
+        print(f"*** 2b. Consolidated {n_expert} expert-parallel parameters")
     # ---- 3. optimizer scalars, model states, latest_universal ----
     osd = _load(optim_by_tp[sorted(optim_by_tp)[0]][0])["optimizer_state_dict"]
     base = osd.get("base_optimizer_state") or osd.get("optimizer_state_dict") or {}

@@ -80,6 +80,13 @@ def load_universal_into_engine(engine, load_dir, tag, load_optimizer_states=True
                     if not os.path.exists(path) or (key != "fp32" and not load_optimizer_states):
                         continue
                     ck = torch.load(path, map_location="cpu", weights_only=False)
+                    if isinstance(ck, dict) and ck.get("is_expert_param") and getattr(u, "group_key", "dp") != "dp":
+                        # all experts of the layer: keep this expert-parallel rank's block (any expert-parallel degree
+                        # that divides the expert count loads the same file)
+                        t = ck["param"]
+                        n_local = u.shapes[i][0]
+                        ep_rank = groups._get_expert_parallel_rank(u.group_key) if t.shape[0] != n_local else 0
+                        ck = t[ep_rank * n_local:(ep_rank + 1) * n_local]
                     full = _tp_slice(ck, u.shapes[i], tp_rank, tp_world).reshape(-1).float()
                     if full.numel() != u.numels[i]:
                         raise RuntimeError(f"universal checkpoint tensor {name}/{key} has {full.numel()} elements, "

@@ -496,3 +496,62 @@ def _autoep_zero_to_fp32(tmp):
 
 def test_zero_to_fp32_reassembles_expert_parallel_weights(tmp_path):
     assert all(run_distributed(_autoep_zero_to_fp32, 2, args=(str(tmp_path), )))
+
+
+def _autoep_universal(tmp, phase):
+    """ep=2 ZeRO-1 checkpoint -> ds_to_universal -> resume at ep=1 (and ep=2): weights and Adam moments follow."""
+    import os
+    import deepspeed_b200 as ds
+    from deepspeed_b200.models.mixtral import MixtralConfig, MixtralForCausalLM
+
+    def build(ep, universal=False):
+        torch.manual_seed(0)
+        cfg = MixtralConfig.tiny(dtype=torch.float32, gradient_checkpointing=False, ep_size=ep,
+                                 router_aux_loss_coef=0.0)
+        dcfg = {"train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}},
+                "zero_optimization": {"stage": 1}, "checkpoint": {"load_universal": universal}}
+        return ds.initialize(model=MixtralForCausalLM(cfg), config=dcfg)[0]
+
+    rank = ds.comm.get_rank()
+    if phase == "save":
+        engine = build(2)
+        torch.manual_seed(5 + rank)
+        ids = torch.randint(0, 512, (2, 16), device=engine.device)
+        for _ in range(2):
+            loss = engine(ids, labels=ids)
+            engine.backward(loss)
+            engine.step()
+        engine.save_checkpoint(tmp, tag="t")
+        z = engine.optimizer
+        moments = {}
+        for (skey, a, b, gi, u, v) in z._segments:
+            if u.group_key != "dp":
+                moments[u.names[0]] = z.optimizer.state[v]["exp_avg"].clone()
+        return {k: v.clone() for k, v in engine.module.state_dict().items() if "experts" in k}, moments
+    engine = build(int(phase), universal=True)
+    engine.load_checkpoint(tmp, tag="t_universal")
+    sd = {k: v.clone() for k, v in engine.module.state_dict().items() if "experts" in k}
+    z = engine.optimizer
+    moments = {}
+    for (skey, a, b, gi, u, v) in z._segments:
+        if u.group_key != "dp":
+            moments[u.names[0]] = z.optimizer.state[v]["exp_avg"].clone()
+    return sd, moments
+
+
+def test_universal_checkpoint_reshards_experts(tmp_path):
+    from deepspeed_b200.checkpoint import ds_to_universal
+    saved = run_distributed(_autoep_universal, 2, args=(str(tmp_path), "save"))
+    args = ds_to_universal.parse_arguments(["--input_folder", str(tmp_path / "t"), "--output_folder",
+                                            str(tmp_path / "t_universal"), "--num_extract_workers", "1",
+                                            "--num_merge_workers", "1"])
+    ds_to_universal.main(args)
+    k = "layers.0.block_sparse_moe.experts.w13"
+    want_full = torch.cat([saved[0][0][k], saved[1][0][k]], 0)
+    one = run_distributed(_autoep_universal, 1, args=(str(tmp_path), "1"))[0]
+    torch.testing.assert_close(one[0][k], want_full)
+    two = run_distributed(_autoep_universal, 2, args=(str(tmp_path), "2"))
+    for r in range(2):
+        torch.testing.assert_close(two[r][0][k], saved[r][0][k])
+        for name, m in saved[r][1].items():
+            torch.testing.assert_close(two[r][1][name].view(-1), m.view(-1))
