@@ -53,6 +53,8 @@ _ALIASES = {
     "deepspeed.runtime.zero.mics": "deepspeed_b200.runtime.zero.mics",
     "deepspeed.runtime.zero.mics_utils": "deepspeed_b200.runtime.zero.mics",
     "deepspeed.comm.backend": "deepspeed_b200.comm.backend",
+    "deepspeed.comm.utils": "deepspeed_b200.comm.utils",
+    "deepspeed.io.utils": "deepspeed_b200.io.utils",
     "deepspeed.comm.torch": "deepspeed_b200.comm.backend",
     "deepspeed.comm.config": "deepspeed_b200.comm.config",
     "deepspeed.module_inject.fusedqkv_utils": "deepspeed_b200.parallel.fusedqkv_utils",

@@ -93,3 +93,64 @@ def _delegate(name):
 
 for _n in _OPS:
     setattr(TorchBackend, _n, _delegate(_n))
+
+
+# ---- module-level switches and helpers of the reference's ``comm/torch.py`` --------------------------------
+def _switch(op):
+
+    def setter(flag=False):
+        from . import comm as C
+        C.set_comm_off(bool(flag), ops=(op, ))
+
+    setter.__name__ = f"{op}_comm_off"
+    setter.__doc__ = f"Turn the ``{op}`` collectives into no-ops (profiling compute without communication)."
+    return setter
+
+
+def all_gather_comm_off(flag=False):
+    _switch("all_gather")(flag)
+
+
+def reduce_scatter_comm_off(flag=False):
+    _switch("reduce_scatter")(flag)
+
+
+def all_reduce_comm_off(flag=False):
+    _switch("all_reduce")(flag)
+
+
+def reduce_comm_off(flag=False):
+    _switch("all_reduce")(flag)
+    _switch("reduce_scatter")(flag)
+
+
+def broadcast_comm_off(flag=False):
+    _switch("broadcast")(flag)
+
+
+def backward_comm_off(flag=False):
+    """Everything a backward pass communicates: gradient reductions."""
+    all_reduce_comm_off(flag)
+    reduce_scatter_comm_off(flag)
+
+
+def disable_compiler_collective(func):
+    """The reference keeps its collectives out of ``torch.compile`` graphs with this decorator; nothing here is traced,
+    so the function is returned as it is."""
+    return func
+
+
+def build_shm_op():
+    """The shared-memory all-reduce for CPU tensors of a single-host job (``comm/shm.py`` over
+    ``csrc/cpu/shm_comm.cpp``), or ``None`` when the native library is not built."""
+    try:
+        from . import shm
+        return shm
+    except Exception:  # noqa: BLE001
+        return None
+
+
+def get_coalescing_manager(group, device, reqs, async_op=False):
+    """``torch.distributed``'s coalescing context (several collectives issued as one)."""
+    import torch.distributed.distributed_c10d as c10d
+    return c10d._coalescing_manager(group, device=device, async_ops=async_op)
