@@ -85,3 +85,25 @@ def test_tuners_agree_on_small_space(tmp_path):
         t.tune(sample_size=2, n_trials=100, early_stopping=100)
         assert t.best_exp["ds_config"]["train_micro_batch_size_per_gpu"] == 8
         assert t.best_exp["ds_config"]["zero_optimization"]["overlap_comm"] is True
+
+
+def test_autotuning_dict_helpers():
+    from deepspeed_b200.autotuning import utils as U
+    cfg = {"a": "$MBS", "b": ["run_$NAME", 3], "c": {"d": "$NVME_PATH/x", "e": "$GAS"}}
+    U.find_replace(cfg, {"mbs": 4, "name": "exp", "gas": "2"})
+    assert cfg == {"a": 4, "b": ["run_exp", "3"], "c": {"d": "$NVME_PATH/x", "e": "2"}}
+    assert U.combine_dict({"x": 1, "n": {"y": 2}}, {"x": 3, "n": {"y": [2, 5]}, "z": 0}) == \
+        {"x": [1, 3], "n": {"y": [2, 5]}, "z": 0}
+    d = {"zero_optimization": {"stage": 3, "offload_optimizer": {"device": "cpu"}}, "k": {"stage": 1}}
+    assert U.get_val_by_key(d, "device") == "cpu" and U.get_val_by_key(d, "nope") is None
+    U.set_val_by_key(d, "stage", 2)
+    assert d["zero_optimization"]["stage"] == 2 and d["k"]["stage"] == 2
+    assert not U.validate_ds_config({"zero_optimization": {"stage": 3, "offload_param": {"device": "nvme"}}})
+    assert U.validate_ds_config({"zero_optimization": {"stage": 3, "offload_param": {"device": "nvme"}},
+                                 "optimizer": {"type": "Adam"}})
+    assert not U.validate_ds_config({"zero_optimization": {"stage": 2, "cpu_offload": True, "cpu_offload_params": True}})
+    cs = [{"a": 1, "t": {"x": 1}}, {"a": 1, "t": {"x": 2}}, {"a": 2, "t": {"x": 1}}]
+    assert U.prune_configs(cs, ["x"]) == [{"a": 1, "t": {}}, {"a": 2, "t": {}}]
+    assert sorted(U.get_tuning_keys({"mbs": [1, 2], "z": {"stage": [1, 2, 3], "bucket": [5]}, "gas": 1})) == \
+        ["mbs", "stage"]
+    assert U.was_interrupted is U.was_interruptted
