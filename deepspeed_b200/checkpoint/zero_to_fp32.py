@@ -113,7 +113,47 @@ def _merge_stage12(fp32_groups_per_rank, param_shapes, world):
     return out
 
 
-def _merge_stage3(flat_per_rank, param_shapes, world):
+def zero3_partitioned_param_info(unpartitioned_numel, world_size):
+    """(elements per rank, padding added to the last rank) of a ZeRO-3 parameter."""
+    remainder = unpartitioned_numel % world_size
+    return _cdiv(unpartitioned_numel, world_size), (world_size - remainder) if remainder else 0
+
+
+class GatheredTensor:
+    """A parameter of a ZeRO-3 checkpoint that is put together only when asked for (reference
+    ``utils/zero_to_fp32.py:421``): it remembers where its pieces sit in the ranks' flat buffers. With ``lazy_mode`` the
+    state dict holds these instead of tensors, so a conversion keeps one parameter in memory at a time."""
+
+    def __init__(self, flat_per_rank, offset, per_rank_numel, shape):
+        self.flat_per_rank, self.offset, self.per, self.shape = flat_per_rank, offset, per_rank_numel, torch.Size(shape)
+        self.dtype = flat_per_rank[0].dtype
+
+    def numel(self):
+        return self.shape.numel()
+
+    def contiguous(self):
+        parts = [f.narrow(0, self.offset, self.per) for f in self.flat_per_rank]
+        return torch.cat(parts, 0).narrow(0, 0, self.numel()).view(self.shape).clone()
+
+
+def to_torch_tensor(state_dict, return_empty_tensor=False):
+    """Materialise the :class:`GatheredTensor` entries of a lazily built state dict (``return_empty_tensor``: only
+    shapes and dtypes, for planning the shards)."""
+    out = OrderedDict()
+    seen = {}
+    for name, t in state_dict.items():
+        if isinstance(t, GatheredTensor):
+            if id(t) in seen:
+                out[name] = out[seen[id(t)]]  # shared parameters stay shared
+                continue
+            seen[id(t)] = name
+            out[name] = torch.empty(t.shape, dtype=t.dtype) if return_empty_tensor else t.contiguous()
+        else:
+            out[name] = t
+    return out
+
+
+def _merge_stage3(flat_per_rank, param_shapes, world, lazy=False):
     """flat_per_rank[rank] = concatenation of all sub-group flats of that rank."""
     out = OrderedDict()
     shapes = OrderedDict()
@@ -122,9 +162,9 @@ def _merge_stage3(flat_per_rank, param_shapes, world):
     off = 0
     for name, shape in shapes.items():
         n = int(torch.Size(shape).numel())
-        per = _cdiv(n, world)
-        parts = [flat_per_rank[r].narrow(0, off, per) for r in range(world)]
-        out[name] = torch.cat(parts, 0).narrow(0, 0, n).view(shape).clone()
+        per, _ = zero3_partitioned_param_info(n, world)
+        g = GatheredTensor(flat_per_rank, off, per, shape)
+        out[name] = g if lazy else g.contiguous()
         off += per
     return out
 
@@ -170,6 +210,32 @@ def _merge_expert_units(optim_states, key="fp32"):
     return out
 
 
+def get_checkpoint_files(checkpoint_dir, glob_pattern):
+    files = _files(checkpoint_dir, glob_pattern)
+    if not files:
+        raise FileNotFoundError(f"can't find {glob_pattern} files in directory '{checkpoint_dir}'")
+    return files
+
+
+def get_optim_files(checkpoint_dir):
+    return get_checkpoint_files(checkpoint_dir, "*_optim_states.pt")
+
+
+def get_model_state_files(checkpoint_dir):
+    return [f for f in get_checkpoint_files(checkpoint_dir, "*_model_states.pt")
+            if "_expert_" not in os.path.basename(f) and not os.path.basename(f).startswith("expert_")]
+
+
+def get_model_state_file(checkpoint_dir, zero_stage):
+    if not os.path.isdir(checkpoint_dir):
+        raise FileNotFoundError(f"Directory '{checkpoint_dir}' doesn't exist")
+    name = "mp_rank_00_model_states.pt" if zero_stage <= 2 else "zero_pp_rank_0_mp_rank_00_model_states.pt"
+    path = os.path.join(checkpoint_dir, name)
+    if not os.path.exists(path):
+        raise FileNotFoundError(f"can't find model states file at '{path}'")
+    return path
+
+
 def get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir, tag=None, exclude_frozen_parameters=False,
                                              lazy_mode=False):
     """Return the consolidated fp32 state dict (parameters + buffers + shared-parameter aliases)."""
@@ -193,7 +259,7 @@ def get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir, tag=None, exclude_f
         state = _merge_stage12(groups, param_shapes, world)
     elif stage == 3:
         flats = [torch.cat([t.float().reshape(-1) for t in o[FP32_FLAT_GROUPS]], 0) for o in optim]
-        state = _merge_stage3(flats, param_shapes, world)
+        state = _merge_stage3(flats, param_shapes, world, lazy=lazy_mode)
     else:
         raise ValueError(f"unknown zero stage {stage}")
     state.update(_merge_expert_units(optim))
@@ -228,16 +294,17 @@ def _parse_size(s):
 def convert_zero_checkpoint_to_fp32_state_dict(checkpoint_dir, output_dir, max_shard_size="5GB",
                                                safe_serialization=False, tag=None, exclude_frozen_parameters=False):
     """Write the consolidated weights as (sharded) ``pytorch_model*.bin`` or ``model*.safetensors`` + index json."""
-    state = get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir, tag, exclude_frozen_parameters)
+    # lazily gathered (ZeRO-3): a parameter is put together when its shard is written, one shard in memory at a time
+    state = get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir, tag, exclude_frozen_parameters, lazy_mode=True)
     if output_dir.endswith((".bin", ".pt")):
         os.makedirs(os.path.dirname(os.path.abspath(output_dir)), exist_ok=True)
-        torch.save(state, output_dir)
+        torch.save(to_torch_tensor(state), output_dir)
         return
     os.makedirs(output_dir, exist_ok=True)
     limit = _parse_size(max_shard_size)
     shards, cur, cur_bytes = [], OrderedDict(), 0
     for k, v in state.items():
-        nb = v.numel() * v.element_size()
+        nb = v.numel() * (4 if isinstance(v, GatheredTensor) else v.element_size())
         if cur and cur_bytes + nb > limit:
             shards.append(cur)
             cur, cur_bytes = OrderedDict(), 0
@@ -246,8 +313,10 @@ def convert_zero_checkpoint_to_fp32_state_dict(checkpoint_dir, output_dir, max_s
     if cur:
         shards.append(cur)
     base, ext = ("model", ".safetensors") if safe_serialization else ("pytorch_model", ".bin")
-    index = {"metadata": {"total_size": sum(v.numel() * v.element_size() for v in state.values())}, "weight_map": {}}
+    index = {"metadata": {"total_size": sum(v.numel() * (4 if isinstance(v, GatheredTensor) else v.element_size())
+                                           for v in state.values())}, "weight_map": {}}
     for i, sh in enumerate(shards):
+        sh = to_torch_tensor(sh)
         name = f"{base}{ext}" if len(shards) == 1 else f"{base}-{i + 1:05d}-of-{len(shards):05d}{ext}"
         path = os.path.join(output_dir, name)
         if safe_serialization:

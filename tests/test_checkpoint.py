@@ -199,3 +199,28 @@ def test_zero3_frozen_params_roundtrip(tmp_path):
                 ref_sd.update(torch.load(os.path.join(out2, f), weights_only=False))
         for n in want:
             torch.testing.assert_close(ref_sd[n].float(), want[n], rtol=0, atol=1e-6)
+
+
+def test_zero_to_fp32_lazy_gathered_tensors_and_file_helpers(tmp_path):
+    import torch
+    from deepspeed_b200.checkpoint import zero_to_fp32 as Z
+    flats = [torch.arange(0, 10).float(), torch.arange(100, 110).float()]  # two ranks' flat buffers
+    g = Z.GatheredTensor(flats, offset=2, per_rank_numel=3, shape=(5, ))
+    assert g.numel() == 5 and g.contiguous().tolist() == [2.0, 3.0, 4.0, 102.0, 103.0]
+    assert Z.zero3_partitioned_param_info(5, 2) == (3, 1) and Z.zero3_partitioned_param_info(6, 2) == (3, 0)
+    lazy = Z._merge_stage3(flats, [{"a": torch.Size([5]), "b": torch.Size([2, 2])}], 2, lazy=True)
+    assert isinstance(lazy["a"], Z.GatheredTensor)
+    lazy["alias"] = lazy["a"]
+    eager = Z.to_torch_tensor(lazy)
+    assert eager["a"].tolist() == [0.0, 1.0, 2.0, 100.0, 101.0] and eager["b"].tolist() == [[3.0, 4.0], [103.0, 104.0]]
+    assert eager["alias"] is eager["a"]
+    assert Z.to_torch_tensor(lazy, return_empty_tensor=True)["b"].shape == (2, 2)
+    (tmp_path / "mp_rank_00_model_states.pt").write_bytes(b"x")
+    (tmp_path / "layer_0_expert_1_mp_rank_00_model_states.pt").write_bytes(b"x")
+    assert [os.path.basename(f) for f in Z.get_model_state_files(str(tmp_path))] == ["mp_rank_00_model_states.pt"]
+    assert Z.get_model_state_file(str(tmp_path), 2).endswith("mp_rank_00_model_states.pt")
+    import pytest
+    with pytest.raises(FileNotFoundError):
+        Z.get_optim_files(str(tmp_path))
+    with pytest.raises(FileNotFoundError):
+        Z.get_model_state_file(str(tmp_path), 3)
