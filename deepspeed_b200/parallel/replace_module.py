@@ -292,3 +292,75 @@ def generic_injection(module, dtype=None, enable_cuda_graph=True):
     except Exception:  # noqa: BLE001
         pass
     return module
+
+
+# ---- generic class-keyed replacement (reference ``replace_module.py:630`` / ``module_quantize.py:57``) -----------
+def _swap_children(model, policy, state_dict=None, prefix="", counter=None):
+    """Depth-first: a child whose class is a key of ``policy`` is replaced by ``fn(child, policy_cls, layer_id[,
+    prefix, state_dict])``; other children are searched. Returns the number of replacements."""
+    counter = counter if counter is not None else [0]
+    for name, child in list(model.named_children()):
+        entry = policy.get(child.__class__)
+        if entry is not None:
+            fn, pol = entry if isinstance(entry, tuple) else (entry, None)
+            try:
+                new = fn(child, pol, counter[0], prefix=prefix + name, state_dict=state_dict)
+            except TypeError:
+                new = fn(child, pol, counter[0]) if pol is not None else fn(child)
+            setattr(model, name, new)
+            counter[0] += 1
+        else:
+            _swap_children(child, policy, state_dict, prefix + name + ".", counter)
+    return counter[0]
+
+
+def replace_module(model, orig_class, replace_fn, _replace_policy, checkpoint=None):
+    """Replace every instance of ``orig_class`` (or, with ``orig_class=None``, of the classes the registered policies
+    name) using ``replace_fn(child, policy, layer_id)``. ``checkpoint``: a ``.pt`` / ``.safetensors`` file whose state
+    dict is handed to ``replace_fn`` when it accepts ``state_dict``."""
+    sd = None
+    if checkpoint is not None:
+        if checkpoint.endswith(".safetensors"):
+            from safetensors.torch import load_file
+            sd = load_file(checkpoint)
+        else:
+            sd = torch.load(checkpoint, map_location="cpu", weights_only=False)
+    policy = {}
+    if orig_class is not None:
+        policy[orig_class] = (replace_fn, _replace_policy)
+    else:
+        for pol in (HFBertLayerPolicy, ):
+            cls = getattr(pol, "_orig_layer_class", None)
+            for c in (cls if isinstance(cls, (list, tuple)) else [cls]):
+                if c is not None:
+                    policy[c] = (replace_fn, pol)
+    assert policy, ("No default policy found! Please specify your policy injection_policy (like "
+                    "{BertLayer: HFBertLayerPolicy}).")
+    _swap_children(model, policy, state_dict=sd)
+    return model
+
+
+def quantize_module(model, orig_class, quantize_fn):
+    """Replace every ``orig_class`` child by ``quantize_fn(child)``."""
+    _swap_children(model, {orig_class: quantize_fn})
+    return model
+
+
+def skip_level_0_prefix(model, state_dict):
+    """Bloom / OPT checkpoints name their weights without the top-level module prefix - unless the keys say
+    otherwise (``model.`` prefix present)."""
+    import re
+    text = str(model)
+    m = re.search(r": (.*?)Model", text) or re.search(r": (.*?)Stack", text) or re.match(r"(.*?)Model", text)
+    if state_dict is not None and any(re.match(r"^model[.]", k) for k in state_dict):
+        return False
+    return m is not None and m.group(1).lower() in ("bloom", "opt")
+
+
+def get_transformer_name(replaced_module):
+    """Dotted path of the ``ModuleList`` holding the transformer layers (``"transformer.h"``, ``"model.layers"``)."""
+    for n, c in replaced_module.named_children():
+        for name, child in c.named_children():
+            if isinstance(child, nn.ModuleList):
+                return f"{n}.{name}"
+    return ""

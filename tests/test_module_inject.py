@@ -165,3 +165,52 @@ def test_top_level_reference_names():
     from deepspeed_b200.runtime.zero import ZeroShardedOptimizer
     assert issubclass(ZeroShardedOptimizer, ZeROOptimizer) and issubclass(ZeROOptimizer, ds.DeepSpeedOptimizer)
     assert ds.is_compile_supported()
+
+
+def test_generic_class_keyed_replacement(tmp_path):
+    import torch
+    import torch.nn as nn
+    from deepspeed_b200.parallel.replace_module import (get_transformer_name, quantize_module, replace_module,
+                                                        skip_level_0_prefix)
+
+    class Block(nn.Module):
+
+        def __init__(self):
+            super().__init__()
+            self.fc = nn.Linear(4, 4)
+
+    class GPTModel(nn.Module):
+
+        def __init__(self):
+            super().__init__()
+            self.transformer = nn.Module()
+            self.transformer.h = nn.ModuleList([Block(), Block()])
+            self.head = nn.Linear(4, 4)
+
+    m = GPTModel()
+    seen = []
+
+    def fn(child, policy, layer_id):
+        seen.append((policy, layer_id))
+        return nn.Identity()
+
+    replace_module(m, Block, fn, "mypolicy")
+    assert seen == [("mypolicy", 0), ("mypolicy", 1)] and isinstance(m.transformer.h[1], nn.Identity)
+    torch.save({"k": torch.ones(1)}, tmp_path / "ck.pt")
+    got = {}
+
+    def fn2(child, policy, layer_id, prefix="", state_dict=None):
+        got[prefix] = state_dict["k"].item()
+        return child
+
+    replace_module(m, nn.Linear, fn2, None, checkpoint=str(tmp_path / "ck.pt"))
+    assert got == {"head": 1.0}
+    quantize_module(m, nn.Linear, lambda lin: nn.ReLU())
+    assert isinstance(m.head, nn.ReLU)
+    assert get_transformer_name(GPTModel()) == "transformer.h"
+
+    class BloomModel(nn.Module):
+        pass
+
+    assert skip_level_0_prefix(BloomModel(), {"h.0.w": 1}) and not skip_level_0_prefix(BloomModel(), {"model.h": 1})
+    assert not skip_level_0_prefix(GPTModel(), None)
