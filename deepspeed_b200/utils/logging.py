@@ -31,6 +31,31 @@ def _build_logger(name="DeepSpeedB200", level=logging.INFO):
     return lg
 
 
+class LoggerFactory:
+    """Reference ``utils/logging.py:22``: named stdout loggers with the framework's line format."""
+
+    @staticmethod
+    def create_logger(name=None, level=logging.WARNING):
+        if name is None:
+            raise ValueError("name for logger cannot be None")
+        return _build_logger(name, level)
+
+
+def get_log_level_from_string(log_level_str):
+    key = str(log_level_str).lower()
+    if key not in LOG_LEVELS:
+        raise ValueError(f"{log_level_str} is not a valid log level. Valid log levels are {list(LOG_LEVELS)}.")
+    return LOG_LEVELS[key]
+
+
+def should_log_le(max_log_level_str):
+    """True when the framework logger's level is at or below the named one (``should_log_le("info")``: info output
+    is on)."""
+    if not isinstance(max_log_level_str, str):
+        raise ValueError(f"{max_log_level_str} is not a string")
+    return logger.getEffectiveLevel() <= get_log_level_from_string(max_log_level_str)
+
+
 logger = _build_logger(level=LOG_LEVELS.get(os.environ.get("DS_LOG_LEVEL", "info").lower(), logging.INFO))
 
 

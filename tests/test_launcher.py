@@ -59,3 +59,28 @@ def test_single_node_launch_runs_and_propagates_failure(tmp_path):
     bad.write_text("import os, sys, time\nif os.environ['RANK']=='1': sys.exit(3)\ntime.sleep(30)\n")
     rc = subprocess.call([sys.executable, "-m", "deepspeed_b200.launcher.launch", f"--world_info={wi}", str(bad)], env=env)
     assert rc == 3
+
+
+def test_elasticity_config_object_and_logger_factory():
+    import logging
+    import pytest
+    from deepspeed_b200.elasticity.config import ElasticityConfig, ElasticityConfigError
+    from deepspeed_b200.utils.logging import LoggerFactory, get_log_level_from_string, should_log_le
+    c = ElasticityConfig({"enabled": True, "max_train_batch_size": 2000, "micro_batch_sizes": [2, 4, 6], "min_gpus": 2})
+    assert (c.max_acceptable_batch_size, c.micro_batches, c.min_gpus, c.max_gpus, c.version) == (2000, [2, 4, 6], 2,
+                                                                                                   10000, 0.2)
+    assert '"min_gpus": 2' in repr(c) and c.repr()["enabled"] is True
+    assert ElasticityConfig({}).micro_batches == [2, 4, 6]
+    for bad in ({"enabled": True}, {"enabled": True, "max_train_batch_size": 8},
+                {"micro_batch_sizes": 4}, {"micro_batch_sizes": [2, -1]}, {"micro_batch_sizes": [2.5]},
+                {"min_gpus": 0}, {"min_gpus": 8, "max_gpus": 4}, {"model_parallel_size": 0}, {"min_time": -1},
+                {"num_gpus_per_node": 0}):
+        with pytest.raises(ElasticityConfigError):
+            ElasticityConfig(bad)
+    lg = LoggerFactory.create_logger("dsb200-test", logging.ERROR)
+    assert lg.level == logging.ERROR and lg.handlers and not lg.propagate
+    with pytest.raises(ValueError):
+        LoggerFactory.create_logger()
+    assert get_log_level_from_string("Warning") == logging.WARNING and isinstance(should_log_le("debug"), bool)
+    with pytest.raises(ValueError):
+        get_log_level_from_string("loud")
