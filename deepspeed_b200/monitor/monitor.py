@@ -64,6 +64,22 @@ class WandbMonitor(Monitor):
                 self._wandb.log({name: value}, step=step)
 
 
+class EventsLogScheduler:
+    """Rate limit per event name: an event is written when at least ``samples_log_interval`` samples have passed since
+    it was last written (reference ``monitor/comet.py:74``)."""
+
+    def __init__(self, samples_log_interval):
+        self._interval = samples_log_interval
+        self._last = {}
+
+    def needs_logging(self, name, current_sample):
+        last = self._last.get(name)
+        if last is None or current_sample - last >= self._interval:
+            self._last[name] = current_sample
+            return True
+        return False
+
+
 class CometMonitor(Monitor):
 
     def __init__(self, cfg):
@@ -83,8 +99,11 @@ class CometMonitor(Monitor):
 
     def write_events(self, event_list):
         if self.enabled and self._exp is not None:
+            if getattr(self, "_sched", None) is None:
+                self._sched = EventsLogScheduler(int(getattr(self.cfg, "samples_log_interval", 0) or 0))
             for name, value, step in event_list:
-                self._exp.log_metric(name, value, step=step)
+                if self._sched.needs_logging(name, step):
+                    self._exp.log_metric(name, value, step=step)
 
 
 class csvMonitor(Monitor):

@@ -84,3 +84,24 @@ def test_elasticity_config_object_and_logger_factory():
     assert get_log_level_from_string("Warning") == logging.WARNING and isinstance(should_log_le("debug"), bool)
     with pytest.raises(ValueError):
         get_log_level_from_string("loud")
+
+
+def test_comet_events_are_rate_limited():
+    from deepspeed_b200.monitor.monitor import CometMonitor, EventsLogScheduler
+    s = EventsLogScheduler(100)
+    assert [s.needs_logging("loss", x) for x in (0, 50, 100, 150, 220)] == [True, False, True, False, True]
+    assert s.needs_logging("lr", 10)
+
+    class Exp:
+        logged = []
+
+        def log_metric(self, name, value, step=None):
+            Exp.logged.append((name, step))
+
+    class Cfg:
+        enabled, samples_log_interval = False, 10
+
+    m = CometMonitor(Cfg())
+    m.enabled, m._exp = True, Exp()
+    m.write_events([("loss", 1.0, 0), ("loss", 1.0, 5), ("loss", 1.0, 12)])
+    assert Exp.logged == [("loss", 0), ("loss", 12)]
