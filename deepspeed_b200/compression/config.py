@@ -32,7 +32,7 @@ _REQUIRED_GROUP_PARAMS = {
 }
 
 
-def _technique(name, given):
+def _technique(name, given, require_groups=True):
     given = given or {}
     shared = copy.deepcopy(_SHARED_DEFAULTS[name])
     user_shared = given.get(SHARED_PARAMETERS, {})
@@ -65,7 +65,7 @@ def _technique(name, given):
             DIFFERENT_GROUPS_RELATED_MODULE_SCOPE: g.get(DIFFERENT_GROUPS_RELATED_MODULE_SCOPE,
                                                          DIFFERENT_GROUPS_RELATED_MODULE_SCOPE_DEFAULT),
         }
-    if shared["enabled"]:
+    if shared["enabled"] and require_groups:
         assert groups, f"{name} is enabled, {DIFFERENT_GROUPS} must be specified"
     return {SHARED_PARAMETERS: shared, DIFFERENT_GROUPS: groups}
 
@@ -82,3 +82,114 @@ def get_compression_config(param_dict):
     for name in TECHNIQUES:
         out[name] = _technique(name, section.get(name))
     return out
+
+
+# ---- per-technique readers under the reference's names (``compression/config.py:65-452``) -------------------------
+# Each takes the ``compression_training`` section (``get_<technique>``) or one technique's sub-dict
+# (``..._shared_parameters`` / ``..._different_groups``) and returns the normalised dictionaries built above.
+def _whole(name, param_dict):
+    return _technique(name, (param_dict or {}).get(name))
+
+
+def _shared(name, sub_param_dict):
+    given = {SHARED_PARAMETERS: (sub_param_dict or {}).get(SHARED_PARAMETERS, {})}
+    return _technique(name, given, require_groups=False)[SHARED_PARAMETERS]
+
+
+def _groups(name, sub_param_dict):
+    sub = sub_param_dict or {}
+    shared = dict(sub.get(SHARED_PARAMETERS, {}))
+    shared["enabled"] = False  # only the groups are wanted here: no "groups must exist" check
+    if name == HEAD_PRUNING:
+        shared.setdefault("num_heads", 0)
+    return _technique(name, {SHARED_PARAMETERS: shared, DIFFERENT_GROUPS: sub.get(DIFFERENT_GROUPS, {})})[DIFFERENT_GROUPS]
+
+
+def get_weight_quantization(param_dict):
+    return _whole(WEIGHT_QUANTIZATION, param_dict)
+
+
+def get_weight_quantization_shared_parameters(param_dict):
+    return _shared(WEIGHT_QUANTIZATION, param_dict)
+
+
+def get_weight_quantization_different_groups(param_dict):
+    return _groups(WEIGHT_QUANTIZATION, param_dict)
+
+
+def get_activation_quantization(param_dict):
+    return _whole(ACTIVATION_QUANTIZATION, param_dict)
+
+
+def get_activation_quantization_shared_parameters(param_dict):
+    return _shared(ACTIVATION_QUANTIZATION, param_dict)
+
+
+def get_activation_quantization_different_groups(param_dict):
+    return _groups(ACTIVATION_QUANTIZATION, param_dict)
+
+
+def get_sparse_pruning(param_dict):
+    return _whole(SPARSE_PRUNING, param_dict)
+
+
+def get_sparse_pruning_shared_parameters(param_dict):
+    return _shared(SPARSE_PRUNING, param_dict)
+
+
+def get_sparse_pruning_different_groups(param_dict):
+    return _groups(SPARSE_PRUNING, param_dict)
+
+
+def get_row_pruning(param_dict):
+    return _whole(ROW_PRUNING, param_dict)
+
+
+def get_row_pruning_shared_parameters(param_dict):
+    return _shared(ROW_PRUNING, param_dict)
+
+
+def get_row_pruning_different_groups(param_dict):
+    return _groups(ROW_PRUNING, param_dict)
+
+
+def get_head_pruning(param_dict):
+    return _whole(HEAD_PRUNING, param_dict)
+
+
+def get_head_pruning_shared_parameters(param_dict):
+    return _shared(HEAD_PRUNING, param_dict)
+
+
+def get_head_pruning_different_groups(param_dict):
+    return _groups(HEAD_PRUNING, param_dict)
+
+
+def get_channel_pruning(param_dict):
+    return _whole(CHANNEL_PRUNING, param_dict)
+
+
+def get_channel_pruning_shared_parameters(param_dict):
+    return _shared(CHANNEL_PRUNING, param_dict)
+
+
+def get_channel_pruning_different_groups(param_dict):
+    return _groups(CHANNEL_PRUNING, param_dict)
+
+
+def get_layer_reduction_enabled(param_dict):
+    return bool(get_layer_reduction(param_dict or {}).get(LAYER_REDUCTION_ENABLED, False))
+
+
+def get_layer_reduction_params(param_dict):
+    lr = get_layer_reduction(param_dict or {})
+    lr.pop(LAYER_REDUCTION_ENABLED, None)
+    return lr if LAYER_REDUCTION in (param_dict or {}) else False
+
+
+def get_quantize_enabled(param_dict):
+    """Weight quantization of the ``compression_training`` section switched on (whole ds_config given)."""
+    section = (param_dict or {}).get(COMPRESSION_TRAINING)
+    if not section:
+        return False
+    return bool(get_weight_quantization_shared_parameters(section.get(WEIGHT_QUANTIZATION, {})).get("enabled", False))

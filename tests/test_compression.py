@@ -149,3 +149,27 @@ def test_layer_reduction_student_init():
     torch.testing.assert_close(student.layer[0].fc1.weight, teacher.layer[1].fc1.weight)
     torch.testing.assert_close(student.layer[1].attn.o.bias, teacher.layer[3].attn.o.bias)
     torch.testing.assert_close(student.emb.weight, teacher.emb.weight)
+
+
+def test_compression_config_getters():
+    from deepspeed_b200.compression import config as C
+    sec = {"weight_quantization": {"shared_parameters": {"enabled": True, "quantize_groups": 4,
+                                                          "fp16_mixed_quantize": {"enabled": True}},
+                                   "different_groups": {"g1": {"params": {"start_bits": 8, "target_bits": 4},
+                                                               "modules": ["attn"]}}},
+           "head_pruning": {"shared_parameters": {"enabled": False}},
+           "layer_reduction": {"enabled": True, "keep_number_layer": 4}}
+    wq = C.get_weight_quantization(sec)
+    assert wq["shared_parameters"]["quantize_groups"] == 4 and wq["shared_parameters"]["fp16_mixed_quantize"] is True
+    assert wq["different_groups"]["g1"]["params"]["quantization_period"] == 1
+    assert wq["different_groups"]["g1"]["modules"] == ["attn"]
+    sh = C.get_weight_quantization_shared_parameters(sec["weight_quantization"])
+    assert sh["enabled"] is True and sh["quantization_type"] == "symmetric"
+    assert list(C.get_weight_quantization_different_groups(sec["weight_quantization"])) == ["g1"]
+    assert C.get_sparse_pruning(sec)["shared_parameters"]["enabled"] is False
+    assert C.get_row_pruning_shared_parameters({})["method"] == "l1"
+    assert C.get_head_pruning_different_groups({}) == {} and C.get_channel_pruning({})["different_groups"] == {}
+    assert C.get_activation_quantization_shared_parameters({})["range_calibration"] == "dynamic"
+    assert C.get_layer_reduction_enabled(sec) and C.get_layer_reduction_params(sec) == {"keep_number_layer": 4}
+    assert C.get_layer_reduction_params({}) is False
+    assert C.get_quantize_enabled({"compression_training": sec}) and not C.get_quantize_enabled({})
