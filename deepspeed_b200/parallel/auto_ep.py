@@ -217,6 +217,82 @@ class GroupedExperts(nn.Module):
         return grouped_mm(h, self.w2, counts)
 
 
+class SplitPlan(NamedTuple):
+    """What one rank sends / receives in the expert dispatch (reference ``auto_ep_layer.py:41``)."""
+    input_splits: list  # rows sent to every expert-parallel rank
+    output_splits: list  # rows received from every rank
+    local_counts: list  # rows per local expert after regrouping
+    perm: torch.Tensor  # received row order -> expert-contiguous order
+
+
+def count_tokens_per_expert(selected_experts, num_experts):
+    """Assignments per expert (reference ``moe/ep_count.py``)."""
+    return torch.bincount(selected_experts.reshape(-1), minlength=num_experts)
+
+
+def compute_split_plan(counts, ep_group, ep_size, num_local_experts):
+    """Exchange the per-expert counts so that every rank knows what it receives (one host read, as in the
+    reference; the fused NVLink dispatch of ``moe/fused_dispatch.py`` avoids it)."""
+    recv_counts = torch.empty_like(counts)
+    dist.all_to_all_single(recv_counts, counts, group=ep_group)
+    c_send = counts.view(ep_size, num_local_experts)
+    c_recv = recv_counts.view(ep_size, num_local_experts)
+    c_recv_l = c_recv.tolist()
+    # received rows are grouped by source rank then by local expert -> regroup by local expert
+    seg, offs = [], 0
+    for r in range(ep_size):
+        for e in range(num_local_experts):
+            seg.append((e, r, offs, c_recv_l[r][e]))
+            offs += c_recv_l[r][e]
+    dev = counts.device
+    perm = torch.cat([torch.arange(o, o + n, device=dev) for (e, r, o, n) in sorted(seg) if n > 0]) \
+        if offs > 0 else torch.empty(0, dtype=torch.long, device=dev)
+    local_counts = [sum(c_recv_l[r][e] for r in range(ep_size)) for e in range(num_local_experts)]
+    return SplitPlan(c_send.sum(dim=1).tolist(), c_recv.sum(dim=1).tolist(), local_counts, perm)
+
+
+def compute_split_plan_from_expert_indices(selected_experts, num_experts, ep_group, ep_size):
+    return compute_split_plan(count_tokens_per_expert(selected_experts, num_experts), ep_group, ep_size,
+                              num_experts // ep_size)
+
+
+def permute_by_local_expert(received, plan):
+    """Rows as they arrived (by source rank, then expert) -> grouped by local expert."""
+    return received.index_select(0, plan.perm)
+
+
+def unpermute_by_local_expert(expert_out, plan):
+    """Inverse of :func:`permute_by_local_expert`."""
+    back = torch.empty_like(expert_out)
+    back.index_copy_(0, plan.perm, expert_out)
+    return back
+
+
+def resolve_score_apply_mode(config_mode, preset_mode):
+    return preset_mode if config_mode in (None, "auto") else config_mode
+
+
+def resolve_combine_impl(combine_impl):
+    """``auto`` and ``weighted_sum`` are the index-add combine of this layer; ``legacy_bmm`` (a dense one-hot batched
+    matmul in the reference) is accepted and served by the same code."""
+    if combine_impl not in ("auto", "weighted_sum", "legacy_bmm"):
+        raise ValueError(f"combine_impl must be one of ('auto', 'weighted_sum', 'legacy_bmm'), got '{combine_impl}'")
+    return "weighted_sum"
+
+
+def apply_scores_before_experts_if_enabled(routed, scores, score_apply):
+    return routed * scores.unsqueeze(1).to(routed.dtype) if score_apply == "pre" else routed
+
+
+def combine_from_routed(routed_out, token_of_row, scores, num_tokens, score_apply="post"):
+    """``out[t] = sum over the rows of token t`` (weighted by the router score unless it was applied before)."""
+    if score_apply == "post":
+        routed_out = routed_out * scores.unsqueeze(1).to(routed_out.dtype)
+    out = routed_out.new_zeros(num_tokens, routed_out.shape[1])
+    out.index_add_(0, token_of_row, routed_out)
+    return out
+
+
 class AutoEPMoELayer(nn.Module):
     """Drop-in MoE block: ``forward(hidden [B,S,H]) -> [B,S,H]`` (or ``(out, router_logits)`` when the block it
     replaces returned that pair).
@@ -287,7 +363,7 @@ class AutoEPMoELayer(nn.Module):
         flat_e = top_i.reshape(-1)
         order = torch.argsort(flat_e, stable=True)              # token-slots sorted by expert
         tok = order // self.top_k
-        counts = torch.bincount(flat_e, minlength=self.num_experts)
+        counts = count_tokens_per_expert(flat_e, self.num_experts)
         if self.ep_size > 1 and self.ep_group is None:
             self.set_deepspeed_parallelism()
         if self.ep_size > 1 and self._use_fused(x):
@@ -301,41 +377,16 @@ class AutoEPMoELayer(nn.Module):
             return FD.fused_combine(expert_out, top_w, comm, plan), r.logits
         routed = x.index_select(0, tok)                         # [T*k, H] expert-sorted
         w = top_w.reshape(-1).index_select(0, order).to(x.dtype)
-        if self.score_apply == "pre":
-            routed = routed * w.unsqueeze(1)
+        routed = apply_scores_before_experts_if_enabled(routed, w, self.score_apply)
         if self.ep_size > 1:
-            # split plan: counts [ep, E_local] exchanged so every rank knows what it receives (one host sync,
-            # same as the reference; the fused NVLink dispatch removes it)
-            recv_counts = torch.empty_like(counts)
-            dist.all_to_all_single(recv_counts, counts, group=self.ep_group)
-            c_send = counts.view(self.ep_size, self.num_local_experts)
-            c_recv = recv_counts.view(self.ep_size, self.num_local_experts)
-            in_splits = c_send.sum(dim=1).tolist()
-            out_splits = c_recv.sum(dim=1).tolist()
-            recv = _AllToAllV.apply(self.ep_group, routed, in_splits, out_splits)
-            # received rows are grouped by source rank then by local expert -> regroup by local expert
-            c_recv_l = c_recv.tolist()
-            offs = 0
-            seg = []
-            for r_ in range(self.ep_size):
-                for e in range(self.num_local_experts):
-                    seg.append((e, r_, offs, c_recv_l[r_][e]))
-                    offs += c_recv_l[r_][e]
-            perm = torch.cat([torch.arange(o, o + n, device=x.device) for (e, r_, o, n) in sorted(seg) if n > 0]) \
-                if offs > 0 else torch.empty(0, dtype=torch.long, device=x.device)
-            local_counts = [sum(c_recv_l[r_][e] for r_ in range(self.ep_size)) for e in range(self.num_local_experts)]
-            expert_in = recv.index_select(0, perm)
-            expert_out = self.experts(expert_in, local_counts)
-            back = torch.empty_like(expert_out)
-            back.index_copy_(0, perm, expert_out)
-            combined = _AllToAllV.apply(self.ep_group, back, out_splits, in_splits)
+            plan = compute_split_plan(counts, self.ep_group, self.ep_size, self.num_local_experts)
+            recv = _AllToAllV.apply(self.ep_group, routed, plan.input_splits, plan.output_splits)
+            expert_out = self.experts(permute_by_local_expert(recv, plan), plan.local_counts)
+            combined = _AllToAllV.apply(self.ep_group, unpermute_by_local_expert(expert_out, plan),
+                                        plan.output_splits, plan.input_splits)
         else:
             combined = self.experts(routed, counts.tolist())
-        if self.score_apply == "post":
-            combined = combined * w.unsqueeze(1)
-        out = torch.zeros_like(x)
-        out.index_add_(0, tok, combined)
-        return out, r.logits
+        return combine_from_routed(combined, tok, w, x.shape[0], self.score_apply), r.logits
 
     def forward(self, hidden_states):
         shape = hidden_states.shape
