@@ -237,18 +237,57 @@ def compute_split_plan(counts, ep_group, ep_size, num_local_experts):
     dist.all_to_all_single(recv_counts, counts, group=ep_group)
     c_send = counts.view(ep_size, num_local_experts)
     c_recv = recv_counts.view(ep_size, num_local_experts)
-    c_recv_l = c_recv.tolist()
-    # received rows are grouped by source rank then by local expert -> regroup by local expert
-    seg, offs = [], 0
-    for r in range(ep_size):
-        for e in range(num_local_experts):
-            seg.append((e, r, offs, c_recv_l[r][e]))
-            offs += c_recv_l[r][e]
+    out_splits = c_recv.sum(dim=1).tolist()  # the one host read: all-to-all-v needs the sizes on the host
+    local_counts = c_recv.sum(dim=0).tolist()
+    # received rows are grouped by source rank then by local expert -> regroup by local expert (index math on the device)
+    perm = regroup_indices(c_recv, sum(out_splits))
+    return SplitPlan(c_send.sum(dim=1).tolist(), out_splits, local_counts, perm)
+
+
+def regroup_indices(counts_rank_expert, total=None):
+    """For rows laid out ``[rank][local expert]`` with the given counts ``[ranks, experts]``: the gather index that
+    lists them ``[local expert][rank]`` (expert-contiguous). Vectorised - no loop over the segments."""
+    R, E = counts_rank_expert.shape
+    flat = counts_rank_expert.reshape(-1).long()
+    src_start = (torch.cumsum(flat, 0) - flat).view(R, E).t().reshape(-1)  # start of segment (r, e), listed (e, r)
+    by_expert = counts_rank_expert.t().reshape(-1).long()
+    dst_start = torch.cumsum(by_expert, 0) - by_expert
+    total = int(flat.sum()) if total is None else int(total)
+    if total == 0:
+        return torch.empty(0, dtype=torch.long, device=counts_rank_expert.device)
+    seg = torch.repeat_interleave(torch.arange(R * E, device=flat.device), by_expert, output_size=total)
+    return src_start[seg] + (torch.arange(total, device=flat.device) - dst_start[seg])
+
+
+def generate_permute_indices(tokens_per_expert_group, experts_per_rank, num_ranks, max_len, alignment, use_cpu=False):
+    """Aligned variant (reference ``moe/ep_kernels.py:190``, a Triton kernel there): every local expert's block is padded
+    to a multiple of ``alignment`` (and at least ``alignment``) so that grouped GEMM tiles never straddle experts.
+    Returns ``(permuted_indices [max_len] with -1 in the padding, m_sizes int32 [experts], m_offsets)``; everything
+    stays on the device."""
+    counts = tokens_per_expert_group.view(num_ranks, experts_per_rank).long()
     dev = counts.device
-    perm = torch.cat([torch.arange(o, o + n, device=dev) for (e, r, o, n) in sorted(seg) if n > 0]) \
-        if offs > 0 else torch.empty(0, dtype=torch.long, device=dev)
-    local_counts = [sum(c_recv_l[r][e] for r in range(ep_size)) for e in range(num_local_experts)]
-    return SplitPlan(c_send.sum(dim=1).tolist(), c_recv.sum(dim=1).tolist(), local_counts, perm)
+    total_per_expert = counts.sum(0).clamp_min(alignment)
+    m_sizes = ((total_per_expert + alignment - 1) // alignment * alignment).to(torch.int32)
+    m_offsets = torch.cumsum(m_sizes, 0)
+    write_start = (m_offsets - m_sizes).long()  # first row of every expert's padded block
+    flat = counts.reshape(-1)
+    src_start = (torch.cumsum(flat, 0) - flat).view(num_ranks, experts_per_rank)
+    by_expert = counts.t()  # [experts, ranks]
+    within_expert = torch.cumsum(by_expert, 1) - by_expert  # offset of rank r's rows inside expert e's block
+    out = torch.full((max_len, ), -1, dtype=torch.int32, device=dev)
+    n = int(flat.sum())
+    if n:
+        seg = torch.repeat_interleave(torch.arange(experts_per_rank * num_ranks, device=dev), by_expert.reshape(-1),
+                                      output_size=n)
+        e, r = seg // num_ranks, seg % num_ranks
+        seg_first = torch.cumsum(by_expert.reshape(-1), 0) - by_expert.reshape(-1)
+        i = torch.arange(n, device=dev) - seg_first[seg]
+        dst = write_start[e] + within_expert[e, r] + i
+        keep = dst < max_len
+        out[dst[keep]] = (src_start[r, e] + i)[keep].to(torch.int32)
+    return out, m_sizes, m_offsets.to(torch.int32)
+
+
 
 
 def compute_split_plan_from_expert_indices(selected_experts, num_experts, ep_group, ep_size):

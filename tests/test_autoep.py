@@ -555,3 +555,32 @@ def test_universal_checkpoint_reshards_experts(tmp_path):
         torch.testing.assert_close(two[r][0][k], saved[r][0][k])
         for name, m in saved[r][1].items():
             torch.testing.assert_close(two[r][1][name].view(-1), m.view(-1))
+
+
+def test_dispatch_index_helpers():
+    from deepspeed_b200.parallel.auto_ep import (combine_from_routed, count_tokens_per_expert, generate_permute_indices,
+                                                 regroup_indices, resolve_combine_impl, resolve_score_apply_mode)
+    torch.manual_seed(0)
+    for _ in range(5):
+        c = torch.randint(0, 5, (3, 4))
+        seg, off = [], 0
+        for r in range(3):
+            for e in range(4):
+                seg.append((e, r, off, int(c[r, e])))
+                off += int(c[r, e])
+        pieces = [torch.arange(o, o + n) for (e, r, o, n) in sorted(seg) if n > 0]
+        want = torch.cat(pieces) if pieces else torch.empty(0, dtype=torch.long)
+        assert torch.equal(regroup_indices(c), want)
+    assert regroup_indices(torch.zeros(2, 2, dtype=torch.long)).numel() == 0
+    c = torch.tensor([[2, 0, 3], [1, 4, 0]])
+    idx, m_sizes, m_offsets = generate_permute_indices(c.reshape(-1), 3, 2, 16, 4)
+    assert m_sizes.tolist() == [4, 4, 4] and m_offsets.tolist() == [4, 8, 12]
+    assert idx.tolist() == [0, 1, 5, -1, 6, 7, 8, 9, 2, 3, 4, -1, -1, -1, -1, -1]
+    assert count_tokens_per_expert(torch.tensor([[0, 2], [2, 3]]), 4).tolist() == [1, 0, 2, 1]
+    out = combine_from_routed(torch.ones(4, 2), torch.tensor([0, 0, 1, 2]), torch.tensor([0.5, 0.25, 1.0, 2.0]), 3)
+    assert out[:, 0].tolist() == [0.75, 1.0, 2.0]
+    assert combine_from_routed(torch.ones(2, 2), torch.tensor([1, 1]), torch.ones(2), 2, "pre")[:, 0].tolist() == [0, 2]
+    assert resolve_score_apply_mode("auto", "post") == "post" and resolve_score_apply_mode("pre", "post") == "pre"
+    assert resolve_combine_impl("legacy_bmm") == "weighted_sum"
+    with pytest.raises(ValueError):
+        resolve_combine_impl("magic")
