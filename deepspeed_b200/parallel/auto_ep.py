@@ -660,6 +660,9 @@ class AutoEP:
             hook_output="topk_tuple" if spec.preset_adapter in ("router_hook", "qwen3_5_moe") and
             spec.router_logits_capture_target == "router" else "logits", tp_group=tp_group)
         self._copy_experts(spec, experts, layer, ep_rank)
+        g13, g2 = repack_expert_requires_grad_flags(experts, spec)
+        layer.experts.w13.requires_grad_(g13)
+        layer.experts.w2.requires_grad_(g2)
         layer.train(block.training)
         layer._autoep_spec = spec
         setattr(parent, leaf, layer)
@@ -679,6 +682,48 @@ class AutoEP:
         log_dist(f"AutoEP: replaced {len(layers)} MoE blocks (ep_size={ep_size}"
                  f"{', folded over TP' if tp_group is not None else ''})", [0])
         return layers
+
+
+def _source_params(experts_source, spec, name):
+    if spec.expert_storage == "module_list":
+        return [_param_of(e, name) for e in experts_source]
+    return [_param_of(experts_source, name)]
+
+
+def repack_expert_requires_grad_flags(experts_source, spec):
+    """(gate/up trainable, down trainable): the stacked tensors are trainable when any of their source weights is."""
+    up = _source_params(experts_source, spec, spec.expert_w1_name)
+    if spec.expert_w3_name is not None:
+        up = up + _source_params(experts_source, spec, spec.expert_w3_name)
+    down = _source_params(experts_source, spec, spec.expert_w2_name)
+    return any(p.requires_grad for p in up), any(p.requires_grad for p in down)
+
+
+def repack_expert_weights(experts_source, spec, ep_rank, ep_size):
+    """This rank's experts in the grouped layout, from either storage of the model (reference ``moe/ep_repack.py:39``):
+    ``(w1 gate [E_local, I, H], w2 down [E_local, H, I], w3 up [E_local, I, H])``."""
+    from ..moe.fused_expert_layout import classify_fused_gate_up_layout
+    nl, inter = spec.num_experts // ep_size, spec.ffn_hidden_size
+    lo = ep_rank * nl
+    if spec.expert_storage == "module_list":
+        pick = lambda name: torch.stack([_param_of(experts_source[lo + i], name).detach() for i in range(nl)])  # noqa: E731
+        return pick(spec.expert_w1_name), pick(spec.expert_w2_name), pick(spec.expert_w3_name)
+    if spec.expert_storage != "fused_3d":
+        raise ValueError(f"Unknown expert_storage type: {spec.expert_storage}")
+    w1 = _param_of(experts_source, spec.expert_w1_name).detach()[lo:lo + nl]
+    w2 = _param_of(experts_source, spec.expert_w2_name).detach()[lo:lo + nl]
+    if spec.expert_w3_name is None:
+        lay = classify_fused_gate_up_layout(tuple(_param_of(experts_source, spec.expert_w1_name).shape),
+                                            tuple(_param_of(experts_source, spec.expert_w2_name).shape))
+        if lay is None:
+            raise ValueError("fused gate/up expert tensors have an unrecognised layout")
+        if lay.needs_transpose:
+            w1, w2 = w1.transpose(1, 2), w2.transpose(1, 2)
+        return w1[:, :inter].contiguous(), w2.contiguous(), w1[:, inter:].contiguous()
+    w3 = _param_of(experts_source, spec.expert_w3_name).detach()[lo:lo + nl]
+    if tuple(w1.shape[1:]) != (inter, spec.hidden_size):
+        w1, w2, w3 = w1.transpose(1, 2), w2.transpose(1, 2), w3.transpose(1, 2)
+    return w1.contiguous(), w2.contiguous(), w3.contiguous()
 
 
 def apply_autoep(model, ep_config, tp_group=None):

@@ -584,3 +584,28 @@ def test_dispatch_index_helpers():
     assert resolve_combine_impl("legacy_bmm") == "weighted_sum"
     with pytest.raises(ValueError):
         resolve_combine_impl("magic")
+
+
+def test_repack_expert_weights_and_frozen_experts():
+    from deepspeed_b200.parallel.auto_ep import repack_expert_requires_grad_flags, repack_expert_weights
+    m = _init(_hf("mixtral"))
+    for p in m.model.layers[0].mlp.experts.parameters():
+        p.requires_grad_(False)
+    auto = AutoEP(m, P.AutoEPConfig(enabled=True))
+    specs = auto.ep_parser()
+    src = m.model.layers[0].mlp.experts
+    w1, w2, w3 = repack_expert_weights(src, specs[0], ep_rank=1, ep_size=2)
+    assert w1.shape == (2, 48, 32) and w2.shape == (2, 32, 48) and w3.shape == (2, 48, 32)
+    torch.testing.assert_close(torch.cat([w1, w3], 1), src.gate_up_proj[2:4])
+    torch.testing.assert_close(w2, src.down_proj[2:4])
+    assert repack_expert_requires_grad_flags(src, specs[0]) == (False, False)
+    layers = auto.replace_moe_layers(specs)
+    assert not layers[0].experts.w13.requires_grad and layers[1].experts.w13.requires_grad
+    blk = _Wrap().block_sparse_moe
+    cfg = P.AutoEPConfig(enabled=True, moe_layer_pattern=r"block_sparse_moe", expert_w1="w1", expert_w2="w2",
+                         expert_w3="w3", top_k=2)
+    w = _Wrap()
+    spec = AutoEP(w, cfg).ep_parser()[0]
+    a, b, c = repack_expert_weights(w.block_sparse_moe.experts, spec, 0, 2)
+    assert a.shape == (2, 24, 16) and torch.equal(c[1], w.block_sparse_moe.experts[1].w3.weight)
+    assert blk is not None
