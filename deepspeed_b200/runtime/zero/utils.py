@@ -148,3 +148,81 @@ def defragment(tensors: List[torch.Tensor]) -> torch.Tensor:
     for t, off, n in infos:
         t.data = flat.narrow(0, off, n)
     return flat
+
+
+# ---- small helpers of the reference's stage_1_and_2.py / stage3.py / partition_parameters.py -----------------------
+def split_half_float_double(tensors):
+    """Tensors bucketed by dtype (fp16, fp32, fp64, bf16 order): one flat collective per bucket."""
+    order = (torch.float16, torch.float32, torch.float64, torch.bfloat16)
+    buckets = [[t for t in tensors if t.dtype == dt] for dt in order]
+    return [b for b in buckets if b]
+
+
+def split_half_float_double_sparse(tensors):
+    """Like :func:`split_half_float_double`, with sparse gradients (``SparseTensor``) in their own buckets first.
+    Returns ``[(dtype, [tensors]), ...]`` (reference ``runtime/engine.py``)."""
+    from ..sparse_tensor import SparseTensor
+    sparse = [t for t in tensors if isinstance(t, SparseTensor)]
+    dense = [t for t in tensors if not isinstance(t, SparseTensor)]
+    out = []
+    if sparse:
+        out.append((SparseTensor.type(), sparse))
+    for dt in (torch.float16, torch.float32, torch.float64, torch.bfloat16):
+        b = [t for t in dense if t.dtype == dt]
+        if b:
+            out.append((dt, b))
+    return out
+
+
+def isclose(a, b, rtol=1e-09, atol=0.0):
+    return abs(a - b) <= max(rtol * max(abs(a), abs(b)), atol)
+
+
+def lcm(x, y):
+    from math import gcd
+    return x * y // gcd(x, y)
+
+
+def get_alignment_padding(tensor_list, alignment):
+    """Elements to append so that the tensors' total count is a multiple of ``alignment``."""
+    rem = sum(t.numel() for t in tensor_list) % alignment
+    return (alignment - rem) if rem else 0
+
+
+def move_to_cpu(tensor_list):
+    for t in tensor_list:
+        t.data = t.data.cpu()
+
+
+def print_rank_msg(msg):
+    from ... import comm as dist
+    print(f"rank {dist.get_rank() if dist.is_initialized() else 0} - {msg}")
+
+
+def get_allgather_dtype(param, param_ds_tensor):
+    """Dtype a parameter travels in: its autocast dtype when torch autocast manages it, else that of its shard."""
+    dt = getattr(param, "autocast_dtype", None) or getattr(param, "ds_autocast_dtype", None)
+    return dt if dt is not None else param_ds_tensor.dtype
+
+
+def get_new_tensor_fn_for_dtype(dtype):
+    """``Tensor.new_tensor`` that casts floating-point results to ``dtype`` (used while ``zero.Init`` is active)."""
+
+    def new_tensor(cls, *args, **kwargs):
+        t = torch.Tensor.new_tensor(cls, *args, **kwargs)
+        return t.to(dtype) if t.is_floating_point() else t
+
+    return new_tensor
+
+
+def zero_wrapper_for_fp_tensor_constructor(fn, target_fp_dtype):
+    """Wrap a tensor constructor (``torch.empty`` ...) so that floating-point tensors come out in ``target_fp_dtype``
+    on the current accelerator unless a device was given."""
+
+    def wrapped(*args, **kwargs):
+        if kwargs.get("device") is None and torch.cuda.is_available():
+            kwargs["device"] = torch.device("cuda", torch.cuda.current_device())
+        t = fn(*args, **kwargs)
+        return t.to(target_fp_dtype) if t.is_floating_point() else t
+
+    return wrapped

@@ -51,3 +51,31 @@ def get_numactl_cmd(bind_core_list, num_local_procs, local_rank):
             cmd += ["-m", str(node_id)]
             break
     return per, cmd
+
+
+def parse_range(rng):
+    """``"3"`` -> ``range(3, 4)``; ``"2-5"`` -> ``range(2, 6)`` (both ends included)."""
+    try:
+        v = int(rng)
+        return range(v, v + 1)
+    except ValueError:
+        parts = rng.split("-")
+        if len(parts) != 2:
+            raise ValueError(f"Bad range: '{rng}', range must be either a number or two number separated by dash")
+        lo, hi = int(parts[0]), int(parts[1])
+        if lo > hi:
+            raise ValueError(f"Bad range: '{rng}', range end must larger than or equal to start")
+        return range(lo, hi + 1)
+
+
+def check_for_numactl_pkg():
+    """True when ``numactl`` is on the PATH; otherwise says how to get it and returns False."""
+    if shutil.which("numactl") is not None:
+        return True
+    for pm, hint in (("apt", "apt install numactl"), ("dnf", "dnf install numactl"), ("yum", "yum install numactl")):
+        if shutil.which(pm) is not None:
+            print(f"numactl is not found; install it with: {hint}")
+            break
+    else:
+        print("numactl is not found on this system")
+    return False

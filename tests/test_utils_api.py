@@ -212,3 +212,35 @@ def _fragments():
 def test_tensor_fragment_views_and_linkage():
     res = run_distributed(_fragments, 2)
     assert all(all(r) for r in res), res
+
+
+def test_small_reference_helpers():
+    import pytest
+    import torch
+    from deepspeed_b200.launcher.launcher_helper import env_mapping
+    from deepspeed_b200.runtime.zero import utils as Z
+    from deepspeed_b200.utils.numa import check_for_numactl_pkg, parse_range
+    env = env_mapping({"PMI_RANK": "3", "OMPI_COMM_WORLD_RANK": "3", "MPI_LOCALRANKID": "1"},
+                      ["PMI_RANK", "OMPI_COMM_WORLD_RANK"], ["MPI_LOCALRANKID", "OMPI_COMM_WORLD_LOCAL_RANK"])
+    assert env["RANK"] == "3" and env["LOCAL_RANK"] == "1"
+    with pytest.raises(EnvironmentError):
+        env_mapping({"A": "1", "B": "2", "L": "0"}, ["A", "B"], ["L"])
+    with pytest.raises(EnvironmentError):
+        env_mapping({"A": "1"}, ["A"], ["L"])
+    assert list(parse_range("4")) == [4] and list(parse_range("2-5")) == [2, 3, 4, 5]
+    for bad in ("5-2", "1-2-3"):
+        with pytest.raises(ValueError):
+            parse_range(bad)
+    assert isinstance(check_for_numactl_pkg(), bool)
+    ts = [torch.zeros(3, dtype=torch.float16), torch.zeros(2), torch.zeros(1, dtype=torch.bfloat16), torch.zeros(4)]
+    b = Z.split_half_float_double(ts)
+    assert [x[0].dtype for x in b] == [torch.float16, torch.float32, torch.bfloat16] and len(b[1]) == 2
+    assert [dt for dt, _ in Z.split_half_float_double_sparse(ts)] == [torch.float16, torch.float32, torch.bfloat16]
+    assert Z.get_alignment_padding(ts, 8) == 6 and Z.get_alignment_padding(ts[:1] + ts[:1] + ts[1:2], 8) == 0
+    assert Z.lcm(4, 6) == 12 and Z.isclose(1.0, 1.0 + 1e-12) and not Z.isclose(1.0, 1.1)
+    mk = Z.zero_wrapper_for_fp_tensor_constructor(torch.ones, torch.bfloat16)
+    assert mk(2).dtype == torch.bfloat16 and mk(2, dtype=torch.int32).dtype == torch.int32
+    p = torch.nn.Parameter(torch.zeros(2))
+    assert Z.get_allgather_dtype(p, torch.zeros(1, dtype=torch.float16)) == torch.float16
+    p.autocast_dtype = torch.bfloat16
+    assert Z.get_allgather_dtype(p, torch.zeros(1, dtype=torch.float16)) == torch.bfloat16
