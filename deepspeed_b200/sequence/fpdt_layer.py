@@ -146,3 +146,26 @@ def FPDT_InputConstruct(tokens, labels, loss_mask, attention_mask, position_ids,
     if position_ids is None:
         position_ids = torch.arange(S, device=tokens.device).unsqueeze(0).expand_as(tokens)
     return pick(tokens), pick(labels), pick(loss_mask), attention_mask, pick(position_ids)
+
+
+# ---- helper functions of the reference module (``sequence/fpdt_layer.py:33, 1115-1124``) ---------------------------
+def apply_rotary_pos_emb_backward(grad_output, freqs_cos, freqs_sin):
+    """Gradient of :func:`deepspeed_b200.sequence.layer.apply_rotary_pos_emb` w.r.t. its input: the adjoint of the
+    half rotation is the rotation by the opposite angle."""
+    rot = freqs_cos.shape[-1]
+    g, rest = grad_output[..., :rot], grad_output[..., rot:]
+    gs = g * freqs_sin
+    g1, g2 = gs[..., :rot // 2], gs[..., rot // 2:]
+    g = g * freqs_cos + torch.cat((g2, -g1), dim=-1)
+    return g if rest.shape[-1] == 0 else torch.cat((g, rest), dim=-1)
+
+
+def bias_gelu(x):
+    """tanh-approximated GELU (the bias is added by the caller)."""
+    return x * 0.5 * (1.0 + torch.tanh(0.79788456 * x * (1 + 0.044715 * x * x)))
+
+
+def bias_gelu_back(g, x):
+    """``g * d/dx bias_gelu(x)``."""
+    t = torch.tanh(0.79788456 * x * (1 + 0.044715 * x * x))
+    return (0.5 * x * ((1 - t * t) * (0.79788456 + 0.1070322243 * x * x)) + 0.5 * (1 + t)) * g

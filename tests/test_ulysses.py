@@ -213,3 +213,24 @@ def test_tiled_loss_and_autograd_compute_mlp_match_plain():
     torch.testing.assert_close(y1, y0)
     for a, b in zip([x.grad] + [p.grad for p in mlp.parameters()], g0):
         torch.testing.assert_close(a, b)
+
+
+def test_fpdt_helper_gradients():
+    import torch
+    from deepspeed_b200.sequence.fpdt_layer import apply_rotary_pos_emb_backward, bias_gelu, bias_gelu_back
+    from deepspeed_b200.sequence.layer import apply_rotary_pos_emb
+    torch.manual_seed(0)
+    x = torch.randn(2, 5, 3, 12, dtype=torch.float64, requires_grad=True)
+    ang = torch.randn(5, 1, 4, dtype=torch.float64)
+    cos, sin = torch.cat([ang.cos(), ang.cos()], -1), torch.cat([ang.sin(), ang.sin()], -1)  # rotate 8 of 12 channels
+    g = torch.randn_like(x)
+    (want, ) = torch.autograd.grad(apply_rotary_pos_emb(x, cos, sin), x, g)
+    torch.testing.assert_close(apply_rotary_pos_emb_backward(g, cos, sin), want)
+    y = torch.randn(7, dtype=torch.float64, requires_grad=True)
+    gy = torch.randn(7, dtype=torch.float64)
+    (w2, ) = torch.autograd.grad(bias_gelu(y), y, gy)
+    torch.testing.assert_close(bias_gelu_back(gy, y.detach()), w2, rtol=1e-6, atol=1e-8)
+    torch.testing.assert_close(bias_gelu(y).detach(), torch.nn.functional.gelu(y.detach(), approximate="tanh"), rtol=1e-6,
+                               atol=1e-7)
+    from deepspeed_b200.monitor import check_comet_availability, check_tb_availability
+    assert isinstance(check_tb_availability(), bool) and isinstance(check_comet_availability(), bool)
