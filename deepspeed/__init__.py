@@ -64,6 +64,9 @@ _ALIASES = {
     "deepspeed.module_inject.tp_plan_converter": "deepspeed_b200.parallel.tp_plan_converter",
     "deepspeed.runtime.tensor_parallel": "deepspeed_b200.runtime.tensor_parallel",
     "deepspeed.runtime.tensor_parallel.tp_manager": "deepspeed_b200.runtime.tensor_parallel.tp_manager",
+    "deepspeed.runtime.tensor_parallel.init_utils": "deepspeed_b200.runtime.tensor_parallel.init_utils",
+    "deepspeed.launcher.launcher_helper": "deepspeed_b200.launcher.launcher_helper",
+    "deepspeed.elasticity.config": "deepspeed_b200.elasticity.config",
     "deepspeed.module_inject.auto_ep": "deepspeed_b200.parallel.auto_ep",
     "deepspeed.module_inject.auto_ep_layer": "deepspeed_b200.parallel.auto_ep",
     "deepspeed.module_inject.auto_ep_config": "deepspeed_b200.parallel.auto_ep_presets",

@@ -306,3 +306,31 @@ def _hf_family_tp2(family):
                                     "falcon_mqa", "phi3", "qwen2", "gemma", "mpt", "codegen"])
 def test_autotp_hf_families_two_ranks(family):
     assert all(run_distributed(_hf_family_tp2, 2, args=(family, )))
+
+
+def test_tp_init_utils(tmp_path):
+    import base64
+    import json
+    import deepspeed_b200 as ds
+    from deepspeed_b200.runtime.tensor_parallel import init_utils as U
+    assert U.infer_config_dtype({"bf16": {"enabled": True}}) is torch.bfloat16
+    assert U.infer_config_dtype({"fp16": {"enabled": True}}) is torch.float16 and U.infer_config_dtype({}) is None
+    p = tmp_path / "c.json"
+    p.write_text('{"train_batch_size": 4}')
+    assert U.load_ds_config(str(p)) == {"train_batch_size": 4} and U.load_ds_config({"a": 1}) == {"a": 1}
+    enc = base64.urlsafe_b64encode(json.dumps({"x": 2}).encode()).decode()
+    assert U.load_ds_config(enc) == {"x": 2}
+    with pytest.raises(ValueError):
+        U.load_ds_config("definitely not a config")
+    saved = ds._TP_MODEL_INIT_ARGS
+    try:
+        ds._TP_MODEL_INIT_ARGS = None
+        U.record_tp_model_init_args(2, torch.bfloat16, None, None)
+        U.record_tp_model_init_args(2, torch.bfloat16, None, None)
+        with pytest.raises(ValueError, match="Conflicting"):
+            U.record_tp_model_init_args(4, torch.bfloat16, None, None)
+        with pytest.raises(ValueError, match="Conflicting"):
+            U.record_tp_model_init_args(2, torch.bfloat16, object(), None)
+    finally:
+        ds._TP_MODEL_INIT_ARGS = saved
+    assert U.tp_group_world_size(None, None) is None
